@@ -1,0 +1,418 @@
+// C ABI (include/b2arrow.h): exception firewall + device memory plumbing around the planner and kernels.
+// There is NO CPU fallback: every b2a_scan_* entry point that needs the device fails with B2A_ECUDA
+// when no CUDA device is usable.
+#include "b2arrow.h"
+#include "ipc/ipc_reader.hpp"
+#include "kernels/decode.cuh"
+#include "scanner/scan_plan.hpp"
+
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <memory>
+#include <string>
+
+using namespace b2a;
+
+static thread_local std::string g_last_error;
+
+struct b2a_reader {
+	Reader reader;
+	std::vector<std::string> meta_keys, meta_vals;
+};
+
+struct b2a_scan {
+	b2a_reader *r = nullptr;
+	ScanPlan plan;
+	int device = 0;
+	int sm_count = 148;
+	b2a_task *d_tasks = nullptr;
+	uint32_t *d_tile_task = nullptr;
+	uint64_t *d_variadic = nullptr;
+	uint32_t *d_err = nullptr;
+	uint8_t *d_image_owned = nullptr;   // allocated by b2a_scan_upload
+	const uint8_t *d_image = nullptr;   // device address of image offset plan.image_lo
+	uint64_t launches = 0;
+	// filter support
+	uint64_t *d_chunk_col = nullptr;
+	uint32_t *d_chunk_rows = nullptr;
+	uint32_t chunk_col_preds = 0;
+	std::vector<uint32_t> chunk_col_key;
+};
+
+static int Fail(int code, const std::string &msg) {
+	g_last_error = msg;
+	return code;
+}
+
+#define B2A_TRY try {
+#define B2A_CATCH                                                                                                      \
+	}                                                                                                                  \
+	catch (const Error &e) {                                                                                           \
+		return Fail(e.code, e.msg);                                                                                    \
+	}                                                                                                                  \
+	catch (const std::bad_alloc &) {                                                                                   \
+		return Fail(B2A_EOOM, "out of host memory");                                                                   \
+	}                                                                                                                  \
+	catch (const std::exception &e) {                                                                                  \
+		return Fail(B2A_EINTERNAL, e.what());                                                                          \
+	}
+
+#define CUDA_OK(expr)                                                                                                  \
+	do {                                                                                                               \
+		cudaError_t _e = (expr);                                                                                       \
+		if (_e != cudaSuccess) {                                                                                       \
+			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " #expr);              \
+		}                                                                                                              \
+	} while (0)
+
+extern "C" {
+
+const char *b2a_version(void) {
+	return "b2arrow 0.1.0 (sm_100a)";
+}
+
+const char *b2a_last_error(void) {
+	return g_last_error.c_str();
+}
+
+int b2a_device_count(int *n) {
+	int c = 0;
+	cudaError_t e = cudaGetDeviceCount(&c);
+	if (e != cudaSuccess) {
+		*n = 0;
+		cudaGetLastError();
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(e));
+	}
+	*n = c;
+	return B2A_OK;
+}
+
+// ------------------------------------------------------------------ reader
+int b2a_reader_open_file(const char *path, b2a_reader **out) {
+	B2A_TRY
+	std::unique_ptr<b2a_reader> r(new b2a_reader());
+	r->reader.OpenFile(path);
+	*out = r.release();
+	return B2A_OK;
+	B2A_CATCH
+}
+
+int b2a_reader_open_buffers(const b2a_ipc_buffer *bufs, uint32_t n, b2a_reader **out) {
+	B2A_TRY
+	std::unique_ptr<b2a_reader> r(new b2a_reader());
+	r->reader.OpenBuffers(bufs, n);
+	*out = r.release();
+	return B2A_OK;
+	B2A_CATCH
+}
+
+void b2a_reader_close(b2a_reader *r) {
+	delete r;
+}
+
+int b2a_reader_num_fields(b2a_reader *r, uint32_t *n_top, uint32_t *n_flat) {
+	B2A_TRY
+	*n_top = static_cast<uint32_t>(r->reader.OutputColumns().size());
+	*n_flat = static_cast<uint32_t>(r->reader.BaseSchema().flat.size());
+	return B2A_OK;
+	B2A_CATCH
+}
+
+static void CopyStr(char *dst, size_t cap, const std::string &s) {
+	size_t n = s.size() < cap - 1 ? s.size() : cap - 1;
+	std::memcpy(dst, s.data(), n);
+	dst[n] = 0;
+}
+
+int b2a_reader_field(b2a_reader *r, uint32_t flat_index, b2a_field_info *out) {
+	B2A_TRY
+	const Schema &s = r->reader.BaseSchema();
+	if (flat_index >= s.flat.size()) {
+		return Fail(B2A_EINVAL, "field index out of range");
+	}
+	const Field &f = *s.flat[flat_index];
+	std::memset(out, 0, sizeof(*out));
+	CopyStr(out->name, sizeof(out->name), f.name);
+	CopyStr(out->format, sizeof(out->format), f.format);
+	out->type_id = f.type_id;
+	out->op = f.op;
+	out->out_width = f.out_width;
+	out->src_width = f.src_width;
+	out->n_children = static_cast<int32_t>(f.children.size());
+	out->first_child = f.children.empty() ? -1 : f.children[0]->flat_index;
+	out->parent = f.parent_flat;
+	out->next_sibling = -1;
+	const std::vector<std::unique_ptr<Field>> *sibs = nullptr;
+	if (f.parent_flat >= 0) {
+		sibs = &s.flat[static_cast<size_t>(f.parent_flat)]->children;
+	} else {
+		sibs = &s.fields;
+	}
+	for (size_t i = 0; i + 1 < sibs->size(); i++) {
+		if ((*sibs)[i].get() == &f) {
+			out->next_sibling = (*sibs)[i + 1]->flat_index;
+		}
+	}
+	out->nullable = f.nullable;
+	out->n_buffers = f.n_buffers;
+	out->decimal_width = f.decimal_width;
+	out->decimal_scale = f.decimal_scale;
+	out->param = f.param;
+	out->dict_id = f.dict_id;
+	out->index_type_id = f.index_type_id;
+	out->index_width = f.index_width;
+	return B2A_OK;
+	B2A_CATCH
+}
+
+int b2a_reader_set_projection(b2a_reader *r, const char *const *names, uint32_t n) {
+	B2A_TRY
+	std::vector<std::string> v;
+	for (uint32_t i = 0; i < n; i++) {
+		v.emplace_back(names[i]);
+	}
+	r->reader.SetProjection(v);
+	return B2A_OK;
+	B2A_CATCH
+}
+
+int b2a_reader_num_batches(b2a_reader *r, uint64_t *n_batches, uint64_t *n_rows) {
+	*n_batches = r->reader.Batches().size();
+	*n_rows = r->reader.TotalRows();
+	return B2A_OK;
+}
+
+int b2a_reader_batch_info(b2a_reader *r, uint64_t batch, b2a_batch_info *out) {
+	B2A_TRY
+	const auto &bs = r->reader.Batches();
+	if (batch >= bs.size()) {
+		return Fail(B2A_EINVAL, "batch index out of range");
+	}
+	const RecordBatch &b = bs[batch];
+	std::memset(out, 0, sizeof(*out));
+	out->rows = b.rows;
+	out->body_offset = b.body_offset;
+	out->body_length = b.body_length;
+	out->meta_offset = b.meta_offset;
+	out->compressed = b.compression >= 0;
+	uint64_t sum = 0;
+	for (auto &s : b.buffers) {
+		sum += s.length;
+	}
+	out->buffer_bytes = sum;
+	return B2A_OK;
+	B2A_CATCH
+}
+
+int b2a_reader_image(b2a_reader *r, const void **data, uint64_t *size) {
+	*data = r->reader.Image();
+	*size = r->reader.ImageSize();
+	return B2A_OK;
+}
+
+int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, const char **value, uint32_t *n) {
+	const auto &m = r->reader.BaseSchema().metadata;
+	*n = static_cast<uint32_t>(m.size());
+	if (i < m.size()) {
+		*key = m[i].first.c_str();
+		*value = m[i].second.c_str();
+	}
+	return B2A_OK;
+}
+
+// ------------------------------------------------------------------ scan
+static void FreeScanDevice(b2a_scan *s) {
+	if (s->device >= 0) {
+		cudaSetDevice(s->device);
+		cudaFree(s->d_tasks);
+		cudaFree(s->d_tile_task);
+		cudaFree(s->d_variadic);
+		cudaFree(s->d_err);
+		cudaFree(s->d_image_owned);
+		cudaFree(s->d_chunk_col);
+		cudaFree(s->d_chunk_rows);
+	}
+}
+
+// device < 0: plan only (layout inspection on a machine without a GPU); every compute call then fails.
+int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, b2a_scan **out) {
+	B2A_TRY
+	std::unique_ptr<b2a_scan> s(new b2a_scan());
+	s->r = r;
+	s->device = device;
+	s->plan.Build(r->reader, batch_lo, batch_hi);
+	if (device >= 0) {
+		CUDA_OK(cudaSetDevice(device));
+		cudaDeviceProp prop;
+		CUDA_OK(cudaGetDeviceProperties(&prop, device));
+		s->sm_count = prop.multiProcessorCount;
+		const ScanPlan &p = s->plan;
+		size_t nt = p.tasks.size() ? p.tasks.size() : 1, nl = p.tile_task.size() ? p.tile_task.size() : 1,
+		       nv = p.variadic.size() ? p.variadic.size() : 1;
+		CUDA_OK(cudaMalloc(&s->d_tasks, nt * sizeof(b2a_task)));
+		CUDA_OK(cudaMalloc(&s->d_tile_task, nl * sizeof(uint32_t)));
+		CUDA_OK(cudaMalloc(&s->d_variadic, nv * sizeof(uint64_t)));
+		CUDA_OK(cudaMalloc(&s->d_err, sizeof(uint32_t)));
+		CUDA_OK(cudaMemcpy(s->d_tasks, p.tasks.data(), p.tasks.size() * sizeof(b2a_task), cudaMemcpyHostToDevice));
+		CUDA_OK(cudaMemcpy(s->d_tile_task, p.tile_task.data(), p.tile_task.size() * sizeof(uint32_t),
+		                   cudaMemcpyHostToDevice));
+		CUDA_OK(cudaMemcpy(s->d_variadic, p.variadic.data(), p.variadic.size() * sizeof(uint64_t),
+		                   cudaMemcpyHostToDevice));
+		CUDA_OK(cudaMemset(s->d_err, 0, sizeof(uint32_t)));
+	}
+	*out = s.release();
+	return B2A_OK;
+	B2A_CATCH
+}
+
+void b2a_scan_destroy(b2a_scan *s) {
+	if (!s) {
+		return;
+	}
+	FreeScanDevice(s);
+	delete s;
+}
+
+int b2a_scan_sizes(b2a_scan *s, uint64_t *image_lo, uint64_t *image_bytes, uint64_t *out_bytes,
+                   uint64_t *algorithmic_bytes, uint64_t *n_tasks, uint64_t *n_tiles) {
+	const ScanPlan &p = s->plan;
+	*image_lo = p.image_lo;
+	*image_bytes = p.image_hi - p.image_lo;
+	*out_bytes = p.out_bytes;
+	*algorithmic_bytes = p.algorithmic_in + p.algorithmic_out;
+	*n_tasks = p.tasks.size();
+	*n_tiles = p.tile_task.size();
+	return B2A_OK;
+}
+
+#define NEED_DEVICE(s)                                                                                                 \
+	do {                                                                                                               \
+		if ((s)->device < 0) {                                                                                         \
+			return Fail(B2A_ECUDA, "scan was planned without a CUDA device; there is no CPU fallback");                \
+		}                                                                                                              \
+		CUDA_OK(cudaSetDevice((s)->device));                                                                           \
+	} while (0)
+
+int b2a_scan_upload(b2a_scan *s, void *cuda_stream) {
+	NEED_DEVICE(s);
+	const ScanPlan &p = s->plan;
+	uint64_t bytes = p.image_hi - p.image_lo;
+	if (!s->d_image_owned) {
+		// +64: the string kernel fetches whole aligned words around the last characters
+		CUDA_OK(cudaMalloc(&s->d_image_owned, bytes + 64));
+	}
+	if (bytes) {
+		CUDA_OK(cudaMemcpyAsync(s->d_image_owned, s->r->reader.Image() + p.image_lo, bytes, cudaMemcpyHostToDevice,
+		                        static_cast<cudaStream_t>(cuda_stream)));
+	}
+	s->d_image = s->d_image_owned;
+	return B2A_OK;
+}
+
+int b2a_scan_set_device_image(b2a_scan *s, const void *d_image) {
+	if ((reinterpret_cast<uintptr_t>(d_image) & 255) != 0) {
+		return Fail(B2A_EINVAL, "device image must be 256-byte aligned");
+	}
+	s->d_image = static_cast<const uint8_t *>(d_image);
+	return B2A_OK;
+}
+
+int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cuda_stream) {
+	NEED_DEVICE(s);
+	if (!s->d_image) {
+		return Fail(B2A_EINVAL, "no device image: call b2a_scan_upload or b2a_scan_set_device_image first");
+	}
+	if (!d_out || (reinterpret_cast<uintptr_t>(d_out) & 255) != 0) {
+		return Fail(B2A_EINVAL, "output arena must be a 256-byte aligned device pointer");
+	}
+	const ScanPlan &p = s->plan;
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	if (p.stats_bytes) {
+		CUDA_OK(cudaMemsetAsync(static_cast<uint8_t *>(d_out) + p.stats_base, 0, p.stats_bytes, st));
+	}
+	DecodeLaunch l;
+	l.d_tasks = s->d_tasks;
+	l.d_tile_task = s->d_tile_task;
+	l.n_tiles = static_cast<uint32_t>(p.tile_task.size());
+	l.image_origin = s->d_image - p.image_lo;
+	l.out = static_cast<uint8_t *>(d_out);
+	uint64_t base = string_ptr_base ? string_ptr_base : reinterpret_cast<uint64_t>(s->d_image);
+	l.string_ptr_origin = base - p.image_lo;
+	l.d_err = s->d_err;
+	l.d_variadic = s->d_variadic;
+	l.sm_count = s->sm_count;
+	int e = LaunchDecode(l, cuda_stream);
+	if (e != 0) {
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
+		                           " launching b2a_decode_kernel");
+	}
+	if (l.n_tiles) {
+		s->launches++;
+	}
+	return B2A_OK;
+}
+
+int b2a_scan_finish(b2a_scan *s, void *cuda_stream) {
+	NEED_DEVICE(s);
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	uint32_t err = 0;
+	CUDA_OK(cudaMemcpyAsync(&err, s->d_err, sizeof(err), cudaMemcpyDeviceToHost, st));
+	CUDA_OK(cudaStreamSynchronize(st));
+	if (err != B2A_DEV_OK) {
+		CUDA_OK(cudaMemsetAsync(s->d_err, 0, sizeof(uint32_t), st));
+		switch (err) {
+		case B2A_DEV_BAD_OFFSETS:
+			return Fail(B2A_EINVAL, "Arrow IPC: offsets buffer is not monotonically increasing or exceeds the data "
+			                        "buffer");
+		case B2A_DEV_MUL_OVERFLOW:
+			return Fail(B2A_ECONVERSION, "Could not convert to Microsecond");
+		case B2A_DEV_STRING_4GB:
+			return Fail(B2A_ECONVERSION, "DuckDB does not support Strings over 4GB");
+		case B2A_DEV_INDEX_U32:
+			return Fail(B2A_ECONVERSION, "DuckDB only supports indices that fit on an uint32");
+		default:
+			return Fail(B2A_EINTERNAL, "unknown device error code " + std::to_string(err));
+		}
+	}
+	return B2A_OK;
+}
+
+int b2a_scan_download(b2a_scan *s, const void *d_out, void *h_out, void *cuda_stream) {
+	NEED_DEVICE(s);
+	CUDA_OK(cudaMemcpyAsync(h_out, d_out, s->plan.out_bytes, cudaMemcpyDeviceToHost,
+	                        static_cast<cudaStream_t>(cuda_stream)));
+	return B2A_OK;
+}
+
+int b2a_scan_column(b2a_scan *s, uint64_t batch, uint32_t flat_field, b2a_column_out *out) {
+	const ScanPlan &p = s->plan;
+	if (batch < p.batch_lo || batch >= p.batch_hi || flat_field >= p.n_flat) {
+		return Fail(B2A_EINVAL, "batch / field out of range");
+	}
+	*out = p.Column(batch, flat_field);
+	return B2A_OK;
+}
+
+int b2a_scan_dictionary(b2a_scan *s, uint32_t flat_field, b2a_column_out *out, uint32_t *dict_flat_field) {
+	auto it = s->plan.dict_cols.find(static_cast<int>(flat_field));
+	if (it == s->plan.dict_cols.end()) {
+		return Fail(B2A_EINVAL, "field is not dictionary encoded");
+	}
+	*out = it->second;
+	if (dict_flat_field) {
+		*dict_flat_field = flat_field;
+	}
+	return B2A_OK;
+}
+
+uint64_t b2a_scan_gpu_launches(b2a_scan *s) {
+	return s->launches;
+}
+
+int b2a_scan_num_chunks(b2a_scan *s, uint64_t *n_chunks) {
+	*n_chunks = s->plan.n_chunks;
+	return B2A_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,334 @@
+// Host framing + slicing.  Reference behaviour restated:
+//  * 8-byte alignment skip before every prefix/body     ipc_file_stream_reader.cpp:133-141
+//  * "ARROW1\0\0" magic at offset 0 is skipped, the footer is never read   :107-119
+//  * prefix = {u32 0xFFFFFFFF, i32 metadata_size}; a different token is an IOException   :121-124
+//  * a truncated prefix, or metadata_size == 0, is a clean end of stream   :126-129 + nanoarrow ENODATA :63-66
+//  * metadata_size < 0 is an IOException                base_stream_reader.cpp:214-227
+//  * first message must be a Schema; afterwards only RecordBatch is accepted by the reference
+//    (base_stream_reader.cpp:86-96).  DictionaryBatch is accepted here in addition (BASELINE config 4).
+#include "ipc_reader.hpp"
+#include "flatbuf.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <unordered_set>
+
+namespace b2a {
+
+static const uint32_t kContinuationToken = 0xFFFFFFFFu;
+
+Reader::~Reader() {
+	if (mmap_base) {
+		munmap(mmap_base, mmap_len);
+	}
+	if (fd >= 0) {
+		close(fd);
+	}
+}
+
+void Reader::OpenFile(const std::string &path) {
+	fd = open(path.c_str(), O_RDONLY);
+	if (fd < 0) {
+		throw Error(B2A_EIO, "Cannot open file \"" + path + "\": " + std::strerror(errno));
+	}
+	struct stat st;
+	if (fstat(fd, &st) != 0) {
+		throw Error(B2A_EIO, "Cannot stat file \"" + path + "\"");
+	}
+	image_size = static_cast<uint64_t>(st.st_size);
+	if (image_size > 0) {
+		mmap_base = mmap(nullptr, image_size, PROT_READ, MAP_PRIVATE, fd, 0);
+		if (mmap_base == MAP_FAILED) {
+			mmap_base = nullptr;
+			throw Error(B2A_EIO, "Cannot mmap file \"" + path + "\"");
+		}
+		mmap_len = image_size;
+		image = static_cast<const uint8_t *>(mmap_base);
+	}
+	Index();
+}
+
+void Reader::OpenBuffers(const b2a_ipc_buffer *bufs, uint32_t n) {
+	if (n == 0) {
+		throw Error(B2A_EINVAL, "scan_arrow_ipc: empty buffer list");
+	}
+	if (n == 1) {
+		image = static_cast<const uint8_t *>(bufs[0].ptr);
+		image_size = bufs[0].size;
+	} else {
+		uint64_t total = 0;
+		for (uint32_t i = 0; i < n; i++) {
+			total = (total + 7) & ~uint64_t(7);
+			total += bufs[i].size;
+		}
+		owned.assign(total, 0);
+		uint64_t pos = 0;
+		for (uint32_t i = 0; i < n; i++) {
+			pos = (pos + 7) & ~uint64_t(7);
+			std::memcpy(owned.data() + pos, bufs[i].ptr, bufs[i].size);
+			pos += bufs[i].size;
+		}
+		image = owned.data();
+		image_size = total;
+	}
+	Index();
+}
+
+static uint64_t Align8(uint64_t v) {
+	return (v + 7) & ~uint64_t(7);
+}
+
+bool Reader::ReadNextMessage(uint64_t &pos) {
+	pos = Align8(pos); // EnsureInputStreamAligned
+	if (pos + 8 > image_size) {
+		return false; // SerializationException on the prefix read == clean EOS
+	}
+	if (pos == 0 && std::memcmp("ARROW1\0\0", image, 8) == 0) {
+		pos = 8;
+		return ReadNextMessage(pos);
+	}
+	uint32_t token;
+	int32_t metadata_size;
+	std::memcpy(&token, image + pos, 4);
+	std::memcpy(&metadata_size, image + pos + 4, 4);
+	if (token != kContinuationToken) {
+		throw Error(B2A_EIO, "Expected continuation token (0xFFFFFFFF) but got " + std::to_string(token));
+	}
+	if (metadata_size < 0) {
+		throw Error(B2A_EIO, "Expected metadata size >= 0 but got " + std::to_string(metadata_size));
+	}
+	if (metadata_size == 0) {
+		return false; // EOS marker (nanoarrow returns ENODATA)
+	}
+	uint64_t meta_pos = pos + 8;
+	if (meta_pos + static_cast<uint64_t>(metadata_size) > image_size) {
+		throw Error(B2A_EIO, "Arrow IPC: message metadata extends past the end of the input");
+	}
+	const uint8_t *meta = image + meta_pos;
+	size_t meta_len = static_cast<size_t>(metadata_size);
+
+	try {
+		fb::Table msg = fb::root(meta, meta_len);
+		int16_t version = msg.scalar<int16_t>(0, 0);
+		if (version < 3) { // MetadataVersion::V4 == 3; nanoarrow rejects older streams
+			throw Error(B2A_EIO, "Arrow IPC: unsupported metadata version (expected V4 or V5)");
+		}
+		uint8_t header_type = msg.scalar<uint8_t>(1, 0);
+		int64_t body_length = msg.scalar<int64_t>(3, 0);
+		if (body_length < 0) {
+			throw Error(B2A_EIO, "Arrow IPC: negative bodyLength");
+		}
+		uint64_t body_offset = Align8(meta_pos + meta_len);
+		if (body_length > 0 && body_offset + static_cast<uint64_t>(body_length) > image_size) {
+			throw Error(B2A_EIO, "Arrow IPC: message body extends past the end of the input");
+		}
+		if (!have_schema) {
+			if (header_type != 1) {
+				throw Error(B2A_EIO, "Expected Schema Arrow IPC message but got " +
+				                         std::string(header_type == 3   ? "RecordBatch"
+				                                     : header_type == 2 ? "DictionaryBatch"
+				                                                        : "Uninitialized"));
+			}
+			SchemaParser::ParseMessageSchema(meta, meta_len, schema);
+			have_schema = true;
+			// per-flat-field first buffer index
+			flat_buffer_start.clear();
+			int nbuf = 0;
+			for (auto *f : schema.flat) {
+				flat_buffer_start.push_back(nbuf);
+				nbuf += f->n_buffers;
+				if (f->variadic) {
+					has_variadic = true;
+				}
+			}
+			flat_buffer_start.push_back(nbuf);
+		} else if (header_type == 3) {
+			fb::Table rb = msg.table(2);
+			if (!rb.valid) {
+				throw Error(B2A_EIO, "Arrow IPC: RecordBatch message without header");
+			}
+			RecordBatch batch;
+			batch.meta_offset = pos;
+			ParseRecordBatch(meta, meta_len, rb.pos, body_offset, static_cast<uint64_t>(body_length), batch, false);
+			total_rows += batch.rows;
+			batches.push_back(std::move(batch));
+		} else if (header_type == 2) {
+			fb::Table db = msg.table(2);
+			if (!db.valid) {
+				throw Error(B2A_EIO, "Arrow IPC: DictionaryBatch message without header");
+			}
+			DictionaryBatch d;
+			d.id = db.scalar<int64_t>(0, 0);
+			d.is_delta = db.scalar<uint8_t>(2, 0) != 0;
+			fb::Table rb = db.table(1);
+			if (!rb.valid) {
+				throw Error(B2A_EIO, "Arrow IPC: DictionaryBatch without data");
+			}
+			d.data.meta_offset = pos;
+			ParseRecordBatch(meta, meta_len, rb.pos, body_offset, static_cast<uint64_t>(body_length), d.data, true);
+			if (d.is_delta) {
+				throw Error(B2A_ENOTIMPL, "Arrow IPC: delta dictionaries are not supported");
+			}
+			if (dictionaries.count(d.id)) {
+				// the reference rejects DICTIONARY_REPLACEMENT (base_stream_reader.cpp:59-61)
+				throw Error(B2A_EIO, "This stream uses unsupported feature DICTIONARY_REPLACEMENT");
+			}
+			dictionaries[d.id] = std::move(d);
+		} else if (header_type == 1) {
+			throw Error(B2A_EIO, "Expected RecordBatch Arrow IPC message but got Schema");
+		} else {
+			throw Error(B2A_EIO, "Expected RecordBatch Arrow IPC message but got " +
+			                         std::string(header_type == 4 ? "Tensor" : "SparseTensor"));
+		}
+		pos = body_offset + static_cast<uint64_t>(body_length);
+	} catch (fb::ParseError &e) {
+		throw Error(B2A_EIO, std::string("Arrow IPC: invalid message flatbuffer: ") + e.what());
+	}
+	return true;
+}
+
+void Reader::Index() {
+	uint64_t pos = 0;
+	while (ReadNextMessage(pos)) {
+	}
+	if (!have_schema) {
+		throw Error(B2A_EIO, "Expected Schema Arrow IPC message but got end of stream");
+	}
+}
+
+void Reader::ParseRecordBatch(const uint8_t *tbl_buf, size_t tbl_len, size_t table_pos, uint64_t body_offset,
+                              uint64_t body_length, RecordBatch &out, bool is_dictionary) {
+	fb::Buf b {tbl_buf, tbl_len};
+	fb::Table rb(b, table_pos);
+	int64_t length = rb.scalar<int64_t>(0, 0);
+	if (length < 0) {
+		throw Error(B2A_EIO, "Arrow IPC: negative RecordBatch length");
+	}
+	out.rows = static_cast<uint64_t>(length);
+	out.body_offset = body_offset;
+	out.body_length = body_length;
+
+	size_t ndata;
+	uint32_t n_nodes = rb.vec(1, ndata, 16);
+	out.nodes.resize(n_nodes);
+	for (uint32_t i = 0; i < n_nodes; i++) {
+		out.nodes[i].length = b.rd<int64_t>(ndata + 16 * size_t(i));
+		out.nodes[i].null_count = b.rd<int64_t>(ndata + 16 * size_t(i) + 8);
+		if (out.nodes[i].length < 0) {
+			throw Error(B2A_EIO, "Arrow IPC: negative FieldNode length");
+		}
+	}
+	size_t bdata;
+	uint32_t n_buffers = rb.vec(2, bdata, 16);
+	out.buffers.resize(n_buffers);
+	for (uint32_t i = 0; i < n_buffers; i++) {
+		int64_t off = b.rd<int64_t>(bdata + 16 * size_t(i));
+		int64_t len = b.rd<int64_t>(bdata + 16 * size_t(i) + 8);
+		if (off < 0 || len < 0 || static_cast<uint64_t>(off) + static_cast<uint64_t>(len) > body_length) {
+			throw Error(B2A_EIO, "Arrow IPC: buffer " + std::to_string(i) + " lies outside the message body");
+		}
+		if ((off & 7) != 0) {
+			throw Error(B2A_EIO, "Arrow IPC: buffer " + std::to_string(i) + " is not 8-byte aligned");
+		}
+		out.buffers[i].offset = body_offset + static_cast<uint64_t>(off);
+		out.buffers[i].length = static_cast<uint64_t>(len);
+	}
+	fb::Table comp = rb.table(3);
+	if (comp.valid) {
+		out.compression = comp.scalar<int8_t>(0, 0);
+	}
+	size_t vdata;
+	uint32_t n_var = rb.vec(4, vdata, 8);
+	for (uint32_t i = 0; i < n_var; i++) {
+		out.variadic_counts.push_back(b.rd<int64_t>(vdata + 8 * size_t(i)));
+	}
+	if (!is_dictionary) {
+		if (n_nodes != schema.flat.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has " + std::to_string(n_nodes) + " field nodes, schema has " +
+			                         std::to_string(schema.flat.size()));
+		}
+		uint64_t expect = static_cast<uint64_t>(flat_buffer_start.back());
+		for (auto c : out.variadic_counts) {
+			expect += static_cast<uint64_t>(c);
+		}
+		if (n_buffers != expect) {
+			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has " + std::to_string(n_buffers) + " buffers, schema needs " +
+			                         std::to_string(expect));
+		}
+	}
+}
+
+std::vector<int> Reader::OutputColumns() const {
+	if (!projected_top.empty()) {
+		return projected_top;
+	}
+	std::vector<int> all(schema.fields.size());
+	for (size_t i = 0; i < all.size(); i++) {
+		all[i] = static_cast<int>(i);
+	}
+	return all;
+}
+
+static std::string Lower(const std::string &s) {
+	std::string r = s;
+	std::transform(r.begin(), r.end(), r.begin(), [](unsigned char c) { return std::tolower(c); });
+	return r;
+}
+
+// QueryResult::DeduplicateColumns (duckdb/src/main/query_result.cpp:71-93)
+static void DeduplicateColumns(std::vector<std::string> &names) {
+	std::unordered_map<std::string, uint64_t> name_map;
+	for (auto &column_name : names) {
+		auto low = Lower(column_name);
+		if (name_map.find(low) == name_map.end()) {
+			name_map[low]++;
+		} else {
+			std::string new_name = column_name + "_" + std::to_string(name_map[low]);
+			auto new_low = Lower(new_name);
+			while (name_map.find(new_low) != name_map.end()) {
+				name_map[low]++;
+				new_name = column_name + "_" + std::to_string(name_map[low]);
+				new_low = Lower(new_name);
+			}
+			column_name = new_name;
+			name_map[new_low]++;
+		}
+	}
+}
+
+void Reader::SetProjection(const std::vector<std::string> &column_names) {
+	if (column_names.empty()) {
+		throw Error(B2A_EINTERNAL, "Can't request zero fields projected from IpcStreamReader");
+	}
+	std::vector<std::string> names;
+	for (auto &f : schema.fields) {
+		names.push_back(f->name);
+	}
+	DeduplicateColumns(names);
+	std::unordered_map<std::string, int> name_to_field;
+	std::unordered_set<std::string> duplicates;
+	for (size_t i = 0; i < names.size(); i++) {
+		if (name_to_field.find(names[i]) != name_to_field.end()) {
+			duplicates.insert(names[i]);
+		}
+		name_to_field.insert({names[i], static_cast<int>(i)});
+	}
+	std::vector<int> proj;
+	for (auto &name : column_names) {
+		if (duplicates.count(name)) {
+			throw Error(B2A_EINTERNAL, "Field '" + name + "' refers to a duplicate column name in IPC file schema");
+		}
+		auto it = name_to_field.find(name);
+		if (it == name_to_field.end()) {
+			throw Error(B2A_EINTERNAL, "Field '" + name + "' does not exist in IPC file schema");
+		}
+		proj.push_back(it->second);
+	}
+	projected_top = std::move(proj);
+}
+
+} // namespace b2a

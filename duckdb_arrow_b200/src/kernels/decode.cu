@@ -1,0 +1,677 @@
+// sm_100a decode kernels: Arrow IPC buffers (resident in HBM as a byte image of the stream) ->
+// DuckDB vectors.  ONE persistent launch walks a tile table covering every (batch, field, buffer)
+// task of the scan; grid = 148 SMs x resident CTAs.  All integer/byte work, HBM-bound; no tensor cores.
+//
+// Each op restates a loop of duckdb/src/function/table/arrow_conversion.cpp (line refs at each op).
+#include "decode.cuh"
+
+#include <cuda_runtime.h>
+
+namespace b2a {
+
+static constexpr int kThreads = 256;
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ldg_stream16(const void *p) {
+	uint4 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+	             : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+	             : "l"(p));
+	return r;
+}
+__device__ __forceinline__ uint2 ldg_stream8(const void *p) {
+	uint2 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+	return r;
+}
+__device__ __forceinline__ void stg_stream16(void *p, uint4 v) {
+	asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+	             : "memory");
+}
+__device__ __forceinline__ uint32_t bswap32(uint32_t v) {
+	return __byte_perm(v, 0, 0x0123);
+}
+__device__ __forceinline__ uint64_t bswap64(uint64_t v) {
+	uint32_t lo = static_cast<uint32_t>(v), hi = static_cast<uint32_t>(v >> 32);
+	return (static_cast<uint64_t>(bswap32(lo)) << 32) | bswap32(hi);
+}
+__device__ __forceinline__ void raise(uint32_t *err, uint32_t code) {
+	atomicMax(err, code);
+}
+
+// byte-swap every `width`-byte element inside a 16-byte vector (K8, big-endian streams)
+__device__ __forceinline__ uint4 bswap_elems(uint4 v, int width) {
+	switch (width) {
+	case 2:
+		v.x = __byte_perm(v.x, 0, 0x2301);
+		v.y = __byte_perm(v.y, 0, 0x2301);
+		v.z = __byte_perm(v.z, 0, 0x2301);
+		v.w = __byte_perm(v.w, 0, 0x2301);
+		break;
+	case 4:
+		v.x = bswap32(v.x);
+		v.y = bswap32(v.y);
+		v.z = bswap32(v.z);
+		v.w = bswap32(v.w);
+		break;
+	case 8: {
+		uint32_t a = bswap32(v.y), b = bswap32(v.x), c = bswap32(v.w), d = bswap32(v.z);
+		v = make_uint4(a, b, c, d);
+		break;
+	}
+	case 16: {
+		uint32_t a = bswap32(v.w), b = bswap32(v.z), c = bswap32(v.y), d = bswap32(v.x);
+		v = make_uint4(a, b, c, d);
+		break;
+	}
+	default:
+		break;
+	}
+	return v;
+}
+
+// effective validity of row r = AND over the task's mask chain (own bitmap + struct / fixed-size-list
+// ancestors).  Reference: SetValidityMask + the parent-mask loops, arrow_conversion.cpp:1143-1151,245-253,313-323
+__device__ __forceinline__ bool eff_valid(const b2a_task &t, const uint8_t *__restrict__ image, uint64_t r) {
+	bool ok = true;
+	for (uint32_t m = 0; m < t.n_masks; m++) {
+		uint64_t rr = t.masks[m].div == 1 ? r : r / t.masks[m].div;
+		uint8_t b = __ldg(image + t.masks[m].src + (rr >> 3));
+		ok = ok && ((b >> (rr & 7)) & 1);
+	}
+	return ok;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: fixed-width copy (DirectConversion, :454-461 — a pointer alias on the CPU, a real copy here)
+// src is 8-byte aligned (IPC buffers), dst 16-byte aligned (our arena), tile starts keep both.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void op_copy(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                        uint64_t row0, uint64_t nrows) {
+	const uint64_t w = t.src_width;
+	const uint8_t *src = image + t.src + row0 * w;
+	uint8_t *dst = out + t.dst + row0 * w;
+	const uint64_t bytes = nrows * w;
+	const uint64_t nvec = bytes >> 4;
+	const bool swap = (t.flags & B2A_TASK_F_BSWAP) && w > 1;
+	const bool aligned16 = ((reinterpret_cast<uintptr_t>(src) & 15) == 0);
+	constexpr int U = 4;
+	if (aligned16) {
+		uint64_t i = threadIdx.x;
+		for (; i + (U - 1) * kThreads < nvec; i += U * kThreads) {
+			uint4 v[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				v[u] = ldg_stream16(src + ((i + u * kThreads) << 4));
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				if (swap) {
+					v[u] = bswap_elems(v[u], static_cast<int>(w));
+				}
+				stg_stream16(dst + ((i + u * kThreads) << 4), v[u]);
+			}
+		}
+		for (; i < nvec; i += kThreads) {
+			uint4 v = ldg_stream16(src + (i << 4));
+			if (swap) {
+				v = bswap_elems(v, static_cast<int>(w));
+			}
+			stg_stream16(dst + (i << 4), v);
+		}
+	} else {
+		uint64_t i = threadIdx.x;
+		for (; i + (U - 1) * kThreads < nvec; i += U * kThreads) {
+			uint2 a[U], b[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				const uint8_t *p = src + ((i + u * kThreads) << 4);
+				a[u] = ldg_stream8(p);
+				b[u] = ldg_stream8(p + 8);
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				uint4 v = make_uint4(a[u].x, a[u].y, b[u].x, b[u].y);
+				if (swap) {
+					v = bswap_elems(v, static_cast<int>(w));
+				}
+				stg_stream16(dst + ((i + u * kThreads) << 4), v);
+			}
+		}
+		for (; i < nvec; i += kThreads) {
+			const uint8_t *p = src + (i << 4);
+			uint2 a = ldg_stream8(p), b = ldg_stream8(p + 8);
+			uint4 v = make_uint4(a.x, a.y, b.x, b.y);
+			if (swap) {
+				v = bswap_elems(v, static_cast<int>(w));
+			}
+			stg_stream16(dst + (i << 4), v);
+		}
+	}
+	// tail (< 16 bytes): whole elements, byte by byte
+	const uint64_t tail0 = nvec << 4;
+	for (uint64_t e = tail0 / w + threadIdx.x; e < nrows; e += kThreads) {
+		for (uint64_t k = 0; k < w; k++) {
+			dst[e * w + k] = src[e * w + (swap ? (w - 1 - k) : k)];
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: validity (GetValidityMask, :63-108).  One thread per 64-row word of the DuckDB ValidityMask.
+// Bytes past ceil(rows/8) stay 0xFF (fresh mask), exactly what the reference's memcpy leaves behind.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t mask_word(const b2a_task &t, const uint8_t *__restrict__ image, uint32_t m,
+                                              uint64_t word, uint64_t nbytes) {
+	const uint8_t *p = image + t.masks[m].src;
+	const uint64_t div = t.masks[m].div;
+	if (div == 1) {
+		uint64_t b0 = word << 3;
+		if (b0 + 8 <= nbytes) {
+			uint2 v = *reinterpret_cast<const uint2 *>(p + b0); // bitmap buffers are 8-byte aligned
+			return (static_cast<uint64_t>(v.y) << 32) | v.x;
+		}
+		uint64_t r = ~uint64_t(0);
+		for (uint64_t k = 0; k < 8 && b0 + k < nbytes; k++) {
+			r = (r & ~(uint64_t(0xFF) << (8 * k))) | (static_cast<uint64_t>(p[b0 + k]) << (8 * k));
+		}
+		return r;
+	}
+	// fixed-size-list broadcast: row r reads bit r/div of the ancestor
+	uint64_t r = ~uint64_t(0);
+	uint64_t row = word << 6;
+	for (int b = 0; b < 64; b++, row++) {
+		if (row >= t.rows) {
+			break;
+		}
+		uint64_t rr = row / div;
+		if (!((p[rr >> 3] >> (rr & 7)) & 1)) {
+			r &= ~(uint64_t(1) << b);
+		}
+	}
+	return r;
+}
+
+__device__ __forceinline__ void op_validity(const b2a_task &t, const uint8_t *__restrict__ image,
+                                            uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows) {
+	const bool add_null = t.flags & B2A_TASK_F_ADD_NULL;
+	const uint64_t total_rows = t.rows + (add_null ? 1 : 0);
+	const uint64_t nbytes = (t.rows + 7) >> 3;
+	const uint64_t w0 = row0 >> 6;
+	// [row0, row0+nrows) is a slice of total_rows (the dispatcher counts the extra NULL slot as a row)
+	(void)total_rows;
+	const uint64_t w1 = (row0 + nrows + 63) >> 6;
+	uint64_t *dst = reinterpret_cast<uint64_t *>(out + t.dst);
+	unsigned long long valid = 0;
+	for (uint64_t w = w0 + threadIdx.x; w < w1; w += kThreads) {
+		uint64_t v = ~uint64_t(0);
+		for (uint32_t m = 0; m < t.n_masks; m++) {
+			v &= mask_word(t, image, m, w, nbytes);
+		}
+		if (add_null && (t.rows >> 6) == w) {
+			v &= ~(uint64_t(1) << (t.rows & 63)); // mask.SetInvalid(size), :105-106
+		}
+		dst[w] = v;
+		uint64_t lo = w << 6;
+		uint64_t counted = v;
+		if (lo + 64 > t.rows) {
+			counted = (t.rows > lo) ? (v & ((uint64_t(1) << (t.rows - lo)) - 1)) : 0;
+		}
+		valid += __popcll(counted);
+	}
+	// popcount: warp reduce, one atomic per warp
+	for (int o = 16; o > 0; o >>= 1) {
+		valid += __shfl_xor_sync(0xffffffffu, valid, o);
+	}
+	if ((threadIdx.x & 31) == 0 && valid && t.aux != B2A_NONE_OFF) {
+		atomicAdd(reinterpret_cast<unsigned long long *>(out + t.aux), valid);
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: bool bit-unpack (:869-891): 16 rows per thread = 2 source bytes -> one 16-byte store
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void op_bool(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                        uint64_t row0, uint64_t nrows) {
+	const uint8_t *src = image + t.src + (row0 >> 3);
+	uint8_t *dst = out + t.dst + row0;
+	const uint64_t ngroups = (nrows + 15) >> 4;
+	for (uint64_t g = threadIdx.x; g < ngroups; g += kThreads) {
+		uint64_t r = g << 4;
+		uint32_t bits = src[g * 2];
+		if (r + 8 < nrows) {
+			bits |= static_cast<uint32_t>(src[g * 2 + 1]) << 8;
+		}
+		uint32_t wds[4];
+#pragma unroll
+		for (int k = 0; k < 4; k++) {
+			uint32_t nib = (bits >> (4 * k)) & 0xF;
+			// spread 4 bits into 4 bytes of 0/1
+			wds[k] = (nib & 1) | ((nib & 2) << 7) | ((nib & 4) << 14) | ((nib & 8) << 21);
+		}
+		if (r + 16 <= nrows) {
+			stg_stream16(dst + r, make_uint4(wds[0], wds[1], wds[2], wds[3]));
+		} else {
+			for (uint64_t k = 0; r + k < nrows; k++) {
+				dst[r + k] = (bits >> k) & 1;
+			}
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: offsets + characters -> string_t (SetVectorString, :409-423; string_t ctor
+// duckdb/src/include/duckdb/common/types/string_type.hpp:43-64).  One row per thread:
+//   len <= 12 : {u32 len, 12 inline bytes zero padded}
+//   len  > 12 : {u32 len, 4 prefix bytes, u64 pointer into the character buffer}
+// Character bytes are fetched with aligned 32-bit loads + funnel shifts (the window of one warp is a
+// contiguous span of the char buffer, so the loads coalesce in L1).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 make_string_t(const uint8_t *__restrict__ chars, uint64_t o0, uint32_t len,
+                                                uint64_t ptr) {
+	const uint8_t *base = chars + o0;
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(base) & ~uintptr_t(3));
+	const uint32_t shift = (static_cast<uint32_t>(reinterpret_cast<uintptr_t>(base)) & 3u) * 8u;
+	const uint32_t need = len > 12 ? 4u : len;                    // bytes of character data to fetch
+	const uint32_t nwords = (need + (shift >> 3) + 3u) >> 2;       // aligned words that cover them
+	uint32_t w0 = 0, w1 = 0, w2 = 0, w3 = 0;
+	if (nwords > 0) {
+		w0 = __ldg(wp);
+	}
+	if (nwords > 1) {
+		w1 = __ldg(wp + 1);
+	}
+	if (nwords > 2) {
+		w2 = __ldg(wp + 2);
+	}
+	if (nwords > 3) {
+		w3 = __ldg(wp + 3);
+	}
+	uint32_t b0 = __funnelshift_r(w0, w1, shift);
+	uint32_t b1 = __funnelshift_r(w1, w2, shift);
+	uint32_t b2 = __funnelshift_r(w2, w3, shift);
+	if (len > 12) {
+		return make_uint4(len, b0, static_cast<uint32_t>(ptr), static_cast<uint32_t>(ptr >> 32));
+	}
+	// zero padding past `len`
+	uint32_t m0 = len >= 4 ? 0xFFFFFFFFu : ((1u << (8 * len)) - 1u);
+	uint32_t m1 = len >= 8 ? 0xFFFFFFFFu : (len > 4 ? ((1u << (8 * (len - 4))) - 1u) : 0u);
+	uint32_t m2 = len >= 12 ? 0xFFFFFFFFu : (len > 8 ? ((1u << (8 * (len - 8))) - 1u) : 0u);
+	return make_uint4(len, b0 & m0, b1 & m1, b2 & m2);
+}
+
+template <typename OFF>
+__device__ __forceinline__ OFF load_off(const uint8_t *p, uint64_t i, bool swap);
+template <>
+__device__ __forceinline__ uint32_t load_off<uint32_t>(const uint8_t *p, uint64_t i, bool swap) {
+	uint32_t v = __ldg(reinterpret_cast<const uint32_t *>(p) + i);
+	return swap ? bswap32(v) : v;
+}
+template <>
+__device__ __forceinline__ uint64_t load_off<uint64_t>(const uint8_t *p, uint64_t i, bool swap) {
+	uint2 v = __ldg(reinterpret_cast<const uint2 *>(p) + i);
+	uint64_t r = (static_cast<uint64_t>(v.y) << 32) | v.x;
+	return swap ? bswap64(r) : r;
+}
+
+template <typename OFF>
+__device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__restrict__ image,
+                                          uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
+                                          uint64_t ptr_origin, uint32_t *err) {
+	const uint8_t *offs = image + t.src;
+	const uint8_t *chars = image + t.src2;
+	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		OFF o0 = load_off<OFF>(offs, i, swap);
+		OFF o1 = load_off<OFF>(offs, i + 1, swap);
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (o1 < o0 || static_cast<uint64_t>(o1) > t.src2_len) {
+			raise(err, B2A_DEV_BAD_OFFSETS);
+		} else if (t.n_masks == 0 || eff_valid(t, image, i)) {
+			uint64_t len = static_cast<uint64_t>(o1) - static_cast<uint64_t>(o0);
+			if (len > 0xFFFFFFFFull) {
+				raise(err, B2A_DEV_STRING_4GB);
+			} else {
+				v = make_string_t(chars, o0, static_cast<uint32_t>(len), ptr_origin + t.src2 + o0);
+			}
+		}
+		stg_stream16(dst + i, v);
+	}
+}
+
+// fixed-size binary (ArrowToDuckDBBlob FIXED_SIZE, :347-360) and UUID-less w:N blobs
+__device__ __forceinline__ void op_blob_fixed(const b2a_task &t, const uint8_t *__restrict__ image,
+                                              uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
+                                              uint64_t ptr_origin) {
+	const uint8_t *chars = image + t.src;
+	const uint64_t w = static_cast<uint64_t>(t.param);
+	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (t.n_masks == 0 || eff_valid(t, image, i)) {
+			v = make_string_t(chars, i * w, static_cast<uint32_t>(w), ptr_origin + t.src + i * w);
+		}
+		stg_stream16(dst + i, v);
+	}
+}
+
+// K4v: Utf8View (SetVectorStringView, :425-452; arrow_string_view_type.hpp:24-85)
+__device__ __forceinline__ void op_string_view(const b2a_task &t, const uint8_t *__restrict__ image,
+                                               uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
+                                               uint64_t ptr_origin, const uint64_t *__restrict__ variadic,
+                                               uint32_t *err) {
+	const uint4 *views = reinterpret_cast<const uint4 *>(image + t.src); // 16-byte views, 8-byte aligned buffer
+	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		const uint2 *vp = reinterpret_cast<const uint2 *>(views + i);
+		uint2 a = __ldg(vp), b = __ldg(vp + 1);
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (t.n_masks == 0 || eff_valid(t, image, i)) {
+			uint32_t len = a.x;
+			if (len <= 12) {
+				uint32_t m0 = len >= 4 ? 0xFFFFFFFFu : ((1u << (8 * len)) - 1u);
+				uint32_t m1 = len >= 8 ? 0xFFFFFFFFu : (len > 4 ? ((1u << (8 * (len - 4))) - 1u) : 0u);
+				uint32_t m2 = len >= 12 ? 0xFFFFFFFFu : (len > 8 ? ((1u << (8 * (len - 8))) - 1u) : 0u);
+				v = make_uint4(len, a.y & m0, b.x & m1, b.y & m2);
+			} else {
+				uint32_t buffer_index = b.x;
+				uint32_t offset = b.y;
+				if (buffer_index >= static_cast<uint32_t>(t.param)) {
+					raise(err, B2A_DEV_BAD_OFFSETS);
+				} else {
+					uint64_t data_off = variadic[t.variadic0 + buffer_index] + offset;
+					v = make_string_t(image, data_off, len, ptr_origin + data_off);
+				}
+			}
+		}
+		stg_stream16(dst + i, v);
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6: list / map offsets -> list_entry_t{offset,length} (ConvertArrowListOffsetsTemplated, :139-165).
+// The reference rebases every 2 048-row chunk to its own first offset (cur_offset starts at 0 per call);
+// aux[k] receives the child row where chunk k starts, aux[n_chunks] the end.
+// ------------------------------------------------------------------------------------------------
+template <typename OFF>
+__device__ __forceinline__ void op_list(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                        uint64_t row0, uint64_t nrows, uint32_t *err) {
+	const uint8_t *offs = image + t.src;
+	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
+	uint64_t *aux = reinterpret_cast<uint64_t *>(out + t.aux);
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		OFF o0 = load_off<OFF>(offs, i, swap);
+		OFF o1 = load_off<OFF>(offs, i + 1, swap);
+		OFF cb = load_off<OFF>(offs, i & ~uint64_t(B2A_VECTOR_SIZE - 1), swap);
+		if (o1 < o0 || o0 < cb) {
+			raise(err, B2A_DEV_BAD_OFFSETS);
+		}
+		uint64_t rel = static_cast<uint64_t>(o0) - static_cast<uint64_t>(cb);
+		uint64_t len = static_cast<uint64_t>(static_cast<OFF>(o1 - o0));
+		stg_stream16(dst + i, make_uint4(static_cast<uint32_t>(rel), static_cast<uint32_t>(rel >> 32),
+		                                 static_cast<uint32_t>(len), static_cast<uint32_t>(len >> 32)));
+		if ((i & (B2A_VECTOR_SIZE - 1)) == 0) {
+			aux[i / B2A_VECTOR_SIZE] = o0;
+		}
+		if (i + 1 == t.rows) {
+			aux[(t.rows + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE] = o1;
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// K7: scalar transforms.  One row per thread; src/dst are naturally aligned for their widths.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int64_t load_i64(const uint8_t *p, uint64_t i, bool swap) {
+	return static_cast<int64_t>(load_off<uint64_t>(p, i, swap));
+}
+__device__ __forceinline__ int32_t load_i32(const uint8_t *p, uint64_t i, bool swap) {
+	return static_cast<int32_t>(load_off<uint32_t>(p, i, swap));
+}
+// TryMultiplyOperator::Operation(int64_t,int64_t,int64_t&) == __builtin_mul_overflow
+// (duckdb/src/function/scalar/operator/multiply.cpp:190-194)
+__device__ __forceinline__ bool try_mul_i64(int64_t a, int64_t b, int64_t &r) {
+	r = static_cast<int64_t>(static_cast<uint64_t>(a) * static_cast<uint64_t>(b));
+	int64_t hi = __mul64hi(a, b);
+	return hi == (r >> 63);
+}
+__device__ __forceinline__ void store_interval(uint8_t *dst, uint64_t i, int32_t months, int32_t days, int64_t micros) {
+	stg_stream16(reinterpret_cast<uint4 *>(dst) + i,
+	             make_uint4(static_cast<uint32_t>(months), static_cast<uint32_t>(days), static_cast<uint32_t>(micros),
+	                        static_cast<uint32_t>(static_cast<uint64_t>(micros) >> 32)));
+}
+
+struct i128 {
+	uint64_t lo;
+	int64_t hi;
+};
+__device__ __forceinline__ i128 load_i128(const uint8_t *p, uint64_t i, bool swap) {
+	const uint2 *q = reinterpret_cast<const uint2 *>(p) + 2 * i;
+	uint2 a = __ldg(q), b = __ldg(q + 1);
+	uint64_t w0 = (static_cast<uint64_t>(a.y) << 32) | a.x, w1 = (static_cast<uint64_t>(b.y) << 32) | b.x;
+	i128 r;
+	if (swap) {
+		r.lo = bswap64(w1);
+		r.hi = static_cast<int64_t>(bswap64(w0));
+	} else {
+		r.lo = w0;
+		r.hi = static_cast<int64_t>(w1);
+	}
+	return r;
+}
+
+__device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                          uint64_t row0, uint64_t nrows, uint32_t *err) {
+	const uint8_t *src = image + t.src;
+	uint8_t *dst = out + t.dst;
+	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		switch (t.op) {
+		case B2A_OP_MUL_I32:   // TimeConversion<int32_t>, :463-478 (valid rows only)
+		case B2A_OP_MUL_I64: { // TimeConversion<int64_t> / TimestampTZConversion, :497-511
+			int64_t r = 0;
+			if (t.n_masks == 0 || eff_valid(t, image, i)) {
+				int64_t v = t.op == B2A_OP_MUL_I32 ? static_cast<int64_t>(load_i32(src, i, swap)) : load_i64(src, i, swap);
+				if (!try_mul_i64(v, t.param, r)) {
+					raise(err, B2A_DEV_MUL_OVERFLOW);
+				}
+			}
+			reinterpret_cast<int64_t *>(dst)[i] = r;
+			break;
+		}
+		case B2A_OP_DIV_I64: // :986-994, :1018-1026 — every row, truncating division
+			reinterpret_cast<int64_t *>(dst)[i] = load_i64(src, i, swap) / t.param;
+			break;
+		case B2A_OP_DATE64: // :951-961
+			reinterpret_cast<int32_t *>(dst)[i] = static_cast<int32_t>(load_i64(src, i, swap) / 86400000ll);
+			break;
+		case B2A_OP_INTERVAL_MUL: { // IntervalConversionUs, :513-525 — every row, NULL slots included
+			int64_t r;
+			if (!try_mul_i64(load_i64(src, i, swap), t.param, r)) {
+				raise(err, B2A_DEV_MUL_OVERFLOW);
+			}
+			store_interval(dst, i, 0, 0, r);
+			break;
+		}
+		case B2A_OP_INTERVAL_DIV: // :1052-1062
+			store_interval(dst, i, 0, 0, load_i64(src, i, swap) / t.param);
+			break;
+		case B2A_OP_INTERVAL_MONTHS: // :527-537
+			store_interval(dst, i, load_i32(src, i, swap), 0, 0);
+			break;
+		case B2A_OP_INTERVAL_MDN: { // :539-549, ArrowInterval{i32 months,i32 days,i64 nanos}
+			int32_t months = load_i32(src, 4 * i, swap), days = load_i32(src, 4 * i + 1, swap);
+			int64_t nanos = load_i64(src, 2 * i + 1, swap);
+			store_interval(dst, i, months, days, nanos / 1000);
+			break;
+		}
+		case B2A_OP_UUID: { // UUIDConversion, :480-495 (valid rows only)
+			uint4 v = make_uint4(0, 0, 0, 0);
+			if (t.n_masks == 0 || eff_valid(t, image, i)) {
+				i128 s = load_i128(src, i, false);
+				uint64_t lower = bswap64(static_cast<uint64_t>(s.hi));
+				uint64_t upper = bswap64(s.lo) ^ (uint64_t(1) << 63);
+				v = make_uint4(static_cast<uint32_t>(lower), static_cast<uint32_t>(lower >> 32),
+				               static_cast<uint32_t>(upper), static_cast<uint32_t>(upper >> 32));
+			}
+			stg_stream16(reinterpret_cast<uint4 *>(dst) + i, v);
+			break;
+		}
+		case B2A_OP_DECIMAL: { // ConvertDecimal, :768-844: TryCast src -> physical type, valid rows only
+			i128 v = {0, 0};
+			bool valid = t.n_masks == 0 || eff_valid(t, image, i);
+			if (valid) {
+				if (t.src_width == 4) {
+					int32_t s = load_i32(src, i, swap);
+					v.lo = static_cast<uint64_t>(static_cast<int64_t>(s));
+					v.hi = s < 0 ? -1 : 0;
+				} else if (t.src_width == 8) {
+					int64_t s = load_i64(src, i, swap);
+					v.lo = static_cast<uint64_t>(s);
+					v.hi = s < 0 ? -1 : 0;
+				} else {
+					v = load_i128(src, i, swap);
+				}
+			}
+			// range check of the narrowing cast (HugeintTryCastInteger, hugeint.cpp:559-582);
+			// a failed cast leaves the slot unwritten in the reference (release build) — we store 0
+			int64_t s64 = static_cast<int64_t>(v.lo);
+			bool fits64 = (v.hi == 0 && s64 >= 0) || (v.hi == -1 && s64 < 0);
+			switch (t.dst_width) {
+			case 2:
+				reinterpret_cast<int16_t *>(dst)[i] =
+				    (valid && fits64 && s64 >= -32768 && s64 <= 32767) ? static_cast<int16_t>(s64) : 0;
+				break;
+			case 4:
+				reinterpret_cast<int32_t *>(dst)[i] =
+				    (valid && fits64 && s64 >= -2147483648ll && s64 <= 2147483647ll) ? static_cast<int32_t>(s64) : 0;
+				break;
+			case 8:
+				reinterpret_cast<int64_t *>(dst)[i] = (valid && fits64) ? s64 : 0;
+				break;
+			default:
+				stg_stream16(reinterpret_cast<uint4 *>(dst) + i,
+				             make_uint4(static_cast<uint32_t>(v.lo), static_cast<uint32_t>(v.lo >> 32),
+				                        static_cast<uint32_t>(static_cast<uint64_t>(v.hi)),
+				                        static_cast<uint32_t>(static_cast<uint64_t>(v.hi) >> 32)));
+				break;
+			}
+			break;
+		}
+		case B2A_OP_DICT_INDEX: { // SetSelectionVector*, :1227-1348: widen to sel_t, NULL -> dictionary length
+			uint64_t idx;
+			const bool sgn = t.flags & B2A_TASK_F_SIGNED;
+			switch (t.src_width) {
+			case 1:
+				idx = sgn ? static_cast<uint64_t>(static_cast<int64_t>(static_cast<int8_t>(src[i]))) : src[i];
+				break;
+			case 2: {
+				uint16_t v = reinterpret_cast<const uint16_t *>(src)[i];
+				if (swap) {
+					v = static_cast<uint16_t>((v >> 8) | (v << 8));
+				}
+				idx = sgn ? static_cast<uint64_t>(static_cast<int64_t>(static_cast<int16_t>(v))) : v;
+				break;
+			}
+			case 4: {
+				uint32_t v = load_off<uint32_t>(src, i, swap);
+				idx = sgn ? static_cast<uint64_t>(static_cast<int64_t>(static_cast<int32_t>(v))) : v;
+				break;
+			}
+			default:
+				idx = load_off<uint64_t>(src, i, swap);
+				break;
+			}
+			if (t.n_masks != 0 && !eff_valid(t, image, i)) {
+				idx = static_cast<uint64_t>(t.param);
+			} else if (t.src_width == 8 && static_cast<uint64_t>(t.param) > 0xFFFFFFFFull && idx > 0xFFFFFFFFull) {
+				raise(err, B2A_DEV_INDEX_U32);
+			}
+			reinterpret_cast<uint32_t *>(dst)[i] = static_cast<uint32_t>(idx);
+			break;
+		}
+		default:
+			break;
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// the one kernel: persistent CTAs stride over the tile table
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+    b2a_decode_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
+                      const uint8_t *__restrict__ image, uint8_t *__restrict__ out, uint64_t ptr_origin,
+                      uint32_t *err, const uint64_t *__restrict__ variadic) {
+	__shared__ b2a_task s_task;
+	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+		const uint32_t ti = __ldg(tile_task + tile);
+		__syncthreads(); // previous tile's readers are done with s_task
+		if (threadIdx.x < sizeof(b2a_task) / 16) {
+			reinterpret_cast<uint4 *>(&s_task)[threadIdx.x] = __ldg(reinterpret_cast<const uint4 *>(tasks + ti) + threadIdx.x);
+		}
+		__syncthreads();
+		const b2a_task &t = s_task;
+		const uint64_t row0 = static_cast<uint64_t>(tile - t.tile0) * t.tile_rows;
+		uint64_t limit = t.rows;
+		if (t.op == B2A_OP_VALIDITY && (t.flags & B2A_TASK_F_ADD_NULL)) {
+			limit += 1;
+		}
+		uint64_t nrows = limit - row0;
+		if (nrows > t.tile_rows) {
+			nrows = t.tile_rows;
+		}
+		switch (t.op) {
+		case B2A_OP_COPY:
+			op_copy(t, image, out, row0, nrows);
+			break;
+		case B2A_OP_VALIDITY:
+			op_validity(t, image, out, row0, nrows);
+			break;
+		case B2A_OP_BOOL:
+			op_bool(t, image, out, row0, nrows);
+			break;
+		case B2A_OP_STRING32:
+			op_string<uint32_t>(t, image, out, row0, nrows, ptr_origin, err);
+			break;
+		case B2A_OP_STRING64:
+			op_string<uint64_t>(t, image, out, row0, nrows, ptr_origin, err);
+			break;
+		case B2A_OP_STRING_VIEW:
+			op_string_view(t, image, out, row0, nrows, ptr_origin, variadic, err);
+			break;
+		case B2A_OP_BLOB_FIXED:
+			op_blob_fixed(t, image, out, row0, nrows, ptr_origin);
+			break;
+		case B2A_OP_LIST32:
+			op_list<uint32_t>(t, image, out, row0, nrows, err);
+			break;
+		case B2A_OP_LIST64:
+			op_list<uint64_t>(t, image, out, row0, nrows, err);
+			break;
+		default:
+			op_scalar(t, image, out, row0, nrows, err);
+			break;
+		}
+	}
+}
+
+int LaunchDecode(const DecodeLaunch &l, void *stream) {
+	if (l.n_tiles == 0) {
+		return 0;
+	}
+	// 8 resident CTAs of 256 threads per SM = 2 048 threads = full occupancy; grid is a multiple of the SM count
+	uint32_t grid = static_cast<uint32_t>(l.sm_count) * 8u;
+	if (grid > l.n_tiles) {
+		grid = l.n_tiles;
+	}
+	b2a_decode_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+	    l.d_tasks, l.d_tile_task, l.n_tiles, l.image_origin, l.out, l.string_ptr_origin, l.d_err, l.d_variadic);
+	return static_cast<int>(cudaGetLastError());
+}
+
+} // namespace b2a

@@ -1,0 +1,53 @@
+// Launch interface of the decode / filter kernels (host side of src/kernels).
+#pragma once
+#include "b2arrow.h"
+#include "task.h"
+
+#include <stdint.h>
+
+#define B2A_NONE_OFF 0xFFFFFFFFFFFFFFFFull
+
+namespace b2a {
+
+struct DecodeLaunch {
+	const b2a_task *d_tasks = nullptr;
+	const uint32_t *d_tile_task = nullptr; // tile -> task index
+	uint32_t n_tiles = 0;
+	const uint8_t *image_origin = nullptr; // device address of stream-image offset 0 (may lie before the allocation)
+	uint8_t *out = nullptr;                // output arena
+	uint64_t string_ptr_origin = 0;        // address of stream-image offset 0 in the consumer's address space
+	uint32_t *d_err = nullptr;
+	const uint64_t *d_variadic = nullptr;  // image offsets of view data buffers
+	int sm_count = 148;
+};
+
+// returns cudaError_t as int
+int LaunchDecode(const DecodeLaunch &l, void *stream);
+
+struct FilterLaunch {
+	const uint8_t *out = nullptr;       // decoded arena
+	const uint64_t *d_chunk_col = nullptr; // per chunk, per predicate: arena offset of the chunk's column data
+	const uint32_t *d_chunk_rows = nullptr;
+	uint64_t n_chunks = 0;
+	uint32_t n_preds = 0;
+	b2a_predicate preds[8];
+	uint8_t widths[8];  // bytes per value of each predicate's column (4 or 8)
+	uint32_t *d_sel = nullptr;
+	uint32_t *d_count = nullptr;
+	unsigned long long *d_total = nullptr;
+	int sm_count = 148;
+};
+int LaunchFilter(const FilterLaunch &l, void *stream);
+
+struct SumProductLaunch {
+	const uint8_t *out = nullptr;
+	const uint64_t *d_chunk_col = nullptr; // per chunk: [a_off, b_off]
+	const uint32_t *d_sel = nullptr;
+	const uint32_t *d_count = nullptr;
+	uint64_t n_chunks = 0;
+	unsigned long long *d_result = nullptr; // lo, hi of the int128 sum
+	int sm_count = 148;
+};
+int LaunchSumProduct(const SumProductLaunch &l, void *stream);
+
+} // namespace b2a

@@ -1,0 +1,411 @@
+#include "scan_plan.hpp"
+
+#include <algorithm>
+#include <cstring>
+
+namespace b2a {
+
+static const uint64_t kNone = UINT64_MAX;
+static const uint64_t kTileBytes = 64 * 1024; // bytes moved (in + out) per tile, roughly
+
+uint64_t ScanPlan::Alloc(uint64_t bytes) {
+	uint64_t off = out_bytes;
+	out_bytes += (bytes + 255) & ~uint64_t(255);
+	return off;
+}
+
+void ScanPlan::Touch(uint64_t off, uint64_t len) {
+	if (len == 0) {
+		return;
+	}
+	image_lo = std::min(image_lo, off);
+	image_hi = std::max(image_hi, off + len);
+	algorithmic_in += len;
+}
+
+// x16: input bytes per row in 1/16 byte units (bitmaps are 2/16 = 1/8 byte per row)
+void ScanPlan::AddTask(b2a_task t, uint64_t in_x16, uint64_t out_per_row) {
+	uint64_t rows = t.rows + ((t.op == B2A_OP_VALIDITY && (t.flags & B2A_TASK_F_ADD_NULL)) ? 1 : 0);
+	if (rows == 0) {
+		return;
+	}
+	uint64_t per_row_x16 = in_x16 + out_per_row * 16;
+	if (per_row_x16 == 0) {
+		per_row_x16 = 1;
+	}
+	uint64_t tile_rows = kTileBytes * 16 / per_row_x16;
+	tile_rows = std::max<uint64_t>(B2A_VECTOR_SIZE, (tile_rows / B2A_VECTOR_SIZE) * B2A_VECTOR_SIZE);
+	tile_rows = std::min<uint64_t>(tile_rows, uint64_t(1) << 22);
+	uint64_t n_tiles = (rows + tile_rows - 1) / tile_rows;
+	if (uint64_t(next_tile) + n_tiles > 0xFFFFFFF0ull || tasks.size() > 0xFFFFFFF0ull) {
+		throw Error(B2A_EINVAL, "scan too large for one launch: split the batch range");
+	}
+	t.tile0 = next_tile;
+	t.tile_rows = static_cast<uint32_t>(tile_rows);
+	uint32_t idx = static_cast<uint32_t>(tasks.size());
+	tasks.push_back(t);
+	tile_task.insert(tile_task.end(), n_tiles, idx);
+	next_tile += static_cast<uint32_t>(n_tiles);
+}
+
+static int BatchBuffers(const Field &f, bool ignore_dictionary) {
+	if (f.dict_id >= 0 && !ignore_dictionary) {
+		return 2;
+	}
+	return f.n_buffers;
+}
+
+void ScanPlan::SkipField(const Field &f, const RecordBatch &rb, size_t &node_idx, size_t &buf_idx, size_t &var_idx,
+                         bool ignore_dictionary) {
+	node_idx++;
+	buf_idx += static_cast<size_t>(BatchBuffers(f, ignore_dictionary));
+	if (f.dict_id >= 0 && !ignore_dictionary) {
+		return; // the value type's children are not part of the record batch
+	}
+	if (f.variadic) {
+		if (var_idx >= rb.variadic_counts.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: missing variadicBufferCounts entry");
+		}
+		buf_idx += static_cast<size_t>(rb.variadic_counts[var_idx++]);
+	}
+	for (auto &c : f.children) {
+		SkipField(*c, rb, node_idx, buf_idx, var_idx, false);
+	}
+}
+
+static void NeedBytes(const BufferSlice &b, uint64_t need, const Field &f, const char *what) {
+	if (b.length < need) {
+		throw Error(B2A_EIO, "Arrow IPC: " + std::string(what) + " buffer of field '" + f.name + "' has " +
+		                         std::to_string(b.length) + " bytes, expected at least " + std::to_string(need));
+	}
+}
+
+void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch &rb, size_t &node_idx, size_t &buf_idx,
+                         size_t &var_idx, const Chain &parent_chain, bool list_child, bool selected,
+                         b2a_column_out *slots, bool as_dictionary_values, bool ignore_dictionary) {
+	if (!selected) {
+		SkipField(f, rb, node_idx, buf_idx, var_idx, ignore_dictionary);
+		return;
+	}
+	const bool is_dict = f.dict_id >= 0 && !ignore_dictionary;
+	const int nb = BatchBuffers(f, ignore_dictionary);
+	if (node_idx >= rb.nodes.size() || buf_idx + static_cast<size_t>(nb) > rb.buffers.size()) {
+		throw Error(B2A_EIO, "Arrow IPC: RecordBatch has too few nodes/buffers for field '" + f.name + "'");
+	}
+	const NodeSlice node = rb.nodes[node_idx++];
+	const BufferSlice *bufs = rb.buffers.data() + buf_idx;
+	buf_idx += static_cast<size_t>(nb);
+	const uint64_t L = static_cast<uint64_t>(node.length);
+
+	b2a_column_out &slot = slots[f.flat_index];
+	std::memset(&slot, 0xFF, sizeof(slot));
+	slot.rows = L;
+	slot.null_count = static_cast<uint64_t>(node.null_count);
+	slot.chars_len = 0;
+
+	// ---- effective validity chain: own bitmap (only when null_count != 0 and the buffer exists,
+	// arrow_conversion.cpp:71) AND the struct / fixed-size-list ancestors
+	Chain chain;
+	if (!list_child) {
+		chain = parent_chain;
+	}
+	if (nb > 0 && node.null_count != 0 && bufs[0].length > 0) {
+		NeedBytes(bufs[0], (L + 7) / 8, f, "validity");
+		if (chain.n >= B2A_MAX_MASKS) {
+			throw Error(B2A_ENOTIMPL, "more than 4 nested nullable struct levels are not supported");
+		}
+		chain.m[chain.n++] = b2a_mask_ref {bufs[0].offset, 1};
+		Touch(bufs[0].offset, (L + 7) / 8);
+	}
+	b2a_task base;
+	std::memset(&base, 0, sizeof(base));
+	base.aux = kNone;
+	base.rows = L;
+	base.flags = big_endian ? B2A_TASK_F_BSWAP : 0;
+	base.n_masks = chain.n;
+	for (uint32_t i = 0; i < chain.n; i++) {
+		base.masks[i] = chain.m[i];
+	}
+
+	if (chain.n > 0 || as_dictionary_values) {
+		b2a_task v = base;
+		v.op = B2A_OP_VALIDITY;
+		if (as_dictionary_values) {
+			v.flags |= B2A_TASK_F_ADD_NULL;
+		}
+		uint64_t total = L + (as_dictionary_values ? 1 : 0);
+		v.dst = Alloc(((total + 63) / 64) * 8);
+		v.aux = slot.stats_off = stats_bytes;
+		stats_bytes += 8;
+		slot.validity_off = v.dst;
+		algorithmic_out += ((total + 63) / 64) * 8;
+		AddTask(v, 2 * chain.n, 0);
+	}
+
+	if (is_dict) {
+		if (!f.children.empty()) {
+			throw Error(B2A_ENOTIMPL, "dictionary-encoded nested types are not supported");
+		}
+		auto it = reader.Dictionaries().find(f.dict_id);
+		if (it == reader.Dictionaries().end()) {
+			throw Error(B2A_EIO, "Arrow IPC: no DictionaryBatch for dictionary id " + std::to_string(f.dict_id));
+		}
+		NeedBytes(bufs[1], L * static_cast<uint64_t>(f.index_width), f, "dictionary index");
+		b2a_task t = base;
+		t.op = B2A_OP_DICT_INDEX;
+		t.src = bufs[1].offset;
+		t.src_width = static_cast<uint8_t>(f.index_width);
+		t.dst_width = 4;
+		t.param = static_cast<int64_t>(it->second.data.rows);
+		bool is_signed = f.index_type_id == B2A_T_TINYINT || f.index_type_id == B2A_T_SMALLINT ||
+		                 f.index_type_id == B2A_T_INTEGER || f.index_type_id == B2A_T_BIGINT;
+		if (is_signed) {
+			t.flags |= B2A_TASK_F_SIGNED;
+		}
+		t.dst = slot.data_off = Alloc(L * 4);
+		Touch(t.src, L * static_cast<uint64_t>(f.index_width));
+		algorithmic_out += L * 4;
+		AddTask(t, 16 * static_cast<uint64_t>(f.index_width), 4);
+		dict_cols[f.flat_index]; // mark: dictionary values must be decoded
+		return;
+	}
+
+	size_t n_variadic = 0;
+	if (f.variadic) {
+		if (var_idx >= rb.variadic_counts.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: missing variadicBufferCounts entry");
+		}
+		n_variadic = static_cast<size_t>(rb.variadic_counts[var_idx++]);
+		if (buf_idx + n_variadic > rb.buffers.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has too few variadic buffers");
+		}
+	}
+
+	b2a_task t = base;
+	t.op = static_cast<uint16_t>(f.op);
+	t.src_width = static_cast<uint8_t>(f.src_width);
+	t.dst_width = static_cast<uint8_t>(f.out_width);
+	t.param = f.param;
+	switch (f.op) {
+	case B2A_OP_NONE:
+		break;
+	case B2A_OP_BOOL:
+		NeedBytes(bufs[1], (L + 7) / 8, f, "data");
+		t.src = bufs[1].offset;
+		t.dst = slot.data_off = Alloc(L);
+		Touch(t.src, (L + 7) / 8);
+		algorithmic_out += L;
+		AddTask(t, 2, 1);
+		break;
+	case B2A_OP_STRING32:
+	case B2A_OP_STRING64: {
+		const uint64_t ow = static_cast<uint64_t>(f.src_width);
+		if (L > 0) {
+			NeedBytes(bufs[1], (L + 1) * ow, f, "offsets");
+		}
+		t.src = bufs[1].offset;
+		t.src2 = bufs[2].offset;
+		t.src2_len = bufs[2].length;
+		if (f.type_id == B2A_T_BLOB) {
+			t.flags |= B2A_TASK_F_BLOB;
+		}
+		t.dst = slot.data_off = Alloc(L * 16);
+		slot.chars_off = bufs[2].offset;
+		slot.chars_len = bufs[2].length;
+		if (L > 0) {
+			Touch(t.src, (L + 1) * ow);
+			Touch(t.src2, t.src2_len);
+			algorithmic_out += L * 16;
+			AddTask(t, 16 * ow + 16 * t.src2_len / L, 16);
+		}
+		break;
+	}
+	case B2A_OP_STRING_VIEW: {
+		NeedBytes(bufs[1], L * 16, f, "views");
+		t.src = bufs[1].offset;
+		t.variadic0 = static_cast<uint32_t>(variadic.size());
+		t.param = static_cast<int64_t>(n_variadic);
+		uint64_t data_bytes = 0;
+		for (size_t i = 0; i < n_variadic; i++) {
+			const BufferSlice &vb = rb.buffers[buf_idx + i];
+			variadic.push_back(vb.offset);
+			Touch(vb.offset, vb.length);
+			data_bytes += vb.length;
+		}
+		t.dst = slot.data_off = Alloc(L * 16);
+		slot.chars_off = 0; // pointers are relative to the stream image itself
+		slot.chars_len = data_bytes;
+		Touch(t.src, L * 16);
+		algorithmic_out += L * 16;
+		AddTask(t, 16 * 16 + (L ? 16 * data_bytes / L : 0), 16);
+		break;
+	}
+	case B2A_OP_BLOB_FIXED:
+		NeedBytes(bufs[1], L * static_cast<uint64_t>(f.param), f, "data");
+		t.src = bufs[1].offset;
+		t.dst = slot.data_off = Alloc(L * 16);
+		slot.chars_off = bufs[1].offset;
+		slot.chars_len = bufs[1].length;
+		Touch(t.src, L * static_cast<uint64_t>(f.param));
+		algorithmic_out += L * 16;
+		AddTask(t, 16 * static_cast<uint64_t>(f.param), 16);
+		break;
+	case B2A_OP_LIST32:
+	case B2A_OP_LIST64: {
+		const uint64_t ow = static_cast<uint64_t>(f.src_width);
+		if (L > 0) {
+			NeedBytes(bufs[1], (L + 1) * ow, f, "offsets");
+		}
+		t.src = bufs[1].offset;
+		t.dst = slot.data_off = Alloc(L * 16);
+		uint64_t n_chunks_col = (L + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
+		t.aux = slot.aux_off = Alloc((n_chunks_col + 1) * 8);
+		if (L > 0) {
+			Touch(t.src, (L + 1) * ow);
+			algorithmic_out += L * 16;
+			AddTask(t, 16 * ow, 16);
+		}
+		break;
+	}
+	default: { // COPY and the elementwise transforms: src_width bytes in, out_width bytes out
+		const uint64_t sw = static_cast<uint64_t>(f.src_width), dw = static_cast<uint64_t>(f.out_width);
+		NeedBytes(bufs[1], L * sw, f, "data");
+		t.src = bufs[1].offset;
+		t.dst = slot.data_off = Alloc(L * dw);
+		Touch(t.src, L * sw);
+		algorithmic_out += L * dw;
+		AddTask(t, 16 * sw, dw);
+		break;
+	}
+	}
+	buf_idx += n_variadic;
+
+	// ---- children
+	switch (f.type_id) {
+	case B2A_T_LIST:
+	case B2A_T_MAP: {
+		Chain empty;
+		EmitField(reader, *f.children.at(0), rb, node_idx, buf_idx, var_idx, empty, true, true, slots, false, false);
+		break;
+	}
+	case B2A_T_STRUCT:
+		for (auto &c : f.children) {
+			size_t child_node = node_idx;
+			EmitField(reader, *c, rb, node_idx, buf_idx, var_idx, chain, false, true, slots, false, false);
+			if (static_cast<uint64_t>(rb.nodes[child_node].length) < L) {
+				throw Error(B2A_EIO, "Arrow IPC: struct child '" + c->name + "' is shorter than its parent");
+			}
+		}
+		break;
+	case B2A_T_ARRAY: {
+		Chain scaled = chain;
+		for (uint32_t i = 0; i < scaled.n; i++) {
+			scaled.m[i].div *= static_cast<uint64_t>(f.param);
+		}
+		size_t child_node = node_idx;
+		EmitField(reader, *f.children.at(0), rb, node_idx, buf_idx, var_idx, scaled, false, true, slots, false, false);
+		if (static_cast<uint64_t>(rb.nodes[child_node].length) < L * static_cast<uint64_t>(f.param)) {
+			throw Error(B2A_EIO, "Arrow IPC: fixed-size-list child is shorter than length * list_size");
+		}
+		break;
+	}
+	default:
+		for (auto &c : f.children) { // types we do not descend into have no children; keep the cursor right
+			SkipField(*c, rb, node_idx, buf_idx, var_idx, false);
+		}
+		break;
+	}
+}
+
+void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
+	const Schema &schema = reader.BaseSchema();
+	const auto &batches = reader.Batches();
+	if (lo > hi || hi > batches.size()) {
+		throw Error(B2A_EINVAL, "batch range out of bounds");
+	}
+	batch_lo = lo;
+	batch_hi = hi;
+	n_flat = static_cast<uint32_t>(schema.flat.size());
+	big_endian = !schema.little_endian;
+	top_columns = reader.OutputColumns();
+	image_lo = UINT64_MAX;
+	image_hi = 0;
+	out_bytes = 0;
+	std::vector<char> selected(schema.fields.size(), 0);
+	for (int c : top_columns) {
+		selected[static_cast<size_t>(c)] = 1;
+	}
+	b2a_column_out none;
+	std::memset(&none, 0xFF, sizeof(none));
+	none.rows = 0;
+	none.null_count = 0;
+	none.chars_len = 0;
+	cols.assign((hi - lo) * n_flat, none);
+
+	for (uint64_t b = lo; b < hi; b++) {
+		const RecordBatch &rb = batches[b];
+		if (rb.compression >= 0) {
+			throw Error(B2A_ENOTIMPL, "Arrow IPC: compressed record batch bodies (zstd/lz4) are not supported by the "
+			                          "B200 scan path yet");
+		}
+		batch_rows.push_back(rb.rows);
+		batch_chunk0.push_back(n_chunks);
+		n_chunks += (rb.rows + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
+		total_rows += rb.rows;
+		size_t node_idx = 0, buf_idx = 0, var_idx = 0;
+		Chain empty;
+		for (size_t c = 0; c < schema.fields.size(); c++) {
+			size_t node0 = node_idx;
+			EmitField(reader, *schema.fields[c], rb, node_idx, buf_idx, var_idx, empty, false, selected[c] != 0,
+			          cols.data() + (b - lo) * n_flat, false, false);
+			// "arrow_scan: array length mismatch" (arrow_conversion.cpp:1454-1456)
+			if (selected[c] && static_cast<uint64_t>(rb.nodes[node0].length) != rb.rows) {
+				throw Error(B2A_EINVAL, "arrow_scan: array length mismatch");
+			}
+		}
+	}
+	// dictionaries: decoded once per scan (ArrowArrayScanState::AddDictionary, arrow_array_scan_state.cpp:29-52)
+	std::vector<int> dict_fields;
+	for (auto &kv : dict_cols) {
+		dict_fields.push_back(kv.first);
+	}
+	std::vector<b2a_column_out> tmp(n_flat, none);
+	for (int flat : dict_fields) {
+		const Field &f = *schema.flat[static_cast<size_t>(flat)];
+		const DictionaryBatch &d = reader.Dictionaries().at(f.dict_id);
+		if (d.data.compression >= 0) {
+			throw Error(B2A_ENOTIMPL, "Arrow IPC: compressed dictionary batches are not supported");
+		}
+		size_t node_idx = 0, buf_idx = 0, var_idx = 0;
+		Chain empty;
+		EmitField(reader, f, d.data, node_idx, buf_idx, var_idx, empty, false, true, tmp.data(), true, true);
+		dict_cols[flat] = tmp[static_cast<size_t>(flat)];
+	}
+	// the popcount cells live in one region at the end of the arena (zeroed before every decode)
+	stats_base = out_bytes;
+	out_bytes += (stats_bytes + 255) & ~uint64_t(255);
+	for (auto &t : tasks) {
+		if (t.op == B2A_OP_VALIDITY) {
+			t.aux += stats_base;
+		}
+	}
+	for (auto &c : cols) {
+		if (c.stats_off != kNone) {
+			c.stats_off += stats_base;
+		}
+	}
+	for (auto &kv : dict_cols) {
+		if (kv.second.stats_off != kNone) {
+			kv.second.stats_off += stats_base;
+		}
+	}
+	if (image_lo == UINT64_MAX) {
+		image_lo = image_hi = 0;
+	}
+	image_lo &= ~uint64_t(255);
+	if (out_bytes == 0) {
+		out_bytes = 256;
+	}
+}
+
+} // namespace b2a

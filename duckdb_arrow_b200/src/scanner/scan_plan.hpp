@@ -1,0 +1,58 @@
+// Scan planner (host): record-batch range x projected fields -> conversion tasks, tile table and the
+// layout of the output arena.  This is the part of ArrowScanFunction / ArrowToDuckDB
+// (duckdb/src/function/table/arrow.cpp:172-201, arrow_conversion.cpp:1421-1484) that decides WHICH
+// conversion runs on WHICH buffer; the conversions themselves are the kernels in src/kernels.
+#pragma once
+#include "../ipc/ipc_reader.hpp"
+#include "../kernels/task.h"
+
+#include <map>
+#include <vector>
+
+namespace b2a {
+
+struct ScanPlan {
+	uint64_t batch_lo = 0, batch_hi = 0;
+	uint32_t n_flat = 0;
+	// slice of the stream image the tasks read: [image_lo, image_hi), image_lo is 256-byte aligned
+	uint64_t image_lo = 0, image_hi = 0;
+	uint64_t out_bytes = 0;
+	uint64_t stats_base = 0, stats_bytes = 0; // region of the arena that must be zeroed before a decode
+	uint64_t algorithmic_in = 0, algorithmic_out = 0;
+	uint64_t total_rows = 0;
+	uint64_t n_chunks = 0; // sum over batches of ceil(rows/2048)
+
+	std::vector<b2a_task> tasks;
+	std::vector<uint32_t> tile_task;
+	std::vector<uint64_t> variadic;
+	std::vector<b2a_column_out> cols;            // [(batch - batch_lo) * n_flat + flat]
+	std::map<int, b2a_column_out> dict_cols;     // flat field -> decoded dictionary values
+	std::vector<int> top_columns;                // projected top-level columns (indices into schema.fields)
+	std::vector<uint64_t> batch_rows;            // rows of each batch in range
+	std::vector<uint64_t> batch_chunk0;          // first global chunk index of each batch
+
+	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
+
+	const b2a_column_out &Column(uint64_t batch, uint32_t flat) const {
+		return cols[(batch - batch_lo) * n_flat + flat];
+	}
+
+private:
+	struct Chain {
+		b2a_mask_ref m[B2A_MAX_MASKS];
+		uint32_t n = 0;
+	};
+	uint64_t Alloc(uint64_t bytes);
+	void Touch(uint64_t off, uint64_t len);
+	void AddTask(b2a_task t, uint64_t in_bytes_per_row_x16, uint64_t out_bytes_per_row);
+	// returns number of nodes consumed
+	void EmitField(const Reader &reader, const Field &f, const RecordBatch &rb, size_t &node_idx, size_t &buf_idx,
+	               size_t &var_idx, const Chain &parent_chain, bool list_child, bool selected, b2a_column_out *slots,
+	               bool as_dictionary_values, bool ignore_dictionary);
+	void SkipField(const Field &f, const RecordBatch &rb, size_t &node_idx, size_t &buf_idx, size_t &var_idx,
+	               bool ignore_dictionary);
+	bool big_endian = false;
+	uint32_t next_tile = 0;
+};
+
+} // namespace b2a

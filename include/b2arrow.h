@@ -1,0 +1,226 @@
+/*
+ * b2arrow.h — thin C ABI between the DuckDB-facing host code (src/ipc, src/scanner,
+ * src/file_scanner, src/writer) and the sm_100a kernels.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers / sizes / POD structs, returns an int
+ * status (b2a_status) and never throws across the boundary.  b2a_last_error() returns the
+ * thread-local message of the last failing call.
+ *
+ * Reference interfaces replaced (paths relative to the pdet/duckdb-arrow checkout):
+ *   - b2a_reader_*      : IPCStreamReader / IPCFileStreamReader / IPCBufferStreamReader
+ *                         (src/ipc/stream_reader/base_stream_reader.cpp:52-212,
+ *                          ipc_file_stream_reader.cpp:47-138, ipc_buffer_stream_reader.cpp:12-76)
+ *                         plus the nanoarrow calls they make (ArrowIpcDecoderDecodeHeader /
+ *                         DecodeSchema / DecodeArrayFromShared, base_stream_reader.cpp:112-140).
+ *   - b2a_scan_*        : ArrowTableFunction::ArrowScanFunction + ArrowToDuckDB
+ *                         (duckdb/src/function/table/arrow.cpp:172-201,
+ *                          duckdb/src/function/table/arrow_conversion.cpp:1421-1484) — one call
+ *                         converts whole record batches instead of one 2 048-row chunk.
+ *   - b2a_scan_filter   : new (the reference has filter_pushdown=false, src/scanner/read_arrow.cpp:46-48);
+ *                         semantics = DuckDB ConstantFilter over the scanned vectors.
+ *   - b2a_writer_*      : ColumnDataCollectionSerializer::Serialize + ArrowAppender + nanoarrow encoder
+ *                         (src/writer/column_data_collection_serializer.cpp:80-120,
+ *                          duckdb/src/common/arrow/arrow_appender.cpp:37-131) and ArrowStreamWriter
+ *                         (src/writer/arrow_stream_writer.cpp:55-82).
+ */
+#ifndef B2ARROW_H
+#define B2ARROW_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2A_VECTOR_SIZE 2048u /* STANDARD_VECTOR_SIZE, duckdb/src/include/duckdb/common/vector_size.hpp:16-20 */
+#define B2A_NONE UINT64_MAX   /* "no such buffer" in every *_off field */
+
+typedef enum b2a_status {
+	B2A_OK = 0,
+	B2A_EINVAL = 1,     /* InvalidInputException */
+	B2A_EIO = 2,        /* IOException (framing, truncated message, bad continuation token) */
+	B2A_ENOTIMPL = 3,   /* NotImplementedException (decimal256, dense union, ...) */
+	B2A_ECONVERSION = 4, /* ConversionException (checked multiply overflow, >4GB string, index > u32) */
+	B2A_ECUDA = 5,      /* CUDA runtime error, or no device: there is no CPU fallback */
+	B2A_EINTERNAL = 6,  /* InternalException (projection of unknown / duplicate column) */
+	B2A_EOOM = 7
+} b2a_status;
+
+/* DuckDB logical types the path can produce (names follow LogicalTypeId). */
+typedef enum b2a_type_id {
+	B2A_T_INVALID = 0,
+	B2A_T_SQLNULL,
+	B2A_T_BOOLEAN,
+	B2A_T_TINYINT,
+	B2A_T_SMALLINT,
+	B2A_T_INTEGER,
+	B2A_T_BIGINT,
+	B2A_T_UTINYINT,
+	B2A_T_USMALLINT,
+	B2A_T_UINTEGER,
+	B2A_T_UBIGINT,
+	B2A_T_HUGEINT,
+	B2A_T_UHUGEINT,
+	B2A_T_FLOAT,
+	B2A_T_DOUBLE,
+	B2A_T_DECIMAL,
+	B2A_T_VARCHAR,
+	B2A_T_BLOB,
+	B2A_T_DATE,
+	B2A_T_TIME,
+	B2A_T_TIMESTAMP,
+	B2A_T_TIMESTAMP_SEC,
+	B2A_T_TIMESTAMP_MS,
+	B2A_T_TIMESTAMP_NS,
+	B2A_T_TIMESTAMP_TZ,
+	B2A_T_INTERVAL,
+	B2A_T_UUID,
+	B2A_T_LIST,
+	B2A_T_STRUCT,
+	B2A_T_MAP,
+	B2A_T_ARRAY
+} b2a_type_id;
+
+/* Conversion op of one field = which kernel body runs for its value buffer(s). */
+typedef enum b2a_op {
+	B2A_OP_NONE = 0,        /* struct / fixed-size-list parent / null: no value buffer */
+	B2A_OP_COPY,            /* DirectConversion, arrow_conversion.cpp:454-461 (+ endian swap) */
+	B2A_OP_BOOL,            /* :869-891 */
+	B2A_OP_STRING32,        /* SetVectorString<uint32_t>, :409-423,926-933 */
+	B2A_OP_STRING64,        /* SetVectorString<uint64_t>, :919-925 */
+	B2A_OP_STRING_VIEW,     /* SetVectorStringView, :425-452 */
+	B2A_OP_BLOB_FIXED,      /* ArrowToDuckDBBlob fixed size, :347-360 */
+	B2A_OP_LIST32,          /* ConvertArrowListOffsetsTemplated<uint32_t>, :139-165 */
+	B2A_OP_LIST64,          /* ... <uint64_t> */
+	B2A_OP_MUL_I32,         /* TimeConversion<int32_t> (checked multiply by param), :463-478 */
+	B2A_OP_MUL_I64,         /* TimeConversion<int64_t>/TimestampTZConversion, :463-511 */
+	B2A_OP_DIV_I64,         /* ns -> us truncating division by param, :986-994,1018-1026 */
+	B2A_OP_DATE64,          /* ms -> days, :951-961 */
+	B2A_OP_INTERVAL_MUL,    /* IntervalConversionUs (unchecked validity!), :513-525 */
+	B2A_OP_INTERVAL_DIV,    /* duration ns, :1052-1062 */
+	B2A_OP_INTERVAL_MONTHS, /* :527-537 */
+	B2A_OP_INTERVAL_MDN,    /* month-day-nano, :539-549 */
+	B2A_OP_DECIMAL,         /* ConvertDecimal narrowing/widening, :768-844 */
+	B2A_OP_UUID,            /* UUIDConversion, :480-495 */
+	B2A_OP_DICT_INDEX,      /* SetSelectionVector*, :1227-1348 */
+	B2A_OP_VALIDITY         /* GetValidityMask, :63-108 (internal: emitted per nullable node) */
+} b2a_op;
+
+/* One node of the schema tree, flattened in pre-order (the order of RecordBatch.nodes). */
+typedef struct b2a_field_info {
+	char name[128];
+	char format[48];      /* Arrow C data interface format string ("l", "d:15,2,64", "u", "tdD", "+l", ...) */
+	int32_t type_id;      /* b2a_type_id: the DuckDB LogicalType, per arrow_duck_schema.cpp:59-297 */
+	int32_t op;           /* b2a_op for the node's value buffer */
+	int32_t out_width;    /* bytes per row of the DuckDB vector (0: no flat data) */
+	int32_t src_width;    /* bytes per value in the Arrow buffer (0: bit-packed / none) */
+	int32_t n_children;
+	int32_t first_child;  /* flat index of first child, -1 if none (children are at first_child, next_sibling, ...) */
+	int32_t next_sibling; /* flat index, -1 if last */
+	int32_t parent;       /* flat index, -1 for top-level columns */
+	int32_t nullable;
+	int32_t n_buffers;    /* IPC buffers this node consumes */
+	int32_t decimal_width;
+	int32_t decimal_scale;
+	int64_t param;        /* fixed size / list size / multiplier / divisor */
+	int64_t dict_id;      /* dictionary id, -1 if the field is not dictionary encoded */
+	int32_t index_type_id; /* b2a_type_id of the dictionary indices (when dict_id >= 0) */
+	int32_t index_width;
+} b2a_field_info;
+
+typedef struct b2a_ipc_buffer { /* scan_arrow_ipc argument: LIST(STRUCT(ptr POINTER, size UBIGINT)) */
+	const void *ptr;
+	uint64_t size;
+} b2a_ipc_buffer;
+
+typedef struct b2a_batch_info {
+	uint64_t rows;
+	uint64_t body_offset;  /* offset of the message body inside the stream image */
+	uint64_t body_length;
+	uint64_t meta_offset;  /* offset of the 8-byte message prefix */
+	uint64_t buffer_bytes; /* sum of Buffer.length over projected columns (algorithmic input bytes) */
+	uint32_t compressed;   /* BodyCompression present */
+	uint32_t pad;
+} b2a_batch_info;
+
+/* Where one field of one record batch landed in the output arena.
+ * Layout of a decoded column = the reference's per-2 048-row vectors laid end to end:
+ * chunk k of the batch is rows [k*2048, (k+1)*2048) of every slab. */
+typedef struct b2a_column_out {
+	uint64_t rows;         /* FieldNode.length */
+	uint64_t null_count;   /* FieldNode.null_count */
+	uint64_t data_off;     /* rows * out_width bytes, B2A_NONE if the type has no flat data */
+	uint64_t validity_off; /* ceil(rows/64) uint64 words; B2A_NONE = mask untouched (all valid) */
+	uint64_t aux_off;      /* LIST/MAP: uint64[ceil(rows/2048)+1] child start row of each chunk (+ end) */
+	uint64_t chars_off;    /* strings: stream-image offset of the character buffer (pointer base) */
+	uint64_t chars_len;
+	uint64_t stats_off;    /* uint64: valid-row count computed on device (popc of the mask) */
+} b2a_column_out;
+
+/* Pushed-down predicate: ConstantFilter{comparison, constant} on a top-level integer-like column. */
+typedef enum b2a_cmp { B2A_CMP_EQ = 0, B2A_CMP_NE, B2A_CMP_LT, B2A_CMP_LE, B2A_CMP_GT, B2A_CMP_GE } b2a_cmp;
+typedef struct b2a_predicate {
+	uint32_t column; /* index into the projected top-level columns */
+	uint32_t cmp;    /* b2a_cmp */
+	int64_t constant;
+} b2a_predicate;
+
+typedef struct b2a_reader b2a_reader;
+typedef struct b2a_scan b2a_scan;
+
+const char *b2a_version(void);
+const char *b2a_last_error(void);
+int b2a_device_count(int *n);
+
+/* ---------------- src/ipc: framing + flatbuffer slicing (host) ---------------- */
+int b2a_reader_open_file(const char *path, b2a_reader **out);
+int b2a_reader_open_buffers(const b2a_ipc_buffer *bufs, uint32_t n, b2a_reader **out);
+void b2a_reader_close(b2a_reader *r);
+/* n_top: projected top-level columns; n_flat: nodes of the (projected) flattened tree */
+int b2a_reader_num_fields(b2a_reader *r, uint32_t *n_top, uint32_t *n_flat);
+int b2a_reader_field(b2a_reader *r, uint32_t flat_index, b2a_field_info *out);
+int b2a_reader_set_projection(b2a_reader *r, const char *const *names, uint32_t n);
+int b2a_reader_num_batches(b2a_reader *r, uint64_t *n_batches, uint64_t *n_rows);
+int b2a_reader_batch_info(b2a_reader *r, uint64_t batch, b2a_batch_info *out);
+/* the host bytes of the stream (mmap of the file, or the caller's single buffer) */
+int b2a_reader_image(b2a_reader *r, const void **data, uint64_t *size);
+int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, const char **value, uint32_t *n);
+
+/* ---------------- src/scanner + kernels: record batches -> DuckDB vectors ---------------- */
+int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, b2a_scan **out);
+void b2a_scan_destroy(b2a_scan *s);
+int b2a_scan_sizes(b2a_scan *s, uint64_t *image_lo, uint64_t *image_bytes, uint64_t *out_bytes,
+                   uint64_t *algorithmic_bytes, uint64_t *n_tasks, uint64_t *n_tiles);
+/* Host image -> device (one cudaMemcpyAsync per call; `host_image` should be pinned for full PCIe rate). */
+int b2a_scan_upload(b2a_scan *s, void *cuda_stream);
+/* Or: the [image_lo, image_lo+image_bytes) slice of the stream is already resident at d_image. */
+int b2a_scan_set_device_image(b2a_scan *s, const void *d_image);
+/* Launch the decode kernels.  d_out = caller-owned device arena of out_bytes (256-byte aligned).
+ * string_ptr_base: address that stream-image offset `image_lo` maps to in the address space of whoever
+ * consumes the string_t pointers (0 => the device image itself). */
+int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cuda_stream);
+/* Block until `cuda_stream` drains and turn the device error word into a status. */
+int b2a_scan_finish(b2a_scan *s, void *cuda_stream);
+int b2a_scan_download(b2a_scan *s, const void *d_out, void *h_out, void *cuda_stream);
+int b2a_scan_column(b2a_scan *s, uint64_t batch, uint32_t flat_field, b2a_column_out *out);
+/* Dictionary of a dictionary-encoded field (decoded once per scan, shared by every batch). */
+int b2a_scan_dictionary(b2a_scan *s, uint32_t flat_field, b2a_column_out *out, uint32_t *dict_flat_field);
+uint64_t b2a_scan_gpu_launches(b2a_scan *s);
+
+/* Predicates -> selection vectors: for every 2 048-row chunk of every batch, sel_t[<=2048] + count.
+ * d_sel: uint32[total_chunks * 2048]; d_count: uint32[total_chunks]; d_total: uint64 (sum of counts). */
+int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds, void *d_sel,
+                    void *d_count, void *d_total, void *cuda_stream);
+int b2a_scan_num_chunks(b2a_scan *s, uint64_t *n_chunks);
+/* Q6-style consumer: sum(a*b) over selected rows of two int64 DECIMAL columns (HUGEINT accumulator, lo/hi). */
+int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_t col_b, const void *d_sel,
+                         const void *d_count, void *d_result_i128, void *cuda_stream);
+
+/* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
+int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2ARROW_H */
