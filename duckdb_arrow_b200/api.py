@@ -1,0 +1,365 @@
+"""Host-side mirror of the reference extension's read surface, on top of the C ABI (include/b2arrow.h).
+
+    read_arrow(path | [paths], columns=...)      src/scanner/read_arrow.cpp:44-86
+    scan_arrow_ipc([(ptr,size) | bytes-like])    src/scanner/scan_arrow_ipc.cpp:20-64
+    ArrowIPCReader / ArrowScan                   IPCStreamReader / ArrowFileScan (src/ipc, src/file_scanner)
+
+PyTorch is used only for device memory and streams.  Nothing here computes on the CPU: decoding always
+goes through b2a_scan_decode and fails loudly without a CUDA device."""
+from __future__ import annotations
+
+import ctypes as C
+import glob as _glob
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _lib
+from ._lib import B2A_NONE, VECTOR_SIZE, B2AError, check, lib
+
+
+@dataclass
+class Field:
+    index: int
+    name: str
+    format: str
+    type: str
+    op: str
+    out_width: int
+    src_width: int
+    children: list
+    parent: int
+    nullable: bool
+    decimal_width: int
+    decimal_scale: int
+    param: int
+    dict_id: int
+    index_type: str
+
+
+class ArrowIPCReader:
+    """Framing + slicing of one Arrow IPC stream / file (host only)."""
+
+    def __init__(self, handle, keepalive=None):
+        self._h = handle
+        self._keep = keepalive
+        n_top, n_flat = C.c_uint32(), C.c_uint32()
+        check(lib.b2a_reader_num_fields(self._h, C.byref(n_top), C.byref(n_flat)))
+        self.n_flat = n_flat.value
+        self.fields: list[Field] = []
+        for i in range(self.n_flat):
+            fi = _lib.FieldInfo()
+            check(lib.b2a_reader_field(self._h, i, C.byref(fi)))
+            self.fields.append(Field(i, fi.name.decode(), fi.format.decode(), _lib.TYPE_NAMES[fi.type_id],
+                                     _lib.OP_NAMES[fi.op], fi.out_width, fi.src_width, [], fi.parent,
+                                     bool(fi.nullable), fi.decimal_width, fi.decimal_scale, fi.param, fi.dict_id,
+                                     _lib.TYPE_NAMES[fi.index_type_id]))
+        for f in self.fields:
+            if f.parent >= 0:
+                self.fields[f.parent].children.append(f.index)
+        self.columns = [f for f in self.fields if f.parent < 0]
+        self.projection = None
+
+    @classmethod
+    def open_file(cls, path: str) -> "ArrowIPCReader":
+        h = C.c_void_p()
+        check(lib.b2a_reader_open_file(path.encode(), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def open_buffers(cls, buffers) -> "ArrowIPCReader":
+        """buffers: list of objects exposing the buffer protocol, or (ptr, size) tuples — the
+        LIST(STRUCT(ptr POINTER, size UBIGINT)) argument of scan_arrow_ipc."""
+        keep, arr = [], (_lib.IpcBuffer * len(buffers))()
+        for i, b in enumerate(buffers):
+            if isinstance(b, tuple):
+                arr[i].ptr, arr[i].size = b
+            else:
+                a = np.frombuffer(b, dtype=np.uint8)
+                keep.append(a)
+                arr[i].ptr, arr[i].size = a.ctypes.data, a.size
+        h = C.c_void_p()
+        check(lib.b2a_reader_open_buffers(arr, len(buffers), C.byref(h)))
+        return cls(h, keep)
+
+    def close(self):
+        if self._h:
+            lib.b2a_reader_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_projection(self, names: list[str]):
+        arr = (C.c_char_p * len(names))(*[n.encode() for n in names])
+        check(lib.b2a_reader_set_projection(self._h, arr, len(names)))
+        self.projection = list(names)
+
+    @property
+    def num_batches(self) -> int:
+        nb, nr = C.c_uint64(), C.c_uint64()
+        check(lib.b2a_reader_num_batches(self._h, C.byref(nb), C.byref(nr)))
+        return nb.value
+
+    @property
+    def num_rows(self) -> int:
+        nb, nr = C.c_uint64(), C.c_uint64()
+        check(lib.b2a_reader_num_batches(self._h, C.byref(nb), C.byref(nr)))
+        return nr.value
+
+    def batch_info(self, i: int) -> _lib.BatchInfo:
+        bi = _lib.BatchInfo()
+        check(lib.b2a_reader_batch_info(self._h, i, C.byref(bi)))
+        return bi
+
+    def image(self) -> np.ndarray:
+        p, n = C.c_void_p(), C.c_uint64()
+        check(lib.b2a_reader_image(self._h, C.byref(p), C.byref(n)))
+        if n.value == 0:
+            return np.zeros(0, np.uint8)
+        return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(n.value,))
+
+    def schema_metadata(self) -> dict:
+        out, n, k, v = {}, C.c_uint32(), C.c_char_p(), C.c_char_p()
+        check(lib.b2a_reader_schema_metadata(self._h, 0, C.byref(k), C.byref(v), C.byref(n)))
+        for i in range(n.value):
+            check(lib.b2a_reader_schema_metadata(self._h, i, C.byref(k), C.byref(v), C.byref(n)))
+            out[k.value.decode()] = v.value.decode()
+        return out
+
+    def output_columns(self) -> list[Field]:
+        if self.projection is None:
+            return self.columns
+        names = _dedup([c.name for c in self.columns])
+        by = {n: c for n, c in zip(names, self.columns)}
+        return [by[n] for n in self.projection]
+
+
+def _dedup(names):
+    """QueryResult::DeduplicateColumns (duckdb/src/main/query_result.cpp:71-93)."""
+    seen, out = {}, []
+    for name in names:
+        low = name.lower()
+        if low not in seen:
+            seen[low] = 1
+            out.append(name)
+        else:
+            new = f"{name}_{seen[low]}"
+            while new.lower() in seen:
+                seen[low] += 1
+                new = f"{name}_{seen[low]}"
+            seen[new.lower()] = 1
+            out.append(new)
+    return out
+
+
+class ArrowScan:
+    """One scan of a batch range of a reader on one GPU (b2a_scan)."""
+
+    def __init__(self, reader: ArrowIPCReader, device: int = 0, batch_lo: int = 0, batch_hi: int | None = None):
+        self.reader = reader
+        self.device = device
+        hi = reader.num_batches if batch_hi is None else batch_hi
+        self.batch_lo, self.batch_hi = batch_lo, hi
+        h = C.c_void_p()
+        check(lib.b2a_scan_create(reader._h, device, batch_lo, hi, C.byref(h)))
+        self._h = h
+        v = [C.c_uint64() for _ in range(6)]
+        check(lib.b2a_scan_sizes(self._h, *[C.byref(x) for x in v]))
+        (self.image_lo, self.image_bytes, self.out_bytes, self.algorithmic_bytes, self.n_tasks,
+         self.n_tiles) = [x.value for x in v]
+        nc = C.c_uint64()
+        check(lib.b2a_scan_num_chunks(self._h, C.byref(nc)))
+        self.n_chunks = nc.value
+        self.d_out = None
+        self.d_image = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.b2a_scan_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- device plumbing (torch: memory + streams only)
+    def _torch(self):
+        import torch
+        if not torch.cuda.is_available():
+            raise B2AError(5, "no CUDA device: the Arrow IPC scan path has no CPU fallback")
+        return torch
+
+    def _stream_ptr(self):
+        torch = self._torch()
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def upload(self):
+        """H2D of the stream image slice (internally allocated device buffer)."""
+        check(lib.b2a_scan_upload(self._h, self._stream_ptr()))
+
+    def set_device_image(self, d_image):
+        """d_image: torch uint8 CUDA tensor holding image[image_lo : image_lo+image_bytes] (256-byte aligned)."""
+        self.d_image = d_image
+        check(lib.b2a_scan_set_device_image(self._h, C.c_void_p(d_image.data_ptr())))
+
+    def alloc_out(self):
+        torch = self._torch()
+        if self.d_out is None:
+            self.d_out = torch.empty(self.out_bytes, dtype=torch.uint8, device=f"cuda:{self.device}")
+        return self.d_out
+
+    def decode(self, d_out=None, string_ptr_base: int = 0):
+        d_out = self.alloc_out() if d_out is None else d_out
+        check(lib.b2a_scan_decode(self._h, C.c_void_p(d_out.data_ptr()), string_ptr_base, self._stream_ptr()))
+        return d_out
+
+    def finish(self):
+        check(lib.b2a_scan_finish(self._h, self._stream_ptr()))
+
+    def download(self, d_out=None, h_out=None) -> np.ndarray:
+        torch = self._torch()
+        d_out = self.d_out if d_out is None else d_out
+        if h_out is None:
+            h_out = torch.empty(self.out_bytes, dtype=torch.uint8, pin_memory=True)
+        check(lib.b2a_scan_download(self._h, C.c_void_p(d_out.data_ptr()), C.c_void_p(h_out.data_ptr()),
+                                    self._stream_ptr()))
+        torch.cuda.current_stream(self.device).synchronize()
+        return h_out.numpy()
+
+    @property
+    def gpu_launches(self) -> int:
+        return int(lib.b2a_scan_gpu_launches(self._h))
+
+    # -- layout
+    def column(self, batch: int, flat: int) -> _lib.ColumnOut:
+        co = _lib.ColumnOut()
+        check(lib.b2a_scan_column(self._h, batch, flat, C.byref(co)))
+        return co
+
+    def dictionary(self, flat: int) -> _lib.ColumnOut:
+        co, df = _lib.ColumnOut(), C.c_uint32()
+        check(lib.b2a_scan_dictionary(self._h, flat, C.byref(co), C.byref(df)))
+        return co
+
+
+def read_arrow(path, columns: list[str] | None = None, device: int = 0) -> "DecodedScan":
+    """`FROM read_arrow('x.arrows')`: full scan of one file (or a list / glob of files) into DuckDB vectors.
+    Returns the decoded vectors on the host in canonical layout (see DecodedScan)."""
+    paths = path if isinstance(path, (list, tuple)) else (sorted(_glob.glob(path)) if any(c in path for c in "*?[") else [path])
+    if not paths:
+        raise B2AError(2, f'No files found that match the pattern "{path}"')
+    parts = []
+    for p in paths:
+        r = ArrowIPCReader.open_file(p)
+        if columns:
+            r.set_projection(columns)
+        parts.append(_scan_to_host(r, device))
+    return parts[0] if len(parts) == 1 else parts
+
+
+def scan_arrow_ipc(buffers, columns: list[str] | None = None, device: int = 0) -> "DecodedScan":
+    r = ArrowIPCReader.open_buffers(buffers)
+    if columns:
+        r.set_projection(columns)
+    return _scan_to_host(r, device)
+
+
+def _scan_to_host(reader: ArrowIPCReader, device: int) -> "DecodedScan":
+    scan = ArrowScan(reader, device)
+    scan.upload()
+    image = reader.image()
+    # string_t pointers refer to the HOST copy of the stream, exactly where the reference's pointers point
+    base = image.ctypes.data + scan.image_lo if image.size else 0
+    scan.decode(string_ptr_base=base)
+    scan.finish()
+    arena = scan.download()
+    return DecodedScan(scan, arena, image, base - scan.image_lo if image.size else 0)
+
+
+class DecodedScan:
+    """Host copy of a decoded scan: `arena` (the output layout of b2a_scan_column) + the stream image the
+    string_t pointers refer to."""
+
+    def __init__(self, scan: ArrowScan, arena: np.ndarray, image: np.ndarray, ptr_origin: int):
+        self.scan, self.arena, self.image, self.ptr_origin = scan, arena, image, ptr_origin
+        self.reader = scan.reader
+
+    @property
+    def num_rows(self):
+        return sum(self.reader.batch_info(b).rows for b in range(self.scan.batch_lo, self.scan.batch_hi))
+
+    def column(self, batch: int, flat: int) -> "ColumnView":
+        return ColumnView(self, self.scan.column(batch, flat), self.reader.fields[flat], batch)
+
+
+class ColumnView:
+    """numpy views of one decoded field of one batch, in the canonical comparison form of SURVEY §8c."""
+
+    def __init__(self, ds: DecodedScan, co: _lib.ColumnOut, field: Field, batch: int, is_dict_values=False):
+        self.ds, self.co, self.field, self.batch = ds, co, field, batch
+        self.rows = int(co.rows)
+        self.is_dict_values = is_dict_values
+
+    @property
+    def is_dictionary(self):
+        return self.field.dict_id >= 0 and not self.is_dict_values
+
+    @property
+    def width(self):
+        return 4 if self.is_dictionary else self.field.out_width
+
+    @property
+    def valid(self) -> np.ndarray:
+        """bool[rows] — first `rows` bits of the ValidityMask; all True when the mask was left untouched."""
+        if self.field.type == "SQLNULL":
+            return np.zeros(self.rows, bool)
+        if self.co.validity_off == B2A_NONE:
+            return np.ones(self.rows, bool)
+        nbytes = (self.rows + 7) // 8
+        raw = self.ds.arena[self.co.validity_off: self.co.validity_off + nbytes]
+        return np.unpackbits(raw, bitorder="little")[: self.rows].astype(bool)
+
+    def validity_words(self, extra_rows=0) -> np.ndarray:
+        n = (self.rows + extra_rows + 63) // 64
+        return self.ds.arena[self.co.validity_off: self.co.validity_off + 8 * n].view(np.uint64)
+
+    @property
+    def data(self) -> np.ndarray:
+        """uint8[rows, width]"""
+        w = self.width
+        if w == 0 or self.co.data_off == B2A_NONE:
+            return np.zeros((self.rows, 0), np.uint8)
+        return self.ds.arena[self.co.data_off: self.co.data_off + self.rows * w].reshape(self.rows, w)
+
+    @property
+    def valid_count(self) -> int:
+        if self.co.stats_off == B2A_NONE:
+            return self.rows
+        return int(self.ds.arena[self.co.stats_off: self.co.stats_off + 8].view(np.uint64)[0])
+
+    def chunk_child_starts(self) -> np.ndarray:
+        n = (self.rows + VECTOR_SIZE - 1) // VECTOR_SIZE + 1
+        return self.ds.arena[self.co.aux_off: self.co.aux_off + 8 * n].view(np.uint64)
+
+    def children(self) -> list["ColumnView"]:
+        if self.is_dictionary:
+            return []
+        return [self.ds.column(self.batch, c) for c in self.field.children]
+
+    def dictionary(self) -> "ColumnView":
+        co = self.ds.scan.dictionary(self.field.index)
+        return ColumnView(self.ds, co, self.field, self.batch, is_dict_values=True)
+
+    def string_parts(self):
+        """(len u32[rows], inline/prefix bytes uint8[rows,12], pointer offset from the column's char buffer i64[rows])"""
+        d = self.data
+        lens = d[:, 0:4].copy().view(np.uint32).ravel()
+        ptr = d[:, 8:16].copy().view(np.uint64).ravel().astype(np.int64)
+        rel = ptr - np.int64(self.ds.ptr_origin + int(self.co.chars_off))
+        return lens, d[:, 4:16], rel

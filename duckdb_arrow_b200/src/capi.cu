@@ -416,3 +416,130 @@ int b2a_scan_num_chunks(b2a_scan *s, uint64_t *n_chunks) {
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------ one-call host path (e2e)
+// read_arrow with HOST buffers in and HOST vectors out: the stream image goes up in slices of whole record
+// batches on one stream, each slice is decoded as soon as it has landed, and its vectors go down on a third
+// stream, so H2D, decode and D2H overlap (PCIe is full duplex).  string_t pointers refer to the host image,
+// exactly where the reference's pointers point (zero-copy string payloads).
+struct HostPipe {
+	cudaStream_t in = nullptr, compute = nullptr, out = nullptr;
+	std::vector<cudaEvent_t> ev_in, ev_c;
+	uint8_t *d_out = nullptr;
+	uint64_t d_out_bytes = 0;
+};
+static thread_local HostPipe g_pipe;
+
+extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices) {
+	NEED_DEVICE(s);
+	const ScanPlan &p = s->plan;
+	HostPipe &hp = g_pipe;
+	if (!hp.in) {
+		CUDA_OK(cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking));
+		CUDA_OK(cudaStreamCreateWithFlags(&hp.compute, cudaStreamNonBlocking));
+		CUDA_OK(cudaStreamCreateWithFlags(&hp.out, cudaStreamNonBlocking));
+	}
+	const uint64_t image_bytes = p.image_hi - p.image_lo;
+	if (!s->d_image_owned) {
+		CUDA_OK(cudaMalloc(&s->d_image_owned, image_bytes + 64));
+	}
+	s->d_image = s->d_image_owned;
+	if (hp.d_out_bytes < p.out_bytes) {
+		cudaFree(hp.d_out);
+		hp.d_out = nullptr;
+		CUDA_OK(cudaMalloc(&hp.d_out, p.out_bytes));
+		hp.d_out_bytes = p.out_bytes;
+	}
+	const uint64_t n_batches = p.batch_hi - p.batch_lo;
+	if (n_slices == 0) {
+		n_slices = 1;
+	}
+	if (n_slices > n_batches) {
+		n_slices = static_cast<uint32_t>(n_batches ? n_batches : 1);
+	}
+	while (hp.ev_in.size() < n_slices + 1) {
+		cudaEvent_t a, b;
+		CUDA_OK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+		CUDA_OK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+		hp.ev_in.push_back(a);
+		hp.ev_c.push_back(b);
+	}
+	const uint8_t *h_image = s->r->reader.Image();
+	uint8_t *h_out = static_cast<uint8_t *>(h_out_pinned);
+	if (p.stats_bytes) {
+		CUDA_OK(cudaMemsetAsync(hp.d_out + p.stats_base, 0, p.stats_bytes, hp.compute));
+	}
+	DecodeLaunch l;
+	l.d_tasks = s->d_tasks;
+	l.d_tile_task = s->d_tile_task;
+	l.image_origin = s->d_image - p.image_lo;
+	l.out = hp.d_out;
+	l.string_ptr_origin = reinterpret_cast<uint64_t>(h_image);
+	l.d_err = s->d_err;
+	l.d_variadic = s->d_variadic;
+	l.sm_count = s->sm_count;
+
+	uint64_t up_to = p.image_lo; // image bytes already scheduled for upload
+	for (uint32_t sl = 0; sl < n_slices; sl++) {
+		const uint64_t b0 = n_batches * sl / n_slices, b1 = n_batches * (sl + 1) / n_slices;
+		if (b0 == b1) {
+			continue;
+		}
+		// upload everything up to the end of this slice's last batch (covers dictionary messages in between)
+		uint64_t hi = 0;
+		for (uint64_t b = b0; b < b1; b++) {
+			hi = std::max(hi, p.batch_image_hi[b]);
+		}
+		if (sl + 1 == n_slices) {
+			hi = p.image_hi;
+		}
+		if (hi > up_to) {
+			CUDA_OK(cudaMemcpyAsync(s->d_image_owned + (up_to - p.image_lo), h_image + up_to, hi - up_to,
+			                        cudaMemcpyHostToDevice, hp.in));
+			up_to = hi;
+		}
+		CUDA_OK(cudaEventRecord(hp.ev_in[sl], hp.in));
+		CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[sl], 0));
+		l.tile_begin = p.batch_tile0[b0];
+		l.n_tiles = p.batch_tile0[b1] - p.batch_tile0[b0];
+		int e = LaunchDecode(l, hp.compute);
+		if (e != 0) {
+			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+		}
+		if (l.n_tiles) {
+			s->launches++;
+		}
+		CUDA_OK(cudaEventRecord(hp.ev_c[sl], hp.compute));
+		CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[sl], 0));
+		const uint64_t o0 = p.batch_out0[b0], o1 = p.batch_out0[b1];
+		if (o1 > o0) {
+			CUDA_OK(cudaMemcpyAsync(h_out + o0, hp.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, hp.out));
+		}
+	}
+	// dictionaries (decoded once per scan) + the popcount cells live after the last batch
+	const uint32_t tail_tile0 = p.batch_tile0.empty() ? 0 : p.batch_tile0.back();
+	const uint64_t tail_out0 = p.batch_out0.empty() ? 0 : p.batch_out0.back();
+	if (up_to < p.image_hi) {
+		CUDA_OK(cudaMemcpyAsync(s->d_image_owned + (up_to - p.image_lo), h_image + up_to, p.image_hi - up_to,
+		                        cudaMemcpyHostToDevice, hp.in));
+	}
+	CUDA_OK(cudaEventRecord(hp.ev_in[n_slices], hp.in));
+	CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[n_slices], 0));
+	l.tile_begin = tail_tile0;
+	l.n_tiles = static_cast<uint32_t>(p.tile_task.size()) - tail_tile0;
+	if (l.n_tiles) {
+		int e = LaunchDecode(l, hp.compute);
+		if (e != 0) {
+			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+		}
+		s->launches++;
+	}
+	CUDA_OK(cudaEventRecord(hp.ev_c[n_slices], hp.compute));
+	CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[n_slices], 0));
+	if (p.out_bytes > tail_out0) {
+		CUDA_OK(cudaMemcpyAsync(h_out + tail_out0, hp.d_out + tail_out0, p.out_bytes - tail_out0, cudaMemcpyDeviceToHost,
+		                        hp.out));
+	}
+	CUDA_OK(cudaStreamSynchronize(hp.out));
+	return b2a_scan_finish(s, hp.compute);
+}

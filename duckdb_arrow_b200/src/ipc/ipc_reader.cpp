@@ -135,16 +135,28 @@ bool Reader::ReadNextMessage(uint64_t &pos) {
 			}
 			SchemaParser::ParseMessageSchema(meta, meta_len, schema);
 			have_schema = true;
-			// per-flat-field first buffer index
+			// nodes / fixed buffers one RecordBatch must carry (dictionary-encoded fields contribute only their
+			// index array: validity + indices, and none of the value type's children)
 			flat_buffer_start.clear();
-			int nbuf = 0;
-			for (auto *f : schema.flat) {
-				flat_buffer_start.push_back(nbuf);
-				nbuf += f->n_buffers;
-				if (f->variadic) {
-					has_variadic = true;
+			struct Count {
+				static void Go(const Field &f, int &nodes, int &bufs, bool &variadic) {
+					nodes++;
+					if (f.dict_id >= 0) {
+						bufs += 2;
+						return;
+					}
+					bufs += f.n_buffers;
+					variadic = variadic || f.variadic;
+					for (auto &c : f.children) {
+						Go(*c, nodes, bufs, variadic);
+					}
 				}
+			};
+			int nodes = 0, nbuf = 0;
+			for (auto &f : schema.fields) {
+				Count::Go(*f, nodes, nbuf, has_variadic);
 			}
+			flat_buffer_start.push_back(nodes);
 			flat_buffer_start.push_back(nbuf);
 		} else if (header_type == 3) {
 			fb::Table rb = msg.table(2);
@@ -247,9 +259,9 @@ void Reader::ParseRecordBatch(const uint8_t *tbl_buf, size_t tbl_len, size_t tab
 		out.variadic_counts.push_back(b.rd<int64_t>(vdata + 8 * size_t(i)));
 	}
 	if (!is_dictionary) {
-		if (n_nodes != schema.flat.size()) {
+		if (n_nodes != static_cast<uint32_t>(flat_buffer_start.front())) {
 			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has " + std::to_string(n_nodes) + " field nodes, schema has " +
-			                         std::to_string(schema.flat.size()));
+			                         std::to_string(flat_buffer_start.front()));
 		}
 		uint64_t expect = static_cast<uint64_t>(flat_buffer_start.back());
 		for (auto c : out.variadic_counts) {

@@ -396,9 +396,53 @@ __device__ __forceinline__ void op_string_view(const b2a_task &t, const uint8_t 
 // The reference rebases every 2 048-row chunk to its own first offset (cur_offset starts at 0 per call);
 // aux[k] receives the child row where chunk k starts, aux[n_chunks] the end.
 // ------------------------------------------------------------------------------------------------
+// Row of THIS list column at which the reference's conversion call that covers row i started.  For a top-level
+// list that is the 2 048-row chunk start.  A list nested under other lists / fixed-size lists is converted once
+// per chunk of the TOP-LEVEL column, over the child range that chunk maps to, so the start is
+// g(k) = offs_{d-1}[...offs_1[k*2048]] for the chunk k that contains i (ArrowToDuckDBList :234-278 recursion).
+// rebase table (in `variadic`): [top_rows, n_levels, (kind, value) x n_levels], kind 0/1 = list32/64 (value = image
+// offset of the ancestor's offsets), kind 2 = fixed-size list (value = list size).
+__device__ __forceinline__ uint64_t rebase_eval(const uint64_t *__restrict__ tab, const uint8_t *__restrict__ image,
+                                                uint64_t k, bool swap) {
+	uint64_t r = k * B2A_VECTOR_SIZE;
+	if (r > tab[0]) {
+		r = tab[0];
+	}
+	const uint64_t n = tab[1];
+	for (uint64_t l = 0; l < n; l++) {
+		const uint64_t kind = tab[2 + 2 * l], val = tab[3 + 2 * l];
+		if (kind == 2) {
+			r *= val;
+		} else if (kind == 0) {
+			r = load_off<uint32_t>(image + val, r, swap);
+		} else {
+			r = load_off<uint64_t>(image + val, r, swap);
+		}
+	}
+	return r;
+}
+__device__ __forceinline__ uint64_t chunk_base_row(const b2a_task &t, const uint8_t *__restrict__ image,
+                                                   const uint64_t *__restrict__ variadic, uint64_t i, bool swap) {
+	if (t.src2_len == 0) {
+		return i & ~uint64_t(B2A_VECTOR_SIZE - 1);
+	}
+	const uint64_t *tab = variadic + t.variadic0;
+	uint64_t lo = 0, hi = (tab[0] + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE; // chunks of the top-level column
+	while (hi - lo > 1) { // largest k with g(k) <= i
+		uint64_t mid = (lo + hi) >> 1;
+		if (rebase_eval(tab, image, mid, swap) <= i) {
+			lo = mid;
+		} else {
+			hi = mid;
+		}
+	}
+	return rebase_eval(tab, image, lo, swap);
+}
+
 template <typename OFF>
 __device__ __forceinline__ void op_list(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
-                                        uint64_t row0, uint64_t nrows, uint32_t *err) {
+                                        uint64_t row0, uint64_t nrows, const uint64_t *__restrict__ variadic,
+                                        uint32_t *err) {
 	const uint8_t *offs = image + t.src;
 	const bool swap = t.flags & B2A_TASK_F_BSWAP;
 	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
@@ -406,7 +450,7 @@ __device__ __forceinline__ void op_list(const b2a_task &t, const uint8_t *__rest
 	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
 		OFF o0 = load_off<OFF>(offs, i, swap);
 		OFF o1 = load_off<OFF>(offs, i + 1, swap);
-		OFF cb = load_off<OFF>(offs, i & ~uint64_t(B2A_VECTOR_SIZE - 1), swap);
+		OFF cb = load_off<OFF>(offs, chunk_base_row(t, image, variadic, i, swap), swap);
 		if (o1 < o0 || o0 < cb) {
 			raise(err, B2A_DEV_BAD_OFFSETS);
 		}
@@ -604,11 +648,12 @@ __device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__re
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
-    b2a_decode_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
+    b2a_decode_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t tile_begin,
+                      uint32_t tile_end,
                       const uint8_t *__restrict__ image, uint8_t *__restrict__ out, uint64_t ptr_origin,
                       uint32_t *err, const uint64_t *__restrict__ variadic) {
 	__shared__ b2a_task s_task;
-	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+	for (uint32_t tile = tile_begin + blockIdx.x; tile < tile_end; tile += gridDim.x) {
 		const uint32_t ti = __ldg(tile_task + tile);
 		__syncthreads(); // previous tile's readers are done with s_task
 		if (threadIdx.x < sizeof(b2a_task) / 16) {
@@ -648,10 +693,10 @@ __global__ void __launch_bounds__(kThreads)
 			op_blob_fixed(t, image, out, row0, nrows, ptr_origin);
 			break;
 		case B2A_OP_LIST32:
-			op_list<uint32_t>(t, image, out, row0, nrows, err);
+			op_list<uint32_t>(t, image, out, row0, nrows, variadic, err);
 			break;
 		case B2A_OP_LIST64:
-			op_list<uint64_t>(t, image, out, row0, nrows, err);
+			op_list<uint64_t>(t, image, out, row0, nrows, variadic, err);
 			break;
 		default:
 			op_scalar(t, image, out, row0, nrows, err);
@@ -664,13 +709,20 @@ int LaunchDecode(const DecodeLaunch &l, void *stream) {
 	if (l.n_tiles == 0) {
 		return 0;
 	}
-	// 8 resident CTAs of 256 threads per SM = 2 048 threads = full occupancy; grid is a multiple of the SM count
-	uint32_t grid = static_cast<uint32_t>(l.sm_count) * 8u;
+	// persistent grid: SM count x resident CTAs per SM (queried once)
+	static int ctas_per_sm = 0;
+	if (ctas_per_sm == 0) {
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, b2a_decode_kernel, kThreads, 0) != cudaSuccess ||
+		    ctas_per_sm <= 0) {
+			ctas_per_sm = 4;
+		}
+	}
+	uint32_t grid = static_cast<uint32_t>(l.sm_count) * static_cast<uint32_t>(ctas_per_sm);
 	if (grid > l.n_tiles) {
 		grid = l.n_tiles;
 	}
 	b2a_decode_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-	    l.d_tasks, l.d_tile_task, l.n_tiles, l.image_origin, l.out, l.string_ptr_origin, l.d_err, l.d_variadic);
+	    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out, l.string_ptr_origin, l.d_err, l.d_variadic);
 	return static_cast<int>(cudaGetLastError());
 }
 

@@ -12,7 +12,8 @@ namespace b2a {
 struct DecodeLaunch {
 	const b2a_task *d_tasks = nullptr;
 	const uint32_t *d_tile_task = nullptr; // tile -> task index
-	uint32_t n_tiles = 0;
+	uint32_t n_tiles = 0;   // tiles to process in this launch ...
+	uint32_t tile_begin = 0; // ... starting at this global tile
 	const uint8_t *image_origin = nullptr; // device address of stream-image offset 0 (may lie before the allocation)
 	uint8_t *out = nullptr;                // output arena
 	uint64_t string_ptr_origin = 0;        // address of stream-image offset 0 in the consumer's address space

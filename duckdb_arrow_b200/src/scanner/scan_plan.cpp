@@ -105,9 +105,9 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 
 	// ---- effective validity chain: own bitmap (only when null_count != 0 and the buffer exists,
 	// arrow_conversion.cpp:71) AND the struct / fixed-size-list ancestors
-	Chain chain;
-	if (!list_child) {
-		chain = parent_chain;
+	Chain chain = parent_chain;
+	if (list_child) {
+		chain.n = 0; // children of lists do not inherit validity (ColumnArrowToDuckDB is called without a parent mask)
 	}
 	if (nb > 0 && node.null_count != 0 && bufs[0].length > 0) {
 		NeedBytes(bufs[0], (L + 7) / 8, f, "validity");
@@ -260,6 +260,16 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		t.dst = slot.data_off = Alloc(L * 16);
 		uint64_t n_chunks_col = (L + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
 		t.aux = slot.aux_off = Alloc((n_chunks_col + 1) * 8);
+		if (!chain.levels.empty()) {
+			t.variadic0 = static_cast<uint32_t>(variadic.size());
+			t.src2_len = chain.levels.size();
+			variadic.push_back(chain.top_rows);
+			variadic.push_back(chain.levels.size());
+			for (auto &lv : chain.levels) {
+				variadic.push_back(lv.first);
+				variadic.push_back(lv.second);
+			}
+		}
 		if (L > 0) {
 			Touch(t.src, (L + 1) * ow);
 			algorithmic_out += L * 16;
@@ -284,8 +294,12 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 	switch (f.type_id) {
 	case B2A_T_LIST:
 	case B2A_T_MAP: {
-		Chain empty;
-		EmitField(reader, *f.children.at(0), rb, node_idx, buf_idx, var_idx, empty, true, true, slots, false, false);
+		Chain down = chain;
+		if (down.levels.empty()) {
+			down.top_rows = L;
+		}
+		down.levels.emplace_back(f.op == B2A_OP_LIST32 ? 0 : 1, bufs[1].offset);
+		EmitField(reader, *f.children.at(0), rb, node_idx, buf_idx, var_idx, down, true, true, slots, false, false);
 		break;
 	}
 	case B2A_T_STRUCT:
@@ -299,6 +313,10 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		break;
 	case B2A_T_ARRAY: {
 		Chain scaled = chain;
+		if (scaled.levels.empty()) {
+			scaled.top_rows = L;
+		}
+		scaled.levels.emplace_back(2, static_cast<uint64_t>(f.param));
 		for (uint32_t i = 0; i < scaled.n; i++) {
 			scaled.m[i].div *= static_cast<uint64_t>(f.param);
 		}
@@ -350,6 +368,11 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 		}
 		batch_rows.push_back(rb.rows);
 		batch_chunk0.push_back(n_chunks);
+		batch_tile0.push_back(next_tile);
+		batch_out0.push_back(out_bytes);
+		const uint64_t save_lo = image_lo, save_hi = image_hi;
+		image_lo = UINT64_MAX;
+		image_hi = 0;
 		n_chunks += (rb.rows + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
 		total_rows += rb.rows;
 		size_t node_idx = 0, buf_idx = 0, var_idx = 0;
@@ -363,7 +386,13 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 				throw Error(B2A_EINVAL, "arrow_scan: array length mismatch");
 			}
 		}
+		batch_image_lo.push_back(image_lo == UINT64_MAX ? 0 : image_lo);
+		batch_image_hi.push_back(image_hi);
+		image_lo = std::min(image_lo, save_lo);
+		image_hi = std::max(image_hi, save_hi);
 	}
+	batch_tile0.push_back(next_tile);
+	batch_out0.push_back(out_bytes);
 	// dictionaries: decoded once per scan (ArrowArrayScanState::AddDictionary, arrow_array_scan_state.cpp:29-52)
 	std::vector<int> dict_fields;
 	for (auto &kv : dict_cols) {

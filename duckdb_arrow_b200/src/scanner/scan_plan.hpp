@@ -30,6 +30,10 @@ struct ScanPlan {
 	std::vector<int> top_columns;                // projected top-level columns (indices into schema.fields)
 	std::vector<uint64_t> batch_rows;            // rows of each batch in range
 	std::vector<uint64_t> batch_chunk0;          // first global chunk index of each batch
+	// per batch (+1 sentinel): first tile, first output byte, and the image range its tasks read
+	std::vector<uint32_t> batch_tile0;
+	std::vector<uint64_t> batch_out0;
+	std::vector<uint64_t> batch_image_lo, batch_image_hi;
 
 	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
 
@@ -41,6 +45,10 @@ private:
 	struct Chain {
 		b2a_mask_ref m[B2A_MAX_MASKS];
 		uint32_t n = 0;
+		// list rebase chain (see chunk_base_row in kernels/decode.cu): ancestors between the top-level column and
+		// this field that change the row indexing
+		std::vector<std::pair<uint64_t, uint64_t>> levels; // (kind, value)
+		uint64_t top_rows = 0;
 	};
 	uint64_t Alloc(uint64_t bytes);
 	void Touch(uint64_t off, uint64_t len);
