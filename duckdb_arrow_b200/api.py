@@ -236,6 +236,43 @@ class ArrowScan:
     def gpu_launches(self) -> int:
         return int(lib.b2a_scan_gpu_launches(self._h))
 
+    # -- pushed-down filters and the Q6-style consumer (new behaviour; the reference filters above the scan)
+    def filter(self, predicates, d_out=None):
+        """predicates: [(column name | projected index, op, int constant)], ANDed.  Returns (sel, count, total):
+        torch tensors uint32[n_chunks*2048], uint32[n_chunks], uint64[1] on the device — one selection vector per
+        2 048-row DuckDB vector."""
+        torch = self._torch()
+        d_out = self.d_out if d_out is None else d_out
+        names = [f.name for f in self.reader.output_columns()]
+        arr = (_lib.Predicate * len(predicates))()
+        for i, (col, op, const) in enumerate(predicates):
+            arr[i].column = names.index(col) if isinstance(col, str) else col
+            arr[i].cmp = _lib.CMP[op]
+            arr[i].constant = int(const)
+        dev = f"cuda:{self.device}"
+        sel = torch.empty(max(1, self.n_chunks) * VECTOR_SIZE, dtype=torch.int32, device=dev)
+        count = torch.zeros(max(1, self.n_chunks), dtype=torch.int32, device=dev)
+        total = torch.zeros(1, dtype=torch.int64, device=dev)
+        check(lib.b2a_scan_filter(self._h, C.c_void_p(d_out.data_ptr()), arr, len(predicates),
+                                  C.c_void_p(sel.data_ptr()), C.c_void_p(count.data_ptr()),
+                                  C.c_void_p(total.data_ptr()), self._stream_ptr()))
+        return sel, count, total
+
+    def sum_product(self, col_a, col_b, sel=None, count=None, d_out=None) -> int:
+        """sum(a*b) over the selected rows (all rows when sel is None) as an exact Python int (HUGEINT)."""
+        torch = self._torch()
+        d_out = self.d_out if d_out is None else d_out
+        names = [f.name for f in self.reader.output_columns()]
+        ia = names.index(col_a) if isinstance(col_a, str) else col_a
+        ib = names.index(col_b) if isinstance(col_b, str) else col_b
+        res = torch.zeros(2, dtype=torch.int64, device=f"cuda:{self.device}")
+        check(lib.b2a_scan_sum_product(self._h, C.c_void_p(d_out.data_ptr()), ia, ib,
+                                       C.c_void_p(sel.data_ptr() if sel is not None else 0),
+                                       C.c_void_p(count.data_ptr() if count is not None else 0),
+                                       C.c_void_p(res.data_ptr()), self._stream_ptr()))
+        lo, hi = [int(x) for x in res.cpu().tolist()]
+        return (hi << 64) | (lo & 0xFFFFFFFFFFFFFFFF)
+
     # -- layout
     def column(self, batch: int, flat: int) -> _lib.ColumnOut:
         co = _lib.ColumnOut()

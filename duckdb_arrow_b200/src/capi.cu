@@ -34,10 +34,10 @@ struct b2a_scan {
 	const uint8_t *d_image = nullptr;   // device address of image offset plan.image_lo
 	uint64_t launches = 0;
 	// filter support
-	uint64_t *d_chunk_col = nullptr;
+	uint64_t *d_chunk_col = nullptr;   // filter: per chunk, per predicate {data, validity}
+	uint64_t *d_chunk_col2 = nullptr;  // sum_product: per chunk {a, va, b, vb}
 	uint32_t *d_chunk_rows = nullptr;
-	uint32_t chunk_col_preds = 0;
-	std::vector<uint32_t> chunk_col_key;
+	std::vector<uint32_t> chunk_col_key, chunk_col2_key;
 };
 
 static int Fail(int code, const std::string &msg) {
@@ -231,6 +231,7 @@ static void FreeScanDevice(b2a_scan *s) {
 		cudaFree(s->d_err);
 		cudaFree(s->d_image_owned);
 		cudaFree(s->d_chunk_col);
+		cudaFree(s->d_chunk_col2);
 		cudaFree(s->d_chunk_rows);
 	}
 }
@@ -542,4 +543,144 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	}
 	CUDA_OK(cudaStreamSynchronize(hp.out));
 	return b2a_scan_finish(s, hp.compute);
+}
+
+// ------------------------------------------------------------------ filter / aggregate consumers
+// Builds (and caches) the per-chunk column table for the given projected top-level columns.
+static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vector<uint32_t> &key, uint64_t **d_table,
+                      std::vector<uint8_t> *widths) {
+	const ScanPlan &p = s->plan;
+	const Schema &schema = s->r->reader.BaseSchema();
+	std::vector<int> flats;
+	for (uint32_t c : cols) {
+		if (c >= p.top_columns.size()) {
+			return Fail(B2A_EINVAL, "predicate column index out of range");
+		}
+		const Field &f = *schema.fields[static_cast<size_t>(p.top_columns[c])];
+		if (f.dict_id >= 0 || f.out_width > 8 || f.out_width == 0 || f.type_id == B2A_T_FLOAT ||
+		    f.type_id == B2A_T_DOUBLE || f.type_id == B2A_T_UBIGINT) {
+			return Fail(B2A_ENOTIMPL, "filter pushdown supports signed integer-like columns (integers, dates, "
+			                          "timestamps, DECIMAL up to 18 digits) only: column '" + f.name + "'");
+		}
+		flats.push_back(f.flat_index);
+		if (widths) {
+			widths->push_back(static_cast<uint8_t>(f.out_width));
+		}
+	}
+	if (!s->d_chunk_rows) {
+		std::vector<uint32_t> rows;
+		for (uint64_t b = 0; b < p.batch_rows.size(); b++) {
+			uint64_t left = p.batch_rows[b];
+			while (left > 0) {
+				uint32_t n = left > B2A_VECTOR_SIZE ? B2A_VECTOR_SIZE : static_cast<uint32_t>(left);
+				rows.push_back(n);
+				left -= n;
+			}
+		}
+		CUDA_OK(cudaMalloc(&s->d_chunk_rows, (rows.size() ? rows.size() : 1) * sizeof(uint32_t)));
+		CUDA_OK(cudaMemcpy(s->d_chunk_rows, rows.data(), rows.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	}
+	if (key == cols && *d_table) {
+		return B2A_OK;
+	}
+	std::vector<uint64_t> table;
+	table.reserve(p.n_chunks * 2 * cols.size());
+	for (uint64_t b = 0; b < p.batch_rows.size(); b++) {
+		const uint64_t nchunks = (p.batch_rows[b] + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
+		for (uint64_t k = 0; k < nchunks; k++) {
+			for (size_t c = 0; c < flats.size(); c++) {
+				const b2a_column_out &co = p.Column(p.batch_lo + b, static_cast<uint32_t>(flats[c]));
+				const Field &f = *schema.flat[static_cast<size_t>(flats[c])];
+				table.push_back(co.data_off + k * B2A_VECTOR_SIZE * static_cast<uint64_t>(f.out_width));
+				table.push_back(co.validity_off == B2A_NONE ? B2A_NONE : co.validity_off + k * (B2A_VECTOR_SIZE / 8));
+			}
+		}
+	}
+	cudaFree(*d_table);
+	*d_table = nullptr;
+	CUDA_OK(cudaMalloc(d_table, (table.size() ? table.size() : 1) * sizeof(uint64_t)));
+	CUDA_OK(cudaMemcpy(*d_table, table.data(), table.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
+	key = cols;
+	return B2A_OK;
+}
+
+extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds,
+                               void *d_sel, void *d_count, void *d_total, void *cuda_stream) {
+	B2A_TRY
+	NEED_DEVICE(s);
+	if (n_preds == 0 || n_preds > 8) {
+		return Fail(B2A_EINVAL, "between 1 and 8 predicates are supported");
+	}
+	std::vector<uint32_t> cols;
+	for (uint32_t i = 0; i < n_preds; i++) {
+		cols.push_back(preds[i].column);
+		if (preds[i].cmp > B2A_CMP_GE) {
+			return Fail(B2A_EINVAL, "unknown comparison");
+		}
+	}
+	std::vector<uint8_t> widths;
+	int rc = ChunkTable(s, cols, s->chunk_col_key, &s->d_chunk_col, &widths);
+	if (rc != B2A_OK) {
+		return rc;
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	CUDA_OK(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), st));
+	FilterLaunch l;
+	l.out = static_cast<const uint8_t *>(d_out);
+	l.d_chunk_col = s->d_chunk_col;
+	l.d_chunk_rows = s->d_chunk_rows;
+	l.n_chunks = s->plan.n_chunks;
+	l.n_preds = n_preds;
+	for (uint32_t i = 0; i < n_preds; i++) {
+		l.preds[i] = preds[i];
+		l.widths[i] = widths[i];
+	}
+	l.d_sel = static_cast<uint32_t *>(d_sel);
+	l.d_count = static_cast<uint32_t *>(d_count);
+	l.d_total = static_cast<unsigned long long *>(d_total);
+	l.sm_count = s->sm_count;
+	int e = LaunchFilter(l, cuda_stream);
+	if (e != 0) {
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+	}
+	if (l.n_chunks) {
+		s->launches++;
+	}
+	return B2A_OK;
+	B2A_CATCH
+}
+
+extern "C" int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_t col_b, const void *d_sel,
+                                    const void *d_count, void *d_result_i128, void *cuda_stream) {
+	B2A_TRY
+	NEED_DEVICE(s);
+	std::vector<uint32_t> cols = {col_a, col_b};
+	std::vector<uint8_t> widths;
+	int rc = ChunkTable(s, cols, s->chunk_col2_key, &s->d_chunk_col2, &widths);
+	if (rc != B2A_OK) {
+		return rc;
+	}
+	if (widths[0] != 8 || widths[1] != 8) {
+		return Fail(B2A_ENOTIMPL, "sum_product needs two 8-byte integer columns (BIGINT / DECIMAL(<=18))");
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	CUDA_OK(cudaMemsetAsync(d_result_i128, 0, 16, st));
+	SumProductLaunch l;
+	l.out = static_cast<const uint8_t *>(d_out);
+	l.d_chunk_col = s->d_chunk_col2;
+	l.d_chunk_rows = s->d_chunk_rows;
+	l.d_sel = static_cast<const uint32_t *>(d_sel);
+	l.d_count = static_cast<const uint32_t *>(d_count);
+	l.n_chunks = s->plan.n_chunks;
+	l.d_result = static_cast<unsigned long long *>(d_result_i128);
+	l.sm_count = s->sm_count;
+	int e = LaunchSumProduct(l, cuda_stream);
+	if (e != 0) {
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+	}
+	if (l.n_chunks) {
+		s->launches++;
+	}
+	return B2A_OK;
+	B2A_CATCH
 }

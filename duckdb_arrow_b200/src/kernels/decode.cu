@@ -342,22 +342,6 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 	}
 }
 
-// fixed-size binary (ArrowToDuckDBBlob FIXED_SIZE, :347-360) and UUID-less w:N blobs
-__device__ __forceinline__ void op_blob_fixed(const b2a_task &t, const uint8_t *__restrict__ image,
-                                              uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
-                                              uint64_t ptr_origin) {
-	const uint8_t *chars = image + t.src;
-	const uint64_t w = static_cast<uint64_t>(t.param);
-	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
-	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
-		uint4 v = make_uint4(0, 0, 0, 0);
-		if (t.n_masks == 0 || eff_valid(t, image, i)) {
-			v = make_string_t(chars, i * w, static_cast<uint32_t>(w), ptr_origin + t.src + i * w);
-		}
-		stg_stream16(dst + i, v);
-	}
-}
-
 // K4v: Utf8View (SetVectorStringView, :425-452; arrow_string_view_type.hpp:24-85)
 __device__ __forceinline__ void op_string_view(const b2a_task &t, const uint8_t *__restrict__ image,
                                                uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
@@ -464,6 +448,49 @@ __device__ __forceinline__ void op_list(const b2a_task &t, const uint8_t *__rest
 		if (i + 1 == t.rows) {
 			aux[(t.rows + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE] = o1;
 		}
+	}
+}
+
+// fixed-size binary (ArrowToDuckDBBlob FIXED_SIZE, :347-360).  Bug-compatible with the reference: its running
+// `offset` advances only on VALID rows (the `continue` at :353-355 skips `offset += blob_len`), so within one
+// conversion call row i reads element  call_start + (#valid rows in [call_start, i))  of the data buffer.
+__device__ __forceinline__ uint64_t count_valid(const b2a_task &t, const uint8_t *__restrict__ image, uint64_t from,
+                                                uint64_t to) {
+	uint64_t n = 0;
+	const uint64_t nbytes = (t.rows + 7) >> 3;
+	for (uint64_t w = from >> 6; (w << 6) < to; w++) {
+		uint64_t v = ~uint64_t(0);
+		for (uint32_t m = 0; m < t.n_masks; m++) {
+			v &= mask_word(t, image, m, w, nbytes);
+		}
+		const uint64_t lo = w << 6;
+		if (from > lo) {
+			v &= ~uint64_t(0) << (from - lo);
+		}
+		if (to < lo + 64) {
+			v &= (uint64_t(1) << (to - lo)) - 1;
+		}
+		n += __popcll(v);
+	}
+	return n;
+}
+
+__device__ __forceinline__ void op_blob_fixed(const b2a_task &t, const uint8_t *__restrict__ image,
+                                              uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
+                                              uint64_t ptr_origin, const uint64_t *__restrict__ variadic) {
+	const uint8_t *chars = image + t.src;
+	const uint64_t w = static_cast<uint64_t>(t.param);
+	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (t.n_masks == 0) {
+			v = make_string_t(chars, i * w, static_cast<uint32_t>(w), ptr_origin + t.src + i * w);
+		} else if (eff_valid(t, image, i)) {
+			const uint64_t call_start = chunk_base_row(t, image, variadic, i, false);
+			const uint64_t e = call_start + count_valid(t, image, call_start, i);
+			v = make_string_t(chars, e * w, static_cast<uint32_t>(w), ptr_origin + t.src + e * w);
+		}
+		stg_stream16(dst + i, v);
 	}
 }
 
@@ -690,7 +717,7 @@ __global__ void __launch_bounds__(kThreads)
 			op_string_view(t, image, out, row0, nrows, ptr_origin, variadic, err);
 			break;
 		case B2A_OP_BLOB_FIXED:
-			op_blob_fixed(t, image, out, row0, nrows, ptr_origin);
+			op_blob_fixed(t, image, out, row0, nrows, ptr_origin, variadic);
 			break;
 		case B2A_OP_LIST32:
 			op_list<uint32_t>(t, image, out, row0, nrows, variadic, err);

@@ -42,7 +42,8 @@ int LaunchFilter(const FilterLaunch &l, void *stream);
 
 struct SumProductLaunch {
 	const uint8_t *out = nullptr;
-	const uint64_t *d_chunk_col = nullptr; // per chunk: [a_off, b_off]
+	const uint64_t *d_chunk_col = nullptr; // per chunk: {a data, a validity, b data, b validity} arena offsets
+	const uint32_t *d_chunk_rows = nullptr;
 	const uint32_t *d_sel = nullptr;
 	const uint32_t *d_count = nullptr;
 	uint64_t n_chunks = 0;

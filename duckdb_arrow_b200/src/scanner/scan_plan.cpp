@@ -244,6 +244,16 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		NeedBytes(bufs[1], L * static_cast<uint64_t>(f.param), f, "data");
 		t.src = bufs[1].offset;
 		t.dst = slot.data_off = Alloc(L * 16);
+		if (!chain.levels.empty()) { // conversion-call boundaries under lists (see op_blob_fixed)
+			t.variadic0 = static_cast<uint32_t>(variadic.size());
+			t.src2_len = chain.levels.size();
+			variadic.push_back(chain.top_rows);
+			variadic.push_back(chain.levels.size());
+			for (auto &lv : chain.levels) {
+				variadic.push_back(lv.first);
+				variadic.push_back(lv.second);
+			}
+		}
 		slot.chars_off = bufs[1].offset;
 		slot.chars_len = bufs[1].length;
 		Touch(t.src, L * static_cast<uint64_t>(f.param));

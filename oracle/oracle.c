@@ -854,7 +854,7 @@ void oracle_slab_free(OSlab *s) {
 
 static void slab_reserve(OSlab *s, uint64_t extra, int with_sel) {
 	uint64_t need = s->rows + extra;
-	if (need <= s->cap && s->valid) {
+	if (need <= s->cap && s->valid && (!with_sel || s->sel)) {
 		return;
 	}
 	uint64_t cap = s->cap ? s->cap : 2048;

@@ -97,3 +97,98 @@ def test_synthetic_lineitem_dictionary(b2a, cuda_device):
     buf = lineitem.stream_bytes(200_000, seed=11, dictionary_strings=True)
     ds = b2a.scan_arrow_ipc([buf])
     compare_scan_with_oracle(ds, list(ipc.open_stream(buf)))
+
+
+# ------------------------------------------------------------------------------------------------ K9 + consumer
+def _device_scan(b2a, buf_or_path):
+    r = (b2a.ArrowIPCReader.open_file(buf_or_path) if isinstance(buf_or_path, str)
+         else b2a.ArrowIPCReader.open_buffers([buf_or_path]))
+    scan = b2a.ArrowScan(r, device=0)
+    scan.upload()
+    scan.decode()
+    scan.finish()
+    return r, scan
+
+
+def _check_filter(scan, table: pa.Table, preds, sel, count, total, batch_rows):
+    """oracle for pushed-down filters = scan, then filter (numpy over pyarrow's decoding), per 2 048-row vector"""
+    import operator
+    ops = {"=": operator.eq, "!=": operator.ne, "<": operator.lt, "<=": operator.le, ">": operator.gt, ">=": operator.ge}
+    mask = np.ones(table.num_rows, bool)
+    for col, op, const in preds:
+        c = table.column(col).combine_chunks()
+        valid = np.asarray(c.is_valid())
+        t = c.type
+        if pa.types.is_decimal(t):
+            vals = np.array([int(x.as_py().scaleb(t.scale)) if x.is_valid else 0 for x in c], dtype=np.int64) \
+                if table.num_rows < 100000 else None
+            if vals is None:
+                vals = np.frombuffer(c.buffers()[1], dtype=np.int64 if t.bit_width == 64 else np.int64)[: len(c)]
+        elif pa.types.is_date32(t):
+            vals = np.frombuffer(c.buffers()[1], dtype=np.int32)[c.offset: c.offset + len(c)].astype(np.int64)
+        else:
+            vals = c.fill_null(0).to_numpy().astype(np.int64)
+        mask &= valid & ops[op](vals, const)
+    sel, count = sel.cpu().numpy().view(np.uint32), count.cpu().numpy().view(np.uint32)
+    assert int(total.item()) == int(mask.sum())
+    chunk, row = 0, 0
+    for n in batch_rows:
+        for k in range(0, n, 2048):
+            m = mask[row + k: row + min(n, k + 2048)]
+            exp = np.nonzero(m)[0].astype(np.uint32)
+            assert count[chunk] == exp.size, f"chunk {chunk}: count {count[chunk]} != {exp.size}"
+            assert np.array_equal(sel[chunk * 2048: chunk * 2048 + exp.size], exp), f"chunk {chunk}: sel differs"
+            chunk += 1
+        row += n
+    return mask
+
+
+def test_filter_and_q6_on_synthetic_lineitem(b2a, cuda_device):
+    from tools import lineitem
+    buf = lineitem.stream_bytes(400_000, seed=5)
+    r, scan = _device_scan(b2a, buf)
+    preds = [("l_shipdate", ">=", 8766), ("l_shipdate", "<", 9131), ("l_quantity", "<", 2400)]
+    sel, count, total = scan.filter(preds)
+    t = ipc.open_stream(buf).read_all()
+    brows = [r.batch_info(i).rows for i in range(r.num_batches)]
+    mask = _check_filter(scan, t, preds, sel, count, total, brows)
+    price = np.frombuffer(t.column("l_extendedprice").combine_chunks().buffers()[1], dtype=np.int64)
+    disc = np.frombuffer(t.column("l_discount").combine_chunks().buffers()[1], dtype=np.int64)
+    exp = sum(int(a) * int(b) for a, b in zip(price[mask], disc[mask]))
+    assert scan.sum_product("l_extendedprice", "l_discount", sel, count) == exp
+    exp_all = int((price.astype(object) * disc.astype(object)).sum())
+    assert scan.sum_product("l_extendedprice", "l_discount") == exp_all
+
+
+def test_q6_known_answer_sf001(b2a, cuda_device, tmp_path):
+    """TPC-H Q6 on data/parquet-testing/lineitem_sf0_01.parquet = 1193053.2253 (test/nodejs/arrow_test.js:424)."""
+    import pyarrow.parquet as pq
+    t = pq.read_table(os.path.join(GOLDEN, "data", "lineitem_sf0_01.parquet"))
+    p = str(tmp_path / "li.arrows")
+    with ipc.new_stream(p, t.schema) as w:
+        for b in t.to_batches(max_chunksize=122880):
+            w.write_batch(b)
+    r, scan = _device_scan(b2a, p)
+    preds = [("l_shipdate", ">=", 8766), ("l_shipdate", "<", 9131), ("l_discount", ">=", 5), ("l_discount", "<=", 7),
+             ("l_quantity", "<", 24)]
+    sel, count, total = scan.filter(preds)
+    revenue = scan.sum_product("l_extendedprice", "l_discount", sel, count)
+    assert revenue == 11930532253, revenue  # DECIMAL(30,4): 1193053.2253
+
+
+def test_filter_with_nulls(b2a, cuda_device):
+    rng = np.random.default_rng(1)
+    n = 10_000
+    vals = rng.integers(-50, 50, n)
+    arr = pa.array(vals, type=pa.int32(), mask=rng.random(n) < 0.3)
+    big = pa.array(rng.integers(-2**40, 2**40, n), type=pa.int64())
+    t = pa.table({"a": arr, "b": big})
+    sink = pa.BufferOutputStream()
+    with ipc.new_stream(sink, t.schema) as w:
+        for b in t.to_batches(max_chunksize=3000):
+            w.write_batch(b)
+    buf = sink.getvalue()
+    r, scan = _device_scan(b2a, buf)
+    preds = [("a", ">", -10), ("b", "<=", 12345)]
+    sel, count, total = scan.filter(preds)
+    _check_filter(scan, t, preds, sel, count, total, [r.batch_info(i).rows for i in range(r.num_batches)])

