@@ -149,6 +149,8 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--columns", default="", help="comma-separated projection (experiments only; the metric is all 16)")
+    ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e leg, no CPU baseline, no clock soak")
     args = ap.parse_args()
     steps, warmup = max(1, args.steps), max(3, args.warmup) if args.impl != "reference" else max(0, args.warmup)
 
@@ -203,6 +205,9 @@ def main():
 
     host, size = build_stream(rows, 42 + rank, pin=True)
     reader = b2a.ArrowIPCReader.open_buffers([(host.data_ptr(), size)])
+    if args.columns:
+        reader.set_projection(args.columns.split(","))
+        config["columns"] = args.columns
     scan = b2a.ArrowScan(reader, device=local_rank)
     assert reader.num_rows == rows
     log(f"[bench] rank {rank}: image {scan.image_bytes / 1e9:.2f} GB, out {scan.out_bytes / 1e9:.2f} GB, "
@@ -253,7 +258,7 @@ def main():
 
     # ---- e2e: host stream -> H2D -> decode -> D2H host vectors
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and not args.profile:
         h_out = torch.empty(scan.out_bytes, dtype=torch.uint8, pin_memory=True)
         scan2 = b2a.ArrowScan(reader, device=local_rank)
         e_steps = max(2, min(steps, 5))
@@ -281,7 +286,7 @@ def main():
 
     # keep the GPU busy for a moment so that the 100 ms nvidia-smi sampler sees clocks under load
     t_busy = time.time()
-    while time.time() - t_busy < 1.0:
+    while time.time() - t_busy < 1.0 and not args.profile:
         for _ in range(20):
             scan.decode(d_out)
         torch.cuda.synchronize()
@@ -301,7 +306,10 @@ def main():
         except Exception:
             traffic = None
     cores = 1
-    cpu_v, cpu_sample = cpu_reference_rate(host.numpy(), size, 64, args.cpu_seconds, cores)
+    if args.profile:
+        cpu_v, cpu_sample = 0.0, "skipped (--profile)"
+    else:
+        cpu_v, cpu_sample = cpu_reference_rate(host.numpy(), size, 64, args.cpu_seconds, cores)
     out = {
         "metric": "read_arrow rows/s (lineitem, all columns)", "value": value, "unit": "rows/s",
         "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms_per_step, "higher_is_better": True,

@@ -7,6 +7,8 @@
 
 #include <cuda_runtime.h>
 
+#include <cstdlib>
+
 namespace b2a {
 
 static constexpr int kThreads = 256;
@@ -316,6 +318,51 @@ __device__ __forceinline__ uint64_t load_off<uint64_t>(const uint8_t *p, uint64_
 	return swap ? bswap64(r) : r;
 }
 
+// Rows are processed kStrUnroll at a time per thread with the loads of all rows issued before the first use
+// (offsets, then characters): the op is a dependent chain offsets -> characters -> store, so memory-level
+// parallelism has to come from independent rows.
+static constexpr int kStrUnroll = 4;
+
+struct StrFetch {
+	uint32_t w0, w1, w2, w3; // aligned words covering the bytes that end up in the string_t
+	uint32_t shift;          // bit offset of the first character inside w0
+};
+
+__device__ __forceinline__ StrFetch fetch_chars(const uint8_t *__restrict__ base, uint32_t len) {
+	StrFetch f;
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(reinterpret_cast<uintptr_t>(base) & ~uintptr_t(3));
+	f.shift = (static_cast<uint32_t>(reinterpret_cast<uintptr_t>(base)) & 3u) * 8u;
+	const uint32_t need = len > 12 ? 4u : len;
+	const uint32_t nwords = (need + (f.shift >> 3) + 3u) >> 2;
+	f.w0 = f.w1 = f.w2 = f.w3 = 0;
+	if (nwords > 0) {
+		f.w0 = __ldg(wp);
+	}
+	if (nwords > 1) {
+		f.w1 = __ldg(wp + 1);
+	}
+	if (nwords > 2) {
+		f.w2 = __ldg(wp + 2);
+	}
+	if (nwords > 3) {
+		f.w3 = __ldg(wp + 3);
+	}
+	return f;
+}
+
+__device__ __forceinline__ uint4 assemble_string_t(const StrFetch &f, uint32_t len, uint64_t ptr) {
+	uint32_t b0 = __funnelshift_r(f.w0, f.w1, f.shift);
+	if (len > 12) {
+		return make_uint4(len, b0, static_cast<uint32_t>(ptr), static_cast<uint32_t>(ptr >> 32));
+	}
+	uint32_t b1 = __funnelshift_r(f.w1, f.w2, f.shift);
+	uint32_t b2 = __funnelshift_r(f.w2, f.w3, f.shift);
+	uint32_t m0 = len >= 4 ? 0xFFFFFFFFu : ((1u << (8 * len)) - 1u);
+	uint32_t m1 = len >= 8 ? 0xFFFFFFFFu : (len > 4 ? ((1u << (8 * (len - 4))) - 1u) : 0u);
+	uint32_t m2 = len >= 12 ? 0xFFFFFFFFu : (len > 8 ? ((1u << (8 * (len - 8))) - 1u) : 0u);
+	return make_uint4(len, b0 & m0, b1 & m1, b2 & m2);
+}
+
 template <typename OFF>
 __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__restrict__ image,
                                           uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
@@ -323,22 +370,57 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 	const uint8_t *offs = image + t.src;
 	const uint8_t *chars = image + t.src2;
 	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	const bool masked = t.n_masks != 0;
+	const uint64_t src2_len = t.src2_len;
+	const uint64_t ptr_base = ptr_origin + t.src2;
 	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
-	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
-		OFF o0 = load_off<OFF>(offs, i, swap);
-		OFF o1 = load_off<OFF>(offs, i + 1, swap);
-		uint4 v = make_uint4(0, 0, 0, 0);
-		if (o1 < o0 || static_cast<uint64_t>(o1) > t.src2_len) {
-			raise(err, B2A_DEV_BAD_OFFSETS);
-		} else if (t.n_masks == 0 || eff_valid(t, image, i)) {
-			uint64_t len = static_cast<uint64_t>(o1) - static_cast<uint64_t>(o0);
-			if (len > 0xFFFFFFFFull) {
-				raise(err, B2A_DEV_STRING_4GB);
-			} else {
-				v = make_string_t(chars, o0, static_cast<uint32_t>(len), ptr_origin + t.src2 + o0);
+	const uint64_t end = row0 + nrows;
+	for (uint64_t base = row0 + threadIdx.x; base < end; base += kStrUnroll * kThreads) {
+		OFF o0[kStrUnroll], o1[kStrUnroll];
+#pragma unroll
+		for (int u = 0; u < kStrUnroll; u++) {
+			const uint64_t i = base + u * kThreads;
+			o0[u] = o1[u] = 0;
+			if (i < end) {
+				o0[u] = load_off<OFF>(offs, i, swap);
+				o1[u] = load_off<OFF>(offs, i + 1, swap);
 			}
 		}
-		stg_stream16(dst + i, v);
+		StrFetch f[kStrUnroll];
+		uint32_t len[kStrUnroll];
+		bool live[kStrUnroll];
+#pragma unroll
+		for (int u = 0; u < kStrUnroll; u++) {
+			const uint64_t i = base + u * kThreads;
+			live[u] = false;
+			len[u] = 0;
+			f[u].w0 = f[u].w1 = f[u].w2 = f[u].w3 = f[u].shift = 0;
+			if (i < end) {
+				if (o1[u] < o0[u] || static_cast<uint64_t>(o1[u]) > src2_len) {
+					raise(err, B2A_DEV_BAD_OFFSETS);
+				} else if (!masked || eff_valid(t, image, i)) {
+					const uint64_t l = static_cast<uint64_t>(o1[u]) - static_cast<uint64_t>(o0[u]);
+					if (l > 0xFFFFFFFFull) {
+						raise(err, B2A_DEV_STRING_4GB);
+					} else {
+						live[u] = true;
+						len[u] = static_cast<uint32_t>(l);
+						f[u] = fetch_chars(chars + o0[u], len[u]);
+					}
+				}
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < kStrUnroll; u++) {
+			const uint64_t i = base + u * kThreads;
+			if (i < end) {
+				uint4 v = make_uint4(0, 0, 0, 0);
+				if (live[u]) {
+					v = assemble_string_t(f[u], len[u], ptr_base + o0[u]);
+				}
+				stg_stream16(dst + i, v);
+			}
+		}
 	}
 }
 
@@ -674,20 +756,51 @@ __device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__re
 // ------------------------------------------------------------------------------------------------
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+	const uint32_t sa = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+static constexpr uint32_t kTaskVecs = sizeof(b2a_task) / 16;
+static_assert(sizeof(b2a_task) % 16 == 0, "b2a_task is copied in 16-byte pieces");
+
+// Persistent CTAs stride over the tile table.  The descriptor of the NEXT tile is fetched with cp.async while the
+// current one is processed (its task index was loaded one iteration earlier), so no tile starts with an exposed
+// tile_task -> task dependent load pair.
 __global__ void __launch_bounds__(kThreads)
     b2a_decode_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t tile_begin,
                       uint32_t tile_end,
                       const uint8_t *__restrict__ image, uint8_t *__restrict__ out, uint64_t ptr_origin,
                       uint32_t *err, const uint64_t *__restrict__ variadic) {
-	__shared__ b2a_task s_task;
-	for (uint32_t tile = tile_begin + blockIdx.x; tile < tile_end; tile += gridDim.x) {
+	__shared__ b2a_task s_task[2];
+	uint32_t tile = tile_begin + blockIdx.x;
+	if (tile >= tile_end) {
+		return;
+	}
+	const uint32_t stride = gridDim.x;
+	const bool loader = threadIdx.x < kTaskVecs;
+	uint32_t ti_next = 0;
+	if (loader) {
 		const uint32_t ti = __ldg(tile_task + tile);
-		__syncthreads(); // previous tile's readers are done with s_task
-		if (threadIdx.x < sizeof(b2a_task) / 16) {
-			reinterpret_cast<uint4 *>(&s_task)[threadIdx.x] = __ldg(reinterpret_cast<const uint4 *>(tasks + ti) + threadIdx.x);
+		reinterpret_cast<uint4 *>(&s_task[0])[threadIdx.x] = __ldg(reinterpret_cast<const uint4 *>(tasks + ti) + threadIdx.x);
+		if (tile + stride < tile_end) {
+			ti_next = __ldg(tile_task + tile + stride);
 		}
-		__syncthreads();
-		const b2a_task &t = s_task;
+	}
+	__syncthreads();
+	for (uint32_t buf = 0;; buf ^= 1) {
+		const uint32_t next = tile + stride;
+		if (loader && next < tile_end) {
+			cp_async16(reinterpret_cast<uint4 *>(&s_task[buf ^ 1]) + threadIdx.x,
+			           reinterpret_cast<const uint4 *>(tasks + ti_next) + threadIdx.x);
+			if (next + stride < tile_end) {
+				ti_next = __ldg(tile_task + next + stride);
+			}
+		}
+		const b2a_task &t = s_task[buf];
 		const uint64_t row0 = static_cast<uint64_t>(tile - t.tile0) * t.tile_rows;
 		uint64_t limit = t.rows;
 		if (t.op == B2A_OP_VALIDITY && (t.flags & B2A_TASK_F_ADD_NULL)) {
@@ -729,6 +842,12 @@ __global__ void __launch_bounds__(kThreads)
 			op_scalar(t, image, out, row0, nrows, err);
 			break;
 		}
+		if (next >= tile_end) {
+			break;
+		}
+		cp_async_wait_all();
+		__syncthreads(); // next descriptor has landed; everyone is done with the current one
+		tile = next;
 	}
 }
 
@@ -744,7 +863,13 @@ int LaunchDecode(const DecodeLaunch &l, void *stream) {
 			ctas_per_sm = 4;
 		}
 	}
-	uint32_t grid = static_cast<uint32_t>(l.sm_count) * static_cast<uint32_t>(ctas_per_sm);
+	static int ctas_override = -1;
+	if (ctas_override < 0) {
+		const char *e = getenv("B2A_CTAS_PER_SM"); // tuning knob for experiments
+		ctas_override = e ? atoi(e) : 0;
+	}
+	uint32_t grid = static_cast<uint32_t>(l.sm_count) *
+	                static_cast<uint32_t>(ctas_override > 0 ? ctas_override : ctas_per_sm);
 	if (grid > l.n_tiles) {
 		grid = l.n_tiles;
 	}

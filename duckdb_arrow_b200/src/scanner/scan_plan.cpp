@@ -1,12 +1,24 @@
 #include "scan_plan.hpp"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b2a {
 
 static const uint64_t kNone = UINT64_MAX;
-static const uint64_t kTileBytes = 64 * 1024; // bytes moved (in + out) per tile, roughly
+// bytes moved (in + out) per tile, roughly; B2A_TILE_BYTES overrides for tuning experiments
+static uint64_t TileBytes() {
+	static uint64_t v = 0;
+	if (v == 0) {
+		const char *e = getenv("B2A_TILE_BYTES");
+		v = e ? strtoull(e, nullptr, 10) : 0;
+		if (v < 4096) {
+			v = 256 * 1024;
+		}
+	}
+	return v;
+}
 
 uint64_t ScanPlan::Alloc(uint64_t bytes) {
 	uint64_t off = out_bytes;
@@ -33,7 +45,7 @@ void ScanPlan::AddTask(b2a_task t, uint64_t in_x16, uint64_t out_per_row) {
 	if (per_row_x16 == 0) {
 		per_row_x16 = 1;
 	}
-	uint64_t tile_rows = kTileBytes * 16 / per_row_x16;
+	uint64_t tile_rows = TileBytes() * 16 / per_row_x16;
 	tile_rows = std::max<uint64_t>(B2A_VECTOR_SIZE, (tile_rows / B2A_VECTOR_SIZE) * B2A_VECTOR_SIZE);
 	tile_rows = std::min<uint64_t>(tile_rows, uint64_t(1) << 22);
 	uint64_t n_tiles = (rows + tile_rows - 1) / tile_rows;
