@@ -10,6 +10,7 @@ LIB_PATH = os.path.join(HERE, "libb2arrow.so")
 
 B2A_NONE = 0xFFFFFFFFFFFFFFFF
 VECTOR_SIZE = 2048
+SCAN_HOST_ALIAS = 0x1
 
 STATUS = {0: "OK", 1: "InvalidInputException", 2: "IOException", 3: "NotImplementedException",
           4: "ConversionException", 5: "CudaError", 6: "InternalException", 7: "OutOfMemoryException"}
@@ -56,7 +57,7 @@ class BatchInfo(C.Structure):
 class ColumnOut(C.Structure):
     _fields_ = [("rows", C.c_uint64), ("null_count", C.c_uint64), ("data_off", C.c_uint64),
                 ("validity_off", C.c_uint64), ("aux_off", C.c_uint64), ("chars_off", C.c_uint64),
-                ("chars_len", C.c_uint64), ("stats_off", C.c_uint64)]
+                ("chars_len", C.c_uint64), ("stats_off", C.c_uint64), ("image_off", C.c_uint64)]
 
 
 class Predicate(C.Structure):
@@ -89,6 +90,8 @@ def _load() -> C.CDLL:
         "b2a_reader_image": (i32, [vp, P(vp), P(u64)]),
         "b2a_reader_schema_metadata": (i32, [vp, u32, P(C.c_char_p), P(C.c_char_p), P(u32)]),
         "b2a_scan_create": (i32, [vp, i32, u64, u64, P(vp)]),
+        "b2a_scan_create_ex": (i32, [vp, i32, u64, u64, u32, P(vp)]),
+        "b2a_scan_upload_bytes": (i32, [vp, P(u64)]),
         "b2a_scan_destroy": (None, [vp]),
         "b2a_scan_sizes": (i32, [vp, P(u64), P(u64), P(u64), P(u64), P(u64), P(u64)]),
         "b2a_scan_upload": (i32, [vp, vp]),

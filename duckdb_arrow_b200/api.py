@@ -159,14 +159,22 @@ def _dedup(names):
 class ArrowScan:
     """One scan of a batch range of a reader on one GPU (b2a_scan)."""
 
-    def __init__(self, reader: ArrowIPCReader, device: int = 0, batch_lo: int = 0, batch_hi: int | None = None):
+    def __init__(self, reader: ArrowIPCReader, device: int = 0, batch_lo: int = 0, batch_hi: int | None = None,
+                 host_alias: bool = False):
+        """host_alias: B2A_SCAN_HOST_ALIAS — DirectConversion columns stay in the host image (zero copy, like the
+        reference); such a scan is consumed through read_host() only."""
         self.reader = reader
         self.device = device
+        self.host_alias = host_alias
         hi = reader.num_batches if batch_hi is None else batch_hi
         self.batch_lo, self.batch_hi = batch_lo, hi
         h = C.c_void_p()
-        check(lib.b2a_scan_create(reader._h, device, batch_lo, hi, C.byref(h)))
+        check(lib.b2a_scan_create_ex(reader._h, device, batch_lo, hi, _lib.SCAN_HOST_ALIAS if host_alias else 0,
+                                     C.byref(h)))
         self._h = h
+        ub = C.c_uint64()
+        check(lib.b2a_scan_upload_bytes(self._h, C.byref(ub)))
+        self.upload_bytes = ub.value
         v = [C.c_uint64() for _ in range(6)]
         check(lib.b2a_scan_sizes(self._h, *[C.byref(x) for x in v]))
         (self.image_lo, self.image_bytes, self.out_bytes, self.algorithmic_bytes, self.n_tasks,
@@ -232,6 +240,15 @@ class ArrowScan:
         torch.cuda.current_stream(self.device).synchronize()
         return h_out.numpy()
 
+    def read_host(self, h_out=None, n_slices: int = 0) -> np.ndarray:
+        """b2a_read_arrow_host: host image -> (pipelined H2D, decode, D2H) -> host vectors in pinned memory."""
+        torch = self._torch()
+        if h_out is None:
+            h_out = torch.empty(self.out_bytes, dtype=torch.uint8, pin_memory=True)
+        check(lib.b2a_read_arrow_host(self._h, C.c_void_p(h_out.data_ptr()), n_slices))
+        self._h_out = h_out
+        return h_out.numpy()
+
     @property
     def gpu_launches(self) -> int:
         return int(lib.b2a_scan_gpu_launches(self._h))
@@ -285,7 +302,7 @@ class ArrowScan:
         return co
 
 
-def read_arrow(path, columns: list[str] | None = None, device: int = 0) -> "DecodedScan":
+def read_arrow(path, columns: list[str] | None = None, device: int = 0, host_alias: bool = True) -> "DecodedScan":
     """`FROM read_arrow('x.arrows')`: full scan of one file (or a list / glob of files) into DuckDB vectors.
     Returns the decoded vectors on the host in canonical layout (see DecodedScan)."""
     paths = path if isinstance(path, (list, tuple)) else (sorted(_glob.glob(path)) if any(c in path for c in "*?[") else [path])
@@ -296,21 +313,28 @@ def read_arrow(path, columns: list[str] | None = None, device: int = 0) -> "Deco
         r = ArrowIPCReader.open_file(p)
         if columns:
             r.set_projection(columns)
-        parts.append(_scan_to_host(r, device))
+        parts.append(_scan_to_host(r, device, host_alias))
     return parts[0] if len(parts) == 1 else parts
 
 
-def scan_arrow_ipc(buffers, columns: list[str] | None = None, device: int = 0) -> "DecodedScan":
+def scan_arrow_ipc(buffers, columns: list[str] | None = None, device: int = 0, host_alias: bool = True) -> "DecodedScan":
     r = ArrowIPCReader.open_buffers(buffers)
     if columns:
         r.set_projection(columns)
-    return _scan_to_host(r, device)
+    return _scan_to_host(r, device, host_alias)
 
 
-def _scan_to_host(reader: ArrowIPCReader, device: int) -> "DecodedScan":
+def _scan_to_host(reader: ArrowIPCReader, device: int, host_alias: bool = True) -> "DecodedScan":
+    """The drop-in path: host stream in, host vectors out (b2a_read_arrow_host).  With host_alias the fixed-width
+    columns alias the host image exactly like the reference's DirectConversion; without it every column goes through
+    upload -> decode -> download (the device-resident layout, copied back whole)."""
+    image = reader.image()
+    if host_alias:
+        scan = ArrowScan(reader, device, host_alias=True)
+        arena = scan.read_host()
+        return DecodedScan(scan, arena, image, image.ctypes.data if image.size else 0)
     scan = ArrowScan(reader, device)
     scan.upload()
-    image = reader.image()
     # string_t pointers refer to the HOST copy of the stream, exactly where the reference's pointers point
     base = image.ctypes.data + scan.image_lo if image.size else 0
     scan.decode(string_ptr_base=base)
@@ -370,6 +394,8 @@ class ColumnView:
     def data(self) -> np.ndarray:
         """uint8[rows, width]"""
         w = self.width
+        if w and self.co.data_off == B2A_NONE and self.co.image_off != B2A_NONE:  # host-alias: the Arrow buffer itself
+            return self.ds.image[self.co.image_off: self.co.image_off + self.rows * w].reshape(self.rows, w)
         if w == 0 or self.co.data_off == B2A_NONE:
             return np.zeros((self.rows, 0), np.uint8)
         return self.ds.arena[self.co.data_off: self.co.data_off + self.rows * w].reshape(self.rows, w)

@@ -238,10 +238,19 @@ static void FreeScanDevice(b2a_scan *s) {
 
 // device < 0: plan only (layout inspection on a machine without a GPU); every compute call then fails.
 int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, b2a_scan **out) {
+	return b2a_scan_create_ex(r, device, batch_lo, batch_hi, 0, out);
+}
+
+int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, uint32_t flags,
+                       b2a_scan **out) {
 	B2A_TRY
+	if (flags & ~B2A_SCAN_HOST_ALIAS) {
+		return Fail(B2A_EINVAL, "unknown scan flags");
+	}
 	std::unique_ptr<b2a_scan> s(new b2a_scan());
 	s->r = r;
 	s->device = device;
+	s->plan.alias_direct = (flags & B2A_SCAN_HOST_ALIAS) != 0;
 	s->plan.Build(r->reader, batch_lo, batch_hi);
 	if (device >= 0) {
 		CUDA_OK(cudaSetDevice(device));
@@ -287,6 +296,11 @@ int b2a_scan_sizes(b2a_scan *s, uint64_t *image_lo, uint64_t *image_bytes, uint6
 	return B2A_OK;
 }
 
+int b2a_scan_upload_bytes(b2a_scan *s, uint64_t *bytes) {
+	*bytes = s->plan.upload_bytes;
+	return B2A_OK;
+}
+
 #define NEED_DEVICE(s)                                                                                                 \
 	do {                                                                                                               \
 		if ((s)->device < 0) {                                                                                         \
@@ -321,6 +335,9 @@ int b2a_scan_set_device_image(b2a_scan *s, const void *d_image) {
 
 int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cuda_stream) {
 	NEED_DEVICE(s);
+	if (s->plan.alias_direct) {
+		return Fail(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan has host-resident direct columns: use b2a_read_arrow_host");
+	}
 	if (!s->d_image) {
 		return Fail(B2A_EINVAL, "no device image: call b2a_scan_upload or b2a_scan_set_device_image first");
 	}
@@ -431,6 +448,18 @@ struct HostPipe {
 };
 static thread_local HostPipe g_pipe;
 
+static int UploadRanges(b2a_scan *s, const ScanPlan::RangeList &ranges, cudaStream_t st) {
+	const ScanPlan &p = s->plan;
+	const uint8_t *h_image = s->r->reader.Image();
+	for (auto &r : ranges) {
+		if (r.second > r.first) {
+			CUDA_OK(cudaMemcpyAsync(s->d_image_owned + (r.first - p.image_lo), h_image + r.first, r.second - r.first,
+			                        cudaMemcpyHostToDevice, st));
+		}
+	}
+	return B2A_OK;
+}
+
 extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices) {
 	NEED_DEVICE(s);
 	const ScanPlan &p = s->plan;
@@ -448,12 +477,13 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	if (hp.d_out_bytes < p.out_bytes) {
 		cudaFree(hp.d_out);
 		hp.d_out = nullptr;
+		hp.d_out_bytes = 0;
 		CUDA_OK(cudaMalloc(&hp.d_out, p.out_bytes));
 		hp.d_out_bytes = p.out_bytes;
 	}
 	const uint64_t n_batches = p.batch_hi - p.batch_lo;
 	if (n_slices == 0) {
-		n_slices = 1;
+		n_slices = 16;
 	}
 	if (n_slices > n_batches) {
 		n_slices = static_cast<uint32_t>(n_batches ? n_batches : 1);
@@ -480,24 +510,16 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
 
-	uint64_t up_to = p.image_lo; // image bytes already scheduled for upload
 	for (uint32_t sl = 0; sl < n_slices; sl++) {
 		const uint64_t b0 = n_batches * sl / n_slices, b1 = n_batches * (sl + 1) / n_slices;
 		if (b0 == b1) {
 			continue;
 		}
-		// upload everything up to the end of this slice's last batch (covers dictionary messages in between)
-		uint64_t hi = 0;
 		for (uint64_t b = b0; b < b1; b++) {
-			hi = std::max(hi, p.batch_image_hi[b]);
-		}
-		if (sl + 1 == n_slices) {
-			hi = p.image_hi;
-		}
-		if (hi > up_to) {
-			CUDA_OK(cudaMemcpyAsync(s->d_image_owned + (up_to - p.image_lo), h_image + up_to, hi - up_to,
-			                        cudaMemcpyHostToDevice, hp.in));
-			up_to = hi;
+			int rc = UploadRanges(s, p.batch_ranges[b], hp.in);
+			if (rc != B2A_OK) {
+				return rc;
+			}
 		}
 		CUDA_OK(cudaEventRecord(hp.ev_in[sl], hp.in));
 		CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[sl], 0));
@@ -520,9 +542,11 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	// dictionaries (decoded once per scan) + the popcount cells live after the last batch
 	const uint32_t tail_tile0 = p.batch_tile0.empty() ? 0 : p.batch_tile0.back();
 	const uint64_t tail_out0 = p.batch_out0.empty() ? 0 : p.batch_out0.back();
-	if (up_to < p.image_hi) {
-		CUDA_OK(cudaMemcpyAsync(s->d_image_owned + (up_to - p.image_lo), h_image + up_to, p.image_hi - up_to,
-		                        cudaMemcpyHostToDevice, hp.in));
+	{
+		int rc = UploadRanges(s, p.tail_ranges, hp.in);
+		if (rc != B2A_OK) {
+			return rc;
+		}
 	}
 	CUDA_OK(cudaEventRecord(hp.ev_in[n_slices], hp.in));
 	CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[n_slices], 0));
@@ -550,6 +574,10 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vector<uint32_t> &key, uint64_t **d_table,
                       std::vector<uint8_t> *widths) {
 	const ScanPlan &p = s->plan;
+	if (p.alias_direct) {
+		return Fail(B2A_EINVAL, "filters / aggregates need device-resident vectors: create the scan without "
+		                        "B2A_SCAN_HOST_ALIAS");
+	}
 	const Schema &schema = s->r->reader.BaseSchema();
 	std::vector<int> flats;
 	for (uint32_t c : cols) {

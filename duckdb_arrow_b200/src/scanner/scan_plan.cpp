@@ -33,6 +33,25 @@ void ScanPlan::Touch(uint64_t off, uint64_t len) {
 	image_lo = std::min(image_lo, off);
 	image_hi = std::max(image_hi, off + len);
 	algorithmic_in += len;
+	if (cur_ranges) {
+		cur_ranges->emplace_back(off, off + len);
+	}
+}
+
+// sort + merge ranges whose gap is small (one bigger copy beats two small ones); ends rounded to 16 bytes
+static void MergeRanges(ScanPlan::RangeList &r, uint64_t limit_hi) {
+	static const uint64_t kGap = 256 * 1024;
+	std::sort(r.begin(), r.end());
+	ScanPlan::RangeList out;
+	for (auto &x : r) {
+		uint64_t lo = x.first & ~uint64_t(15), hi = std::min(limit_hi, (x.second + 15) & ~uint64_t(15));
+		if (!out.empty() && lo <= out.back().second + kGap) {
+			out.back().second = std::max(out.back().second, hi);
+		} else {
+			out.emplace_back(lo, hi);
+		}
+	}
+	r.swap(out);
 }
 
 // x16: input bytes per row in 1/16 byte units (bitmaps are 2/16 = 1/8 byte per row)
@@ -302,6 +321,10 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 	default: { // COPY and the elementwise transforms: src_width bytes in, out_width bytes out
 		const uint64_t sw = static_cast<uint64_t>(f.src_width), dw = static_cast<uint64_t>(f.out_width);
 		NeedBytes(bufs[1], L * sw, f, "data");
+		if (alias_direct && f.op == B2A_OP_COPY && (!big_endian || sw == 1)) {
+			slot.image_off = bufs[1].offset; // DirectConversion: the host vector points at the Arrow buffer itself
+			break;
+		}
 		t.src = bufs[1].offset;
 		t.dst = slot.data_off = Alloc(L * dw);
 		Touch(t.src, L * sw);
@@ -392,6 +415,8 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 		batch_chunk0.push_back(n_chunks);
 		batch_tile0.push_back(next_tile);
 		batch_out0.push_back(out_bytes);
+		batch_ranges.emplace_back();
+		cur_ranges = &batch_ranges.back();
 		const uint64_t save_lo = image_lo, save_hi = image_hi;
 		image_lo = UINT64_MAX;
 		image_hi = 0;
@@ -415,6 +440,7 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	}
 	batch_tile0.push_back(next_tile);
 	batch_out0.push_back(out_bytes);
+	cur_ranges = &tail_ranges;
 	// dictionaries: decoded once per scan (ArrowArrayScanState::AddDictionary, arrow_array_scan_state.cpp:29-52)
 	std::vector<int> dict_fields;
 	for (auto &kv : dict_cols) {
@@ -450,10 +476,22 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 			kv.second.stats_off += stats_base;
 		}
 	}
+	cur_ranges = nullptr;
 	if (image_lo == UINT64_MAX) {
 		image_lo = image_hi = 0;
 	}
 	image_lo &= ~uint64_t(255);
+	upload_bytes = 0;
+	for (auto &r : batch_ranges) {
+		MergeRanges(r, reader.ImageSize());
+		for (auto &x : r) {
+			upload_bytes += x.second - x.first;
+		}
+	}
+	MergeRanges(tail_ranges, reader.ImageSize());
+	for (auto &x : tail_ranges) {
+		upload_bytes += x.second - x.first;
+	}
 	if (out_bytes == 0) {
 		out_bytes = 256;
 	}

@@ -35,6 +35,15 @@ struct ScanPlan {
 	std::vector<uint64_t> batch_out0;
 	std::vector<uint64_t> batch_image_lo, batch_image_hi;
 
+	// host-alias mode (B2A_SCAN_HOST_ALIAS): DirectConversion columns alias the host image, no task is emitted
+	bool alias_direct = false;
+	// image ranges the tasks of each batch read (merged when close), + the ranges of the dictionary batches;
+	// the host path uploads exactly these
+	typedef std::vector<std::pair<uint64_t, uint64_t>> RangeList;
+	std::vector<RangeList> batch_ranges;
+	RangeList tail_ranges;
+	uint64_t upload_bytes = 0;
+
 	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
 
 	const b2a_column_out &Column(uint64_t batch, uint32_t flat) const {
@@ -61,6 +70,7 @@ private:
 	               bool ignore_dictionary);
 	bool big_endian = false;
 	uint32_t next_tile = 0;
+	RangeList *cur_ranges = nullptr;
 };
 
 } // namespace b2a

@@ -156,6 +156,8 @@ typedef struct b2a_column_out {
 	uint64_t chars_off;    /* strings: stream-image offset of the character buffer (pointer base) */
 	uint64_t chars_len;
 	uint64_t stats_off;    /* uint64: valid-row count computed on device (popc of the mask) */
+	uint64_t image_off;    /* B2A_SCAN_HOST_ALIAS: the vector aliases the stream image at this offset (rows * out_width
+	                          bytes, the reference's DirectConversion); data_off is then B2A_NONE.  Else B2A_NONE. */
 } b2a_column_out;
 
 /* Pushed-down predicate: ConstantFilter{comparison, constant} on a top-level integer-like column. */
@@ -189,9 +191,18 @@ int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, cons
 
 /* ---------------- src/scanner + kernels: record batches -> DuckDB vectors ---------------- */
 int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, b2a_scan **out);
+/* flags: B2A_SCAN_HOST_ALIAS = the consumer of the vectors lives on the HOST next to the stream image, so columns the
+ * reference converts with DirectConversion (arrow_conversion.cpp:454-461: FlatVector::SetData on the Arrow buffer, no
+ * copy) are NOT moved through the GPU either: b2a_column_out.image_off points into the host image.  Only buffers that
+ * need real conversion work (strings, bools, validity, lists, scalar transforms, swapped endianness) are uploaded,
+ * converted and downloaded.  Such a scan can be used with b2a_read_arrow_host only. */
+#define B2A_SCAN_HOST_ALIAS 0x1u
+int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, uint32_t flags, b2a_scan **out);
 void b2a_scan_destroy(b2a_scan *s);
 int b2a_scan_sizes(b2a_scan *s, uint64_t *image_lo, uint64_t *image_bytes, uint64_t *out_bytes,
                    uint64_t *algorithmic_bytes, uint64_t *n_tasks, uint64_t *n_tiles);
+/* bytes b2a_read_arrow_host moves host -> device per call (the merged image ranges the tasks read) */
+int b2a_scan_upload_bytes(b2a_scan *s, uint64_t *bytes);
 /* Host image -> device (one cudaMemcpyAsync per call; `host_image` should be pinned for full PCIe rate). */
 int b2a_scan_upload(b2a_scan *s, void *cuda_stream);
 /* Or: the [image_lo, image_lo+image_bytes) slice of the stream is already resident at d_image. */

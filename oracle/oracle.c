@@ -997,3 +997,106 @@ uint64_t oracle_scan_batch_checksum(const OArray *batch, OType *const *types, in
 	}
 	return sum;
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * a1 + a2 of SURVEY §8: what the reference does to a record-batch message BEFORE the scan loop.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* IPCFileStreamReader::DecodeBody (src/ipc/stream_reader/ipc_file_stream_reader.cpp:71-89): a fresh allocation of
+ * body_size bytes filled by BufferedFileReader::ReadData (duckdb/src/common/serializer/buffered_file_reader.cpp:25-49),
+ * i.e. through a FILE_BUFFER_SIZE = 4096 byte bounce buffer
+ * (duckdb/src/include/duckdb/common/serializer/buffered_file_writer.hpp:16).  fs.Read() is restated as a memcpy out of
+ * the in-memory file image (page-cache-warm file, no syscall cost: a lower bound of the reference's cost). */
+#define O_FILE_BUFFER_SIZE 4096
+uint8_t *oracle_decode_body(const uint8_t *file_image, uint64_t body_len) {
+	uint8_t *target = (uint8_t *)malloc(body_len ? body_len : 1);
+	uint8_t bounce[O_FILE_BUFFER_SIZE];
+	uint64_t file_pos = 0;
+	uint8_t *target_buffer = target, *end_ptr = target + body_len;
+	idx_t offset = 0, read_data = 0;
+	for (;;) {
+		idx_t to_read = (idx_t)(end_ptr - target_buffer);
+		if (to_read > read_data - offset) {
+			to_read = read_data - offset;
+		}
+		if (to_read > 0) {
+			memcpy(target_buffer, bounce + offset, to_read);
+			offset += to_read;
+			target_buffer += to_read;
+		}
+		if (target_buffer < end_ptr) {
+			offset = 0;
+			read_data = body_len - file_pos < O_FILE_BUFFER_SIZE ? body_len - file_pos : O_FILE_BUFFER_SIZE;
+			memcpy(bounce, file_image + file_pos, read_data); /* fs.Read(*handle, data.get(), FILE_BUFFER_SIZE) */
+			file_pos += read_data;
+		} else {
+			return target;
+		}
+	}
+}
+
+/* nanoarrow ArrowArrayViewValidate(NANOARROW_VALIDATION_LEVEL_FULL) as called by ArrowIpcDecoderDecodeArrayFromShared
+ * (call sites: src/ipc/stream_reader/base_stream_reader.cpp:117,124,135,139).  nanoarrow (apache/arrow-nanoarrow
+ * @4bf5a93, 0.7.0-SNAPSHOT) is not in the reference tree; its published FULL level walks every offsets buffer and
+ * requires offsets[i] >= offsets[i-1] (ArrowAssertIncreasingInt32/Int64), first offset >= 0 and last offset <= size
+ * of the data buffer; recursion over children and the dictionary.  Returns 0 when valid. */
+int oracle_validate_full(const OArray *array, const OType *type) {
+	if (type->has_dictionary) {
+		OType vt = *type;
+		vt.has_dictionary = 0;
+		return array->dictionary ? oracle_validate_full(array->dictionary, &vt) : 0;
+	}
+	int is_var = (type->id == O_VARCHAR || type->id == O_BLOB) &&
+	             (type->size_type == O_SIZE_NORMAL || type->size_type == O_SIZE_SUPER);
+	int is_list = type->id == O_LIST || type->id == O_MAP;
+	if ((is_var || is_list) && array->length > 0 && array->n_buffers > 1 && array->buffers[1]) {
+		idx_t n = (idx_t)(array->offset + array->length) + 1;
+		if (type->size_type == O_SIZE_SUPER) {
+			const int64_t *o = (const int64_t *)array->buffers[1];
+			if (o[0] < 0) {
+				return 1;
+			}
+			for (idx_t i = 1; i < n; i++) {
+				if (o[i] < o[i - 1]) {
+					return 1;
+				}
+			}
+		} else {
+			const int32_t *o = (const int32_t *)array->buffers[1];
+			if (o[0] < 0) {
+				return 1;
+			}
+			for (idx_t i = 1; i < n; i++) {
+				if (o[i] < o[i - 1]) {
+					return 1;
+				}
+			}
+		}
+	}
+	for (int c = 0; c < type->n_children && c < (int)array->n_children; c++) {
+		int rc = oracle_validate_full(array->children[c], type->children[c]);
+		if (rc) {
+			return rc;
+		}
+	}
+	return 0;
+}
+
+/* One record-batch message the way the reference's read_arrow handles it: DecodeBody (a1), FULL validation (a2), then
+ * the scan loop (a4-a9).  `body` is the message body inside the in-memory file image; `batch` describes the same body
+ * as Arrow C data (sliced by pyarrow, untimed).  Timed CPU baseline only. */
+uint64_t oracle_read_arrow_batch_checksum(const uint8_t *body, uint64_t body_len, const OArray *batch,
+                                          OType *const *types, int n_cols) {
+	uint8_t *copy = oracle_decode_body(body, body_len);
+	uint64_t sum = body_len ? copy[body_len - 1] : 0;
+	for (int c = 0; c < n_cols; c++) {
+		if (oracle_validate_full(batch->children[c], types[c])) {
+			free(copy);
+			return UINT64_MAX;
+		}
+	}
+	sum += oracle_scan_batch_checksum(batch, types, n_cols);
+	free(copy);
+	return sum;
+}
+

@@ -90,6 +90,12 @@ void oracle_slab_free(OSlab *s);
  * chunk and discards the vectors; returns a checksum so the work cannot be optimised away. */
 uint64_t oracle_scan_batch_checksum(const OArray *batch, OType *const *types, int n_cols);
 
+/* a1 + a2 + the scan: DecodeBody through the 4 KiB bounce buffer, nanoarrow FULL validation, scan (see oracle.c) */
+uint8_t *oracle_decode_body(const uint8_t *file_image, uint64_t body_len);
+int oracle_validate_full(const OArray *array, const OType *type);
+uint64_t oracle_read_arrow_batch_checksum(const uint8_t *body, uint64_t body_len, const OArray *batch,
+                                          OType *const *types, int n_cols);
+
 #ifdef __cplusplus
 }
 #endif

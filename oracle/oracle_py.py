@@ -82,6 +82,11 @@ def lib() -> C.CDLL:
         _lib.oracle_slab_free.argtypes = [C.POINTER(OSlab)]
         _lib.oracle_scan_batch_checksum.restype = C.c_uint64
         _lib.oracle_scan_batch_checksum.argtypes = [C.c_void_p, C.POINTER(C.POINTER(OType)), C.c_int]
+        _lib.oracle_read_arrow_batch_checksum.restype = C.c_uint64
+        _lib.oracle_read_arrow_batch_checksum.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p,
+                                                          C.POINTER(C.POINTER(OType)), C.c_int]
+        _lib.oracle_validate_full.restype = C.c_int
+        _lib.oracle_validate_full.argtypes = [C.c_void_p, C.POINTER(OType)]
     return _lib
 
 
@@ -255,3 +260,55 @@ def scan_batches_checksum(batches: list[pa.RecordBatch]) -> int:
             if st.release:
                 C.CFUNCTYPE(None, C.POINTER(ty))(st.release)(C.byref(st))
     return total
+
+
+def validate_full(arr: pa.Array) -> bool:
+    """nanoarrow FULL validation of one array (True = valid)."""
+    L = lib()
+    typ = make_type(arr.type)
+    c_arr, c_sch = ArrowArray(), ArrowSchema()
+    arr._export_to_c(C.addressof(c_arr), C.addressof(c_sch))
+    try:
+        return L.oracle_validate_full(C.addressof(c_arr), C.byref(typ)) == 0
+    finally:
+        for st, ty in ((c_arr, ArrowArray), (c_sch, ArrowSchema)):
+            if st.release:
+                C.CFUNCTYPE(None, C.POINTER(ty))(st.release)(C.byref(st))
+
+
+def stream_messages(buf, max_batches: int | None = None):
+    """[(body address, body bytes, RecordBatch)] of an in-memory IPC stream (pyarrow does the framing, untimed).
+    The returned list keeps the message bodies alive."""
+    import pyarrow.ipc as ipc
+    reader = ipc.MessageReader.open_stream(pa.py_buffer(buf) if not isinstance(buf, pa.Buffer) else buf)
+    schema, out = None, []
+    for msg in reader:
+        if msg.type == "schema":
+            schema = ipc.read_schema(msg)
+        elif msg.type == "record batch":
+            out.append((msg.body.address, msg.body.size, ipc.read_record_batch(msg, schema), msg))
+            if max_batches and len(out) >= max_batches:
+                break
+    return out
+
+
+def read_arrow_checksum(messages) -> int:
+    """Timed CPU baseline body: per record-batch message DecodeBody (4 KiB bounce copy) + FULL validation + scan."""
+    L = lib()
+    total = 0
+    if not messages:
+        return 0
+    types = [make_type(f.type) for f in messages[0][2].schema]
+    tarr = (C.POINTER(OType) * len(types))(*[C.pointer(t) for t in types])
+    for addr, size, b, _ in messages:
+        c_arr, c_sch = ArrowArray(), ArrowSchema()
+        b._export_to_c(C.addressof(c_arr), C.addressof(c_sch))
+        r = L.oracle_read_arrow_batch_checksum(addr, size, C.addressof(c_arr), tarr, len(types))
+        for st, ty in ((c_arr, ArrowArray), (c_sch, ArrowSchema)):
+            if st.release:
+                C.CFUNCTYPE(None, C.POINTER(ty))(st.release)(C.byref(st))
+        if r == 0xFFFFFFFFFFFFFFFF:
+            raise OracleError(3, "Arrow IPC: offsets are not monotonically increasing")
+        total += r
+    return total & 0xFFFFFFFFFFFFFFFF
+

@@ -84,12 +84,37 @@ def test_lineitem_sf001_parquet_fixture(b2a, cuda_device, tmp_path):
     compare_scan_with_oracle(ds, _pa_batches(p))
 
 
+@pytest.mark.parametrize("host_alias", [True, False])
 @pytest.mark.parametrize("rows,batch_rows", [(300_000, 122_880), (5000, 1000), (2048, 2048), (2049, 4096), (1, 1)])
-def test_synthetic_lineitem(b2a, cuda_device, rows, batch_rows):
+def test_synthetic_lineitem(b2a, cuda_device, rows, batch_rows, host_alias):
+    """host_alias=True: the drop-in host path (fixed-width vectors alias the host stream like DirectConversion);
+    False: every column through upload -> decode kernel -> download."""
     from tools import lineitem
     buf = lineitem.stream_bytes(rows, seed=7, batch_rows=batch_rows)
-    ds = b2a.scan_arrow_ipc([buf])
+    ds = b2a.scan_arrow_ipc([buf], host_alias=host_alias)
     compare_scan_with_oracle(ds, list(ipc.open_stream(buf)))
+    if host_alias:
+        co = ds.scan.column(0, 0)
+        assert co.data_off == b2a.B2A_NONE and co.image_off != b2a.B2A_NONE
+        assert ds.scan.upload_bytes < ds.scan.image_bytes or rows < 100
+
+
+@pytest.mark.parametrize("name", ["generated_primitive", "generated_nested", "generated_datetime"])
+@pytest.mark.parametrize("endian", ["little", "big"])
+def test_device_layout_path_on_integration_files(b2a, cuda_device, name, endian):
+    """same files as above through the non-aliased (device-resident layout) path"""
+    path = os.path.join(LE if endian == "little" else BE, name + ".stream")
+    ds = b2a.read_arrow(path, host_alias=False)
+    compare_scan_with_oracle(ds, _pa_batches(path))
+
+
+def test_host_alias_scan_rejects_device_consumers(b2a, cuda_device):
+    from tools import lineitem
+    buf = lineitem.stream_bytes(5000, seed=2)
+    r = b2a.ArrowIPCReader.open_buffers([buf])
+    scan = b2a.ArrowScan(r, device=0, host_alias=True)
+    with pytest.raises(b2a.B2AError):
+        scan.decode()
 
 
 def test_synthetic_lineitem_dictionary(b2a, cuda_device):
