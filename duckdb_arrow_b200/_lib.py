@@ -64,6 +64,21 @@ class Predicate(C.Structure):
     _fields_ = [("column", C.c_uint32), ("cmp", C.c_uint32), ("constant", C.c_int64)]
 
 
+class Vector(C.Structure):
+    pass
+
+
+Vector._fields_ = [("type_id", C.c_int32), ("decimal_width", C.c_int32), ("decimal_scale", C.c_int32),
+                   ("n_children", C.c_int32), ("param", C.c_int64), ("name", C.c_char_p), ("timezone", C.c_char_p),
+                   ("data", C.c_void_p), ("validity", C.c_void_p), ("rows", C.c_uint64),
+                   ("children", C.POINTER(Vector))]
+
+
+class WriteOptions(C.Structure):
+    _fields_ = [("row_group_size", C.c_uint64), ("n_kv_metadata", C.c_uint32), ("kv_keys", C.POINTER(C.c_char_p)),
+                ("kv_values", C.POINTER(C.c_char_p))]
+
+
 CMP = {"=": 0, "==": 0, "!=": 1, "<>": 1, "<": 2, "<=": 3, ">": 4, ">=": 5}
 
 
@@ -106,6 +121,15 @@ def _load() -> C.CDLL:
         "b2a_scan_filter": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
+        "b2a_writer_create": (i32, [P(Vector), u32, u64, P(WriteOptions), i32, P(vp)]),
+        "b2a_writer_destroy": (None, [vp]),
+        "b2a_writer_measure": (i32, [vp, vp]),
+        "b2a_writer_sizes": (i32, [vp, P(u64), P(u64), P(u64), P(u64)]),
+        "b2a_writer_encode": (i32, [vp, vp, vp]),
+        "b2a_writer_finish": (i32, [vp, vp]),
+        "b2a_writer_headers": (i32, [vp, vp]),
+        "b2a_writer_batch": (i32, [vp, u64, P(BatchInfo)]),
+        "b2a_writer_gpu_launches": (u64, [vp]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):

@@ -426,3 +426,150 @@ class ColumnView:
         ptr = d[:, 8:16].copy().view(np.uint64).ravel().astype(np.int64)
         rel = ptr - np.int64(self.ds.ptr_origin + int(self.co.chars_off))
         return lens, d[:, 4:16], rel
+
+
+# ======================================================================================================== writer
+class DeviceVector:
+    """A flat DuckDB vector (or the end-to-end concatenation of the vectors of a column) in device memory —
+    the Python face of b2a_vector.  `data` / `validity` are torch CUDA tensors (uint8 bytes / int64 mask words);
+    VARCHAR data is string_t[rows] whose pointers are device addresses, LIST / MAP data is list_entry_t[rows]."""
+
+    def __init__(self, type: str, rows: int, data=None, validity=None, children=(), name: str = "",
+                 decimal=(0, 0), param: int = 0, timezone: str | None = None, keep=()):
+        self.type, self.rows, self.data, self.validity = type, int(rows), data, validity
+        self.children, self.name, self.decimal, self.param, self.timezone = list(children), name, decimal, param, timezone
+        self.keep = list(keep)  # tensors the string_t pointers refer to (string heaps)
+
+    def _fill(self, cv: _lib.Vector, keep: list):
+        cv.type_id = _lib.T[self.type]
+        cv.decimal_width, cv.decimal_scale = self.decimal
+        cv.param = self.param
+        name = self.name.encode()
+        keep.append(name)
+        cv.name = name
+        if self.timezone is not None:
+            tz = self.timezone.encode()
+            keep.append(tz)
+            cv.timezone = tz
+        cv.data = self.data.data_ptr() if self.data is not None and self.data.numel() else None
+        cv.validity = self.validity.data_ptr() if self.validity is not None else None
+        cv.rows = self.rows
+        cv.n_children = len(self.children)
+        if self.children:
+            arr = (_lib.Vector * len(self.children))()
+            keep.append(arr)
+            for i, c in enumerate(self.children):
+                c._fill(arr[i], keep)
+            cv.children = arr
+
+
+class ArrowWriter:
+    """b2a_writer: COPY ... (FORMAT ARROWS) of a device-resident table (src/writer/write_arrow_stream.cpp)."""
+
+    def __init__(self, columns: list[DeviceVector], rows: int, row_group_size: int = 122_880,
+                 kv_metadata: dict | None = None, device: int = 0):
+        self.device, self.columns = device, columns
+        self._keep: list = []
+        arr = (_lib.Vector * len(columns))()
+        for i, c in enumerate(columns):
+            c._fill(arr[i], self._keep)
+        opt = _lib.WriteOptions()
+        opt.row_group_size = row_group_size
+        kv = kv_metadata or {}
+        if kv:
+            ks = (C.c_char_p * len(kv))(*[str(k).encode() for k in kv])
+            vs = (C.c_char_p * len(kv))(*[str(v).encode() for v in kv.values()])
+            self._keep += [ks, vs]
+            opt.n_kv_metadata, opt.kv_keys, opt.kv_values = len(kv), ks, vs
+        h = C.c_void_p()
+        check(lib.b2a_writer_create(arr, len(columns), rows, C.byref(opt), device, C.byref(h)))
+        self._h = h
+        self.stream_bytes = self.n_batches = self.body_bytes = self.algorithmic_bytes = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.b2a_writer_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream_ptr(self):
+        import torch
+        if not torch.cuda.is_available():
+            raise B2AError(5, "no CUDA device: the Arrow IPC writer path has no CPU fallback")
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def measure(self):
+        check(lib.b2a_writer_measure(self._h, self._stream_ptr()))
+        v = [C.c_uint64() for _ in range(4)]
+        check(lib.b2a_writer_sizes(self._h, *[C.byref(x) for x in v]))
+        self.stream_bytes, self.n_batches, self.body_bytes, self.algorithmic_bytes = [x.value for x in v]
+
+    def encode(self, d_stream):
+        check(lib.b2a_writer_encode(self._h, C.c_void_p(d_stream.data_ptr()), self._stream_ptr()))
+
+    def finish(self):
+        check(lib.b2a_writer_finish(self._h, self._stream_ptr()))
+
+    def headers(self, h_stream: np.ndarray):
+        check(lib.b2a_writer_headers(self._h, C.c_void_p(h_stream.ctypes.data)))
+
+    def batch(self, i: int) -> _lib.BatchInfo:
+        bi = _lib.BatchInfo()
+        check(lib.b2a_writer_batch(self._h, i, C.byref(bi)))
+        return bi
+
+    @property
+    def gpu_launches(self) -> int:
+        return int(lib.b2a_writer_gpu_launches(self._h))
+
+    def write(self) -> np.ndarray:
+        """measure -> encode -> finish -> D2H -> headers; returns the complete IPC stream (host, pinned)."""
+        import torch
+        if self.stream_bytes is None:
+            self.measure()
+        d_stream = torch.empty(self.stream_bytes, dtype=torch.uint8, device=f"cuda:{self.device}")
+        self.encode(d_stream)
+        self.finish()
+        h = torch.empty(self.stream_bytes, dtype=torch.uint8, pin_memory=True)
+        h.copy_(d_stream)
+        torch.cuda.current_stream(self.device).synchronize()
+        out = h.numpy()
+        self.headers(out)
+        self._h_stream = h
+        return out
+
+
+def copy_to_arrows(columns: list[DeviceVector], path: str | None = None, row_group_size: int = 122_880,
+                   chunk_size: int | None = None, kv_metadata: dict | None = None, device: int = 0) -> np.ndarray:
+    """`COPY tbl TO 'x.arrows' (FORMAT ARROWS, ROW_GROUP_SIZE n, KV_METADATA {...})`
+    (src/writer/write_arrow_stream.cpp:54-125: `chunk_size` is an alias of `row_group_size`)."""
+    rows = columns[0].rows if columns else 0
+    w = ArrowWriter(columns, rows, chunk_size or row_group_size, kv_metadata, device)
+    stream = w.write()
+    if path is not None:
+        with open(path, "wb") as f:
+            f.write(memoryview(stream))
+    stream_copy = stream.copy()
+    w.close()
+    return stream_copy
+
+
+def to_arrow_ipc(columns: list[DeviceVector], device: int = 0) -> list[tuple[bytes, bool]]:
+    """`FROM to_arrow_ipc((FROM t))`: rows of (ipc BLOB, header BOOL) — first the schema message, then one
+    record-batch message per 120 x 2 048 rows (src/writer/to_arrow_ipc.cpp:21,116-155, to_arrow_ipc.hpp:28)."""
+    rows = columns[0].rows if columns else 0
+    w = ArrowWriter(columns, rows, 120 * VECTOR_SIZE, None, device)
+    stream = w.write()
+    out = []
+    first = w.batch(0).meta_offset if w.n_batches else w.stream_bytes - 8
+    out.append((bytes(stream[:first]), True))
+    for i in range(w.n_batches):
+        bi = w.batch(i)
+        out.append((bytes(stream[bi.meta_offset: bi.body_offset + bi.body_length]), False))
+    w.close()
+    return out

@@ -45,6 +45,13 @@ static int Fail(int code, const std::string &msg) {
 	return code;
 }
 
+namespace b2a {
+// shared with capi_writer.cu: one thread-local error slot behind b2a_last_error()
+int SetLastError(int code, const std::string &msg) {
+	return Fail(code, msg);
+}
+} // namespace b2a
+
 #define B2A_TRY try {
 #define B2A_CATCH                                                                                                      \
 	}                                                                                                                  \

@@ -1,0 +1,442 @@
+// C ABI of the writer direction (include/b2arrow.h: b2a_writer_*): device memory plumbing around the write planner
+// and the encode kernels.  No CPU fallback: without a CUDA device every compute entry point fails with B2A_ECUDA.
+#include "b2arrow.h"
+#include "kernels/encode.cuh"
+#include "writer/write_plan.hpp"
+
+#include <cuda_runtime.h>
+
+#include <cstring>
+#include <memory>
+#include <string>
+
+using namespace b2a;
+
+namespace b2a {
+int SetLastError(int code, const std::string &msg); // capi.cu
+}
+
+struct b2a_writer {
+	WritePlan plan;
+	int device = 0;
+	int sm_count = 148;
+	std::vector<void *> allocs; // selection vectors, scratch chunks
+	b2a_enc_task *d_tasks = nullptr;
+	uint32_t *d_tile_task = nullptr;
+	size_t cap_tasks = 0, cap_tiles = 0;
+	uint32_t n_enc_tasks = 0, n_enc_tiles = 0;
+	uint64_t *d_null_counts = nullptr;
+	uint32_t *d_err = nullptr;
+	uint64_t launches = 0;
+	bool measured = false, finished = false;
+};
+
+#define W_TRY try {
+#define W_CATCH                                                                                                        \
+	}                                                                                                                  \
+	catch (const Error &e) {                                                                                           \
+		return SetLastError(e.code, e.msg);                                                                            \
+	}                                                                                                                  \
+	catch (const std::bad_alloc &) {                                                                                   \
+		return SetLastError(B2A_EOOM, "out of host memory");                                                           \
+	}                                                                                                                  \
+	catch (const std::exception &e) {                                                                                  \
+		return SetLastError(B2A_EINTERNAL, e.what());                                                                  \
+	}
+
+#define W_CUDA(expr)                                                                                                   \
+	do {                                                                                                               \
+		cudaError_t _e = (expr);                                                                                       \
+		if (_e != cudaSuccess) {                                                                                       \
+			return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " #expr);      \
+		}                                                                                                              \
+	} while (0)
+
+#define W_NEED_DEVICE(w)                                                                                               \
+	do {                                                                                                               \
+		if ((w)->device < 0) {                                                                                         \
+			return SetLastError(B2A_ECUDA, "writer was planned without a CUDA device; there is no CPU fallback");      \
+		}                                                                                                              \
+		W_CUDA(cudaSetDevice((w)->device));                                                                            \
+	} while (0)
+
+static int UploadTasks(b2a_writer *w, const std::vector<b2a_enc_task> &tasks, const std::vector<uint32_t> &tiles,
+                       cudaStream_t st) {
+	if (tasks.size() > w->cap_tasks) {
+		cudaFree(w->d_tasks);
+		w->d_tasks = nullptr;
+		w->cap_tasks = 0;
+		W_CUDA(cudaMalloc(&w->d_tasks, tasks.size() * sizeof(b2a_enc_task)));
+		w->cap_tasks = tasks.size();
+	}
+	if (tiles.size() > w->cap_tiles) {
+		cudaFree(w->d_tile_task);
+		w->d_tile_task = nullptr;
+		w->cap_tiles = 0;
+		W_CUDA(cudaMalloc(&w->d_tile_task, tiles.size() * sizeof(uint32_t)));
+		w->cap_tiles = tiles.size();
+	}
+	// the host vectors are pageable and die with the caller's scope: plain synchronous copies, ordered after `st`
+	W_CUDA(cudaStreamSynchronize(st));
+	if (!tasks.empty()) {
+		W_CUDA(cudaMemcpy(w->d_tasks, tasks.data(), tasks.size() * sizeof(b2a_enc_task), cudaMemcpyHostToDevice));
+	}
+	if (!tiles.empty()) {
+		W_CUDA(cudaMemcpy(w->d_tile_task, tiles.data(), tiles.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+	}
+	return B2A_OK;
+}
+
+static int DeviceAlloc(b2a_writer *w, size_t bytes, void **out) {
+	W_CUDA(cudaMalloc(out, bytes ? bytes : 8));
+	w->allocs.push_back(*out);
+	return B2A_OK;
+}
+
+extern "C" {
+
+int b2a_writer_create(const b2a_vector *columns, uint32_t n_columns, uint64_t rows, const b2a_write_options *opt,
+                      int device, b2a_writer **out) {
+	W_TRY
+	std::unique_ptr<b2a_writer> w(new b2a_writer());
+	w->device = device;
+	w->plan.Build(columns, n_columns, rows, opt);
+	if (device >= 0) {
+		W_CUDA(cudaSetDevice(device));
+		cudaDeviceProp prop;
+		W_CUDA(cudaGetDeviceProperties(&prop, device));
+		w->sm_count = prop.multiProcessorCount;
+		W_CUDA(cudaMalloc(&w->d_err, sizeof(uint32_t)));
+		W_CUDA(cudaMemset(w->d_err, 0, sizeof(uint32_t)));
+	}
+	*out = w.release();
+	return B2A_OK;
+	W_CATCH
+}
+
+void b2a_writer_destroy(b2a_writer *w) {
+	if (!w) {
+		return;
+	}
+	if (w->device >= 0) {
+		cudaSetDevice(w->device);
+		for (void *p : w->allocs) {
+			cudaFree(p);
+		}
+		cudaFree(w->d_tasks);
+		cudaFree(w->d_tile_task);
+		cudaFree(w->d_null_counts);
+		cudaFree(w->d_err);
+	}
+	delete w;
+}
+
+int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
+	W_TRY
+	W_NEED_DEVICE(w);
+	if (w->measured) {
+		return B2A_OK;
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	WritePlan &p = w->plan;
+	EncodeLaunch l;
+	l.sm_count = w->sm_count;
+	l.d_err = w->d_err;
+	for (;;) {
+		// ---- fixed-size lists under a selection: child selection = sel[i / k] * k + i % k
+		for (;;) {
+			std::vector<b2a_enc_task> tasks;
+			std::vector<uint32_t> tiles;
+			const size_t n_before = p.nodes.size();
+			for (size_t i = 0; i < n_before; i++) {
+				if (!p.nodes[i].needs_expand_array || !p.nodes[i].children.empty()) {
+					continue;
+				}
+				const WVec v = p.vecs[static_cast<size_t>(p.nodes[i].vec)];
+				const uint64_t k = static_cast<uint64_t>(v.param), child_rows = p.nodes[i].rows * k;
+				void *sel = nullptr;
+				int rc = DeviceAlloc(w, child_rows * 4, &sel);
+				if (rc != B2A_OK) {
+					return rc;
+				}
+				b2a_enc_task t;
+				std::memset(&t, 0, sizeof(t));
+				t.op = B2A_ENC_EXPAND_ARRAY;
+				t.sel = p.nodes[i].sel;
+				t.rows = child_rows;
+				t.param = v.param;
+				t.dst = reinterpret_cast<uint64_t>(sel);
+				t.tile_rows = 16384;
+				t.tile0 = static_cast<uint32_t>(tiles.size());
+				tiles.insert(tiles.end(), (child_rows + t.tile_rows - 1) / t.tile_rows, static_cast<uint32_t>(tasks.size()));
+				tasks.push_back(t);
+				int child = p.AddNode(v.children.at(0), child_rows, 0, reinterpret_cast<uint64_t>(sel));
+				p.nodes[i].children.push_back(child);
+			}
+			if (tasks.empty()) {
+				break;
+			}
+			int rc = UploadTasks(w, tasks, tiles, st);
+			if (rc != B2A_OK) {
+				return rc;
+			}
+			l.d_tasks = w->d_tasks;
+			l.d_tile_task = w->d_tile_task;
+			l.n_tasks = static_cast<uint32_t>(tasks.size());
+			l.n_tiles = static_cast<uint32_t>(tiles.size());
+			if (l.n_tiles) {
+				int e = LaunchEncExpand(l, st);
+				if (e != 0) {
+					return SetLastError(B2A_ECUDA, std::string("CUDA error: ") +
+					                                   cudaGetErrorString(static_cast<cudaError_t>(e)));
+				}
+				w->launches++;
+			}
+		}
+		// ---- strings and lists: per-tile sums, per-task scan, totals back to the host
+		std::vector<int> pending = p.PendingScanNodes();
+		if (pending.empty()) {
+			break;
+		}
+		uint64_t n_tiles_total = 0;
+		for (int ni : pending) {
+			n_tiles_total += WritePlan::ScanTiles(p.nodes[static_cast<size_t>(ni)].rows);
+		}
+		void *chunk = nullptr;
+		int rc = DeviceAlloc(w, (n_tiles_total + pending.size()) * 8, &chunk);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+		uint64_t *base = static_cast<uint64_t *>(chunk);
+		uint64_t cursor = 0;
+		for (size_t j = 0; j < pending.size(); j++) {
+			WNode &n = p.nodes[static_cast<size_t>(pending[j])];
+			n.scratch = reinterpret_cast<uint64_t>(base + cursor);
+			n.counter = reinterpret_cast<uint64_t>(base + n_tiles_total + j);
+			cursor += WritePlan::ScanTiles(n.rows);
+		}
+		std::vector<b2a_enc_task> tasks;
+		std::vector<uint32_t> tiles;
+		p.ScanTasks(pending, tasks, tiles);
+		rc = UploadTasks(w, tasks, tiles, st);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+		l.d_tasks = w->d_tasks;
+		l.d_tile_task = w->d_tile_task;
+		l.n_tasks = static_cast<uint32_t>(tasks.size());
+		l.n_tiles = static_cast<uint32_t>(tiles.size());
+		int e = LaunchEncMeasure(l, st);
+		if (e != 0) {
+			return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+		}
+		w->launches += 2;
+		std::vector<uint64_t> totals(pending.size());
+		W_CUDA(cudaMemcpyAsync(totals.data(), base + n_tiles_total, pending.size() * 8, cudaMemcpyDeviceToHost, st));
+		W_CUDA(cudaStreamSynchronize(st));
+		// ---- lists: child selection vectors (ArrowListData::AppendOffsets child_sel), children become new nodes
+		std::vector<b2a_enc_task> xtasks;
+		std::vector<uint32_t> xtiles;
+		for (size_t j = 0; j < pending.size(); j++) {
+			const int ni = pending[j];
+			p.nodes[static_cast<size_t>(ni)].total = totals[j];
+			p.nodes[static_cast<size_t>(ni)].measured = true;
+			const WVec v = p.vecs[static_cast<size_t>(p.nodes[static_cast<size_t>(ni)].vec)];
+			if (v.op != B2A_ENC_LIST32 && v.op != B2A_ENC_LIST64) {
+				continue;
+			}
+			const WVec &cv = p.vecs[static_cast<size_t>(v.children.at(0))];
+			if (cv.rows > 0xFFFFFFFFull) {
+				return SetLastError(B2A_EINVAL, "writer: list child vector exceeds the sel_t (uint32) range");
+			}
+			void *sel = nullptr;
+			rc = DeviceAlloc(w, totals[j] * 4, &sel);
+			if (rc != B2A_OK) {
+				return rc;
+			}
+			b2a_enc_task t = tasks[j];
+			t.dst = reinterpret_cast<uint64_t>(sel);
+			t.tile0 = static_cast<uint32_t>(xtiles.size());
+			xtiles.insert(xtiles.end(), WritePlan::ScanTiles(t.rows), static_cast<uint32_t>(xtasks.size()));
+			xtasks.push_back(t);
+			int child = p.AddNode(v.children.at(0), totals[j], 0, reinterpret_cast<uint64_t>(sel));
+			p.nodes[static_cast<size_t>(ni)].children.push_back(child);
+		}
+		if (!xtasks.empty()) {
+			rc = UploadTasks(w, xtasks, xtiles, st);
+			if (rc != B2A_OK) {
+				return rc;
+			}
+			l.d_tasks = w->d_tasks;
+			l.d_tile_task = w->d_tile_task;
+			l.n_tasks = static_cast<uint32_t>(xtasks.size());
+			l.n_tiles = static_cast<uint32_t>(xtiles.size());
+			e = LaunchEncExpand(l, st);
+			if (e != 0) {
+				return SetLastError(B2A_ECUDA,
+				                    std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+			}
+			w->launches++;
+		}
+	}
+	// ---- everything is sized: lay the stream out and stage the encode tasks
+	p.Layout();
+	cudaFree(w->d_null_counts);
+	w->d_null_counts = nullptr;
+	W_CUDA(cudaMalloc(&w->d_null_counts, (p.nodes.size() ? p.nodes.size() : 1) * 8));
+	for (size_t i = 0; i < p.nodes.size(); i++) {
+		p.nodes[i].null_counter = reinterpret_cast<uint64_t>(w->d_null_counts + i);
+	}
+	std::vector<b2a_enc_task> tasks;
+	std::vector<uint32_t> tiles;
+	p.EncodeTasks(tasks, tiles);
+	int rc = UploadTasks(w, tasks, tiles, st);
+	if (rc != B2A_OK) {
+		return rc;
+	}
+	w->n_enc_tasks = static_cast<uint32_t>(tasks.size());
+	w->n_enc_tiles = static_cast<uint32_t>(tiles.size());
+	w->measured = true;
+	return B2A_OK;
+	W_CATCH
+}
+
+int b2a_writer_sizes(b2a_writer *w, uint64_t *stream_bytes, uint64_t *n_batches, uint64_t *body_bytes,
+                     uint64_t *algorithmic_bytes) {
+	if (!w->plan.laid_out) {
+		return SetLastError(B2A_EINVAL, "writer: call b2a_writer_measure first");
+	}
+	*stream_bytes = w->plan.stream_bytes;
+	*n_batches = w->plan.batches.size();
+	*body_bytes = w->plan.body_bytes;
+	*algorithmic_bytes = w->plan.algorithmic_in + w->plan.algorithmic_out;
+	return B2A_OK;
+}
+
+int b2a_writer_encode(b2a_writer *w, void *d_stream, void *cuda_stream) {
+	W_TRY
+	W_NEED_DEVICE(w);
+	if (!w->measured) {
+		return SetLastError(B2A_EINVAL, "writer: call b2a_writer_measure first");
+	}
+	if (!d_stream || (reinterpret_cast<uintptr_t>(d_stream) & 255) != 0) {
+		return SetLastError(B2A_EINVAL, "writer: the stream buffer must be a 256-byte aligned device pointer");
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	W_CUDA(cudaMemsetAsync(w->d_null_counts, 0, (w->plan.nodes.size() ? w->plan.nodes.size() : 1) * 8, st));
+	EncodeLaunch l;
+	l.sm_count = w->sm_count;
+	l.d_err = w->d_err;
+	l.d_tasks = w->d_tasks;
+	l.d_tile_task = w->d_tile_task;
+	l.n_tasks = w->n_enc_tasks;
+	l.n_tiles = w->n_enc_tiles;
+	l.stream_out = static_cast<uint8_t *>(d_stream);
+	int e = LaunchEncode(l, st);
+	if (e != 0) {
+		return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
+		                                   " launching b2a_encode_kernel");
+	}
+	if (l.n_tiles) {
+		w->launches++;
+	}
+	w->finished = false;
+	return B2A_OK;
+	W_CATCH
+}
+
+int b2a_writer_finish(b2a_writer *w, void *cuda_stream) {
+	W_TRY
+	W_NEED_DEVICE(w);
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	WritePlan &p = w->plan;
+	std::vector<uint64_t> nulls(p.nodes.size() ? p.nodes.size() : 1, 0);
+	uint32_t err = 0;
+	W_CUDA(cudaMemcpyAsync(nulls.data(), w->d_null_counts, nulls.size() * 8, cudaMemcpyDeviceToHost, st));
+	W_CUDA(cudaMemcpyAsync(&err, w->d_err, sizeof(err), cudaMemcpyDeviceToHost, st));
+	W_CUDA(cudaStreamSynchronize(st));
+	if (err != 0) {
+		W_CUDA(cudaMemsetAsync(w->d_err, 0, sizeof(uint32_t), st));
+		switch (err) {
+		case B2A_DEV_ENC_OFFSET_I32:
+			return SetLastError(B2A_EINVAL, "Arrow Appender: The maximum total string size for regular string buffers "
+			                                "is 2147483647 but the offset exceeds this.\n* SET "
+			                                "arrow_large_buffer_size=true to use large string buffers");
+		case B2A_DEV_ENC_LIST_I32:
+			return SetLastError(B2A_EINVAL, "Arrow Appender: The maximum combined list offset for regular list buffers "
+			                                "is 2147483647 but the offset exceeds this.\n* SET "
+			                                "arrow_large_buffer_size=true to use large list buffers");
+		default:
+			return SetLastError(B2A_EINTERNAL, "unknown device error code " + std::to_string(err));
+		}
+	}
+	for (size_t i = 0; i < p.nodes.size(); i++) {
+		const WVec &v = p.vecs[static_cast<size_t>(p.nodes[i].vec)];
+		p.nodes[i].null_count = v.type_id == B2A_T_SQLNULL ? static_cast<int64_t>(p.nodes[i].rows)
+		                                                   : static_cast<int64_t>(nulls[i]);
+	}
+	// "Arrow doesn't accept NULL keys on Maps" (map_data.hpp:97-100)
+	for (size_t i = 0; i < p.nodes.size(); i++) {
+		const WVec &v = p.vecs[static_cast<size_t>(p.nodes[i].vec)];
+		if (v.type_id == B2A_T_MAP && !p.nodes[i].children.empty()) {
+			const WNode &entries = p.nodes[static_cast<size_t>(p.nodes[i].children[0])];
+			if (!entries.children.empty() && p.nodes[static_cast<size_t>(entries.children[0])].null_count > 0) {
+				return SetLastError(B2A_EINVAL, "Arrow doesn't accept NULL keys on Maps");
+			}
+		}
+	}
+	w->finished = true;
+	return B2A_OK;
+	W_CATCH
+}
+
+int b2a_writer_headers(b2a_writer *w, void *h_stream) {
+	W_TRY
+	if (!w->finished) {
+		return SetLastError(B2A_EINVAL, "writer: call b2a_writer_finish first (null counts are part of the headers)");
+	}
+	const WritePlan &p = w->plan;
+	uint8_t *h = static_cast<uint8_t *>(h_stream);
+	std::memcpy(h, p.schema_message.data(), p.schema_message.size());
+	for (auto &b : p.batches) {
+		std::vector<NodeSlice> nodes;
+		std::vector<BufferSlice> buffers;
+		for (int ni : b.preorder) {
+			const WNode &n = p.nodes[static_cast<size_t>(ni)];
+			const WVec &v = p.vecs[static_cast<size_t>(n.vec)];
+			nodes.push_back(NodeSlice {static_cast<int64_t>(n.rows), n.null_count});
+			for (int k = 0; k < v.n_buffers; k++) {
+				buffers.push_back(n.buf[k]);
+			}
+		}
+		std::vector<uint8_t> msg = EncodeRecordBatchMessage(b.rows, nodes, buffers, b.body_length);
+		if (msg.size() != p.batch_header_bytes) {
+			return SetLastError(B2A_EINTERNAL, "writer: record batch header size changed after layout");
+		}
+		std::memcpy(h + b.meta_offset, msg.data(), msg.size());
+	}
+	std::vector<uint8_t> eos = EncodeEndOfStream();
+	std::memcpy(h + p.stream_bytes - eos.size(), eos.data(), eos.size());
+	return B2A_OK;
+	W_CATCH
+}
+
+int b2a_writer_batch(b2a_writer *w, uint64_t i, b2a_batch_info *out) {
+	const WritePlan &p = w->plan;
+	if (!p.laid_out || i >= p.batches.size()) {
+		return SetLastError(B2A_EINVAL, "writer: batch index out of range (or b2a_writer_measure not called)");
+	}
+	std::memset(out, 0, sizeof(*out));
+	out->rows = p.batches[i].rows;
+	out->meta_offset = p.batches[i].meta_offset;
+	out->body_offset = p.batches[i].body_offset;
+	out->body_length = p.batches[i].body_length;
+	out->buffer_bytes = p.batches[i].body_length;
+	return B2A_OK;
+}
+
+uint64_t b2a_writer_gpu_launches(b2a_writer *w) {
+	return w->launches;
+}
+
+} // extern "C"

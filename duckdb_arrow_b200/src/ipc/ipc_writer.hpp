@@ -1,0 +1,42 @@
+// Host-side Arrow IPC message encoder: Schema message, RecordBatch message headers, end-of-stream marker.
+// Replaces what the reference gets from nanoarrow's encoder (ArrowIpcEncoderEncodeSchema /
+// EncodeSimpleRecordBatch / FinalizeBuffer, call sites src/writer/column_data_collection_serializer.cpp:57-95)
+// and ArrowStreamWriter::{WriteSchema,Finalize} (src/writer/arrow_stream_writer.cpp:55-82).  Bodies are NOT built
+// here: the encode kernels write every buffer at the offset this header announces.
+#pragma once
+#include "ipc_reader.hpp"
+
+#include <string>
+#include <utility>
+#include <vector>
+
+namespace b2a {
+
+// Arrow type of one written field, derived from the DuckDB LogicalType by the rules of
+// duckdb/src/common/arrow/arrow_converter.cpp:115-432 (SetArrowFormat) with default ClientProperties
+// (regular 32-bit offsets, no lossless conversion, no string views, no list views).
+struct WriteField {
+	std::string name;
+	bool nullable = true;
+	int type_id = B2A_T_INVALID; // DuckDB type
+	int decimal_width = 0, decimal_scale = 0;
+	int64_t param = 0; // ARRAY size
+	std::string timezone;
+	std::vector<WriteField> children;
+	std::string format; // the C-data-interface format string the reference would set (for tests / diagnostics)
+};
+
+// Fills `format` (recursively) and validates that the type is writable; throws b2a::Error(B2A_ENOTIMPL) otherwise.
+void ResolveArrowFormat(WriteField &f);
+
+// Encapsulated messages: 0xFFFFFFFF, int32 metadata size (padded so the body starts 8-byte aligned), flatbuffer.
+std::vector<uint8_t> EncodeSchemaMessage(const std::vector<WriteField> &fields,
+                                         const std::vector<std::pair<std::string, std::string>> &kv_metadata);
+std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<NodeSlice> &nodes,
+                                              const std::vector<BufferSlice> &buffers, uint64_t body_length);
+// size of a RecordBatch message header with the given node / buffer counts (independent of the values)
+size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers);
+// ArrowStreamWriter::Finalize: FFFFFFFF 00000000
+std::vector<uint8_t> EncodeEndOfStream();
+
+} // namespace b2a

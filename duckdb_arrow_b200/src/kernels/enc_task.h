@@ -1,0 +1,49 @@
+// Device-visible descriptor of one encode task of the writer = one Arrow buffer (or offsets+data pair) of one
+// field of one record batch.  The write planner (src/writer/write_plan.cpp) emits them; b2a_encode_kernel walks
+// the whole table in one launch, like the decode side.
+#pragma once
+#include <stdint.h>
+
+/* ops: each restates one ArrowAppender routine (duckdb/src/include/duckdb/common/arrow/appender/...) */
+enum b2a_enc_op {
+	B2A_ENC_NONE = 0,
+	B2A_ENC_VALIDITY,     /* AppendValidity, append_data.hpp:127-149 (+ null_count) */
+	B2A_ENC_COPY,         /* ArrowScalarBaseData<T>::Append, scalar_data.hpp:90-119 */
+	B2A_ENC_WIDEN16,      /* ArrowScalarData<int32_t,int16_t>: DECIMAL(<=4) int16 -> decimal32 */
+	B2A_ENC_INTERVAL,     /* ArrowIntervalConverter: interval_t -> month-day-nano, NULLs skipped */
+	B2A_ENC_BOOL,         /* ArrowBoolData::Append, bool_data.cpp:12-39 */
+	B2A_ENC_STRING32,     /* ArrowVarcharData<string_t, ArrowVarcharConverter, int32_t>, varchar_data.hpp:53-111 */
+	B2A_ENC_STRING64,     /* ... int64_t offsets (arrow_large_buffer_size) */
+	B2A_ENC_LIST32,       /* ArrowListData<int32_t>::AppendOffsets, list_data.hpp:56-98 */
+	B2A_ENC_LIST64,
+	B2A_ENC_EXPAND_ARRAY, /* child selection of a fixed-size list under a selection (fixed_size_list_data.cpp:16-28) */
+	B2A_ENC_FILL_VALID    /* all-valid bitmap: ResizeValidity(.., 0xFF), append_data.hpp:116-119 */
+};
+
+#define B2A_ENC_F_LAST_PAD 0x1u /* unused */
+
+#define B2A_ENC_STR_TILE 2048u /* rows per tile of the scan-based ops (256 threads x 8 rows) */
+
+/* writer device error codes (atomicMax), continuing the numbering of task.h */
+#define B2A_DEV_ENC_OFFSET_I32 16u /* "Arrow Appender: The maximum total string size for regular string buffers is ..." */
+#define B2A_DEV_ENC_LIST_I32 17u   /* "Arrow Appender: The maximum combined list offset for regular list buffers is ..." */
+
+struct __attribute__((aligned(16))) b2a_enc_task {
+	uint64_t src;      /* device address: input vector data */
+	uint64_t validity; /* device address: ValidityMask words of the input vector, 0 = all valid */
+	uint64_t sel;      /* device address: uint32 selection (input row of output row i), 0 = identity */
+	uint64_t row0;     /* identity mapping: input row of output row 0 */
+	uint64_t rows;     /* output rows */
+	uint64_t dst;      /* stream offset of the main buffer (values / offsets / bits); EXPAND: device address of child sel */
+	uint64_t dst2;     /* stream offset of the character buffer */
+	uint64_t scratch;  /* device address: uint64 per tile of this task — tile sums, then (after the scan) tile bases */
+	uint64_t counter;  /* device address of a uint64: null_count (VALIDITY, atomicAdd) / total (scan kernel) */
+	int64_t param;     /* EXPAND_ARRAY: list size */
+	uint32_t tile0;
+	uint32_t tile_rows;
+	uint16_t op;
+	uint8_t src_width;
+	uint8_t dst_width;
+	uint32_t flags;
+	uint64_t dst_len; /* unpadded byte length of the main buffer (zero padding up to 8 is written by the last tile) */
+};

@@ -1,0 +1,704 @@
+// sm_100a encode kernels: DuckDB vectors (resident in HBM) -> Arrow IPC record-batch bodies, every buffer written
+// at its final stream offset.  Mirror image of decode.cu; each op restates one ArrowAppender routine
+// (duckdb/src/include/duckdb/common/arrow/appender/*.hpp, duckdb/src/common/arrow/appender/*.cpp).
+//
+//   pass 1  b2a_enc_measure_kernel : per 1 024-row tile, sum of string lengths / list lengths of valid rows
+//           b2a_enc_scan_kernel    : per task, exclusive scan of its tile sums (tile bases) + total
+//           b2a_enc_expand_kernel  : child selection vectors of lists (ArrowListData::AppendOffsets child_sel)
+//   pass 2  b2a_encode_kernel      : ONE launch for all buffers of all batches (persistent CTAs over a tile table)
+//
+// All integer/byte work, HBM-bound; no tensor cores.
+#include "encode.cuh"
+
+#include <cuda_runtime.h>
+
+#include <cstdlib>
+
+namespace b2a {
+
+static constexpr int kThreads = 256;
+static constexpr int kRowsPerThread = B2A_ENC_STR_TILE / kThreads; // 4
+static constexpr uint32_t kStageBytes = 40 * 1024;                 // shared-memory staging of one tile's characters
+
+__device__ __forceinline__ void enc_raise(uint32_t *err, uint32_t code) {
+	atomicMax(err, code);
+}
+__device__ __forceinline__ uint64_t map_row(const b2a_enc_task &t, uint64_t i) {
+	return t.sel ? static_cast<uint64_t>(__ldg(reinterpret_cast<const uint32_t *>(t.sel) + i)) : t.row0 + i;
+}
+__device__ __forceinline__ bool src_valid(const b2a_enc_task &t, uint64_t src_row) {
+	if (!t.validity) {
+		return true;
+	}
+	const uint64_t w = __ldg(reinterpret_cast<const unsigned long long *>(t.validity) + (src_row >> 6));
+	return (w >> (src_row & 63)) & 1;
+}
+__device__ __forceinline__ uint4 ld16(const void *p) {
+	uint4 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+	             : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+	             : "l"(p));
+	return r;
+}
+__device__ __forceinline__ uint2 ld8(const void *p) {
+	uint2 r;
+	asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+	return r;
+}
+__device__ __forceinline__ void st16(void *p, uint4 v) {
+	asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+	             : "memory");
+}
+__device__ __forceinline__ void st8(void *p, uint2 v) {
+	asm volatile("st.global.cs.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+// zero bytes [from, to) of the stream (buffer padding up to the next 8-byte boundary; nanoarrow pads with zeros)
+__device__ __forceinline__ void zero_range(uint8_t *p, uint64_t from, uint64_t to) {
+	for (uint64_t k = from + threadIdx.x; k < to; k += kThreads) {
+		p[k] = 0;
+	}
+}
+__device__ __forceinline__ uint64_t align8(uint64_t v) {
+	return (v + 7) & ~uint64_t(7);
+}
+
+// block-wide exclusive scan of one uint64 per thread; returns the exclusive prefix, *total = block sum
+__device__ __forceinline__ uint64_t block_exclusive_scan(uint64_t v, uint64_t *total) {
+	__shared__ uint64_t warp_sums[kThreads / 32];
+	__shared__ uint64_t block_total;
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	uint64_t inc = v;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		uint64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= static_cast<uint32_t>(o)) {
+			inc += n;
+		}
+	}
+	__syncthreads(); // previous use of warp_sums is over
+	if (lane == 31) {
+		warp_sums[warp] = inc;
+	}
+	__syncthreads();
+	uint64_t base = 0;
+#pragma unroll
+	for (int w = 0; w < kThreads / 32; w++) {
+		if (static_cast<uint32_t>(w) < warp) {
+			base += warp_sums[w];
+		}
+	}
+	if (threadIdx.x == kThreads - 1) {
+		block_total = base + inc;
+	}
+	__syncthreads();
+	*total = block_total;
+	return base + inc - v;
+}
+
+// length contributed by output row i of a STRING / LIST task (0 for NULL rows), and the raw 16-byte entry
+__device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i, uint4 &e, bool &valid) {
+	const uint64_t sr = map_row(t, i);
+	valid = src_valid(t, sr);
+	e = ld16(reinterpret_cast<const uint4 *>(t.src) + sr);
+	if (!valid) {
+		return 0;
+	}
+	if (t.op == B2A_ENC_STRING32 || t.op == B2A_ENC_STRING64) {
+		return e.x; // string_t.length
+	}
+	return (static_cast<uint64_t>(e.w) << 32) | e.z; // list_entry_t.length
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 1a: per-tile sums.  Simple grid-stride over the tile table (tiles are small and uniform).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+    b2a_enc_measure_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task,
+                           uint32_t n_tiles) {
+	__shared__ uint64_t warp_sums[kThreads / 32];
+	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+		const b2a_enc_task &t = tasks[__ldg(tile_task + tile)];
+		const uint32_t k = tile - t.tile0;
+		const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+		uint64_t sum = 0;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + u * kThreads + threadIdx.x; // any assignment works for a sum: coalesced
+			if (i < t.rows) {
+				uint4 e;
+				bool valid;
+				sum += entry_len(t, i, e, valid);
+			}
+		}
+		for (int o = 16; o > 0; o >>= 1) {
+			sum += __shfl_xor_sync(0xffffffffu, sum, o);
+		}
+		if ((threadIdx.x & 31) == 0) {
+			warp_sums[threadIdx.x >> 5] = sum;
+		}
+		__syncthreads();
+		if (threadIdx.x == 0) {
+			uint64_t s = 0;
+			for (int w = 0; w < kThreads / 32; w++) {
+				s += warp_sums[w];
+			}
+			reinterpret_cast<uint64_t *>(t.scratch)[k] = s;
+		}
+		__syncthreads();
+	}
+}
+
+// pass 1b: one warp per task: exclusive scan of its tile sums in place, total -> counters[t.counter]
+__global__ void __launch_bounds__(32)
+    b2a_enc_scan_kernel(const b2a_enc_task *__restrict__ tasks, uint32_t n_tasks) {
+	for (uint32_t ti = blockIdx.x; ti < n_tasks; ti += gridDim.x) {
+		const b2a_enc_task &t = tasks[ti];
+		const uint64_t n = (t.rows + B2A_ENC_STR_TILE - 1) / B2A_ENC_STR_TILE;
+		uint64_t *s = reinterpret_cast<uint64_t *>(t.scratch);
+		uint64_t carry = 0;
+		for (uint64_t base = 0; base < n; base += 32) {
+			const uint64_t i = base + threadIdx.x;
+			const uint64_t v = i < n ? s[i] : 0;
+			uint64_t inc = v;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				uint64_t x = __shfl_up_sync(0xffffffffu, inc, o);
+				if (threadIdx.x >= static_cast<uint32_t>(o)) {
+					inc += x;
+				}
+			}
+			if (i < n) {
+				s[i] = carry + inc - v;
+			}
+			carry += __shfl_sync(0xffffffffu, inc, 31);
+		}
+		if (threadIdx.x == 0) {
+			*reinterpret_cast<uint64_t *>(t.counter) = carry;
+		}
+	}
+}
+
+// pass 1c: child selection vectors.  LIST: sel[new_offset(i) + k] = entry.offset + k for every valid row i
+// (list_data.hpp:93-95); EXPAND_ARRAY: sel[i] = parent_sel[i / size] * size + i % size.
+__global__ void __launch_bounds__(kThreads)
+    b2a_enc_expand_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task,
+                          uint32_t n_tiles) {
+	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+		const b2a_enc_task &t = tasks[__ldg(tile_task + tile)];
+		const uint32_t k = tile - t.tile0;
+		uint32_t *out = reinterpret_cast<uint32_t *>(t.dst);
+		if (t.op == B2A_ENC_EXPAND_ARRAY) {
+			const uint64_t row0 = static_cast<uint64_t>(k) * t.tile_rows;
+			const uint64_t end = min(t.rows, row0 + t.tile_rows);
+			const uint64_t size = static_cast<uint64_t>(t.param);
+			for (uint64_t i = row0 + threadIdx.x; i < end; i += kThreads) {
+				out[i] = static_cast<uint32_t>(map_row(t, i / size) * size + i % size);
+			}
+			continue;
+		}
+		const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+		uint64_t len[kRowsPerThread], off0[kRowsPerThread], sum = 0;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+			len[u] = 0;
+			off0[u] = 0;
+			if (i < t.rows) {
+				uint4 e;
+				bool valid;
+				len[u] = entry_len(t, i, e, valid);
+				off0[u] = (static_cast<uint64_t>(e.y) << 32) | e.x; // list_entry_t.offset
+			}
+			sum += len[u];
+		}
+		uint64_t total;
+		uint64_t pos = reinterpret_cast<const uint64_t *>(t.scratch)[k] + block_exclusive_scan(sum, &total);
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			for (uint64_t j = 0; j < len[u]; j++) {
+				out[pos + j] = static_cast<uint32_t>(off0[u] + j);
+			}
+			pos += len[u];
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass 2 ops
+// ------------------------------------------------------------------------------------------------
+
+// K10: validity.  Arrow bitmap bit i = validity of input row map(i); the buffer is created 0xFF-filled
+// (ResizeValidity) so bits past `rows` in the last byte stay 1; bytes past ceil(rows/8) up to the 8-byte
+// boundary are zero padding.  One thread per 64-bit output word.  null_count -> counters[t.counter].
+__device__ __forceinline__ void enc_validity(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                             uint64_t nrows) {
+	const unsigned long long *mask = reinterpret_cast<const unsigned long long *>(t.validity);
+	const uint32_t *sel = reinterpret_cast<const uint32_t *>(t.sel);
+	unsigned long long *dst = reinterpret_cast<unsigned long long *>(stream + t.dst);
+	const uint64_t w0 = row0 >> 6, w1 = (row0 + nrows + 63) >> 6;
+	const uint64_t nbytes = (t.rows + 7) >> 3;
+	unsigned long long nulls = 0;
+	for (uint64_t w = w0 + threadIdx.x; w < w1; w += kThreads) {
+		const uint64_t first = w << 6;
+		uint64_t v = ~uint64_t(0);
+		if (mask) {
+			if (sel) {
+				v = 0;
+				for (int b = 0; b < 64 && first + b < t.rows; b++) {
+					const uint64_t sr = __ldg(sel + first + b);
+					v |= ((__ldg(mask + (sr >> 6)) >> (sr & 63)) & 1ull) << b;
+				}
+			} else {
+				const uint64_t s0 = t.row0 + first;
+				const uint32_t sh = static_cast<uint32_t>(s0 & 63);
+				v = __ldg(mask + (s0 >> 6)) >> sh;
+				if (sh && first + (64 - sh) < t.rows) { // the next word exists only if rows reach into it
+					v |= __ldg(mask + (s0 >> 6) + 1) << (64 - sh);
+				}
+			}
+		}
+		const uint64_t live = t.rows - first >= 64 ? 64 : t.rows - first; // rows in this word
+		const uint64_t live_mask = live == 64 ? ~uint64_t(0) : ((uint64_t(1) << live) - 1);
+		nulls += __popcll(~v & live_mask);
+		v |= ~live_mask; // bits past the last row: 1 ...
+		const uint64_t bytes_here = nbytes - (w << 3) >= 8 ? 8 : nbytes - (w << 3);
+		if (bytes_here < 8) {
+			v &= (uint64_t(1) << (8 * bytes_here)) - 1; // ... but padding bytes are zero
+		}
+		dst[w] = v;
+	}
+	for (int o = 16; o > 0; o >>= 1) {
+		nulls += __shfl_xor_sync(0xffffffffu, nulls, o);
+	}
+	if ((threadIdx.x & 31) == 0 && nulls) {
+		atomicAdd(reinterpret_cast<unsigned long long *>(t.counter), nulls);
+	}
+}
+
+// K11: scalar values (ArrowScalarBaseData::Append).  Identity mapping = a straight copy (16-byte vectors when both
+// sides allow, else 8-byte); through a selection = element gather.  NULL slots are copied like the reference does.
+__device__ __forceinline__ void enc_copy(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                         uint64_t nrows) {
+	const uint64_t w = t.src_width;
+	uint8_t *dst = stream + t.dst + row0 * w;
+	if (t.sel) {
+		const uint32_t *sel = reinterpret_cast<const uint32_t *>(t.sel) + row0;
+		const uint8_t *src = reinterpret_cast<const uint8_t *>(t.src);
+		for (uint64_t i = threadIdx.x; i < nrows; i += kThreads) {
+			const uint64_t sr = __ldg(sel + i);
+			switch (w) {
+			case 1:
+				dst[i] = __ldg(src + sr);
+				break;
+			case 2:
+				reinterpret_cast<uint16_t *>(dst)[i] = __ldg(reinterpret_cast<const uint16_t *>(src) + sr);
+				break;
+			case 4:
+				reinterpret_cast<uint32_t *>(dst)[i] = __ldg(reinterpret_cast<const uint32_t *>(src) + sr);
+				break;
+			case 8:
+				st8(reinterpret_cast<uint2 *>(dst) + i, ld8(reinterpret_cast<const uint2 *>(src) + sr));
+				break;
+			default: { // 16
+				const uint2 *p = reinterpret_cast<const uint2 *>(src) + 2 * sr;
+				st8(reinterpret_cast<uint2 *>(dst) + 2 * i, ld8(p));
+				st8(reinterpret_cast<uint2 *>(dst) + 2 * i + 1, ld8(p + 1));
+				break;
+			}
+			}
+		}
+		return;
+	}
+	const uint8_t *src = reinterpret_cast<const uint8_t *>(t.src) + (t.row0 + row0) * w;
+	const uint64_t bytes = nrows * w;
+	const uintptr_t a = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst);
+	uint64_t done = 0;
+	if ((a & 15) == 0) {
+		const uint64_t nvec = bytes >> 4;
+		constexpr int U = 4;
+		uint64_t i = threadIdx.x;
+		for (; i + (U - 1) * kThreads < nvec; i += U * kThreads) {
+			uint4 v[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				v[u] = ld16(src + ((i + u * kThreads) << 4));
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				st16(dst + ((i + u * kThreads) << 4), v[u]);
+			}
+		}
+		for (; i < nvec; i += kThreads) {
+			st16(dst + (i << 4), ld16(src + (i << 4)));
+		}
+		done = nvec << 4;
+	} else if ((a & 7) == 0) {
+		const uint64_t nvec = bytes >> 3;
+		constexpr int U = 4;
+		uint64_t i = threadIdx.x;
+		for (; i + (U - 1) * kThreads < nvec; i += U * kThreads) {
+			uint2 v[U];
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				v[u] = ld8(src + ((i + u * kThreads) << 3));
+			}
+#pragma unroll
+			for (int u = 0; u < U; u++) {
+				st8(dst + ((i + u * kThreads) << 3), v[u]);
+			}
+		}
+		for (; i < nvec; i += kThreads) {
+			st8(dst + (i << 3), ld8(src + (i << 3)));
+		}
+		done = nvec << 3;
+	}
+	for (uint64_t k = done + threadIdx.x; k < bytes; k += kThreads) {
+		dst[k] = src[k];
+	}
+}
+
+// ArrowScalarData<int32_t,int16_t> (DECIMAL width <= 4) and ArrowIntervalConverter (NULL rows skipped -> 0 here)
+__device__ __forceinline__ void enc_convert(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                            uint64_t nrows) {
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		const uint64_t sr = map_row(t, i);
+		if (t.op == B2A_ENC_WIDEN16) {
+			reinterpret_cast<int32_t *>(stream + t.dst)[i] =
+			    static_cast<int32_t>(__ldg(reinterpret_cast<const int16_t *>(t.src) + sr));
+		} else { // interval_t{i32 months, i32 days, i64 micros} -> ArrowInterval{i32, i32, i64 nanos}
+			uint2 a = make_uint2(0, 0), b = make_uint2(0, 0);
+			if (src_valid(t, sr)) {
+				const uint2 *p = reinterpret_cast<const uint2 *>(t.src) + 2 * sr;
+				a = ld8(p);
+				const uint2 m = ld8(p + 1);
+				const int64_t micros = static_cast<int64_t>((static_cast<uint64_t>(m.y) << 32) | m.x);
+				const uint64_t nanos = static_cast<uint64_t>(micros) * 1000ull; // Interval::NANOS_PER_MICRO
+				b = make_uint2(static_cast<uint32_t>(nanos), static_cast<uint32_t>(nanos >> 32));
+			}
+			uint2 *d = reinterpret_cast<uint2 *>(stream + t.dst) + 2 * i;
+			st8(d, a);
+			st8(d + 1, b);
+		}
+	}
+}
+
+// K13: bool bytes -> bits (ArrowBoolData::Append): the bit buffer starts all ones, a bit is cleared only for a VALID
+// false; bits past `rows` in the last byte stay 1.  One warp ballot per 32 rows.
+__device__ __forceinline__ void enc_bool(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                         uint64_t nrows) {
+	uint32_t *dst = reinterpret_cast<uint32_t *>(stream + t.dst);
+	const uint8_t *src = reinterpret_cast<const uint8_t *>(t.src);
+	const uint64_t end = row0 + nrows;
+	const uint64_t nbytes = (t.rows + 7) >> 3;
+	for (uint64_t base = row0 + (threadIdx.x & ~31u); base < end; base += kThreads) {
+		const uint64_t i = base + (threadIdx.x & 31);
+		bool bit = true;
+		if (i < t.rows) {
+			const uint64_t sr = map_row(t, i);
+			bit = !src_valid(t, sr) || __ldg(src + sr) != 0;
+		}
+		uint32_t word = __ballot_sync(0xffffffffu, bit);
+		if ((threadIdx.x & 31) == 0) {
+			const uint64_t byte0 = base >> 3;
+			const uint64_t bytes_here = nbytes - byte0 >= 4 ? 4 : nbytes - byte0;
+			if (bytes_here < 4) {
+				word &= (1u << (8 * bytes_here)) - 1;
+			}
+			dst[base >> 5] = word;
+		}
+	}
+}
+
+// K12: string_t -> offsets (running sum of lengths, NULL rows repeat the previous offset) + character bytes
+// (ArrowVarcharData::AppendTemplated).  Tile = 1 024 rows, thread = 4 consecutive rows.  The tile's characters form
+// one contiguous window of the data buffer: they are assembled in shared memory (inlined strings from registers,
+// long strings by warp-cooperative coalesced loads) and leave with aligned 16-byte stores.  Windows larger than the
+// staging area are written straight to global memory.
+template <typename OFF>
+__device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                           uint8_t *stage, uint32_t *err) {
+	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	const uint32_t lane = threadIdx.x & 31;
+	uint4 e[kRowsPerThread];
+	uint32_t len[kRowsPerThread];
+	uint64_t sum = 0;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		len[u] = 0;
+		e[u] = make_uint4(0, 0, 0, 0);
+		if (i < t.rows) {
+			bool valid;
+			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid));
+		}
+		sum += len[u];
+	}
+	uint64_t window;
+	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+	const uint64_t rel0 = block_exclusive_scan(sum, &window);
+	// ---- offsets: out[i + 1] = running sum through row i; out[0] = 0
+	OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
+	if (k == 0 && threadIdx.x == 0) {
+		offs[0] = 0;
+	}
+	{
+		uint64_t run = tile_base + rel0;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+			run += len[u];
+			if (i < t.rows) {
+				if (sizeof(OFF) == 4 && run > 0x7FFFFFFFull) {
+					enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
+				}
+				offs[i + 1] = static_cast<OFF>(run);
+			}
+		}
+	}
+	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the character buffer up to 8 bytes
+		const uint64_t total = tile_base + window;
+		zero_range(stream, t.dst2 + total, t.dst2 + align8(total));
+	}
+	if (window == 0) {
+		return;
+	}
+	// ---- characters
+	uint8_t *gdst = stream + t.dst2 + tile_base; // window start in the stream
+	const uint32_t phase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(gdst) & 15);
+	const bool staged = window + phase <= kStageBytes;
+	uint8_t *wdst = staged ? stage + phase : gdst; // where row bytes go: window-relative
+	uint64_t rel = rel0;
+	uint32_t long_mask[kRowsPerThread];
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		if (len[u] > 0 && len[u] <= 12) { // inlined: bytes live in e[u].y/z/w
+			const uint32_t wds[3] = {e[u].y, e[u].z, e[u].w};
+			for (uint32_t b = 0; b < len[u]; b++) {
+				wdst[rel + b] = static_cast<uint8_t>(wds[b >> 2] >> (8 * (b & 3)));
+			}
+		}
+		long_mask[u] = __ballot_sync(0xffffffffu, len[u] > 12);
+		rel += len[u];
+	}
+	// long strings: the whole warp copies one string at a time with coalesced byte loads
+	rel = rel0;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		uint32_t m = long_mask[u];
+		while (m) {
+			const int src_lane = __ffs(m) - 1;
+			m &= m - 1;
+			const uint32_t l = __shfl_sync(0xffffffffu, len[u], src_lane);
+			const uint32_t plo = __shfl_sync(0xffffffffu, e[u].z, src_lane);
+			const uint32_t phi = __shfl_sync(0xffffffffu, e[u].w, src_lane);
+			const uint64_t r = __shfl_sync(0xffffffffu, rel, src_lane);
+			const uint8_t *p = reinterpret_cast<const uint8_t *>((static_cast<uint64_t>(phi) << 32) | plo);
+			for (uint32_t b = lane; b < l; b += 32) {
+				wdst[r + b] = __ldg(p + b);
+			}
+		}
+		rel += len[u];
+	}
+	if (!staged) {
+		return;
+	}
+	__syncthreads();
+	// stage -> global: head bytes up to the first 16-byte boundary, aligned vectors, tail bytes
+	const uint64_t total = window;
+	uint64_t head = phase ? 16 - phase : 0;
+	if (head > total) {
+		head = total;
+	}
+	for (uint64_t b = threadIdx.x; b < head; b += kThreads) {
+		gdst[b] = stage[phase + b];
+	}
+	const uint64_t nvec = (total - head) >> 4;
+	const uint4 *svec = reinterpret_cast<const uint4 *>(stage + phase + head); // 16-byte aligned in shared memory
+	uint4 *gvec = reinterpret_cast<uint4 *>(gdst + head);
+	for (uint64_t v = threadIdx.x; v < nvec; v += kThreads) {
+		st16(gvec + v, svec[v]);
+	}
+	for (uint64_t b = head + (nvec << 4) + threadIdx.x; b < total; b += kThreads) {
+		gdst[b] = stage[phase + b];
+	}
+}
+
+// ArrowListData<BUFTYPE>::AppendOffsets: offsets only (children are appended through the selection built by
+// b2a_enc_expand_kernel)
+template <typename OFF>
+__device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                         uint32_t *err) {
+	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	uint64_t len[kRowsPerThread], sum = 0;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		len[u] = 0;
+		if (i < t.rows) {
+			uint4 e;
+			bool valid;
+			len[u] = entry_len(t, i, e, valid);
+		}
+		sum += len[u];
+	}
+	uint64_t window;
+	uint64_t run = reinterpret_cast<const uint64_t *>(t.scratch)[k] + block_exclusive_scan(sum, &window);
+	OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
+	if (k == 0 && threadIdx.x == 0) {
+		offs[0] = 0;
+	}
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		run += len[u];
+		if (i < t.rows) {
+			if (sizeof(OFF) == 4 && run > 0x7FFFFFFFull) {
+				enc_raise(err, B2A_DEV_ENC_LIST_I32);
+			}
+			offs[i + 1] = static_cast<OFF>(run);
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// the encode kernel: persistent CTAs stride over the tile table, next descriptor prefetched with cp.async
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void enc_cp_async16(void *smem, const void *gmem) {
+	const uint32_t sa = static_cast<uint32_t>(__cvta_generic_to_shared(smem));
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void enc_cp_async_wait_all() {
+	asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+static constexpr uint32_t kEncTaskVecs = sizeof(b2a_enc_task) / 16;
+static_assert(sizeof(b2a_enc_task) % 16 == 0, "b2a_enc_task is copied in 16-byte pieces");
+
+__global__ void __launch_bounds__(kThreads)
+    b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
+                      uint8_t *__restrict__ stream, uint32_t *err) {
+	__shared__ b2a_enc_task s_task[2];
+	__shared__ __align__(16) uint8_t stage[kStageBytes];
+	uint32_t tile = blockIdx.x;
+	if (tile >= n_tiles) {
+		return;
+	}
+	const uint32_t stride = gridDim.x;
+	const bool loader = threadIdx.x < kEncTaskVecs;
+	uint32_t ti_next = 0;
+	if (loader) {
+		const uint32_t ti = __ldg(tile_task + tile);
+		reinterpret_cast<uint4 *>(&s_task[0])[threadIdx.x] =
+		    __ldg(reinterpret_cast<const uint4 *>(tasks + ti) + threadIdx.x);
+		if (tile + stride < n_tiles) {
+			ti_next = __ldg(tile_task + tile + stride);
+		}
+	}
+	__syncthreads();
+	for (uint32_t buf = 0;; buf ^= 1) {
+		const uint32_t next = tile + stride;
+		if (loader && next < n_tiles) {
+			enc_cp_async16(reinterpret_cast<uint4 *>(&s_task[buf ^ 1]) + threadIdx.x,
+			               reinterpret_cast<const uint4 *>(tasks + ti_next) + threadIdx.x);
+			if (next + stride < n_tiles) {
+				ti_next = __ldg(tile_task + next + stride);
+			}
+		}
+		const b2a_enc_task &t = s_task[buf];
+		const uint32_t k = tile - t.tile0;
+		const uint64_t row0 = static_cast<uint64_t>(k) * t.tile_rows;
+		uint64_t nrows = t.rows > row0 ? t.rows - row0 : 0;
+		if (nrows > t.tile_rows) {
+			nrows = t.tile_rows;
+		}
+		switch (t.op) {
+		case B2A_ENC_VALIDITY:
+		case B2A_ENC_FILL_VALID:
+			enc_validity(t, stream, row0, nrows);
+			break;
+		case B2A_ENC_COPY:
+			enc_copy(t, stream, row0, nrows);
+			break;
+		case B2A_ENC_WIDEN16:
+		case B2A_ENC_INTERVAL:
+			enc_convert(t, stream, row0, nrows);
+			break;
+		case B2A_ENC_BOOL:
+			enc_bool(t, stream, row0, nrows);
+			break;
+		case B2A_ENC_STRING32:
+			enc_string<int32_t>(t, stream, k, stage, err);
+			break;
+		case B2A_ENC_STRING64:
+			enc_string<int64_t>(t, stream, k, stage, err);
+			break;
+		case B2A_ENC_LIST32:
+			enc_list<int32_t>(t, stream, k, err);
+			break;
+		case B2A_ENC_LIST64:
+			enc_list<int64_t>(t, stream, k, err);
+			break;
+		default:
+			break;
+		}
+		if (row0 + t.tile_rows >= t.rows) { // last tile of the task: zero padding of the main buffer up to 8 bytes
+			zero_range(stream, t.dst + t.dst_len, t.dst + align8(t.dst_len));
+		}
+		if (next >= n_tiles) {
+			break;
+		}
+		enc_cp_async_wait_all();
+		__syncthreads();
+		tile = next;
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+static uint32_t PersistentGrid(const void *kernel, int sm_count, uint32_t n_tiles) {
+	int per_sm = 0;
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm <= 0) {
+		per_sm = 2;
+	}
+	uint32_t grid = static_cast<uint32_t>(sm_count) * static_cast<uint32_t>(per_sm);
+	return grid > n_tiles ? n_tiles : grid;
+}
+
+int LaunchEncMeasure(const EncodeLaunch &l, void *stream) {
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	if (l.n_tiles) {
+		uint32_t grid = static_cast<uint32_t>(l.sm_count) * 8;
+		grid = grid > l.n_tiles ? l.n_tiles : grid;
+		b2a_enc_measure_kernel<<<grid, kThreads, 0, st>>>(l.d_tasks, l.d_tile_task, l.n_tiles);
+	}
+	if (l.n_tasks) {
+		uint32_t grid = l.n_tasks < 65535u ? l.n_tasks : 65535u;
+		b2a_enc_scan_kernel<<<grid, 32, 0, st>>>(l.d_tasks, l.n_tasks);
+	}
+	return static_cast<int>(cudaGetLastError());
+}
+
+int LaunchEncExpand(const EncodeLaunch &l, void *stream) {
+	if (l.n_tiles == 0) {
+		return 0;
+	}
+	uint32_t grid = static_cast<uint32_t>(l.sm_count) * 8;
+	grid = grid > l.n_tiles ? l.n_tiles : grid;
+	b2a_enc_expand_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(l.d_tasks, l.d_tile_task,
+	                                                                              l.n_tiles);
+	return static_cast<int>(cudaGetLastError());
+}
+
+int LaunchEncode(const EncodeLaunch &l, void *stream) {
+	if (l.n_tiles == 0) {
+		return 0;
+	}
+	const uint32_t grid = PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel), l.sm_count, l.n_tiles);
+	b2a_encode_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+	    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
+	return static_cast<int>(cudaGetLastError());
+}
+
+} // namespace b2a

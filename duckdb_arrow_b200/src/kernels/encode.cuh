@@ -1,0 +1,25 @@
+// Launch interface of the encode kernels (host side of src/kernels, writer direction).
+#pragma once
+#include "b2arrow.h"
+#include "enc_task.h"
+
+#include <stdint.h>
+
+namespace b2a {
+
+struct EncodeLaunch {
+	const b2a_enc_task *d_tasks = nullptr;
+	const uint32_t *d_tile_task = nullptr;
+	uint32_t n_tasks = 0;
+	uint32_t n_tiles = 0;
+	uint8_t *stream_out = nullptr;  // device image of the IPC stream being produced
+	uint32_t *d_err = nullptr;
+	int sm_count = 148;
+};
+
+// each returns cudaError_t as int
+int LaunchEncMeasure(const EncodeLaunch &l, void *stream); // tile sums + per-task scan
+int LaunchEncExpand(const EncodeLaunch &l, void *stream);  // child selection vectors
+int LaunchEncode(const EncodeLaunch &l, void *stream);     // pass 2
+
+} // namespace b2a

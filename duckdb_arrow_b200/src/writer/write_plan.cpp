@@ -1,0 +1,359 @@
+#include "write_plan.hpp"
+
+#include <algorithm>
+#include <cstring>
+
+namespace b2a {
+
+static const uint64_t kCopyTileBytes = 256 * 1024;
+
+static uint64_t Align8(uint64_t v) {
+	return (v + 7) & ~uint64_t(7);
+}
+
+int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
+	if (depth > 32) {
+		throw Error(B2A_EINVAL, "writer: type nesting too deep");
+	}
+	WVec w;
+	w.type_id = v.type_id;
+	w.param = v.param;
+	w.data = reinterpret_cast<uint64_t>(v.data);
+	w.validity = reinterpret_cast<uint64_t>(v.validity);
+	w.rows = v.rows;
+	wf.name = v.name ? v.name : "";
+	wf.type_id = v.type_id;
+	wf.decimal_width = v.decimal_width;
+	wf.decimal_scale = v.decimal_scale;
+	wf.param = v.param;
+	wf.timezone = v.timezone ? v.timezone : "";
+	auto fixed = [&](int width) {
+		w.op = B2A_ENC_COPY;
+		w.src_width = w.dst_width = width;
+		w.n_buffers = 2;
+	};
+	switch (v.type_id) {
+	case B2A_T_SQLNULL:
+		w.n_buffers = 0;
+		break;
+	case B2A_T_BOOLEAN:
+		w.op = B2A_ENC_BOOL;
+		w.src_width = 1;
+		w.n_buffers = 2;
+		break;
+	case B2A_T_TINYINT:
+	case B2A_T_UTINYINT:
+		fixed(1);
+		break;
+	case B2A_T_SMALLINT:
+	case B2A_T_USMALLINT:
+		fixed(2);
+		break;
+	case B2A_T_INTEGER:
+	case B2A_T_UINTEGER:
+	case B2A_T_FLOAT:
+	case B2A_T_DATE:
+		fixed(4);
+		break;
+	case B2A_T_BIGINT:
+	case B2A_T_UBIGINT:
+	case B2A_T_DOUBLE:
+	case B2A_T_TIME:
+	case B2A_T_TIMESTAMP:
+	case B2A_T_TIMESTAMP_SEC:
+	case B2A_T_TIMESTAMP_MS:
+	case B2A_T_TIMESTAMP_NS:
+	case B2A_T_TIMESTAMP_TZ:
+		fixed(8);
+		break;
+	case B2A_T_HUGEINT:
+		fixed(16);
+		break;
+	case B2A_T_DECIMAL:
+		if (v.decimal_width <= 4) { // ArrowScalarData<int32_t, int16_t>, arrow_appender.cpp:218-220
+			w.op = B2A_ENC_WIDEN16;
+			w.src_width = 2;
+			w.dst_width = 4;
+			w.n_buffers = 2;
+		} else {
+			fixed(v.decimal_width <= 9 ? 4 : v.decimal_width <= 18 ? 8 : 16);
+		}
+		break;
+	case B2A_T_INTERVAL:
+		w.op = B2A_ENC_INTERVAL;
+		w.src_width = w.dst_width = 16;
+		w.n_buffers = 2;
+		break;
+	case B2A_T_VARCHAR:
+	case B2A_T_BLOB:
+		w.op = B2A_ENC_STRING32;
+		w.src_width = 16;
+		w.dst_width = 4;
+		w.n_buffers = 3;
+		break;
+	case B2A_T_LIST:
+	case B2A_T_MAP:
+		w.op = B2A_ENC_LIST32;
+		w.src_width = 16;
+		w.dst_width = 4;
+		w.n_buffers = 2;
+		break;
+	case B2A_T_STRUCT:
+	case B2A_T_ARRAY:
+		w.n_buffers = 1;
+		break;
+	default:
+		throw Error(B2A_ENOTIMPL, "Unsupported type in DuckDB -> Arrow Conversion: type id " +
+		                              std::to_string(v.type_id));
+	}
+	if (w.op != B2A_ENC_NONE && v.rows > 0 && !v.data) {
+		throw Error(B2A_EINVAL, "writer: vector '" + wf.name + "' has no data pointer");
+	}
+	const int idx = static_cast<int>(vecs.size());
+	vecs.push_back(w);
+	if (v.n_children < 0 || (v.n_children > 0 && !v.children)) {
+		throw Error(B2A_EINVAL, "writer: bad children of '" + wf.name + "'");
+	}
+	wf.children.resize(static_cast<size_t>(v.n_children));
+	for (int c = 0; c < v.n_children; c++) {
+		int ci = AddVec(v.children[c], wf.children[static_cast<size_t>(c)], depth + 1);
+		vecs[static_cast<size_t>(idx)].children.push_back(ci);
+	}
+	if (v.type_id == B2A_T_MAP && v.n_children == 1) {
+		vecs[static_cast<size_t>(vecs[static_cast<size_t>(idx)].children[0])].no_validity_buffer = true;
+	}
+	return idx;
+}
+
+void WritePlan::Build(const b2a_vector *columns, uint32_t n_columns, uint64_t rows, const b2a_write_options *opt) {
+	if (n_columns == 0 || !columns) {
+		throw Error(B2A_EINVAL, "writer: no columns");
+	}
+	row_group_size = (opt && opt->row_group_size) ? opt->row_group_size : 122880;
+	if (opt) {
+		for (uint32_t i = 0; i < opt->n_kv_metadata; i++) {
+			kv_metadata.emplace_back(opt->kv_keys[i], opt->kv_values[i]);
+		}
+	}
+	total_rows = rows;
+	fields.resize(n_columns);
+	for (uint32_t c = 0; c < n_columns; c++) {
+		if (columns[c].rows != rows) {
+			throw Error(B2A_EINVAL, "writer: column " + std::to_string(c) + " has " + std::to_string(columns[c].rows) +
+			                            " rows, expected " + std::to_string(rows));
+		}
+		top_vecs.push_back(AddVec(columns[c], fields[c], 0));
+		ResolveArrowFormat(fields[c]);
+	}
+	schema_message = EncodeSchemaMessage(fields, kv_metadata);
+	for (uint64_t r0 = 0; r0 < rows; r0 += row_group_size) {
+		WBatch b;
+		b.row0 = r0;
+		b.rows = std::min(row_group_size, rows - r0);
+		batches.push_back(b);
+	}
+	for (auto &b : batches) {
+		for (int tv : top_vecs) {
+			int n = AddNode(tv, b.rows, b.row0, 0);
+			b.top.push_back(n);
+		}
+	}
+}
+
+int WritePlan::AddNode(int vec, uint64_t rows, uint64_t row0, uint64_t sel) {
+	const WVec v = vecs[static_cast<size_t>(vec)];
+	if (!sel && row0 + rows > v.rows) {
+		throw Error(B2A_EINVAL, "writer: vector shorter than the rows it must provide");
+	}
+	WNode n;
+	n.vec = vec;
+	n.rows = rows;
+	n.row0 = row0;
+	n.sel = sel;
+	std::memset(n.buf, 0, sizeof(n.buf));
+	const int idx = static_cast<int>(nodes.size());
+	nodes.push_back(n);
+	if (v.type_id == B2A_T_STRUCT) {
+		for (int c : v.children) {
+			int ci = AddNode(c, rows, row0, sel);
+			nodes[static_cast<size_t>(idx)].children.push_back(ci);
+		}
+	} else if (v.type_id == B2A_T_ARRAY) {
+		const uint64_t k = static_cast<uint64_t>(v.param);
+		if (!sel) { // fixed_size_list_data.cpp:16-28: child rows [from*size, to*size)
+			int ci = AddNode(v.children.at(0), rows * k, row0 * k, 0);
+			nodes[static_cast<size_t>(idx)].children.push_back(ci);
+		} else {
+			nodes[static_cast<size_t>(idx)].needs_expand_array = true;
+		}
+	}
+	return idx;
+}
+
+std::vector<int> WritePlan::PendingScanNodes() const {
+	std::vector<int> out;
+	for (size_t i = 0; i < nodes.size(); i++) {
+		if (!nodes[i].measured && IsScanOp(vecs[static_cast<size_t>(nodes[i].vec)].op)) {
+			out.push_back(static_cast<int>(i));
+		}
+	}
+	return out;
+}
+
+void WritePlan::Preorder(int node, std::vector<int> &out) const {
+	out.push_back(node);
+	for (int c : nodes[static_cast<size_t>(node)].children) {
+		Preorder(c, out);
+	}
+}
+
+void WritePlan::Layout() {
+	size_t n_nodes = 0, n_buffers = 0;
+	uint64_t cursor = schema_message.size();
+	body_bytes = 0;
+	algorithmic_in = algorithmic_out = 0;
+	for (size_t bi = 0; bi < batches.size(); bi++) {
+		WBatch &b = batches[bi];
+		b.preorder.clear();
+		for (int t : b.top) {
+			Preorder(t, b.preorder);
+		}
+		uint64_t off = 0;
+		size_t nb = 0;
+		for (int ni : b.preorder) {
+			WNode &n = nodes[static_cast<size_t>(ni)];
+			const WVec &v = vecs[static_cast<size_t>(n.vec)];
+			nb += static_cast<size_t>(v.n_buffers);
+			if (v.n_buffers >= 1) { // validity
+				uint64_t len = v.no_validity_buffer ? 0 : (n.rows + 7) / 8;
+				n.buf[0] = BufferSlice {off, len};
+				off += Align8(len);
+				if (v.validity) {
+					algorithmic_in += len;
+				}
+			}
+			if (v.n_buffers >= 2) {
+				uint64_t len = 0;
+				switch (v.op) {
+				case B2A_ENC_BOOL:
+					len = (n.rows + 7) / 8;
+					break;
+				case B2A_ENC_STRING32:
+				case B2A_ENC_LIST32:
+					len = (n.rows + 1) * 4;
+					break;
+				case B2A_ENC_STRING64:
+				case B2A_ENC_LIST64:
+					len = (n.rows + 1) * 8;
+					break;
+				default:
+					len = n.rows * static_cast<uint64_t>(v.dst_width);
+					break;
+				}
+				n.buf[1] = BufferSlice {off, len};
+				off += Align8(len);
+				algorithmic_in += n.rows * static_cast<uint64_t>(v.src_width);
+			}
+			if (v.n_buffers >= 3) {
+				n.buf[2] = BufferSlice {off, n.total};
+				off += Align8(n.total);
+			}
+		}
+		if (bi == 0) {
+			n_nodes = b.preorder.size();
+			n_buffers = nb;
+			batch_header_bytes = RecordBatchMessageSize(n_nodes, n_buffers);
+		}
+		b.meta_offset = cursor;
+		b.body_offset = cursor + batch_header_bytes;
+		b.body_length = off;
+		cursor = b.body_offset + off;
+		body_bytes += off;
+	}
+	algorithmic_out = body_bytes;
+	stream_bytes = cursor + 8; // end-of-stream marker
+	laid_out = true;
+}
+
+b2a_enc_task WritePlan::BaseTask(const WNode &n, const WVec &v) const {
+	b2a_enc_task t;
+	std::memset(&t, 0, sizeof(t));
+	t.src = v.data;
+	t.validity = v.validity;
+	t.sel = n.sel;
+	t.row0 = n.row0;
+	t.rows = n.rows;
+	t.param = v.param;
+	t.op = static_cast<uint16_t>(v.op);
+	t.src_width = static_cast<uint8_t>(v.src_width);
+	t.dst_width = static_cast<uint8_t>(v.dst_width);
+	t.scratch = n.scratch;
+	t.counter = n.counter;
+	return t;
+}
+
+static void PushTask(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task, b2a_enc_task t,
+                     uint64_t n_tiles) {
+	if (tile_task.size() + n_tiles > 0xFFFFFFF0ull) {
+		throw Error(B2A_EINVAL, "writer: table too large for one launch");
+	}
+	t.tile0 = static_cast<uint32_t>(tile_task.size());
+	tile_task.insert(tile_task.end(), n_tiles, static_cast<uint32_t>(tasks.size()));
+	tasks.push_back(t);
+}
+
+void WritePlan::ScanTasks(const std::vector<int> &node_ids, std::vector<b2a_enc_task> &tasks,
+                          std::vector<uint32_t> &tile_task) const {
+	for (int ni : node_ids) {
+		const WNode &n = nodes[static_cast<size_t>(ni)];
+		b2a_enc_task t = BaseTask(n, vecs[static_cast<size_t>(n.vec)]);
+		t.tile_rows = B2A_ENC_STR_TILE;
+		PushTask(tasks, tile_task, t, ScanTiles(n.rows));
+	}
+}
+
+void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const {
+	for (auto &b : batches) {
+		for (int ni : b.preorder) {
+			const WNode &n = nodes[static_cast<size_t>(ni)];
+			const WVec &v = vecs[static_cast<size_t>(n.vec)];
+			if (v.n_buffers >= 1 && !v.no_validity_buffer && n.rows > 0) {
+				b2a_enc_task t = BaseTask(n, v);
+				t.op = B2A_ENC_VALIDITY;
+				t.dst = b.body_offset + n.buf[0].offset;
+				t.dst_len = n.buf[0].length;
+				t.counter = n.null_counter;
+				t.tile_rows = 1u << 20;
+				PushTask(tasks, tile_task, t, (n.rows + t.tile_rows - 1) / t.tile_rows);
+			}
+			if (v.n_buffers < 2) {
+				continue;
+			}
+			b2a_enc_task t = BaseTask(n, v);
+			t.dst = b.body_offset + n.buf[1].offset;
+			t.dst_len = n.buf[1].length;
+			if (IsScanOp(v.op)) {
+				t.tile_rows = B2A_ENC_STR_TILE;
+				if (v.n_buffers >= 3) {
+					t.dst2 = b.body_offset + n.buf[2].offset;
+				}
+				PushTask(tasks, tile_task, t, ScanTiles(n.rows));
+				continue;
+			}
+			if (n.rows == 0) {
+				continue;
+			}
+			uint64_t tile_rows;
+			if (v.op == B2A_ENC_BOOL) {
+				tile_rows = 1u << 18;
+			} else {
+				tile_rows = kCopyTileBytes / static_cast<uint64_t>(v.src_width + v.dst_width);
+				tile_rows = std::max<uint64_t>(2048, tile_rows / 2048 * 2048);
+			}
+			t.tile_rows = static_cast<uint32_t>(tile_rows);
+			PushTask(tasks, tile_task, t, (n.rows + tile_rows - 1) / tile_rows);
+		}
+	}
+}
+
+} // namespace b2a

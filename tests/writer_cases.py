@@ -1,0 +1,131 @@
+"""Seeded input tables for the writer tests (the types DuckDB's ArrowAppender can write), and a helper that rebuilds
+pyarrow arrays from (nodes, buffers) as produced by the oracle / found in a record batch."""
+from __future__ import annotations
+
+import decimal
+
+import numpy as np
+import pyarrow as pa
+
+
+def _nullify(rng, values: list, p=0.15):
+    return [None if rng.random() < p else v for v in values]
+
+
+def scalar_table(n=5000, seed=1) -> pa.Table:
+    rng = np.random.default_rng(seed)
+    words = ["", "a", "bc", "twelve bytes", "thirteen byte", "a considerably longer string value €µ",
+             "x" * 100, "mid-size str"]
+    cols = {
+        "i8": pa.array(_nullify(rng, rng.integers(-128, 128, n).tolist()), pa.int8()),
+        "i16": pa.array(rng.integers(-2**15, 2**15, n), pa.int16()),
+        "i32": pa.array(_nullify(rng, rng.integers(-2**31, 2**31, n).tolist()), pa.int32()),
+        "i64": pa.array(_nullify(rng, rng.integers(-2**62, 2**62, n).tolist()), pa.int64()),
+        "u8": pa.array(rng.integers(0, 256, n), pa.uint8()),
+        "u16": pa.array(rng.integers(0, 2**16, n), pa.uint16()),
+        "u32": pa.array(_nullify(rng, rng.integers(0, 2**32, n).tolist()), pa.uint32()),
+        "u64": pa.array(rng.integers(0, 2**63, n).astype(np.uint64), pa.uint64()),
+        "f32": pa.array(_nullify(rng, rng.random(n).astype(np.float32).tolist()), pa.float32()),
+        "f64": pa.array(rng.random(n), pa.float64()),
+        "b": pa.array(_nullify(rng, (rng.random(n) < 0.5).tolist()), pa.bool_()),
+        "b_nonull": pa.array(rng.random(n) < 0.3, pa.bool_()),
+        "date": pa.array(_nullify(rng, rng.integers(0, 20000, n).tolist()), pa.date32()),
+        "ts_us": pa.array(_nullify(rng, rng.integers(0, 2**50, n).tolist()), pa.timestamp("us")),
+        "ts_s": pa.array(rng.integers(0, 2**31, n), pa.timestamp("s")),
+        "ts_ms": pa.array(rng.integers(0, 2**41, n), pa.timestamp("ms")),
+        "ts_ns": pa.array(rng.integers(0, 2**60, n), pa.timestamp("ns")),
+        "ts_tz": pa.array(_nullify(rng, rng.integers(0, 2**50, n).tolist()), pa.timestamp("us", tz="UTC")),
+        "time": pa.array(rng.integers(0, 86400_000_000, n), pa.time64("us")),
+        "dec4": pa.array(_nullify(rng, [decimal.Decimal(int(x)).scaleb(-1) for x in rng.integers(-999, 1000, n)]),
+                         pa.decimal32(4, 1)),
+        "dec9": pa.array([decimal.Decimal(int(x)).scaleb(-2) for x in rng.integers(-10**8, 10**8, n)],
+                         pa.decimal32(9, 2)),
+        "dec18": pa.array(_nullify(rng, [decimal.Decimal(int(x)).scaleb(-3) for x in rng.integers(-10**17, 10**17, n)]),
+                          pa.decimal64(18, 3)),
+        "dec38": pa.array(_nullify(rng, [decimal.Decimal(int(x) * 10**15 + 7).scaleb(-4)
+                                         for x in rng.integers(-10**17, 10**17, n)]), pa.decimal128(38, 4)),
+        "s": pa.array(_nullify(rng, [words[i] for i in rng.integers(0, len(words), n)]), pa.string()),
+        "s_nonull": pa.array([words[i] + str(i) for i in rng.integers(0, len(words), n)], pa.string()),
+        "bin": pa.array(_nullify(rng, [bytes(rng.integers(0, 256, int(l)).astype(np.uint8))
+                                       for l in rng.integers(0, 40, n)]), pa.binary()),
+        "nul": pa.nulls(n),
+        "iv": pa.array(_nullify(rng, [pa.MonthDayNano([int(a), int(b), int(c) * 1000]) for a, b, c in
+                                      zip(rng.integers(-100, 100, n), rng.integers(-1000, 1000, n),
+                                          rng.integers(-10**12, 10**12, n))]), pa.month_day_nano_interval()),
+    }
+    return pa.table(cols)
+
+
+def nested_table(n=3000, seed=2) -> pa.Table:
+    rng = np.random.default_rng(seed)
+
+    def ilist(maxlen=5, p=0.15):
+        return [None if rng.random() < p else rng.integers(-1000, 1000, int(rng.integers(0, maxlen))).tolist()
+                for _ in range(n)]
+
+    strs = ["", "k", "key-two", "a key longer than twelve", "zz"]
+    cols = {
+        "l_i64": pa.array(ilist(), pa.list_(pa.int64())),
+        "l_str": pa.array([None if rng.random() < 0.1 else
+                           [None if rng.random() < 0.2 else strs[int(j)] for j in rng.integers(0, len(strs), int(rng.integers(0, 4)))]
+                           for _ in range(n)], pa.list_(pa.string())),
+        "ll": pa.array([None if rng.random() < 0.1 else
+                        [None if rng.random() < 0.2 else rng.integers(0, 9, int(rng.integers(0, 3))).tolist()
+                         for _ in range(int(rng.integers(0, 4)))] for _ in range(n)], pa.list_(pa.list_(pa.int32()))),
+        "st": pa.array([None if rng.random() < 0.1 else {"a": int(i) if i % 7 else None, "b": strs[i % len(strs)]}
+                        for i in range(n)], pa.struct([("a", pa.int32()), ("b", pa.string())])),
+        "l_st": pa.array([None if rng.random() < 0.1 else
+                          [{"x": int(j), "y": None if j % 3 == 0 else float(j)} for j in range(int(rng.integers(0, 4)))]
+                          for _ in range(n)], pa.list_(pa.struct([("x", pa.int64()), ("y", pa.float64())]))),
+        "m": pa.array([None if rng.random() < 0.1 else
+                       [(f"k{j}", None if j % 4 == 0 else int(j)) for j in range(int(rng.integers(0, 4)))]
+                       for _ in range(n)], pa.map_(pa.string(), pa.int64())),
+        "arr": pa.array([None if rng.random() < 0.15 else [int(i), None if i % 5 == 0 else int(i + 1), int(i + 2)]
+                         for i in range(n)], pa.list_(pa.int32(), 3)),
+        "l_arr": pa.array([None if rng.random() < 0.1 else
+                           [None if rng.random() < 0.2 else [int(j), int(j) + 1] for j in range(int(rng.integers(0, 4)))]
+                           for _ in range(n)], pa.list_(pa.list_(pa.int16(), 2))),
+        "st_l": pa.array([{"v": None if i % 6 == 0 else list(range(i % 4)), "w": bool(i % 2)} for i in range(n)],
+                         pa.struct([("v", pa.list_(pa.int8())), ("w", pa.bool_())])),
+    }
+    return pa.table(cols)
+
+
+def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[bytes]) -> list[pa.Array]:
+    """Rebuild pyarrow arrays from pre-order (length, null_count) nodes and buffers (validity first)."""
+    ni, bi = [0], [0]
+
+    def take_buf():
+        b = buffers[bi[0]]
+        bi[0] += 1
+        return pa.py_buffer(b) if len(b) else None
+
+    def build(t: pa.DataType) -> pa.Array:
+        length, nulls = nodes[ni[0]]
+        ni[0] += 1
+        if pa.types.is_null(t):
+            return pa.nulls(length)
+        validity = take_buf()
+        if pa.types.is_struct(t):
+            kids = [build(t.field(i).type) for i in range(t.num_fields)]
+            return pa.StructArray.from_buffers(t, length, [validity], nulls, children=kids)
+        if pa.types.is_list(t) or pa.types.is_map(t):
+            offs = take_buf() or pa.py_buffer(b"\0\0\0\0")
+            if pa.types.is_map(t):
+                child = build(pa.struct([pa.field("key", t.key_type, nullable=False), pa.field("value", t.item_type)]))
+            else:
+                child = build(t.value_type)
+            return pa.Array.from_buffers(t, length, [validity, offs], nulls, children=[child])
+        if pa.types.is_fixed_size_list(t):
+            child = build(t.value_type)
+            return pa.Array.from_buffers(t, length, [validity], nulls, children=[child])
+        if pa.types.is_string(t) or pa.types.is_binary(t):
+            offs = take_buf() or pa.py_buffer(b"\0\0\0\0")
+            data = take_buf() or pa.py_buffer(b"")
+            return pa.Array.from_buffers(t, length, [validity, offs, data], nulls)
+        data = take_buf() or pa.py_buffer(b"")
+        return pa.Array.from_buffers(t, length, [validity, data], nulls)
+
+    out = [build(t) for t in types]
+    assert ni[0] == len(nodes) and bi[0] == len(buffers), "nodes / buffers not fully consumed"
+    return out
