@@ -22,7 +22,7 @@ enum b2a_enc_op {
 
 #define B2A_ENC_F_LAST_PAD 0x1u /* unused */
 
-#define B2A_ENC_STR_TILE 2048u /* rows per tile of the scan-based ops (256 threads x 8 rows) */
+#define B2A_ENC_STR_TILE 1024u /* rows per tile of the scan-based ops (256 threads x 4 rows) */
 
 /* writer device error codes (atomicMax), continuing the numbering of task.h */
 #define B2A_DEV_ENC_OFFSET_I32 16u /* "Arrow Appender: The maximum total string size for regular string buffers is ..." */

@@ -100,7 +100,7 @@ __device__ __forceinline__ uint64_t block_exclusive_scan(uint64_t v, uint64_t *t
 __device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i, uint4 &e, bool &valid) {
 	const uint64_t sr = map_row(t, i);
 	valid = src_valid(t, sr);
-	e = ld16(reinterpret_cast<const uint4 *>(t.src) + sr);
+	e = __ldg(reinterpret_cast<const uint4 *>(t.src) + sr); // L1-cached: a thread reads 4 adjacent entries
 	if (!valid) {
 		return 0;
 	}
@@ -410,6 +410,54 @@ __device__ __forceinline__ void enc_bool(const b2a_enc_task &t, uint8_t *__restr
 	}
 }
 
+// Writes the `len` bytes of one string to dst.  Inlined strings (len <= 12) come out of the string_t registers;
+// longer ones are fetched from the pointer as aligned 32-bit words (one load per word, funnel-shifted into place).
+// Every thread of a warp copies its own string, so a warp moves 32 strings per loop trip.
+__device__ __forceinline__ void put_string(uint8_t *dst, const uint4 &e, uint32_t len) {
+	if (len == 0) {
+		return;
+	}
+	if (len <= 12) {
+#pragma unroll
+		for (int w = 0; w < 3; w++) {
+			const uint32_t word = w == 0 ? e.y : (w == 1 ? e.z : e.w);
+#pragma unroll
+			for (int b = 0; b < 4; b++) {
+				if (static_cast<uint32_t>(4 * w + b) < len) {
+					dst[4 * w + b] = static_cast<uint8_t>(word >> (8 * b));
+				}
+			}
+		}
+		return;
+	}
+	const uintptr_t p = (static_cast<uintptr_t>(e.w) << 32) | e.z;
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(p & ~uintptr_t(3));
+	const uint32_t shift = (static_cast<uint32_t>(p) & 3u) * 8u;
+	const uint32_t total_words = (len + (shift >> 3) + 3u) >> 2; // aligned words that cover the string
+	uint32_t lo = __ldg(wp);
+	uint32_t widx = 1;
+	for (uint32_t k = 0; k < len; k += 4) {
+		uint32_t hi = 0;
+		if (widx < total_words) {
+			hi = __ldg(wp + widx);
+		}
+		widx++;
+		const uint32_t word = __funnelshift_r(lo, hi, shift);
+		const uint32_t nb = len - k;
+		dst[k] = static_cast<uint8_t>(word);
+		if (nb > 1) {
+			dst[k + 1] = static_cast<uint8_t>(word >> 8);
+		}
+		if (nb > 2) {
+			dst[k + 2] = static_cast<uint8_t>(word >> 16);
+		}
+		if (nb > 3) {
+			dst[k + 3] = static_cast<uint8_t>(word >> 24);
+		}
+		lo = hi;
+	}
+}
+
 // K12: string_t -> offsets (running sum of lengths, NULL rows repeat the previous offset) + character bytes
 // (ArrowVarcharData::AppendTemplated).  Tile = 1 024 rows, thread = 4 consecutive rows.  The tile's characters form
 // one contiguous window of the data buffer: they are assembled in shared memory (inlined strings from registers,
@@ -419,7 +467,6 @@ template <typename OFF>
 __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                            uint8_t *stage, uint32_t *err) {
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
-	const uint32_t lane = threadIdx.x & 31;
 	uint4 e[kRowsPerThread];
 	uint32_t len[kRowsPerThread];
 	uint64_t sum = 0;
@@ -467,38 +514,22 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 	uint8_t *gdst = stream + t.dst2 + tile_base; // window start in the stream
 	const uint32_t phase = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(gdst) & 15);
 	const bool staged = window + phase <= kStageBytes;
-	uint8_t *wdst = staged ? stage + phase : gdst; // where row bytes go: window-relative
-	uint64_t rel = rel0;
-	uint32_t long_mask[kRowsPerThread];
+	{
+		uint64_t rel = rel0;
+		if (staged) { // separate paths so that the stores compile to st.shared / st.global, not generic stores
+			uint8_t *wdst = stage + phase;
 #pragma unroll
-	for (int u = 0; u < kRowsPerThread; u++) {
-		if (len[u] > 0 && len[u] <= 12) { // inlined: bytes live in e[u].y/z/w
-			const uint32_t wds[3] = {e[u].y, e[u].z, e[u].w};
-			for (uint32_t b = 0; b < len[u]; b++) {
-				wdst[rel + b] = static_cast<uint8_t>(wds[b >> 2] >> (8 * (b & 3)));
+			for (int u = 0; u < kRowsPerThread; u++) {
+				put_string(wdst + rel, e[u], len[u]);
+				rel += len[u];
+			}
+		} else {
+#pragma unroll
+			for (int u = 0; u < kRowsPerThread; u++) {
+				put_string(gdst + rel, e[u], len[u]);
+				rel += len[u];
 			}
 		}
-		long_mask[u] = __ballot_sync(0xffffffffu, len[u] > 12);
-		rel += len[u];
-	}
-	// long strings: the whole warp copies one string at a time with coalesced byte loads
-	rel = rel0;
-#pragma unroll
-	for (int u = 0; u < kRowsPerThread; u++) {
-		uint32_t m = long_mask[u];
-		while (m) {
-			const int src_lane = __ffs(m) - 1;
-			m &= m - 1;
-			const uint32_t l = __shfl_sync(0xffffffffu, len[u], src_lane);
-			const uint32_t plo = __shfl_sync(0xffffffffu, e[u].z, src_lane);
-			const uint32_t phi = __shfl_sync(0xffffffffu, e[u].w, src_lane);
-			const uint64_t r = __shfl_sync(0xffffffffu, rel, src_lane);
-			const uint8_t *p = reinterpret_cast<const uint8_t *>((static_cast<uint64_t>(phi) << 32) | plo);
-			for (uint32_t b = lane; b < l; b += 32) {
-				wdst[r + b] = __ldg(p + b);
-			}
-		}
-		rel += len[u];
 	}
 	if (!staged) {
 		return;
@@ -575,7 +606,7 @@ __device__ __forceinline__ void enc_cp_async_wait_all() {
 static constexpr uint32_t kEncTaskVecs = sizeof(b2a_enc_task) / 16;
 static_assert(sizeof(b2a_enc_task) % 16 == 0, "b2a_enc_task is copied in 16-byte pieces");
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 4)
     b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
                       uint8_t *__restrict__ stream, uint32_t *err) {
 	__shared__ b2a_enc_task s_task[2];

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--row-group-size", type=int, default=122_880)
     ap.add_argument("--verify-batches", type=int, default=3)
+    ap.add_argument("--columns", default="", help="comma-separated subset (experiments)")
     args = ap.parse_args()
     import pyarrow as pa
     import pyarrow.ipc as ipc
@@ -45,7 +46,10 @@ def main():
     d_out = scan.decode()
     scan.finish()
     cols = []
+    want = set(args.columns.split(",")) if args.columns else None
     for f in reader.columns:
+        if want and f.name not in want:
+            continue
         parts = []
         for b in range(reader.num_batches):
             co = scan.column(b, f.index)
@@ -97,7 +101,7 @@ def main():
         if i >= args.verify_batches:
             break
         ok = ok and a.num_rows == b.num_rows and all(
-            a.column(c).to_pylist() == b.column(c).to_pylist() for c in range(a.num_columns))
+            a.column(n).to_pylist() == b.column(n).to_pylist() for n in b.schema.names)
     peak, kind = measured_peak()
     alg = w.algorithmic_bytes
     print(json.dumps({
