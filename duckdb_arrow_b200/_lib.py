@@ -79,6 +79,24 @@ class WriteOptions(C.Structure):
                 ("kv_values", C.POINTER(C.c_char_p))]
 
 
+class MultiFileOptions(C.Structure):
+    _fields_ = [("union_by_name", C.c_uint32), ("filename", C.c_uint32), ("hive_partitioning", C.c_uint32),
+                ("hive_types_autocast", C.c_uint32), ("filename_column", C.c_char_p)]
+
+
+class MfColumnInfo(C.Structure):
+    _fields_ = [("name", C.c_char * 128), ("type_name", C.c_char * 256), ("type_id", C.c_int32),
+                ("decimal_width", C.c_int32), ("decimal_scale", C.c_int32), ("kind", C.c_int32)]
+
+
+class MfMapInfo(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("local_flat", C.c_int32), ("from_type_id", C.c_int32), ("to_type_id", C.c_int32),
+                ("constant_is_null", C.c_int32), ("pad", C.c_int32), ("constant", C.c_char_p)]
+
+
+MF_MAP_LOCAL, MF_MAP_CAST, MF_MAP_NULL, MF_MAP_CONSTANT = 0, 1, 2, 3
+MF_COL_DATA, MF_COL_FILENAME, MF_COL_HIVE = 0, 1, 2
+
 CMP = {"=": 0, "==": 0, "!=": 1, "<>": 1, "<": 2, "<=": 3, ">": 4, ">=": 5}
 
 
@@ -121,6 +139,21 @@ def _load() -> C.CDLL:
         "b2a_scan_filter": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
+        "b2a_multifile_open": (i32, [P(C.c_char_p), u32, P(MultiFileOptions), P(vp)]),
+        "b2a_multifile_close": (None, [vp]),
+        "b2a_multifile_counts": (i32, [vp, P(u32), P(u32), P(u32)]),
+        "b2a_multifile_column": (i32, [vp, u32, P(MfColumnInfo)]),
+        "b2a_multifile_set_projection": (i32, [vp, P(C.c_char_p), u32]),
+        "b2a_multifile_projected": (i32, [vp, u32, P(u32)]),
+        "b2a_multifile_file": (i32, [vp, u32, P(C.c_char_p), P(vp)]),
+        "b2a_multifile_map": (i32, [vp, u32, u32, P(MfMapInfo)]),
+        "b2a_multifile_finalize_create": (i32, [vp, u32, vp, P(vp)]),
+        "b2a_multifile_finalize_destroy": (None, [vp]),
+        "b2a_multifile_finalize_sizes": (i32, [vp, P(u64), P(u64)]),
+        "b2a_multifile_finalize_run": (i32, [vp, vp, vp, u64, u64, vp]),
+        "b2a_multifile_finalize_finish": (i32, [vp, vp]),
+        "b2a_multifile_finalize_column": (i32, [vp, u64, u32, P(ColumnOut)]),
+        "b2a_multifile_finalize_gpu_launches": (u64, [vp]),
         "b2a_writer_create": (i32, [P(Vector), u32, u64, P(WriteOptions), i32, P(vp)]),
         "b2a_writer_destroy": (None, [vp]),
         "b2a_writer_measure": (i32, [vp, vp]),

@@ -40,9 +40,10 @@ class Field:
 class ArrowIPCReader:
     """Framing + slicing of one Arrow IPC stream / file (host only)."""
 
-    def __init__(self, handle, keepalive=None):
+    def __init__(self, handle, keepalive=None, owned=True):
         self._h = handle
         self._keep = keepalive
+        self._owned = owned  # False: the handle belongs to a b2a_multifile
         n_top, n_flat = C.c_uint32(), C.c_uint32()
         check(lib.b2a_reader_num_fields(self._h, C.byref(n_top), C.byref(n_flat)))
         self.n_flat = n_flat.value
@@ -84,7 +85,8 @@ class ArrowIPCReader:
 
     def close(self):
         if self._h:
-            lib.b2a_reader_close(self._h)
+            if self._owned:
+                lib.b2a_reader_close(self._h)
             self._h = None
 
     def __del__(self):
@@ -302,19 +304,22 @@ class ArrowScan:
         return co
 
 
-def read_arrow(path, columns: list[str] | None = None, device: int = 0, host_alias: bool = True) -> "DecodedScan":
-    """`FROM read_arrow('x.arrows')`: full scan of one file (or a list / glob of files) into DuckDB vectors.
-    Returns the decoded vectors on the host in canonical layout (see DecodedScan)."""
-    paths = path if isinstance(path, (list, tuple)) else (sorted(_glob.glob(path)) if any(c in path for c in "*?[") else [path])
-    if not paths:
-        raise B2AError(2, f'No files found that match the pattern "{path}"')
-    parts = []
-    for p in paths:
-        r = ArrowIPCReader.open_file(p)
-        if columns:
-            r.set_projection(columns)
-        parts.append(_scan_to_host(r, device, host_alias))
-    return parts[0] if len(parts) == 1 else parts
+def read_arrow(path, columns: list[str] | None = None, device: int = 0, host_alias: bool = True,
+               union_by_name: bool = False, filename=False, hive_partitioning: bool = False,
+               hive_types_autocast: bool = True):
+    """`FROM read_arrow('x.arrows')` / `read_arrow([...])` / `read_arrow('dir/*.arrow', union_by_name=true, ...)`.
+    One plain path without multi-file options -> DecodedScan (the decoded vectors on the host in canonical layout);
+    a list, a glob or any multi-file option -> MultiFileScan (src/file_scanner: global schema, per-file column mapping,
+    casts on the device, constant columns)."""
+    multi = (isinstance(path, (list, tuple)) or any(c in path for c in "*?[") or union_by_name or filename
+             or hive_partitioning)
+    if multi:
+        return MultiFileScan(path, columns=columns, device=device, union_by_name=union_by_name, filename=filename,
+                             hive_partitioning=hive_partitioning, hive_types_autocast=hive_types_autocast)
+    r = ArrowIPCReader.open_file(path)
+    if columns:
+        r.set_projection(columns)
+    return _scan_to_host(r, device, host_alias)
 
 
 def scan_arrow_ipc(buffers, columns: list[str] | None = None, device: int = 0, host_alias: bool = True) -> "DecodedScan":
@@ -426,6 +431,189 @@ class ColumnView:
         ptr = d[:, 8:16].copy().view(np.uint64).ravel().astype(np.int64)
         rel = ptr - np.int64(self.ds.ptr_origin + int(self.co.chars_off))
         return lens, d[:, 4:16], rel
+
+
+# ==================================================================================================== multi-file
+@dataclass
+class GlobalColumn:
+    index: int
+    name: str
+    type: str      # LogicalType::ToString() of the global column
+    type_id: str   # TYPE_NAMES entry
+    kind: int      # MF_COL_DATA | MF_COL_FILENAME | MF_COL_HIVE
+    decimal: tuple
+
+
+@dataclass
+class ConstantColumn:
+    """A constant vector of a multi-file scan: filename / hive partition value (text + global type), or NULL."""
+    rows: int
+    value: str | None
+    column: GlobalColumn
+
+
+class CastColumnView(ColumnView):
+    """A column that went through a multi-file cast: data (and VARCHAR heap) live in the file's FINAL arena, the
+    validity mask is the source vector's (scan arena)."""
+
+    def __init__(self, ds, co, field, batch, final: np.ndarray, final_origin: int):
+        super().__init__(ds, co, field, batch)
+        self.final, self.final_origin = final, final_origin
+
+    @property
+    def data(self) -> np.ndarray:
+        w = self.field.out_width
+        return self.final[self.co.data_off: self.co.data_off + self.rows * w].reshape(self.rows, w)
+
+    def string_parts(self):
+        d = self.data
+        lens = d[:, 0:4].copy().view(np.uint32).ravel()
+        ptr = d[:, 8:16].copy().view(np.uint64).ravel().astype(np.int64)
+        return lens, d[:, 4:16], ptr - np.int64(self.final_origin + int(self.co.chars_off))
+
+
+class MultiFileFile:
+    """One file of a multi-file scan, decoded (and cast) on the device and copied back to the host."""
+
+    def __init__(self, mfs: "MultiFileScan", index: int, path: str, reader: ArrowIPCReader):
+        self.mfs, self.index, self.path, self.reader = mfs, index, path, reader
+        self.ds = None
+        self._fin = None
+        self.final = None
+        self.gpu_launches = 0
+
+    def map(self, column: int) -> _lib.MfMapInfo:
+        mi = _lib.MfMapInfo()
+        check(lib.b2a_multifile_map(self.mfs._h, self.index, column, C.byref(mi)))
+        return mi
+
+    def scan(self, batch_lo: int = 0, batch_hi: int | None = None):
+        """upload -> decode -> casts -> download (device-resident layout copied back; string_t pointers are host
+        addresses of the file's stream image / of the cast heap)."""
+        import torch
+        mfs = self.mfs
+        image = self.reader.image()
+        scan = ArrowScan(self.reader, mfs.device, batch_lo, batch_hi)
+        scan.upload()
+        base = image.ctypes.data + scan.image_lo if image.size else 0
+        scan.decode(string_ptr_base=base)
+        fin = C.c_void_p()
+        check(lib.b2a_multifile_finalize_create(mfs._h, self.index, scan._h, C.byref(fin)))
+        self._fin = fin
+        fb, nc = C.c_uint64(), C.c_uint64()
+        check(lib.b2a_multifile_finalize_sizes(fin, C.byref(fb), C.byref(nc)))
+        self.n_casts = nc.value
+        h_final = torch.empty(max(fb.value, 1), dtype=torch.uint8, pin_memory=True)
+        if nc.value:
+            d_final = torch.empty(fb.value, dtype=torch.uint8, device=f"cuda:{mfs.device}")
+            check(lib.b2a_multifile_finalize_run(fin, C.c_void_p(scan.d_out.data_ptr()), C.c_void_p(d_final.data_ptr()),
+                                                 base, h_final.data_ptr(), scan._stream_ptr()))
+            check(lib.b2a_multifile_finalize_finish(fin, scan._stream_ptr()))
+            h_final.copy_(d_final)
+        scan.finish()
+        arena = scan.download()
+        self._h_final = h_final
+        self.final = h_final.numpy()
+        self.ds = DecodedScan(scan, arena, image, base - scan.image_lo if image.size else 0)
+        self.gpu_launches = scan.gpu_launches + int(lib.b2a_multifile_finalize_gpu_launches(fin))
+        return self
+
+    def close(self):
+        if self._fin:
+            lib.b2a_multifile_finalize_destroy(self._fin)
+            self._fin = None
+        if self.ds is not None:
+            self.ds.scan.close()
+
+    def column(self, batch: int, column: int):
+        """Vector of GLOBAL column `column` for record batch `batch` of this file: ColumnView (the file's own vector),
+        CastColumnView, or ConstantColumn."""
+        mi = self.map(column)
+        gc = self.mfs.all_columns[column]
+        if mi.kind in (_lib.MF_MAP_NULL, _lib.MF_MAP_CONSTANT):
+            rows = self.reader.batch_info(batch).rows
+            value = None if mi.constant_is_null else mi.constant.decode()
+            return ConstantColumn(int(rows), value, gc)
+        if mi.kind == _lib.MF_MAP_LOCAL:
+            return self.ds.column(batch, mi.local_flat)
+        co = _lib.ColumnOut()
+        check(lib.b2a_multifile_finalize_column(self._fin, batch, column, C.byref(co)))
+        src = self.reader.fields[mi.local_flat]
+        width = {"VARCHAR": 16, "DOUBLE": 8, "FLOAT": 4, "BIGINT": 8, "UBIGINT": 8, "INTEGER": 4, "UINTEGER": 4,
+                 "SMALLINT": 2, "USMALLINT": 2, "TINYINT": 1, "UTINYINT": 1, "TIMESTAMP": 8}[gc.type_id]
+        f = Field(src.index, gc.name, "", gc.type_id, "CAST", width, src.out_width, [], -1, True, 0, 0, 0, -1, "INVALID")
+        return CastColumnView(self.ds, co, f, batch, self.final, self._h_final.data_ptr())
+
+
+class MultiFileScan:
+    """read_arrow over several files (src/file_scanner + DuckDB's MultiFileReader in the reference)."""
+
+    def __init__(self, paths, columns=None, device: int = 0, union_by_name=False, filename=False,
+                 hive_partitioning=False, hive_types_autocast=True):
+        self.device = device
+        plist = list(paths) if isinstance(paths, (list, tuple)) else [paths]
+        arr = (C.c_char_p * len(plist))(*[p.encode() for p in plist])
+        opt = _lib.MultiFileOptions()
+        opt.union_by_name = int(bool(union_by_name))
+        opt.filename = int(bool(filename))
+        self._fn_col = filename.encode() if isinstance(filename, str) else None
+        opt.filename_column = self._fn_col
+        opt.hive_partitioning = int(bool(hive_partitioning))
+        opt.hive_types_autocast = int(bool(hive_types_autocast))
+        h = C.c_void_p()
+        check(lib.b2a_multifile_open(arr, len(plist), C.byref(opt), C.byref(h)))
+        self._h = h
+        if columns:
+            names = (C.c_char_p * len(columns))(*[n.encode() for n in columns])
+            check(lib.b2a_multifile_set_projection(self._h, names, len(columns)))
+        nf, nc, npj = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        check(lib.b2a_multifile_counts(self._h, C.byref(nf), C.byref(nc), C.byref(npj)))
+        self.all_columns = []
+        for i in range(nc.value):
+            ci = _lib.MfColumnInfo()
+            check(lib.b2a_multifile_column(self._h, i, C.byref(ci)))
+            self.all_columns.append(GlobalColumn(i, ci.name.decode(), ci.type_name.decode(), _lib.TYPE_NAMES[ci.type_id],
+                                                 ci.kind, (ci.decimal_width, ci.decimal_scale)))
+        self.columns = []
+        for i in range(npj.value):
+            c = C.c_uint32()
+            check(lib.b2a_multifile_projected(self._h, i, C.byref(c)))
+            self.columns.append(self.all_columns[c.value])
+        self.files = []
+        for i in range(nf.value):
+            path, rh = C.c_char_p(), C.c_void_p()
+            check(lib.b2a_multifile_file(self._h, i, C.byref(path), C.byref(rh)))
+            self.files.append(MultiFileFile(self, i, path.value.decode(), ArrowIPCReader(rh, owned=False)))
+
+    @property
+    def names(self):
+        return [c.name for c in self.columns]
+
+    @property
+    def types(self):
+        return [c.type for c in self.columns]
+
+    @property
+    def num_rows(self):
+        return sum(f.reader.num_rows for f in self.files)
+
+    def scan_all(self):
+        for f in self.files:
+            f.scan()
+        return self
+
+    def close(self):
+        for f in self.files:
+            f.close()
+        if getattr(self, "_h", None):
+            lib.b2a_multifile_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # ======================================================================================================== writer

@@ -17,11 +17,14 @@ SOURCES = [
     "ipc/ipc_writer.cpp",
     "scanner/scan_plan.cpp",
     "writer/write_plan.cpp",
+    "file_scanner/multi_file.cpp",
     "kernels/decode.cu",
     "kernels/filter.cu",
     "kernels/encode.cu",
+    "kernels/cast.cu",
     "capi.cu",
     "capi_writer.cu",
+    "capi_multifile.cu",
 ]
 
 NVCC_FLAGS = [

@@ -1,10 +1,8 @@
 // C ABI (include/b2arrow.h): exception firewall + device memory plumbing around the planner and kernels.
 // There is NO CPU fallback: every b2a_scan_* entry point that needs the device fails with B2A_ECUDA
 // when no CUDA device is usable.
-#include "b2arrow.h"
-#include "ipc/ipc_reader.hpp"
+#include "capi_internal.hpp"
 #include "kernels/decode.cuh"
-#include "scanner/scan_plan.hpp"
 
 #include <cuda_runtime.h>
 
@@ -15,30 +13,6 @@
 using namespace b2a;
 
 static thread_local std::string g_last_error;
-
-struct b2a_reader {
-	Reader reader;
-	std::vector<std::string> meta_keys, meta_vals;
-};
-
-struct b2a_scan {
-	b2a_reader *r = nullptr;
-	ScanPlan plan;
-	int device = 0;
-	int sm_count = 148;
-	b2a_task *d_tasks = nullptr;
-	uint32_t *d_tile_task = nullptr;
-	uint64_t *d_variadic = nullptr;
-	uint32_t *d_err = nullptr;
-	uint8_t *d_image_owned = nullptr;   // allocated by b2a_scan_upload
-	const uint8_t *d_image = nullptr;   // device address of image offset plan.image_lo
-	uint64_t launches = 0;
-	// filter support
-	uint64_t *d_chunk_col = nullptr;   // filter: per chunk, per predicate {data, validity}
-	uint64_t *d_chunk_col2 = nullptr;  // sum_product: per chunk {a, va, b, vb}
-	uint32_t *d_chunk_rows = nullptr;
-	std::vector<uint32_t> chunk_col_key, chunk_col2_key;
-};
 
 static int Fail(int code, const std::string &msg) {
 	g_last_error = msg;

@@ -292,7 +292,7 @@ static std::string Lower(const std::string &s) {
 }
 
 // QueryResult::DeduplicateColumns (duckdb/src/main/query_result.cpp:71-93)
-static void DeduplicateColumns(std::vector<std::string> &names) {
+void DeduplicateColumns(std::vector<std::string> &names) {
 	std::unordered_map<std::string, uint64_t> name_map;
 	for (auto &column_name : names) {
 		auto low = Lower(column_name);

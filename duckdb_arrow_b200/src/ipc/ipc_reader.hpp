@@ -38,6 +38,9 @@ struct DictionaryBatch {
 	RecordBatch data;
 };
 
+// QueryResult::DeduplicateColumns (duckdb/src/main/query_result.cpp:71-93)
+void DeduplicateColumns(std::vector<std::string> &names);
+
 class Reader {
 public:
 	Reader() {

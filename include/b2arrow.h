@@ -231,6 +231,82 @@ int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_
 /* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
 int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
 
+/* ---------------- src/file_scanner: multi-file read_arrow (lists, globs, union_by_name, filename, hive) ----------------
+ * Replaces what the reference gets from DuckDB's MultiFileReader framework through ArrowMultiFileInfo / ArrowFileScan
+ * (src/file_scanner/arrow_multi_file_info.cpp:57-72,103-121, src/file_scanner/arrow_file_scan.cpp:11-26,75-80):
+ *   bind     MultiFileReader::BindReader / BindUnionReader / BindOptions
+ *            (duckdb/src/common/multi_file/multi_file_reader.cpp:220-286,528-580,653-672)
+ *   mapping  MultiFileColumnMapper, by name (duckdb/src/common/multi_file/multi_file_column_mapper.cpp:134-192,494-585)
+ *   finalize MultiFileReader::FinalizeChunk (multi_file_reader.cpp:435-458): column reference | cast | constant
+ * Binding runs on the host; the cast expressions run on the device over whole decoded record batches
+ * (b2a_multifile_finalize_*); constants (filename, hive partition values, union_by_name NULL columns) stay constants,
+ * like DuckDB's CONSTANT_VECTORs. */
+typedef struct b2a_multifile_options {
+	uint32_t union_by_name;       /* read_arrow(..., union_by_name = true) */
+	uint32_t filename;            /* filename = true: adds the VARCHAR column `filename_column` */
+	uint32_t hive_partitioning;   /* hive_partitioning = true: key=value path components become columns */
+	uint32_t hive_types_autocast; /* default 1: partition values that all parse as BIGINT / DATE get that type */
+	const char *filename_column;  /* NULL: "filename" */
+} b2a_multifile_options;
+
+typedef enum b2a_mf_column_kind { B2A_MF_COL_DATA = 0, B2A_MF_COL_FILENAME = 1, B2A_MF_COL_HIVE = 2 } b2a_mf_column_kind;
+typedef enum b2a_mf_map_kind {
+	B2A_MF_MAP_LOCAL = 0,   /* the file's own vector (b2a_scan_column of local_flat) */
+	B2A_MF_MAP_CAST = 1,    /* the file's vector cast to the global type (b2a_multifile_finalize_column) */
+	B2A_MF_MAP_NULL = 2,    /* constant NULL (column missing from this file under union_by_name) */
+	B2A_MF_MAP_CONSTANT = 3 /* constant value given as text (filename / hive partition value) */
+} b2a_mf_map_kind;
+
+typedef struct b2a_mf_column_info {
+	char name[128];
+	char type_name[256];  /* LogicalType::ToString() of the global column type */
+	int32_t type_id;      /* b2a_type_id */
+	int32_t decimal_width;
+	int32_t decimal_scale;
+	int32_t kind;         /* b2a_mf_column_kind */
+} b2a_mf_column_info;
+
+typedef struct b2a_mf_map_info {
+	int32_t kind;         /* b2a_mf_map_kind */
+	int32_t local_flat;   /* flat field index inside the file (LOCAL / CAST), else -1 */
+	int32_t from_type_id; /* CAST: the file's column type */
+	int32_t to_type_id;   /* the global column type */
+	int32_t constant_is_null;
+	int32_t pad;
+	const char *constant; /* CONSTANT: text of the value (owned by the multi-file handle) */
+} b2a_mf_map_info;
+
+typedef struct b2a_multifile b2a_multifile;
+typedef struct b2a_mf_finalize b2a_mf_finalize;
+
+/* paths: file names and/or glob patterns (expanded in sorted order, like FileSystem::Glob) */
+int b2a_multifile_open(const char *const *paths, uint32_t n_paths, const b2a_multifile_options *opt,
+                       b2a_multifile **out);
+void b2a_multifile_close(b2a_multifile *m);
+int b2a_multifile_counts(b2a_multifile *m, uint32_t *n_files, uint32_t *n_columns, uint32_t *n_projected);
+int b2a_multifile_column(b2a_multifile *m, uint32_t column, b2a_mf_column_info *out);
+/* projection pushdown over GLOBAL column names; each file's reader is narrowed to the local columns it must deliver */
+int b2a_multifile_set_projection(b2a_multifile *m, const char *const *names, uint32_t n);
+int b2a_multifile_projected(b2a_multifile *m, uint32_t i, uint32_t *column);
+/* the reader of file `file` is owned by the multi-file handle: scan it with b2a_scan_create, do not close it */
+int b2a_multifile_file(b2a_multifile *m, uint32_t file, const char **path, b2a_reader **reader);
+int b2a_multifile_map(b2a_multifile *m, uint32_t file, uint32_t column, b2a_mf_map_info *out);
+/* the cast expressions of file `file` over a decoded scan of its reader */
+int b2a_multifile_finalize_create(b2a_multifile *m, uint32_t file, b2a_scan *scan, b2a_mf_finalize **out);
+void b2a_multifile_finalize_destroy(b2a_mf_finalize *fin);
+int b2a_multifile_finalize_sizes(b2a_mf_finalize *fin, uint64_t *final_bytes, uint64_t *n_casts);
+/* d_out: the decoded arena of the scan; d_final: device arena of final_bytes (256-byte aligned) for the cast results.
+ * src_string_ptr_base: the string_ptr_base the scan was decoded with (0 = device image addresses);
+ * dst_string_ptr_base: address final-arena offset 0 maps to for the consumer of VARCHAR results (0 = d_final). */
+int b2a_multifile_finalize_run(b2a_mf_finalize *fin, const void *d_out, void *d_final, uint64_t src_string_ptr_base,
+                               uint64_t dst_string_ptr_base, void *cuda_stream);
+/* waits for the stream and maps the device error word to ConversionException / NotImplementedException */
+int b2a_multifile_finalize_finish(b2a_mf_finalize *fin, void *cuda_stream);
+/* location of a CAST column of one batch: data_off / chars_off are offsets into the FINAL arena, validity_off and
+ * stats_off into the SCAN arena (the mask is shared with the source vector) */
+int b2a_multifile_finalize_column(b2a_mf_finalize *fin, uint64_t batch, uint32_t column, b2a_column_out *out);
+uint64_t b2a_multifile_finalize_gpu_launches(b2a_mf_finalize *fin);
+
 /* ---------------- src/writer + kernels: DuckDB vectors -> Arrow IPC stream ----------------
  * Replaces ColumnDataCollectionSerializer::Serialize (src/writer/column_data_collection_serializer.cpp:80-120),
  * ArrowAppender (duckdb/src/common/arrow/arrow_appender.cpp:37-131 + appender/<type>_data.hpp), the nanoarrow

@@ -1,0 +1,305 @@
+"""Multi-file read_arrow (src/file_scanner): binding on the host (CPU tests) and the scanned rows on the GPU, pinned
+to the expectations of the reference's test/sql/multifile_reading.test (files under tests/golden/data/multifile are
+the reference's own fixtures)."""
+import math
+import os
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from logical import column_to_py
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "data")
+MF = os.path.join(GOLDEN, "multifile")
+
+PA_TYPE = {"VARCHAR": pa.string(), "DOUBLE": pa.float64(), "FLOAT": pa.float32(), "BIGINT": pa.int64(),
+           "INTEGER": pa.int32(), "SMALLINT": pa.int16(), "TINYINT": pa.int8(), "UBIGINT": pa.uint64(),
+           "UINTEGER": pa.uint32(), "USMALLINT": pa.uint16(), "UTINYINT": pa.uint8(), "TIMESTAMP": pa.int64(),
+           "DATE": pa.int32()}
+
+
+def rows_of(mfs):
+    """materialise the scan as Python tuples, file by file, batch by batch (the reference's output order for one
+    thread)"""
+    out = []
+    for f in mfs.files:
+        f.scan()
+        for b in range(f.reader.num_batches):
+            cols = []
+            for gc in mfs.columns:
+                v = f.column(b, gc.index)
+                if hasattr(v, "value"):  # ConstantColumn
+                    val = v.value
+                    if val is not None and gc.type_id == "BIGINT":
+                        val = int(val)
+                    cols.append([val] * v.rows)
+                else:
+                    vals = column_to_py(v, PA_TYPE[gc.type_id])
+                    cols.append([x.decode() if isinstance(x, bytes) else x for x in vals])
+            out += list(zip(*cols))
+    return out
+
+
+def mf(*names):
+    return [os.path.join(MF, n) for n in names]
+
+
+# ----------------------------------------------------------------------------------------------- host binding (CPU)
+def test_bind_first_file_schema(b2a):
+    s = b2a.read_arrow(mf("glob/f1.arrow", "different_order.arrows"))
+    assert s.names == ["fruit", "variety", "weight"]
+    assert s.types == ["VARCHAR", "VARCHAR", "DOUBLE"]
+    m = [s.files[1].map(i) for i in range(3)]
+    assert [x.kind for x in m] == [0, 0, 0]  # all LOCAL, matched by name
+    # different_order.arrows is (fruit, weight, variety)
+    assert [x.local_flat for x in m] == [0, 2, 1]
+
+
+def test_bind_glob_sorted_and_counts(b2a):
+    s = b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"))
+    assert [os.path.basename(f.path) for f in s.files] == ["f1.arrow", "f2.arrow", "f3.arrow"]
+    assert s.num_rows == 6
+    s2 = b2a.read_arrow([os.path.join(GOLDEN, "test.arrows")] * 2)
+    assert s2.num_rows == 30974  # multifile_reading.test:11-14
+
+
+def test_bind_schema_mismatch_errors(b2a):
+    # multifile_reading.test:49-57
+    for files in ([os.path.join(GOLDEN, "test.arrows"), mf("glob/f1.arrow")[0]],
+                  mf("fruit_extra.arrows", "glob/f1.arrow")):
+        with pytest.raises(b2a.B2AError, match="If you are trying to read files with different schemas, try setting "
+                                               "union_by_name=True"):
+            b2a.read_arrow(files)
+
+
+def test_bind_union_by_name(b2a):
+    s = b2a.read_arrow(mf("fruit_extra.arrows", "glob/f1.arrow"), union_by_name=True)
+    assert s.names == ["fruit", "variety", "weight", "tasteness"]
+    assert s.files[1].map(3).kind == 2  # constant NULL
+    # multifile_reading.test:104-112: typeof(weight)
+    three = mf("different_type_int.arrows", "glob/f1.arrow", "different_type.arrows")
+    assert b2a.read_arrow(three, union_by_name=True).types[0] == "VARCHAR"
+    assert b2a.read_arrow(three).types[0] == "BIGINT"
+    assert b2a.read_arrow(mf("different_type.arrows", "glob/f1.arrow")).types[2] == "VARCHAR"
+    assert b2a.read_arrow(mf("glob/f1.arrow", "different_type.arrows")).types[2] == "DOUBLE"
+
+
+def test_bind_filename_and_hive(b2a):
+    s = b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), filename=True)
+    assert s.names[-1] == "filename" and s.types[-1] == "VARCHAR"
+    assert s.files[2].map(3).constant.decode().endswith("glob/f3.arrow")
+    h = b2a.read_arrow(os.path.join(MF, "hive", "*", "*.arrow"), hive_partitioning=True)
+    assert h.names == ["fruit", "variety", "weight", "part"] and h.types[-1] == "VARCHAR"
+    assert [f.map(3).constant.decode() for f in h.files] == ["a", "a", "b", "b"]
+    with pytest.raises(b2a.B2AError, match="Option filename adds column"):
+        b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), filename="fruit")
+    with pytest.raises(b2a.B2AError, match="No files found that match the pattern"):
+        b2a.read_arrow(os.path.join(MF, "glob", "*.nothing"))
+
+
+def test_bind_projection_narrows_readers(b2a):
+    s = b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), columns=["weight", "variety"])
+    assert s.names == ["weight", "variety"]
+    assert s.files[0].reader.projection is None  # python mirror untouched; the C++ reader holds the projection
+    with pytest.raises(b2a.B2AError, match="not found in FROM clause"):
+        b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), columns=["nope"])
+
+
+def test_hive_type_autodetect(b2a, tmp_path):
+    import pyarrow.ipc as ipc
+    t = pa.table({"x": pa.array([1, 2], pa.int32())})
+    for year in (2023, 2024):
+        d = tmp_path / f"year={year}" / "day=2024-01-02"
+        d.mkdir(parents=True)
+        with ipc.new_stream(str(d / "p.arrows"), t.schema) as w:
+            w.write_table(t)
+    s = b2a.read_arrow(str(tmp_path / "*" / "*" / "*.arrows"), hive_partitioning=True)
+    assert dict(zip(s.names, s.types)) == {"x": "INTEGER", "day": "DATE", "year": "BIGINT"}
+    s = b2a.read_arrow(str(tmp_path / "*" / "*" / "*.arrows"), hive_partitioning=True, hive_types_autocast=False)
+    assert dict(zip(s.names, s.types)) == {"x": "INTEGER", "day": "VARCHAR", "year": "VARCHAR"}
+
+
+# ----------------------------------------------------------------------------------------------- scanned rows (GPU)
+F1 = [("apple", "gala", 134.2), ("orange", "navel", 142.1)]
+F2 = [("apple", "honeycrisp", 158.6), ("orange", "valencia", 96.7)]
+F3 = [("apple", "fuji", None), ("orange", "cara cara", None)]
+
+
+@pytest.mark.gpu
+def test_glob_rows(b2a, cuda_device):
+    # multifile_reading.test:17-25
+    assert rows_of(b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"))) == F1 + F2 + F3
+    # :28-36 projection
+    got = rows_of(b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), columns=["weight", "variety"]))
+    assert got == [(w, v) for _, v, w in F1 + F2 + F3]
+
+
+@pytest.mark.gpu
+def test_file_list_count(b2a, cuda_device):
+    s = b2a.read_arrow([os.path.join(GOLDEN, "test.arrows")] * 2, columns=["message"])
+    assert len(rows_of(s)) == 30974
+    assert sum(f.column(b, s.columns[0].index).rows for f in s.files for b in range(f.reader.num_batches)) == 30974
+
+
+@pytest.mark.gpu
+def test_union_by_name_rows(b2a, cuda_device):
+    # multifile_reading.test:60-67
+    got = rows_of(b2a.read_arrow(mf("fruit_extra.arrows", "glob/f1.arrow"), union_by_name=True))
+    assert got == [("apple", "pink lady", 2.2, 10.0), ("orange", "jiha", None, None),
+                   ("apple", "gala", 134.2, None), ("orange", "navel", 142.1, None)]
+
+
+@pytest.mark.gpu
+def test_different_column_order_rows(b2a, cuda_device):
+    # multifile_reading.test:70-77 (ORDER BY ALL)
+    got = rows_of(b2a.read_arrow(mf("different_order.arrows", "glob/f1.arrow")))
+    assert got == [("apple", 2.2, "pink lady"), ("orange", None, "jiha"), ("apple", 134.2, "gala"),
+                   ("orange", 142.1, "navel")]
+
+
+@pytest.mark.gpu
+def test_different_types_rows(b2a, cuda_device):
+    # multifile_reading.test:80-96: VARCHAR global <- DOUBLE file, and DOUBLE global <- VARCHAR file
+    got = rows_of(b2a.read_arrow(mf("different_type.arrows", "glob/f1.arrow")))
+    assert got == [("apple", "pink lady", "2.2"), ("orange", "jiha", None), ("apple", "gala", "134.2"),
+                   ("orange", "navel", "142.1")]
+    got = rows_of(b2a.read_arrow(mf("glob/f1.arrow", "different_type.arrows")))
+    assert got == F1 + [("apple", "pink lady", 2.2), ("orange", "jiha", None)]
+    # :114-120 different type AND order
+    got = rows_of(b2a.read_arrow(mf("glob/f1.arrow", "different_type_order.arrows")))
+    assert got == F1 + [("apple", "pink lady", 2.2), ("orange", "jiha", None)]
+    # :104-112: three files, BIGINT global from the first file: DOUBLE -> BIGINT rounds, VARCHAR -> BIGINT rounds
+    three = mf("different_type_int.arrows", "glob/f1.arrow", "different_type.arrows")
+    got = rows_of(b2a.read_arrow(three))
+    assert got == [(2, "apple", "pink lady"), (8, "orange", "jiha"), (134, "apple", "gala"), (142, "orange", "navel"),
+                   (2, "apple", "pink lady"), (None, "orange", "jiha")]
+    got = rows_of(b2a.read_arrow(three, union_by_name=True))
+    assert [r[0] for r in got] == ["2", "8", "134.2", "142.1", "2.2", None]
+
+
+@pytest.mark.gpu
+def test_filename_and_hive_rows(b2a, cuda_device):
+    # multifile_reading.test:123-143
+    got = rows_of(b2a.read_arrow(os.path.join(MF, "glob", "*.arrow"), filename=True))
+    assert [(r[0], r[1], r[2], os.path.relpath(r[3], GOLDEN)) for r in got] == \
+        [r + (f"multifile/glob/f{i}.arrow",) for i, fr in ((1, F1), (2, F2), (3, F3)) for r in fr]
+    got = rows_of(b2a.read_arrow(os.path.join(MF, "hive", "*", "*.arrow"), hive_partitioning=True))
+    assert got == [r + ("a",) for r in F1 + F2] + [r + ("b",) for r in F1 + F3]
+
+
+def _write(path, table, batch=None):
+    import pyarrow.ipc as ipc
+    with ipc.new_stream(path, table.schema) as w:
+        w.write_table(table, max_chunksize=batch)
+
+
+@pytest.mark.gpu
+def test_numeric_casts_against_numpy(b2a, cuda_device, tmp_path):
+    """every numeric widening / float->int / int->varchar cast of the device kernel vs numpy / Python (DuckDB semantics
+    restated: static_cast for widening, nearbyint for FLOAT/DOUBLE -> integer, decimal text for integer -> VARCHAR)"""
+    rng = np.random.default_rng(5)
+    n = 5000
+    i8 = rng.integers(-128, 128, n, dtype=np.int8)
+    u16 = rng.integers(0, 65536, n, dtype=np.uint16)
+    i32 = rng.integers(-2**31, 2**31, n, dtype=np.int32)
+    i64 = rng.integers(-2**62, 2**62, n, dtype=np.int64)
+    f32 = rng.standard_normal(n).astype(np.float32) * 1000
+    f64 = np.concatenate([rng.standard_normal(n - 6) * 1e6, [0.5, 1.5, 2.5, -0.5, -1.5, 1e15 + 0.5]])
+    mask = rng.random(n) < 0.1
+    first = pa.table({"a": pa.array(np.zeros(1, np.int64)), "b": pa.array(np.zeros(1, np.float64)),
+                      "c": pa.array(np.zeros(1, np.int64)), "d": pa.array(["x"]), "e": pa.array(np.zeros(1, np.float64)),
+                      "f": pa.array(np.zeros(1, np.int32)), "g": pa.array(np.zeros(1, np.float64)),
+                      "h": pa.array(["x"])})
+    second = pa.table({"a": pa.array(i8, mask=mask), "b": pa.array(i32, mask=mask), "c": pa.array(f64, mask=mask),
+                       "d": pa.array(i64, mask=mask), "e": pa.array(f32, mask=mask), "f": pa.array(u16, mask=mask),
+                       "g": pa.array(i64, mask=mask), "h": pa.array(u16, mask=mask)})
+    _write(str(tmp_path / "a.arrows"), first)
+    _write(str(tmp_path / "b.arrows"), second, batch=2100)
+    s = b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "b.arrows")])
+    assert s.types == ["BIGINT", "DOUBLE", "BIGINT", "VARCHAR", "DOUBLE", "INTEGER", "DOUBLE", "VARCHAR"]
+    got = rows_of(s)[1:]
+    exp = {"a": i8.astype(np.int64), "b": i32.astype(np.float64), "c": np.rint(f64).astype(np.int64),
+           "d": [str(int(x)) for x in i64], "e": f32.astype(np.float64), "f": u16.astype(np.int32),
+           "g": i64.astype(np.float64), "h": [str(int(x)) for x in u16]}
+    for ci, name in enumerate("abcdefgh"):
+        for r in range(n):
+            want = None if mask[r] else exp[name][r]
+            have = got[r][ci]
+            if want is None:
+                assert have is None
+            elif isinstance(want, str):
+                assert have == want, (name, r)
+            else:
+                assert have == want, (name, r, have, want)
+
+
+@pytest.mark.gpu
+def test_double_to_varchar_shortest_roundtrip(b2a, cuda_device, tmp_path):
+    """DOUBLE / FLOAT -> VARCHAR is fmt's "{}" (shortest digits that round-trip; fixed notation for 1e-4 <= |v| < 1e16,
+    else exponent form with a sign and >= 2 digits) — the same digits and layout as Python's repr(float); the
+    reference pins '134.2' / '142.1' / '2.2' (multifile_reading.test:80-96)."""
+    rng = np.random.default_rng(11)
+    special = [0.0, -0.0, 1.0, -1.0, 0.1, 0.2, 0.3, 1e15, 1e16, 123456789012345680.0, 1e-4, 1e-5, 1.5e-5, 5e-324,
+               2.2250738585072014e-308, 1.7976931348623157e308, 9007199254740993.0, 1e22, 1e23, 0.30000000000000004,
+               float("inf"), float("-inf"), float("nan"), 134.2, 142.1, 2.2, 100.0, 1e100, 4.35, 0.000123456]
+    bits = rng.integers(0, 2**63, 4000, dtype=np.uint64)
+    rand = bits.view(np.float64)
+    rand = rand[np.isfinite(rand)]
+    vals = np.concatenate([np.array(special), rand, rng.standard_normal(2000), rng.integers(-10**6, 10**6, 1000) / 100.0])
+    f32 = np.concatenate([rng.standard_normal(1000).astype(np.float32), np.array([0.1, 3.4028235e38, 1e-45, 16777216.0],
+                                                                                  np.float32)])
+    f32 = np.resize(f32, vals.size)
+    _write(str(tmp_path / "a.arrows"), pa.table({"v": pa.array(["seed"]), "w": pa.array(["seed"])}))
+    _write(str(tmp_path / "b.arrows"), pa.table({"v": pa.array(vals), "w": pa.array(f32)}), batch=3000)
+    got = rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "b.arrows")]))[1:]
+
+    def fmt(x):
+        if math.isnan(x):
+            return "nan"
+        return repr(float(x))
+
+    def fmt32(x):
+        if math.isnan(x):
+            return "nan"
+        # shortest digits that round-trip as FLOAT, laid out like repr
+        s = np.format_float_scientific(np.float32(x), unique=True, trim="-")
+        mant, e = s.split("e")
+        digits = mant.replace("-", "").replace(".", "")
+        e = int(e)
+        sign = "-" if mant.startswith("-") else ""
+        if -4 <= e < 16:
+            if e < 0:
+                return sign + "0." + "0" * (-e - 1) + digits
+            ip = digits[: e + 1].ljust(e + 1, "0")
+            fp = digits[e + 1:] or "0"
+            return sign + ip + "." + fp
+        return sign + digits[0] + ("." + digits[1:] if len(digits) > 1 else "") + "e" + ("-" if e < 0 else "+") + f"{abs(e):02d}"
+
+    for r, (v, w) in enumerate(zip(vals, f32)):
+        assert got[r][0] == fmt(v), (r, v, got[r][0], fmt(v))
+        assert got[r][1] == fmt32(w), (r, w, got[r][1], fmt32(w))
+
+
+@pytest.mark.gpu
+def test_varchar_to_double_exact_or_loud(b2a, cuda_device, tmp_path):
+    texts = ["2.2", "134.2", "-0.5", "1e3", "  7.25 ", "+3", "1234567890123456", "1E-5", "nan", "inf", "-Infinity", "0",
+             "-0.0", ".5", "5."]
+    _write(str(tmp_path / "a.arrows"), pa.table({"v": pa.array([1.0])}))
+    _write(str(tmp_path / "b.arrows"), pa.table({"v": pa.array(texts + [None])}))
+    got = [r[0] for r in rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "b.arrows")]))[1:]]
+    for t, g in zip(texts, got):
+        want = float(t)
+        assert (math.isnan(g) and math.isnan(want)) or (g == want and math.copysign(1, g) == math.copysign(1, want)), t
+    assert got[-1] is None
+    # needs more than the exact fast path: refuse loudly instead of approximating
+    _write(str(tmp_path / "c.arrows"), pa.table({"v": pa.array(["0.1234567890123456789012"])}))
+    with pytest.raises(b2a.B2AError, match="extended precision"):
+        rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "c.arrows")]))
+    _write(str(tmp_path / "d.arrows"), pa.table({"v": pa.array(["abc"])}))
+    with pytest.raises(b2a.B2AError, match="could not convert a string"):
+        rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "d.arrows")]))
+    _write(str(tmp_path / "e.arrows"), pa.table({"v": pa.array([1e300])}))
+    _write(str(tmp_path / "i.arrows"), pa.table({"v": pa.array([1], pa.int32())}))
+    with pytest.raises(b2a.B2AError, match="out of range"):
+        rows_of(b2a.read_arrow([str(tmp_path / "i.arrows"), str(tmp_path / "e.arrows")]))
