@@ -303,3 +303,44 @@ def test_varchar_to_double_exact_or_loud(b2a, cuda_device, tmp_path):
     _write(str(tmp_path / "i.arrows"), pa.table({"v": pa.array([1], pa.int32())}))
     with pytest.raises(b2a.B2AError, match="out of range"):
         rows_of(b2a.read_arrow([str(tmp_path / "i.arrows"), str(tmp_path / "e.arrows")]))
+
+
+@pytest.mark.gpu
+def test_lineitem_glob_dictionary_union_by_name(b2a, cuda_device, tmp_path):
+    """BASELINE config 4 in small: glob of lineitem files, dictionary-encoded strings, two schema variants under
+    union_by_name (column order + INTEGER l_linenumber cast to BIGINT on the device); rows equal pyarrow's reading."""
+    import pyarrow.ipc as ipc
+    from tools.bench_multifile import write_files
+    pattern = write_files(str(tmp_path), 30_000, 3, seed=9)
+    s = b2a.read_arrow(pattern, union_by_name=True)
+    assert s.types[3] == "BIGINT" and s.types[8] == "VARCHAR" and s.types[4] == "DECIMAL(15,2)"
+    pa_t = dict(PA_TYPE)
+    pa_t["DECIMAL"] = pa.decimal64(15, 2)
+    got = []
+    for f in s.files:
+        f.scan()
+        assert f.n_casts == (f.reader.num_batches if f.index % 2 else 0)
+        for b in range(f.reader.num_batches):
+            cols = []
+            for gc in s.columns:
+                v = f.column(b, gc.index)
+                vals = column_to_py(v, pa.dictionary(pa.int32(), pa.string()) if v.is_dictionary else pa_t[gc.type_id])
+                cols.append([x.decode() if isinstance(x, bytes) else x for x in vals])
+            got += list(zip(*cols))
+    exp = []
+    for f in s.files:
+        t = ipc.open_stream(f.path).read_all()
+        cols = []
+        for gc in s.columns:
+            c = t.column(gc.name)
+            if pa.types.is_dictionary(c.type):
+                c = c.cast(pa.string())
+            if pa.types.is_decimal(c.type):
+                cols.append([int(x.scaleb(2)) for x in c.to_pylist()])
+            elif pa.types.is_date(c.type):
+                cols.append(c.cast(pa.int32()).to_pylist())
+            else:
+                cols.append(c.to_pylist())
+        exp += list(zip(*cols))
+    assert len(got) == len(exp) == 90_000
+    assert got == exp
