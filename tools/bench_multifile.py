@@ -52,6 +52,7 @@ def main():
     ap.add_argument("--rows-per-file", type=int, default=600_037_902 // 64)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--streams", type=int, default=4)
     args = ap.parse_args()
     import torch
     import duckdb_arrow_b200 as b2a
@@ -91,12 +92,23 @@ def main():
             d_final = torch.empty(max(fb.value, 256), dtype=torch.uint8, device=dev)
             files.append((f, scan, d_out, fin, d_final, nc.value, fb.value))
 
+        # files are independent: their decode (+cast) launches go round-robin over a few streams so that the tail of one
+        # file's persistent grid overlaps the ramp-up of the next
+        side = [torch.cuda.Stream(device=dev) for _ in range(args.streams)]
+
         def step():
-            for f, scan, d_out, fin, d_final, n_casts, _ in files:
-                scan.decode(d_out)
-                if n_casts:
-                    check(lib.b2a_multifile_finalize_run(fin, C.c_void_p(d_out.data_ptr()),
-                                                         C.c_void_p(d_final.data_ptr()), 0, 0, sp))
+            for st in side:
+                st.wait_stream(stream)
+            for i, (f, scan, d_out, fin, d_final, n_casts, _) in enumerate(files):
+                st = side[i % len(side)]
+                with torch.cuda.stream(st):
+                    scan.decode(d_out)
+                    if n_casts:
+                        check(lib.b2a_multifile_finalize_run(fin, C.c_void_p(d_out.data_ptr()),
+                                                             C.c_void_p(d_final.data_ptr()), 0, 0,
+                                                             C.c_void_p(st.cuda_stream)))
+            for st in side:
+                stream.wait_stream(st)
 
         def finish():
             for f, scan, d_out, fin, d_final, n_casts, _ in files:
