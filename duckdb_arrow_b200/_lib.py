@@ -135,6 +135,8 @@ def _load() -> C.CDLL:
         "b2a_scan_column": (i32, [vp, u64, u32, P(ColumnOut)]),
         "b2a_scan_dictionary": (i32, [vp, u32, P(ColumnOut), P(u32)]),
         "b2a_scan_gpu_launches": (u64, [vp]),
+        "b2a_scan_scratch": (i32, [vp, P(u64), P(u64), P(u64)]),
+        "b2a_scan_download_scratch": (i32, [vp, vp, vp]),
         "b2a_scan_num_chunks": (i32, [vp, P(u64)]),
         "b2a_scan_filter": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),

@@ -184,6 +184,10 @@ class ArrowScan:
         nc = C.c_uint64()
         check(lib.b2a_scan_num_chunks(self._h, C.byref(nc)))
         self.n_chunks = nc.value
+        so, sb, nj = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(lib.b2a_scan_scratch(self._h, C.byref(so), C.byref(sb), C.byref(nj)))
+        # compressed bodies: scratch region behind the image slice that receives the decompressed buffers
+        self.scratch_offset, self.scratch_bytes, self.n_decompress_jobs = so.value, sb.value, nj.value
         self.d_out = None
         self.d_image = None
 
@@ -215,8 +219,25 @@ class ArrowScan:
 
     def set_device_image(self, d_image):
         """d_image: torch uint8 CUDA tensor holding image[image_lo : image_lo+image_bytes] (256-byte aligned)."""
+        need = self.scratch_offset + self.scratch_bytes + 64 if self.scratch_bytes else self.image_bytes
+        if d_image.numel() < need:
+            raise B2AError(1, f"device image too small: {d_image.numel()} bytes, the scan needs {need} "
+                              "(stream slice + decompression scratch)")
         self.d_image = d_image
         check(lib.b2a_scan_set_device_image(self._h, C.c_void_p(d_image.data_ptr())))
+
+    @property
+    def device_image_bytes(self) -> int:
+        """bytes a caller-provided device image must have (stream slice, + scratch of compressed scans)"""
+        return self.scratch_offset + self.scratch_bytes + 64 if self.scratch_bytes else self.image_bytes + 64
+
+    def download_scratch(self):
+        """host copy (pinned) of the decompressed buffers: what string_t pointers of a compressed scan refer to"""
+        torch = self._torch()
+        h = torch.empty(max(1, self.scratch_bytes), dtype=torch.uint8, pin_memory=True)
+        check(lib.b2a_scan_download_scratch(self._h, C.c_void_p(h.data_ptr()), self._stream_ptr()))
+        torch.cuda.current_stream(self.device).synchronize()
+        return h
 
     def alloc_out(self):
         torch = self._torch()
@@ -334,12 +355,26 @@ def _scan_to_host(reader: ArrowIPCReader, device: int, host_alias: bool = True) 
     columns alias the host image exactly like the reference's DirectConversion; without it every column goes through
     upload -> decode -> download (the device-resident layout, copied back whole)."""
     image = reader.image()
-    if host_alias:
+    compressed = any(reader.batch_info(b).compressed for b in range(reader.num_batches))
+    if host_alias and not compressed:
         scan = ArrowScan(reader, device, host_alias=True)
         arena = scan.read_host()
         return DecodedScan(scan, arena, image, image.ctypes.data if image.size else 0)
     scan = ArrowScan(reader, device)
     scan.upload()
+    if scan.scratch_bytes:
+        # compressed bodies: the Arrow buffers the string_t pointers refer to exist only after decompression; the host
+        # consumer gets a copy of the scratch region and pointers into it
+        import torch
+        h_scratch = torch.empty(scan.scratch_bytes, dtype=torch.uint8, pin_memory=True)
+        base = h_scratch.data_ptr() - scan.scratch_offset
+        scan.decode(string_ptr_base=base)
+        scan.finish()
+        check(lib.b2a_scan_download_scratch(scan._h, C.c_void_p(h_scratch.data_ptr()), scan._stream_ptr()))
+        arena = scan.download()
+        ds = DecodedScan(scan, arena, image, base - scan.image_lo)
+        ds._h_scratch = h_scratch
+        return ds
     # string_t pointers refer to the HOST copy of the stream, exactly where the reference's pointers point
     base = image.ctypes.data + scan.image_lo if image.size else 0
     scan.decode(string_ptr_base=base)
@@ -496,6 +531,9 @@ class MultiFileFile:
         scan = ArrowScan(self.reader, mfs.device, batch_lo, batch_hi)
         scan.upload()
         base = image.ctypes.data + scan.image_lo if image.size else 0
+        if scan.scratch_bytes:  # compressed bodies: string_t pointers refer to the host copy of the scratch region
+            self._h_scratch = torch.empty(scan.scratch_bytes, dtype=torch.uint8, pin_memory=True)
+            base = self._h_scratch.data_ptr() - scan.scratch_offset
         scan.decode(string_ptr_base=base)
         fin = C.c_void_p()
         check(lib.b2a_multifile_finalize_create(mfs._h, self.index, scan._h, C.byref(fin)))
@@ -511,6 +549,8 @@ class MultiFileFile:
             check(lib.b2a_multifile_finalize_finish(fin, scan._stream_ptr()))
             h_final.copy_(d_final)
         scan.finish()
+        if scan.scratch_bytes:
+            check(lib.b2a_scan_download_scratch(scan._h, C.c_void_p(self._h_scratch.data_ptr()), scan._stream_ptr()))
         arena = scan.download()
         self._h_final = h_final
         self.final = h_final.numpy()

@@ -22,6 +22,7 @@ SOURCES = [
     "kernels/filter.cu",
     "kernels/encode.cu",
     "kernels/cast.cu",
+    "kernels/decomp.cu",
     "capi.cu",
     "capi_writer.cu",
     "capi_multifile.cu",

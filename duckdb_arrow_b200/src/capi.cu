@@ -3,6 +3,7 @@
 // when no CUDA device is usable.
 #include "capi_internal.hpp"
 #include "kernels/decode.cuh"
+#include "kernels/decomp.cuh"
 
 #include <cuda_runtime.h>
 
@@ -214,7 +215,45 @@ static void FreeScanDevice(b2a_scan *s) {
 		cudaFree(s->d_chunk_col);
 		cudaFree(s->d_chunk_col2);
 		cudaFree(s->d_chunk_rows);
+		cudaFree(s->d_jobs);
+		cudaFree(s->d_workspaces);
+		cudaFree(s->d_decomp_state);
 	}
+}
+
+// total device bytes behind image offset image_lo: the uploaded slice (+ the scratch region of compressed scans)
+static uint64_t DeviceImageBytes(const ScanPlan &p) {
+	return p.compressed ? (p.scratch_base - p.image_lo) + p.scratch_bytes : (p.image_hi - p.image_lo);
+}
+
+// expands the compressed buffers of jobs [j0, j1) into the scratch region (no-op for uncompressed scans)
+static int LaunchJobs(b2a_scan *s, uint32_t j0, uint32_t j1, cudaStream_t st) {
+	if (j1 <= j0) {
+		return B2A_OK;
+	}
+	cudaError_t ce = cudaMemsetAsync(s->d_decomp_state, 0, sizeof(uint32_t), st);
+	if (ce != cudaSuccess) {
+		g_last_error = std::string("CUDA error: ") + cudaGetErrorString(ce);
+		return B2A_ECUDA;
+	}
+	DecompLaunch l;
+	l.d_jobs = s->d_jobs;
+	l.job_begin = j0;
+	l.job_end = j1;
+	l.image_origin = const_cast<uint8_t *>(s->d_image) - s->plan.image_lo;
+	l.d_workspaces = s->d_workspaces;
+	l.n_workers = s->n_workers;
+	l.d_counter = s->d_decomp_state;
+	l.d_err = s->d_decomp_state + 1;
+	l.sm_count = s->sm_count;
+	int e = LaunchDecompress(l, st);
+	if (e != 0) {
+		g_last_error = std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
+		               " launching b2a_decompress_kernel";
+		return B2A_ECUDA;
+	}
+	s->launches++;
+	return B2A_OK;
 }
 
 // device < 0: plan only (layout inspection on a machine without a GPU); every compute call then fails.
@@ -251,6 +290,17 @@ int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t ba
 		CUDA_OK(cudaMemcpy(s->d_variadic, p.variadic.data(), p.variadic.size() * sizeof(uint64_t),
 		                   cudaMemcpyHostToDevice));
 		CUDA_OK(cudaMemset(s->d_err, 0, sizeof(uint32_t)));
+		if (!p.jobs.empty()) {
+			s->n_workers = DecompWorkers(s->sm_count);
+			if (s->n_workers > p.jobs.size()) {
+				s->n_workers = static_cast<uint32_t>(p.jobs.size());
+			}
+			CUDA_OK(cudaMalloc(&s->d_jobs, p.jobs.size() * sizeof(b2a_decomp_job)));
+			CUDA_OK(cudaMemcpy(s->d_jobs, p.jobs.data(), p.jobs.size() * sizeof(b2a_decomp_job), cudaMemcpyHostToDevice));
+			CUDA_OK(cudaMalloc(&s->d_workspaces, static_cast<size_t>(s->n_workers) * DecompWorkspaceBytes()));
+			CUDA_OK(cudaMalloc(&s->d_decomp_state, 2 * sizeof(uint32_t)));
+			CUDA_OK(cudaMemset(s->d_decomp_state, 0, 2 * sizeof(uint32_t)));
+		}
 	}
 	*out = s.release();
 	return B2A_OK;
@@ -296,7 +346,7 @@ int b2a_scan_upload(b2a_scan *s, void *cuda_stream) {
 	uint64_t bytes = p.image_hi - p.image_lo;
 	if (!s->d_image_owned) {
 		// +64: the string kernel fetches whole aligned words around the last characters
-		CUDA_OK(cudaMalloc(&s->d_image_owned, bytes + 64));
+		CUDA_OK(cudaMalloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
 	}
 	if (bytes) {
 		CUDA_OK(cudaMemcpyAsync(s->d_image_owned, s->r->reader.Image() + p.image_lo, bytes, cudaMemcpyHostToDevice,
@@ -330,6 +380,12 @@ int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cu
 	if (p.stats_bytes) {
 		CUDA_OK(cudaMemsetAsync(static_cast<uint8_t *>(d_out) + p.stats_base, 0, p.stats_bytes, st));
 	}
+	{
+		int rc = LaunchJobs(s, 0, static_cast<uint32_t>(p.jobs.size()), st);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+	}
 	DecodeLaunch l;
 	l.d_tasks = s->d_tasks;
 	l.d_tile_task = s->d_tile_task;
@@ -356,8 +412,21 @@ int b2a_scan_finish(b2a_scan *s, void *cuda_stream) {
 	NEED_DEVICE(s);
 	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
 	uint32_t err = 0;
+	uint32_t zerr[2] = {0, 0};
 	CUDA_OK(cudaMemcpyAsync(&err, s->d_err, sizeof(err), cudaMemcpyDeviceToHost, st));
+	if (s->d_decomp_state) {
+		CUDA_OK(cudaMemcpyAsync(zerr, s->d_decomp_state, sizeof(zerr), cudaMemcpyDeviceToHost, st));
+	}
 	CUDA_OK(cudaStreamSynchronize(st));
+	if (zerr[1] != 0) {
+		CUDA_OK(cudaMemsetAsync(s->d_decomp_state, 0, 2 * sizeof(uint32_t), st));
+		CUDA_OK(cudaMemsetAsync(s->d_err, 0, sizeof(uint32_t), st));
+		static const char *names[] = {"", "Unknown frame descriptor", "Src size is incorrect", "Data corruption detected",
+		                              "Destination buffer is too small", "Unsupported frame parameter"};
+		// base_stream_reader.cpp:17-21: "ZSTD_decompress([buffer ...]) failed with error '...'" (IOException)
+		return Fail(B2A_EIO, std::string("ZSTD_decompress of a compressed IPC buffer failed with error '") +
+		                         names[zerr[1] < 6 ? zerr[1] : 3] + "'");
+	}
 	if (err != B2A_DEV_OK) {
 		CUDA_OK(cudaMemsetAsync(s->d_err, 0, sizeof(uint32_t), st));
 		switch (err) {
@@ -402,6 +471,25 @@ int b2a_scan_dictionary(b2a_scan *s, uint32_t flat_field, b2a_column_out *out, u
 	if (dict_flat_field) {
 		*dict_flat_field = flat_field;
 	}
+	return B2A_OK;
+}
+
+int b2a_scan_scratch(b2a_scan *s, uint64_t *scratch_offset, uint64_t *scratch_bytes, uint64_t *n_jobs) {
+	const ScanPlan &p = s->plan;
+	*scratch_offset = p.compressed ? p.scratch_base - p.image_lo : 0;
+	*scratch_bytes = p.compressed ? p.scratch_bytes : 0;
+	*n_jobs = p.jobs.size();
+	return B2A_OK;
+}
+
+int b2a_scan_download_scratch(b2a_scan *s, void *h_scratch, void *cuda_stream) {
+	NEED_DEVICE(s);
+	const ScanPlan &p = s->plan;
+	if (!p.compressed || !s->d_image) {
+		return B2A_OK;
+	}
+	CUDA_OK(cudaMemcpyAsync(h_scratch, s->d_image + (p.scratch_base - p.image_lo), p.scratch_bytes, cudaMemcpyDeviceToHost,
+	                        static_cast<cudaStream_t>(cuda_stream)));
 	return B2A_OK;
 }
 
@@ -450,9 +538,8 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.compute, cudaStreamNonBlocking));
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.out, cudaStreamNonBlocking));
 	}
-	const uint64_t image_bytes = p.image_hi - p.image_lo;
 	if (!s->d_image_owned) {
-		CUDA_OK(cudaMalloc(&s->d_image_owned, image_bytes + 64));
+		CUDA_OK(cudaMalloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
 	}
 	s->d_image = s->d_image_owned;
 	if (hp.d_out_bytes < p.out_bytes) {
@@ -504,6 +591,12 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		}
 		CUDA_OK(cudaEventRecord(hp.ev_in[sl], hp.in));
 		CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[sl], 0));
+		{
+			int rc = LaunchJobs(s, p.batch_job0[b0], p.batch_job0[b1], hp.compute);
+			if (rc != B2A_OK) {
+				return rc;
+			}
+		}
 		l.tile_begin = p.batch_tile0[b0];
 		l.n_tiles = p.batch_tile0[b1] - p.batch_tile0[b0];
 		int e = LaunchDecode(l, hp.compute);
@@ -531,6 +624,13 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	}
 	CUDA_OK(cudaEventRecord(hp.ev_in[n_slices], hp.in));
 	CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[n_slices], 0));
+	{
+		int rc = LaunchJobs(s, p.batch_job0.empty() ? 0 : p.batch_job0.back(), static_cast<uint32_t>(p.jobs.size()),
+		                    hp.compute);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+	}
 	l.tile_begin = tail_tile0;
 	l.n_tiles = static_cast<uint32_t>(p.tile_task.size()) - tail_tile0;
 	if (l.n_tiles) {

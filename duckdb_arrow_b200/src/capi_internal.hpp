@@ -29,6 +29,11 @@ struct b2a_scan {
 	uint64_t *d_chunk_col2 = nullptr;  // sum_product: per chunk {a, va, b, vb}
 	uint32_t *d_chunk_rows = nullptr;
 	std::vector<uint32_t> chunk_col_key, chunk_col2_key;
+	// compressed bodies: decompress jobs, per-warp decoder workspaces, job counter + error word
+	b2a_decomp_job *d_jobs = nullptr;
+	void *d_workspaces = nullptr;
+	uint32_t *d_decomp_state = nullptr; // [0] job counter, [1] zstd error code
+	uint32_t n_workers = 0;
 };
 
 namespace b2a {

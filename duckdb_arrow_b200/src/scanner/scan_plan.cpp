@@ -26,9 +26,93 @@ uint64_t ScanPlan::Alloc(uint64_t bytes) {
 	return off;
 }
 
+// Buffers of a compressed batch are addressed through VIRTUAL offsets while the plan is built:
+// bit 62 | candidate index << 36 | offset inside the uncompressed buffer; Resolve() maps them into the scratch region.
+static const uint64_t kVirtBit = uint64_t(1) << 62;
+static const int kVirtShift = 36;
+
+RecordBatch ScanPlan::VirtualBatch(const Reader &reader, const RecordBatch &rb) {
+	if (rb.compression != 1) {
+		// the reference installs a ZSTD decompressor only (base_stream_reader.cpp:38-50); LZ4_FRAME bodies fail there too
+		throw Error(B2A_ENOTIMPL, "Arrow IPC: record batch bodies compressed with LZ4_FRAME are not supported (ZSTD only)");
+	}
+	if (alias_direct) {
+		throw Error(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan cannot alias compressed bodies: create the scan without it");
+	}
+	RecordBatch v = rb;
+	const uint8_t *image = reader.Image();
+	for (auto &b : v.buffers) {
+		if (b.length == 0) {
+			continue;
+		}
+		if (b.length < 8 || b.offset + b.length > reader.ImageSize()) {
+			throw Error(B2A_EIO, "Arrow IPC: compressed buffer is shorter than its 8-byte length prefix");
+		}
+		int64_t ulen;
+		std::memcpy(&ulen, image + b.offset, 8);
+		if (big_endian) {
+			ulen = static_cast<int64_t>(__builtin_bswap64(static_cast<uint64_t>(ulen)));
+		}
+		DecompCand c;
+		c.src_off = b.offset + 8;
+		c.src_len = b.length - 8;
+		c.job = -1;
+		if (ulen == -1) {
+			c.codec = B2A_CODEC_RAW;
+			c.dst_len = c.src_len;
+		} else if (ulen < 0) {
+			throw Error(B2A_EIO, "Arrow IPC: invalid uncompressed length in a compressed buffer");
+		} else {
+			c.codec = B2A_CODEC_ZSTD;
+			c.dst_len = static_cast<uint64_t>(ulen);
+		}
+		if (c.dst_len >= (uint64_t(1) << kVirtShift) || cands.size() >= (uint64_t(1) << (62 - kVirtShift))) {
+			throw Error(B2A_EINVAL, "compressed scan too large for one plan: split the batch range");
+		}
+		b.offset = kVirtBit | (static_cast<uint64_t>(cands.size()) << kVirtShift);
+		b.length = c.dst_len;
+		cands.push_back(c);
+	}
+	compressed = true;
+	return v;
+}
+
+uint64_t ScanPlan::Resolve(uint64_t off) const {
+	if (off == kNone || !(off & kVirtBit)) {
+		return off;
+	}
+	const DecompCand &c = cands[(off & ~kVirtBit) >> kVirtShift];
+	const uint64_t intra = off & ((uint64_t(1) << kVirtShift) - 1);
+	if (c.job < 0) {
+		return scratch_base; // never read (an untouched / empty buffer)
+	}
+	return jobs[static_cast<size_t>(c.job)].dst + intra;
+}
+
 void ScanPlan::Touch(uint64_t off, uint64_t len) {
 	if (len == 0) {
 		return;
+	}
+	if (off & kVirtBit) {
+		DecompCand &c = cands[(off & ~kVirtBit) >> kVirtShift];
+		if (c.job >= 0) {
+			return;
+		}
+		c.job = static_cast<int64_t>(jobs.size());
+		b2a_decomp_job j;
+		std::memset(&j, 0, sizeof(j));
+		j.src = c.src_off;
+		j.src_len = c.src_len;
+		j.dst = scratch_bytes; // relative to scratch_base until Build() finishes
+		j.dst_len = c.dst_len;
+		j.codec = c.codec;
+		scratch_bytes += (c.dst_len + 63) & ~uint64_t(63);
+		jobs.push_back(j);
+		off = c.src_off;
+		len = c.src_len;
+		if (len == 0) {
+			return;
+		}
 	}
 	image_lo = std::min(image_lo, off);
 	image_hi = std::max(image_hi, off + len);
@@ -406,11 +490,12 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	cols.assign((hi - lo) * n_flat, none);
 
 	for (uint64_t b = lo; b < hi; b++) {
-		const RecordBatch &rb = batches[b];
-		if (rb.compression >= 0) {
-			throw Error(B2A_ENOTIMPL, "Arrow IPC: compressed record batch bodies (zstd/lz4) are not supported by the "
-			                          "B200 scan path yet");
+		RecordBatch virt;
+		if (batches[b].compression >= 0) {
+			virt = VirtualBatch(reader, batches[b]);
 		}
+		const RecordBatch &rb = batches[b].compression >= 0 ? virt : batches[b];
+		batch_job0.push_back(static_cast<uint32_t>(jobs.size()));
 		batch_rows.push_back(rb.rows);
 		batch_chunk0.push_back(n_chunks);
 		batch_tile0.push_back(next_tile);
@@ -440,6 +525,7 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	}
 	batch_tile0.push_back(next_tile);
 	batch_out0.push_back(out_bytes);
+	batch_job0.push_back(static_cast<uint32_t>(jobs.size()));
 	cur_ranges = &tail_ranges;
 	// dictionaries: decoded once per scan (ArrowArrayScanState::AddDictionary, arrow_array_scan_state.cpp:29-52)
 	std::vector<int> dict_fields;
@@ -450,12 +536,14 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	for (int flat : dict_fields) {
 		const Field &f = *schema.flat[static_cast<size_t>(flat)];
 		const DictionaryBatch &d = reader.Dictionaries().at(f.dict_id);
+		RecordBatch virt;
 		if (d.data.compression >= 0) {
-			throw Error(B2A_ENOTIMPL, "Arrow IPC: compressed dictionary batches are not supported");
+			virt = VirtualBatch(reader, d.data);
 		}
+		const RecordBatch &drb = d.data.compression >= 0 ? virt : d.data;
 		size_t node_idx = 0, buf_idx = 0, var_idx = 0;
 		Chain empty;
-		EmitField(reader, f, d.data, node_idx, buf_idx, var_idx, empty, false, true, tmp.data(), true, true);
+		EmitField(reader, f, drb, node_idx, buf_idx, var_idx, empty, false, true, tmp.data(), true, true);
 		dict_cols[flat] = tmp[static_cast<size_t>(flat)];
 	}
 	// the popcount cells live in one region at the end of the arena (zeroed before every decode)
@@ -481,6 +569,30 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 		image_lo = image_hi = 0;
 	}
 	image_lo &= ~uint64_t(255);
+	if (compressed) {
+		// the scratch region follows the uploaded slice in the image offset space; virtual offsets become real ones
+		scratch_base = (image_hi + 255) & ~uint64_t(255);
+		scratch_bytes += 64; // the string kernel fetches whole aligned words around the last characters
+		for (auto &j : jobs) {
+			j.dst += scratch_base;
+		}
+		for (auto &t : tasks) {
+			t.src = Resolve(t.src);
+			t.src2 = Resolve(t.src2);
+			for (uint32_t i = 0; i < t.n_masks; i++) {
+				t.masks[i].src = Resolve(t.masks[i].src);
+			}
+		}
+		for (auto &v : variadic) {
+			v = Resolve(v);
+		}
+		for (auto &c : cols) {
+			c.chars_off = Resolve(c.chars_off);
+		}
+		for (auto &kv : dict_cols) {
+			kv.second.chars_off = Resolve(kv.second.chars_off);
+		}
+	}
 	upload_bytes = 0;
 	for (auto &r : batch_ranges) {
 		MergeRanges(r, reader.ImageSize());

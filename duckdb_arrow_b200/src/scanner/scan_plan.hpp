@@ -4,6 +4,7 @@
 // conversion runs on WHICH buffer; the conversions themselves are the kernels in src/kernels.
 #pragma once
 #include "../ipc/ipc_reader.hpp"
+#include "../kernels/decomp.cuh"
 #include "../kernels/task.h"
 
 #include <map>
@@ -44,6 +45,14 @@ struct ScanPlan {
 	RangeList tail_ranges;
 	uint64_t upload_bytes = 0;
 
+	// ---- compressed bodies (RecordBatch.compression): every projected buffer of a compressed batch is one job of the
+	// decompress launch; its output lives in the scratch region [scratch_base, scratch_base + scratch_bytes) of the
+	// image offset space (directly behind the uploaded slice), and the tasks read it from there
+	std::vector<b2a_decomp_job> jobs;
+	std::vector<uint32_t> batch_job0; // first job of each batch (+1 sentinel); dictionary jobs follow
+	uint64_t scratch_base = 0, scratch_bytes = 0;
+	bool compressed = false;
+
 	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
 
 	const b2a_column_out &Column(uint64_t batch, uint32_t flat) const {
@@ -71,6 +80,15 @@ private:
 	bool big_endian = false;
 	uint32_t next_tile = 0;
 	RangeList *cur_ranges = nullptr;
+	// candidate jobs: one per non-empty buffer of a compressed batch; becomes a job when a task first touches it
+	struct DecompCand {
+		uint64_t src_off, src_len, dst_len;
+		uint32_t codec;
+		int64_t job;
+	};
+	std::vector<DecompCand> cands;
+	RecordBatch VirtualBatch(const Reader &reader, const RecordBatch &rb);
+	uint64_t Resolve(uint64_t off) const;
 };
 
 } // namespace b2a

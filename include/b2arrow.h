@@ -218,6 +218,14 @@ int b2a_scan_column(b2a_scan *s, uint64_t batch, uint32_t flat_field, b2a_column
 /* Dictionary of a dictionary-encoded field (decoded once per scan, shared by every batch). */
 int b2a_scan_dictionary(b2a_scan *s, uint32_t flat_field, b2a_column_out *out, uint32_t *dict_flat_field);
 uint64_t b2a_scan_gpu_launches(b2a_scan *s);
+/* Compressed bodies (RecordBatch.compression = ZSTD; the reference decompresses buffer by buffer with ZSTD_decompress,
+ * src/ipc/stream_reader/base_stream_reader.cpp:11-50): every projected buffer is expanded on the device into a scratch
+ * region that lies `scratch_offset` bytes behind image offset image_lo, before the decode launch of the same call.
+ * A caller-provided device image (b2a_scan_set_device_image) must therefore be scratch_offset + scratch_bytes + 64 long;
+ * its first image_bytes hold the stream slice.  string_t pointers of a compressed scan point into the scratch region:
+ * a host consumer copies it with b2a_scan_download_scratch and passes string_ptr_base = h_scratch - scratch_offset. */
+int b2a_scan_scratch(b2a_scan *s, uint64_t *scratch_offset, uint64_t *scratch_bytes, uint64_t *n_jobs);
+int b2a_scan_download_scratch(b2a_scan *s, void *h_scratch, void *cuda_stream);
 
 /* Predicates -> selection vectors: for every 2 048-row chunk of every batch, sel_t[<=2048] + count.
  * d_sel: uint32[total_chunks * 2048]; d_count: uint32[total_chunks]; d_total: uint64 (sum of counts). */
