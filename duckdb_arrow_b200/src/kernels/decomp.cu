@@ -1,6 +1,6 @@
 // b2a_decompress_kernel: one warp per compressed IPC buffer at a time (jobs are handed out through an atomic counter,
 // largest-first is not needed: buffers of one batch are similar).  RAW jobs are a warp-wide copy; ZSTD jobs run the
-// frame decoder of zstd_decode.cuh on lane 0 with the warp's workspace (entropy tables + literal buffer) in global memory.
+// frame decoder of zstd_decode.cuh warp-wide (see its header) with the warp's workspace (entropy tables + literal buffer) in global memory.
 #include "decomp.cuh"
 
 #include "zstd_decode.cuh"
@@ -10,13 +10,18 @@
 namespace b2a {
 
 static constexpr int kWarpsPerCta = 4;
+// per warp in shared memory: the entropy tables
+static constexpr uint32_t kSmemPerWarp = (sizeof(zstd::Tables) + 15) & ~15u;
+static constexpr uint32_t kSmemPerCta = kSmemPerWarp * kWarpsPerCta;
+static_assert(kSmemPerCta <= 227 * 1024, "decompress kernel: shared memory per CTA");
 
 uint64_t DecompWorkspaceBytes() {
 	return (sizeof(zstd::Workspace) + 255) & ~uint64_t(255);
 }
 
 uint32_t DecompWorkers(int sm_count) {
-	return static_cast<uint32_t>(sm_count) * 4 * kWarpsPerCta;
+	const uint32_t ctas_per_sm = (227u * 1024u) / (kSmemPerCta + 1024u);
+	return static_cast<uint32_t>(sm_count) * (ctas_per_sm ? ctas_per_sm : 1) * kWarpsPerCta;
 }
 
 __global__ void __launch_bounds__(kWarpsPerCta * 32) b2a_decompress_kernel(DecompLaunch l, uint64_t ws_bytes) {
@@ -27,6 +32,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) b2a_decompress_kernel(Decom
 	}
 	zstd::Workspace *w =
 	    reinterpret_cast<zstd::Workspace *>(static_cast<uint8_t *>(l.d_workspaces) + static_cast<uint64_t>(worker) * ws_bytes);
+	extern __shared__ __align__(16) uint8_t smem[];
+	uint8_t *my = smem + (threadIdx.x >> 5) * kSmemPerWarp;
+	const zstd::Ctx cx = {static_cast<int>(lane), 32, reinterpret_cast<zstd::Tables *>(my)};
 	while (true) {
 		uint32_t j = 0;
 		if (lane == 0) {
@@ -50,9 +58,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) b2a_decompress_kernel(Decom
 			for (uint64_t i = (n8 << 3) + lane; i < job.dst_len; i += 32) {
 				dst[i] = src[i];
 			}
-		} else if (lane == 0) {
-			const int rc = zstd::decode_frame(*w, src, job.src_len, dst, job.dst_len);
-			if (rc != zstd::OK) {
+		} else {
+			// every lane runs the decoder (uniform control flow, lane-parallel copies and Huffman streams)
+			const int rc = zstd::decode_frame(cx, *w, src, job.src_len, dst, job.dst_len);
+			if (rc != zstd::OK && lane == 0) {
 				atomicMax(l.d_err, static_cast<uint32_t>(rc));
 			}
 		}
@@ -65,7 +74,17 @@ int LaunchDecompress(const DecompLaunch &l, void *stream) {
 		return 0;
 	}
 	const uint32_t ctas = (l.n_workers + kWarpsPerCta - 1) / kWarpsPerCta;
-	b2a_decompress_kernel<<<ctas, kWarpsPerCta * 32, 0, static_cast<cudaStream_t>(stream)>>>(l, DecompWorkspaceBytes());
+	static bool attr_set = false;
+	if (!attr_set) {
+		cudaError_t e = cudaFuncSetAttribute(b2a_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                                     static_cast<int>(kSmemPerCta));
+		if (e != cudaSuccess) {
+			return static_cast<int>(e);
+		}
+		attr_set = true;
+	}
+	b2a_decompress_kernel<<<ctas, kWarpsPerCta * 32, kSmemPerCta, static_cast<cudaStream_t>(stream)>>>(
+	    l, DecompWorkspaceBytes());
 	return static_cast<int>(cudaGetLastError());
 }
 

@@ -9,7 +9,14 @@ extern "C" int b2a_test_zstd_decode(const uint8_t *src, size_t len, uint8_t *dst
 	if (!w) {
 		return -1;
 	}
-	int rc = b2a::zstd::decode_frame(*w, src, len, dst, dst_size);
+	b2a::zstd::Tables *t = new (std::nothrow) b2a::zstd::Tables();
+	if (!t) {
+		delete w;
+		return -1;
+	}
+	const b2a::zstd::Ctx cx = {0, 1, t};
+	int rc = b2a::zstd::decode_frame(cx, *w, src, len, dst, dst_size);
+	delete t;
 	delete w;
 	return rc;
 }
