@@ -7,6 +7,7 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -216,6 +217,7 @@ static void FreeScanDevice(b2a_scan *s) {
 		cudaFree(s->d_chunk_col2);
 		cudaFree(s->d_chunk_rows);
 		cudaFree(s->d_jobs);
+		cudaFree(s->d_job_order);
 		cudaFree(s->d_workspaces);
 		cudaFree(s->d_decomp_state);
 	}
@@ -240,6 +242,7 @@ static int LaunchJobs(b2a_scan *s, uint32_t j0, uint32_t j1, cudaStream_t st) {
 	l.d_jobs = s->d_jobs;
 	l.job_begin = j0;
 	l.job_end = j1;
+	l.d_order = (j0 == 0 && j1 == s->plan.jobs.size()) ? s->d_job_order : nullptr;
 	l.image_origin = const_cast<uint8_t *>(s->d_image) - s->plan.image_lo;
 	l.d_workspaces = s->d_workspaces;
 	l.n_workers = s->n_workers;
@@ -297,6 +300,15 @@ int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t ba
 			}
 			CUDA_OK(cudaMalloc(&s->d_jobs, p.jobs.size() * sizeof(b2a_decomp_job)));
 			CUDA_OK(cudaMemcpy(s->d_jobs, p.jobs.data(), p.jobs.size() * sizeof(b2a_decomp_job), cudaMemcpyHostToDevice));
+			std::vector<uint32_t> order(p.jobs.size());
+			for (size_t i = 0; i < order.size(); i++) {
+				order[i] = static_cast<uint32_t>(i);
+			}
+			std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+				return p.jobs[a].dst_len > p.jobs[b].dst_len;
+			});
+			CUDA_OK(cudaMalloc(&s->d_job_order, order.size() * sizeof(uint32_t)));
+			CUDA_OK(cudaMemcpy(s->d_job_order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
 			CUDA_OK(cudaMalloc(&s->d_workspaces, static_cast<size_t>(s->n_workers) * DecompWorkspaceBytes()));
 			CUDA_OK(cudaMalloc(&s->d_decomp_state, 2 * sizeof(uint32_t)));
 			CUDA_OK(cudaMemset(s->d_decomp_state, 0, 2 * sizeof(uint32_t)));

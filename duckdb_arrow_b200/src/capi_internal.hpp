@@ -31,6 +31,7 @@ struct b2a_scan {
 	std::vector<uint32_t> chunk_col_key, chunk_col2_key;
 	// compressed bodies: decompress jobs, per-warp decoder workspaces, job counter + error word
 	b2a_decomp_job *d_jobs = nullptr;
+	uint32_t *d_job_order = nullptr; // all jobs, largest output first (whole-scan launches: shortens the tail)
 	void *d_workspaces = nullptr;
 	uint32_t *d_decomp_state = nullptr; // [0] job counter, [1] zstd error code
 	uint32_t n_workers = 0;

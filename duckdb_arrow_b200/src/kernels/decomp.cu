@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) b2a_decompress_kernel(Decom
 		if (j >= l.job_end) {
 			break;
 		}
-		const b2a_decomp_job job = l.d_jobs[j];
+		const b2a_decomp_job job = l.d_jobs[l.d_order ? l.d_order[j] : j];
 		const uint8_t *src = l.image_origin + job.src;
 		uint8_t *dst = l.image_origin + job.dst;
 		if (job.codec == B2A_CODEC_RAW) {

@@ -25,6 +25,7 @@ namespace b2a {
 struct DecompLaunch {
 	const b2a_decomp_job *d_jobs = nullptr;
 	uint32_t job_begin = 0, job_end = 0;
+	const uint32_t *d_order = nullptr; // optional: the k-th job handed out is d_order[k] (largest first); covers all jobs
 	uint8_t *image_origin = nullptr; // device address of stream-image offset 0
 	void *d_workspaces = nullptr;    // DecompWorkspaceBytes() per worker warp
 	uint32_t n_workers = 0;
