@@ -458,6 +458,102 @@ __device__ __forceinline__ void put_string(uint8_t *dst, const uint4 &e, uint32_
 	}
 }
 
+// Same contract as put_string, for the shared-memory stage: the bytes leave in aligned 32-bit stores (plus at most three
+// byte stores at either end, because neighbouring strings share those words), and the source words of a long string are
+// fetched eight at a time before anything is stored — a warp issues in order, so a loop that stores each word right after
+// loading it pays one memory latency per word.
+__device__ __forceinline__ void emit_words(uint8_t *dst, const uint32_t (&w)[9], uint32_t r, uint32_t n) {
+#pragma unroll
+	for (uint32_t i = 0; i < 8; i++) {
+		if (i < n) {
+			*reinterpret_cast<uint32_t *>(dst + 4 * i) = __funnelshift_r(w[i], w[i + 1], r);
+		}
+	}
+}
+
+__device__ __forceinline__ void put_string_words(uint8_t *dst, const uint4 &e, uint32_t len) {
+	if (len == 0) {
+		return;
+	}
+	const uint32_t dalign = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst)) & 3u;
+	uint32_t head = (4u - dalign) & 3u;
+	if (head > len) {
+		head = len;
+	}
+	const uint32_t body = (len - head) >> 2, tail = (len - head) & 3u;
+	if (len <= 12) {
+		// source = the 12 inlined bytes in registers
+		const uint32_t w[5] = {e.y, e.z, e.w, 0u, 0u};
+#pragma unroll
+		for (uint32_t j = 0; j < 3; j++) {
+			if (j < head) {
+				dst[j] = static_cast<uint8_t>(w[0] >> (8 * j));
+			}
+		}
+		const uint32_t r = head * 8; // source byte `head` is byte (head & 3) of word 0 (head <= 3)
+		uint8_t *d = dst + head;
+#pragma unroll
+		for (uint32_t k = 0; k < 3; k++) {
+			if (k < body) {
+				*reinterpret_cast<uint32_t *>(d + 4 * k) = __funnelshift_r(w[k], w[k + 1], r);
+			}
+		}
+		const uint32_t v = body == 0 ? __funnelshift_r(w[0], w[1], r)
+		                             : (body == 1 ? __funnelshift_r(w[1], w[2], r) : __funnelshift_r(w[2], w[3], r));
+#pragma unroll
+		for (uint32_t j = 0; j < 3; j++) {
+			if (j < tail) {
+				d[4 * body + j] = static_cast<uint8_t>(v >> (8 * j));
+			}
+		}
+		return;
+	}
+	const uintptr_t p = (static_cast<uintptr_t>(e.w) << 32) | e.z;
+	const uint32_t *wp = reinterpret_cast<const uint32_t *>(p & ~uintptr_t(3));
+	const uint32_t sshift = static_cast<uint32_t>(p) & 3u;
+	const uint32_t last = (sshift + len - 1) >> 2; // index of the last aligned source word that holds string bytes
+	// head bytes (<= 3) come out of source words 0 and 1
+	const uint32_t w0 = __ldg(wp), w1 = last >= 1 ? __ldg(wp + 1) : 0u;
+#pragma unroll
+	for (uint32_t j = 0; j < 3; j++) {
+		if (j < head) {
+			const uint32_t b = sshift + j;
+			dst[j] = static_cast<uint8_t>((b < 4 ? w0 : w1) >> (8 * (b & 3)));
+		}
+	}
+	const uint32_t s = sshift + head;
+	const uint32_t r = (s & 3u) * 8u;
+	uint32_t idx = (s >> 2) + 1; // next source word to fetch
+	uint32_t lo = (s >> 2) == 0 ? w0 : w1;
+	uint8_t *d = dst + head;
+	uint32_t left = body;
+	while (left > 0) {
+		uint32_t w[9];
+		w[0] = lo;
+#pragma unroll
+		for (uint32_t i = 0; i < 8; i++) {
+			w[i + 1] = idx + i <= last ? __ldg(wp + idx + i) : 0u;
+		}
+		const uint32_t n = left < 8 ? left : 8;
+		emit_words(d, w, r, n);
+		// the word after the last emitted one becomes the new low word
+		lo = n == 8 ? w[8] : (n == 7 ? w[7] : (n == 6 ? w[6] : (n == 5 ? w[5] : (n == 4 ? w[4] : (n == 3 ? w[3] : (n == 2 ? w[2] : w[1]))))));
+		idx += n;
+		d += 4 * n;
+		left -= n;
+	}
+	if (tail) {
+		const uint32_t hi = idx <= last ? __ldg(wp + idx) : 0u;
+		const uint32_t v = __funnelshift_r(lo, hi, r);
+#pragma unroll
+		for (uint32_t j = 0; j < 3; j++) {
+			if (j < tail) {
+				d[j] = static_cast<uint8_t>(v >> (8 * j));
+			}
+		}
+	}
+}
+
 // K12: string_t -> offsets (running sum of lengths, NULL rows repeat the previous offset) + character bytes
 // (ArrowVarcharData::AppendTemplated).  Tile = 1 024 rows, thread = 4 consecutive rows.  The tile's characters form
 // one contiguous window of the data buffer: they are assembled in shared memory (inlined strings from registers,
@@ -520,7 +616,7 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 			uint8_t *wdst = stage + phase;
 #pragma unroll
 			for (int u = 0; u < kRowsPerThread; u++) {
-				put_string(wdst + rel, e[u], len[u]);
+				put_string_words(wdst + rel, e[u], len[u]);
 				rel += len[u];
 			}
 		} else {
