@@ -409,7 +409,18 @@ int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cu
 	l.d_err = s->d_err;
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
+	// tiles from phase2_tile0 on read vectors the earlier tiles decode (REE gathers): a second launch on the same stream
+	const uint32_t total_tiles = l.n_tiles, p2 = p.phase2_tile0 < total_tiles ? p.phase2_tile0 : total_tiles;
+	l.n_tiles = p2;
 	int e = LaunchDecode(l, cuda_stream);
+	if (e == 0 && p2 < total_tiles) {
+		if (l.n_tiles) {
+			s->launches++;
+		}
+		l.tile_begin = p2;
+		l.n_tiles = total_tiles - p2;
+		e = LaunchDecode(l, cuda_stream);
+	}
 	if (e != 0) {
 		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
 		                           " launching b2a_decode_kernel");
@@ -562,6 +573,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		hp.d_out_bytes = p.out_bytes;
 	}
 	const uint64_t n_batches = p.batch_hi - p.batch_lo;
+	const bool has_phase2 = p.phase2_tile0 < p.tile_task.size();
 	if (n_slices == 0) {
 		n_slices = 16;
 	}
@@ -621,7 +633,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		CUDA_OK(cudaEventRecord(hp.ev_c[sl], hp.compute));
 		CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[sl], 0));
 		const uint64_t o0 = p.batch_out0[b0], o1 = p.batch_out0[b1];
-		if (o1 > o0) {
+		if (o1 > o0 && !has_phase2) {
 			CUDA_OK(cudaMemcpyAsync(h_out + o0, hp.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, hp.out));
 		}
 	}
@@ -643,9 +655,20 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 			return rc;
 		}
 	}
+	const uint32_t all_tiles = static_cast<uint32_t>(p.tile_task.size());
+	const uint32_t p2_tile0 = has_phase2 ? p.phase2_tile0 : all_tiles;
 	l.tile_begin = tail_tile0;
-	l.n_tiles = static_cast<uint32_t>(p.tile_task.size()) - tail_tile0;
+	l.n_tiles = p2_tile0 - tail_tile0;
 	if (l.n_tiles) {
+		int e = LaunchDecode(l, hp.compute);
+		if (e != 0) {
+			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+		}
+		s->launches++;
+	}
+	if (has_phase2) {
+		l.tile_begin = p2_tile0;
+		l.n_tiles = all_tiles - p2_tile0;
 		int e = LaunchDecode(l, hp.compute);
 		if (e != 0) {
 			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
@@ -654,8 +677,10 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	}
 	CUDA_OK(cudaEventRecord(hp.ev_c[n_slices], hp.compute));
 	CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[n_slices], 0));
-	if (p.out_bytes > tail_out0) {
-		CUDA_OK(cudaMemcpyAsync(h_out + tail_out0, hp.d_out + tail_out0, p.out_bytes - tail_out0, cudaMemcpyDeviceToHost,
+	// REE gathers write into the batches' regions after the per-slice copies would have left: one copy of the whole arena
+	const uint64_t d2h_from = has_phase2 ? 0 : tail_out0;
+	if (p.out_bytes > d2h_from) {
+		CUDA_OK(cudaMemcpyAsync(h_out + d2h_from, hp.d_out + d2h_from, p.out_bytes - d2h_from, cudaMemcpyDeviceToHost,
 		                        hp.out));
 	}
 	CUDA_OK(cudaStreamSynchronize(hp.out));

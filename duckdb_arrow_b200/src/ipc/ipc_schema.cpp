@@ -285,7 +285,31 @@ void MapFieldToDuckDB(Field &f) {
 		}
 		throw Error(B2A_ENOTIMPL, "Arrow IPC: sparse unions are not supported by the B200 scan path");
 	} else if (fmt == "+r") {
-		throw Error(B2A_ENOTIMPL, "Arrow IPC: run-end encoded arrays are not supported by the B200 scan path");
+		// arrow_duck_schema.cpp:276-297: the DuckDB type is the type of the `values` child; run ends are int16/32/64
+		if (f.children.size() != 2) {
+			throw Error(B2A_EINVAL, "Arrow IPC: a run-end encoded field needs exactly two children");
+		}
+		const Field &re = *f.children[0], &vals = *f.children[1];
+		if (re.type_id != B2A_T_SMALLINT && re.type_id != B2A_T_INTEGER && re.type_id != B2A_T_BIGINT) {
+			throw Error(B2A_ENOTIMPL, "Type '" + re.format + "' not implemented for RunEndEncoding");
+		}
+		// FlattenRunEndsSwitch (arrow_conversion.cpp:665-719): flat physical value types only
+		const bool flat_value = vals.children.empty() && vals.dict_id < 0 && vals.op != B2A_OP_REE &&
+		                        (vals.out_width == 1 || vals.out_width == 2 || vals.out_width == 4 ||
+		                         vals.out_width == 8 || vals.out_width == 16) &&
+		                        vals.type_id != B2A_T_BLOB && vals.type_id != B2A_T_UHUGEINT && vals.type_id != B2A_T_UUID;
+		if (!flat_value) {
+			throw Error(B2A_ENOTIMPL, "RunEndEncoded value type '" + vals.format + "' not supported yet");
+		}
+		f.type_id = vals.type_id;
+		f.op = B2A_OP_REE;
+		f.out_width = vals.out_width;
+		// run ends are read as int16 or int32; int64 run ends are read through an int32 pointer, like the reference
+		// does (arrow_conversion.cpp:760-762 instantiates FlattenRunEndsSwitch<int32_t> for INT64)
+		f.src_width = re.type_id == B2A_T_SMALLINT ? 2 : 4;
+		f.decimal_width = vals.decimal_width;
+		f.decimal_scale = vals.decimal_scale;
+		f.n_buffers = 0;
 	} else {
 		throw Error(B2A_ENOTIMPL, "Unsupported Internal Arrow Type " + fmt);
 	}

@@ -835,6 +835,83 @@ __device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__re
 }
 
 // ------------------------------------------------------------------------------------------------
+// Run-end encoded: FindRunIndex + FlattenRunEnds (arrow_conversion.cpp:551-663).  One row per thread: binary search of
+// the first run end that is greater than the row, then the DECODED value of that run (already in the arena: this op
+// runs in the second launch) is copied; when the values can be NULL the result mask is written through a warp ballot.
+// Rows past the last run end are left untouched, like the reference's loop leaves them.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int64_t ree_run_end(const uint8_t *re, uint32_t width, uint64_t i, bool swap) {
+	if (width == 2) {
+		uint16_t v = reinterpret_cast<const uint16_t *>(re)[i];
+		if (swap) {
+			v = static_cast<uint16_t>((v >> 8) | (v << 8));
+		}
+		return static_cast<int16_t>(v);
+	}
+	uint32_t v = reinterpret_cast<const uint32_t *>(re)[i];
+	return static_cast<int32_t>(swap ? bswap32(v) : v);
+}
+
+__device__ __forceinline__ void op_ree(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                       uint64_t row0, uint64_t nrows) {
+	const uint8_t *re = image + t.src;
+	const uint8_t *vals = out + t.src2;
+	const uint64_t *vmask = t.src2_len == B2A_NONE_OFF ? nullptr : reinterpret_cast<const uint64_t *>(out + t.src2_len);
+	uint8_t *dst = out + t.dst;
+	uint32_t *omask = t.aux == B2A_NONE_OFF ? nullptr : reinterpret_cast<uint32_t *>(out + t.aux);
+	const uint64_t R = static_cast<uint64_t>(t.param);
+	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	const uint32_t w = t.dst_width;
+	const uint64_t end = row0 + nrows;
+	// whole warps walk the tile so that the ballot always covers 32 consecutive rows
+	for (uint64_t base = row0 + (threadIdx.x & ~31u); base < end; base += kThreads) {
+		const uint64_t i = base + (threadIdx.x & 31u);
+		bool valid = true;
+		if (i < end) {
+			uint64_t lo = 0, hi = R;
+			while (lo < hi) {
+				const uint64_t mid = (lo + hi) >> 1;
+				if (static_cast<int64_t>(i) >= ree_run_end(re, t.src_width, mid, swap)) {
+					lo = mid + 1;
+				} else {
+					hi = mid;
+				}
+			}
+			if (lo < R) {
+				valid = !vmask || ((vmask[lo >> 6] >> (lo & 63)) & 1ull);
+				if (valid) {
+					const uint8_t *s = vals + lo * w;
+					uint8_t *d = dst + i * w;
+					switch (w) {
+					case 1:
+						*d = *s;
+						break;
+					case 2:
+						*reinterpret_cast<uint16_t *>(d) = *reinterpret_cast<const uint16_t *>(s);
+						break;
+					case 4:
+						*reinterpret_cast<uint32_t *>(d) = *reinterpret_cast<const uint32_t *>(s);
+						break;
+					case 8:
+						*reinterpret_cast<uint64_t *>(d) = *reinterpret_cast<const uint64_t *>(s);
+						break;
+					default:
+						*reinterpret_cast<uint4 *>(d) = *reinterpret_cast<const uint4 *>(s);
+						break;
+					}
+				}
+			}
+		}
+		if (omask) {
+			const uint32_t bits = __ballot_sync(0xFFFFFFFFu, valid);
+			if ((threadIdx.x & 31u) == 0) {
+				omask[base >> 5] = bits;
+			}
+		}
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
@@ -918,6 +995,9 @@ __global__ void __launch_bounds__(kThreads)
 			break;
 		case B2A_OP_LIST64:
 			op_list<uint64_t>(t, image, out, row0, nrows, variadic, err);
+			break;
+		case B2A_OP_REE:
+			op_ree(t, image, out, row0, nrows);
 			break;
 		default:
 			op_scalar(t, image, out, row0, nrows, err);

@@ -9,6 +9,7 @@
 #define B2A_TASK_F_SIGNED 0x2u     /* DICT_INDEX / DECIMAL: source is signed */
 #define B2A_TASK_F_ADD_NULL 0x4u   /* VALIDITY of a dictionary: extra NULL slot at index `rows` */
 #define B2A_TASK_F_BLOB 0x8u
+#define B2A_TASK_F_PHASE2 0x10u    /* reads vectors another task decoded (REE gather): runs in the second launch */
 
 /* device error codes (atomicMax into the scan's error word) */
 #define B2A_DEV_OK 0u

@@ -1,6 +1,7 @@
 #include "scan_plan.hpp"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -217,6 +218,78 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 	slot.rows = L;
 	slot.null_count = static_cast<uint64_t>(node.null_count);
 	slot.chars_len = 0;
+
+	// ---- run-end encoded (ColumnArrowToDuckDBRunEndEncoded, arrow_conversion.cpp:721-767): no buffers of its own; the
+	// `values` child is decoded like an independent column of R rows (its own validity only — the reference passes
+	// neither the parent mask nor the parent chain on), the `run_ends` child is read raw by the gather task, which runs in
+	// the second launch because it reads the DECODED values (FlattenRunEnds, :579-663).
+	if (f.op == B2A_OP_REE && !is_dict) {
+		if (as_dictionary_values) {
+			throw Error(B2A_ENOTIMPL, "run-end encoded dictionary values are not supported");
+		}
+		const Field &re = *f.children.at(0), &vals = *f.children.at(1);
+		if (node_idx >= rb.nodes.size() || buf_idx + 2 > rb.buffers.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has too few nodes/buffers for field '" + f.name + "'");
+		}
+		const NodeSlice rnode = rb.nodes[node_idx++];
+		const BufferSlice *rbufs = rb.buffers.data() + buf_idx;
+		buf_idx += 2;
+		const uint64_t R = static_cast<uint64_t>(rnode.length), rw = static_cast<uint64_t>(re.out_width);
+		NeedBytes(rbufs[1], R * rw, re, "run ends");
+		Touch(rbufs[1].offset, R * rw);
+		Chain empty;
+		const size_t vnode = node_idx;
+		const bool save_alias = alias_direct;
+		alias_direct = false; // the gather reads the values from the arena even in a host-alias scan
+		EmitField(reader, vals, rb, node_idx, buf_idx, var_idx, empty, true, true, slots, false, false);
+		alias_direct = save_alias;
+		if (static_cast<uint64_t>(rb.nodes[vnode].length) != R) {
+			throw Error(B2A_EIO, "Arrow IPC: run_ends and values of field '" + f.name + "' differ in length");
+		}
+		const b2a_column_out vs = slots[vals.flat_index];
+		const uint64_t w = static_cast<uint64_t>(f.out_width);
+		b2a_task g;
+		std::memset(&g, 0, sizeof(g));
+		g.op = B2A_OP_REE;
+		g.flags = (big_endian ? B2A_TASK_F_BSWAP : 0) | B2A_TASK_F_PHASE2;
+		g.rows = L;
+		g.src = rbufs[1].offset;
+		g.src_width = static_cast<uint8_t>(f.src_width);
+		g.dst_width = static_cast<uint8_t>(w);
+		g.param = static_cast<int64_t>(R);
+		g.src2 = vs.data_off;         // ARENA offset of the decoded values
+		g.src2_len = vs.validity_off; // ARENA offset of their ValidityMask, or none
+		g.dst = slot.data_off = Alloc(L * w);
+		g.aux = kNone;
+		if (vs.validity_off != kNone) {
+			// the result mask is only written when the values can be NULL (value_format.validity.AllValid(), :603)
+			g.aux = slot.validity_off = Alloc(((L + 63) / 64) * 8);
+			algorithmic_out += ((L + 63) / 64) * 8;
+		}
+		if (vs.validity_off == kNone && !list_child && parent_chain.n > 0) {
+			// a struct parent ANDs its NULLs into the child's mask BEFORE the child is converted (:1143-1151); FlattenRunEnds
+			// leaves that mask alone when no value is NULL (and overwrites it otherwise — the branch above)
+			b2a_task v;
+			std::memset(&v, 0, sizeof(v));
+			v.op = B2A_OP_VALIDITY;
+			v.rows = L;
+			v.flags = big_endian ? B2A_TASK_F_BSWAP : 0;
+			v.n_masks = parent_chain.n;
+			for (uint32_t i = 0; i < parent_chain.n; i++) {
+				v.masks[i] = parent_chain.m[i];
+			}
+			v.dst = slot.validity_off = Alloc(((L + 63) / 64) * 8);
+			v.aux = slot.stats_off = stats_bytes;
+			stats_bytes += 8;
+			algorithmic_out += ((L + 63) / 64) * 8;
+			AddTask(v, 2 * parent_chain.n, 0);
+		}
+		slot.chars_off = vs.chars_off;
+		slot.chars_len = vs.chars_len;
+		algorithmic_out += L * w;
+		phase2_pending.push_back(g);
+		return;
+	}
 
 	// ---- effective validity chain: own bitmap (only when null_count != 0 and the buffer exists,
 	// arrow_conversion.cpp:71) AND the struct / fixed-size-list ancestors
@@ -546,6 +619,12 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 		EmitField(reader, f, drb, node_idx, buf_idx, var_idx, empty, false, true, tmp.data(), true, true);
 		dict_cols[flat] = tmp[static_cast<size_t>(flat)];
 	}
+	// tasks that read decoded vectors (REE gathers) go last: they are launched after everything else has run
+	phase2_tile0 = next_tile;
+	for (auto &g : phase2_pending) {
+		AddTask(g, 0, g.dst_width);
+	}
+	phase2_pending.clear();
 	// the popcount cells live in one region at the end of the arena (zeroed before every decode)
 	stats_base = out_bytes;
 	out_bytes += (stats_bytes + 255) & ~uint64_t(255);
@@ -562,6 +641,14 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	for (auto &kv : dict_cols) {
 		if (kv.second.stats_off != kNone) {
 			kv.second.stats_off += stats_base;
+		}
+	}
+	if (getenv("B2A_DUMP_TASKS")) {
+		for (auto &t : tasks) {
+			fprintf(stderr, "task op=%u src=%llu src2=%llu src2_len=%llu dst=%llu aux=%llu rows=%llu sw=%u dw=%u flags=%u tile0=%u tile_rows=%u param=%lld\n",
+			        t.op, (unsigned long long)t.src, (unsigned long long)t.src2, (unsigned long long)t.src2_len,
+			        (unsigned long long)t.dst, (unsigned long long)t.aux, (unsigned long long)t.rows, t.src_width,
+			        t.dst_width, t.flags, t.tile0, t.tile_rows, (long long)t.param);
 		}
 	}
 	cur_ranges = nullptr;

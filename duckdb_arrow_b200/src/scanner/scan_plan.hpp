@@ -52,6 +52,8 @@ struct ScanPlan {
 	std::vector<uint32_t> batch_job0; // first job of each batch (+1 sentinel); dictionary jobs follow
 	uint64_t scratch_base = 0, scratch_bytes = 0;
 	bool compressed = false;
+	// tiles [phase2_tile0, n_tiles) belong to tasks that read vectors decoded by the tiles before them (REE)
+	uint32_t phase2_tile0 = 0;
 
 	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
 
@@ -87,6 +89,7 @@ private:
 		int64_t job;
 	};
 	std::vector<DecompCand> cands;
+	std::vector<b2a_task> phase2_pending;
 	RecordBatch VirtualBatch(const Reader &reader, const RecordBatch &rb);
 	uint64_t Resolve(uint64_t off) const;
 };

@@ -104,7 +104,9 @@ typedef enum b2a_op {
 	B2A_OP_DECIMAL,         /* ConvertDecimal narrowing/widening, :768-844 */
 	B2A_OP_UUID,            /* UUIDConversion, :480-495 */
 	B2A_OP_DICT_INDEX,      /* SetSelectionVector*, :1227-1348 */
-	B2A_OP_VALIDITY         /* GetValidityMask, :63-108 (internal: emitted per nullable node) */
+	B2A_OP_VALIDITY,        /* GetValidityMask, :63-108 (internal: emitted per nullable node) */
+	B2A_OP_REE              /* ColumnArrowToDuckDBRunEndEncoded + FlattenRunEnds, :551-767: the field has the type of its
+	                           values child; run ends are searched per row and the decoded values gathered */
 } b2a_op;
 
 /* One node of the schema tree, flattened in pre-order (the order of RecordBatch.nodes). */

@@ -34,6 +34,11 @@ typedef struct OState {
 	const void *dict_key[O_MAX_DICTS];
 	struct OVector *dict_vec[O_MAX_DICTS];
 	int n_dicts;
+	/* ArrowRunEndEncodingState (arrow_array_scan_state.hpp): run_ends + values vectors, decoded once per array */
+	const void *ree_key[O_MAX_DICTS];
+	struct OVector *ree_runs[O_MAX_DICTS];
+	struct OVector *ree_values[O_MAX_DICTS];
+	int n_rees;
 	int alias_direct; /* 1: DirectConversion re-points the vector like the reference (timed baseline); 0: copies */
 	char *err;
 	int errlen;
@@ -461,8 +466,16 @@ static int ColumnArrowToDuckDBDictionary(OState *st, OVector *vector, const OArr
                                          const OType *type, int64_t nested_offset, OVector *parent_mask,
                                          uint64_t parent_offset);
 
+static int ColumnArrowToDuckDBRunEndEncoded(OState *st, OVector *vector, const OArray *array, idx_t size,
+                                            const OType *type, int64_t nested_offset, OVector *parent_mask,
+                                            uint64_t parent_offset);
+
 static int ConvertChild(OState *st, OVector *child_vector, const OArray *child_array, idx_t size, const OType *child_type,
                         int64_t nested_offset, OVector *parent_mask, uint64_t parent_offset) {
+	if (child_type->run_end_encoded) {
+		return ColumnArrowToDuckDBRunEndEncoded(st, child_vector, child_array, size, child_type, nested_offset,
+		                                        parent_mask, parent_offset);
+	}
 	if (child_type->has_dictionary) {
 		return ColumnArrowToDuckDBDictionary(st, child_vector, child_array, size, child_type, nested_offset, parent_mask,
 		                                     parent_offset);
@@ -911,6 +924,115 @@ static void slab_append(OSlab *s, const OVector *v, const OType *type, idx_t cou
 	s->rows += count;
 }
 
+/* ref :551-577 FindRunIndex: first run end strictly greater than offset, count if none */
+static idx_t FindRunIndex(const uint8_t *run_ends, int width, idx_t count, idx_t offset) {
+	idx_t begin = 0, end = count;
+	while (begin < end) {
+		idx_t middle = (begin + end) / 2;
+		idx_t v = width == 2 ? (idx_t)((const int16_t *)run_ends)[middle] : (idx_t)((const int32_t *)run_ends)[middle];
+		if (offset >= v) {
+			begin = middle + 1;
+		} else {
+			end = middle;
+		}
+	}
+	return begin;
+}
+
+/* ref :579-663 FlattenRunEnds<RUN_END_TYPE, VALUE_TYPE>: VALUE_TYPE is copied as `width` bytes */
+static void FlattenRunEnds(OVector *result, const OVector *runs, const OVector *values, int run_width,
+                           idx_t compressed_size, idx_t scan_offset, idx_t count) {
+	const uint8_t *run_ends_data = runs->data;
+	const int w = values->width;
+	idx_t run = FindRunIndex(run_ends_data, run_width, compressed_size, scan_offset);
+	idx_t logical_index = scan_offset, index = 0;
+	const int values_all_valid = all_valid(values);
+	for (; run < compressed_size; ++run) {
+		idx_t run_end = run_width == 2 ? (idx_t)((const int16_t *)run_ends_data)[run]
+		                               : (idx_t)((const int32_t *)run_ends_data)[run];
+		idx_t to_scan = run_end - (logical_index + index);
+		if (to_scan > count - index) {
+			to_scan = count - index;
+		}
+		if (values_all_valid || row_is_valid(values, run)) {
+			for (idx_t i = 0; i < to_scan; i++) {
+				memcpy(result->data + (index + i) * (idx_t)w, values->data + run * (idx_t)w, (size_t)w);
+				/* validity.SetValid on a mask that was never allocated is a no-op; an allocated one gets the bit */
+				if (!values_all_valid && result->validity) {
+					result->validity[(index + i) >> 6] |= (uint64_t)1 << ((index + i) & 63);
+				}
+			}
+		} else {
+			for (idx_t i = 0; i < to_scan; i++) {
+				set_invalid(result, index + i);
+			}
+		}
+		index += to_scan;
+		if (index >= count) {
+			break;
+		}
+	}
+}
+
+/* ref :721-767 ColumnArrowToDuckDBRunEndEncoded */
+static int ColumnArrowToDuckDBRunEndEncoded(OState *st, OVector *vector, const OArray *array, idx_t size,
+                                            const OType *type, int64_t nested_offset, OVector *parent_mask,
+                                            uint64_t parent_offset) {
+	(void)parent_mask; /* the reference does not use it either */
+	const OArray *run_ends_array = array->children[0], *values_array = array->children[1];
+	const OType *run_ends_type = type->children[0], *values_type = type->children[1];
+	idx_t compressed_size = (idx_t)run_ends_array->length;
+	int slot = -1;
+	for (int i = 0; i < st->n_rees; i++) {
+		if (st->ree_key[i] == (const void *)array) {
+			slot = i;
+		}
+	}
+	if (slot < 0) {
+		if (st->n_rees >= O_MAX_DICTS) {
+			return fail(st, O_ENOTIMPL, "oracle: too many run-end encoded arrays in one scan");
+		}
+		slot = st->n_rees++;
+		st->ree_key[slot] = (const void *)array;
+		st->ree_runs[slot] = vector_new(run_ends_type, compressed_size);
+		st->ree_values[slot] = vector_new(values_type, compressed_size);
+		const int save_alias = st->alias_direct;
+		TRY(ColumnArrowToDuckDB(st, st->ree_runs[slot], run_ends_array, compressed_size, run_ends_type, -1, NULL, 0));
+		GetValidityMask(st->ree_values[slot], values_array, st, compressed_size, (int64_t)parent_offset, nested_offset, 0);
+		TRY(ColumnArrowToDuckDB(st, st->ree_values[slot], values_array, compressed_size, values_type, -1, NULL, 0));
+		st->alias_direct = save_alias;
+	}
+	idx_t scan_offset = GetEffectiveOffset(array, (int64_t)parent_offset, st, nested_offset);
+	int run_width;
+	switch (run_ends_type->id) {
+	case O_SMALLINT:
+		run_width = 2;
+		break;
+	case O_INTEGER:
+	case O_BIGINT: /* ref :760-762: INT64 run ends are flattened through FlattenRunEndsSwitch<int32_t> */
+		run_width = 4;
+		break;
+	default:
+		return fail(st, O_ENOTIMPL, "Type not implemented for RunEndEncoding");
+	}
+	switch (values_type->width) {
+	case 1:
+	case 2:
+	case 4:
+	case 8:
+	case 16:
+		break;
+	default:
+		return fail(st, O_ENOTIMPL, "RunEndEncoded value type not supported yet");
+	}
+	if (values_type->id == O_LIST || values_type->id == O_MAP || values_type->id == O_BLOB ||
+	    values_type->id == O_UHUGEINT || values_type->id == O_UUID) {
+		return fail(st, O_ENOTIMPL, "RunEndEncoded value type not supported yet");
+	}
+	FlattenRunEnds(vector, st->ree_runs[slot], st->ree_values[slot], run_width, compressed_size, scan_offset, size);
+	return O_OK;
+}
+
 /* The scan loop: ArrowScanFunction (duckdb/src/function/table/arrow.cpp:172-201) + ArrowToDuckDB (:1421-1484) */
 int oracle_scan_column(const OArray *array, const OType *type, int64_t parent_offset, OSlab **out, char *errbuf,
                        int errlen) {
@@ -932,6 +1054,8 @@ int oracle_scan_column(const OArray *array, const OType *type, int64_t parent_of
 		OVector *vec = vector_new(&vt, O_VECTOR_SIZE); /* DataChunk vector, Reset() between calls */
 		if (type->has_dictionary) {
 			rc = ColumnArrowToDuckDBDictionary(&st, vec, array, output_size, type, -1, NULL, 0);
+		} else if (type->run_end_encoded) { /* ArrowToDuckDB :1466-1469 */
+			rc = ColumnArrowToDuckDBRunEndEncoded(&st, vec, array, output_size, type, -1, NULL, 0);
 		} else {
 			GetValidityMask(vec, array, &st, output_size, parent_offset, -1, 0); /* SetValidityMask :1477 */
 			rc = ColumnArrowToDuckDB(&st, vec, array, output_size, type, -1, NULL, 0);
@@ -943,6 +1067,10 @@ int oracle_scan_column(const OArray *array, const OType *type, int64_t parent_of
 	}
 	for (int i = 0; i < st.n_dicts; i++) {
 		vector_free(st.dict_vec[i]);
+	}
+	for (int i = 0; i < st.n_rees; i++) {
+		vector_free(st.ree_runs[i]);
+		vector_free(st.ree_values[i]);
 	}
 	if (rc != O_OK) {
 		oracle_slab_free(slab);

@@ -50,6 +50,7 @@ typedef struct OType {
 	int32_t n_children;
 	int32_t has_dictionary;
 	struct OType **children;
+	int32_t run_end_encoded; /* 1: children = {run_ends type, values type}; id / width are those of the values */
 } OType;
 
 /* the subset of struct ArrowArray the converter reads */

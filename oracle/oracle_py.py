@@ -34,7 +34,8 @@ class OType(C.Structure):
 
 OType._fields_ = [("id", C.c_int32), ("width", C.c_int32), ("size_type", C.c_int32), ("datetime", C.c_int32),
                   ("bit_width", C.c_int32), ("index_type", C.c_int32), ("fixed_size", C.c_int64),
-                  ("n_children", C.c_int32), ("has_dictionary", C.c_int32), ("children", C.POINTER(C.POINTER(OType)))]
+                  ("n_children", C.c_int32), ("has_dictionary", C.c_int32), ("children", C.POINTER(C.POINTER(OType))),
+                  ("run_end_encoded", C.c_int32)]
 
 
 class ArrowArray(C.Structure):  # Arrow C data interface; OArray in oracle.h is its prefix
@@ -122,6 +123,17 @@ def make_type(t: pa.DataType) -> OType:
         inner.index_type = T[{"int8": "TINYINT", "int16": "SMALLINT", "int32": "INTEGER", "int64": "BIGINT",
                               "uint8": "UTINYINT", "uint16": "USMALLINT", "uint32": "UINTEGER",
                               "uint64": "UBIGINT"}[str(it)]]
+        return inner
+    if pa.types.is_run_end_encoded(t):
+        # arrow_duck_schema.cpp:276-297: the column has the type of its values; children = {run_ends, values}
+        inner = make_type(t.value_type)
+        kids = [make_type(t.run_end_type), make_type(t.value_type)]
+        arr = (C.POINTER(OType) * 2)(*[C.pointer(k) for k in kids])
+        _keep.extend(kids)
+        _keep.append(arr)
+        inner.children = arr
+        inner.n_children = 2
+        inner.run_end_encoded = 1
         return inner
     if isinstance(t, pa.BaseExtensionType):
         if getattr(t, "extension_name", "") == "arrow.uuid":

@@ -32,8 +32,8 @@ def _string(rec: np.ndarray) -> bytes:
 
 
 def _storage_type(t):
-    while isinstance(t, pa.BaseExtensionType):
-        t = t.storage_type
+    while isinstance(t, pa.BaseExtensionType) or pa.types.is_run_end_encoded(t):
+        t = t.value_type if pa.types.is_run_end_encoded(t) else t.storage_type
     return t
 
 

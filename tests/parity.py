@@ -31,6 +31,8 @@ def _storage(arr: pa.Array) -> pa.Array:
 def _char_base(arr: pa.Array) -> int:
     """address of the character buffer the oracle's string_t pointers point into"""
     arr = _storage(arr)
+    if pa.types.is_run_end_encoded(arr.type):  # the flattened strings still point into the values' character buffer
+        arr = _storage(arr.values)
     t = arr.type
     if pa.types.is_fixed_size_binary(t):
         return arr.buffers()[1].address
