@@ -51,7 +51,7 @@ class ArrowIPCReader:
         for i in range(self.n_flat):
             fi = _lib.FieldInfo()
             check(lib.b2a_reader_field(self._h, i, C.byref(fi)))
-            self.fields.append(Field(i, fi.name.decode(), fi.format.decode(), _lib.TYPE_NAMES[fi.type_id],
+            self.fields.append(Field(i, fi.name.decode("utf-8", "replace"), fi.format.decode("utf-8", "replace"), _lib.TYPE_NAMES[fi.type_id],
                                      _lib.OP_NAMES[fi.op], fi.out_width, fi.src_width, [], fi.parent,
                                      bool(fi.nullable), fi.decimal_width, fi.decimal_scale, fi.param, fi.dict_id,
                                      _lib.TYPE_NAMES[fi.index_type_id]))
