@@ -419,7 +419,7 @@ int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cu
 		}
 		l.tile_begin = p2;
 		l.n_tiles = total_tiles - p2;
-		e = LaunchDecode(l, cuda_stream);
+		e = LaunchPhase2(l, cuda_stream);
 	}
 	if (e != 0) {
 		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
@@ -669,7 +669,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	if (has_phase2) {
 		l.tile_begin = p2_tile0;
 		l.n_tiles = all_tiles - p2_tile0;
-		int e = LaunchDecode(l, hp.compute);
+		int e = LaunchPhase2(l, hp.compute);
 		if (e != 0) {
 			return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
 		}

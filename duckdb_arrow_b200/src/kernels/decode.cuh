@@ -24,6 +24,8 @@ struct DecodeLaunch {
 
 // returns cudaError_t as int
 int LaunchDecode(const DecodeLaunch &l, void *stream);
+// tiles of tasks flagged B2A_TASK_F_PHASE2 (they read vectors the decode launch produced): b2a_ree_kernel
+int LaunchPhase2(const DecodeLaunch &l, void *stream);
 
 struct FilterLaunch {
 	const uint8_t *out = nullptr;       // decoded arena
