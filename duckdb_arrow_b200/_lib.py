@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb2arrow.so")
+# B2A_LIB: another build of the SAME library (kernel A/B experiments); there is still no fallback if it is missing
+LIB_PATH = os.environ.get("B2A_LIB") or os.path.join(HERE, "libb2arrow.so")
 
 B2A_NONE = 0xFFFFFFFFFFFFFFFF
 VECTOR_SIZE = 2048

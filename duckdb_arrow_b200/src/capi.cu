@@ -409,6 +409,7 @@ int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cu
 	l.d_err = s->d_err;
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
+	l.lean = p.lean;
 	// tiles from phase2_tile0 on read vectors the earlier tiles decode (REE gathers): a second launch on the same stream
 	const uint32_t total_tiles = l.n_tiles, p2 = p.phase2_tile0 < total_tiles ? p.phase2_tile0 : total_tiles;
 	l.n_tiles = p2;
@@ -601,6 +602,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	l.d_err = s->d_err;
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
+	l.lean = p.lean;
 
 	for (uint32_t sl = 0; sl < n_slices; sl++) {
 		const uint64_t b0 = n_batches * sl / n_slices, b1 = n_batches * (sl + 1) / n_slices;

@@ -928,6 +928,10 @@ static_assert(sizeof(b2a_task) % 16 == 0, "b2a_task is copied in 16-byte pieces"
 // Persistent CTAs stride over the tile table.  The descriptor of the NEXT tile is fetched with cp.async while the
 // current one is processed (its task index was loaded one iteration earlier), so no tile starts with an exposed
 // tile_task -> task dependent load pair.
+// kFull = false is the lean instantiation for scans whose tasks are all COPY / VALIDITY / BOOL / STRING32 / STRING64
+// (TPC-H lineitem, most flat tables): without the rarely used ops in its switch the register allocation of the hot
+// paths is not disturbed by them (adding ONE op to the switch cost 3.5 %, see b2a_ree_kernel).
+template <bool kFull>
 __global__ void __launch_bounds__(kThreads)
     b2a_decode_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t tile_begin,
                       uint32_t tile_end,
@@ -985,19 +989,29 @@ __global__ void __launch_bounds__(kThreads)
 			op_string<uint64_t>(t, image, out, row0, nrows, ptr_origin, err);
 			break;
 		case B2A_OP_STRING_VIEW:
-			op_string_view(t, image, out, row0, nrows, ptr_origin, variadic, err);
+			if (kFull) {
+				op_string_view(t, image, out, row0, nrows, ptr_origin, variadic, err);
+			}
 			break;
 		case B2A_OP_BLOB_FIXED:
-			op_blob_fixed(t, image, out, row0, nrows, ptr_origin, variadic);
+			if (kFull) {
+				op_blob_fixed(t, image, out, row0, nrows, ptr_origin, variadic);
+			}
 			break;
 		case B2A_OP_LIST32:
-			op_list<uint32_t>(t, image, out, row0, nrows, variadic, err);
+			if (kFull) {
+				op_list<uint32_t>(t, image, out, row0, nrows, variadic, err);
+			}
 			break;
 		case B2A_OP_LIST64:
-			op_list<uint64_t>(t, image, out, row0, nrows, variadic, err);
+			if (kFull) {
+				op_list<uint64_t>(t, image, out, row0, nrows, variadic, err);
+			}
 			break;
 		default:
-			op_scalar(t, image, out, row0, nrows, err);
+			if (kFull) {
+				op_scalar(t, image, out, row0, nrows, err);
+			}
 			break;
 		}
 		if (next >= tile_end) {
@@ -1013,12 +1027,16 @@ int LaunchDecode(const DecodeLaunch &l, void *stream) {
 	if (l.n_tiles == 0) {
 		return 0;
 	}
-	// persistent grid: SM count x resident CTAs per SM (queried once)
-	static int ctas_per_sm = 0;
-	if (ctas_per_sm == 0) {
-		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, b2a_decode_kernel, kThreads, 0) != cudaSuccess ||
-		    ctas_per_sm <= 0) {
-			ctas_per_sm = 4;
+	// persistent grid: SM count x resident CTAs per SM (queried once per instantiation)
+	static int ctas_per_sm[2] = {0, 0};
+	const int v = l.lean ? 0 : 1;
+	if (ctas_per_sm[v] == 0) {
+		cudaError_t qe = l.lean ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[v], b2a_decode_kernel<false>,
+		                                                                        kThreads, 0)
+		                        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm[v], b2a_decode_kernel<true>,
+		                                                                        kThreads, 0);
+		if (qe != cudaSuccess || ctas_per_sm[v] <= 0) {
+			ctas_per_sm[v] = 4;
 		}
 	}
 	static int ctas_override = -1;
@@ -1027,12 +1045,19 @@ int LaunchDecode(const DecodeLaunch &l, void *stream) {
 		ctas_override = e ? atoi(e) : 0;
 	}
 	uint32_t grid = static_cast<uint32_t>(l.sm_count) *
-	                static_cast<uint32_t>(ctas_override > 0 ? ctas_override : ctas_per_sm);
+	                static_cast<uint32_t>(ctas_override > 0 ? ctas_override : ctas_per_sm[v]);
 	if (grid > l.n_tiles) {
 		grid = l.n_tiles;
 	}
-	b2a_decode_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-	    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out, l.string_ptr_origin, l.d_err, l.d_variadic);
+	if (l.lean) {
+		b2a_decode_kernel<false><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out, l.string_ptr_origin,
+		    l.d_err, l.d_variadic);
+	} else {
+		b2a_decode_kernel<true><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out, l.string_ptr_origin,
+		    l.d_err, l.d_variadic);
+	}
 	return static_cast<int>(cudaGetLastError());
 }
 

@@ -20,6 +20,7 @@ struct DecodeLaunch {
 	uint32_t *d_err = nullptr;
 	const uint64_t *d_variadic = nullptr;  // image offsets of view data buffers
 	int sm_count = 148;
+	bool lean = false; // every task is COPY / VALIDITY / BOOL / STRING32 / STRING64: the lean kernel instantiation
 };
 
 // returns cudaError_t as int

@@ -619,6 +619,11 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 		EmitField(reader, f, drb, node_idx, buf_idx, var_idx, empty, false, true, tmp.data(), true, true);
 		dict_cols[flat] = tmp[static_cast<size_t>(flat)];
 	}
+	lean = true;
+	for (auto &t : tasks) {
+		lean = lean && (t.op == B2A_OP_COPY || t.op == B2A_OP_VALIDITY || t.op == B2A_OP_BOOL || t.op == B2A_OP_STRING32 ||
+		                t.op == B2A_OP_STRING64);
+	}
 	// tasks that read decoded vectors (REE gathers) go last: they are launched after everything else has run
 	phase2_tile0 = next_tile;
 	for (auto &g : phase2_pending) {

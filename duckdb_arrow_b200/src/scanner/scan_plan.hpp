@@ -54,6 +54,8 @@ struct ScanPlan {
 	bool compressed = false;
 	// tiles [phase2_tile0, n_tiles) belong to tasks that read vectors decoded by the tiles before them (REE)
 	uint32_t phase2_tile0 = 0;
+	// no task outside {COPY, VALIDITY, BOOL, STRING32, STRING64}: the lean decode kernel can run the scan
+	bool lean = false;
 
 	void Build(const Reader &reader, uint64_t lo, uint64_t hi);
 
