@@ -453,6 +453,15 @@ int b2a_scan_finish(b2a_scan *s, void *cuda_stream) {
 	}
 	if (err != B2A_DEV_OK) {
 		CUDA_OK(cudaMemsetAsync(s->d_err, 0, sizeof(uint32_t), st));
+		if ((err & 0xFFu) == B2A_DEV_UNION_TAG) {
+			const uint32_t tag = (err >> 8) & 0xFFu;
+			if (tag >= 128) { // NumericCast<uint8_t>(int8_t) throws first (arrow_conversion.cpp:1209)
+				return Fail(B2A_EINTERNAL, "Information loss on integer cast: value " +
+				                               std::to_string(static_cast<int>(tag) - 256) +
+				                               " outside of target range [0, 255]");
+			}
+			return Fail(B2A_EINVAL, "Arrow union tag out of range: " + std::to_string(tag));
+		}
 		switch (err) {
 		case B2A_DEV_BAD_OFFSETS:
 			return Fail(B2A_EINVAL, "Arrow IPC: offsets buffer is not monotonically increasing or exceeds the data "

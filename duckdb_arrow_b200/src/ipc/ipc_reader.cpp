@@ -134,6 +134,15 @@ bool Reader::ReadNextMessage(uint64_t &pos) {
 				                                                        : "Uninitialized"));
 			}
 			SchemaParser::ParseMessageSchema(meta, meta_len, schema);
+			if (version == 3) {
+				// MetadataVersion V4 unions carry a validity buffer of their own (two buffers); only the V5 layout
+				// (type ids only) is handled
+				for (const Field *fl : schema.flat) {
+					if (fl->type_id == B2A_T_UNION) {
+						throw Error(B2A_ENOTIMPL, "Arrow IPC: unions of metadata version V4 streams are not supported");
+					}
+				}
+			}
 			have_schema = true;
 			// nodes / fixed buffers one RecordBatch must carry (dictionary-encoded fields contribute only their
 			// index array: validity + indices, and none of the value type's children)

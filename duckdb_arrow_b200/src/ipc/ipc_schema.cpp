@@ -283,7 +283,29 @@ void MapFieldToDuckDB(Field &f) {
 		if (fmt[2] != 's') {
 			throw Error(B2A_ENOTIMPL, std::string("Unsupported Internal Arrow Type: \"") + fmt[2] + "\" Union");
 		}
-		throw Error(B2A_ENOTIMPL, "Arrow IPC: sparse unions are not supported by the B200 scan path");
+		// arrow_duck_schema.cpp:235-259: LogicalType::UNION(members); the type ids of the format string are ignored by the
+		// reference (":242 TODO: what are these type ids actually for?") and the type_id byte is used as the member index
+		if (f.children.empty()) {
+			throw Error(B2A_EINVAL, "Attempted to convert a UNION with no fields to DuckDB which is not supported");
+		}
+		if (f.children.size() > 256) {
+			throw Error(B2A_EINVAL, "Arrow IPC: a union has at most 256 members");
+		}
+		for (auto &c : f.children) {
+			// the reference boxes every member value (GetValue / SetValue, :1216-1217); the device path handles the flat
+			// members that boxing leaves bit-identical
+			const bool flat = c->children.empty() && c->dict_id < 0 && c->op != B2A_OP_REE && c->op != B2A_OP_STRING_VIEW &&
+			                  c->type_id != B2A_T_SQLNULL && c->type_id != B2A_T_BLOB;
+			if (!flat) {
+				throw Error(B2A_ENOTIMPL, "Arrow IPC: union member '" + c->name + "' of type '" + c->format +
+				                              "' is not supported by the B200 scan path (flat members only)");
+			}
+		}
+		f.type_id = B2A_T_UNION;
+		f.op = B2A_OP_UNION;
+		f.out_width = 1; // the tag
+		f.src_width = 1;
+		f.n_buffers = 1; // MetadataVersion V5: type ids only
 	} else if (fmt == "+r") {
 		// arrow_duck_schema.cpp:276-297: the DuckDB type is the type of the `values` child; run ends are int16/32/64
 		if (f.children.size() != 2) {

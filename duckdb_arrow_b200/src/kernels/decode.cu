@@ -911,6 +911,55 @@ __device__ __forceinline__ void op_ree(const b2a_task &t, const uint8_t *__restr
 	}
 }
 
+// Sparse UNION (arrow_conversion.cpp:1173-1221).  Per row: tag = type_ids[row_idx] with row_idx the row WITHIN THE
+// 2 048-ROW CHUNK — the reference indexes the type id buffer without the chunk offset (:1209) while the members are
+// converted at it, so past the first chunk of a batch the tags repeat the batch's first 2 048; kept as is.  The member
+// the tag names is boxed (GetValue) and stored back with SetValue: union row valid iff that member row is, tag child =
+// tag, member m valid where tag == m and its own value is.  variadic[v0 .. v0+n) = arena offsets of the members'
+// decoded masks (none = all valid), variadic[v0+n .. v0+2n) = arena offsets of the masks written here.
+__device__ __forceinline__ void op_union(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                         uint64_t row0, uint64_t nrows, const uint64_t *__restrict__ variadic,
+                                         uint32_t *err) {
+	const int8_t *type_ids = reinterpret_cast<const int8_t *>(image + t.src);
+	uint8_t *tags = out + t.dst;
+	uint32_t *umask = reinterpret_cast<uint32_t *>(out + t.aux);
+	const uint32_t n = static_cast<uint32_t>(t.param);
+	const uint64_t *offs = variadic + t.variadic0;
+	const uint64_t end = row0 + nrows;
+	const uint32_t lane = threadIdx.x & 31u;
+	for (uint64_t base = row0 + (threadIdx.x & ~31u); base < end; base += kThreads) {
+		const uint64_t i = base + lane;
+		uint32_t tag = 0xFFFFFFFFu;
+		if (i < end) {
+			const int8_t raw_tag = type_ids[i % B2A_VECTOR_SIZE];
+			tag = static_cast<uint8_t>(raw_tag);
+			if (raw_tag < 0 || tag >= n) {
+				raise(err, B2A_DEV_UNION_TAG | (tag << 8));
+				tag = 0xFFFFFFFFu;
+			} else {
+				tags[i] = static_cast<uint8_t>(tag);
+			}
+		}
+		bool valid = false;
+		for (uint32_t m = 0; m < n; m++) {
+			const uint64_t raw_off = __ldg(offs + m);
+			const uint32_t raw = raw_off == B2A_NONE_OFF ? 0xFFFFFFFFu
+			                                             : reinterpret_cast<const uint32_t *>(out + raw_off)[base >> 5];
+			const uint32_t eq = __ballot_sync(0xFFFFFFFFu, tag == m);
+			if (tag == m) {
+				valid = (raw >> lane) & 1u;
+			}
+			if (lane == 0) {
+				reinterpret_cast<uint32_t *>(out + __ldg(offs + n + m))[base >> 5] = eq & raw;
+			}
+		}
+		const uint32_t bits = __ballot_sync(0xFFFFFFFFu, valid);
+		if (lane == 0) {
+			umask[base >> 5] = bits;
+		}
+	}
+}
+
 // ------------------------------------------------------------------------------------------------
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
@@ -1061,11 +1110,12 @@ int LaunchDecode(const DecodeLaunch &l, void *stream) {
 	return static_cast<int>(cudaGetLastError());
 }
 
-// Second-launch kernel: the tiles of tasks that read DECODED vectors (run-end encoded gathers).  Kept out of
+// Second-launch kernel: the tiles of tasks that read DECODED vectors (run-end encoded gathers, sparse unions).  Kept out of
 // b2a_decode_kernel on purpose: with the extra op in its switch the hot kernel lost 3.5 % (register allocation).
 __global__ void __launch_bounds__(kThreads)
     b2a_ree_kernel(const b2a_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t tile_begin,
-                   uint32_t tile_end, const uint8_t *__restrict__ image, uint8_t *__restrict__ out) {
+                   uint32_t tile_end, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                   const uint64_t *__restrict__ variadic, uint32_t *err) {
 	__shared__ b2a_task s_task;
 	for (uint32_t tile = tile_begin + blockIdx.x; tile < tile_end; tile += gridDim.x) {
 		__syncthreads();
@@ -1082,6 +1132,8 @@ __global__ void __launch_bounds__(kThreads)
 		}
 		if (t.op == B2A_OP_REE) {
 			op_ree(t, image, out, row0, nrows);
+		} else if (t.op == B2A_OP_UNION) {
+			op_union(t, image, out, row0, nrows, variadic, err);
 		}
 	}
 }
@@ -1095,7 +1147,7 @@ int LaunchPhase2(const DecodeLaunch &l, void *stream) {
 		grid = l.n_tiles;
 	}
 	b2a_ree_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-	    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out);
+	    l.d_tasks, l.d_tile_task, l.tile_begin, l.tile_begin + l.n_tiles, l.image_origin, l.out, l.d_variadic, l.d_err);
 	return static_cast<int>(cudaGetLastError());
 }
 

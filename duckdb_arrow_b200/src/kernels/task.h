@@ -9,7 +9,7 @@
 #define B2A_TASK_F_SIGNED 0x2u     /* DICT_INDEX / DECIMAL: source is signed */
 #define B2A_TASK_F_ADD_NULL 0x4u   /* VALIDITY of a dictionary: extra NULL slot at index `rows` */
 #define B2A_TASK_F_BLOB 0x8u
-#define B2A_TASK_F_PHASE2 0x10u    /* reads vectors another task decoded (REE gather): runs in the second launch */
+#define B2A_TASK_F_PHASE2 0x10u    /* reads vectors another task decoded (REE gather, UNION): runs in the second launch */
 
 /* device error codes (atomicMax into the scan's error word) */
 #define B2A_DEV_OK 0u
@@ -17,6 +17,7 @@
 #define B2A_DEV_MUL_OVERFLOW 2u    /* "Could not convert ... to Microsecond" */
 #define B2A_DEV_STRING_4GB 3u      /* "DuckDB does not support Strings over 4GB" */
 #define B2A_DEV_INDEX_U32 4u       /* "DuckDB only supports indices that fit on an uint32" */
+#define B2A_DEV_UNION_TAG 5u       /* "Arrow union tag out of range: %d" */
 
 struct b2a_mask_ref {
 	uint64_t src; /* image offset of an Arrow validity bitmap */

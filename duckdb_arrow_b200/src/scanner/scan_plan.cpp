@@ -291,6 +291,61 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		return;
 	}
 
+	// ---- sparse union (arrow_conversion.cpp:1173-1221).  One buffer (type ids).  Every member is converted like an
+	// independent column (own validity only: unlike the STRUCT case the parent's NULLs are not ANDed into the members, and
+	// the final SetValue loop overwrites the union's own mask row by row), then per row the member `tag` names is boxed
+	// and stored back: the union row is valid iff that member's row is, the tag child holds the tag, member m is valid
+	// where tag == m and its value is.  The gather task computes tags + all masks in the second launch, from the type
+	// ids and the members' DECODED masks.
+	if (f.op == B2A_OP_UNION && !is_dict) {
+		if (as_dictionary_values) {
+			throw Error(B2A_ENOTIMPL, "union dictionary values are not supported");
+		}
+		if (list_child) {
+			// under a list the reference reads type_ids[0 .. child_size) while the members start at the list's offset
+			throw Error(B2A_ENOTIMPL, "unions below a list are not supported by the B200 scan path");
+		}
+		NeedBytes(bufs[0], L, f, "type ids");
+		Touch(bufs[0].offset, L);
+		const size_t n = f.children.size();
+		const uint64_t mask_bytes = ((L + 63) / 64) * 8;
+		b2a_task g;
+		std::memset(&g, 0, sizeof(g));
+		g.op = B2A_OP_UNION;
+		g.flags = B2A_TASK_F_PHASE2;
+		g.rows = L;
+		g.src = bufs[0].offset;
+		g.src_width = 1;
+		g.dst_width = 1;
+		g.param = static_cast<int64_t>(n);
+		g.dst = slot.data_off = Alloc(L);
+		g.aux = slot.validity_off = Alloc(mask_bytes);
+		algorithmic_out += L + mask_bytes;
+		std::vector<uint64_t> raw(n), fin(n);
+		Chain empty;
+		const bool save_alias = alias_direct;
+		alias_direct = false;
+		for (size_t m = 0; m < n; m++) {
+			const Field &c = *f.children[m];
+			const size_t child_node = node_idx;
+			EmitField(reader, c, rb, node_idx, buf_idx, var_idx, empty, true, true, slots, false, false);
+			if (static_cast<uint64_t>(rb.nodes[child_node].length) < L) {
+				throw Error(B2A_EIO, "Arrow IPC: union member '" + c.name + "' is shorter than its parent");
+			}
+			b2a_column_out &cs = slots[c.flat_index];
+			raw[m] = cs.validity_off;
+			fin[m] = cs.validity_off = Alloc(mask_bytes);
+			cs.stats_off = kNone;
+			algorithmic_out += mask_bytes;
+		}
+		alias_direct = save_alias;
+		g.variadic0 = static_cast<uint32_t>(variadic.size());
+		variadic.insert(variadic.end(), raw.begin(), raw.end());
+		variadic.insert(variadic.end(), fin.begin(), fin.end());
+		phase2_pending.push_back(g);
+		return;
+	}
+
 	// ---- effective validity chain: own bitmap (only when null_count != 0 and the buffer exists,
 	// arrow_conversion.cpp:71) AND the struct / fixed-size-list ancestors
 	Chain chain = parent_chain;

@@ -79,7 +79,9 @@ typedef enum b2a_type_id {
 	B2A_T_LIST,
 	B2A_T_STRUCT,
 	B2A_T_MAP,
-	B2A_T_ARRAY
+	B2A_T_ARRAY,
+	B2A_T_UNION /* sparse union (arrow_duck_schema.cpp:235-259): a STRUCT-like node whose OWN data is the UTINYINT tag
+	               per row (DuckDB's UNION = STRUCT{tag, members...}); children = the members */
 } b2a_type_id;
 
 /* Conversion op of one field = which kernel body runs for its value buffer(s). */
@@ -105,8 +107,10 @@ typedef enum b2a_op {
 	B2A_OP_UUID,            /* UUIDConversion, :480-495 */
 	B2A_OP_DICT_INDEX,      /* SetSelectionVector*, :1227-1348 */
 	B2A_OP_VALIDITY,        /* GetValidityMask, :63-108 (internal: emitted per nullable node) */
-	B2A_OP_REE              /* ColumnArrowToDuckDBRunEndEncoded + FlattenRunEnds, :551-767: the field has the type of its
+	B2A_OP_REE,             /* ColumnArrowToDuckDBRunEndEncoded + FlattenRunEnds, :551-767: the field has the type of its
 	                           values child; run ends are searched per row and the decoded values gathered */
+	B2A_OP_UNION            /* sparse UNION, :1173-1221: tag bytes, the union's mask and the members' masks from the
+	                           type_ids buffer and the members' own validity */
 } b2a_op;
 
 /* One node of the schema tree, flattened in pre-order (the order of RecordBatch.nodes). */

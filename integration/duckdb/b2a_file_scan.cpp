@@ -115,6 +115,13 @@ LogicalType B2AFileScan::TypeOf(uint32_t flat) const {
 		}
 		return LogicalType::STRUCT(std::move(children));
 	}
+	case B2A_T_UNION: { // arrow_duck_schema.cpp:235-259
+		child_list_t<LogicalType> members;
+		for (int32_t c = f.first_child; c >= 0; c = fields[NumericCast<uint32_t>(c)].next_sibling) {
+			members.emplace_back(fields[NumericCast<uint32_t>(c)].name, TypeOf(NumericCast<uint32_t>(c)));
+		}
+		return LogicalType::UNION(std::move(members));
+	}
 	default:
 		throw NotImplementedException("Unsupported Internal Arrow Type %s", f.format);
 	}
@@ -260,6 +267,21 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 	case B2A_T_STRUCT: {
 		auto &entries = StructVector::GetEntries(vec);
 		idx_t i = 0;
+		for (int32_t c = f.first_child; c >= 0; c = fields[NumericCast<uint32_t>(c)].next_sibling) {
+			PointVector(*entries[i++], NumericCast<uint32_t>(c), offset, count);
+		}
+		return;
+	}
+	case B2A_T_UNION: {
+		// DuckDB's UNION vector is STRUCT{tag UTINYINT, members...}: the node's own data are the tags and its mask is
+		// also the tag child's (Vector::SetValue sets both, vector.cpp:442-517)
+		auto &entries = StructVector::GetEntries(vec);
+		Vector &tag = *entries[0];
+		FlatVector::SetData(tag, slab->data + co.data_off + offset);
+		FlatVector::Validity(tag).Initialize(reinterpret_cast<validity_t *>(slab->data + co.validity_off) + offset / 64,
+		                                     count);
+		tag.GetBuffer()->SetAuxiliaryData(make_uniq<B2ASlabAuxData>(slab));
+		idx_t i = 1;
 		for (int32_t c = f.first_child; c >= 0; c = fields[NumericCast<uint32_t>(c)].next_sibling) {
 			PointVector(*entries[i++], NumericCast<uint32_t>(c), offset, count);
 		}

@@ -71,7 +71,7 @@ static OVector *vector_new(const OType *type, idx_t capacity) {
 	if (type->width > 0) {
 		v->data = (uint8_t *)calloc(capacity ? capacity : 1, (size_t)type->width);
 	}
-	if (type->id == O_STRUCT) {
+	if (type->id == O_STRUCT || type->id == O_UNION) {
 		v->n_children = type->n_children;
 		v->children = (OVector **)calloc((size_t)type->n_children, sizeof(OVector *));
 		for (int i = 0; i < type->n_children; i++) {
@@ -130,6 +130,11 @@ static int row_is_valid(const OVector *v, idx_t i) {
 static void set_invalid(OVector *v, idx_t i) {
 	mask_ensure(v, i + 1);
 	v->validity[i >> 6] &= ~((uint64_t)1 << (i & 63));
+}
+static void set_valid(OVector *v, idx_t i) { /* ValidityMask::Set(i, true): nothing to do without a buffer */
+	if (v->validity) {
+		v->validity[i >> 6] |= (uint64_t)1 << (i & 63);
+	}
 }
 static int all_valid(const OVector *v) {
 	return v->validity == NULL;
@@ -733,6 +738,65 @@ static int ColumnArrowToDuckDB(OState *st, OVector *vector, const OArray *array,
 			                 (uint64_t)array->offset));
 		}
 		break;
+	case O_UNION: { /* :1173-1221 (sparse union; the vector here = DuckDB's STRUCT{tag, members...} with the tag child
+	                   folded into the node's own data + validity) */
+		const int8_t *type_ids = (const int8_t *)array->buffers[array->n_buffers == 1 ? 0 : 1];
+		idx_t n = (idx_t)array->n_children;
+		OVector **children = (OVector **)calloc(n, sizeof(OVector *));
+		int rc = O_OK;
+		for (idx_t c = 0; c < n && rc == O_OK; c++) {
+			children[c] = vector_new(type->children[c], size);
+			GetValidityMask(children[c], array->children[c], st, size, (int64_t)po, nested_offset, 0); /* :1187 */
+			/* :1190-1203 — the member is converted with the union's mask as parent_mask and parent_offset = false (0) */
+			rc = ConvertChild(st, children[c], array->children[c], size, type->children[c], nested_offset, vector, 0);
+		}
+		for (idx_t row_idx = 0; row_idx < size && rc == O_OK; row_idx++) {
+			/* :1209 type_ids[row_idx]: NOT offset by the chunk / parent offset the members were converted at */
+			int8_t raw = type_ids[row_idx];
+			if (raw < 0) { /* NumericCast<uint8_t> */
+				char msg[128];
+				snprintf(msg, sizeof(msg), "Information loss on integer cast: value %d outside of target range [0, 255]", raw);
+				rc = fail(st, O_EINVAL, msg);
+				break;
+			}
+			uint8_t tag = (uint8_t)raw;
+			if (tag >= n) {
+				char msg[64];
+				snprintf(msg, sizeof(msg), "Arrow union tag out of range: %d", tag);
+				rc = fail(st, O_EINVAL, msg);
+				break;
+			}
+			const OVector *src = children[tag];
+			int is_null = src->is_constant_null || !row_is_valid(src, row_idx);
+			/* :1216-1217 vector.SetValue(row, value.IsNull() ? Value() : Value::UNION(members, tag, value)); Vector::SetValue
+			 * (vector.cpp:442-517): validity.Set(row, !null), then child by child */
+			if (is_null) {
+				set_invalid(vector, row_idx);
+				for (idx_t c = 0; c < n; c++) {
+					set_invalid(vector->children[c], row_idx);
+				}
+			} else {
+				set_valid(vector, row_idx);
+				vector->data[row_idx] = tag;
+				for (idx_t c = 0; c < n; c++) {
+					OVector *dst = vector->children[c];
+					if (c == tag) {
+						set_valid(dst, row_idx);
+						memcpy(dst->data + row_idx * (idx_t)dst->width, src->data + row_idx * (idx_t)src->width,
+						       (size_t)dst->width);
+					} else {
+						set_invalid(dst, row_idx);
+					}
+				}
+			}
+		}
+		for (idx_t c = 0; c < n; c++) {
+			vector_free(children[c]);
+		}
+		free(children);
+		TRY(rc);
+		break;
+	}
 	default:
 		return fail(st, O_ENOTIMPL, "Unsupported type for arrow conversion");
 	}
@@ -840,7 +904,8 @@ static OSlab *slab_new(const OType *type) {
 	OSlab *s = (OSlab *)calloc(1, sizeof(OSlab));
 	s->width = type->has_dictionary ? 0 : type->width;
 	s->type_id = type->id;
-	if (!type->has_dictionary && (type->id == O_STRUCT || type->id == O_LIST || type->id == O_MAP || type->id == O_ARRAY)) {
+	if (!type->has_dictionary && (type->id == O_STRUCT || type->id == O_LIST || type->id == O_MAP || type->id == O_ARRAY ||
+	                              type->id == O_UNION)) {
 		s->n_children = type->n_children;
 		s->children = (OSlab **)calloc((size_t)type->n_children, sizeof(OSlab *));
 		for (int i = 0; i < type->n_children; i++) {
@@ -909,7 +974,7 @@ static void slab_append(OSlab *s, const OVector *v, const OType *type, idx_t cou
 		memcpy(s->data + s->rows * (uint64_t)s->width, v->data, count * (uint64_t)s->width);
 	}
 	if (!v->sel) {
-		if (type->id == O_STRUCT) {
+		if (type->id == O_STRUCT || type->id == O_UNION) {
 			for (int c = 0; c < type->n_children; c++) {
 				slab_append(s->children[c], v->children[c], type->children[c], count);
 			}

@@ -19,11 +19,12 @@ T = {n: i for i, n in enumerate(
     ["INVALID", "SQLNULL", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT", "UINTEGER",
      "UBIGINT", "HUGEINT", "UHUGEINT", "FLOAT", "DOUBLE", "DECIMAL", "VARCHAR", "BLOB", "DATE", "TIME", "TIMESTAMP",
      "TIMESTAMP_SEC", "TIMESTAMP_MS", "TIMESTAMP_NS", "TIMESTAMP_TZ", "INTERVAL", "UUID", "LIST", "STRUCT", "MAP",
-     "ARRAY"])}
+     "ARRAY", "UNION"])}
 WIDTH = {"BOOLEAN": 1, "TINYINT": 1, "UTINYINT": 1, "SMALLINT": 2, "USMALLINT": 2, "INTEGER": 4, "UINTEGER": 4,
          "FLOAT": 4, "DATE": 4, "BIGINT": 8, "UBIGINT": 8, "DOUBLE": 8, "TIME": 8, "TIMESTAMP": 8, "TIMESTAMP_SEC": 8,
          "TIMESTAMP_MS": 8, "TIMESTAMP_NS": 8, "TIMESTAMP_TZ": 8, "HUGEINT": 16, "UHUGEINT": 16, "UUID": 16,
-         "INTERVAL": 16, "VARCHAR": 16, "BLOB": 16, "LIST": 16, "MAP": 16, "SQLNULL": 0, "STRUCT": 0, "ARRAY": 0, "DECIMAL": 0}
+         "INTERVAL": 16, "VARCHAR": 16, "BLOB": 16, "LIST": 16, "MAP": 16, "SQLNULL": 0, "STRUCT": 0, "ARRAY": 0, "DECIMAL": 0,
+         "UNION": 1}
 SIZE_NORMAL, SIZE_SUPER, SIZE_FIXED, SIZE_VIEW = 0, 1, 2, 3
 DT = {"ms": 0, "us": 1, "ns": 2, "s": 3, "days": 4, "months": 5, "mdn": 6}
 
@@ -198,6 +199,14 @@ def make_type(t: pa.DataType) -> OType:
         if t.num_fields == 0:
             raise OracleError(3, "Attempted to convert a STRUCT with no fields to DuckDB which is not supported")
         simple("STRUCT")
+        kids = [make_type(t.field(i).type) for i in range(t.num_fields)]
+    elif pa.types.is_union(t):
+        # arrow_duck_schema.cpp:235-259: sparse only; the declared type codes are ignored
+        if t.mode != "sparse":
+            raise OracleError(2, 'Unsupported Internal Arrow Type: "d" Union')
+        if t.num_fields == 0:
+            raise OracleError(3, "Attempted to convert a UNION with no fields to DuckDB which is not supported")
+        simple("UNION")
         kids = [make_type(t.field(i).type) for i in range(t.num_fields)]
     else:
         raise OracleError(2, f"Unsupported Internal Arrow Type {t}")

@@ -69,6 +69,11 @@ def slab_to_py(slab, t: pa.DataType) -> list:
     if pa.types.is_struct(t):
         kids = [slab_to_py(slab.children[i], t.field(i).type) for i in range(t.num_fields)]
         return [tuple(k[i] for k in kids) if valid[i] else None for i in range(n)]
+    if pa.types.is_union(t):
+        # DuckDB UNION = STRUCT{tag, members...}: the logical value of a valid row is the tagged member's value
+        kids = [slab_to_py(slab.children[i], t.field(i).type) for i in range(t.num_fields)]
+        tags = slab.data.ravel()
+        return [kids[int(tags[i])][i] if valid[i] else None for i in range(n)]
     if pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t):
         if pa.types.is_map(t):
             ct = pa.struct([pa.field("key", t.key_type), pa.field("value", t.item_type)])
@@ -116,7 +121,7 @@ class _ViewSlab:
             self.children = [_ViewSlab(kids[0], c_lo, c_hi)]
         elif ft in ("LIST", "MAP"):
             self.children = [_ViewSlab(kids[0], 0, 0)]
-        elif ft == "STRUCT":
+        elif ft in ("STRUCT", "UNION"):
             self.children = [_ViewSlab(k, lo, hi) for k in kids]
         elif ft == "ARRAY":
             self.children = [_ViewSlab(kids[0], lo * cv.field.param, hi * cv.field.param)]

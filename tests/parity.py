@@ -112,7 +112,11 @@ def compare_values(cv, slab, arr, path, lo, hi, ftype):
         sub = child_arr.slice(c_lo, c_hi - c_lo) if False else child_arr
         compare_child(child_cv, slab.children[0], sub, path + "[]", c_lo, c_hi)
         return
-    if ftype == "STRUCT":
+    if ftype == "UNION":
+        p, o = cv.data[lo:hi], slab.data[:n]
+        bad = np.nonzero((p != o).any(axis=1) & ovalid)[0]
+        assert bad.size == 0, f"{path}: union tags differ at rows {bad[:8]}"
+    if ftype in ("STRUCT", "UNION"):
         for i, ccv in enumerate(cv.children()):
             compare_child(ccv, slab.children[i], arr.field(i) if hasattr(arr, "field") else arr, f"{path}.{ccv.field.name}",
                           lo, hi)

@@ -1,0 +1,120 @@
+"""Sparse unions (second half: arrow_conversion.cpp:1173-1221; type mapping arrow_duck_schema.cpp:235-259).
+The reference's tests hold no union fixture that passes (test/sql/arrow_testing.test:72-74 skips generated_union because of
+its dense column), so the oracle's restatement is pinned against pyarrow's own reading of the same arrays for batches of at
+most 2 048 rows, where the reference's chunk-offset quirk (type_ids indexed without the chunk offset, :1209) cannot show;
+the quirk itself is pinned by construction in test_oracle_union_reads_type_ids_without_chunk_offset.  The GPU path is then
+compared with the oracle bit for bit, quirk included."""
+import numpy as np
+import pyarrow as pa
+import pyarrow.ipc as ipc
+import pytest
+
+from logical import slab_to_py
+from parity import compare_scan_with_oracle
+
+
+def _union_array(n, seed=0, null_every=7):
+    rng = np.random.default_rng(seed)
+    ids = pa.array(rng.integers(0, 4, n).astype(np.int8))
+    i64 = pa.array([None if i % null_every == 0 else int(v) for i, v in enumerate(rng.integers(-10**12, 10**12, n))],
+                   pa.int64())
+    s = pa.array([None if i % 11 == 3 else "s" * (i % 30) + str(i) for i in range(n)], pa.string())
+    f = pa.array(rng.standard_normal(n), pa.float64())  # no NULLs: no validity buffer on the wire
+    b = pa.array([None if i % 5 == 1 else bool(i & 2) for i in range(n)], pa.bool_())
+    return pa.UnionArray.from_sparse(ids, [i64, s, f, b], ["i", "s", "f", "b"])
+
+
+def _table(n, seed=0):
+    u = _union_array(n, seed)
+    inner = pa.StructArray.from_arrays([_union_array(n, seed + 1, 3), pa.array(range(n), pa.int32())], ["u", "k"],
+                                       mask=pa.array([i % 13 == 0 for i in range(n)]))
+    return pa.table([u, inner, pa.array(range(n), pa.int64())], names=["u", "st", "plain"])
+
+
+def _stream(table, chunk=None, **opt):
+    sink = pa.BufferOutputStream()
+    with ipc.new_stream(sink, table.schema, options=ipc.IpcWriteOptions(**opt)) as w:
+        w.write_table(table, max_chunksize=chunk)
+    return sink.getvalue()
+
+
+def _norm(v):
+    return [x.decode() if isinstance(x, bytes) else x for x in v]
+
+
+def test_oracle_union_matches_pyarrow_within_one_chunk():
+    from oracle import oracle_py as O
+    for n in (0, 1, 63, 64, 65, 2048):
+        u = _union_array(n, seed=n)
+        got = _norm(slab_to_py(O.scan_column(u), u.type))
+        assert got == u.to_pylist(), n
+
+
+def test_oracle_union_reads_type_ids_without_chunk_offset():
+    """arrow_conversion.cpp:1209 reads type_ids[row_idx] with row_idx counted from the start of the CHUNK while the members
+    are converted at chunk_offset: rows 2048.. of a batch are tagged with the batch's first type ids."""
+    from oracle import oracle_py as O
+    n = 5000
+    u = _union_array(n, seed=3)
+    slab = O.scan_column(u)
+    tags = np.frombuffer(u.buffers()[0] if u.buffers()[0] is not None else u.buffers()[1], np.int8)[:n]
+    kids = [u.field(i).to_pylist() for i in range(4)]
+    expect = [kids[int(tags[r % 2048])][r] for r in range(n)]
+    assert _norm(slab_to_py(slab, u.type)) == expect
+    assert np.array_equal(slab.data.ravel()[slab.valid], (tags[np.arange(n) % 2048])[slab.valid].astype(np.uint8))
+
+
+def test_oracle_union_tag_out_of_range():
+    from oracle import oracle_py as O
+    a = pa.array([1, 2, 3], pa.int64())
+    u = pa.UnionArray.from_sparse(pa.array([0, 1, 0], pa.int8()), [a, a], ["a", "b"])
+    bad = pa.UnionArray.from_buffers(u.type, 3, [None, pa.py_buffer(np.array([0, 5, 0], np.int8))], children=[a, a])
+    with pytest.raises(O.OracleError, match="Arrow union tag out of range: 5"):
+        O.scan_column(bad)
+
+
+def test_union_schema_on_host(b2a):
+    r = b2a.ArrowIPCReader.open_buffers([_stream(_table(100))])
+    assert [c.type for c in r.columns] == ["UNION", "STRUCT", "BIGINT"]
+    assert r.columns[0].op == "UNION"
+    s = b2a.ArrowScan(r, device=-1)
+    assert s.n_tiles > 0
+    a = pa.array([1, 2], pa.int64())
+    dense = pa.UnionArray.from_dense(pa.array([0, 0], pa.int8()), pa.array([0, 1], pa.int32()), [a], ["a"])
+    with pytest.raises(b2a.B2AError, match='Unsupported Internal Arrow Type: "d" Union'):
+        b2a.ArrowIPCReader.open_buffers([_stream(pa.table([dense], names=["d"]))])
+    nested = pa.UnionArray.from_sparse(pa.array([0, 0], pa.int8()), [pa.array([[1], [2]], pa.list_(pa.int32()))], ["l"])
+    with pytest.raises(b2a.B2AError, match="flat members only"):
+        b2a.ArrowIPCReader.open_buffers([_stream(pa.table([nested], names=["n"]))])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("host_alias", [True, False])
+@pytest.mark.parametrize("n,chunk", [(1500, None), (9000, None), (9000, 2500), (64, None)])
+def test_union_scan_matches_oracle(b2a, cuda_device, host_alias, n, chunk):
+    buf = _stream(_table(n, seed=n), chunk=chunk)
+    ds = b2a.scan_arrow_ipc([buf], host_alias=host_alias)
+    compare_scan_with_oracle(ds, list(ipc.open_stream(buf)))
+
+
+@pytest.mark.gpu
+def test_union_compressed_and_projected(b2a, cuda_device):
+    t = _table(6000, seed=5)
+    buf = _stream(t, compression="zstd")
+    ds = b2a.scan_arrow_ipc([buf], columns=["plain", "u"])
+    compare_scan_with_oracle(ds, list(ipc.open_stream(buf)), columns=["plain", "u"])
+
+
+@pytest.mark.gpu
+def test_union_tag_out_of_range_raises(b2a, cuda_device):
+    a = pa.array(range(100), pa.int64())
+    u = pa.UnionArray.from_sparse(pa.array([0] * 100, pa.int8()), [a, a], ["a", "b"])
+    ids = np.zeros(100, np.int8)
+    ids[37] = 9
+    bad = pa.UnionArray.from_buffers(u.type, 100, [None, pa.py_buffer(ids)], children=[a, a])
+    with pytest.raises(b2a.B2AError, match="Arrow union tag out of range: 9"):
+        b2a.scan_arrow_ipc([_stream(pa.table([bad], names=["u"]))])
+    ids[37] = -3
+    neg = pa.UnionArray.from_buffers(u.type, 100, [None, pa.py_buffer(ids)], children=[a, a])
+    with pytest.raises(b2a.B2AError, match="Information loss on integer cast: value -3"):
+        b2a.scan_arrow_ipc([_stream(pa.table([neg], names=["u"]))])
