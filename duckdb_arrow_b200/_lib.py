@@ -24,7 +24,7 @@ T = {n: i for i, n in enumerate(TYPE_NAMES)}
 
 OP_NAMES = ["NONE", "COPY", "BOOL", "STRING32", "STRING64", "STRING_VIEW", "BLOB_FIXED", "LIST32", "LIST64",
             "MUL_I32", "MUL_I64", "DIV_I64", "DATE64", "INTERVAL_MUL", "INTERVAL_DIV", "INTERVAL_MONTHS",
-            "INTERVAL_MDN", "DECIMAL", "UUID", "DICT_INDEX", "VALIDITY", "REE", "UNION"]
+            "INTERVAL_MDN", "DECIMAL", "UUID", "DICT_INDEX", "VALIDITY", "REE", "UNION", "LISTVIEW32", "LISTVIEW64"]
 
 
 class B2AError(Exception):

@@ -450,6 +450,11 @@ class ColumnView:
         n = (self.rows + VECTOR_SIZE - 1) // VECTOR_SIZE + 1
         return self.ds.arena[self.co.aux_off: self.co.aux_off + 8 * n].view(np.uint64)
 
+    def chunk_child_windows(self) -> np.ndarray:
+        """list views: (child start row, child rows) of every 2 048-row chunk (b2a_column_out.aux_off)"""
+        n = (self.rows + VECTOR_SIZE - 1) // VECTOR_SIZE
+        return self.ds.arena[self.co.aux_off: self.co.aux_off + 16 * n].view(np.uint64).reshape(n, 2)
+
     def children(self) -> list["ColumnView"]:
         if self.is_dictionary:
             return []

@@ -269,7 +269,12 @@ void MapFieldToDuckDB(Field &f) {
 		f.src_width = 4;
 		f.n_buffers = 2;
 	} else if (fmt == "+vl" || fmt == "+vL") {
-		throw Error(B2A_ENOTIMPL, "Arrow IPC: list-view arrays are not supported by the B200 scan path yet");
+		// arrow_duck_schema.cpp: ArrowListInfo::ListView; buffers = validity, offsets, sizes
+		f.type_id = B2A_T_LIST;
+		f.op = fmt == "+vl" ? B2A_OP_LISTVIEW32 : B2A_OP_LISTVIEW64;
+		f.out_width = 16;
+		f.src_width = fmt == "+vl" ? 4 : 8;
+		f.n_buffers = 3;
 	} else if (fmt.size() > 2 && fmt[0] == '+' && fmt[1] == 'w') {
 		f.type_id = B2A_T_ARRAY;
 		f.n_buffers = 1;

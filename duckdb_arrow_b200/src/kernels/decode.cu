@@ -960,6 +960,84 @@ __device__ __forceinline__ void op_union(const b2a_task &t, const uint8_t *__res
 	}
 }
 
+// List views (ConvertArrowListViewOffsetsTemplated, arrow_conversion.cpp:166-203).  Per 2 048-row chunk (= one conversion
+// call of the reference): lowest = min(offsets[0], offsets[i] of the non-empty views), list_size = sum of the sizes;
+// entry i = {offsets[i] <= lowest ? 0 : offsets[i] - lowest, sizes[i]}; aux[chunk] = {lowest, list_size} is the window of
+// the child column this chunk's child vector covers.  One CTA per chunk: 8 rows per thread in registers, block-wide
+// min / sum.  offsets[i] + sizes[i] beyond the child array fails like nanoarrow's FULL validation.
+template <typename T>
+__device__ __forceinline__ void op_listview(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                            uint64_t row0, uint64_t nrows, uint32_t *err) {
+	constexpr uint32_t kPer = B2A_VECTOR_SIZE / kThreads;
+	__shared__ uint64_t s_min[kThreads / 32], s_sum[kThreads / 32];
+	const T *offsets = reinterpret_cast<const T *>(image + t.src);
+	const T *sizes = reinterpret_cast<const T *>(image + t.src2);
+	ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(out + t.dst);
+	ulonglong2 *aux = reinterpret_cast<ulonglong2 *>(out + t.aux);
+	const bool swap = t.flags & B2A_TASK_F_BSWAP;
+	const uint64_t child_len = static_cast<uint64_t>(t.param);
+	for (uint64_t c0 = row0; c0 < row0 + nrows; c0 += B2A_VECTOR_SIZE) {
+		const uint64_t cn = min(static_cast<uint64_t>(B2A_VECTOR_SIZE), row0 + nrows - c0);
+		uint64_t o[kPer], z[kPer];
+		T first = offsets[c0];
+		if (swap) {
+			first = sizeof(T) == 4 ? static_cast<T>(bswap32(static_cast<uint32_t>(first))) : static_cast<T>(bswap64(first));
+		}
+		uint64_t lo = first, sum = 0;
+#pragma unroll
+		for (uint32_t k = 0; k < kPer; k++) {
+			const uint64_t r = threadIdx.x + k * kThreads;
+			o[k] = 0;
+			z[k] = 0;
+			if (r < cn) {
+				T ov = offsets[c0 + r], zv = sizes[c0 + r];
+				if (swap) {
+					ov = sizeof(T) == 4 ? static_cast<T>(bswap32(static_cast<uint32_t>(ov))) : static_cast<T>(bswap64(ov));
+					zv = sizeof(T) == 4 ? static_cast<T>(bswap32(static_cast<uint32_t>(zv))) : static_cast<T>(bswap64(zv));
+				}
+				o[k] = ov;
+				z[k] = zv;
+				if (o[k] > child_len || z[k] > child_len - o[k]) {
+					raise(err, B2A_DEV_BAD_OFFSETS);
+				}
+				if (z[k] != 0 && o[k] < lo) {
+					lo = o[k];
+				}
+				sum += z[k];
+			}
+		}
+#pragma unroll
+		for (int d = 16; d > 0; d >>= 1) {
+			const uint64_t ol = __shfl_xor_sync(0xFFFFFFFFu, lo, d), os = __shfl_xor_sync(0xFFFFFFFFu, sum, d);
+			lo = ol < lo ? ol : lo;
+			sum += os;
+		}
+		__syncthreads(); // the previous chunk's readers are done with s_min / s_sum
+		if ((threadIdx.x & 31u) == 0) {
+			s_min[threadIdx.x >> 5] = lo;
+			s_sum[threadIdx.x >> 5] = sum;
+		}
+		__syncthreads();
+		lo = s_min[0];
+		sum = s_sum[0];
+#pragma unroll
+		for (uint32_t w = 1; w < kThreads / 32; w++) {
+			lo = s_min[w] < lo ? s_min[w] : lo;
+			sum += s_sum[w];
+		}
+#pragma unroll
+		for (uint32_t k = 0; k < kPer; k++) {
+			const uint64_t r = threadIdx.x + k * kThreads;
+			if (r < cn) {
+				dst[c0 + r] = make_ulonglong2(o[k] <= lo ? 0 : o[k] - lo, z[k]);
+			}
+		}
+		if (threadIdx.x == 0) {
+			aux[c0 / B2A_VECTOR_SIZE] = make_ulonglong2(lo, sum);
+		}
+	}
+}
+
 // ------------------------------------------------------------------------------------------------
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
@@ -1134,6 +1212,10 @@ __global__ void __launch_bounds__(kThreads)
 			op_ree(t, image, out, row0, nrows);
 		} else if (t.op == B2A_OP_UNION) {
 			op_union(t, image, out, row0, nrows, variadic, err);
+		} else if (t.op == B2A_OP_LISTVIEW32) {
+			op_listview<uint32_t>(t, image, out, row0, nrows, err);
+		} else if (t.op == B2A_OP_LISTVIEW64) {
+			op_listview<uint64_t>(t, image, out, row0, nrows, err);
 		}
 	}
 }

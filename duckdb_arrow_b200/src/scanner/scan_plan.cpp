@@ -196,6 +196,27 @@ static void NeedBytes(const BufferSlice &b, uint64_t need, const Field &f, const
 	}
 }
 
+// Below a list view only types whose conversion does not depend on where the conversion call starts can share one
+// decoded child column: the chunks' child ranges [lowest offset, + sum of sizes) may overlap or leave gaps.
+static void CheckListViewChild(const Field &f) {
+	if (f.dict_id >= 0) {
+		return;
+	}
+	switch (f.op) {
+	case B2A_OP_LIST32:
+	case B2A_OP_LIST64:
+	case B2A_OP_LISTVIEW32:
+	case B2A_OP_LISTVIEW64:
+	case B2A_OP_BLOB_FIXED:
+		throw Error(B2A_ENOTIMPL, "Arrow IPC: '" + f.format + "' below a list view is not supported by the B200 scan path");
+	default:
+		break;
+	}
+	for (auto &c : f.children) {
+		CheckListViewChild(*c);
+	}
+}
+
 void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch &rb, size_t &node_idx, size_t &buf_idx,
                          size_t &var_idx, const Chain &parent_chain, bool list_child, bool selected,
                          b2a_column_out *slots, bool as_dictionary_values, bool ignore_dictionary) {
@@ -530,6 +551,35 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		}
 		break;
 	}
+	case B2A_OP_LISTVIEW32:
+	case B2A_OP_LISTVIEW64: {
+		// ConvertArrowListViewOffsetsTemplated (:166-203): per conversion call (= per 2 048-row chunk at the top level)
+		// entries {offsets[i] - lowest offset, sizes[i]}, child converted for sum(sizes) rows from the lowest offset
+		if (!chain.levels.empty()) {
+			throw Error(B2A_ENOTIMPL, "Arrow IPC: list views below a list are not supported by the B200 scan path");
+		}
+		CheckListViewChild(*f.children.at(0));
+		const uint64_t ow = static_cast<uint64_t>(f.src_width);
+		NeedBytes(bufs[1], L * ow, f, "offsets");
+		NeedBytes(bufs[2], L * ow, f, "sizes");
+		if (node_idx >= rb.nodes.size()) {
+			throw Error(B2A_EIO, "Arrow IPC: RecordBatch has too few nodes for field '" + f.name + "'");
+		}
+		t.src = bufs[1].offset;
+		t.src2 = bufs[2].offset;
+		t.param = rb.nodes[node_idx].length; // child rows: offsets[i] + sizes[i] must stay inside (FULL validation)
+		t.flags |= B2A_TASK_F_PHASE2;        // runs in the cold-op kernel (needs a block-wide reduction per chunk)
+		t.dst = slot.data_off = Alloc(L * 16);
+		uint64_t n_chunks_col = (L + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
+		t.aux = slot.aux_off = Alloc((n_chunks_col + 1) * 16);
+		if (L > 0) {
+			Touch(t.src, L * ow);
+			Touch(t.src2, L * ow);
+			algorithmic_out += L * 16;
+			phase2_pending.push_back(t);
+		}
+		break;
+	}
 	default: { // COPY and the elementwise transforms: src_width bytes in, out_width bytes out
 		const uint64_t sw = static_cast<uint64_t>(f.src_width), dw = static_cast<uint64_t>(f.out_width);
 		NeedBytes(bufs[1], L * sw, f, "data");
@@ -552,6 +602,11 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 	case B2A_T_LIST:
 	case B2A_T_MAP: {
 		Chain down = chain;
+		if (f.op == B2A_OP_LISTVIEW32 || f.op == B2A_OP_LISTVIEW64) {
+			// the child is decoded once for the whole child array; each chunk's vector is a window of it (aux pairs)
+			EmitField(reader, *f.children.at(0), rb, node_idx, buf_idx, var_idx, down, true, true, slots, false, false);
+			break;
+		}
 		if (down.levels.empty()) {
 			down.top_rows = L;
 		}

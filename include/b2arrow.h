@@ -109,8 +109,10 @@ typedef enum b2a_op {
 	B2A_OP_VALIDITY,        /* GetValidityMask, :63-108 (internal: emitted per nullable node) */
 	B2A_OP_REE,             /* ColumnArrowToDuckDBRunEndEncoded + FlattenRunEnds, :551-767: the field has the type of its
 	                           values child; run ends are searched per row and the decoded values gathered */
-	B2A_OP_UNION            /* sparse UNION, :1173-1221: tag bytes, the union's mask and the members' masks from the
+	B2A_OP_UNION,           /* sparse UNION, :1173-1221: tag bytes, the union's mask and the members' masks from the
 	                           type_ids buffer and the members' own validity */
+	B2A_OP_LISTVIEW32,      /* ConvertArrowListViewOffsetsTemplated, :166-203 (+vl): offsets + sizes buffers */
+	B2A_OP_LISTVIEW64       /* +vL */
 } b2a_op;
 
 /* One node of the schema tree, flattened in pre-order (the order of RecordBatch.nodes). */
@@ -158,7 +160,9 @@ typedef struct b2a_column_out {
 	uint64_t null_count;   /* FieldNode.null_count */
 	uint64_t data_off;     /* rows * out_width bytes, B2A_NONE if the type has no flat data */
 	uint64_t validity_off; /* ceil(rows/64) uint64 words; B2A_NONE = mask untouched (all valid) */
-	uint64_t aux_off;      /* LIST/MAP: uint64[ceil(rows/2048)+1] child start row of each chunk (+ end) */
+	uint64_t aux_off;      /* LIST/MAP: uint64[ceil(rows/2048)+1] child start row of each chunk (+ end);
+	                          list views (B2A_OP_LISTVIEW*): uint64[ceil(rows/2048)][2] = {child start row, child rows} per
+	                          chunk (the reference converts sum(sizes) child rows from the chunk's lowest offset) */
 	uint64_t chars_off;    /* strings: stream-image offset of the character buffer (pointer base) */
 	uint64_t chars_len;
 	uint64_t stats_off;    /* uint64: valid-row count computed on device (popc of the mask) */

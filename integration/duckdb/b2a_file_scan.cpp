@@ -293,7 +293,15 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 		FlatVector::SetData(vec, slab->data + co.data_off + offset * sizeof(list_entry_t));
 		const auto starts = reinterpret_cast<const uint64_t *>(slab->data + co.aux_off);
 		const idx_t k = offset / STANDARD_VECTOR_SIZE;
-		const idx_t child_lo = NumericCast<idx_t>(starts[k]), child_hi = NumericCast<idx_t>(starts[k + 1]);
+		idx_t child_lo, child_hi;
+		if (f.op == B2A_OP_LISTVIEW32 || f.op == B2A_OP_LISTVIEW64) {
+			// list views: {lowest offset, sum of sizes} per chunk (ConvertArrowListViewOffsetsTemplated's child window)
+			child_lo = NumericCast<idx_t>(starts[2 * k]);
+			child_hi = child_lo + NumericCast<idx_t>(starts[2 * k + 1]);
+		} else {
+			child_lo = NumericCast<idx_t>(starts[k]);
+			child_hi = NumericCast<idx_t>(starts[k + 1]);
+		}
 		auto &child = ListVector::GetEntry(vec);
 		PointVector(child, NumericCast<uint32_t>(f.first_child), child_lo, child_hi - child_lo);
 		ListVector::SetListSize(vec, child_hi - child_lo);

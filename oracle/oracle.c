@@ -193,6 +193,31 @@ typedef struct {
 static ListOffsetData ConvertArrowListOffsets(OVector *vector, const OArray *array, idx_t size, const OType *type,
                                               idx_t effective_offset) {
 	ListOffsetData result = {0, 0};
+	if (type->list_view) { /* ConvertArrowListViewOffsetsTemplated :166-203 */
+		uint64_t *le = (uint64_t *)vector->data;
+		const int wide = type->size_type != O_SIZE_NORMAL;
+		const uint32_t *o32 = (const uint32_t *)array->buffers[1] + effective_offset;
+		const uint32_t *s32 = (const uint32_t *)array->buffers[2] + effective_offset;
+		const uint64_t *o64 = (const uint64_t *)array->buffers[1] + effective_offset;
+		const uint64_t *s64 = (const uint64_t *)array->buffers[2] + effective_offset;
+		uint64_t lowest_offset = size ? (wide ? o64[0] : o32[0]) : 0;
+		for (idx_t i = 0; i < size; i++) {
+			uint64_t off = wide ? o64[i] : o32[i], len = wide ? s64[i] : s32[i];
+			le[2 * i] = off;
+			le[2 * i + 1] = len;
+			result.list_size += len;
+			if (len != 0 && off < lowest_offset) {
+				lowest_offset = off;
+			}
+		}
+		result.start_offset = lowest_offset;
+		if (result.start_offset) {
+			for (idx_t i = 0; i < size; i++) {
+				le[2 * i] = le[2 * i] <= result.start_offset ? 0 : le[2 * i] - result.start_offset;
+			}
+		}
+		return result;
+	}
 	if (size == 0) {
 		return result;
 	}
@@ -1242,7 +1267,7 @@ int oracle_validate_full(const OArray *array, const OType *type) {
 	int is_var = (type->id == O_VARCHAR || type->id == O_BLOB) &&
 	             (type->size_type == O_SIZE_NORMAL || type->size_type == O_SIZE_SUPER);
 	int is_list = type->id == O_LIST || type->id == O_MAP;
-	if ((is_var || is_list) && array->length > 0 && array->n_buffers > 1 && array->buffers[1]) {
+	if ((is_var || (is_list && !type->list_view)) && array->length > 0 && array->n_buffers > 1 && array->buffers[1]) {
 		idx_t n = (idx_t)(array->offset + array->length) + 1;
 		if (type->size_type == O_SIZE_SUPER) {
 			const int64_t *o = (const int64_t *)array->buffers[1];
@@ -1263,6 +1288,19 @@ int oracle_validate_full(const OArray *array, const OType *type) {
 				if (o[i] < o[i - 1]) {
 					return 1;
 				}
+			}
+		}
+	}
+	if (is_list && type->list_view && array->length > 0 && array->n_children > 0) {
+		/* list views: every [offset, offset + size) lies inside the child */
+		uint64_t child_len = (uint64_t)array->children[0]->length;
+		for (idx_t i = (idx_t)array->offset; i < (idx_t)(array->offset + array->length); i++) {
+			uint64_t o = type->size_type == O_SIZE_SUPER ? ((const uint64_t *)array->buffers[1])[i]
+			                                            : ((const uint32_t *)array->buffers[1])[i];
+			uint64_t z = type->size_type == O_SIZE_SUPER ? ((const uint64_t *)array->buffers[2])[i]
+			                                            : ((const uint32_t *)array->buffers[2])[i];
+			if (o > child_len || z > child_len - o) {
+				return 1;
 			}
 		}
 	}

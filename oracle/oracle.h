@@ -52,6 +52,7 @@ typedef struct OType {
 	struct OType **children;
 	/* O_UNION (sparse): width 1 = the UTINYINT tag child of DuckDB's STRUCT{tag, members...}; children = the members */
 	int32_t run_end_encoded; /* 1: children = {run_ends type, values type}; id / width are those of the values */
+	int32_t list_view;       /* O_LIST only: ArrowListInfo::IsView() — buffers = validity, offsets, sizes */
 } OType;
 
 /* the subset of struct ArrowArray the converter reads */

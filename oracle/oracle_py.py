@@ -36,7 +36,7 @@ class OType(C.Structure):
 OType._fields_ = [("id", C.c_int32), ("width", C.c_int32), ("size_type", C.c_int32), ("datetime", C.c_int32),
                   ("bit_width", C.c_int32), ("index_type", C.c_int32), ("fixed_size", C.c_int64),
                   ("n_children", C.c_int32), ("has_dictionary", C.c_int32), ("children", C.POINTER(C.POINTER(OType))),
-                  ("run_end_encoded", C.c_int32)]
+                  ("run_end_encoded", C.c_int32), ("list_view", C.c_int32)]
 
 
 class ArrowArray(C.Structure):  # Arrow C data interface; OArray in oracle.h is its prefix
@@ -188,6 +188,9 @@ def make_type(t: pa.DataType) -> OType:
                else DT["months"])
     elif pa.types.is_list(t) or pa.types.is_large_list(t):
         simple("LIST", size_type=SIZE_SUPER if pa.types.is_large_list(t) else SIZE_NORMAL)
+        kids = [make_type(t.value_type)]
+    elif pa.types.is_list_view(t) or pa.types.is_large_list_view(t):
+        simple("LIST", size_type=SIZE_SUPER if pa.types.is_large_list_view(t) else SIZE_NORMAL, list_view=1)
         kids = [make_type(t.value_type)]
     elif pa.types.is_map(t):
         simple("MAP", size_type=SIZE_NORMAL)

@@ -74,17 +74,22 @@ def slab_to_py(slab, t: pa.DataType) -> list:
         kids = [slab_to_py(slab.children[i], t.field(i).type) for i in range(t.num_fields)]
         tags = slab.data.ravel()
         return [kids[int(tags[i])][i] if valid[i] else None for i in range(n)]
-    if pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t):
+    if pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t) or pa.types.is_list_view(t) \
+            or pa.types.is_large_list_view(t):
         if pa.types.is_map(t):
             ct = pa.struct([pa.field("key", t.key_type), pa.field("value", t.item_type)])
         else:
             ct = t.value_type
         child = slab_to_py(slab.children[0], ct)
         ent = slab.data.copy().view(np.uint64).reshape(n, 2)
-        out, cum = [], 0
+        # list_entry_t offsets are relative to the child vector of the row's 2 048-row chunk; the chunks' child vectors
+        # (sum of the chunk's lengths each) lie end to end in the child slab
+        out, cum, base = [], 0, 0
         for i in range(n):
-            ln = int(ent[i, 1])
-            out.append(child[cum:cum + ln] if valid[i] else None)
+            if i % 2048 == 0:
+                base = cum
+            off, ln = int(ent[i, 0]), int(ent[i, 1])
+            out.append(child[base + off: base + off + ln] if valid[i] else None)
             cum += ln
         return out
     if pa.types.is_fixed_size_list(t):
@@ -97,11 +102,12 @@ def slab_to_py(slab, t: pa.DataType) -> list:
 class _ViewSlab:
     """adapts a product ColumnView to the slab interface of slab_to_py (host string pointers required)"""
 
-    def __init__(self, cv, lo=0, hi=None):
-        hi = cv.rows if hi is None else hi
-        self.rows = hi - lo
-        self.valid = cv.valid[lo:hi]
-        self.data = cv.data[lo:hi]
+    def __init__(self, cv, lo=0, hi=None, ranges=None):
+        if ranges is None:
+            ranges = [(lo, cv.rows if hi is None else hi)]
+        self.rows = sum(b - a for a, b in ranges)
+        self.valid = np.concatenate([cv.valid[a:b] for a, b in ranges]) if ranges else cv.valid[0:0]
+        self.data = np.concatenate([cv.data[a:b] for a, b in ranges]) if ranges else cv.data[0:0]
         self.sel = None
         self.dict = None
         self.children = []
@@ -112,19 +118,24 @@ class _ViewSlab:
             return
         kids = cv.children()
         ft = cv.field.type
-        if ft in ("LIST", "MAP") and self.rows:
-            starts = cv.chunk_child_starts()
-            if lo == 0 and hi == cv.rows:
-                c_lo, c_hi = int(starts[0]), int(starts[-1])
-            else:
+        whole = len(ranges) == 1 and ranges[0] == (0, cv.rows)
+        if ft in ("LIST", "MAP") and cv.field.op.startswith("LISTVIEW") and self.rows:
+            if not whole:
+                raise NotImplementedError("nested list view slices")
+            win = cv.chunk_child_windows()
+            self.children = [_ViewSlab(kids[0], ranges=[(int(a), int(a + b)) for a, b in win])]
+        elif ft in ("LIST", "MAP") and self.rows:
+            if not whole:
                 raise NotImplementedError("nested list slices")
-            self.children = [_ViewSlab(kids[0], c_lo, c_hi)]
+            starts = cv.chunk_child_starts()
+            self.children = [_ViewSlab(kids[0], int(starts[0]), int(starts[-1]))]
         elif ft in ("LIST", "MAP"):
             self.children = [_ViewSlab(kids[0], 0, 0)]
         elif ft in ("STRUCT", "UNION"):
-            self.children = [_ViewSlab(k, lo, hi) for k in kids]
+            self.children = [_ViewSlab(k, ranges=ranges) for k in kids]
         elif ft == "ARRAY":
-            self.children = [_ViewSlab(kids[0], lo * cv.field.param, hi * cv.field.param)]
+            k = cv.field.param
+            self.children = [_ViewSlab(kids[0], ranges=[(a * k, b * k) for a, b in ranges])]
 
 
 def column_to_py(cv, t: pa.DataType) -> list:

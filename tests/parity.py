@@ -96,6 +96,23 @@ def compare_values(cv, slab, arr, path, lo, hi, ftype):
         assert np.array_equal(pin[long_][:, :4], oin[long_][:, :4]), f"{path}: prefixes differ"
         assert np.array_equal(prel[long_], orel[long_]), f"{path}: string pointers differ"
         return
+    if ftype == "LIST" and cv.field.op.startswith("LISTVIEW"):
+        assert lo == 0 and hi == cv.rows, "list views are compared whole"
+        assert np.array_equal(cv.data[lo:hi], slab.data[:n]), f"{path}: list_entry_t differ"
+        child_cv, child_arr = cv.children()[0], _storage(arr).values
+        win = cv.chunk_child_windows() if n else np.zeros((0, 2), np.uint64)
+        offs, sizes = _view_offsets_sizes(arr)
+        done = 0
+        for k in range((n + VS - 1) // VS):
+            o, z = offs[k * VS:(k + 1) * VS], sizes[k * VS:(k + 1) * VS]
+            lowest = min([int(o[0])] + [int(a) for a, b in zip(o, z) if b != 0])
+            assert (int(win[k, 0]), int(win[k, 1])) == (lowest, int(z.sum())), f"{path}: child window of chunk {k} differs"
+            c_lo, c_hi = lowest, lowest + int(z.sum())
+            compare_child(child_cv, _slab_slice(slab.children[0], done, done + c_hi - c_lo), child_arr, f"{path}[{k}]",
+                          c_lo, c_hi)
+            done += c_hi - c_lo
+        assert done == slab.children[0].rows
+        return
     if ftype in ("LIST", "MAP"):
         assert np.array_equal(cv.data[lo:hi], slab.data[:n]), f"{path}: list_entry_t differ"
         child_cv = cv.children()[0]
@@ -146,6 +163,40 @@ def compare_child(ccv, cslab, carr, path, lo, hi):
     if ccv.field.type == "SQLNULL":
         return
     compare_values(ccv, cslab, carr, path, lo, hi, ccv.field.type)
+
+
+class _SlabSlice:
+    pass
+
+
+def _slab_slice(slab, a, b):
+    """rows [a, b) of an oracle slab (flat / struct / fixed-size-list / dictionary children only)"""
+    s = _SlabSlice()
+    s.rows = b - a
+    s.width, s.type_id, s.all_null = slab.width, slab.type_id, slab.all_null
+    s.valid = slab.valid[a:b]
+    s.data = slab.data[a:b]
+    s.sel = slab.sel[a:b] if slab.sel is not None else None
+    s.dict = slab.dict
+    if slab.children and slab.type_id == O.T["ARRAY"]:
+        k = slab.children[0].rows // slab.rows if slab.rows else 0
+        s.children = [_slab_slice(slab.children[0], a * k, b * k)]
+    elif slab.children and slab.type_id in (O.T["STRUCT"], O.T["UNION"]):
+        s.children = [_slab_slice(c, a, b) for c in slab.children]
+    elif slab.children:
+        raise NotImplementedError("slice of a list slab")
+    else:
+        s.children = []
+    return s
+
+
+def _view_offsets_sizes(arr):
+    arr = _storage(arr)
+    dt = np.int64 if pa.types.is_large_list_view(arr.type) else np.int32
+    bufs = arr.buffers()
+    n = len(arr)
+    return (np.frombuffer(bufs[1], dtype=dt)[arr.offset: arr.offset + n].astype(np.int64),
+            np.frombuffer(bufs[2], dtype=dt)[arr.offset: arr.offset + n].astype(np.int64))
 
 
 def _list_offsets(arr):
