@@ -19,12 +19,12 @@ STATUS = {0: "OK", 1: "InvalidInputException", 2: "IOException", 3: "NotImplemen
 TYPE_NAMES = ["INVALID", "SQLNULL", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT",
               "UINTEGER", "UBIGINT", "HUGEINT", "UHUGEINT", "FLOAT", "DOUBLE", "DECIMAL", "VARCHAR", "BLOB", "DATE",
               "TIME", "TIMESTAMP", "TIMESTAMP_S", "TIMESTAMP_MS", "TIMESTAMP_NS", "TIMESTAMP WITH TIME ZONE",
-              "INTERVAL", "UUID", "LIST", "STRUCT", "MAP", "ARRAY", "UNION"]
+              "INTERVAL", "UUID", "LIST", "STRUCT", "MAP", "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON"]
 T = {n: i for i, n in enumerate(TYPE_NAMES)}
 
 OP_NAMES = ["NONE", "COPY", "BOOL", "STRING32", "STRING64", "STRING_VIEW", "BLOB_FIXED", "LIST32", "LIST64",
             "MUL_I32", "MUL_I64", "DIV_I64", "DATE64", "INTERVAL_MUL", "INTERVAL_DIV", "INTERVAL_MONTHS",
-            "INTERVAL_MDN", "DECIMAL", "UUID", "DICT_INDEX", "VALIDITY", "REE", "UNION", "LISTVIEW32", "LISTVIEW64"]
+            "INTERVAL_MDN", "DECIMAL", "UUID", "DICT_INDEX", "VALIDITY", "REE", "UNION", "LISTVIEW32", "LISTVIEW64", "BOOL8"]
 
 
 class B2AError(Exception):

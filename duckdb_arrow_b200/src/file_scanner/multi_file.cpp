@@ -71,6 +71,14 @@ static const char *ScalarTypeName(int t) {
 		return "INTERVAL";
 	case B2A_T_UUID:
 		return "UUID";
+	case B2A_T_TIME_TZ:
+		return "TIME WITH TIME ZONE";
+	case B2A_T_BIT:
+		return "BIT";
+	case B2A_T_VARINT:
+		return "VARINT";
+	case B2A_T_JSON:
+		return "JSON";
 	default:
 		return "INVALID";
 	}
@@ -112,8 +120,9 @@ MfType TypeOfField(const Field &f) {
 		t.name = "MAP(" + TypeOfField(*entries.children[0]).name + ", " + TypeOfField(*entries.children[1]).name + ")";
 		break;
 	}
+	case B2A_T_UNION:
 	case B2A_T_STRUCT: {
-		t.name = "STRUCT(";
+		t.name = f.type_id == B2A_T_UNION ? "UNION(" : "STRUCT(";
 		for (size_t i = 0; i < f.children.size(); i++) {
 			t.name += (i ? ", " : "") + FieldName(f.children[i]->name) + " " + TypeOfField(*f.children[i]).name;
 		}

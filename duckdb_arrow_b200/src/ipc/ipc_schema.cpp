@@ -32,6 +32,7 @@ int TypeWidth(int t) {
 	case B2A_T_TIMESTAMP_MS:
 	case B2A_T_TIMESTAMP_NS:
 	case B2A_T_TIMESTAMP_TZ:
+	case B2A_T_TIME_TZ:
 		return 8;
 	case B2A_T_HUGEINT:
 	case B2A_T_UHUGEINT:
@@ -86,7 +87,98 @@ static int DecimalPhysicalWidth(int width) {
 	return 16;
 }
 
+static void MapStorageToDuckDB(Field &f);
+
+// value of a string member of a flat JSON object ('{"type_name":"hugeint","vendor_name":"DuckDB"}'); "" when absent
+static std::string JsonMember(const std::string &json, const std::string &key) {
+	const std::string needle = "\"" + key + "\"";
+	size_t p = json.find(needle);
+	if (p == std::string::npos) {
+		return std::string();
+	}
+	p = json.find(':', p + needle.size());
+	if (p == std::string::npos) {
+		return std::string();
+	}
+	p = json.find('"', p);
+	if (p == std::string::npos) {
+		return std::string();
+	}
+	std::string out;
+	for (p++; p < json.size() && json[p] != '"'; p++) {
+		if (json[p] == '\\' && p + 1 < json.size()) {
+			p++;
+		}
+		out += json[p];
+	}
+	return out;
+}
+
+static const char *IndexFormat(int type_id) {
+	switch (type_id) {
+	case B2A_T_TINYINT: return "c";
+	case B2A_T_SMALLINT: return "s";
+	case B2A_T_INTEGER: return "i";
+	case B2A_T_BIGINT: return "l";
+	case B2A_T_UTINYINT: return "C";
+	case B2A_T_USMALLINT: return "S";
+	case B2A_T_UINTEGER: return "I";
+	default: return "L";
+	}
+}
+
+// ArrowType::GetTypeFromSchema (arrow_duck_schema.cpp:372-386) + the default registrations
+// (arrow_type_extension.cpp:366-390): a field with ARROW:extension:name whose {name, vendor, type, format} — or, for the
+// 1:n types json / bit / varint, {name, vendor, type} — is registered gets the extension's type; anything else keeps the
+// storage type.  For dictionary-encoded fields the reference looks the extension up with the INDEX format.
+static void ApplyExtension(Field &f) {
+	const std::string name = MetaValue(f, "ARROW:extension:name");
+	if (name.empty()) {
+		return;
+	}
+	const std::string meta = MetaValue(f, "ARROW:extension:metadata");
+	const std::string vendor = JsonMember(meta, "vendor_name"), type_name = JsonMember(meta, "type_name");
+	const std::string fmt = f.dict_id >= 0 ? IndexFormat(f.index_type_id) : f.format;
+	const bool duck = name == "arrow.opaque" && vendor == "DuckDB";
+	if (name == "arrow.json" && vendor.empty() && type_name.empty()) {
+		if (fmt != "u" && fmt != "U" && fmt != "vu") {
+			throw Error(B2A_EINVAL, "Arrow extension type \"" + fmt + "\" not supported for arrow.json");
+		}
+		f.type_id = B2A_T_JSON;
+		return;
+	}
+	if (duck && (type_name == "bit" || type_name == "varint")) {
+		if (fmt != "z" && fmt != "Z") {
+			throw Error(B2A_EINVAL, "Arrow extension type \"" + fmt + "\" not supported for " +
+			                            (type_name == "bit" ? "BIT type" : "Varint"));
+		}
+		f.type_id = type_name == "bit" ? B2A_T_BIT : B2A_T_VARINT;
+		return;
+	}
+	if (f.dict_id >= 0) {
+		return; // the 1:1 extensions are registered under their storage format, which an index format never matches
+	}
+	if (name == "arrow.uuid" && vendor.empty() && type_name.empty() && fmt == "w:16") {
+		f.type_id = B2A_T_UUID; // conversion: UUIDConversion, arrow_conversion.cpp:480-495
+		f.op = B2A_OP_UUID;
+		f.src_width = 16;
+		f.out_width = 16;
+	} else if (name == "arrow.bool8" && vendor.empty() && type_name.empty() && fmt == "c") {
+		f.type_id = B2A_T_BOOLEAN; // storage converted as TINYINT, then ArrowBool8::ArrowToDuck (:344-350)
+		f.op = B2A_OP_BOOL8;
+	} else if (duck && (type_name == "hugeint" || type_name == "uhugeint") && fmt == "w:16") {
+		SetCopy(f, type_name == "hugeint" ? B2A_T_HUGEINT : B2A_T_UHUGEINT); // DirectConversion, :902-911
+	} else if (duck && type_name == "time_tz" && fmt == "w:8") {
+		SetCopy(f, B2A_T_TIME_TZ);
+	}
+}
+
 void MapFieldToDuckDB(Field &f) {
+	MapStorageToDuckDB(f);
+	ApplyExtension(f);
+}
+
+static void MapStorageToDuckDB(Field &f) {
 	// `f.format` and the tag-specific attributes (param, decimal_*, src_width) are set by the parser
 	const std::string &fmt = f.format;
 	f.op = B2A_OP_NONE;
@@ -159,11 +251,6 @@ void MapFieldToDuckDB(Field &f) {
 		f.out_width = 16;
 		f.src_width = static_cast<int>(f.param);
 		f.n_buffers = 2;
-		if (MetaValue(f, "ARROW:extension:name") == "arrow.uuid" && f.param == 16) {
-			f.type_id = B2A_T_UUID; // arrow_type_extension.cpp:366-390 (arrow.uuid), conversion :480-495
-			f.op = B2A_OP_UUID;
-			f.src_width = 16;
-		}
 	} else if (fmt == "tsn:") {
 		SetCopy(f, B2A_T_TIMESTAMP_NS);
 	} else if (fmt == "tsu:") {

@@ -1038,6 +1038,27 @@ __device__ __forceinline__ void op_listview(const b2a_task &t, const uint8_t *__
 	}
 }
 
+// arrow.bool8 (ArrowBool8::ArrowToDuck, arrow_type_extension.cpp:344-350): result[i] = (bool)source[i], i.e. 1 for
+// every non-zero int8.  Eight rows per 64-bit word when both sides are 8-byte aligned.
+__device__ __forceinline__ void op_bool8(const b2a_task &t, const uint8_t *__restrict__ image, uint8_t *__restrict__ out,
+                                         uint64_t row0, uint64_t nrows) {
+	const uint8_t *src = image + t.src + row0;
+	uint8_t *dst = out + t.dst + row0;
+	uint64_t done = 0;
+	if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 7u) == 0) {
+		const uint64_t words = nrows / 8;
+		for (uint64_t w = threadIdx.x; w < words; w += kThreads) {
+			const uint64_t v = __ldg(reinterpret_cast<const uint64_t *>(src) + w);
+			const uint64_t nz = (((v & 0x7F7F7F7F7F7F7F7Full) + 0x7F7F7F7F7F7F7F7Full) | v) >> 7;
+			reinterpret_cast<uint64_t *>(dst)[w] = nz & 0x0101010101010101ull;
+		}
+		done = words * 8;
+	}
+	for (uint64_t i = done + threadIdx.x; i < nrows; i += kThreads) {
+		dst[i] = src[i] != 0;
+	}
+}
+
 // ------------------------------------------------------------------------------------------------
 // the one kernel: persistent CTAs stride over the tile table
 // ------------------------------------------------------------------------------------------------
@@ -1212,6 +1233,8 @@ __global__ void __launch_bounds__(kThreads)
 			op_ree(t, image, out, row0, nrows);
 		} else if (t.op == B2A_OP_UNION) {
 			op_union(t, image, out, row0, nrows, variadic, err);
+		} else if (t.op == B2A_OP_BOOL8) {
+			op_bool8(t, image, out, row0, nrows);
 		} else if (t.op == B2A_OP_LISTVIEW32) {
 			op_listview<uint32_t>(t, image, out, row0, nrows, err);
 		} else if (t.op == B2A_OP_LISTVIEW64) {

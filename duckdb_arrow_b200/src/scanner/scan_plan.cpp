@@ -470,7 +470,7 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		t.src = bufs[1].offset;
 		t.src2 = bufs[2].offset;
 		t.src2_len = bufs[2].length;
-		if (f.type_id == B2A_T_BLOB) {
+		if (f.type_id == B2A_T_BLOB || f.type_id == B2A_T_BIT || f.type_id == B2A_T_VARINT) {
 			t.flags |= B2A_TASK_F_BLOB;
 		}
 		t.dst = slot.data_off = Alloc(L * 16);
@@ -591,6 +591,11 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		t.dst = slot.data_off = Alloc(L * dw);
 		Touch(t.src, L * sw);
 		algorithmic_out += L * dw;
+		if (f.op == B2A_OP_BOOL8) { // rarely used: lives in the second-launch kernel, not in the hot one's switch
+			t.flags |= B2A_TASK_F_PHASE2;
+			phase2_pending.push_back(t);
+			break;
+		}
 		AddTask(t, 16 * sw, dw);
 		break;
 	}
@@ -737,7 +742,7 @@ void ScanPlan::Build(const Reader &reader, uint64_t lo, uint64_t hi) {
 	// tasks that read decoded vectors (REE gathers) go last: they are launched after everything else has run
 	phase2_tile0 = next_tile;
 	for (auto &g : phase2_pending) {
-		AddTask(g, 0, g.dst_width);
+		AddTask(g, 16 * static_cast<uint64_t>(g.op == B2A_OP_BOOL8 ? 1 : 0), g.dst_width);
 	}
 	phase2_pending.clear();
 	// the popcount cells live in one region at the end of the arena (zeroed before every decode)

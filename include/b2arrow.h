@@ -80,8 +80,13 @@ typedef enum b2a_type_id {
 	B2A_T_STRUCT,
 	B2A_T_MAP,
 	B2A_T_ARRAY,
-	B2A_T_UNION /* sparse union (arrow_duck_schema.cpp:235-259): a STRUCT-like node whose OWN data is the UTINYINT tag
+	B2A_T_UNION, /* sparse union (arrow_duck_schema.cpp:235-259): a STRUCT-like node whose OWN data is the UTINYINT tag
 	               per row (DuckDB's UNION = STRUCT{tag, members...}); children = the members */
+	/* Arrow extension types registered by default (duckdb/src/common/arrow/arrow_type_extension.cpp:366-390) */
+	B2A_T_TIME_TZ, /* arrow.opaque {DuckDB, time_tz} over w:8: dtime_tz_t bits, copied */
+	B2A_T_BIT,     /* arrow.opaque {DuckDB, bit} over z / Z: string_t like BLOB */
+	B2A_T_VARINT,  /* arrow.opaque {DuckDB, varint} over z / Z */
+	B2A_T_JSON     /* arrow.json over u / U / vu: VARCHAR with the JSON alias */
 } b2a_type_id;
 
 /* Conversion op of one field = which kernel body runs for its value buffer(s). */
@@ -112,7 +117,8 @@ typedef enum b2a_op {
 	B2A_OP_UNION,           /* sparse UNION, :1173-1221: tag bytes, the union's mask and the members' masks from the
 	                           type_ids buffer and the members' own validity */
 	B2A_OP_LISTVIEW32,      /* ConvertArrowListViewOffsetsTemplated, :166-203 (+vl): offsets + sizes buffers */
-	B2A_OP_LISTVIEW64       /* +vL */
+	B2A_OP_LISTVIEW64,      /* +vL */
+	B2A_OP_BOOL8            /* arrow.bool8 over int8: ArrowBool8::ArrowToDuck, arrow_type_extension.cpp:344-350 (v != 0) */
 } b2a_op;
 
 /* One node of the schema tree, flattened in pre-order (the order of RecordBatch.nodes). */

@@ -98,6 +98,14 @@ LogicalType B2AFileScan::TypeOf(uint32_t flat) const {
 		return LogicalType::INTERVAL;
 	case B2A_T_UUID:
 		return LogicalType::UUID;
+	case B2A_T_TIME_TZ:
+		return LogicalType::TIME_TZ;
+	case B2A_T_BIT:
+		return LogicalType::BIT;
+	case B2A_T_VARINT:
+		return LogicalType::VARINT;
+	case B2A_T_JSON:
+		return LogicalType::JSON();
 	case B2A_T_LIST:
 		return LogicalType::LIST(TypeOf(NumericCast<uint32_t>(f.first_child)));
 	case B2A_T_ARRAY:

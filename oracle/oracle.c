@@ -588,6 +588,16 @@ static int ColumnArrowToDuckDB(OState *st, OVector *vector, const OArray *array,
 		vector->is_constant_null = 1; /* vector.Reference(Value()) */
 		break;
 	case O_BOOLEAN: { /* :869-891 */
+		if (type->bool8) {
+			/* :851-860 extension with arrow_to_duckdb: the storage is converted into a TINYINT vector (DirectConversion),
+			 * then ArrowBool8::ArrowToDuck (arrow_type_extension.cpp:344-350): result_ptr[i] = source_ptr[i] (int8 -> bool) */
+			idx_t off = GetEffectiveOffset(array, po, st, nested_offset);
+			const int8_t *source_ptr = (const int8_t *)array->buffers[1] + off;
+			for (idx_t i = 0; i < size; i++) {
+				vector->data[i] = source_ptr[i] != 0;
+			}
+			break;
+		}
 		idx_t effective_offset = GetEffectiveOffset(array, po, st, nested_offset);
 		const uint8_t *src_ptr = (const uint8_t *)array->buffers[1] + effective_offset / 8;
 		uint8_t *tgt_ptr = vector->data;
@@ -605,12 +615,13 @@ static int ColumnArrowToDuckDB(OState *st, OVector *vector, const OArray *array,
 	}
 	case O_TINYINT: case O_SMALLINT: case O_INTEGER: case O_FLOAT: case O_DOUBLE: case O_UTINYINT: case O_USMALLINT:
 	case O_UINTEGER: case O_UBIGINT: case O_BIGINT: case O_HUGEINT: case O_UHUGEINT: case O_TIMESTAMP:
-	case O_TIMESTAMP_SEC: case O_TIMESTAMP_MS: case O_TIMESTAMP_NS: /* :892-911 */
+	case O_TIMESTAMP_SEC: case O_TIMESTAMP_MS: case O_TIMESTAMP_NS: case O_TIME_TZ: /* :892-911 */
 		DirectConversion(vector, array, st, nested_offset, parent_offset, size);
 		break;
 	case O_UUID:
 		UUIDConversion(vector, array, st, nested_offset, po, size);
 		break;
+	case O_JSON: /* LogicalType::JSON() is VARCHAR with an alias */
 	case O_VARCHAR: { /* :915-942 */
 		idx_t off = GetEffectiveOffset(array, po, st, nested_offset);
 		switch (type->size_type) {
@@ -737,6 +748,8 @@ static int ColumnArrowToDuckDB(OState *st, OVector *vector, const OArray *array,
 	case O_DECIMAL: /* :1078-1108 */
 		TRY(ConvertDecimal(st, vector, array, size, nested_offset, parent_offset, type));
 		break;
+	case O_BIT:
+	case O_VARINT:
 	case O_BLOB: /* :1109-1115 */
 		TRY(ArrowToDuckDBBlob(st, vector, array, size, type, nested_offset, po));
 		break;
@@ -1264,7 +1277,8 @@ int oracle_validate_full(const OArray *array, const OType *type) {
 		vt.has_dictionary = 0;
 		return array->dictionary ? oracle_validate_full(array->dictionary, &vt) : 0;
 	}
-	int is_var = (type->id == O_VARCHAR || type->id == O_BLOB) &&
+	int is_var = (type->id == O_VARCHAR || type->id == O_BLOB || type->id == O_JSON || type->id == O_BIT ||
+	              type->id == O_VARINT) &&
 	             (type->size_type == O_SIZE_NORMAL || type->size_type == O_SIZE_SUPER);
 	int is_list = type->id == O_LIST || type->id == O_MAP;
 	if ((is_var || (is_list && !type->list_view)) && array->length > 0 && array->n_buffers > 1 && array->buffers[1]) {

@@ -31,7 +31,7 @@ enum {
 	O_INVALID = 0, O_SQLNULL, O_BOOLEAN, O_TINYINT, O_SMALLINT, O_INTEGER, O_BIGINT, O_UTINYINT, O_USMALLINT,
 	O_UINTEGER, O_UBIGINT, O_HUGEINT, O_UHUGEINT, O_FLOAT, O_DOUBLE, O_DECIMAL, O_VARCHAR, O_BLOB, O_DATE, O_TIME,
 	O_TIMESTAMP, O_TIMESTAMP_SEC, O_TIMESTAMP_MS, O_TIMESTAMP_NS, O_TIMESTAMP_TZ, O_INTERVAL, O_UUID, O_LIST,
-	O_STRUCT, O_MAP, O_ARRAY, O_UNION
+	O_STRUCT, O_MAP, O_ARRAY, O_UNION, O_TIME_TZ, O_BIT, O_VARINT, O_JSON
 };
 
 /* ArrowVariableSizeType (duckdb/src/include/duckdb/function/table/arrow/enum/arrow_variable_size_type.hpp) */
@@ -52,6 +52,7 @@ typedef struct OType {
 	struct OType **children;
 	/* O_UNION (sparse): width 1 = the UTINYINT tag child of DuckDB's STRUCT{tag, members...}; children = the members */
 	int32_t run_end_encoded; /* 1: children = {run_ends type, values type}; id / width are those of the values */
+	int32_t bool8;           /* O_BOOLEAN only: arrow.bool8 — storage converted as TINYINT, then ArrowBool8::ArrowToDuck */
 	int32_t list_view;       /* O_LIST only: ArrowListInfo::IsView() — buffers = validity, offsets, sizes */
 } OType;
 

@@ -19,12 +19,12 @@ T = {n: i for i, n in enumerate(
     ["INVALID", "SQLNULL", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT", "UINTEGER",
      "UBIGINT", "HUGEINT", "UHUGEINT", "FLOAT", "DOUBLE", "DECIMAL", "VARCHAR", "BLOB", "DATE", "TIME", "TIMESTAMP",
      "TIMESTAMP_SEC", "TIMESTAMP_MS", "TIMESTAMP_NS", "TIMESTAMP_TZ", "INTERVAL", "UUID", "LIST", "STRUCT", "MAP",
-     "ARRAY", "UNION"])}
+     "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON"])}
 WIDTH = {"BOOLEAN": 1, "TINYINT": 1, "UTINYINT": 1, "SMALLINT": 2, "USMALLINT": 2, "INTEGER": 4, "UINTEGER": 4,
          "FLOAT": 4, "DATE": 4, "BIGINT": 8, "UBIGINT": 8, "DOUBLE": 8, "TIME": 8, "TIMESTAMP": 8, "TIMESTAMP_SEC": 8,
          "TIMESTAMP_MS": 8, "TIMESTAMP_NS": 8, "TIMESTAMP_TZ": 8, "HUGEINT": 16, "UHUGEINT": 16, "UUID": 16,
          "INTERVAL": 16, "VARCHAR": 16, "BLOB": 16, "LIST": 16, "MAP": 16, "SQLNULL": 0, "STRUCT": 0, "ARRAY": 0, "DECIMAL": 0,
-         "UNION": 1}
+         "UNION": 1, "TIME_TZ": 8, "BIT": 16, "VARINT": 16, "JSON": 16}
 SIZE_NORMAL, SIZE_SUPER, SIZE_FIXED, SIZE_VIEW = 0, 1, 2, 3
 DT = {"ms": 0, "us": 1, "ns": 2, "s": 3, "days": 4, "months": 5, "mdn": 6}
 
@@ -36,7 +36,8 @@ class OType(C.Structure):
 OType._fields_ = [("id", C.c_int32), ("width", C.c_int32), ("size_type", C.c_int32), ("datetime", C.c_int32),
                   ("bit_width", C.c_int32), ("index_type", C.c_int32), ("fixed_size", C.c_int64),
                   ("n_children", C.c_int32), ("has_dictionary", C.c_int32), ("children", C.POINTER(C.POINTER(OType))),
-                  ("run_end_encoded", C.c_int32), ("list_view", C.c_int32)]
+                  ("run_end_encoded", C.c_int32), ("bool8", C.c_int32),
+                  ("list_view", C.c_int32)]
 
 
 class ArrowArray(C.Structure):  # Arrow C data interface; OArray in oracle.h is its prefix
@@ -137,10 +138,35 @@ def make_type(t: pa.DataType) -> OType:
         inner.run_end_encoded = 1
         return inner
     if isinstance(t, pa.BaseExtensionType):
-        if getattr(t, "extension_name", "") == "arrow.uuid":
+        # ArrowType::GetTypeFromSchema (arrow_duck_schema.cpp:372-386) + the default registrations
+        # (arrow_type_extension.cpp:366-390)
+        name, st = getattr(t, "extension_name", ""), t.storage_type
+        vendor, type_name = getattr(t, "vendor_name", ""), getattr(t, "type_name", "")
+        inner = make_type(st)
+        if name == "arrow.uuid" and st == pa.binary(16):
             simple("UUID")
             return o
-        return make_type(t.storage_type)
+        if name == "arrow.bool8" and st == pa.int8():
+            simple("BOOLEAN", bool8=1)
+            return o
+        if name == "arrow.json":
+            if not (pa.types.is_string(st) or pa.types.is_large_string(st) or pa.types.is_string_view(st)):
+                raise OracleError(3, f'Arrow extension type "{st}" not supported for arrow.json')
+            inner.id = T["JSON"]
+            return inner
+        if name == "arrow.opaque" and vendor == "DuckDB":
+            if type_name in ("hugeint", "uhugeint") and st == pa.binary(16):
+                simple(type_name.upper())
+                return o
+            if type_name == "time_tz" and st == pa.binary(8):
+                simple("TIME_TZ")
+                return o
+            if type_name in ("bit", "varint"):
+                if not (pa.types.is_binary(st) or pa.types.is_large_binary(st)):
+                    raise OracleError(3, f'Arrow extension type "{st}" not supported for {type_name}')
+                inner.id = T[type_name.upper()]
+                return inner
+        return inner
     if pa.types.is_null(t):
         simple("SQLNULL")
     elif pa.types.is_boolean(t):

@@ -84,7 +84,7 @@ def compare_column(cv, slab: O.Slab, arr: pa.Array, path: str = "col", lo: int =
 def compare_values(cv, slab, arr, path, lo, hi, ftype):
     n = hi - lo
     ovalid = slab.valid[:n]
-    if ftype in ("VARCHAR", "BLOB"):
+    if ftype in ("VARCHAR", "BLOB", "JSON", "BIT", "VARINT"):
         base = cv.ds.ptr_origin + int(cv.co.chars_off)
         plen, pin, prel = _string_canon(cv.data[lo:hi], base)
         olen, oin, orel = _string_canon(slab.data[:n], _char_base(arr))
