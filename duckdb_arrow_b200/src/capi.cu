@@ -8,6 +8,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -545,6 +547,8 @@ int b2a_scan_num_chunks(b2a_scan *s, uint64_t *n_chunks) {
 struct HostPipe {
 	cudaStream_t in = nullptr, compute = nullptr, out = nullptr;
 	std::vector<cudaEvent_t> ev_in, ev_c;
+	std::vector<cudaEvent_t> ev_out; // B2A_PIPE_TRACE only
+	cudaEvent_t ev_start = nullptr;
 	uint8_t *d_out = nullptr;
 	uint64_t d_out_bytes = 0;
 };
@@ -590,12 +594,23 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	if (n_slices > n_batches) {
 		n_slices = static_cast<uint32_t>(n_batches ? n_batches : 1);
 	}
+	static const bool trace = getenv("B2A_PIPE_TRACE") != nullptr; // per-slice timeline on stderr (experiments)
 	while (hp.ev_in.size() < n_slices + 1) {
-		cudaEvent_t a, b;
-		CUDA_OK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
-		CUDA_OK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+		cudaEvent_t a, b, c;
+		CUDA_OK(cudaEventCreateWithFlags(&a, trace ? cudaEventDefault : cudaEventDisableTiming));
+		CUDA_OK(cudaEventCreateWithFlags(&b, trace ? cudaEventDefault : cudaEventDisableTiming));
 		hp.ev_in.push_back(a);
 		hp.ev_c.push_back(b);
+		if (trace) {
+			CUDA_OK(cudaEventCreate(&c));
+			hp.ev_out.push_back(c);
+		}
+	}
+	if (trace) {
+		if (!hp.ev_start) {
+			CUDA_OK(cudaEventCreate(&hp.ev_start));
+		}
+		CUDA_OK(cudaEventRecord(hp.ev_start, hp.in));
 	}
 	const uint8_t *h_image = s->r->reader.Image();
 	uint8_t *h_out = static_cast<uint8_t *>(h_out_pinned);
@@ -647,6 +662,9 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		if (o1 > o0 && !has_phase2) {
 			CUDA_OK(cudaMemcpyAsync(h_out + o0, hp.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, hp.out));
 		}
+		if (trace) {
+			CUDA_OK(cudaEventRecord(hp.ev_out[sl], hp.out));
+		}
 	}
 	// dictionaries (decoded once per scan) + the popcount cells live after the last batch
 	const uint32_t tail_tile0 = p.batch_tile0.empty() ? 0 : p.batch_tile0.back();
@@ -695,6 +713,16 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		                        hp.out));
 	}
 	CUDA_OK(cudaStreamSynchronize(hp.out));
+	if (trace) {
+		CUDA_OK(cudaStreamSynchronize(hp.compute));
+		for (uint32_t sl = 0; sl < n_slices; sl++) {
+			float a = 0, b = 0, c = 0;
+			cudaEventElapsedTime(&a, hp.ev_start, hp.ev_in[sl]);
+			cudaEventElapsedTime(&b, hp.ev_start, hp.ev_c[sl]);
+			cudaEventElapsedTime(&c, hp.ev_start, hp.ev_out[sl]);
+			fprintf(stderr, "[b2a pipe] slice %2u: h2d done %7.2f ms, decode done %7.2f ms, d2h done %7.2f ms\n", sl, a, b, c);
+		}
+	}
 	return b2a_scan_finish(s, hp.compute);
 }
 
