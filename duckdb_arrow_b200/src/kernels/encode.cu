@@ -580,23 +580,44 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 	uint64_t window;
 	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
 	const uint64_t rel0 = block_exclusive_scan(sum, &window);
-	// ---- offsets: out[i + 1] = running sum through row i; out[0] = 0
+	// ---- offsets: out[i + 1] = running sum through row i; out[0] = 0.  Thread t owns the ALIGNED group of positions
+	// row0 + 4t .. row0 + 4t + 3 = {its exclusive prefix, the sums through its first three rows}: one 16-byte (int32) or
+	// two 16-byte (int64) coalesced stores instead of four scattered 4-byte ones; the sum through its fourth row is the
+	// next thread's (or the next tile's first thread's) prefix, and the owner of the last row writes out[rows] itself.
 	OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
-	if (k == 0 && threadIdx.x == 0) {
-		offs[0] = 0;
-	}
 	{
-		uint64_t run = tile_base + rel0;
+		uint64_t v[kRowsPerThread + 1];
+		v[0] = tile_base + rel0;
 #pragma unroll
 		for (int u = 0; u < kRowsPerThread; u++) {
-			const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
-			run += len[u];
-			if (i < t.rows) {
-				if (sizeof(OFF) == 4 && run > 0x7FFFFFFFull) {
-					enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
-				}
-				offs[i + 1] = static_cast<OFF>(run);
+			v[u + 1] = v[u] + len[u];
+		}
+		if (sizeof(OFF) == 4 && v[kRowsPerThread] > 0x7FFFFFFFull) {
+			enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
+		}
+		const uint64_t p0 = row0 + static_cast<uint64_t>(threadIdx.x) * kRowsPerThread;
+		OFF *o = offs + p0;
+		static_assert(kRowsPerThread == 4, "offset groups are four positions wide");
+		if (p0 + 3 <= t.rows && (reinterpret_cast<uintptr_t>(o) & 15u) == 0) {
+			if (sizeof(OFF) == 4) {
+				st16(o, make_uint4(static_cast<uint32_t>(v[0]), static_cast<uint32_t>(v[1]), static_cast<uint32_t>(v[2]),
+				                   static_cast<uint32_t>(v[3])));
+			} else {
+				st16(o, make_uint4(static_cast<uint32_t>(v[0]), static_cast<uint32_t>(v[0] >> 32),
+				                   static_cast<uint32_t>(v[1]), static_cast<uint32_t>(v[1] >> 32)));
+				st16(o + 2, make_uint4(static_cast<uint32_t>(v[2]), static_cast<uint32_t>(v[2] >> 32),
+				                       static_cast<uint32_t>(v[3]), static_cast<uint32_t>(v[3] >> 32)));
 			}
+		} else {
+#pragma unroll
+			for (int u = 0; u < kRowsPerThread; u++) {
+				if (p0 + u <= t.rows) {
+					o[u] = static_cast<OFF>(v[u]);
+				}
+			}
+		}
+		if (p0 + kRowsPerThread == t.rows) {
+			o[kRowsPerThread] = static_cast<OFF>(v[kRowsPerThread]);
 		}
 	}
 	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the character buffer up to 8 bytes
@@ -614,10 +635,147 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 		uint64_t rel = rel0;
 		if (staged) { // separate paths so that the stores compile to st.shared / st.global, not generic stores
 			uint8_t *wdst = stage + phase;
+			// ---- contiguous-heap fast path.  Vectors that come out of a scan keep their strings end to end in row order
+			// (Arrow character buffers, DuckDB string heaps filled by one append): then pointer - (offset of the string in
+			// this tile's window) is the same address for every non-inlined string, and the window is one memcpy from
+			// there — coalesced word loads instead of one word loop per string.  Inlined strings need not exist in that
+			// memory: their bytes are patched in from the string_t registers afterwards.  The copy spans first .. last
+			// non-inlined string only, and a tile qualifies only if every warp holds a non-inlined string: any run of
+			// inlined strings in between is then shorter than 256 rows x 12 B < 4 KiB, the smallest page, so every byte
+			// read lies in the page of a byte some string_t points at.
+			__shared__ unsigned long long s_base, s_lo, s_hi;
+			// (tiles that average under 8 B per row — flags, codes — rarely qualify and skip all of this)
+			const bool try_fast = window >= 8ull * B2A_ENC_STR_TILE;
+			bool fast = false;
+			if (try_fast) {
+				unsigned long long my_base = 0;
+				bool has_long = false, bad = false;
+				{
+					uint64_t r = rel0;
+	#pragma unroll
+					for (int u = 0; u < kRowsPerThread; u++) {
+						if (len[u] > 12) {
+							const unsigned long long b = ((static_cast<unsigned long long>(e[u].w) << 32) | e[u].z) - r;
+							bad = bad || (has_long && b != my_base);
+							my_base = b;
+							has_long = true;
+						}
+						r += len[u];
+					}
+				}
+				const uint32_t longs = __ballot_sync(0xffffffffu, has_long);
+				const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+				if (longs == 0) {
+					bad = true;
+				} else if (lane == static_cast<uint32_t>(__ffs(longs) - 1)) {
+					if (warp == 0) { // first non-inlined string of the tile
+						uint64_t r = rel0;
+						bool done = false;
+	#pragma unroll
+						for (int u = 0; u < kRowsPerThread; u++) {
+							if (!done && len[u] > 12) {
+								s_lo = r;
+								done = true;
+							}
+							r += len[u];
+						}
+						s_base = my_base;
+					}
+				}
+				if (longs != 0 && warp == kThreads / 32 - 1 && lane == 31u - static_cast<uint32_t>(__clz(longs))) {
+					uint64_t r = rel0, hi = 0; // end of the last non-inlined string of the tile
+	#pragma unroll
+					for (int u = 0; u < kRowsPerThread; u++) {
+						r += len[u];
+						if (len[u] > 12) {
+							hi = r;
+						}
+					}
+					s_hi = hi;
+				}
+				__syncthreads();
+				bad = bad || (has_long && my_base != s_base);
+				fast = !__syncthreads_or(bad);
+			}
+			if (fast) {
+				const uint64_t lo = s_lo, n = s_hi - lo;
+				const uint8_t *S = reinterpret_cast<const uint8_t *>(s_base) + lo;
+				uint8_t *D = wdst + lo;
+				const uint32_t head = min(n, static_cast<uint64_t>((4u - (static_cast<uint32_t>(
+				                                                            reinterpret_cast<uintptr_t>(D)) & 3u)) & 3u));
+				if (threadIdx.x < head) {
+					D[threadIdx.x] = __ldg(S + threadIdx.x);
+				}
+				const uint64_t words = (n - head) >> 2;
+				const uintptr_t sa = reinterpret_cast<uintptr_t>(S) + head;
+				const uint32_t *wp = reinterpret_cast<const uint32_t *>(sa & ~uintptr_t(3));
+				const uint32_t sh = (static_cast<uint32_t>(sa) & 3u) * 8u;
+				uint32_t *dw = reinterpret_cast<uint32_t *>(D + head);
+				// destination word j = funnel(source word j, j + 1).  Words up to the first 16-byte boundary of the
+				// SOURCE one by one, then source-aligned chunks of four words: one 16-byte load + the next chunk's first
+				// word per chunk, four chunks (80 B) in flight per thread
+				const uint64_t j0 = min(words, static_cast<uint64_t>((16u - (static_cast<uint32_t>(
+				                                                           reinterpret_cast<uintptr_t>(wp)) & 15u)) & 15u) >> 2);
+				if (threadIdx.x < j0) {
+					const uint32_t a = __ldg(wp + threadIdx.x), b = sh ? __ldg(wp + threadIdx.x + 1) : 0u;
+					dw[threadIdx.x] = __funnelshift_r(a, b, sh);
+				}
+				const uint64_t chunks = (words - j0) >> 2;
+				const uint4 *cp = reinterpret_cast<const uint4 *>(wp + j0);
+				uint32_t *cd = dw + j0;
+				constexpr uint32_t kU = 4;
+				uint64_t c = threadIdx.x;
+				for (; c + (kU - 1) * kThreads < chunks; c += kU * kThreads) {
+					uint4 v[kU];
+					uint32_t nx[kU];
 #pragma unroll
-			for (int u = 0; u < kRowsPerThread; u++) {
-				put_string_words(wdst + rel, e[u], len[u]);
-				rel += len[u];
+					for (uint32_t k = 0; k < kU; k++) {
+						v[k] = __ldg(cp + c + k * kThreads);
+						nx[k] = sh ? __ldg(reinterpret_cast<const uint32_t *>(cp + c + k * kThreads + 1)) : 0u;
+					}
+#pragma unroll
+					for (uint32_t k = 0; k < kU; k++) {
+						uint32_t *o = cd + 4 * (c + k * kThreads);
+						o[0] = __funnelshift_r(v[k].x, v[k].y, sh);
+						o[1] = __funnelshift_r(v[k].y, v[k].z, sh);
+						o[2] = __funnelshift_r(v[k].z, v[k].w, sh);
+						o[3] = __funnelshift_r(v[k].w, nx[k], sh);
+					}
+				}
+				for (; c < chunks; c += kThreads) {
+					const uint4 v = __ldg(cp + c);
+					const uint32_t nx = sh ? __ldg(reinterpret_cast<const uint32_t *>(cp + c + 1)) : 0u;
+					uint32_t *o = cd + 4 * c;
+					o[0] = __funnelshift_r(v.x, v.y, sh);
+					o[1] = __funnelshift_r(v.y, v.z, sh);
+					o[2] = __funnelshift_r(v.z, v.w, sh);
+					o[3] = __funnelshift_r(v.w, nx, sh);
+				}
+				{
+					const uint64_t j = j0 + (chunks << 2) + threadIdx.x;
+					if (j < words) {
+						const uint32_t a = __ldg(wp + j), b = sh ? __ldg(wp + j + 1) : 0u;
+						dw[j] = __funnelshift_r(a, b, sh);
+					}
+				}
+				const uint64_t tail0 = head + (words << 2);
+				if (tail0 + threadIdx.x < n) {
+					D[tail0 + threadIdx.x] = __ldg(S + tail0 + threadIdx.x);
+				}
+				__syncthreads(); // the inlined strings below overwrite bytes of the span just copied
+#pragma unroll
+				for (int u = 0; u < kRowsPerThread; u++) {
+					if (len[u] <= 12) {
+						put_string_words(wdst + rel, e[u], len[u]);
+					}
+					rel += len[u];
+				}
+			} else {
+#pragma unroll
+				for (int u = 0; u < kRowsPerThread; u++) {
+					put_string_words(wdst + rel, e[u], len[u]);
+					rel += len[u];
+				}
 			}
 		} else {
 #pragma unroll

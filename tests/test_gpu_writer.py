@@ -142,3 +142,54 @@ def test_unsupported_type_is_not_implemented(b2a):
     from duckdb_arrow_b200 import DeviceVector
     with pytest.raises(b2a.B2AError, match="Unsupported type"):
         b2a.ArrowWriter([DeviceVector("UUID", 0, None, None, name="u")], 0, device=-1)
+
+
+@pytest.mark.parametrize("layout", ["contiguous", "reversed", "displaced", "gapped"])
+def test_string_heap_layouts(b2a, cuda_device, layout):
+    """enc_string's contiguous-heap fast path (one coalesced window copy + inlined strings patched from registers)
+    against heaps that qualify, that do not, and that almost do — bodies bit-exact vs the oracle in every case."""
+    rng = np.random.default_rng(11)
+    n = 9000
+    lens = rng.integers(13, 60, n)
+    short = rng.random(n) < 0.35
+    lens[short] = rng.integers(0, 13, int(short.sum()))
+    lens[3000:3400] = rng.integers(0, 13, 400)  # whole warps of inlined strings: those tiles must take the slow path
+    vals = [None if i % 37 == 5 else "".join(chr(97 + (i + k) % 26) for k in range(int(lens[i]))) for i in range(n)]
+    table = pa.table({"s": pa.array(vals, pa.string()), "k": pa.array(range(n), pa.int32())})
+    host = table_vectors(table)
+    hv = host[0]
+    start, length = hv.str_start.copy(), hv.str_len.copy()
+    heap = hv.heap
+    if layout == "reversed":
+        order = np.arange(n)[::-1]
+    elif layout in ("displaced", "gapped"):
+        order = np.arange(n)
+    if layout != "contiguous":
+        gap = 3 if layout == "gapped" else 0
+        new_start = np.zeros(n, start.dtype)
+        pieces, pos = [], 0
+        for i in order:
+            new_start[i] = pos
+            pieces.append(heap[start[i]: start[i] + length[i]])
+            pos += int(length[i])
+            if gap and i % 500 == 499:
+                pieces.append(np.full(gap, 35, np.uint8))
+                pos += gap
+        new_heap = np.concatenate(pieces + [np.zeros(64, np.uint8)])
+        if layout == "displaced":  # one long string of an otherwise contiguous tile lives somewhere else
+            for i in (1500, 5000):
+                while length[i] <= 12:
+                    i += 1
+                new_heap = np.concatenate([new_heap, heap[start[i]: start[i] + length[i]]])
+                new_start[i] = len(new_heap) - int(length[i])
+        hv.str_start, hv.heap = new_start, new_heap
+    dev = [to_device(h) for h in host]
+    for rgs in (122_880, 2048):
+        w = b2a.ArrowWriter(dev, n, rgs)
+        stream = w.write()
+        exp = OW.serialize_batches(host, n, rgs)
+        assert w.n_batches == len(exp)
+        for i, (rows, nodes, slices, body) in enumerate(exp):
+            bi = w.batch(i)
+            assert bytes(stream[bi.body_offset: bi.body_offset + bi.body_length]) == body, (layout, rgs, i)
+        assert same_rows(ipc.open_stream(pa.py_buffer(stream)).read_all(), table)
