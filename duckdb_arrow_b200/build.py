@@ -16,6 +16,7 @@ SOURCES = [
     "ipc/ipc_reader.cpp",
     "ipc/ipc_writer.cpp",
     "scanner/scan_plan.cpp",
+    "scanner/host_stage.cpp",
     "writer/write_plan.cpp",
     "file_scanner/multi_file.cpp",
     "kernels/decode.cu",
@@ -23,6 +24,7 @@ SOURCES = [
     "kernels/encode.cu",
     "kernels/cast.cu",
     "kernels/decomp.cu",
+    "kernels/scatter.cu",
     "capi.cu",
     "capi_writer.cu",
     "capi_multifile.cu",

@@ -13,6 +13,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 
 using namespace b2a;
 
@@ -220,6 +221,7 @@ static void FreeScanDevice(b2a_scan *s) {
 		cudaFree(s->d_chunk_rows);
 		cudaFree(s->d_jobs);
 		cudaFree(s->d_job_order);
+		cudaFree(s->d_stage_pieces);
 		cudaFree(s->d_workspaces);
 		cudaFree(s->d_decomp_state);
 	}
@@ -548,6 +550,11 @@ struct HostPipe {
 	cudaStream_t in = nullptr, compute = nullptr, out = nullptr;
 	std::vector<cudaEvent_t> ev_in, ev_c;
 	std::vector<cudaEvent_t> ev_out; // B2A_PIPE_TRACE only
+	// staged uploads: ring of pinned host buffers + their device twins
+	static constexpr uint32_t kRing = 3;
+	uint8_t *h_stage[kRing] = {nullptr, nullptr, nullptr};
+	uint8_t *d_stage[kRing] = {nullptr, nullptr, nullptr};
+	uint64_t stage_bytes = 0;
 	cudaEvent_t ev_start = nullptr;
 	uint8_t *d_out = nullptr;
 	uint64_t d_out_bytes = 0;
@@ -628,19 +635,101 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	l.sm_count = s->sm_count;
 	l.lean = p.lean;
 
+	// ---- how the bytes get up: a pinned image is read by the copy engine range by range; anything else (an mmap'ed
+	// file, a pageable buffer) is packed into pinned staging buffers by host threads, one large copy per slice
+	if (s->stage_mode == 0 || (s->stage_mode == 2 && s->stage_plan.n_slices != n_slices)) {
+		cudaPointerAttributes attr;
+		const bool pinned = cudaPointerGetAttributes(&attr, h_image) == cudaSuccess &&
+		                    (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+		(void)cudaGetLastError();
+		const char *force = getenv("B2A_H2D_STAGE"); // "1": stage pinned images too, "0": never stage (experiments)
+		const bool stage = force ? force[0] == '1' : !pinned;
+		s->stage_mode = stage ? 2 : 1;
+		if (stage) {
+			s->stage_plan.Build(p, n_slices);
+			std::vector<ScatterPiece> sp;
+			sp.reserve(s->stage_plan.pieces.size());
+			for (auto &pc : s->stage_plan.pieces) {
+				sp.push_back(ScatterPiece {pc.stage, pc.dst, pc.bytes});
+			}
+			cudaFree(s->d_stage_pieces);
+			s->d_stage_pieces = nullptr;
+			if (!sp.empty()) {
+				CUDA_OK(cudaMalloc(&s->d_stage_pieces, sp.size() * sizeof(ScatterPiece)));
+				CUDA_OK(cudaMemcpy(s->d_stage_pieces, sp.data(), sp.size() * sizeof(ScatterPiece), cudaMemcpyHostToDevice));
+			}
+		}
+	}
+	const bool staged = s->stage_mode == 2 && !s->stage_plan.pieces.empty();
+	std::unique_ptr<StageWorkers> workers;
+	if (staged) {
+		const uint64_t need = (s->stage_plan.max_slice_bytes + 255) & ~uint64_t(255);
+		if (hp.stage_bytes < need) {
+			for (uint32_t k = 0; k < HostPipe::kRing; k++) {
+				cudaFreeHost(hp.h_stage[k]);
+				cudaFree(hp.d_stage[k]);
+				hp.h_stage[k] = hp.d_stage[k] = nullptr;
+			}
+			hp.stage_bytes = 0;
+			for (uint32_t k = 0; k < HostPipe::kRing; k++) {
+				CUDA_OK(cudaHostAlloc(&hp.h_stage[k], need, cudaHostAllocDefault));
+				CUDA_OK(cudaMalloc(&hp.d_stage[k], need));
+			}
+			hp.stage_bytes = need;
+		}
+		static const uint32_t n_threads = [] {
+			const char *e = getenv("B2A_STAGE_THREADS");
+			int n = e ? atoi(e) : 0;
+			if (n <= 0) {
+				const unsigned hw = std::thread::hardware_concurrency();
+				n = hw >= 16 ? 8 : (hw >= 4 ? static_cast<int>(hw / 2) : 1);
+			}
+			return static_cast<uint32_t>(n);
+		}();
+		workers.reset(new StageWorkers(s->stage_plan, h_image, hp.h_stage, HostPipe::kRing, n_threads));
+		workers->Allow(HostPipe::kRing - 1);
+	}
 	for (uint32_t sl = 0; sl < n_slices; sl++) {
 		const uint64_t b0 = n_batches * sl / n_slices, b1 = n_batches * (sl + 1) / n_slices;
 		if (b0 == b1) {
 			continue;
 		}
-		for (uint64_t b = b0; b < b1; b++) {
-			int rc = UploadRanges(s, p.batch_ranges[b], hp.in);
-			if (rc != B2A_OK) {
-				return rc;
+		if (staged) {
+			const uint32_t k = sl % HostPipe::kRing;
+			workers->WaitPacked(sl);
+			if (sl >= HostPipe::kRing) { // the device twin is free once slice sl - kRing has been scattered out of it
+				CUDA_OK(cudaStreamWaitEvent(hp.in, hp.ev_c[sl - HostPipe::kRing], 0));
+			}
+			if (s->stage_plan.slice_bytes[sl]) {
+				CUDA_OK(cudaMemcpyAsync(hp.d_stage[k], hp.h_stage[k], s->stage_plan.slice_bytes[sl], cudaMemcpyHostToDevice,
+				                        hp.in));
+			}
+		} else {
+			for (uint64_t b = b0; b < b1; b++) {
+				int rc = UploadRanges(s, p.batch_ranges[b], hp.in);
+				if (rc != B2A_OK) {
+					return rc;
+				}
 			}
 		}
 		CUDA_OK(cudaEventRecord(hp.ev_in[sl], hp.in));
 		CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_in[sl], 0));
+		if (staged) {
+			const uint32_t q0 = s->stage_plan.slice_piece0[sl], q1 = s->stage_plan.slice_piece0[sl + 1];
+			int e = LaunchScatter(s->d_stage_pieces + q0, q1 - q0, hp.d_stage[sl % HostPipe::kRing], s->d_image_owned,
+			                      s->sm_count, hp.compute);
+			if (e != 0) {
+				return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+			}
+			if (q1 > q0) {
+				s->launches++;
+			}
+			// the pinned buffer of slice sl + 1 may be refilled once slice sl + 1 - kRing has crossed the bus
+			if (sl + 1 >= HostPipe::kRing) {
+				CUDA_OK(cudaEventSynchronize(hp.ev_in[sl + 1 - HostPipe::kRing]));
+			}
+			workers->Allow(sl + 1);
+		}
 		{
 			int rc = LaunchJobs(s, p.batch_job0[b0], p.batch_job0[b1], hp.compute);
 			if (rc != B2A_OK) {

@@ -2,6 +2,8 @@
 #pragma once
 #include "b2arrow.h"
 #include "ipc/ipc_reader.hpp"
+#include "kernels/scatter.cuh"
+#include "scanner/host_stage.hpp"
 #include "scanner/scan_plan.hpp"
 
 #include <string>
@@ -35,6 +37,10 @@ struct b2a_scan {
 	void *d_workspaces = nullptr;
 	uint32_t *d_decomp_state = nullptr; // [0] job counter, [1] zstd error code
 	uint32_t n_workers = 0;
+	// host path over a pageable image (mmap'ed file): staged uploads, see scanner/host_stage.hpp
+	int stage_mode = 0; // 0 undecided, 1 direct cudaMemcpyAsync per range (pinned image), 2 staged
+	b2a::StagePlan stage_plan;
+	b2a::ScatterPiece *d_stage_pieces = nullptr;
 };
 
 namespace b2a {
