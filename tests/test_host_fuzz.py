@@ -40,3 +40,42 @@ def test_mutated_streams_never_crash(b2a):
                 bi = r.batch_info(i)
                 assert bi.body_offset + bi.body_length <= len(b)
     assert planned > 0 and rejected > 0
+
+
+def test_mutated_streams_of_the_rarer_layouts_never_crash(b2a):
+    """same contract for sparse unions, list views, run-end encoded and extension-typed columns (streams built here)"""
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+    n = 300
+    ids = pa.array(np.arange(n, dtype=np.int8) % 2)
+    union = pa.UnionArray.from_sparse(ids, [pa.array(range(n), pa.int64()), pa.array([str(i) * 3 for i in range(n)])],
+                                      ["i", "s"])
+    lens = np.arange(n, dtype=np.int32) % 4
+    offs = np.concatenate([[0], np.cumsum(lens)])[:-1].astype(np.int32)
+    lv = pa.ListViewArray.from_arrays(pa.array(offs), pa.array(lens), pa.array(range(int(lens.sum())), pa.int32()))
+    ree = pa.RunEndEncodedArray.from_arrays(pa.array([100, 200, n], pa.int32()), pa.array(["a", None, "ccc"]))
+    b8 = pa.ExtensionArray.from_storage(pa.bool8(), pa.array((np.arange(n) % 3).astype(np.int8)))
+    js = pa.ExtensionArray.from_storage(pa.json_(pa.string()), pa.array(['{"k":%d}' % i for i in range(n)]))
+    t = pa.table([union, lv, ree, b8, js], names=["u", "lv", "ree", "b8", "js"])
+    sink = pa.BufferOutputStream()
+    with ipc.new_stream(sink, t.schema) as w:
+        w.write_table(t, max_chunksize=128)
+    data = sink.getvalue().to_pybytes()
+    rng = np.random.default_rng(21)
+    planned = rejected = 0
+    for it in range(400):
+        b = bytearray(data)
+        if it % 4 == 0:
+            b = b[:int(rng.integers(0, len(b)))]
+        else:
+            for _ in range(int(rng.integers(1, 5))):
+                b[int(rng.integers(0, len(b)))] = int(rng.integers(0, 256))
+        try:
+            r = b2a.ArrowIPCReader.open_buffers([bytes(b)])
+            s = b2a.ArrowScan(r, device=-1)
+        except b2a.B2AError:
+            rejected += 1
+            continue
+        planned += 1
+        assert s.image_lo + s.image_bytes <= len(b) + 16
+    assert planned > 0 and rejected > 0
