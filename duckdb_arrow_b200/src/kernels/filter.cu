@@ -37,80 +37,120 @@ __device__ __forceinline__ bool cmp_i64(int64_t v, uint32_t cmp, int64_t c) {
 
 // chunk_col: per chunk, per predicate: {arena offset of the chunk's first value, arena offset of the chunk's first
 // validity word or B2A_NONE_OFF}
+//
+// One CTA per 2 048-row vector, 8 rows per thread (row = k * 256 + thread, k = 0..7, so that a warp reads 32 adjacent
+// values).  All values of a predicate column are requested before the first comparison (8 loads in flight per thread and
+// column; no short-circuit between predicates — the bytes are cheap, a dependent second round of loads is not), every
+// k gives one ballot, the 64 (k, warp) counts are scanned by warp 0, and the passing rows are written in ascending row
+// order: three barriers per vector.
+static constexpr int kFilterRowsPerThread = B2A_VECTOR_SIZE / kFilterThreads; // 8
+
+template <typename T>
+__device__ __forceinline__ void load_pred_values(const uint8_t *__restrict__ p, uint32_t rows, int64_t (&v)[kFilterRowsPerThread]) {
+#pragma unroll
+	for (int k = 0; k < kFilterRowsPerThread; k++) {
+		const uint32_t r = k * kFilterThreads + threadIdx.x;
+		v[k] = r < rows ? static_cast<int64_t>(__ldg(reinterpret_cast<const T *>(p) + r)) : 0;
+	}
+}
+
 __global__ void __launch_bounds__(kFilterThreads)
     b2a_filter_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
                       const uint32_t *__restrict__ chunk_rows, uint64_t n_chunks, FilterParams fp,
                       uint32_t *__restrict__ sel, uint32_t *__restrict__ count, unsigned long long *total) {
-	__shared__ uint32_t warp_counts[kFilterThreads / 32];
-	__shared__ uint32_t running;
+	constexpr int kWarps = kFilterThreads / 32;
+	__shared__ uint32_t counts[kFilterRowsPerThread * kWarps]; // (k, warp) -> passing rows, then exclusive prefix
+	__shared__ uint32_t chunk_total;
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	for (uint64_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-		const uint32_t rows = chunk_rows[chunk];
+		const uint32_t rows = __ldg(chunk_rows + chunk);
 		const uint64_t *cc = chunk_col + chunk * 2 * fp.n_preds;
 		uint32_t *csel = sel + chunk * B2A_VECTOR_SIZE;
-		if (threadIdx.x == 0) {
-			running = 0;
+		uint32_t pass = 0; // bit k: row k * 256 + thread passes
+#pragma unroll
+		for (int k = 0; k < kFilterRowsPerThread; k++) {
+			pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
 		}
-		__syncthreads();
-		for (uint32_t base = 0; base < rows; base += kFilterThreads) {
-			const uint32_t r = base + threadIdx.x;
-			bool pass = r < rows;
-			for (uint32_t p = 0; p < fp.n_preds && pass; p++) {
-				const uint64_t doff = cc[2 * p], voff = cc[2 * p + 1];
-				if (voff != B2A_NONE_OFF) {
-					uint64_t w = reinterpret_cast<const uint64_t *>(out + voff)[r >> 6];
-					pass = (w >> (r & 63)) & 1;
-				}
-				if (pass) {
-					int64_t v;
-					switch (fp.widths[p]) {
-					case 1:
-						v = reinterpret_cast<const int8_t *>(out + doff)[r];
-						break;
-					case 2:
-						v = reinterpret_cast<const int16_t *>(out + doff)[r];
-						break;
-					case 4:
-						v = reinterpret_cast<const int32_t *>(out + doff)[r];
-						break;
-					default:
-						v = reinterpret_cast<const int64_t *>(out + doff)[r];
-						break;
+		for (uint32_t p = 0; p < fp.n_preds; p++) {
+			const uint64_t doff = __ldg(cc + 2 * p), voff = __ldg(cc + 2 * p + 1);
+			int64_t v[kFilterRowsPerThread];
+			switch (fp.widths[p]) {
+			case 1:
+				load_pred_values<int8_t>(out + doff, rows, v);
+				break;
+			case 2:
+				load_pred_values<int16_t>(out + doff, rows, v);
+				break;
+			case 4:
+				load_pred_values<int32_t>(out + doff, rows, v);
+				break;
+			default:
+				load_pred_values<int64_t>(out + doff, rows, v);
+				break;
+			}
+			if (voff != B2A_NONE_OFF) {
+#pragma unroll
+				for (int k = 0; k < kFilterRowsPerThread; k++) {
+					const uint32_t r = k * kFilterThreads + threadIdx.x;
+					if (r < rows) {
+						const uint64_t w = __ldg(reinterpret_cast<const unsigned long long *>(out + voff) + (r >> 6));
+						if (!((w >> (r & 63)) & 1)) {
+							pass &= ~(1u << k);
+						}
 					}
-					pass = cmp_i64(v, fp.preds[p].cmp, fp.preds[p].constant);
 				}
 			}
-			// warp-level compaction: ballot + popc prefix
-			const uint32_t ballot = __ballot_sync(0xffffffffu, pass);
-			const uint32_t before = __popc(ballot & ((1u << lane) - 1u));
-			if (lane == 0) {
-				warp_counts[warp] = __popc(ballot);
-			}
-			__syncthreads();
-			uint32_t woff = running;
-			for (uint32_t w = 0; w < warp; w++) {
-				woff += warp_counts[w];
-			}
-			if (pass) {
-				csel[woff + before] = r;
-			}
-			__syncthreads();
-			if (threadIdx.x == 0) {
-				uint32_t s = 0;
-				for (uint32_t w = 0; w < kFilterThreads / 32; w++) {
-					s += warp_counts[w];
+			const uint32_t cmp = fp.preds[p].cmp;
+			const int64_t c = fp.preds[p].constant;
+#pragma unroll
+			for (int k = 0; k < kFilterRowsPerThread; k++) {
+				if (!cmp_i64(v[k], cmp, c)) {
+					pass &= ~(1u << k);
 				}
-				running += s;
 			}
-			__syncthreads();
 		}
-		if (threadIdx.x == 0) {
-			count[chunk] = running;
-			if (running) {
-				atomicAdd(total, static_cast<unsigned long long>(running));
+		// ---- compaction: ascending row order = k-major, then warp, then lane
+		uint32_t before[kFilterRowsPerThread];
+#pragma unroll
+		for (int k = 0; k < kFilterRowsPerThread; k++) {
+			const uint32_t ballot = __ballot_sync(0xffffffffu, (pass >> k) & 1u);
+			before[k] = __popc(ballot & ((1u << lane) - 1u));
+			if (lane == 0) {
+				counts[k * kWarps + warp] = __popc(ballot);
 			}
 		}
 		__syncthreads();
+		if (warp == 0) { // exclusive scan of the 64 counts: two per lane
+			const uint32_t a = counts[2 * lane], b = counts[2 * lane + 1];
+			uint32_t inc = a + b;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
+				if (lane >= static_cast<uint32_t>(o)) {
+					inc += n;
+				}
+			}
+			counts[2 * lane] = inc - a - b;
+			counts[2 * lane + 1] = inc - b;
+			if (lane == 31) {
+				chunk_total = inc;
+			}
+		}
+		__syncthreads();
+#pragma unroll
+		for (int k = 0; k < kFilterRowsPerThread; k++) {
+			if ((pass >> k) & 1u) {
+				csel[counts[k * kWarps + warp] + before[k]] = k * kFilterThreads + threadIdx.x;
+			}
+		}
+		if (threadIdx.x == 0) {
+			const uint32_t n = chunk_total;
+			count[chunk] = n;
+			if (n) {
+				atomicAdd(total, static_cast<unsigned long long>(n));
+			}
+		}
+		__syncthreads(); // counts / chunk_total are reused by the next vector
 	}
 }
 
@@ -140,15 +180,20 @@ __global__ void __launch_bounds__(kFilterThreads)
     b2a_sum_product_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
                            const uint32_t *__restrict__ chunk_rows, const uint32_t *__restrict__ sel,
                            const uint32_t *__restrict__ count, uint64_t n_chunks, unsigned long long *result) {
+	// one WARP per 2 048-row vector: a selective filter leaves a few rows per lane, and eight vectors per CTA keep eight
+	// independent {table entry -> count -> selection -> values} load chains in flight instead of one
 	__int128 acc = 0;
-	for (uint64_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-		const int64_t *a = reinterpret_cast<const int64_t *>(out + chunk_col[4 * chunk]);
-		const int64_t *b = reinterpret_cast<const int64_t *>(out + chunk_col[4 * chunk + 2]);
-		const uint32_t n = sel ? count[chunk] : chunk_rows[chunk];
+	const uint32_t lane = threadIdx.x & 31;
+	const uint64_t n_warps = static_cast<uint64_t>(gridDim.x) * (kFilterThreads / 32);
+	for (uint64_t chunk = static_cast<uint64_t>(blockIdx.x) * (kFilterThreads / 32) + (threadIdx.x >> 5); chunk < n_chunks;
+	     chunk += n_warps) {
+		const int64_t *a = reinterpret_cast<const int64_t *>(out + __ldg(chunk_col + 4 * chunk));
+		const int64_t *b = reinterpret_cast<const int64_t *>(out + __ldg(chunk_col + 4 * chunk + 2));
+		const uint32_t n = sel ? count[chunk] : __ldg(chunk_rows + chunk);
 		const uint32_t *csel = sel ? sel + chunk * B2A_VECTOR_SIZE : nullptr;
-		for (uint32_t k = threadIdx.x; k < n; k += kFilterThreads) {
+		for (uint32_t k = lane; k < n; k += 32) {
 			const uint32_t r = csel ? csel[k] : k;
-			acc += static_cast<__int128>(a[r]) * static_cast<__int128>(b[r]);
+			acc += static_cast<__int128>(__ldg(a + r)) * static_cast<__int128>(__ldg(b + r));
 		}
 	}
 	uint64_t lo = static_cast<uint64_t>(acc), hi = static_cast<uint64_t>(acc >> 64);
