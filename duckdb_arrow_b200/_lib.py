@@ -166,6 +166,7 @@ def _load() -> C.CDLL:
         "b2a_writer_headers": (i32, [vp, vp]),
         "b2a_writer_batch": (i32, [vp, u64, P(BatchInfo)]),
         "b2a_writer_gpu_launches": (u64, [vp]),
+        "b2a_writer_schema_message": (i32, [vp, P(vp), P(u64)]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):

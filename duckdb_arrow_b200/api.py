@@ -751,6 +751,12 @@ class ArrowWriter:
     def headers(self, h_stream: np.ndarray):
         check(lib.b2a_writer_headers(self._h, C.c_void_p(h_stream.ctypes.data)))
 
+    def schema_message(self) -> bytes:
+        """the encapsulated Schema message (host only; works without a device)"""
+        ptr, size = C.c_void_p(), C.c_uint64()
+        check(lib.b2a_writer_schema_message(self._h, C.byref(ptr), C.byref(size)))
+        return C.string_at(ptr, size.value)
+
     def batch(self, i: int) -> _lib.BatchInfo:
         bi = _lib.BatchInfo()
         check(lib.b2a_writer_batch(self._h, i, C.byref(bi)))

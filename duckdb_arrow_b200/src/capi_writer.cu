@@ -29,6 +29,7 @@ struct b2a_writer {
 	uint32_t *d_err = nullptr;
 	uint64_t launches = 0;
 	bool measured = false, finished = false;
+	bool enc_full = false; // the encode tasks hold an op of b2a_encode_kernel<true> only
 };
 
 #define W_TRY try {
@@ -142,6 +143,29 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	EncodeLaunch l;
 	l.sm_count = w->sm_count;
 	l.d_err = w->d_err;
+	// ---- UNION members: mask = union row valid AND tag == member AND member value valid, over the input rows
+	for (size_t i = 0; i < p.vecs.size(); i++) {
+		if (p.vecs[i].union_member < 0 || p.vecs[i].union_mask_ready) {
+			continue;
+		}
+		const WVec &u = p.vecs[static_cast<size_t>(p.vecs[i].union_vec)];
+		void *mask = nullptr;
+		int rc = DeviceAlloc(w, ((u.rows + 63) / 64 + 1) * 8, &mask);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+		int e = LaunchEncUnionMask(reinterpret_cast<const void *>(u.data), reinterpret_cast<const void *>(u.validity),
+		                           reinterpret_cast<const void *>(p.vecs[i].validity),
+		                           static_cast<uint32_t>(p.vecs[i].union_member), u.rows, mask, w->sm_count, st);
+		if (e != 0) {
+			return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+		}
+		if (u.rows) {
+			w->launches++;
+		}
+		p.vecs[i].validity = reinterpret_cast<uint64_t>(mask);
+		p.vecs[i].union_mask_ready = true;
+	}
 	for (;;) {
 		// ---- fixed-size lists under a selection: child selection = sel[i / k] * k + i % k
 		for (;;) {
@@ -296,6 +320,10 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	}
 	w->n_enc_tasks = static_cast<uint32_t>(tasks.size());
 	w->n_enc_tiles = static_cast<uint32_t>(tiles.size());
+	w->enc_full = false;
+	for (auto &t : tasks) {
+		w->enc_full = w->enc_full || B2A_ENC_OP_IS_RARE(t.op);
+	}
 	w->measured = true;
 	return B2A_OK;
 	W_CATCH
@@ -332,6 +360,7 @@ int b2a_writer_encode(b2a_writer *w, void *d_stream, void *cuda_stream) {
 	l.n_tasks = w->n_enc_tasks;
 	l.n_tiles = w->n_enc_tiles;
 	l.stream_out = static_cast<uint8_t *>(d_stream);
+	l.full = w->enc_full;
 	int e = LaunchEncode(l, st);
 	if (e != 0) {
 		return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)) +
@@ -437,6 +466,15 @@ int b2a_writer_batch(b2a_writer *w, uint64_t i, b2a_batch_info *out) {
 
 uint64_t b2a_writer_gpu_launches(b2a_writer *w) {
 	return w->launches;
+}
+
+int b2a_writer_schema_message(b2a_writer *w, const void **data, uint64_t *size) {
+	if (!w || !data || !size) {
+		return SetLastError(B2A_EINVAL, "writer: null argument");
+	}
+	*data = w->plan.schema_message.data();
+	*size = w->plan.schema_message.size();
+	return B2A_OK;
 }
 
 } // extern "C"

@@ -100,8 +100,25 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		empty(ArrowTypeTag::Utf8);
 		break;
 	case B2A_T_BLOB:
+	case B2A_T_BIT: // arrow_converter.cpp:268-279 without arrow_lossless_conversion: plain binary
 		empty(ArrowTypeTag::Binary);
 		break;
+	case B2A_T_UUID: // arrow_converter.cpp:172-186: a 36-character string unless arrow_lossless_conversion
+		empty(ArrowTypeTag::Utf8);
+		break;
+	case B2A_T_UNION: { // "+us:0,1,..": sparse, type id i = member i (arrow_converter.cpp:331-361)
+		std::vector<int32_t> ids(f.children.size());
+		for (size_t i = 0; i < ids.size(); i++) {
+			ids[i] = static_cast<int32_t>(i);
+		}
+		uint32_t ids_vec = b.create_struct_vector(ids.data(), ids.size(), 4, 4);
+		b.start_table();
+		b.add_scalar<int16_t>(0, 0, 0); // UnionMode::Sparse
+		b.add_offset(1, ids_vec);
+		o.tag = ArrowTypeTag::Union;
+		o.table = b.end_table();
+		break;
+	}
 	case B2A_T_DATE:
 		b.start_table();
 		b.add_scalar<int16_t>(0, DATE_DAY, DATE_MILLI);
@@ -109,6 +126,7 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		o.table = b.end_table();
 		break;
 	case B2A_T_TIME:
+	case B2A_T_TIME_TZ: // arrow_converter.cpp:202-209: the offset is dropped, "ttu"
 		b.start_table();
 		b.add_scalar<int16_t>(0, UNIT_MICRO, UNIT_MILLI);
 		b.add_scalar<int32_t>(1, 64, 32);
@@ -262,12 +280,27 @@ void ResolveArrowFormat(WriteField &f) {
 		f.format = "u";
 		break;
 	case B2A_T_BLOB:
+	case B2A_T_BIT:
 		f.format = "z";
 		break;
+	case B2A_T_UUID:
+		f.format = "u";
+		break;
+	case B2A_T_UNION: {
+		if (f.children.empty()) {
+			throw Error(B2A_EINVAL, "writer: UNION without members");
+		}
+		f.format = "+us:";
+		for (size_t i = 0; i < f.children.size(); i++) {
+			f.format += (i ? "," : "") + std::to_string(i);
+		}
+		break;
+	}
 	case B2A_T_DATE:
 		f.format = "tdD";
 		break;
 	case B2A_T_TIME:
+	case B2A_T_TIME_TZ:
 		f.format = "ttu";
 		break;
 	case B2A_T_TIMESTAMP:

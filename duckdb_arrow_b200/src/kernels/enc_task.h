@@ -17,8 +17,14 @@ enum b2a_enc_op {
 	B2A_ENC_LIST32,       /* ArrowListData<int32_t>::AppendOffsets, list_data.hpp:56-98 */
 	B2A_ENC_LIST64,
 	B2A_ENC_EXPAND_ARRAY, /* child selection of a fixed-size list under a selection (fixed_size_list_data.cpp:16-28) */
-	B2A_ENC_FILL_VALID    /* all-valid bitmap: ResizeValidity(.., 0xFF), append_data.hpp:116-119 */
+	B2A_ENC_FILL_VALID,   /* all-valid bitmap: ResizeValidity(.., 0xFF), append_data.hpp:116-119 */
+	/* ops below run in the full instantiation of b2a_encode_kernel only (rare types; keeps the common one lean) */
+	B2A_ENC_TIMETZ,       /* ArrowScalarData<int64_t, dtime_tz_t, ArrowTimeTzConverter>: bits >> 24, NULLs skipped */
+	B2A_ENC_UUID32,       /* ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>: 36 characters per valid row */
+	B2A_ENC_UNION_TAG     /* ArrowUnionData::Append, union_data.cpp:24-52: type id = tag of a valid row, else 0 */
 };
+
+#define B2A_ENC_OP_IS_RARE(op) ((op) >= B2A_ENC_TIMETZ)
 
 #define B2A_ENC_F_LAST_PAD 0x1u /* unused */
 

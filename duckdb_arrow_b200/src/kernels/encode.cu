@@ -107,6 +107,9 @@ __device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i,
 	if (t.op == B2A_ENC_STRING32 || t.op == B2A_ENC_STRING64) {
 		return e.x; // string_t.length
 	}
+	if (t.op == B2A_ENC_UUID32) {
+		return 36; // UUID::STRING_SIZE (ArrowUUIDConverter::GetLength, varchar_data.hpp:33-37); e = the hugeint_t
+	}
 	return (static_cast<uint64_t>(e.w) << 32) | e.z; // list_entry_t.length
 }
 
@@ -383,6 +386,47 @@ __device__ __forceinline__ void enc_convert(const b2a_enc_task &t, uint8_t *__re
 	}
 }
 
+// ArrowTimeTzConverter (scalar_data.hpp:54-68): dtime_tz_t keeps the time in the upper 40 bits -> int64 micros;
+// SkipNulls: NULL slots stay unwritten in the reference (0 here)
+__device__ __forceinline__ void enc_timetz(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                           uint64_t nrows) {
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		const uint64_t sr = map_row(t, i);
+		uint64_t v = 0;
+		if (src_valid(t, sr)) {
+			v = __ldg(reinterpret_cast<const unsigned long long *>(t.src) + sr) >> 24; // dtime_tz_t::OFFSET_BITS
+		}
+		reinterpret_cast<uint64_t *>(stream + t.dst)[i] = v;
+	}
+}
+
+// ArrowUnionData::Append (union_data.cpp:34-47): type id = tag of a valid union row, 0 for a NULL one
+__device__ __forceinline__ void enc_union_tag(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                              uint64_t nrows) {
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		const uint64_t sr = map_row(t, i);
+		stream[t.dst + i] = src_valid(t, sr) ? __ldg(reinterpret_cast<const uint8_t *>(t.src) + sr) : uint8_t(0);
+	}
+}
+
+// UUID::ToString (duckdb/src/common/types/uuid.cpp:70-101): the sign bit of `upper` is flipped back, 8-4-4-4-12
+// lower-case hex digits.  e = hugeint_t{u64 lower; i64 upper}.
+__device__ __forceinline__ void put_uuid(uint8_t *dst, const uint4 &e) {
+	const uint64_t upper = ((static_cast<uint64_t>(e.w) << 32) | e.z) ^ (1ull << 63);
+	const uint64_t lower = (static_cast<uint64_t>(e.y) << 32) | e.x;
+	uint32_t pos = 0;
+#pragma unroll
+	for (int b = 0; b < 16; b++) {
+		const uint32_t byte = static_cast<uint32_t>((b < 8 ? upper >> (56 - 8 * b) : lower >> (120 - 8 * b)) & 0xFF);
+		const uint32_t hi = byte >> 4, lo = byte & 15;
+		dst[pos++] = static_cast<uint8_t>(hi < 10 ? '0' + hi : 'a' + hi - 10);
+		dst[pos++] = static_cast<uint8_t>(lo < 10 ? '0' + lo : 'a' + lo - 10);
+		if (b == 3 || b == 5 || b == 7 || b == 9) {
+			dst[pos++] = '-';
+		}
+	}
+}
+
 // K13: bool bytes -> bits (ArrowBoolData::Append): the bit buffer starts all ones, a bit is cleared only for a VALID
 // false; bits past `rows` in the last byte stay 1.  One warp ballot per 32 rows.
 __device__ __forceinline__ void enc_bool(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
@@ -559,7 +603,7 @@ __device__ __forceinline__ void put_string_words(uint8_t *dst, const uint4 &e, u
 // one contiguous window of the data buffer: they are assembled in shared memory (inlined strings from registers,
 // long strings by warp-cooperative coalesced loads) and leave with aligned 16-byte stores.  Windows larger than the
 // staging area are written straight to global memory.
-template <typename OFF>
+template <typename OFF, bool UUID = false>
 __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                            uint8_t *stage, uint32_t *err) {
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
@@ -645,7 +689,7 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 			// read lies in the page of a byte some string_t points at.
 			__shared__ unsigned long long s_base, s_lo, s_hi;
 			// (tiles that average under 8 B per row — flags, codes — rarely qualify and skip all of this)
-			const bool try_fast = window >= 8ull * B2A_ENC_STR_TILE;
+			const bool try_fast = !UUID && window >= 8ull * B2A_ENC_STR_TILE;
 			bool fast = false;
 			if (try_fast) {
 				unsigned long long my_base = 0;
@@ -773,14 +817,26 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 			} else {
 #pragma unroll
 				for (int u = 0; u < kRowsPerThread; u++) {
-					put_string_words(wdst + rel, e[u], len[u]);
+					if (UUID) {
+						if (len[u]) {
+							put_uuid(wdst + rel, e[u]);
+						}
+					} else {
+						put_string_words(wdst + rel, e[u], len[u]);
+					}
 					rel += len[u];
 				}
 			}
 		} else {
 #pragma unroll
 			for (int u = 0; u < kRowsPerThread; u++) {
-				put_string(gdst + rel, e[u], len[u]);
+				if (UUID) { // (never taken: 1 024 x 36 bytes always fit the stage)
+					if (len[u]) {
+						put_uuid(gdst + rel, e[u]);
+					}
+				} else {
+					put_string(gdst + rel, e[u], len[u]);
+				}
 				rel += len[u];
 			}
 		}
@@ -860,6 +916,9 @@ __device__ __forceinline__ void enc_cp_async_wait_all() {
 static constexpr uint32_t kEncTaskVecs = sizeof(b2a_enc_task) / 16;
 static_assert(sizeof(b2a_enc_task) % 16 == 0, "b2a_enc_task is copied in 16-byte pieces");
 
+// FULL = false: the ops of the common types only (what a lineitem COPY runs); FULL = true adds the rare ones
+// (TIME_TZ, UUID -> string, UNION type ids) — kept out of the common instantiation's switch like on the decode side
+template <bool FULL>
 __global__ void __launch_bounds__(kThreads, 4)
     b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
                       uint8_t *__restrict__ stream, uint32_t *err) {
@@ -925,6 +984,15 @@ __global__ void __launch_bounds__(kThreads, 4)
 			enc_list<int64_t>(t, stream, k, err);
 			break;
 		default:
+			if (FULL) {
+				if (t.op == B2A_ENC_TIMETZ) {
+					enc_timetz(t, stream, row0, nrows);
+				} else if (t.op == B2A_ENC_UNION_TAG) {
+					enc_union_tag(t, stream, row0, nrows);
+				} else if (t.op == B2A_ENC_UUID32) {
+					enc_string<int32_t, true>(t, stream, k, stage, err);
+				}
+			}
 			break;
 		}
 		if (row0 + t.tile_rows >= t.rows) { // last tile of the task: zero padding of the main buffer up to 8 bytes
@@ -980,9 +1048,57 @@ int LaunchEncode(const EncodeLaunch &l, void *stream) {
 	if (l.n_tiles == 0) {
 		return 0;
 	}
-	const uint32_t grid = PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel), l.sm_count, l.n_tiles);
-	b2a_encode_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-	    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
+	if (l.full) {
+		const uint32_t grid =
+		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<true>), l.sm_count, l.n_tiles);
+		b2a_encode_kernel<true><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
+	} else {
+		const uint32_t grid =
+		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<false>), l.sm_count, l.n_tiles);
+		b2a_encode_kernel<false><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
+	}
+	return static_cast<int>(cudaGetLastError());
+}
+
+// one thread per input row of the UNION vector, one ballot per 32 rows -> the 32-bit halves of the member's
+// ValidityMask words: union row valid AND tag == member AND member value valid
+__global__ void __launch_bounds__(kThreads)
+    b2a_enc_union_mask_kernel(const uint8_t *__restrict__ tags, const uint64_t *__restrict__ union_valid,
+                              const uint64_t *__restrict__ member_valid, uint32_t member, uint64_t rows,
+                              uint32_t *__restrict__ out) {
+	const uint64_t padded = (rows + 63) & ~uint64_t(63);
+	for (uint64_t i = static_cast<uint64_t>(blockIdx.x) * kThreads + threadIdx.x; i < padded;
+	     i += static_cast<uint64_t>(gridDim.x) * kThreads) {
+		bool v = false;
+		if (i < rows) {
+			v = __ldg(tags + i) == member;
+			if (union_valid) {
+				v = v && ((__ldg(union_valid + (i >> 6)) >> (i & 63)) & 1);
+			}
+			if (member_valid) {
+				v = v && ((__ldg(member_valid + (i >> 6)) >> (i & 63)) & 1);
+			}
+		}
+		const uint32_t word = __ballot_sync(0xffffffffu, v);
+		if ((threadIdx.x & 31) == 0) {
+			out[i >> 5] = word;
+		}
+	}
+}
+
+int LaunchEncUnionMask(const void *tags, const void *union_valid, const void *member_valid, uint32_t member,
+                       uint64_t rows, void *out_words, int sm_count, void *stream) {
+	if (rows == 0) {
+		return 0;
+	}
+	uint64_t blocks = (rows + kThreads - 1) / kThreads;
+	const uint64_t cap = static_cast<uint64_t>(sm_count) * 8;
+	b2a_enc_union_mask_kernel<<<static_cast<uint32_t>(blocks > cap ? cap : blocks), kThreads, 0,
+	                            static_cast<cudaStream_t>(stream)>>>(
+	    static_cast<const uint8_t *>(tags), static_cast<const uint64_t *>(union_valid),
+	    static_cast<const uint64_t *>(member_valid), member, rows, static_cast<uint32_t *>(out_words));
 	return static_cast<int>(cudaGetLastError());
 }
 

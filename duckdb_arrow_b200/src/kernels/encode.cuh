@@ -15,11 +15,15 @@ struct EncodeLaunch {
 	uint8_t *stream_out = nullptr;  // device image of the IPC stream being produced
 	uint32_t *d_err = nullptr;
 	int sm_count = 148;
+	bool full = false; // some task needs an op of the full instantiation (B2A_ENC_OP_IS_RARE)
 };
 
 // each returns cudaError_t as int
 int LaunchEncMeasure(const EncodeLaunch &l, void *stream); // tile sums + per-task scan
 int LaunchEncExpand(const EncodeLaunch &l, void *stream);  // child selection vectors
 int LaunchEncode(const EncodeLaunch &l, void *stream);     // pass 2
+// member masks of a UNION vector (write_plan.hpp: WVec::union_member); out_words = uint64[ceil(rows / 64)]
+int LaunchEncUnionMask(const void *tags, const void *union_valid, const void *member_valid, uint32_t member,
+                       uint64_t rows, void *out_words, int sm_count, void *stream);
 
 } // namespace b2a

@@ -66,6 +66,25 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	case B2A_T_TIMESTAMP_TZ:
 		fixed(8);
 		break;
+	case B2A_T_TIME_TZ: // ArrowScalarData<int64_t, dtime_tz_t, ArrowTimeTzConverter>, arrow_appender.cpp:164-171
+		w.op = B2A_ENC_TIMETZ;
+		w.src_width = w.dst_width = 8;
+		w.n_buffers = 2;
+		break;
+	case B2A_T_UUID: // ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>, arrow_appender.cpp:180-191
+		w.op = B2A_ENC_UUID32;
+		w.src_width = 16;
+		w.dst_width = 4;
+		w.n_buffers = 3;
+		break;
+	case B2A_T_UNION: // ArrowUnionData, arrow_appender.cpp:276-278: one buffer (type ids), members as children
+		if (v.n_children < 1 || v.n_children > 256) {
+			throw Error(B2A_EINVAL, "writer: UNION needs 1 to 256 members");
+		}
+		w.is_union = true;
+		w.src_width = w.dst_width = 1;
+		w.n_buffers = 1;
+		break;
 	case B2A_T_HUGEINT:
 		fixed(16);
 		break;
@@ -86,6 +105,7 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		break;
 	case B2A_T_VARCHAR:
 	case B2A_T_BLOB:
+	case B2A_T_BIT: // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
 		w.op = B2A_ENC_STRING32;
 		w.src_width = 16;
 		w.dst_width = 4;
@@ -106,7 +126,7 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		throw Error(B2A_ENOTIMPL, "Unsupported type in DuckDB -> Arrow Conversion: type id " +
 		                              std::to_string(v.type_id));
 	}
-	if (w.op != B2A_ENC_NONE && v.rows > 0 && !v.data) {
+	if ((w.op != B2A_ENC_NONE || w.is_union) && v.rows > 0 && !v.data) {
 		throw Error(B2A_EINVAL, "writer: vector '" + wf.name + "' has no data pointer");
 	}
 	const int idx = static_cast<int>(vecs.size());
@@ -116,8 +136,32 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	}
 	wf.children.resize(static_cast<size_t>(v.n_children));
 	for (int c = 0; c < v.n_children; c++) {
+		if (v.type_id == B2A_T_UNION) {
+			// the appender boxes every row into a Value and SetValue()s it into fresh member vectors; what that leaves
+			// in nested members (NULLs pushed down recursively) is not restated here: flat members only
+			switch (v.children[c].type_id) {
+			case B2A_T_LIST:
+			case B2A_T_MAP:
+			case B2A_T_STRUCT:
+			case B2A_T_ARRAY:
+			case B2A_T_UNION:
+			case B2A_T_SQLNULL:
+				throw Error(B2A_ENOTIMPL, "writer: UNION member '" +
+				                              std::string(v.children[c].name ? v.children[c].name : "") +
+				                              "' has a nested or NULL type (flat members only)");
+			default:
+				break;
+			}
+			if (v.children[c].rows != v.rows) {
+				throw Error(B2A_EINVAL, "writer: UNION member shorter than the union");
+			}
+		}
 		int ci = AddVec(v.children[c], wf.children[static_cast<size_t>(c)], depth + 1);
 		vecs[static_cast<size_t>(idx)].children.push_back(ci);
+		if (v.type_id == B2A_T_UNION) {
+			vecs[static_cast<size_t>(ci)].union_vec = idx;
+			vecs[static_cast<size_t>(ci)].union_member = c;
+		}
 	}
 	if (v.type_id == B2A_T_MAP && v.n_children == 1) {
 		vecs[static_cast<size_t>(vecs[static_cast<size_t>(idx)].children[0])].no_validity_buffer = true;
@@ -173,7 +217,7 @@ int WritePlan::AddNode(int vec, uint64_t rows, uint64_t row0, uint64_t sel) {
 	std::memset(n.buf, 0, sizeof(n.buf));
 	const int idx = static_cast<int>(nodes.size());
 	nodes.push_back(n);
-	if (v.type_id == B2A_T_STRUCT) {
+	if (v.type_id == B2A_T_STRUCT || v.type_id == B2A_T_UNION) {
 		for (int c : v.children) {
 			int ci = AddNode(c, rows, row0, sel);
 			nodes[static_cast<size_t>(idx)].children.push_back(ci);
@@ -224,6 +268,12 @@ void WritePlan::Layout() {
 			WNode &n = nodes[static_cast<size_t>(ni)];
 			const WVec &v = vecs[static_cast<size_t>(n.vec)];
 			nb += static_cast<size_t>(v.n_buffers);
+			if (v.is_union) { // type ids, one byte per row; no validity buffer
+				n.buf[0] = BufferSlice {off, n.rows};
+				off += Align8(n.rows);
+				algorithmic_in += n.rows + (v.validity ? (n.rows + 7) / 8 : 0);
+				continue;
+			}
 			if (v.n_buffers >= 1) { // validity
 				uint64_t len = v.no_validity_buffer ? 0 : (n.rows + 7) / 8;
 				n.buf[0] = BufferSlice {off, len};
@@ -317,6 +367,17 @@ void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32
 		for (int ni : b.preorder) {
 			const WNode &n = nodes[static_cast<size_t>(ni)];
 			const WVec &v = vecs[static_cast<size_t>(n.vec)];
+			if (v.is_union) {
+				if (n.rows > 0) {
+					b2a_enc_task t = BaseTask(n, v);
+					t.op = B2A_ENC_UNION_TAG;
+					t.dst = b.body_offset + n.buf[0].offset;
+					t.dst_len = n.buf[0].length;
+					t.tile_rows = 1u << 16;
+					PushTask(tasks, tile_task, t, (n.rows + t.tile_rows - 1) / t.tile_rows);
+				}
+				continue;
+			}
 			if (v.n_buffers >= 1 && !v.no_validity_buffer && n.rows > 0) {
 				b2a_enc_task t = BaseTask(n, v);
 				t.op = B2A_ENC_VALIDITY;

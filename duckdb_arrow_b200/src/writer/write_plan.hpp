@@ -24,6 +24,13 @@ struct WVec {
 	uint64_t data = 0, validity = 0; // device addresses
 	uint64_t rows = 0;
 	bool no_validity_buffer = false; // the entries struct of a MAP: its validity buffer is never materialised
+	// UNION (ArrowUnionData, union_data.cpp): the node's single buffer holds the type ids (no validity buffer); a
+	// member is appended with the mask "union row valid AND tag == member AND member value valid", which
+	// b2a_writer_measure computes once per member vector (LaunchEncUnionMask) and stores in `validity`
+	bool is_union = false;
+	int union_vec = -1;    // member: index of the UNION vector it belongs to
+	int union_member = -1; // member: its tag
+	bool union_mask_ready = false;
 	std::vector<int> children;       // indices into WritePlan::vecs
 };
 
@@ -83,7 +90,8 @@ struct WritePlan {
 	               std::vector<uint32_t> &tile_task) const;
 
 	static bool IsScanOp(int op) {
-		return op == B2A_ENC_STRING32 || op == B2A_ENC_STRING64 || op == B2A_ENC_LIST32 || op == B2A_ENC_LIST64;
+		return op == B2A_ENC_STRING32 || op == B2A_ENC_STRING64 || op == B2A_ENC_LIST32 || op == B2A_ENC_LIST64 ||
+		       op == B2A_ENC_UUID32;
 	}
 	static uint64_t ScanTiles(uint64_t rows) {
 		uint64_t n = (rows + B2A_ENC_STR_TILE - 1) / B2A_ENC_STR_TILE;

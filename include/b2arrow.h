@@ -341,7 +341,8 @@ typedef struct b2a_vector {
 	int32_t type_id;          /* b2a_type_id of the DuckDB LogicalType */
 	int32_t decimal_width;    /* DECIMAL(width, scale) */
 	int32_t decimal_scale;
-	int32_t n_children;       /* STRUCT: fields; LIST / ARRAY: 1; MAP: 1 (the STRUCT(key, value) entry vector) */
+	int32_t n_children;       /* STRUCT: fields; LIST / ARRAY: 1; MAP: 1 (the STRUCT(key, value) entry vector);
+	                             UNION: the members (flat types), data = the UTINYINT tags, validity = the union's */
 	int64_t param;            /* ARRAY: list size */
 	const char *name;         /* column name / struct field name (NULL: "") */
 	const char *timezone;     /* TIMESTAMP_TZ: ClientProperties.time_zone (NULL: "UTC") */
@@ -380,6 +381,10 @@ int b2a_writer_headers(b2a_writer *w, void *h_stream);
 /* rows / meta_offset / body_offset / body_length of record batch i of the produced stream */
 int b2a_writer_batch(b2a_writer *w, uint64_t i, b2a_batch_info *out);
 uint64_t b2a_writer_gpu_launches(b2a_writer *w);
+/* The encapsulated Schema message of the stream (ArrowStreamWriter::WriteSchema, src/writer/arrow_stream_writer.cpp:55-60;
+ * types = ArrowConverter::ToArrowSchema, duckdb/src/common/arrow/arrow_converter.cpp:115-432).  Host only: available
+ * right after b2a_writer_create, also without a device.  The pointer stays valid until b2a_writer_destroy. */
+int b2a_writer_schema_message(b2a_writer *w, const void **data, uint64_t *size);
 
 #ifdef __cplusplus
 }

@@ -9,6 +9,9 @@ Restates DuckDB's ArrowAppender, one function per appender, over host vectors (t
   ArrowStructData           duckdb/src/common/arrow/appender/struct_data.cpp:17-30
   ArrowFixedSizeListData    duckdb/src/common/arrow/appender/fixed_size_list_data.cpp:16-28
   ArrowMapData              .../appender/map_data.hpp:38-64
+  ArrowTimeTzConverter      .../appender/scalar_data.hpp:54-68 (TIME_TZ -> time64[us], the offset is dropped)
+  ArrowUUIDConverter        .../appender/varchar_data.hpp:33-43 + UUID::ToString duckdb/src/common/types/uuid.cpp:70-101
+  ArrowUnionData            duckdb/src/common/arrow/appender/union_data.cpp:24-52 (flat members)
 and the body packing of the nanoarrow encoder the reference calls (ArrowIpcEncoderEncodeSimpleRecordBatch,
 src/writer/column_data_collection_serializer.cpp:86-92): buffers in pre-order, each padded with zeros to 8 bytes.
 nanoarrow is not in the reference tree (CMakeLists.txt:7-13), so the exact FILE bytes of the reference writer are
@@ -48,6 +51,21 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
     if t == "SQLNULL":  # ArrowNullData: no buffers, null_count = length
         nodes.append((n, n))
         return
+    if t == "UNION":
+        # per row: Value v = input.GetValue(row); tag = v.IsNull() ? 0 : tag(v); member[tag] gets the boxed value, every
+        # other member NULL; one buffer (type ids), null_count 0, no validity buffer (Finalize: n_buffers = 1).
+        # hv.data = the tag child of DuckDB's UNION vector (UTINYINT per row), hv.validity = the union's own mask.
+        valid_full = np.ones(hv.rows, bool) if hv.validity is None else hv.validity
+        tags_full = hv.data.view(np.uint8)
+        nodes.append((n, 0))
+        buffers.append(np.where(valid_full[idx], tags_full[idx], 0).astype(np.uint8).tobytes())
+        for m, c in enumerate(hv.children):
+            own = np.ones(c.rows, bool) if c.validity is None else c.validity
+            import copy
+            member = copy.copy(c)
+            member.validity = valid_full & (tags_full == m) & own
+            append(member, idx, nodes, buffers)
+        return
     valid = _valid(hv, idx)
     vbuf, nulls = _validity_buffer(valid)
     if getattr(hv, "_no_validity_buffer", False):
@@ -59,7 +77,21 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
         bits = np.ones(((n + 7) // 8) * 8, bool)
         bits[:n] = ~valid | data  # only a VALID false clears the bit
         buffers.append(np.packbits(bits, bitorder="little").tobytes())
-    elif t in ("VARCHAR", "BLOB"):
+    elif t == "UUID":  # 36 characters per valid row, NULL rows repeat the previous offset
+        offs = np.zeros(n + 1, np.int64)
+        np.cumsum(np.where(valid, 36, 0), out=offs[1:])
+        raw = hv.data.view(np.uint64).reshape(-1, 2)[idx]
+        chars = bytearray()
+        for (lower, upper), ok in zip(raw.tolist(), valid.tolist()):
+            if ok:
+                h = "%016x%016x" % (upper ^ (1 << 63), lower)  # the sign bit of `upper` is flipped back
+                chars += f"{h[:8]}-{h[8:12]}-{h[12:16]}-{h[16:20]}-{h[20:]}".encode()
+        buffers.append(offs.astype(np.int32).tobytes())
+        buffers.append(bytes(chars))
+    elif t == "TIME_TZ":  # dtime_tz_t: micros in the upper 40 bits (OFFSET_BITS = 24); NULL slots unwritten (0 here)
+        bits = hv.data.view(np.uint64)[idx]
+        buffers.append(np.where(valid, bits >> np.uint64(24), 0).astype(np.int64).tobytes())
+    elif t in ("VARCHAR", "BLOB", "BIT"):
         length = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
         offs = np.zeros(n + 1, np.int64)
         np.cumsum(length, out=offs[1:])

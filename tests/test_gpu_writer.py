@@ -8,9 +8,9 @@ import pyarrow.ipc as ipc
 import pytest
 
 from oracle import oracle_write as OW
-from tests_helpers import same_rows
+from tests_helpers import pylist, same_rows
 from vectors import table_vectors, to_device
-from writer_cases import nested_table, scalar_table
+from writer_cases import nested_table, rare_columns, scalar_table
 
 pytestmark = pytest.mark.gpu
 
@@ -139,9 +139,50 @@ def test_null_map_keys_are_rejected(b2a, cuda_device):
 
 
 def test_unsupported_type_is_not_implemented(b2a):
+    """UHUGEINT / VARINT have no case in SetArrowFormat without arrow_lossless_conversion (arrow_converter.cpp:115-395)"""
     from duckdb_arrow_b200 import DeviceVector
-    with pytest.raises(b2a.B2AError, match="Unsupported type"):
-        b2a.ArrowWriter([DeviceVector("UUID", 0, None, None, name="u")], 0, device=-1)
+    for t in ("UHUGEINT", "VARINT"):
+        with pytest.raises(b2a.B2AError, match="Unsupported type"):
+            b2a.ArrowWriter([DeviceVector(t, 0, None, None, name="u")], 0, device=-1)
+
+
+@pytest.mark.parametrize("rgs", [122_880, 2048, 1000])
+def test_uuid_time_tz_bit_union_bit_exact_vs_oracle(b2a, cuda_device, rgs):
+    """the appenders of b2a_encode_kernel<true>: ArrowUUIDConverter (36-character strings), ArrowTimeTzConverter,
+    BIT as binary, ArrowUnionData (type ids + members masked by tag / union validity, also below a LIST) — bodies
+    bit-exact vs the oracle, and pyarrow reads the stream back to the expected rows"""
+    n = 6000
+    cols, expected, types = rare_columns(n)
+    w = b2a.ArrowWriter([to_device(h) for h in cols], n, rgs)
+    stream = w.write()
+    exp = OW.serialize_batches(cols, n, rgs)
+    assert w.n_batches == len(exp)
+    for i, (rows, nodes, slices, body) in enumerate(exp):
+        bi = w.batch(i)
+        assert bi.rows == rows and bi.body_length == len(body)
+        got = bytes(stream[bi.body_offset: bi.body_offset + bi.body_length])
+        if got != body:
+            bad = next(k for k in range(len(body)) if got[k] != body[k])
+            which = max(j for j, (o, l) in enumerate(slices) if o <= bad)
+            raise AssertionError(f"batch {i}: body differs at byte {bad} (buffer #{which} {slices[which]})")
+    rd = ipc.open_stream(pa.py_buffer(stream))
+    assert [f.type for f in rd.schema] == types and rd.schema.names == list(expected)
+    got = rd.read_all()
+    for name, e in expected.items():
+        assert pylist(got.column(name)) == e, name
+    # FieldNodes: a union node has null_count 0 and one buffer
+    batch0 = next(iter(ipc.open_stream(pa.py_buffer(stream))))
+    assert batch0.column("u").null_count == 0
+    # and this repo's own reader decodes the union back (sparse-union read path, tests/test_union.py)
+    r = b2a.ArrowIPCReader.open_buffers([stream])
+    assert {f.name: f.format for f in r.columns}["u"] == "+us:0,1,2,3"
+
+
+def test_union_with_nested_member_is_rejected(b2a):
+    from duckdb_arrow_b200 import DeviceVector
+    m = DeviceVector("LIST", 0, None, None, [DeviceVector("INTEGER", 0, None, None, name="l")], name="m")
+    with pytest.raises(b2a.B2AError, match="flat members only"):
+        b2a.ArrowWriter([DeviceVector("UNION", 0, None, None, [m], name="u")], 0, device=-1)
 
 
 @pytest.mark.parametrize("layout", ["contiguous", "reversed", "displaced", "gapped"])

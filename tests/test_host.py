@@ -186,3 +186,46 @@ def test_plan_layout_lineitem(b2a):
     for (a, n), (b_, _) in zip(offs, offs[1:]):
         assert a + n <= b_, "output slabs overlap"
     assert s.n_chunks == sum((r.batch_info(b).rows + 2047) // 2048 for b in range(r.num_batches))
+
+
+def test_writer_schema_message_types_read_by_pyarrow(b2a):
+    """Host half of COPY ... (FORMAT ARROWS): the Schema message for every writable DuckDB type carries the Arrow type
+    ArrowConverter::ToArrowSchema gives it (duckdb/src/common/arrow/arrow_converter.cpp:115-395) — read back by pyarrow.
+    No device needed (b2a_writer_schema_message)."""
+    import pyarrow.ipc as ipc
+    from duckdb_arrow_b200 import DeviceVector as DV
+
+    def v(t, name, kids=(), **kw):
+        return DV(t, 0, None, None, list(kids), name, **kw)
+
+    cols = [
+        v("BOOLEAN", "b"), v("TINYINT", "i8"), v("USMALLINT", "u16"), v("BIGINT", "i64"), v("HUGEINT", "h"),
+        v("FLOAT", "f"), v("DOUBLE", "g"), v("DECIMAL", "d4", decimal=(4, 1)), v("DECIMAL", "d15", decimal=(15, 2)),
+        v("DECIMAL", "d38", decimal=(38, 4)), v("VARCHAR", "s"), v("BLOB", "z"), v("BIT", "bits"), v("UUID", "id"),
+        v("DATE", "dt"), v("TIME", "t"), v("TIME_TZ", "ttz"), v("TIMESTAMP", "ts"), v("TIMESTAMP_S", "ts_s"),
+        v("TIMESTAMP_MS", "ts_ms"), v("TIMESTAMP_NS", "ts_ns"),
+        v("TIMESTAMP WITH TIME ZONE", "tstz", timezone="Europe/Amsterdam"), v("INTERVAL", "iv"), v("SQLNULL", "n"),
+        v("LIST", "l", [v("INTEGER", "x")]), v("STRUCT", "st", [v("INTEGER", "a"), v("VARCHAR", "b")]),
+        v("MAP", "m", [v("STRUCT", "e", [v("VARCHAR", "k"), v("BIGINT", "v")])]),
+        v("ARRAY", "arr", [v("SMALLINT", "x")], param=3),
+        v("UNION", "u", [v("BIGINT", "num"), v("VARCHAR", "str"), v("BOOLEAN", "flag")]),
+    ]
+    w = b2a.ArrowWriter(cols, 0, kv_metadata={"k": "v"}, device=-1)
+    sch = ipc.read_schema(pa.py_buffer(w.schema_message()))
+    w.close()
+    exp = {
+        "b": pa.bool_(), "i8": pa.int8(), "u16": pa.uint16(), "i64": pa.int64(), "h": pa.decimal128(38, 0),
+        "f": pa.float32(), "g": pa.float64(), "d4": pa.decimal32(4, 1), "d15": pa.decimal64(15, 2),
+        "d38": pa.decimal128(38, 4), "s": pa.string(), "z": pa.binary(), "bits": pa.binary(), "id": pa.string(),
+        "dt": pa.date32(), "t": pa.time64("us"), "ttz": pa.time64("us"), "ts": pa.timestamp("us"),
+        "ts_s": pa.timestamp("s"), "ts_ms": pa.timestamp("ms"), "ts_ns": pa.timestamp("ns"),
+        "tstz": pa.timestamp("us", tz="Europe/Amsterdam"), "iv": pa.month_day_nano_interval(), "n": pa.null(),
+        "l": pa.list_(pa.field("l", pa.int32())), "st": pa.struct([("a", pa.int32()), ("b", pa.string())]),
+        "m": pa.map_(pa.string(), pa.int64()), "arr": pa.list_(pa.field("", pa.int16()), 3),
+        "u": pa.sparse_union([pa.field("num", pa.int64()), pa.field("str", pa.string()), pa.field("flag", pa.bool_())]),
+    }
+    assert sch.names == list(exp)
+    for name, t in exp.items():
+        assert sch.field(name).type == t, (name, sch.field(name).type)
+    assert sch.field("u").type.type_codes == [0, 1, 2] and sch.field("u").type.mode == "sparse"
+    assert sch.metadata == {b"k": b"v"}

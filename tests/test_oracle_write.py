@@ -7,9 +7,9 @@ import pyarrow as pa
 import pytest
 
 from oracle import oracle_write as OW
-from tests_helpers import same_rows
+from tests_helpers import pylist, same_rows
 from vectors import table_vectors
-from writer_cases import arrays_from_buffers, nested_table, scalar_table
+from writer_cases import arrays_from_buffers, nested_table, rare_columns, scalar_table
 
 
 def _lineitem(n):
@@ -38,6 +38,34 @@ def test_write_oracle_round_trips_through_pyarrow(case, rgs):
         exp = table.slice(row, n)
         assert same_rows(got, exp), f"{case}: batch at row {row} differs"
         row += n
+
+
+@pytest.mark.parametrize("rgs", [1000, 122_880])
+def test_write_oracle_uuid_time_tz_bit_union(rgs):
+    """UUID -> 36-character strings (checked against Python's uuid module), TIME_TZ -> time64[us], BIT -> binary, sparse
+    UNION (type ids + masked members): the oracle's buffers, reassembled by pyarrow, give the expected rows"""
+    cols, expected, types = rare_columns(3000)
+    row = 0
+    for n, nodes, slices, body in OW.serialize_batches(cols, 3000, rgs):
+        bufs = [body[o:o + l] for o, l in slices]
+        arrays = arrays_from_buffers(types, nodes, bufs)
+        for arr, (name, exp) in zip(arrays, expected.items()):
+            arr.validate(full=True)
+            assert pylist(arr) == exp[row: row + n], name
+        row += n
+    assert row == 3000
+
+
+def test_union_null_rows_get_tag_zero_and_all_members_null():
+    """union_data.cpp:34-47: a NULL union row is written as type id 0 with every member NULL at that row"""
+    from vectors import from_arrow, union_vector
+    u = union_vector(np.array([1, 1, 0]), [from_arrow(pa.array([7, 8, 9], pa.int32()), "a"),
+                                          from_arrow(pa.array(["x", None, "z"], pa.string()), "b")],
+                     np.array([True, False, True]), "u")
+    (n, nodes, slices, body), = OW.serialize_batches([u], 3, 100)
+    assert nodes == [(3, 0), (3, 2), (3, 2)]
+    assert body[slices[0][0]: slices[0][0] + 3] == bytes([1, 0, 0])
+    assert body[slices[1][0]] == 0b11111100 and body[slices[3][0]] == 0b11111001
 
 
 def test_validity_buffer_semantics():

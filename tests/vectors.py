@@ -125,6 +125,32 @@ def from_arrow(arr: pa.Array, name: str = "") -> HostVector:
     raise NotImplementedError(str(t))
 
 
+def uuid_vector(values: list, name: str = "") -> HostVector:
+    """uuid.UUID | None -> DuckDB UUID vector: hugeint_t{u64 lower; i64 upper} with the top bit of `upper` flipped
+    (UUID::FromString, duckdb/src/common/types/uuid.cpp:8-68)"""
+    n = len(values)
+    data = np.zeros((n, 2), np.uint64)
+    valid = np.array([v is not None for v in values], bool)
+    for i, v in enumerate(values):
+        if v is not None:
+            data[i, 0] = v.int & ((1 << 64) - 1)
+            data[i, 1] = (v.int >> 64) ^ (1 << 63)
+    return HostVector("UUID", n, data.view(np.uint8).reshape(-1), None if valid.all() else valid, name=name)
+
+
+def time_tz_vector(micros: np.ndarray, offset_s: np.ndarray, valid: np.ndarray | None, name: str = "") -> HostVector:
+    """dtime_tz_t(time, offset): bits = micros << 24 | (MAX_OFFSET - offset) (datetime.hpp: OFFSET_BITS = 24,
+    MAX_OFFSET = 16 * 60 * 60 - 1)"""
+    bits = (micros.astype(np.uint64) << np.uint64(24)) | (57599 - offset_s.astype(np.int64)).astype(np.uint64)
+    return HostVector("TIME_TZ", len(micros), bits.view(np.uint8).reshape(-1), valid, name=name)
+
+
+def union_vector(tags: np.ndarray, members: list[HostVector], valid: np.ndarray | None, name: str = "") -> HostVector:
+    """DuckDB UNION vector = STRUCT{tag UTINYINT, members...}; here (like on the read side) the node's own data are
+    the tags"""
+    return HostVector("UNION", len(tags), tags.astype(np.uint8), valid, members, name=name)
+
+
 def _values_offsets(arr, dtype):
     buf = arr.buffers()[1]
     if buf is None:
@@ -143,7 +169,7 @@ def to_device(hv: HostVector, device: int = 0):
     dev = f"cuda:{device}"
     keep = []
     data = None
-    if hv.type in ("VARCHAR", "BLOB"):
+    if hv.type in ("VARCHAR", "BLOB", "BIT"):
         heap = torch.from_numpy(np.concatenate([hv.heap, np.zeros(16, np.uint8)])).to(dev)
         keep.append(heap)
         rec = make_string_t(hv.str_start, hv.str_len, hv.heap, heap.data_ptr())

@@ -91,6 +91,64 @@ def nested_table(n=3000, seed=2) -> pa.Table:
     return pa.table(cols)
 
 
+def rare_columns(n=5000, seed=4):
+    """The writable types Arrow has no 1:1 array for (so they cannot come from vectors.from_arrow): UUID (written as its
+    36-character string), TIME_TZ (time64[us], offset dropped), BIT (the internal bytes as binary) and sparse UNIONs
+    with flat members -> (HostVectors, the table pyarrow must read back)"""
+    import uuid
+    from vectors import HostVector, from_arrow, time_tz_vector, union_vector, uuid_vector
+    rng = np.random.default_rng(seed)
+    raw = rng.integers(0, 256, (n, 16)).astype(np.uint8)
+    raw[0], raw[1 % n] = 0, 255
+    ids = [None if rng.random() < 0.15 else uuid.UUID(bytes=raw[i].tobytes()) for i in range(n)]
+    ids_nn = [uuid.UUID(bytes=raw[::-1][i].tobytes()) for i in range(n)]
+    micros = rng.integers(0, 86_400_000_000, n)
+    offs = rng.integers(-57599, 57600, n)
+    tz_valid = rng.random(n) >= 0.2
+    bits = from_arrow(pa.array(_nullify(rng, [bytes(rng.integers(0, 256, int(l)).astype(np.uint8))
+                                                for l in rng.integers(1, 30, n)]), pa.binary()), "bits")
+    bits_expected = pa.array([None if not v else bits.heap[s:s + l].tobytes() for v, s, l in
+                              zip(np.ones(n, bool) if bits.validity is None else bits.validity, bits.str_start,
+                                  bits.str_len)], pa.binary())
+    bits.type = "BIT"
+    # union(num BIGINT, str VARCHAR, flag BOOLEAN, d DECIMAL(4,1)): NULL union rows, NULL member values
+    tags = rng.integers(0, 4, n)
+    u_valid = rng.random(n) >= 0.1
+    words = ["", "u", "union member", "a union member longer than twelve bytes"]
+    m_num = pa.array(_nullify(rng, rng.integers(-2**40, 2**40, n).tolist()), pa.int64())
+    m_str = pa.array(_nullify(rng, [words[i] for i in rng.integers(0, len(words), n)]), pa.string())
+    m_flag = pa.array(_nullify(rng, (rng.random(n) < 0.5).tolist()), pa.bool_())
+    m_dec = pa.array(_nullify(rng, [decimal.Decimal(int(x)).scaleb(-1) for x in rng.integers(-999, 1000, n)]),
+                     pa.decimal32(4, 1))
+    members = [m_num, m_str, m_flag, m_dec]
+    names = ["num", "str", "flag", "d"]
+    union = union_vector(tags, [from_arrow(a, nm) for a, nm in zip(members, names)], u_valid, "u")
+    exp_union = [None if not u_valid[i] else members[int(tags[i])][i].as_py() for i in range(n)]
+    # the same union below a LIST (the members are appended through the list's child selection)
+    lens = rng.integers(0, 4, n)
+    l_valid = rng.random(n) >= 0.1
+    starts = np.minimum(np.cumsum(lens) - lens, max(n - 4, 0))
+    ent = np.stack([starts, lens], 1).astype(np.uint64)
+    inner = union_vector(tags, [from_arrow(a, nm) for a, nm in zip(members, names)], u_valid, "l")
+    l_union = HostVector("LIST", n, ent.view(np.uint8).reshape(-1), None if l_valid.all() else l_valid, [inner],
+                         name="l_u")
+    exp_l_union = [None if not l_valid[i] else exp_union[int(starts[i]): int(starts[i] + lens[i])] for i in range(n)]
+    cols = [uuid_vector(ids, "id"), uuid_vector(ids_nn, "id_nn"),
+            time_tz_vector(micros, offs, None if tz_valid.all() else tz_valid, "ttz"), bits, union, l_union]
+    expected = {
+        "id": [None if v is None else str(v) for v in ids],
+        "id_nn": [str(v) for v in ids_nn],
+        "ttz": pa.array(np.where(tz_valid, micros, 0), pa.int64(), mask=~tz_valid).cast(pa.time64("us")).to_pylist(),
+        "bits": bits_expected.to_pylist(),
+        "u": exp_union,
+        "l_u": exp_l_union,
+    }
+    types = [pa.string(), pa.string(), pa.time64("us"), pa.binary(),
+             pa.sparse_union([pa.field(nm, a.type) for a, nm in zip(members, names)]),
+             pa.list_(pa.sparse_union([pa.field(nm, a.type) for a, nm in zip(members, names)]))]
+    return cols, expected, types
+
+
 def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[bytes]) -> list[pa.Array]:
     """Rebuild pyarrow arrays from pre-order (length, null_count) nodes and buffers (validity first)."""
     ni, bi = [0], [0]
@@ -105,6 +163,10 @@ def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[byt
         ni[0] += 1
         if pa.types.is_null(t):
             return pa.nulls(length)
+        if pa.types.is_union(t):  # sparse, V5: type ids only
+            ids = take_buf() or pa.py_buffer(b"")
+            kids = [build(t.field(i).type) for i in range(t.num_fields)]
+            return pa.UnionArray.from_buffers(t, length, [None, ids], children=kids)
         validity = take_buf()
         if pa.types.is_struct(t):
             kids = [build(t.field(i).type) for i in range(t.num_fields)]
