@@ -6,6 +6,9 @@
 
 #include <cuda_runtime.h>
 
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -30,6 +33,23 @@ struct b2a_writer {
 	uint64_t launches = 0;
 	bool measured = false, finished = false;
 	bool enc_full = false; // the encode tasks hold an op of b2a_encode_kernel<true> only
+};
+
+// B2A_WRITER_TRACE=1: wall-clock phases of b2a_writer_measure on stderr (where pass 1's milliseconds go)
+struct PhaseTrace {
+	bool on;
+	std::chrono::steady_clock::time_point t0;
+	PhaseTrace() : on(std::getenv("B2A_WRITER_TRACE") != nullptr), t0(std::chrono::steady_clock::now()) {
+	}
+	void Mark(const char *what) {
+		if (!on) {
+			return;
+		}
+		auto t1 = std::chrono::steady_clock::now();
+		std::fprintf(stderr, "[b2a writer] %-28s %8.3f ms\n", what,
+		             std::chrono::duration<double, std::milli>(t1 - t0).count());
+		t0 = t1;
+	}
 };
 
 #define W_TRY try {
@@ -140,6 +160,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	}
 	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
 	WritePlan &p = w->plan;
+	PhaseTrace trace;
 	EncodeLaunch l;
 	l.sm_count = w->sm_count;
 	l.d_err = w->d_err;
@@ -241,11 +262,14 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		}
 		std::vector<b2a_enc_task> tasks;
 		std::vector<uint32_t> tiles;
+		trace.Mark("scratch alloc");
 		p.ScanTasks(pending, tasks, tiles);
+		trace.Mark("scan tasks (host)");
 		rc = UploadTasks(w, tasks, tiles, st);
 		if (rc != B2A_OK) {
 			return rc;
 		}
+		trace.Mark("scan tasks upload");
 		l.d_tasks = w->d_tasks;
 		l.d_tile_task = w->d_tile_task;
 		l.n_tasks = static_cast<uint32_t>(tasks.size());
@@ -258,6 +282,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		std::vector<uint64_t> totals(pending.size());
 		W_CUDA(cudaMemcpyAsync(totals.data(), base + n_tiles_total, pending.size() * 8, cudaMemcpyDeviceToHost, st));
 		W_CUDA(cudaStreamSynchronize(st));
+		trace.Mark("measure kernels + totals");
 		// ---- lists: child selection vectors (ArrowListData::AppendOffsets child_sel), children become new nodes
 		std::vector<b2a_enc_task> xtasks;
 		std::vector<uint32_t> xtiles;
@@ -304,7 +329,9 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		}
 	}
 	// ---- everything is sized: lay the stream out and stage the encode tasks
+	trace.Mark("list expansion");
 	p.Layout();
+	trace.Mark("layout (host)");
 	cudaFree(w->d_null_counts);
 	w->d_null_counts = nullptr;
 	W_CUDA(cudaMalloc(&w->d_null_counts, (p.nodes.size() ? p.nodes.size() : 1) * 8));
@@ -313,11 +340,14 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	}
 	std::vector<b2a_enc_task> tasks;
 	std::vector<uint32_t> tiles;
+	trace.Mark("null count alloc");
 	p.EncodeTasks(tasks, tiles);
+	trace.Mark("encode tasks (host)");
 	int rc = UploadTasks(w, tasks, tiles, st);
 	if (rc != B2A_OK) {
 		return rc;
 	}
+	trace.Mark("encode tasks upload");
 	w->n_enc_tasks = static_cast<uint32_t>(tasks.size());
 	w->n_enc_tiles = static_cast<uint32_t>(tiles.size());
 	w->enc_full = false;

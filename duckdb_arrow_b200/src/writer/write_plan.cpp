@@ -290,6 +290,7 @@ void WritePlan::Layout() {
 					break;
 				case B2A_ENC_STRING32:
 				case B2A_ENC_LIST32:
+				case B2A_ENC_UUID32:
 					len = (n.rows + 1) * 4;
 					break;
 				case B2A_ENC_STRING64:
