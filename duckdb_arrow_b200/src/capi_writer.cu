@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 
 using namespace b2a;
@@ -81,21 +82,53 @@ struct PhaseTrace {
 		W_CUDA(cudaSetDevice((w)->device));                                                                            \
 	} while (0)
 
-static int UploadTasks(b2a_writer *w, const std::vector<b2a_enc_task> &tasks, const std::vector<uint32_t> &tiles,
-                       cudaStream_t st) {
-	if (tasks.size() > w->cap_tasks) {
-		cudaFree(w->d_tasks);
+// Device memory of a writer comes from the device's default stream-ordered pool with the release threshold raised once
+// per device: a COPY creates one writer per prepared batch collection, and cudaMalloc / cudaFree (0.1-0.5 ms each, six
+// per writer) were a third of pass 1 (B2A_WRITER_TRACE).  Pool allocations cost microseconds once the pool is warm.
+static void KeepPoolWarm(int device) {
+	static std::mutex mu;
+	static std::vector<int> done;
+	std::lock_guard<std::mutex> lock(mu);
+	for (int d : done) {
+		if (d == device) {
+			return;
+		}
+	}
+	cudaMemPool_t pool;
+	if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+		uint64_t threshold = UINT64_MAX;
+		cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+	}
+	done.push_back(device);
+}
+
+static int ReserveTasks(b2a_writer *w, size_t n_tasks, size_t n_tiles, cudaStream_t st) {
+	if (n_tasks > w->cap_tasks) {
+		if (w->d_tasks) {
+			W_CUDA(cudaFreeAsync(w->d_tasks, st));
+		}
 		w->d_tasks = nullptr;
 		w->cap_tasks = 0;
-		W_CUDA(cudaMalloc(&w->d_tasks, tasks.size() * sizeof(b2a_enc_task)));
-		w->cap_tasks = tasks.size();
+		W_CUDA(cudaMallocAsync(&w->d_tasks, n_tasks * sizeof(b2a_enc_task), st));
+		w->cap_tasks = n_tasks;
 	}
-	if (tiles.size() > w->cap_tiles) {
-		cudaFree(w->d_tile_task);
+	if (n_tiles > w->cap_tiles) {
+		if (w->d_tile_task) {
+			W_CUDA(cudaFreeAsync(w->d_tile_task, st));
+		}
 		w->d_tile_task = nullptr;
 		w->cap_tiles = 0;
-		W_CUDA(cudaMalloc(&w->d_tile_task, tiles.size() * sizeof(uint32_t)));
-		w->cap_tiles = tiles.size();
+		W_CUDA(cudaMallocAsync(&w->d_tile_task, n_tiles * sizeof(uint32_t), st));
+		w->cap_tiles = n_tiles;
+	}
+	return B2A_OK;
+}
+
+static int UploadTasks(b2a_writer *w, const std::vector<b2a_enc_task> &tasks, const std::vector<uint32_t> &tiles,
+                       cudaStream_t st) {
+	int rc = ReserveTasks(w, tasks.size(), tiles.size(), st);
+	if (rc != B2A_OK) {
+		return rc;
 	}
 	// the host vectors are pageable and die with the caller's scope: plain synchronous copies, ordered after `st`
 	W_CUDA(cudaStreamSynchronize(st));
@@ -108,8 +141,8 @@ static int UploadTasks(b2a_writer *w, const std::vector<b2a_enc_task> &tasks, co
 	return B2A_OK;
 }
 
-static int DeviceAlloc(b2a_writer *w, size_t bytes, void **out) {
-	W_CUDA(cudaMalloc(out, bytes ? bytes : 8));
+static int DeviceAlloc(b2a_writer *w, size_t bytes, void **out, cudaStream_t st) {
+	W_CUDA(cudaMallocAsync(out, bytes ? bytes : 8, st));
 	w->allocs.push_back(*out);
 	return B2A_OK;
 }
@@ -124,11 +157,13 @@ int b2a_writer_create(const b2a_vector *columns, uint32_t n_columns, uint64_t ro
 	w->plan.Build(columns, n_columns, rows, opt);
 	if (device >= 0) {
 		W_CUDA(cudaSetDevice(device));
-		cudaDeviceProp prop;
-		W_CUDA(cudaGetDeviceProperties(&prop, device));
-		w->sm_count = prop.multiProcessorCount;
-		W_CUDA(cudaMalloc(&w->d_err, sizeof(uint32_t)));
-		W_CUDA(cudaMemset(w->d_err, 0, sizeof(uint32_t)));
+		int sms = 0; // (cudaGetDeviceProperties fills the whole struct: a millisecond per writer)
+		W_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+		w->sm_count = sms;
+		KeepPoolWarm(device);
+		W_CUDA(cudaMallocAsync(&w->d_err, sizeof(uint32_t), 0));
+		W_CUDA(cudaMemsetAsync(w->d_err, 0, sizeof(uint32_t), 0));
+		W_CUDA(cudaStreamSynchronize(0));
 	}
 	*out = w.release();
 	return B2A_OK;
@@ -141,13 +176,16 @@ void b2a_writer_destroy(b2a_writer *w) {
 	}
 	if (w->device >= 0) {
 		cudaSetDevice(w->device);
+		cudaDeviceSynchronize(); // whatever could still read these buffers has finished; the frees go back to the pool
 		for (void *p : w->allocs) {
-			cudaFree(p);
+			cudaFreeAsync(p, 0);
 		}
-		cudaFree(w->d_tasks);
-		cudaFree(w->d_tile_task);
-		cudaFree(w->d_null_counts);
-		cudaFree(w->d_err);
+		for (void *p : {static_cast<void *>(w->d_tasks), static_cast<void *>(w->d_tile_task),
+		                static_cast<void *>(w->d_null_counts), static_cast<void *>(w->d_err)}) {
+			if (p) {
+				cudaFreeAsync(p, 0);
+			}
+		}
 	}
 	delete w;
 }
@@ -164,6 +202,16 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	EncodeLaunch l;
 	l.sm_count = w->sm_count;
 	l.d_err = w->d_err;
+	{ // one allocation for both task uploads of the common case (the encode tasks are the larger set)
+		size_t est_tiles = 16;
+		for (auto &n : p.nodes) {
+			est_tiles += static_cast<size_t>(n.rows / B2A_ENC_STR_TILE + 3);
+		}
+		int rc = ReserveTasks(w, 2 * p.nodes.size() + 16, est_tiles, st);
+		if (rc != B2A_OK) {
+			return rc;
+		}
+	}
 	// ---- UNION members: mask = union row valid AND tag == member AND member value valid, over the input rows
 	for (size_t i = 0; i < p.vecs.size(); i++) {
 		if (p.vecs[i].union_member < 0 || p.vecs[i].union_mask_ready) {
@@ -171,7 +219,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		}
 		const WVec &u = p.vecs[static_cast<size_t>(p.vecs[i].union_vec)];
 		void *mask = nullptr;
-		int rc = DeviceAlloc(w, ((u.rows + 63) / 64 + 1) * 8, &mask);
+		int rc = DeviceAlloc(w, ((u.rows + 63) / 64 + 1) * 8, &mask, st);
 		if (rc != B2A_OK) {
 			return rc;
 		}
@@ -200,7 +248,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 				const WVec v = p.vecs[static_cast<size_t>(p.nodes[i].vec)];
 				const uint64_t k = static_cast<uint64_t>(v.param), child_rows = p.nodes[i].rows * k;
 				void *sel = nullptr;
-				int rc = DeviceAlloc(w, child_rows * 4, &sel);
+				int rc = DeviceAlloc(w, child_rows * 4, &sel, st);
 				if (rc != B2A_OK) {
 					return rc;
 				}
@@ -248,7 +296,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 			n_tiles_total += WritePlan::ScanTiles(p.nodes[static_cast<size_t>(ni)].rows);
 		}
 		void *chunk = nullptr;
-		int rc = DeviceAlloc(w, (n_tiles_total + pending.size()) * 8, &chunk);
+		int rc = DeviceAlloc(w, (n_tiles_total + pending.size()) * 8, &chunk, st);
 		if (rc != B2A_OK) {
 			return rc;
 		}
@@ -299,7 +347,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 				return SetLastError(B2A_EINVAL, "writer: list child vector exceeds the sel_t (uint32) range");
 			}
 			void *sel = nullptr;
-			rc = DeviceAlloc(w, totals[j] * 4, &sel);
+			rc = DeviceAlloc(w, totals[j] * 4, &sel, st);
 			if (rc != B2A_OK) {
 				return rc;
 			}
@@ -332,9 +380,11 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	trace.Mark("list expansion");
 	p.Layout();
 	trace.Mark("layout (host)");
-	cudaFree(w->d_null_counts);
+	if (w->d_null_counts) {
+		W_CUDA(cudaFreeAsync(w->d_null_counts, st));
+	}
 	w->d_null_counts = nullptr;
-	W_CUDA(cudaMalloc(&w->d_null_counts, (p.nodes.size() ? p.nodes.size() : 1) * 8));
+	W_CUDA(cudaMallocAsync(&w->d_null_counts, (p.nodes.size() ? p.nodes.size() : 1) * 8, st));
 	for (size_t i = 0; i < p.nodes.size(); i++) {
 		p.nodes[i].null_counter = reinterpret_cast<uint64_t>(w->d_null_counts + i);
 	}
