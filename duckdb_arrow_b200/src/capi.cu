@@ -451,6 +451,14 @@ int b2a_scan_finish(b2a_scan *s, void *cuda_stream) {
 		CUDA_OK(cudaMemsetAsync(s->d_err, 0, sizeof(uint32_t), st));
 		static const char *names[] = {"", "Unknown frame descriptor", "Src size is incorrect", "Data corruption detected",
 		                              "Destination buffer is too small", "Unsupported frame parameter"};
+		if (zerr[1] > B2A_DECOMP_LZ4_ERR) {
+			// no reference text: the reference has no LZ4 decompressor; liblz4's LZ4F_getErrorName strings
+			static const char *lnames[] = {"", "ERROR_frameType_unknown", "ERROR_srcSize_wrong", "ERROR_decompressionFailed",
+			                               "ERROR_dstMaxSize_tooSmall", "ERROR_parameter_unsupported"};
+			const uint32_t c = zerr[1] - B2A_DECOMP_LZ4_ERR;
+			return Fail(B2A_EIO, std::string("LZ4F_decompress of a compressed IPC buffer failed with error '") +
+			                         lnames[c < 6 ? c : 3] + "'");
+		}
 		// base_stream_reader.cpp:17-21: "ZSTD_decompress([buffer ...]) failed with error '...'" (IOException)
 		return Fail(B2A_EIO, std::string("ZSTD_decompress of a compressed IPC buffer failed with error '") +
 		                         names[zerr[1] < 6 ? zerr[1] : 3] + "'");

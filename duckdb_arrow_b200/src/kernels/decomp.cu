@@ -1,8 +1,10 @@
 // b2a_decompress_kernel: one warp per compressed IPC buffer at a time (jobs are handed out through an atomic counter,
 // largest-first is not needed: buffers of one batch are similar).  RAW jobs are a warp-wide copy; ZSTD jobs run the
-// frame decoder of zstd_decode.cuh warp-wide (see its header) with the warp's workspace (entropy tables + literal buffer) in global memory.
+// frame decoder of zstd_decode.cuh warp-wide (see its header) with the warp's workspace (entropy tables + literal buffer) in global memory;
+// LZ4 jobs run lz4_decode.cuh the same way (no workspace).
 #include "decomp.cuh"
 
+#include "lz4_decode.cuh"
 #include "zstd_decode.cuh"
 
 #include <cuda_runtime.h>
@@ -57,6 +59,12 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) b2a_decompress_kernel(Decom
 			}
 			for (uint64_t i = (n8 << 3) + lane; i < job.dst_len; i += 32) {
 				dst[i] = src[i];
+			}
+		} else if (job.codec == B2A_CODEC_LZ4) {
+			const lz4::Ctx lx = {static_cast<int>(lane), 32};
+			const int rc = lz4::decode_frame(lx, src, job.src_len, dst, job.dst_len);
+			if (rc != lz4::OK && lane == 0) {
+				atomicMax(l.d_err, B2A_DECOMP_LZ4_ERR + static_cast<uint32_t>(rc));
 			}
 		} else {
 			// every lane runs the decoder (uniform control flow, lane-parallel copies and Huffman streams)

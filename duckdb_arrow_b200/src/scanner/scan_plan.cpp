@@ -33,10 +33,12 @@ static const uint64_t kVirtBit = uint64_t(1) << 62;
 static const int kVirtShift = 36;
 
 RecordBatch ScanPlan::VirtualBatch(const Reader &reader, const RecordBatch &rb) {
-	if (rb.compression != 1) {
-		// the reference installs a ZSTD decompressor only (base_stream_reader.cpp:38-50); LZ4_FRAME bodies fail there too
-		throw Error(B2A_ENOTIMPL, "Arrow IPC: record batch bodies compressed with LZ4_FRAME are not supported (ZSTD only)");
+	if (rb.compression != 0 && rb.compression != 1) {
+		throw Error(B2A_ENOTIMPL, "Arrow IPC: unknown body compression codec " + std::to_string(rb.compression));
 	}
+	// 1 = ZSTD (the codec the reference installs, base_stream_reader.cpp:38-50); 0 = LZ4_FRAME (the
+	// reference fails on it for want of a decompressor; here it is decoded by kernels/lz4_decode.cuh)
+	const uint32_t frame_codec = rb.compression == 1 ? B2A_CODEC_ZSTD : B2A_CODEC_LZ4;
 	if (alias_direct) {
 		throw Error(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan cannot alias compressed bodies: create the scan without it");
 	}
@@ -64,7 +66,7 @@ RecordBatch ScanPlan::VirtualBatch(const Reader &reader, const RecordBatch &rb) 
 		} else if (ulen < 0) {
 			throw Error(B2A_EIO, "Arrow IPC: invalid uncompressed length in a compressed buffer");
 		} else {
-			c.codec = B2A_CODEC_ZSTD;
+			c.codec = frame_codec;
 			c.dst_len = static_cast<uint64_t>(ulen);
 		}
 		if (c.dst_len >= (uint64_t(1) << kVirtShift) || cands.size() >= (uint64_t(1) << (62 - kVirtShift))) {

@@ -235,7 +235,8 @@ int b2a_scan_column(b2a_scan *s, uint64_t batch, uint32_t flat_field, b2a_column
 int b2a_scan_dictionary(b2a_scan *s, uint32_t flat_field, b2a_column_out *out, uint32_t *dict_flat_field);
 uint64_t b2a_scan_gpu_launches(b2a_scan *s);
 /* Compressed bodies (RecordBatch.compression = ZSTD; the reference decompresses buffer by buffer with ZSTD_decompress,
- * src/ipc/stream_reader/base_stream_reader.cpp:11-50): every projected buffer is expanded on the device into a scratch
+ * src/ipc/stream_reader/base_stream_reader.cpp:11-50; LZ4_FRAME, which the reference has no decompressor for, is
+ * decoded as well): every projected buffer is expanded on the device into a scratch
  * region that lies `scratch_offset` bytes behind image offset image_lo, before the decode launch of the same call.
  * A caller-provided device image (b2a_scan_set_device_image) must therefore be scratch_offset + scratch_bytes + 64 long;
  * its first image_bytes hold the stream slice.  string_t pointers of a compressed scan point into the scratch region:

@@ -49,6 +49,24 @@ def test_oracle_matches_golden_json(name, endian):
                 assert same(g, e), f"{name}[{endian}] batch {bi} column {gname} row {i}: {g!r} != {e!r}"
 
 
+@pytest.mark.parametrize("name", ["generated_zstd", "generated_uncompressible_zstd",
+                                  "generated_lz4", "generated_uncompressible_lz4"])
+def test_oracle_matches_golden_json_compressed(name):
+    """2.0.0-compression (test/sql/arrow_testing.test:59-64 reads the zstd pair; the lz4 pair pins SURVEY §8f N-4):
+    bodies decompressed by pyarrow, converted by the oracle, equal to the fixture's golden contents"""
+    folder = os.path.join(GOLDEN, "arrow-testing", "2.0.0-compression")
+    batches = _batches(os.path.join(folder, name + ".stream"))
+    golden = golden_json(os.path.join(folder, name + ".json.gz"))
+    assert len(batches) == len(golden)
+    for bi, (batch, gold) in enumerate(zip(batches, golden)):
+        for ci, (gname, gvals) in enumerate(gold):
+            arr = batch.column(ci)
+            got = slab_to_py(O.scan_column(arr), arr.type)
+            assert len(got) == len(gvals)
+            for i, (g, e) in enumerate(zip(got, gvals)):
+                assert same(g, e), f"{name} batch {bi} column {gname} row {i}: {g!r} != {e!r}"
+
+
 def test_oracle_matches_pyarrow_on_test_arrows():
     """test/sql/read_arrow.test:36-55: count(*) = 15487, the commit lookup, and 2927 Wednesdays."""
     t = ipc.open_stream(os.path.join(GOLDEN, "data", "test.arrows")).read_all()

@@ -1,7 +1,8 @@
 #!/usr/bin/env python
-"""read_arrow of a ZSTD-compressed lineitem stream (IpcWriteOptions(compression='zstd'), what the reference reads through
-ZSTD_decompress per buffer): device-resident decompress + decode, CUDA events.  One JSON line.
-python tools/bench_zstd.py [--sf 1] [--steps 5]"""
+"""read_arrow of a compressed lineitem stream (IpcWriteOptions(compression='zstd'), what the reference reads through
+ZSTD_decompress per buffer; --codec lz4 = LZ4_FRAME bodies, which the reference cannot read): device-resident
+decompress + decode, CUDA events.  One JSON line.
+python tools/bench_zstd.py [--sf 1] [--steps 5] [--codec zstd|lz4]"""
 from __future__ import annotations
 
 import argparse
@@ -20,6 +21,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--level", type=int, default=1)
+    ap.add_argument("--codec", default="zstd", choices=["zstd", "lz4"])
     ap.add_argument("--columns", default="")
     args = ap.parse_args()
     import pyarrow as pa
@@ -31,12 +33,13 @@ def main():
     rows = int(6_001_215 * args.sf)
     t0 = time.time()
     sink = pa.BufferOutputStream()
-    opt = ipc.IpcWriteOptions(compression=pa.Codec("zstd", compression_level=args.level))
+    codec = pa.Codec("zstd", compression_level=args.level) if args.codec == "zstd" else pa.Codec("lz4")
+    opt = ipc.IpcWriteOptions(compression=codec)
     with ipc.new_stream(sink, lineitem.schema(), options=opt) as w:
         for b in lineitem.iter_batches(rows, seed=42, unique=16):
             w.write_batch(b)
     buf = sink.getvalue()
-    print(f"[bench_zstd] {rows} rows -> {buf.size / 1e9:.3f} GB compressed in {time.time() - t0:.1f}s", file=sys.stderr)
+    print(f"[bench_compressed] {rows} rows -> {buf.size / 1e9:.3f} GB compressed in {time.time() - t0:.1f}s", file=sys.stderr)
     reader = b2a.ArrowIPCReader.open_buffers([buf])
     if args.columns:
         reader.set_projection(args.columns.split(","))
@@ -66,13 +69,13 @@ def main():
     cpu_s = time.time() - t0
     peak, kind = measured_peak()
     print(json.dumps({
-        "metric": "read_arrow rows/s, ZSTD-compressed lineitem (device-resident decompress + decode)",
+        "metric": f"read_arrow rows/s, {args.codec.upper()}-compressed lineitem (device-resident decompress + decode)",
         "unit": "rows/s", "value": rows / (ms / 1e3), "ms_per_step": ms, "rows": rows,
         "compressed_bytes": int(scan.image_bytes), "decompressed_bytes": int(scan.scratch_bytes),
         "ratio": scan.scratch_bytes / max(1, scan.image_bytes), "jobs": int(scan.n_decompress_jobs),
         "decompressed_gb_per_s": scan.scratch_bytes / (ms / 1e3) / 1e9,
         "pyarrow_cpu_decompress_rows_per_s": n / cpu_s, "pyarrow_cpu_threads": pa.cpu_count(),
-        "config": {"workload": f"lineitem SF{args.sf:g}, zstd level {args.level}, 122880-row batches"}}))
+        "config": {"workload": f"lineitem SF{args.sf:g}, " + (f"zstd level {args.level}" if args.codec == "zstd" else "lz4 frame") + ", 122880-row batches"}}))
 
 
 if __name__ == "__main__":
