@@ -201,6 +201,9 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the scan path has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    from duckdb_arrow_b200 import parallel
+    numa = parallel.bind_to_device_numa_node(local_rank) if os.environ.get("B2A_NUMA_BIND", "1") != "0" else {}
+    log(f"[bench] rank {rank}: numa {numa}, {len(os.sched_getaffinity(0))} cpus")
     dist = None
     if world > 1:
         import torch.distributed as dist

@@ -26,6 +26,52 @@ def file_shard(paths: list[str], rank: int, world: int) -> list[str]:
     return list(paths[rank::world])
 
 
+def _parse_cpulist(text: str) -> set[int]:
+    cpus: set[int] = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def device_numa_node(pci_bus_id: str, sysfs: str = "/sys") -> int:
+    """NUMA node the PCIe device hangs off (-1: unknown / single node / virtualised)."""
+    try:
+        with open(f"{sysfs}/bus/pci/devices/{pci_bus_id.lower()}/numa_node") as f:
+            return int(f.read().strip())
+    except (OSError, ValueError):
+        return -1
+
+
+def bind_to_device_numa_node(device: int, sysfs: str = "/sys") -> dict:
+    """One process per GPU: run this rank's host threads on the cores of the NUMA node its GPU hangs off, BEFORE the
+    pinned buffers are allocated, so that first-touch places them in that node's memory and the rank's H2D / D2H
+    traffic stays off the inter-socket link.  The end-to-end leg streams ~8.7 GB per step and GPU through host memory;
+    nothing else of the path is shared between ranks.  Best effort: returns what it did, never raises."""
+    import os
+    info = {"device": device, "numa_node": -1, "bound": False}
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(device)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        info["pci"] = bdf
+        node = device_numa_node(bdf, sysfs)
+        info["numa_node"] = node
+        if node < 0:
+            return info
+        with open(f"{sysfs}/devices/system/node/node{node}/cpulist") as f:
+            cpus = _parse_cpulist(f.read()) & set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            info["bound"] = True
+            info["cpus"] = len(cpus)
+    except Exception as e:  # noqa: BLE001 - topology files differ between kernels / containers
+        info["error"] = repr(e)
+    return info
+
+
 def _to_limbs(v: int) -> list[int]:
     u = v & ((1 << (LIMB_BITS * N_LIMBS)) - 1)
     return [(u >> (LIMB_BITS * i)) & ((1 << LIMB_BITS) - 1) for i in range(N_LIMBS)]

@@ -72,3 +72,23 @@ def test_combine_counts_gloo_world2():
 
 def test_combine_counts_without_group_is_identity():
     assert P.combine_counts({"rows": 5, "sum": -3}) == {"rows": 5, "sum": -3}
+
+
+def test_numa_binding_helpers(tmp_path):
+    """bind_to_device_numa_node: cpulist parsing, sysfs lookup, and 'unknown node' = no-op (the GPU box is a VM with one
+    virtual node and numa_node = -1)."""
+    import importlib.util
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("_par", os.path.join(root, "duckdb_arrow_b200", "parallel.py"))
+    par = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(par)
+    assert par._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert par._parse_cpulist("") == set()
+    d = tmp_path / "bus" / "pci" / "devices" / "0000:9c:00.0"
+    d.mkdir(parents=True)
+    (d / "numa_node").write_text("1\n")
+    assert par.device_numa_node("0000:9C:00.0", str(tmp_path)) == 1
+    assert par.device_numa_node("0000:aa:00.0", str(tmp_path)) == -1
+    info = par.bind_to_device_numa_node(0, str(tmp_path))  # no CUDA device here: best effort, never raises
+    assert info["bound"] is False
