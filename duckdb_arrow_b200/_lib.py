@@ -77,7 +77,11 @@ Vector._fields_ = [("type_id", C.c_int32), ("decimal_width", C.c_int32), ("decim
 
 class WriteOptions(C.Structure):
     _fields_ = [("row_group_size", C.c_uint64), ("n_kv_metadata", C.c_uint32), ("kv_keys", C.POINTER(C.c_char_p)),
-                ("kv_values", C.POINTER(C.c_char_p))]
+                ("kv_values", C.POINTER(C.c_char_p)), ("flags", C.c_uint32)]
+
+
+WRITE_LARGE_OFFSETS = 0x1  # B2A_WRITE_LARGE_OFFSETS
+WRITE_LIST_VIEW = 0x2  # B2A_WRITE_LIST_VIEW
 
 
 class MultiFileOptions(C.Structure):

@@ -339,7 +339,7 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 			p.nodes[static_cast<size_t>(ni)].total = totals[j];
 			p.nodes[static_cast<size_t>(ni)].measured = true;
 			const WVec v = p.vecs[static_cast<size_t>(p.nodes[static_cast<size_t>(ni)].vec)];
-			if (v.op != B2A_ENC_LIST32 && v.op != B2A_ENC_LIST64) {
+			if (!WritePlan::IsListOp(v.op)) {
 				continue;
 			}
 			const WVec &cv = p.vecs[static_cast<size_t>(v.children.at(0))];

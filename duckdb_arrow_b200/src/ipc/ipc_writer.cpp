@@ -97,14 +97,14 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		break;
 	}
 	case B2A_T_VARCHAR:
-		empty(ArrowTypeTag::Utf8);
+		empty(f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
 		break;
 	case B2A_T_BLOB:
 	case B2A_T_BIT: // arrow_converter.cpp:268-279 without arrow_lossless_conversion: plain binary
-		empty(ArrowTypeTag::Binary);
+		empty(f.large_offsets ? ArrowTypeTag::LargeBinary : ArrowTypeTag::Binary);
 		break;
 	case B2A_T_UUID: // arrow_converter.cpp:172-186: a 36-character string unless arrow_lossless_conversion
-		empty(ArrowTypeTag::Utf8);
+		empty(f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
 		break;
 	case B2A_T_UNION: { // "+us:0,1,..": sparse, type id i = member i (arrow_converter.cpp:331-361)
 		std::vector<int32_t> ids(f.children.size());
@@ -153,7 +153,8 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		o.table = b.end_table();
 		break;
 	case B2A_T_LIST:
-		empty(ArrowTypeTag::List);
+		empty(f.list_view ? (f.large_offsets ? ArrowTypeTag::LargeListView : ArrowTypeTag::ListView)
+		                  : (f.large_offsets ? ArrowTypeTag::LargeList : ArrowTypeTag::List));
 		break;
 	case B2A_T_STRUCT:
 		empty(ArrowTypeTag::Struct_);
@@ -277,14 +278,12 @@ void ResolveArrowFormat(WriteField &f) {
 		           std::to_string(DecimalBitWidth(f.decimal_width));
 		break;
 	case B2A_T_VARCHAR:
-		f.format = "u";
+	case B2A_T_UUID:
+		f.format = f.large_offsets ? "U" : "u";
 		break;
 	case B2A_T_BLOB:
 	case B2A_T_BIT:
-		f.format = "z";
-		break;
-	case B2A_T_UUID:
-		f.format = "u";
+		f.format = f.large_offsets ? "Z" : "z";
 		break;
 	case B2A_T_UNION: {
 		if (f.children.empty()) {
@@ -323,7 +322,7 @@ void ResolveArrowFormat(WriteField &f) {
 		break;
 	case B2A_T_LIST:
 		kids(1);
-		f.format = "+l";
+		f.format = f.list_view ? (f.large_offsets ? "+vL" : "+vl") : (f.large_offsets ? "+L" : "+l");
 		f.children[0].name = "l"; // arrow_converter.cpp:330
 		break;
 	case B2A_T_STRUCT:

@@ -22,6 +22,8 @@ struct WriteField {
 	int decimal_width = 0, decimal_scale = 0;
 	int64_t param = 0; // ARRAY size
 	std::string timezone;
+	bool list_view = false;     // arrow_output_list_view: "+vl" / "+vL"
+	bool large_offsets = false; // arrow_large_buffer_size: "U" / "Z" / "+L" (set by the write planner)
 	std::vector<WriteField> children;
 	std::string format; // the C-data-interface format string the reference would set (for tests / diagnostics)
 };

@@ -21,7 +21,11 @@ enum b2a_enc_op {
 	/* ops below run in the full instantiation of b2a_encode_kernel only (rare types; keeps the common one lean) */
 	B2A_ENC_TIMETZ,       /* ArrowScalarData<int64_t, dtime_tz_t, ArrowTimeTzConverter>: bits >> 24, NULLs skipped */
 	B2A_ENC_UUID32,       /* ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>: 36 characters per valid row */
-	B2A_ENC_UNION_TAG     /* ArrowUnionData::Append, union_data.cpp:24-52: type id = tag of a valid row, else 0 */
+	B2A_ENC_UNION_TAG,    /* ArrowUnionData::Append, union_data.cpp:24-52: type id = tag of a valid row, else 0 */
+	B2A_ENC_UUID64,       /* ArrowVarcharData<hugeint_t, ArrowUUIDConverter> (int64 offsets, arrow_large_buffer_size) */
+	B2A_ENC_LISTVIEW32,   /* ArrowListViewData<int32_t>::AppendListMetadata, list_view_data.hpp:59-103: offsets -> dst,
+	                         sizes -> dst2, `rows` entries each; a NULL row = {running offset, 0} */
+	B2A_ENC_LISTVIEW64
 };
 
 #define B2A_ENC_OP_IS_RARE(op) ((op) >= B2A_ENC_TIMETZ)

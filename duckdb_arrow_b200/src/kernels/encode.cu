@@ -107,7 +107,7 @@ __device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i,
 	if (t.op == B2A_ENC_STRING32 || t.op == B2A_ENC_STRING64) {
 		return e.x; // string_t.length
 	}
-	if (t.op == B2A_ENC_UUID32) {
+	if (t.op == B2A_ENC_UUID32 || t.op == B2A_ENC_UUID64) {
 		return 36; // UUID::STRING_SIZE (ArrowUUIDConverter::GetLength, varchar_data.hpp:33-37); e = the hugeint_t
 	}
 	return (static_cast<uint64_t>(e.w) << 32) | e.z; // list_entry_t.length
@@ -867,7 +867,9 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 
 // ArrowListData<BUFTYPE>::AppendOffsets: offsets only (children are appended through the selection built by
 // b2a_enc_expand_kernel)
-template <typename OFF>
+// VIEW: ArrowListViewData<BUFTYPE>::AppendListMetadata — offsets[i] = the running offset BEFORE row i, sizes[i] = its
+// length (0 for a NULL row), no trailing offset; the child selection is the same
+template <typename OFF, bool VIEW = false>
 __device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                          uint32_t *err) {
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
@@ -886,6 +888,25 @@ __device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restr
 	uint64_t window;
 	uint64_t run = reinterpret_cast<const uint64_t *>(t.scratch)[k] + block_exclusive_scan(sum, &window);
 	OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
+	if (VIEW) {
+		OFF *sizes = reinterpret_cast<OFF *>(stream + t.dst2);
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+			if (i < t.rows) {
+				if (sizeof(OFF) == 4 && run + len[u] > 0x7FFFFFFFull) {
+					enc_raise(err, B2A_DEV_ENC_LIST_I32);
+				}
+				offs[i] = static_cast<OFF>(run);
+				sizes[i] = static_cast<OFF>(len[u]);
+				if (sizeof(OFF) == 4 && i + 1 == t.rows && (t.rows & 1)) {
+					sizes[i + 1] = 0; // zero padding of the sizes buffer up to 8 bytes (the main buffer: last-tile code)
+				}
+			}
+			run += len[u];
+		}
+		return;
+	}
 	if (k == 0 && threadIdx.x == 0) {
 		offs[0] = 0;
 	}
@@ -991,6 +1012,12 @@ __global__ void __launch_bounds__(kThreads, 4)
 					enc_union_tag(t, stream, row0, nrows);
 				} else if (t.op == B2A_ENC_UUID32) {
 					enc_string<int32_t, true>(t, stream, k, stage, err);
+				} else if (t.op == B2A_ENC_UUID64) {
+					enc_string<int64_t, true>(t, stream, k, stage, err);
+				} else if (t.op == B2A_ENC_LISTVIEW32) {
+					enc_list<int32_t, true>(t, stream, k, err);
+				} else if (t.op == B2A_ENC_LISTVIEW64) {
+					enc_list<int64_t, true>(t, stream, k, err);
 				}
 			}
 			break;

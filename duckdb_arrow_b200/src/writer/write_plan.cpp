@@ -72,9 +72,10 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 2;
 		break;
 	case B2A_T_UUID: // ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>, arrow_appender.cpp:180-191
-		w.op = B2A_ENC_UUID32;
+		w.op = large_offsets ? B2A_ENC_UUID64 : B2A_ENC_UUID32;
 		w.src_width = 16;
-		w.dst_width = 4;
+		w.dst_width = large_offsets ? 8 : 4;
+		wf.large_offsets = large_offsets;
 		w.n_buffers = 3;
 		break;
 	case B2A_T_UNION: // ArrowUnionData, arrow_appender.cpp:276-278: one buffer (type ids), members as children
@@ -106,18 +107,24 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	case B2A_T_VARCHAR:
 	case B2A_T_BLOB:
 	case B2A_T_BIT: // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
-		w.op = B2A_ENC_STRING32;
+		w.op = large_offsets ? B2A_ENC_STRING64 : B2A_ENC_STRING32;
 		w.src_width = 16;
-		w.dst_width = 4;
+		w.dst_width = large_offsets ? 8 : 4;
+		wf.large_offsets = large_offsets;
 		w.n_buffers = 3;
 		break;
 	case B2A_T_LIST:
-	case B2A_T_MAP:
-		w.op = B2A_ENC_LIST32;
+	case B2A_T_MAP: { // no large map in Arrow: ArrowMapData<int32_t> whatever the offset size, arrow_appender.cpp:296-299
+		const bool large = large_offsets && v.type_id == B2A_T_LIST;
+		const bool view = list_view && v.type_id == B2A_T_LIST; // arrow_appender.cpp:280-299
+		w.op = view ? (large ? B2A_ENC_LISTVIEW64 : B2A_ENC_LISTVIEW32) : (large ? B2A_ENC_LIST64 : B2A_ENC_LIST32);
 		w.src_width = 16;
-		w.dst_width = 4;
-		w.n_buffers = 2;
+		w.dst_width = large ? 8 : 4;
+		wf.large_offsets = large;
+		wf.list_view = view;
+		w.n_buffers = view ? 3 : 2; // ArrowListViewData::Finalize: validity, offsets, sizes
 		break;
+	}
 	case B2A_T_STRUCT:
 	case B2A_T_ARRAY:
 		w.n_buffers = 1;
@@ -174,6 +181,8 @@ void WritePlan::Build(const b2a_vector *columns, uint32_t n_columns, uint64_t ro
 		throw Error(B2A_EINVAL, "writer: no columns");
 	}
 	row_group_size = (opt && opt->row_group_size) ? opt->row_group_size : 122880;
+	large_offsets = opt && (opt->flags & B2A_WRITE_LARGE_OFFSETS);
+	list_view = opt && (opt->flags & B2A_WRITE_LIST_VIEW);
 	if (opt) {
 		for (uint32_t i = 0; i < opt->n_kv_metadata; i++) {
 			kv_metadata.emplace_back(opt->kv_keys[i], opt->kv_values[i]);
@@ -295,6 +304,7 @@ void WritePlan::Layout() {
 					break;
 				case B2A_ENC_STRING64:
 				case B2A_ENC_LIST64:
+				case B2A_ENC_UUID64:
 					len = (n.rows + 1) * 8;
 					break;
 				default:
@@ -306,8 +316,10 @@ void WritePlan::Layout() {
 				algorithmic_in += n.rows * static_cast<uint64_t>(v.src_width);
 			}
 			if (v.n_buffers >= 3) {
-				n.buf[2] = BufferSlice {off, n.total};
-				off += Align8(n.total);
+				// strings: the characters; list views: the sizes buffer
+				const uint64_t len = IsListViewOp(v.op) ? n.rows * static_cast<uint64_t>(v.dst_width) : n.total;
+				n.buf[2] = BufferSlice {off, len};
+				off += Align8(len);
 			}
 		}
 		if (bi == 0) {

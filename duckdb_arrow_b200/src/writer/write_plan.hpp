@@ -67,6 +67,8 @@ struct WritePlan {
 	std::vector<WNode> nodes;
 	std::vector<WBatch> batches;
 	uint64_t row_group_size = 122880;
+	bool large_offsets = false; // B2A_WRITE_LARGE_OFFSETS
+	bool list_view = false;     // B2A_WRITE_LIST_VIEW
 	uint64_t total_rows = 0;
 
 	std::vector<uint8_t> schema_message;
@@ -91,7 +93,13 @@ struct WritePlan {
 
 	static bool IsScanOp(int op) {
 		return op == B2A_ENC_STRING32 || op == B2A_ENC_STRING64 || op == B2A_ENC_LIST32 || op == B2A_ENC_LIST64 ||
-		       op == B2A_ENC_UUID32;
+		       op == B2A_ENC_UUID32 || op == B2A_ENC_UUID64 || op == B2A_ENC_LISTVIEW32 || op == B2A_ENC_LISTVIEW64;
+	}
+	static bool IsListViewOp(int op) {
+		return op == B2A_ENC_LISTVIEW32 || op == B2A_ENC_LISTVIEW64;
+	}
+	static bool IsListOp(int op) { // ops whose node has a child appended through a selection
+		return op == B2A_ENC_LIST32 || op == B2A_ENC_LIST64 || IsListViewOp(op);
 	}
 	static uint64_t ScanTiles(uint64_t rows) {
 		uint64_t n = (rows + B2A_ENC_STR_TILE - 1) / B2A_ENC_STR_TILE;

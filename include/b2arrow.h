@@ -358,7 +358,17 @@ typedef struct b2a_write_options {
 	uint32_t n_kv_metadata;       /* COPY option kv_metadata (write_arrow_stream.cpp:87-105) */
 	const char *const *kv_keys;
 	const char *const *kv_values;
+	uint32_t flags;               /* B2A_WRITE_* (ClientProperties of the session, arrow_stream_writer.cpp:11) */
 } b2a_write_options;
+
+/* SET arrow_large_buffer_size = true (ClientProperties.arrow_offset_size = LARGE): VARCHAR / UUID -> "U", BLOB / BIT
+ * -> "Z", LIST -> "+L" with int64 offsets (arrow_appender.cpp:184-188,237-251,288-292; arrow_converter.cpp:179-196,
+ * 262-279,289-293).  MAP keeps int32 offsets: Arrow has no large map (arrow_appender.cpp:296-299). */
+#define B2A_WRITE_LARGE_OFFSETS 0x1u
+/* SET arrow_output_list_view = true (ClientProperties.arrow_use_list_view): LIST -> "+vl" ("+vL" with LARGE_OFFSETS):
+ * ArrowListViewData, an offsets and a sizes buffer of `rows` entries each (appender/list_view_data.hpp:59-103,
+ * arrow_appender.cpp:281-286, arrow_converter.cpp:282-287).  MAP is not affected. */
+#define B2A_WRITE_LIST_VIEW 0x2u
 
 typedef struct b2a_writer b2a_writer;
 

@@ -43,9 +43,14 @@ def _validity_buffer(valid: np.ndarray) -> tuple[bytes, int]:
     return np.packbits(bits, bitorder="little").tobytes(), int(n - valid.sum())
 
 
-def append(hv, idx: np.ndarray, nodes: list, buffers: list):
+def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False, view: bool = False):
     """Append rows `idx` (input row indices: the UnifiedVectorFormat selection) of vector hv; pre-order output.
-    nodes: [(length, null_count)], buffers: [bytes] (unpadded)."""
+    nodes: [(length, null_count)], buffers: [bytes] (unpadded).
+    large: ClientProperties.arrow_offset_size == LARGE (SET arrow_large_buffer_size): int64 offsets for VARCHAR / BLOB /
+    BIT / UUID / LIST (arrow_appender.cpp:184-188,237-251,288-292); MAP stays int32 (:296-299).
+    view: ClientProperties.arrow_use_list_view (SET arrow_output_list_view): LIST -> ArrowListViewData, an offsets and a
+    sizes buffer of n entries each (appender/list_view_data.hpp:59-103); MAP is not affected."""
+    off_t = np.int64 if large else np.int32
     n = len(idx)
     t = hv.type
     if t == "SQLNULL":  # ArrowNullData: no buffers, null_count = length
@@ -64,7 +69,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
             import copy
             member = copy.copy(c)
             member.validity = valid_full & (tags_full == m) & own
-            append(member, idx, nodes, buffers)
+            append(member, idx, nodes, buffers, large, view)
         return
     valid = _valid(hv, idx)
     vbuf, nulls = _validity_buffer(valid)
@@ -86,7 +91,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
             if ok:
                 h = "%016x%016x" % (upper ^ (1 << 63), lower)  # the sign bit of `upper` is flipped back
                 chars += f"{h[:8]}-{h[8:12]}-{h[12:16]}-{h[16:20]}-{h[20:]}".encode()
-        buffers.append(offs.astype(np.int32).tobytes())
+        buffers.append(offs.astype(off_t).tobytes())
         buffers.append(bytes(chars))
     elif t == "TIME_TZ":  # dtime_tz_t: micros in the upper 40 bits (OFFSET_BITS = 24); NULL slots unwritten (0 here)
         bits = hv.data.view(np.uint64)[idx]
@@ -95,12 +100,12 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
         length = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
         offs = np.zeros(n + 1, np.int64)
         np.cumsum(length, out=offs[1:])
-        if n and offs[-1] > 2147483647:
+        if n and not large and offs[-1] > 2147483647:
             raise OverflowError("Arrow Appender: The maximum total string size for regular string buffers is "
                                 "2147483647 but the offset exceeds this")
         total = int(offs[-1])
         pos = np.arange(total, dtype=np.int64) - np.repeat(offs[:-1], length) + np.repeat(hv.str_start[idx], length)
-        buffers.append(offs.astype(np.int32).tobytes())
+        buffers.append(offs.astype(off_t).tobytes())
         buffers.append(hv.heap[pos].tobytes() if total else b"")
     elif t in ("LIST", "MAP"):
         ent = hv.data.view(np.uint64).reshape(-1, 2)[idx]
@@ -110,18 +115,25 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
         total = int(offs[-1])
         child_sel = (np.arange(total, dtype=np.int64) - np.repeat(offs[:-1], length)
                      + np.repeat(ent[:, 0].astype(np.int64), length))
-        buffers.append(offs.astype(np.int32).tobytes())
+        if t == "LIST" and view:  # offsets[i] = running offset before row i (also for NULL rows), sizes[i] = length
+            if n and not large and offs[-1] > 2147483647:
+                raise OverflowError("Arrow Appender: The maximum combined list offset for regular list buffers is "
+                                    "2147483647 but the offset exceeds this")
+            buffers.append(offs[:-1].astype(off_t).tobytes())
+            buffers.append(length.astype(off_t).tobytes())
+        else:
+            buffers.append(offs.astype(off_t if t == "LIST" else np.int32).tobytes())
         child = hv.children[0]
         if t == "MAP":
             child._no_validity_buffer = True  # the entries struct's validity buffer is never resized (map_data.hpp)
-        append(child, child_sel, nodes, buffers)
+        append(child, child_sel, nodes, buffers, large, view)
     elif t == "STRUCT":
         for c in hv.children:
-            append(c, idx, nodes, buffers)
+            append(c, idx, nodes, buffers, large, view)
     elif t == "ARRAY":
         k = hv.param
         child_idx = (idx[:, None] * k + np.arange(k)[None, :]).reshape(-1)
-        append(hv.children[0], child_idx, nodes, buffers)
+        append(hv.children[0], child_idx, nodes, buffers, large, view)
     elif t == "DECIMAL" and hv.decimal[0] <= 4:
         buffers.append(hv.data.view(np.int16)[idx].astype(np.int32).tobytes())
     elif t == "INTERVAL":
@@ -135,7 +147,8 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list):
         buffers.append(hv.data.reshape(-1, w)[idx].tobytes() if n else b"")
 
 
-def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880):
+def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, large: bool = False,
+                      view: bool = False):
     """-> [(rows, nodes, buffers[(offset, length)], body bytes)] per record batch"""
     out = []
     for r0 in range(0, rows, row_group_size):
@@ -143,7 +156,7 @@ def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880):
         idx = np.arange(r0, r0 + n, dtype=np.int64)
         nodes, bufs = [], []
         for c in columns:
-            append(c, idx, nodes, bufs)
+            append(c, idx, nodes, bufs, large, view)
         body, slices = b"", []
         for b in bufs:
             slices.append((len(body), len(b)))

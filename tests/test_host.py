@@ -229,3 +229,53 @@ def test_writer_schema_message_types_read_by_pyarrow(b2a):
         assert sch.field(name).type == t, (name, sch.field(name).type)
     assert sch.field("u").type.type_codes == [0, 1, 2] and sch.field("u").type.mode == "sparse"
     assert sch.metadata == {b"k": b"v"}
+
+
+def test_writer_schema_message_large_offsets(b2a):
+    """B2A_WRITE_LARGE_OFFSETS = SET arrow_large_buffer_size: "U" / "Z" / "+L" for VARCHAR + UUID / BLOB + BIT / LIST, at
+    every nesting level; MAP stays a (32-bit) map (arrow_converter.cpp:179-196,262-293; arrow_appender.cpp:296-299)."""
+    import pyarrow.ipc as ipc
+    from duckdb_arrow_b200 import DeviceVector as DV
+
+    def v(t, name, kids=(), **kw):
+        return DV(t, 0, None, None, list(kids), name, **kw)
+
+    cols = [v("VARCHAR", "s"), v("BLOB", "z"), v("BIT", "bits"), v("UUID", "id"), v("BIGINT", "i64"),
+            v("LIST", "l", [v("VARCHAR", "x")]), v("LIST", "ll", [v("LIST", "x", [v("INTEGER", "y")])]),
+            v("STRUCT", "st", [v("INTEGER", "a"), v("VARCHAR", "b")]),
+            v("MAP", "m", [v("STRUCT", "e", [v("VARCHAR", "k"), v("LIST", "v", [v("BIGINT", "w")])])]),
+            v("ARRAY", "arr", [v("VARCHAR", "x")], param=2)]
+    w = b2a.ArrowWriter(cols, 0, device=-1, arrow_large_buffer_size=True)
+    sch = ipc.read_schema(pa.py_buffer(w.schema_message()))
+    w.close()
+    exp = {"s": pa.large_string(), "z": pa.large_binary(), "bits": pa.large_binary(), "id": pa.large_string(),
+           "i64": pa.int64(), "l": pa.large_list(pa.field("l", pa.large_string())),
+           "ll": pa.large_list(pa.field("l", pa.large_list(pa.field("l", pa.int32())))),
+           "st": pa.struct([("a", pa.int32()), ("b", pa.large_string())]),
+           "m": pa.map_(pa.large_string(), pa.large_list(pa.field("l", pa.int64()))),
+           "arr": pa.list_(pa.field("", pa.large_string()), 2)}
+    for name, t in exp.items():
+        assert sch.field(name).type == t, (name, sch.field(name).type)
+
+
+def test_writer_schema_message_list_views(b2a):
+    """B2A_WRITE_LIST_VIEW = SET arrow_output_list_view: "+vl" (with large offsets "+vL") for LIST at every level, MAP
+    untouched (arrow_converter.cpp:282-287)."""
+    import pyarrow.ipc as ipc
+    from duckdb_arrow_b200 import DeviceVector as DV
+
+    def v(t, name, kids=(), **kw):
+        return DV(t, 0, None, None, list(kids), name, **kw)
+
+    def cols():
+        return [v("LIST", "l", [v("VARCHAR", "x")]), v("LIST", "ll", [v("LIST", "x", [v("INTEGER", "y")])]),
+                v("MAP", "m", [v("STRUCT", "e", [v("VARCHAR", "k"), v("LIST", "v", [v("BIGINT", "w")])])])]
+    for large in (False, True):
+        w = b2a.ArrowWriter(cols(), 0, device=-1, arrow_large_buffer_size=large, arrow_output_list_view=True)
+        sch = ipc.read_schema(pa.py_buffer(w.schema_message()))
+        w.close()
+        lv = pa.large_list_view if large else pa.list_view
+        s = pa.large_string() if large else pa.string()
+        assert sch.field("l").type == lv(pa.field("l", s))
+        assert sch.field("ll").type == lv(pa.field("l", lv(pa.field("l", pa.int32()))))
+        assert sch.field("m").type == pa.map_(s, lv(pa.field("l", pa.int64())))

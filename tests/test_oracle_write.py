@@ -9,7 +9,7 @@ import pytest
 from oracle import oracle_write as OW
 from tests_helpers import pylist, same_rows
 from vectors import table_vectors
-from writer_cases import arrays_from_buffers, nested_table, rare_columns, scalar_table
+from writer_cases import arrays_from_buffers, large_type, nested_table, rare_columns, scalar_table, writer_type
 
 
 def _lineitem(n):
@@ -83,3 +83,57 @@ def test_bool_null_rows_keep_bit_set():
     data = body[slices[1][0]: slices[1][0] + slices[1][1]]
     assert data == bytes([0b11111011])
     assert nodes == [(4, 2)]
+
+
+@pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("nested", 1000), ("lineitem", 5000), ("rare", 1000)])
+def test_write_oracle_large_offsets(case, rgs):
+    """SET arrow_large_buffer_size = true (arrow_appender.cpp:184-188,237-251,288-292): int64 offsets for VARCHAR / BLOB /
+    BIT / UUID / LIST, int32 for MAP — the buffers reassemble, as large_utf8 / large_binary / large_list arrays, into the
+    same rows, and apart from the offsets buffers the bodies are those of the regular run."""
+    if case == "rare":
+        cols, expected, types = rare_columns(3000)
+        rows, names = 3000, list(expected)
+    else:
+        table = {"scalar": lambda: scalar_table(5000), "nested": lambda: nested_table(3000),
+                 "lineitem": lambda: _lineitem(12_345)}[case]()
+        cols, rows, names, types = table_vectors(table), table.num_rows, table.schema.names, [f.type for f in table.schema]
+        expected = {n: pylist(table.column(n)) for n in names}
+    ltypes = [large_type(t) for t in types]
+    assert ltypes != types
+    row = 0
+    regular = OW.serialize_batches(cols, rows, rgs)
+    for (n, nodes, slices, body), (n0, nodes0, slices0, _) in zip(OW.serialize_batches(cols, rows, rgs, large=True), regular):
+        assert (n, nodes) == (n0, nodes0) and len(slices) == len(slices0)
+        widened = sum(1 for (_, l), (_, l0) in zip(slices, slices0) if l != l0)
+        assert widened and all(l in (l0, 2 * l0) for (_, l), (_, l0) in zip(slices, slices0))
+        bufs = [body[o:o + l] for o, l in slices]
+        for arr, name in zip(arrays_from_buffers(ltypes, nodes, bufs), names):
+            arr.validate(full=True)
+            assert pylist(arr) == expected[name][row: row + n], name
+        row += n
+    assert row == rows
+
+
+@pytest.mark.parametrize("large", [False, True])
+@pytest.mark.parametrize("case,rgs", [("nested", 1000), ("nested", 4096), ("rare", 1000)])
+def test_write_oracle_list_views(case, rgs, large):
+    """SET arrow_output_list_view = true (ArrowListViewData, appender/list_view_data.hpp:59-103): every LIST node carries an
+    offsets and a sizes buffer of `rows` entries (NULL row = {running offset, 0}); MAPs stay maps. pyarrow rebuilds the
+    same rows from the buffers as list_view / large_list_view arrays."""
+    if case == "rare":
+        cols, expected, types = rare_columns(3000)
+        rows, names = 3000, list(expected)
+    else:
+        table = nested_table(3000)
+        cols, rows, names, types = table_vectors(table), table.num_rows, table.schema.names, [f.type for f in table.schema]
+        expected = {n: pylist(table.column(n)) for n in names}
+    vtypes = [writer_type(t, large, True) for t in types]
+    assert any("list_view" in str(t) for t in vtypes)
+    row = 0
+    for n, nodes, slices, body in OW.serialize_batches(cols, rows, rgs, large=large, view=True):
+        bufs = [body[o:o + l] for o, l in slices]
+        for arr, name in zip(arrays_from_buffers(vtypes, nodes, bufs), names):
+            arr.validate(full=True)
+            assert pylist(arr) == expected[name][row: row + n], name
+        row += n
+    assert row == rows

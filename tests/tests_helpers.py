@@ -17,7 +17,11 @@ def pylist(arr) -> list:
     (which is what the scalars of a list<union> are) at the unsliced positions"""
     if isinstance(arr, pa.ChunkedArray):
         return [v for c in arr.chunks for v in pylist(c)]
-    if pa.types.is_list(arr.type) and pa.types.is_union(arr.type.value_type):
+    if (pa.types.is_list_view(arr.type) or pa.types.is_large_list_view(arr.type)) and pa.types.is_union(arr.type.value_type):
+        vals, offs, sizes = arr.values.to_pylist(), arr.offsets.to_pylist(), arr.sizes.to_pylist()
+        valid = arr.is_valid().to_pylist()
+        return [vals[offs[i]: offs[i] + sizes[i]] if valid[i] else None for i in range(len(arr))]
+    if (pa.types.is_list(arr.type) or pa.types.is_large_list(arr.type)) and pa.types.is_union(arr.type.value_type):
         vals = arr.values.to_pylist()
         offs = arr.offsets.to_pylist()
         valid = arr.is_valid().to_pylist()

@@ -171,18 +171,23 @@ def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[byt
         if pa.types.is_struct(t):
             kids = [build(t.field(i).type) for i in range(t.num_fields)]
             return pa.StructArray.from_buffers(t, length, [validity], nulls, children=kids)
-        if pa.types.is_list(t) or pa.types.is_map(t):
-            offs = take_buf() or pa.py_buffer(b"\0\0\0\0")
+        if pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t):
+            offs = take_buf() or pa.py_buffer(b"\0" * 8)
             if pa.types.is_map(t):
                 child = build(pa.struct([pa.field("key", t.key_type, nullable=False), pa.field("value", t.item_type)]))
             else:
                 child = build(t.value_type)
             return pa.Array.from_buffers(t, length, [validity, offs], nulls, children=[child])
+        if pa.types.is_list_view(t) or pa.types.is_large_list_view(t):
+            offs, sizes = take_buf() or pa.py_buffer(b""), take_buf() or pa.py_buffer(b"")
+            child = build(t.value_type)
+            return pa.Array.from_buffers(t, length, [validity, offs, sizes], nulls, children=[child])
         if pa.types.is_fixed_size_list(t):
             child = build(t.value_type)
             return pa.Array.from_buffers(t, length, [validity], nulls, children=[child])
-        if pa.types.is_string(t) or pa.types.is_binary(t):
-            offs = take_buf() or pa.py_buffer(b"\0\0\0\0")
+        if (pa.types.is_string(t) or pa.types.is_binary(t) or pa.types.is_large_string(t)
+                or pa.types.is_large_binary(t)):
+            offs = take_buf() or pa.py_buffer(b"\0" * 8)
             data = take_buf() or pa.py_buffer(b"")
             return pa.Array.from_buffers(t, length, [validity, offs, data], nulls)
         data = take_buf() or pa.py_buffer(b"")
@@ -191,3 +196,34 @@ def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[byt
     out = [build(t) for t in types]
     assert ni[0] == len(nodes) and bi[0] == len(buffers), "nodes / buffers not fully consumed"
     return out
+
+
+def writer_type(t: pa.DataType, large: bool = False, view: bool = False) -> pa.DataType:
+    """The Arrow type the reference's converter gives the same DuckDB type under SET arrow_large_buffer_size = true
+    (arrow_converter.cpp:179-196,262-293: utf8 -> large_utf8, binary -> large_binary, list -> large_list) and / or SET
+    arrow_output_list_view = true (:282-287: list -> list_view / large_list_view); map, struct and fixed-size list keep
+    their kind, their children change."""
+    def rec(x):
+        return writer_type(x, large, view)
+    if pa.types.is_string(t):
+        return pa.large_string() if large else t
+    if pa.types.is_binary(t):
+        return pa.large_binary() if large else t
+    if pa.types.is_list(t):
+        f = t.value_field.with_type(rec(t.value_type))
+        if view:
+            return pa.large_list_view(f) if large else pa.list_view(f)
+        return pa.large_list(f) if large else pa.list_(f)
+    if pa.types.is_fixed_size_list(t):
+        return pa.list_(t.value_field.with_type(rec(t.value_type)), t.list_size)
+    if pa.types.is_map(t):
+        return pa.map_(rec(t.key_type), t.item_field.with_type(rec(t.item_type)))
+    if pa.types.is_struct(t):
+        return pa.struct([t.field(i).with_type(rec(t.field(i).type)) for i in range(t.num_fields)])
+    if pa.types.is_union(t):
+        return pa.sparse_union([t.field(i).with_type(rec(t.field(i).type)) for i in range(t.num_fields)], t.type_codes)
+    return t
+
+
+def large_type(t: pa.DataType) -> pa.DataType:
+    return writer_type(t, large=True)
