@@ -518,7 +518,7 @@ int b2a_writer_headers(b2a_writer *w, void *h_stream) {
 				buffers.push_back(n.buf[k]);
 			}
 		}
-		std::vector<uint8_t> msg = EncodeRecordBatchMessage(b.rows, nodes, buffers, b.body_length);
+		std::vector<uint8_t> msg = EncodeRecordBatchMessage(b.rows, nodes, buffers, b.body_length, p.n_variadic);
 		if (msg.size() != p.batch_header_bytes) {
 			return SetLastError(B2A_EINTERNAL, "writer: record batch header size changed after layout");
 		}

@@ -97,7 +97,7 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		break;
 	}
 	case B2A_T_VARCHAR:
-		empty(f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
+		empty(f.string_view ? ArrowTypeTag::Utf8View : f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
 		break;
 	case B2A_T_BLOB:
 	case B2A_T_BIT: // arrow_converter.cpp:268-279 without arrow_lossless_conversion: plain binary
@@ -279,7 +279,7 @@ void ResolveArrowFormat(WriteField &f) {
 		break;
 	case B2A_T_VARCHAR:
 	case B2A_T_UUID:
-		f.format = f.large_offsets ? "U" : "u";
+		f.format = f.string_view ? "vu" : f.large_offsets ? "U" : "u";
 		break;
 	case B2A_T_BLOB:
 	case B2A_T_BIT:
@@ -387,8 +387,12 @@ std::vector<uint8_t> EncodeSchemaMessage(const std::vector<WriteField> &fields,
 }
 
 std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<NodeSlice> &nodes,
-                                              const std::vector<BufferSlice> &buffers, uint64_t body_length) {
+                                              const std::vector<BufferSlice> &buffers, uint64_t body_length,
+                                              size_t n_variadic) {
 	fb::Builder b;
+	// RecordBatch.variadicBufferCounts (field 4): one entry per view-typed field in pre-order, each with its ONE data buffer
+	const std::vector<int64_t> counts(n_variadic, 1);
+	uint32_t var_vec = n_variadic ? b.create_struct_vector(counts.data(), counts.size(), 8, 8) : 0;
 	static_assert(sizeof(NodeSlice) == 16 && sizeof(BufferSlice) == 16, "FieldNode / Buffer structs are 16 bytes");
 	uint32_t buf_vec = b.create_struct_vector(buffers.data(), buffers.size(), 16, 8);
 	uint32_t node_vec = b.create_struct_vector(nodes.data(), nodes.size(), 16, 8);
@@ -396,15 +400,18 @@ std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<N
 	b.add_scalar_force<int64_t>(0, static_cast<int64_t>(rows));
 	b.add_offset(1, node_vec);
 	b.add_offset(2, buf_vec);
+	if (var_vec) {
+		b.add_offset(4, var_vec);
+	}
 	uint32_t rb = b.end_table();
 	return FinishMessage(b, 3 /* MessageHeader::RecordBatch */, rb, static_cast<int64_t>(body_length));
 }
 
-size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers) {
+size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers, size_t n_variadic) {
 	// scalar fields are elided when they equal their default, so size the message with non-default values
 	std::vector<NodeSlice> nodes(n_nodes, NodeSlice {1, 1});
 	std::vector<BufferSlice> buffers(n_buffers, BufferSlice {8, 8});
-	return EncodeRecordBatchMessage(1, nodes, buffers, 8).size();
+	return EncodeRecordBatchMessage(1, nodes, buffers, 8, n_variadic).size();
 }
 
 std::vector<uint8_t> EncodeEndOfStream() {

@@ -22,6 +22,7 @@ struct WriteField {
 	int decimal_width = 0, decimal_scale = 0;
 	int64_t param = 0; // ARRAY size
 	std::string timezone;
+	bool string_view = false;   // produce_arrow_string_view: "vu"
 	bool list_view = false;     // arrow_output_list_view: "+vl" / "+vL"
 	bool large_offsets = false; // arrow_large_buffer_size: "U" / "Z" / "+L" (set by the write planner)
 	std::vector<WriteField> children;
@@ -35,9 +36,10 @@ void ResolveArrowFormat(WriteField &f);
 std::vector<uint8_t> EncodeSchemaMessage(const std::vector<WriteField> &fields,
                                          const std::vector<std::pair<std::string, std::string>> &kv_metadata);
 std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<NodeSlice> &nodes,
-                                              const std::vector<BufferSlice> &buffers, uint64_t body_length);
+                                              const std::vector<BufferSlice> &buffers, uint64_t body_length,
+                                              size_t n_variadic = 0);
 // size of a RecordBatch message header with the given node / buffer counts (independent of the values)
-size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers);
+size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers, size_t n_variadic = 0);
 // ArrowStreamWriter::Finalize: FFFFFFFF 00000000
 std::vector<uint8_t> EncodeEndOfStream();
 

@@ -25,7 +25,9 @@ enum b2a_enc_op {
 	B2A_ENC_UUID64,       /* ArrowVarcharData<hugeint_t, ArrowUUIDConverter> (int64 offsets, arrow_large_buffer_size) */
 	B2A_ENC_LISTVIEW32,   /* ArrowListViewData<int32_t>::AppendListMetadata, list_view_data.hpp:59-103: offsets -> dst,
 	                         sizes -> dst2, `rows` entries each; a NULL row = {running offset, 0} */
-	B2A_ENC_LISTVIEW64
+	B2A_ENC_LISTVIEW64,
+	B2A_ENC_STRINGVIEW    /* ArrowVarcharToStringViewData::Append, varchar_data.hpp:136-187: arrow_string_view_t[rows] -> dst,
+	                         the characters of the strings longer than 12 bytes -> dst2 (buffer index 0, int32 offset) */
 };
 
 #define B2A_ENC_OP_IS_RARE(op) ((op) >= B2A_ENC_TIMETZ)

@@ -107,6 +107,9 @@ __device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i,
 	if (t.op == B2A_ENC_STRING32 || t.op == B2A_ENC_STRING64) {
 		return e.x; // string_t.length
 	}
+	if (t.op == B2A_ENC_STRINGVIEW) {
+		return e.x > 12u ? e.x : 0; // only the non-inlined strings reach the data buffer
+	}
 	if (t.op == B2A_ENC_UUID32 || t.op == B2A_ENC_UUID64) {
 		return 36; // UUID::STRING_SIZE (ArrowUUIDConverter::GetLength, varchar_data.hpp:33-37); e = the hugeint_t
 	}
@@ -923,6 +926,66 @@ __device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restr
 	}
 }
 
+// ArrowVarcharToStringViewData::Append (varchar_data.hpp:136-187): one 16-byte view per row — NULL: zeros; length <= 12:
+// {length, bytes, zero padding}; longer: {length, first 4 bytes, buffer index 0, int32 offset} with the characters
+// appended to the single data buffer (dst2).  Rare op: one thread copies its own long strings.
+__device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                                uint32_t *err) {
+	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	uint4 e[kRowsPerThread];
+	uint32_t len[kRowsPerThread]; // bytes that go to the data buffer (0 for NULL / inlined rows)
+	bool valid[kRowsPerThread];
+	uint64_t sum = 0;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		len[u] = 0;
+		valid[u] = false;
+		e[u] = make_uint4(0, 0, 0, 0);
+		if (i < t.rows) {
+			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid[u]));
+		}
+		sum += len[u];
+	}
+	uint64_t window;
+	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+	uint64_t run = tile_base + block_exclusive_scan(sum, &window);
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		if (i >= t.rows) {
+			continue;
+		}
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (valid[u] && len[u] == 0) { // inlined: string_t and the view share the layout; bytes past the length are zeroed
+			const uint32_t n = e[u].x;
+			auto keep = [n](uint32_t w, uint32_t first) {
+				return n >= first + 4 ? w : n <= first ? 0u : (w & ((1u << (8 * (n - first))) - 1u));
+			};
+			v = make_uint4(n, keep(e[u].y, 0), keep(e[u].z, 4), keep(e[u].w, 8));
+		} else if (valid[u]) {
+			if (run > 0x7FFFFFFFull) { // the view's offset is an int32 (UnsafeNumericCast<int32_t>(append_data.offset))
+				enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
+			}
+			v = make_uint4(e[u].x, e[u].y, 0u, static_cast<uint32_t>(run));
+			const uint8_t *src = reinterpret_cast<const uint8_t *>((static_cast<uintptr_t>(e[u].w) << 32) | e[u].z);
+			uint8_t *dst = stream + t.dst2 + run;
+			for (uint32_t b = 0; b < len[u]; b++) {
+				dst[b] = __ldg(src + b);
+			}
+			run += len[u];
+		}
+		// buffers start on 8-byte boundaries of the stream (not 16): two 8-byte stores
+		uint2 *o = reinterpret_cast<uint2 *>(stream + t.dst) + 2 * i;
+		o[0] = make_uint2(v.x, v.y);
+		o[1] = make_uint2(v.z, v.w);
+	}
+	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the data buffer up to 8 bytes
+		const uint64_t total = tile_base + window;
+		zero_range(stream, t.dst2 + total, t.dst2 + align8(total));
+	}
+}
+
 // ------------------------------------------------------------------------------------------------
 // the encode kernel: persistent CTAs stride over the tile table, next descriptor prefetched with cp.async
 // ------------------------------------------------------------------------------------------------
@@ -1018,6 +1081,8 @@ __global__ void __launch_bounds__(kThreads, 4)
 					enc_list<int32_t, true>(t, stream, k, err);
 				} else if (t.op == B2A_ENC_LISTVIEW64) {
 					enc_list<int64_t, true>(t, stream, k, err);
+				} else if (t.op == B2A_ENC_STRINGVIEW) {
+					enc_string_view(t, stream, k, err);
 				}
 			}
 			break;

@@ -72,6 +72,11 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 2;
 		break;
 	case B2A_T_UUID: // ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>, arrow_appender.cpp:180-191
+		if (string_view) {
+			// the reference declares "vu" for a UUID column (arrow_converter.cpp:176-177) but appends offsets + characters
+			// (arrow_appender.cpp:180-191): schema and buffers disagree there, nothing to be compatible with
+			throw Error(B2A_ENOTIMPL, "writer: UUID columns under produce_arrow_string_view are not supported");
+		}
 		w.op = large_offsets ? B2A_ENC_UUID64 : B2A_ENC_UUID32;
 		w.src_width = 16;
 		w.dst_width = large_offsets ? 8 : 4;
@@ -105,6 +110,14 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 2;
 		break;
 	case B2A_T_VARCHAR:
+		if (string_view) { // ArrowVarcharToStringViewData, arrow_appender.cpp:234-235: validity, views, one data buffer
+			w.op = B2A_ENC_STRINGVIEW;
+			w.src_width = w.dst_width = 16;
+			w.n_buffers = 3;
+			wf.string_view = true;
+			break;
+		}
+		/* fall through */
 	case B2A_T_BLOB:
 	case B2A_T_BIT: // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
 		w.op = large_offsets ? B2A_ENC_STRING64 : B2A_ENC_STRING32;
@@ -183,6 +196,7 @@ void WritePlan::Build(const b2a_vector *columns, uint32_t n_columns, uint64_t ro
 	row_group_size = (opt && opt->row_group_size) ? opt->row_group_size : 122880;
 	large_offsets = opt && (opt->flags & B2A_WRITE_LARGE_OFFSETS);
 	list_view = opt && (opt->flags & B2A_WRITE_LIST_VIEW);
+	string_view = opt && (opt->flags & B2A_WRITE_STRING_VIEW);
 	if (opt) {
 		for (uint32_t i = 0; i < opt->n_kv_metadata; i++) {
 			kv_metadata.emplace_back(opt->kv_keys[i], opt->kv_values[i]);
@@ -325,7 +339,11 @@ void WritePlan::Layout() {
 		if (bi == 0) {
 			n_nodes = b.preorder.size();
 			n_buffers = nb;
-			batch_header_bytes = RecordBatchMessageSize(n_nodes, n_buffers);
+			n_variadic = 0;
+			for (int ni : b.preorder) {
+				n_variadic += vecs[static_cast<size_t>(nodes[static_cast<size_t>(ni)].vec)].op == B2A_ENC_STRINGVIEW;
+			}
+			batch_header_bytes = RecordBatchMessageSize(n_nodes, n_buffers, n_variadic);
 		}
 		b.meta_offset = cursor;
 		b.body_offset = cursor + batch_header_bytes;

@@ -69,6 +69,8 @@ struct WritePlan {
 	uint64_t row_group_size = 122880;
 	bool large_offsets = false; // B2A_WRITE_LARGE_OFFSETS
 	bool list_view = false;     // B2A_WRITE_LIST_VIEW
+	bool string_view = false;   // B2A_WRITE_STRING_VIEW
+	size_t n_variadic = 0;      // string-view nodes per batch: RecordBatch.variadicBufferCounts = [1] * n_variadic
 	uint64_t total_rows = 0;
 
 	std::vector<uint8_t> schema_message;
@@ -93,7 +95,8 @@ struct WritePlan {
 
 	static bool IsScanOp(int op) {
 		return op == B2A_ENC_STRING32 || op == B2A_ENC_STRING64 || op == B2A_ENC_LIST32 || op == B2A_ENC_LIST64 ||
-		       op == B2A_ENC_UUID32 || op == B2A_ENC_UUID64 || op == B2A_ENC_LISTVIEW32 || op == B2A_ENC_LISTVIEW64;
+		       op == B2A_ENC_UUID32 || op == B2A_ENC_UUID64 || op == B2A_ENC_LISTVIEW32 || op == B2A_ENC_LISTVIEW64 ||
+		       op == B2A_ENC_STRINGVIEW;
 	}
 	static bool IsListViewOp(int op) {
 		return op == B2A_ENC_LISTVIEW32 || op == B2A_ENC_LISTVIEW64;

@@ -369,6 +369,10 @@ typedef struct b2a_write_options {
  * ArrowListViewData, an offsets and a sizes buffer of `rows` entries each (appender/list_view_data.hpp:59-103,
  * arrow_appender.cpp:281-286, arrow_converter.cpp:282-287).  MAP is not affected. */
 #define B2A_WRITE_LIST_VIEW 0x2u
+/* SET produce_arrow_string_view = true: VARCHAR -> "vu" (ArrowVarcharToStringViewData, appender/varchar_data.hpp:129-202;
+ * arrow_appender.cpp:234-235, arrow_converter.cpp:189-190): 16-byte views + ONE variadic data buffer holding the strings
+ * longer than 12 bytes end to end (RecordBatch.variadicBufferCounts = [1] per such field).  BLOB / BIT keep offsets. */
+#define B2A_WRITE_STRING_VIEW 0x4u
 
 typedef struct b2a_writer b2a_writer;
 

@@ -43,13 +43,18 @@ def _validity_buffer(valid: np.ndarray) -> tuple[bytes, int]:
     return np.packbits(bits, bitorder="little").tobytes(), int(n - valid.sum())
 
 
-def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False, view: bool = False):
+def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False, view: bool = False,
+           sview: bool = False):
     """Append rows `idx` (input row indices: the UnifiedVectorFormat selection) of vector hv; pre-order output.
     nodes: [(length, null_count)], buffers: [bytes] (unpadded).
     large: ClientProperties.arrow_offset_size == LARGE (SET arrow_large_buffer_size): int64 offsets for VARCHAR / BLOB /
     BIT / UUID / LIST (arrow_appender.cpp:184-188,237-251,288-292); MAP stays int32 (:296-299).
     view: ClientProperties.arrow_use_list_view (SET arrow_output_list_view): LIST -> ArrowListViewData, an offsets and a
-    sizes buffer of n entries each (appender/list_view_data.hpp:59-103); MAP is not affected."""
+    sizes buffer of n entries each (appender/list_view_data.hpp:59-103); MAP is not affected.
+    sview: ClientProperties.produce_arrow_string_view: VARCHAR -> ArrowVarcharToStringViewData (varchar_data.hpp:129-202):
+    16-byte views {length, 12 bytes zero padded} / {length, first 4 bytes, buffer index 0, int32 offset} (NULL: zeros) and
+    one data buffer with the strings longer than 12 bytes; the fourth C-data buffer (data-buffer sizes) is not part of the
+    IPC body (it becomes RecordBatch.variadicBufferCounts)."""
     off_t = np.int64 if large else np.int32
     n = len(idx)
     t = hv.type
@@ -69,7 +74,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
             import copy
             member = copy.copy(c)
             member.validity = valid_full & (tags_full == m) & own
-            append(member, idx, nodes, buffers, large, view)
+            append(member, idx, nodes, buffers, large, view, sview)
         return
     valid = _valid(hv, idx)
     vbuf, nulls = _validity_buffer(valid)
@@ -96,6 +101,26 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
     elif t == "TIME_TZ":  # dtime_tz_t: micros in the upper 40 bits (OFFSET_BITS = 24); NULL slots unwritten (0 here)
         bits = hv.data.view(np.uint64)[idx]
         buffers.append(np.where(valid, bits >> np.uint64(24), 0).astype(np.int64).tobytes())
+    elif t == "VARCHAR" and sview:
+        slen = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
+        is_long = slen > 12
+        long_len = np.where(is_long, slen, 0)
+        offs = np.zeros(n + 1, np.int64)
+        np.cumsum(long_len, out=offs[1:])
+        views = np.zeros((n, 16), np.uint8)
+        views[:, 0:4] = slen.astype("<u4").view(np.uint8).reshape(n, 4)
+        head = np.minimum(slen, np.where(is_long, 4, 12))  # bytes stored in the view itself
+        tot = int(head.sum())
+        if tot:
+            r = np.repeat(np.arange(n), head)
+            c = np.arange(tot, dtype=np.int64) - np.repeat(np.cumsum(head) - head, head)
+            views[r, 4 + c] = hv.heap[np.repeat(hv.str_start[idx], head) + c]
+        views[is_long, 12:16] = offs[:-1][is_long].astype("<i4").view(np.uint8).reshape(-1, 4)
+        total = int(offs[-1])
+        pos = (np.arange(total, dtype=np.int64) - np.repeat(offs[:-1], long_len)
+               + np.repeat(hv.str_start[idx], long_len))
+        buffers.append(views.tobytes())
+        buffers.append(hv.heap[pos].tobytes() if total else b"")
     elif t in ("VARCHAR", "BLOB", "BIT"):
         length = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
         offs = np.zeros(n + 1, np.int64)
@@ -126,14 +151,14 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
         child = hv.children[0]
         if t == "MAP":
             child._no_validity_buffer = True  # the entries struct's validity buffer is never resized (map_data.hpp)
-        append(child, child_sel, nodes, buffers, large, view)
+        append(child, child_sel, nodes, buffers, large, view, sview)
     elif t == "STRUCT":
         for c in hv.children:
-            append(c, idx, nodes, buffers, large, view)
+            append(c, idx, nodes, buffers, large, view, sview)
     elif t == "ARRAY":
         k = hv.param
         child_idx = (idx[:, None] * k + np.arange(k)[None, :]).reshape(-1)
-        append(hv.children[0], child_idx, nodes, buffers, large, view)
+        append(hv.children[0], child_idx, nodes, buffers, large, view, sview)
     elif t == "DECIMAL" and hv.decimal[0] <= 4:
         buffers.append(hv.data.view(np.int16)[idx].astype(np.int32).tobytes())
     elif t == "INTERVAL":
@@ -148,7 +173,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
 
 
 def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, large: bool = False,
-                      view: bool = False):
+                      view: bool = False, sview: bool = False):
     """-> [(rows, nodes, buffers[(offset, length)], body bytes)] per record batch"""
     out = []
     for r0 in range(0, rows, row_group_size):
@@ -156,7 +181,7 @@ def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, l
         idx = np.arange(r0, r0 + n, dtype=np.int64)
         nodes, bufs = [], []
         for c in columns:
-            append(c, idx, nodes, bufs, large, view)
+            append(c, idx, nodes, bufs, large, view, sview)
         body, slices = b"", []
         for b in bufs:
             slices.append((len(body), len(b)))

@@ -108,6 +108,30 @@ def test_device_layout_path_on_integration_files(b2a, cuda_device, name, endian)
     compare_scan_with_oracle(ds, _pa_batches(path))
 
 
+@pytest.mark.parametrize("host_alias", [True, False])
+def test_string_views_written_by_pyarrow(b2a, cuda_device, host_alias):
+    """Utf8View columns (SetVectorStringView, arrow_conversion.cpp:425-452; a10): inlined, prefixed and NULL
+    views, top level and below a list, several batches — vs the oracle over pyarrow's decoding of the same stream"""
+    rng = np.random.default_rng(21)
+    words = ["", "a", "twelve bytes", "thirteen bytes", "a considerably longer string value", "x" * 100]
+    n = 9000
+    pick = rng.integers(0, len(words), n)
+    s = [None if rng.random() < 0.1 else words[int(k)] + str(i % 97) for i, k in enumerate(pick)]
+    t = pa.table({
+        "sv": pa.array(s, pa.string_view()),
+        "l_sv": pa.array([None if i % 11 == 0 else [s[i], s[(i * 7) % n]][: i % 3] for i in range(n)],
+                         pa.list_(pa.string_view())),
+        "i": pa.array(np.arange(n, dtype=np.int64)),
+    })
+    sink = pa.BufferOutputStream()
+    with ipc.new_stream(sink, t.schema) as w:
+        for b in t.to_batches(max_chunksize=2500):
+            w.write_batch(b)
+    buf = sink.getvalue().to_pybytes()
+    ds = b2a.scan_arrow_ipc([buf], host_alias=host_alias)
+    compare_scan_with_oracle(ds, list(ipc.open_stream(buf)))
+
+
 def test_host_alias_scan_rejects_device_consumers(b2a, cuda_device):
     from tools import lineitem
     buf = lineitem.stream_bytes(5000, seed=2)

@@ -279,3 +279,24 @@ def test_writer_schema_message_list_views(b2a):
         assert sch.field("l").type == lv(pa.field("l", s))
         assert sch.field("ll").type == lv(pa.field("l", lv(pa.field("l", pa.int32()))))
         assert sch.field("m").type == pa.map_(s, lv(pa.field("l", pa.int64())))
+
+
+def test_writer_schema_message_string_views(b2a):
+    """B2A_WRITE_STRING_VIEW = SET produce_arrow_string_view: VARCHAR -> "vu" at every level, BLOB keeps "z"
+    (arrow_converter.cpp:189-197,262-267); a UUID column is refused (the reference's schema and appender disagree there)."""
+    import pyarrow.ipc as ipc
+    from duckdb_arrow_b200 import B2AError, DeviceVector as DV
+
+    def v(t, name, kids=(), **kw):
+        return DV(t, 0, None, None, list(kids), name, **kw)
+
+    cols = [v("VARCHAR", "s"), v("BLOB", "z"), v("LIST", "l", [v("VARCHAR", "x")]),
+            v("MAP", "m", [v("STRUCT", "e", [v("VARCHAR", "k"), v("BIGINT", "v")])])]
+    w = b2a.ArrowWriter(cols, 0, device=-1, produce_arrow_string_view=True, arrow_large_buffer_size=True)
+    sch = ipc.read_schema(pa.py_buffer(w.schema_message()))
+    w.close()
+    assert sch.field("s").type == pa.string_view() and sch.field("z").type == pa.large_binary()
+    assert sch.field("l").type == pa.large_list(pa.field("l", pa.string_view()))
+    assert sch.field("m").type == pa.map_(pa.string_view(), pa.int64())
+    with pytest.raises(B2AError, match="UUID"):
+        b2a.ArrowWriter([v("UUID", "id")], 0, device=-1, produce_arrow_string_view=True)

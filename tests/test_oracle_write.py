@@ -137,3 +137,38 @@ def test_write_oracle_list_views(case, rgs, large):
             assert pylist(arr) == expected[name][row: row + n], name
         row += n
     assert row == rows
+
+
+@pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("nested", 1000), ("lineitem", 5000)])
+def test_write_oracle_string_views(case, rgs):
+    """SET produce_arrow_string_view = true (ArrowVarcharToStringViewData, varchar_data.hpp:129-202): VARCHAR columns (also
+    below lists / structs / maps) become views + one data buffer holding only the strings longer than 12 bytes; pyarrow
+    validates the views (prefix, buffer index, offset) and rebuilds the same rows."""
+    table = {"scalar": lambda: scalar_table(5000), "nested": lambda: nested_table(3000),
+             "lineitem": lambda: _lineitem(12_345)}[case]()
+    cols, names, types = table_vectors(table), table.schema.names, [f.type for f in table.schema]
+    vtypes = [writer_type(t, sview=True) for t in types]
+    assert vtypes != types
+    row = 0
+    for n, nodes, slices, body in OW.serialize_batches(cols, table.num_rows, rgs, sview=True):
+        bufs = [body[o:o + l] for o, l in slices]
+        arrays = arrays_from_buffers(vtypes, nodes, bufs)
+        for arr, name in zip(arrays, names):
+            arr.validate(full=True)
+            assert pylist(arr) == pylist(table.column(name).slice(row, n)), name
+        row += n
+    assert row == table.num_rows
+
+
+def test_string_view_layout():
+    """the three view forms: NULL = 16 zero bytes; <= 12 bytes inlined and zero padded; longer = prefix + index 0 + offset"""
+    t = pa.table({"s": pa.array(["", "abc", None, "exactly12byt", "thirteen bytes", None, "a second long string"])})
+    (n, nodes, slices, body), = OW.serialize_batches(table_vectors(t), 7, 100, sview=True)
+    views = np.frombuffer(body[slices[1][0]: slices[1][0] + slices[1][1]], np.uint8).reshape(7, 16)
+    data = body[slices[2][0]: slices[2][0] + slices[2][1]]
+    assert nodes == [(7, 2)] and data == b"thirteen bytesa second long string"
+    assert views[0].tobytes() == bytes(16) and views[2].tobytes() == bytes(16) and views[5].tobytes() == bytes(16)
+    assert views[1].tobytes() == b"\x03\0\0\0abc" + bytes(9)
+    assert views[3].tobytes() == b"\x0c\0\0\0exactly12byt"
+    assert views[4].tobytes() == b"\x0e\0\0\0thir" + bytes(4) + bytes(4)
+    assert views[6].tobytes() == b"\x14\0\0\0a se" + bytes(4) + b"\x0e\0\0\0"

@@ -182,6 +182,9 @@ def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[byt
             offs, sizes = take_buf() or pa.py_buffer(b""), take_buf() or pa.py_buffer(b"")
             child = build(t.value_type)
             return pa.Array.from_buffers(t, length, [validity, offs, sizes], nulls, children=[child])
+        if pa.types.is_string_view(t):  # validity, views, the one variadic data buffer
+            views, data = take_buf() or pa.py_buffer(b""), take_buf() or pa.py_buffer(b"")
+            return pa.Array.from_buffers(t, length, [validity, views, data], nulls)
         if pa.types.is_fixed_size_list(t):
             child = build(t.value_type)
             return pa.Array.from_buffers(t, length, [validity], nulls, children=[child])
@@ -198,15 +201,15 @@ def arrays_from_buffers(types: list[pa.DataType], nodes: list, buffers: list[byt
     return out
 
 
-def writer_type(t: pa.DataType, large: bool = False, view: bool = False) -> pa.DataType:
+def writer_type(t: pa.DataType, large: bool = False, view: bool = False, sview: bool = False) -> pa.DataType:
     """The Arrow type the reference's converter gives the same DuckDB type under SET arrow_large_buffer_size = true
     (arrow_converter.cpp:179-196,262-293: utf8 -> large_utf8, binary -> large_binary, list -> large_list) and / or SET
     arrow_output_list_view = true (:282-287: list -> list_view / large_list_view); map, struct and fixed-size list keep
     their kind, their children change."""
     def rec(x):
-        return writer_type(x, large, view)
-    if pa.types.is_string(t):
-        return pa.large_string() if large else t
+        return writer_type(x, large, view, sview)
+    if pa.types.is_string(t):  # produce_arrow_string_view wins over the offset size (arrow_converter.cpp:189-197)
+        return pa.string_view() if sview else pa.large_string() if large else t
     if pa.types.is_binary(t):
         return pa.large_binary() if large else t
     if pa.types.is_list(t):
