@@ -27,6 +27,8 @@ def main():
     ap.add_argument("--row-group-size", type=int, default=122_880)
     ap.add_argument("--verify-batches", type=int, default=3)
     ap.add_argument("--columns", default="", help="comma-separated subset (experiments)")
+    ap.add_argument("--large-offsets", action="store_true", help="SET arrow_large_buffer_size = true")
+    ap.add_argument("--string-view", action="store_true", help="SET produce_arrow_string_view = true")
     args = ap.parse_args()
     import pyarrow as pa
     import pyarrow.ipc as ipc
@@ -61,7 +63,8 @@ def main():
     stream = torch.cuda.current_stream()
 
     def new_writer():
-        return b2a.ArrowWriter(cols, rows, args.row_group_size)
+        return b2a.ArrowWriter(cols, rows, args.row_group_size, arrow_large_buffer_size=args.large_offsets,
+                               produce_arrow_string_view=args.string_view)
 
     w = new_writer()
     w.measure()
@@ -112,7 +115,8 @@ def main():
         "roofline": {"bound": "hbm", "kernel": "b2a_encode_kernel", "achieved": alg / (encode_ms / 1e3) / 1e9,
                      "peak": peak, "peak_kind": kind, "unit": "GB/s", "frac": alg / (encode_ms / 1e3) / 1e9 / peak},
         "verified_batches_equal_source": bool(ok), "gpu_launches_per_copy": int(w2.gpu_launches if False else 3),
-        "config": {"workload": f"lineitem SF{args.sf:g} COPY TO arrows, row_group_size {args.row_group_size}"}}))
+        "config": {"workload": f"lineitem SF{args.sf:g} COPY TO arrows, row_group_size {args.row_group_size}",
+                   "arrow_large_buffer_size": args.large_offsets, "produce_arrow_string_view": args.string_view}}))
 
 
 if __name__ == "__main__":
