@@ -928,7 +928,7 @@ __device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restr
 
 // ArrowVarcharToStringViewData::Append (varchar_data.hpp:136-187): one 16-byte view per row — NULL: zeros; length <= 12:
 // {length, bytes, zero padding}; longer: {length, first 4 bytes, buffer index 0, int32 offset} with the characters
-// appended to the single data buffer (dst2).  Rare op: one thread copies its own long strings.
+// appended to the single data buffer (dst2).  Rare op: the long strings are copied one at a time per warp, bytes strided over the lanes.
 __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                                 uint32_t *err) {
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
@@ -950,9 +950,13 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 	uint64_t window;
 	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
 	uint64_t run = tile_base + block_exclusive_scan(sum, &window);
+	unsigned long long cp_src[kRowsPerThread], cp_dst[kRowsPerThread];
+	uint32_t cp_len[kRowsPerThread];
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		const uint64_t i = row0 + threadIdx.x * kRowsPerThread + u;
+		cp_len[u] = 0;
+		cp_src[u] = cp_dst[u] = 0;
 		if (i >= t.rows) {
 			continue;
 		}
@@ -968,17 +972,31 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 				enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
 			}
 			v = make_uint4(e[u].x, e[u].y, 0u, static_cast<uint32_t>(run));
-			const uint8_t *src = reinterpret_cast<const uint8_t *>((static_cast<uintptr_t>(e[u].w) << 32) | e[u].z);
-			uint8_t *dst = stream + t.dst2 + run;
-			for (uint32_t b = 0; b < len[u]; b++) {
-				dst[b] = __ldg(src + b);
-			}
+			cp_src[u] = (static_cast<unsigned long long>(e[u].w) << 32) | e[u].z;
+			cp_dst[u] = t.dst2 + run;
+			cp_len[u] = len[u];
 			run += len[u];
 		}
 		// buffers start on 8-byte boundaries of the stream (not 16): two 8-byte stores
 		uint2 *o = reinterpret_cast<uint2 *>(stream + t.dst) + 2 * i;
 		o[0] = make_uint2(v.x, v.y);
 		o[1] = make_uint2(v.z, v.w);
+	}
+	// the long strings, one at a time per warp with the bytes strided over the lanes: coalesced loads and stores
+	const uint32_t lane = threadIdx.x & 31u;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		unsigned m = __ballot_sync(0xFFFFFFFFu, cp_len[u] != 0);
+		while (m) {
+			const int owner = __ffs(m) - 1;
+			m &= m - 1;
+			const uint8_t *src = reinterpret_cast<const uint8_t *>(__shfl_sync(0xFFFFFFFFu, cp_src[u], owner));
+			uint8_t *dst = stream + __shfl_sync(0xFFFFFFFFu, cp_dst[u], owner);
+			const uint32_t n = __shfl_sync(0xFFFFFFFFu, cp_len[u], owner);
+			for (uint32_t b = lane; b < n; b += 32) {
+				dst[b] = __ldg(src + b);
+			}
+		}
 	}
 	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the data buffer up to 8 bytes
 		const uint64_t total = tile_base + window;
