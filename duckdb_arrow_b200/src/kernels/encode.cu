@@ -982,19 +982,38 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 		o[0] = make_uint2(v.x, v.y);
 		o[1] = make_uint2(v.z, v.w);
 	}
-	// the long strings, one at a time per warp with the bytes strided over the lanes: coalesced loads and stores
+	// the long strings: four at a time per warp (independent loads in flight), the bytes of each strided over the lanes
+	// — coalesced loads and stores; bytes past the first 32 of a string follow in a per-string loop
 	const uint32_t lane = threadIdx.x & 31u;
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		unsigned m = __ballot_sync(0xFFFFFFFFu, cp_len[u] != 0);
 		while (m) {
-			const int owner = __ffs(m) - 1;
-			m &= m - 1;
-			const uint8_t *src = reinterpret_cast<const uint8_t *>(__shfl_sync(0xFFFFFFFFu, cp_src[u], owner));
-			uint8_t *dst = stream + __shfl_sync(0xFFFFFFFFu, cp_dst[u], owner);
-			const uint32_t n = __shfl_sync(0xFFFFFFFFu, cp_len[u], owner);
-			for (uint32_t b = lane; b < n; b += 32) {
-				dst[b] = __ldg(src + b);
+			const uint8_t *src[4];
+			uint8_t *dst[4];
+			uint32_t n[4];
+			uint8_t byte[4];
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				const int owner = m ? __ffs(m) - 1 : 0;
+				const bool have = m != 0;
+				m &= m - 1;
+				src[q] = reinterpret_cast<const uint8_t *>(__shfl_sync(0xFFFFFFFFu, cp_src[u], owner));
+				dst[q] = stream + __shfl_sync(0xFFFFFFFFu, cp_dst[u], owner);
+				n[q] = have ? __shfl_sync(0xFFFFFFFFu, cp_len[u], owner) : (__shfl_sync(0xFFFFFFFFu, cp_len[u], owner), 0u);
+			}
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				byte[q] = lane < n[q] ? __ldg(src[q] + lane) : 0;
+			}
+#pragma unroll
+			for (int q = 0; q < 4; q++) {
+				if (lane < n[q]) {
+					dst[q][lane] = byte[q];
+				}
+				for (uint32_t b = lane + 32; b < n[q]; b += 32) {
+					dst[q][b] = __ldg(src[q] + b);
+				}
 			}
 		}
 	}
