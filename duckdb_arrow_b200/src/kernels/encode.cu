@@ -1039,8 +1039,11 @@ static_assert(sizeof(b2a_enc_task) % 16 == 0, "b2a_enc_task is copied in 16-byte
 
 // FULL = false: the ops of the common types only (what a lineitem COPY runs); FULL = true adds the rare ones
 // (TIME_TZ, UUID -> string, UNION type ids) — kept out of the common instantiation's switch like on the decode side
+#ifndef B2A_ENC_MIN_BLOCKS
+#define B2A_ENC_MIN_BLOCKS 4 // resident CTAs per SM the register budget is sized for (A/B: -DB2A_ENC_MIN_BLOCKS=5)
+#endif
 template <bool FULL>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
     b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
                       uint8_t *__restrict__ stream, uint32_t *err) {
 	__shared__ b2a_enc_task s_task[2];
