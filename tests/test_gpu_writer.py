@@ -332,3 +332,27 @@ def test_string_views_bit_exact_vs_oracle(b2a, cuda_device, case, rgs):
     from parity import compare_scan_with_oracle
     data = bytes(stream)
     compare_scan_with_oracle(b2a.scan_arrow_ipc([data]), list(ipc.open_stream(pa.BufferReader(data))))
+
+
+@pytest.mark.parametrize("settings", [dict(arrow_large_buffer_size=True), dict(arrow_output_list_view=True),
+                                      dict(produce_arrow_string_view=True),
+                                      dict(arrow_large_buffer_size=True, arrow_output_list_view=True,
+                                           produce_arrow_string_view=True)])
+def test_writer_settings_edge_sizes(b2a, cuda_device, settings):
+    """zero rows, one row, a batch boundary at an odd row count and every setting at once: bodies vs the oracle and the
+    rows pyarrow reads back"""
+    kw = dict(large=settings.get("arrow_large_buffer_size", False), view=settings.get("arrow_output_list_view", False),
+              sview=settings.get("produce_arrow_string_view", False))
+    for table, rgs in [(nested_table(5).slice(0, 0), 100), (nested_table(1, seed=3), 100), (nested_table(777, seed=6), 333),
+                       (scalar_table(1001, seed=8), 1001)]:
+        host = table_vectors(table)
+        w = b2a.ArrowWriter([to_device(h) for h in host], table.num_rows, rgs, **settings)
+        stream = w.write()
+        _bodies_equal(w, stream, OW.serialize_batches(host, table.num_rows, rgs, **kw))
+        rd = ipc.open_stream(pa.py_buffer(stream))
+        assert [f.type for f in rd.schema] == [writer_type(f.type, **kw) for f in table.schema]
+        got = rd.read_all()
+        got.validate(full=True)
+        assert got.num_rows == table.num_rows
+        for name in table.schema.names:
+            assert pylist(got.column(name)) == pylist(table.column(name)), name
