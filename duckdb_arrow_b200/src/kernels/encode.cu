@@ -929,6 +929,10 @@ __device__ __forceinline__ void enc_list(const b2a_enc_task &t, uint8_t *__restr
 // ArrowVarcharToStringViewData::Append (varchar_data.hpp:136-187): one 16-byte view per row — NULL: zeros; length <= 12:
 // {length, bytes, zero padding}; longer: {length, first 4 bytes, buffer index 0, int32 offset} with the characters
 // appended to the single data buffer (dst2).  Rare op: the long strings are copied one at a time per warp, bytes strided over the lanes.
+#ifndef B2A_ENC_VIEW_COPIES
+#define B2A_ENC_VIEW_COPIES 4
+#endif
+static constexpr int kViewCopies = B2A_ENC_VIEW_COPIES; // long strings a warp copies at a time (loads in flight)
 __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                                 uint32_t *err) {
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
@@ -989,12 +993,12 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 	for (int u = 0; u < kRowsPerThread; u++) {
 		unsigned m = __ballot_sync(0xFFFFFFFFu, cp_len[u] != 0);
 		while (m) {
-			const uint8_t *src[4];
-			uint8_t *dst[4];
-			uint32_t n[4];
-			uint8_t byte[4];
+			const uint8_t *src[kViewCopies];
+			uint8_t *dst[kViewCopies];
+			uint32_t n[kViewCopies];
+			uint8_t byte[kViewCopies];
 #pragma unroll
-			for (int q = 0; q < 4; q++) {
+			for (int q = 0; q < kViewCopies; q++) {
 				const int owner = m ? __ffs(m) - 1 : 0;
 				const bool have = m != 0;
 				m &= m - 1;
@@ -1003,11 +1007,11 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 				n[q] = have ? __shfl_sync(0xFFFFFFFFu, cp_len[u], owner) : (__shfl_sync(0xFFFFFFFFu, cp_len[u], owner), 0u);
 			}
 #pragma unroll
-			for (int q = 0; q < 4; q++) {
+			for (int q = 0; q < kViewCopies; q++) {
 				byte[q] = lane < n[q] ? __ldg(src[q] + lane) : 0;
 			}
 #pragma unroll
-			for (int q = 0; q < 4; q++) {
+			for (int q = 0; q < kViewCopies; q++) {
 				if (lane < n[q]) {
 					dst[q][lane] = byte[q];
 				}
