@@ -345,5 +345,17 @@ def main():
         dist.destroy_process_group()
 
 
+def _stdout_for_the_json_line_only():
+    """The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version line to fd 1
+    when NCCL_DEBUG is set in the environment): send fd 1 to stderr for the whole run and keep the real stdout for
+    print()."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real, "w", buffering=1)
+
+
 if __name__ == "__main__":
+    _stdout_for_the_json_line_only()
     main()
+    sys.stdout.flush()
