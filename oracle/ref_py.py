@@ -57,6 +57,10 @@ def lib() -> C.CDLL:
         _lib.ref_export_next.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_char_p, C.c_int]
         _lib.ref_export_end.argtypes = [C.c_void_p]
         _lib.ref_source_id.restype = C.c_char_p
+        _lib.ref_file_open.restype = C.c_void_p
+        _lib.ref_file_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
+        _lib.ref_file_read.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_char_p, C.c_int]
+        _lib.ref_file_close.argtypes = [C.c_void_p]
         err = C.create_string_buffer(512)
         if _lib.ref_open(err, 512) != 0:
             raise RefError(4, err.value.decode())
@@ -176,3 +180,26 @@ def export(sql: str, batch_rows: int = 122_880, flags: int = 0):
 
 def source_id() -> str:
     return lib().ref_source_id().decode()
+
+
+class BufferedFile:
+    """DuckDB's BufferedFileReader (the reference reads every IPC message through it, 4 KiB at a time)."""
+
+    def __init__(self, path: str):
+        err = C.create_string_buffer(512)
+        self._h = lib().ref_file_open(path.encode(), err, 512)
+        if not self._h:
+            raise RefError(4, err.value.decode())
+
+    def read_into(self, location: int, size: int, dst_address: int) -> None:
+        err = C.create_string_buffer(512)
+        if lib().ref_file_read(self._h, location, size, dst_address, err, 512) != 0:
+            raise RefError(4, err.value.decode())
+
+    def close(self):
+        if self._h:
+            lib().ref_file_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()

@@ -15,6 +15,8 @@
 #include "duckdb.hpp"
 #include "duckdb/common/arrow/arrow_converter.hpp"
 #include "duckdb/common/arrow/arrow_wrapper.hpp"
+#include "duckdb/common/file_system.hpp"
+#include "duckdb/common/serializer/buffered_file_reader.hpp"
 #include "duckdb/common/types/vector.hpp"
 #include "duckdb/function/table/arrow.hpp"
 #include "duckdb/function/table_function.hpp"
@@ -30,6 +32,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <vector>
 
 using namespace duckdb;
 
@@ -287,6 +290,24 @@ void slab_reserve(RSlab *s, uint64_t extra, bool with_sel) {
 	s->cap = cap;
 }
 
+// Bytes of heap-owned strings, kept for the last 512 scans (the Python side reads them after the scan returns).
+std::vector<std::vector<char *>> g_kept(1);
+char *keep_bytes(const char *p, uint32_t len) {
+	char *c = (char *)malloc(len);
+	memcpy(c, p, len);
+	g_kept.back().push_back(c);
+	return c;
+}
+void keep_next_scan() {
+	if (g_kept.size() >= 512) {
+		for (auto c : g_kept.front()) {
+			free(c);
+		}
+		g_kept.erase(g_kept.begin());
+	}
+	g_kept.emplace_back();
+}
+
 // Appends rows [0, count) of the vector the reference produced.  FLAT / CONSTANT(NULL) / DICTIONARY vectors are what
 // ArrowToDuckDB leaves behind; anything else is flattened first (never seen on this path).
 void slab_append(RSlab *s, Vector &v, idx_t count, idx_t dict_len_hint) {
@@ -379,7 +400,26 @@ void slab_append(RSlab *s, Vector &v, idx_t count, idx_t dict_len_hint) {
 		break;
 	default:
 		if (s->width) {
-			memcpy(s->data + s->rows * (uint64_t)s->width, FlatVector::GetData(v), count * (uint64_t)s->width);
+			auto dst = s->data + s->rows * (uint64_t)s->width;
+			memcpy(dst, FlatVector::GetData(v), count * (uint64_t)s->width);
+			// strings the reference copied into the vector's own string heap (ArrowToDuckDBBlob -> AddStringOrBlob,
+			// arrow_conversion.cpp:342-390) die with the DataChunk: keep their bytes alive for the caller
+			if (t.InternalType() == PhysicalType::VARCHAR && v.GetAuxiliary() &&
+			    v.GetAuxiliary()->GetBufferType() == VectorBufferType::STRING_BUFFER) {
+				for (idx_t i = 0; i < count; i++) {
+					if (!mask.RowIsValid(i)) {
+						continue;
+					}
+					uint32_t len;
+					memcpy(&len, dst + i * 16, 4);
+					if (len > 12) {
+						const char *ptr;
+						memcpy(&ptr, dst + i * 16 + 8, 8);
+						char *keep = keep_bytes(ptr, len);
+						memcpy(dst + i * 16 + 8, &keep, 8);
+					}
+				}
+			}
 		}
 	}
 	s->rows += count;
@@ -405,6 +445,7 @@ int ref_open(char *err, int errlen) {
 int ref_scan_column(ArrowArrayStream *stream, uint64_t dictionary_length, RSlab **out, char *err, int errlen) {
 	*out = nullptr;
 	RSlab *slab = nullptr;
+	keep_next_scan();
 	try {
 		auto &s = session();
 		auto &context = *s.con->context;
@@ -445,8 +486,9 @@ void ref_slab_free(RSlab *s) {
 int64_t ref_scan_stream(ArrowArrayStream *stream, uint64_t *checksum, char *err, int errlen) {
 	try {
 		auto &s = session();
-		auto &context = *s.con->context;
-		s.con->BeginTransaction();
+		Connection con(*s.db); // own connection: callable from several threads at once (one stream each)
+		auto &context = *con.context;
+		con.BeginTransaction();
 		int64_t rows = 0;
 		uint64_t sum = 0;
 		try {
@@ -467,10 +509,10 @@ int64_t ref_scan_stream(ArrowArrayStream *stream, uint64_t *checksum, char *err,
 				}
 			}
 		} catch (...) {
-			s.con->Rollback();
+			con.Rollback();
 			throw;
 		}
-		s.con->Commit();
+		con.Commit();
 		if (checksum) {
 			*checksum = sum;
 		}
@@ -479,6 +521,37 @@ int64_t ref_scan_stream(ArrowArrayStream *stream, uint64_t *checksum, char *err,
 		fail(err, errlen, e);
 		return -1;
 	}
+}
+
+// a1 of the reference's read path: IPCFileStreamReader reads every message through DuckDB's BufferedFileReader
+// (src/ipc/stream_reader/ipc_file_stream_reader.cpp:47-138 -> duckdb/src/common/serializer/buffered_file_reader.cpp:25-49,
+// a 4 KiB bounce buffer).  ref_file_read does exactly that ReadData call for one message at `location`.
+void *ref_file_open(const char *path, char *err, int errlen) {
+	try {
+		auto &s = session();
+		auto &fs = FileSystem::GetFileSystem(*s.db->instance);
+		return new BufferedFileReader(fs, path);
+	} catch (std::exception &e) {
+		fail(err, errlen, e);
+		return nullptr;
+	}
+}
+
+int ref_file_read(void *handle, uint64_t location, uint64_t size, void *dst, char *err, int errlen) {
+	try {
+		auto r = (BufferedFileReader *)handle;
+		if (r->CurrentOffset() != location) {
+			r->Seek(location);
+		}
+		r->ReadData((data_ptr_t)dst, size);
+		return 0;
+	} catch (std::exception &e) {
+		return fail(err, errlen, e);
+	}
+}
+
+void ref_file_close(void *handle) {
+	delete (BufferedFileReader *)handle;
 }
 
 // The writer side: scans the whole stream with the reference's reader into ONE DataChunk (what

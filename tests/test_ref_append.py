@@ -1,0 +1,178 @@
+"""Pins the WRITE-direction restatement (oracle/oracle_write.py) to the REFERENCE ITSELF: the same rows go through the
+reference's own ArrowConverter::ToArrowArray / ArrowAppender (duckdb/src/common/arrow/arrow_converter.cpp:19-25,
+arrow_appender.cpp:37-131, appender/*.hpp — compiled from /root/reference/duckdb into oracle/_ref), fed ONE DataChunk per
+record batch the way ColumnDataCollectionSerializer::Serialize(ColumnDataCollection&) feeds it
+(src/writer/column_data_collection_serializer.cpp:97-115), under each SET variant; every Arrow buffer it produces —
+validity (0xFF fill, bits past the last row), offsets, characters, values incl. the NULL slots of fixed-width buffers
+where the appender copies them — must equal the restatement's byte for byte, and so must (length, null_count) of every
+node.  The GPU writer is compared against the same restatement in tests/test_gpu_writer.py."""
+import ctypes
+
+import numpy as np
+import pyarrow as pa
+import pytest
+
+from oracle import oracle_write as OW
+from oracle import ref_py as R
+from vectors import table_vectors
+from writer_cases import nested_table, scalar_table
+
+pytestmark = pytest.mark.skipif(not R.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+def _bytes(buf, size):
+    if buf is None or size == 0:
+        return b""
+    return ctypes.string_at(buf.address, size)
+
+
+def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path="") -> None:
+    """Pre-order (length, null_count) + buffers of what the reference appender produced; `notes[i]` says which kind of
+    buffer bufs[i] is and the validity of its rows (for the buffers whose NULL slots the appender leaves unwritten)."""
+    t, n = arr.type, len(arr)
+    assert arr.offset == 0
+    b = arr.buffers()
+    if pa.types.is_null(t):
+        nodes.append((n, n))
+        return
+    if pa.types.is_union(t):
+        nodes.append((n, 0))
+        bufs.append(_bytes(b[1], n))
+        notes.append((path, "type_ids", None, 1))
+        for i in range(t.num_fields):
+            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}")
+        return
+    nodes.append((n, arr.null_count))
+    valid = np.asarray(arr.is_valid().to_numpy(zero_copy_only=False), bool) if n else np.zeros(0, bool)
+    bufs.append(_bytes(b[0], (n + 7) // 8))
+    notes.append((path, "validity", None, 0))
+    if pa.types.is_struct(t):
+        for i in range(t.num_fields):
+            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}")
+    elif pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t):
+        w = 8 if pa.types.is_large_list(t) else 4
+        bufs.append(_bytes(b[1], (n + 1) * w))
+        notes.append((path, "offsets", None, w))
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+    elif pa.types.is_list_view(t) or pa.types.is_large_list_view(t):
+        w = 8 if pa.types.is_large_list_view(t) else 4
+        bufs.append(_bytes(b[1], n * w))
+        notes.append((path, "view_offsets", None, w))
+        bufs.append(_bytes(b[2], n * w))
+        notes.append((path, "view_sizes", None, w))
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+    elif pa.types.is_fixed_size_list(t):
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+    elif pa.types.is_string_view(t):
+        bufs.append(_bytes(b[1], n * 16))
+        notes.append((path, "views", valid, 16))
+        views = np.frombuffer(bufs[-1], np.uint8).reshape(n, 16) if n else np.zeros((0, 16), np.uint8)
+        lens = views[:, 0:4].copy().view(np.int32).ravel()
+        total = int(lens[(lens > 12) & valid].sum())
+        bufs.append(_bytes(b[2], total) if len(b) > 2 else b"")
+        notes.append((path, "view_data", None, 1))
+    elif (pa.types.is_string(t) or pa.types.is_binary(t) or pa.types.is_large_string(t) or pa.types.is_large_binary(t)):
+        w = 8 if (pa.types.is_large_string(t) or pa.types.is_large_binary(t)) else 4
+        bufs.append(_bytes(b[1], (n + 1) * w))
+        notes.append((path, "offsets", None, w))
+        last = int(np.frombuffer(bufs[-1], np.int64 if w == 8 else np.int32)[-1]) if n else 0
+        bufs.append(_bytes(b[2], last))
+        notes.append((path, "chars", None, 1))
+    elif pa.types.is_boolean(t):
+        bufs.append(_bytes(b[1], (n + 7) // 8))
+        notes.append((path, "bool", None, 0))
+    else:
+        w = t.bit_width // 8
+        bufs.append(_bytes(b[1], n * w))
+        notes.append((path, "values", valid, w))
+
+
+def _table(case):
+    if case == "scalar":
+        return scalar_table(5000)
+    if case == "nested":
+        return nested_table(3000)
+    import pyarrow.ipc as ipc
+    from tools import lineitem
+    return ipc.open_stream(lineitem.stream_bytes(12_345, seed=9, batch_rows=4000)).read_all()
+
+
+# Columns whose NULL slots are NOT a function of the input in the reference: the scan leaves them unwritten
+# (ConvertDecimal narrowing, arrow_conversion.cpp:776-781) or the appender skips them (SkipNulls converters:
+# ArrowIntervalConverter, scalar_data.hpp:34-52) — compared on valid rows only.
+def _same_buffer(rb: bytes, ob: bytes, note) -> tuple[bool, str]:
+    if rb == ob:
+        return True, "exact"
+    path, kind, valid, w = note
+    if valid is not None and len(rb) == len(ob) and w:
+        a = np.frombuffer(rb, np.uint8).reshape(-1, w)
+        b = np.frombuffer(ob, np.uint8).reshape(-1, w)
+        if np.array_equal(a[valid], b[valid]):
+            return True, "valid rows"
+    return False, ""
+
+
+@pytest.mark.parametrize("flags", [0, R.FLAG_LARGE, R.FLAG_LIST_VIEW, R.FLAG_STRING_VIEW,
+                                   R.FLAG_LARGE | R.FLAG_LIST_VIEW])
+@pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("scalar", 5000), ("nested", 1000), ("nested", 3000),
+                                      ("lineitem", 5000)])
+def test_appender_restatement_equals_reference(case, rgs, flags):
+    table = _table(case)
+    cols = table_vectors(table)
+    kw = dict(large=bool(flags & R.FLAG_LARGE), view=bool(flags & R.FLAG_LIST_VIEW), sview=bool(flags & R.FLAG_STRING_VIEW))
+    row = 0
+    loose = set()
+    for n, nodes, slices, body in OW.serialize_batches(cols, table.num_rows, rgs, **kw):
+        part = table.slice(row, n).combine_chunks()
+        ref = R.append(part, flags)
+        assert len(ref) == n
+        rnodes, rbufs, notes = [], [], []
+        for i in range(ref.type.num_fields):
+            ref_nodes_buffers(ref.field(i), rnodes, rbufs, notes, ref.type.field(i).name)
+        assert rnodes == nodes, f"{case} rows {row}+{n}: (length, null_count) differ"
+        assert len(rbufs) == len(slices)
+        for k, ((o, l), rb) in enumerate(zip(slices, rbufs)):
+            ob = body[o:o + l]
+            assert len(rb) == l, f"{case} rows {row}+{n}: buffer {k} {notes[k][:2]} has {len(rb)} bytes, restatement {l}"
+            ok, how = _same_buffer(rb, ob, notes[k])
+            assert ok, f"{case} rows {row}+{n}: buffer {k} {notes[k][:2]} differs"
+            if how != "exact":
+                loose.add(notes[k][0])
+        row += n
+    assert row == table.num_rows
+    # only the columns whose NULL slots the reference leaves unwritten may fall back to the valid-row comparison
+    allowed = {"dec4", "iv"}
+    assert loose <= allowed, f"NULL slots differ in {sorted(loose - allowed)}"
+
+
+def test_appender_validity_tail_bits_and_null_slots():
+    """append_data.hpp:117-149: 0xFF fill, bits past the last row stay 1; scalar_data.hpp:90-119: NULL slots of a plain
+    scalar column carry the source vector's bytes (here: what arrow_scan aliased from the Arrow buffer)"""
+    vals = pa.Array.from_buffers(pa.int32(), 5, [pa.py_buffer(bytes([0b01101])),
+                                                 pa.py_buffer(np.array([7, 8, 9, 10, 11], np.int32).tobytes())])
+    ref = R.append(pa.RecordBatch.from_arrays([vals], names=["v"]))
+    col = ref.field(0)
+    assert ctypes.string_at(col.buffers()[0].address, 1) == bytes([0b11101101])
+    assert col.null_count == 2
+    assert np.frombuffer(ctypes.string_at(col.buffers()[1].address, 20), np.int32).tolist() == [7, 8, 9, 10, 11]
+    t = pa.table({"v": vals})
+    (n, nodes, slices, body), = OW.serialize_batches(table_vectors(t), 5, 100)
+    assert body[slices[0][0]] == 0b11101101 and nodes == [(5, 2)]
+    assert np.frombuffer(body[slices[1][0]: slices[1][0] + 20], np.int32).tolist() == [7, 8, 9, 10, 11]
+
+
+def test_dbgen_export_has_a_bitmap_per_column():
+    """What a reference-written lineitem batch looks like (SURVEY App. A's open question, answered by the appender
+    itself): every column carries a 0xFF validity buffer with null_count 0"""
+    R.query("call dbgen(sf=0.01)")
+    try:
+        b = next(iter(R.export("select * from lineitem", 20_000)))
+    finally:
+        for t in ("lineitem", "orders", "partsupp", "part", "customer", "supplier", "nation", "region"):
+            R.query(f"drop table {t}")
+    assert b.num_rows == 20_000 and b.num_columns == 16
+    assert [str(f.type) for f in b.schema][:5] == ["int64", "int64", "int64", "int64", "decimal64(15, 2)"]
+    for col in b.columns:
+        assert col.null_count == 0
+        v = col.buffers()[0]
+        assert v is not None and ctypes.string_at(v.address, 2500) == b"\xff" * 2500

@@ -1,0 +1,265 @@
+"""Pins the CPU restatement (oracle/oracle.c) to the REFERENCE ITSELF: the reference's DuckDB compiled from
+/root/reference/duckdb (oracle/build_ref.py -> oracle/_ref/libduckdb_ref.so) converts the same Arrow arrays through
+ArrowTableFunction::ArrowScanFunction / ArrowToDuckDB (duckdb/src/function/table/arrow.cpp:172-201,
+arrow_conversion.cpp:1421-1484), driven like src/file_scanner/arrow_file_scan.cpp:30-72 drives it, and every 2 048-row
+vector it produces must equal the restatement's bit for bit (canonical form of SURVEY §8c: validity bits, bytes of
+valid rows, string_t = length + inline bytes / prefix + pointed-to bytes, list entries + children, sel_t + dictionary).
+
+Inputs: the reference's own fixtures (arrow-testing integration streams, data/test.arrows, data/fruit.arrow), the
+round-trip cases of duckdb/test/arrow/arrow_roundtrip.cpp:45-92 restated as pyarrow arrays, and the writer tables."""
+import ctypes
+import decimal
+import os
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.ipc as ipc
+import pytest
+
+from parity import GOLDEN, O
+from oracle import ref_py as R
+
+pytestmark = pytest.mark.skipif(not R.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+STRINGY = {16, 17, 33, 34, 35}  # VARCHAR, BLOB, BIT, VARINT, JSON
+LE = os.path.join(GOLDEN, "arrow-testing", "1.0.0-littleendian")
+BE = os.path.join(GOLDEN, "arrow-testing", "1.0.0-bigendian")
+FILES = ["generated_null_trivial", "generated_primitive_large_offsets", "generated_custom_metadata",
+         "generated_datetime", "generated_decimal", "generated_map_non_canonical", "generated_map",
+         "generated_nested_large_offsets", "generated_nested", "generated_null", "generated_primitive_no_batches",
+         "generated_primitive_zerolength", "generated_primitive", "generated_recursive_nested",
+         "generated_dictionary", "generated_dictionary_unsigned"]
+
+
+def _strings(data16: np.ndarray):
+    out = []
+    for rec in data16:
+        ln = int(rec[0:4].view(np.uint32)[0])
+        if ln <= 12:
+            out.append((ln, rec[4:16].tobytes(), b""))
+        else:
+            ptr = int(rec[8:16].view(np.uint64)[0])
+            out.append((ln, rec[4:8].tobytes(), ctypes.string_at(ptr, ln)))
+    return out
+
+
+def assert_same_slab(ref: O.Slab, ora: O.Slab, where: str):
+    assert ref.rows == ora.rows, f"{where}: rows {ref.rows} != {ora.rows}"
+    if ref.sel is not None or ora.sel is not None:
+        assert ref.sel is not None and ora.sel is not None, f"{where}: only one side produced a dictionary vector"
+        assert np.array_equal(ref.sel, ora.sel), f"{where}: sel_t differ"
+        if ref.rows:
+            # the oracle keeps the NULL slot only when the mask was grown for it; compare the slots sel can reach
+            n = int(ref.sel.max()) + 1
+            assert ref.dict.rows >= n and ora.dict.rows >= n, f"{where}: dictionary shorter than sel"
+            _cmp_rows(ref.dict, ora.dict, n, where + ".dict")
+        return
+    assert np.array_equal(ref.valid, ora.valid), \
+        f"{where}: validity differs at rows {np.flatnonzero(ref.valid != ora.valid)[:8]}"
+    _cmp_rows(ref, ora, ref.rows, where)
+
+
+def _cmp_rows(ref, ora, n, where):
+    assert np.array_equal(ref.valid[:n], ora.valid[:n]), f"{where}: validity"
+    v = ref.valid[:n]
+    assert ref.width == ora.width, f"{where}: width {ref.width} != {ora.width}"
+    if ref.width:
+        a, b = ref.data[:n][v], ora.data[:n][v]
+        if ref.type_id in STRINGY:
+            assert _strings(a) == _strings(b), f"{where}: string_t differ"
+        else:
+            assert np.array_equal(a, b), f"{where}: bytes of valid rows differ at {np.flatnonzero((a != b).any(1))[:8]}"
+    assert len(ref.children) == len(ora.children), f"{where}: children"
+    for i, (c, d) in enumerate(zip(ref.children, ora.children)):
+        assert_same_slab(c, d, f"{where}.{i}")
+
+
+def check(arr: pa.Array, where: str):
+    try:
+        ref = R.scan_column(arr)
+    except R.RefError as e:
+        with pytest.raises(O.OracleError) as oe:
+            O.scan_column(arr)
+        msg = str(e).split(":", 1)[1].strip()
+        assert msg.split("\n")[0][:40] in str(oe.value), f"{where}: reference said {e}, oracle said {oe.value}"
+        return "error"
+    ora = O.scan_column(arr)
+    assert_same_slab(ref, ora, where)
+    return "ok"
+
+
+@pytest.mark.parametrize("endian", ["little", "big"])
+@pytest.mark.parametrize("name", FILES)
+def test_oracle_equals_reference_on_arrow_testing(name, endian):
+    folder = LE if endian == "little" else BE
+    for bi, batch in enumerate(ipc.open_stream(os.path.join(folder, name + ".stream"))):
+        for ci in range(batch.num_columns):
+            check(batch.column(ci), f"{name}[{endian}] batch {bi} col {batch.schema.field(ci).name}")
+
+
+@pytest.mark.parametrize("name", ["generated_zstd", "generated_uncompressible_zstd", "generated_lz4",
+                                  "generated_uncompressible_lz4"])
+def test_oracle_equals_reference_on_compressed(name):
+    folder = os.path.join(GOLDEN, "arrow-testing", "2.0.0-compression")
+    for bi, batch in enumerate(ipc.open_stream(os.path.join(folder, name + ".stream"))):
+        for ci in range(batch.num_columns):
+            check(batch.column(ci), f"{name} batch {bi} col {ci}")
+
+
+def test_oracle_equals_reference_on_extension_data():
+    """data/test.arrows (16 batches) and data/fruit.arrow (NULL doubles): test/sql/read_arrow.test:36-55,
+    read_arrow_file.test:9-17"""
+    for bi, batch in enumerate(ipc.open_stream(os.path.join(GOLDEN, "data", "test.arrows"))):
+        for ci in range(batch.num_columns):
+            check(batch.column(ci), f"test.arrows batch {bi} col {ci}")
+    b = ipc.open_file(os.path.join(GOLDEN, "data", "fruit.arrow")).get_batch(0)
+    for ci in range(b.num_columns):
+        check(b.column(ci), f"fruit col {ci}")
+
+
+def test_reference_failures_are_the_documented_ones():
+    """test/sql/arrow_testing.test:67-82"""
+    with pytest.raises(R.RefError, match="Unsupported Internal Arrow Type for Decimal"):
+        for b in ipc.open_stream(os.path.join(LE, "generated_decimal256.stream")):
+            for c in b.columns:
+                R.scan_column(c)
+    with pytest.raises(R.RefError, match="Could not convert Interval to Microsecond"):
+        for b in ipc.open_stream(os.path.join(LE, "generated_interval.stream")):
+            for i in range(b.num_columns):
+                try:
+                    c = b.column(i)
+                except KeyError:
+                    continue
+                R.scan_column(c)
+
+
+def _roundtrip_cases():
+    """duckdb/test/arrow/arrow_roundtrip.cpp:45-92 (ints, nulls, bools, strings, structs, lists, maps, decimals 4/9/18/38,
+    intervals, large offsets, string views) restated as Arrow arrays; > 2 048 rows so the chunk loop is exercised."""
+    n = 5000
+    rng = np.random.default_rng(7)
+    D = decimal.Decimal
+    mask = rng.random(n) < 0.2
+    cases = {
+        "i64": pa.array(rng.integers(-2**62, 2**62, n), pa.int64()),
+        "i32_nulls": pa.array(rng.integers(-2**31, 2**31, n), pa.int32(), mask=mask),
+        "u16": pa.array(rng.integers(0, 2**16, n), pa.uint16(), mask=mask),
+        "f64": pa.array(rng.random(n), pa.float64(), mask=mask),
+        "bool": pa.array(rng.random(n) < 0.5, pa.bool_(), mask=mask),
+        "str": pa.array([None if m else "s" * int(k) for m, k in zip(mask, rng.integers(0, 30, n))]),
+        "large_str": pa.array([None if m else "L" * int(k) for m, k in zip(mask, rng.integers(0, 30, n))], pa.large_string()),
+        "str_view": pa.array([None if m else "view-" * int(k) for m, k in zip(mask, rng.integers(0, 6, n))], pa.string_view()),
+        "bin": pa.array([None if m else bytes(int(k)) for m, k in zip(mask, rng.integers(0, 30, n))], pa.binary()),
+        "fsb": pa.array([bytes([i % 256] * 5) for i in range(n)], pa.binary(5)),
+        "date32": pa.array(rng.integers(0, 20000, n).astype(np.int32), pa.int32(), mask=mask).view(pa.date32()),
+        "date64": pa.array(rng.integers(0, 20000, n) * 86_400_000, pa.int64(), mask=mask).view(pa.date64()),
+        "time32s": pa.array(rng.integers(0, 86400, n).astype(np.int32), pa.int32()).view(pa.time32("s")),
+        "time32ms": pa.array(rng.integers(0, 86_400_000, n).astype(np.int32), pa.int32()).view(pa.time32("ms")),
+        "time64ns": pa.array(rng.integers(0, 86_400_000_000_000, n), pa.int64()).view(pa.time64("ns")),
+        "ts_s": pa.array(rng.integers(0, 2**31, n), pa.int64()).view(pa.timestamp("s")),
+        "ts_ns": pa.array(rng.integers(0, 2**60, n), pa.int64(), mask=mask).view(pa.timestamp("ns")),
+        "ts_tz_ms": pa.array(rng.integers(0, 2**41, n), pa.int64(), mask=mask).view(pa.timestamp("ms", tz="UTC")),
+        "ts_tz_ns": pa.array(rng.integers(0, 2**60, n), pa.int64()).view(pa.timestamp("ns", tz="Europe/Amsterdam")),
+        "dur_s": pa.array(rng.integers(0, 2**30, n), pa.int64()).view(pa.duration("s")),
+        "dur_ns": pa.array(rng.integers(0, 2**60, n), pa.int64(), mask=mask).view(pa.duration("ns")),
+        "iv_m": pa.array(rng.integers(0, 1000, n).astype(np.int32), pa.int32()).view(pa.month_interval())
+        if hasattr(pa, "month_interval") else None,
+        "iv_mdn": pa.array([pa.MonthDayNano([int(a), int(b), int(c)]) for a, b, c in
+                            zip(rng.integers(-50, 50, n), rng.integers(-50, 50, n), rng.integers(-10**12, 10**12, n))],
+                           pa.month_day_nano_interval()),
+        "dec4": pa.array([D(int(x)).scaleb(-1) for x in rng.integers(-999, 1000, n)], pa.decimal128(4, 1)),
+        "dec9": pa.array([D(int(x)).scaleb(-2) for x in rng.integers(-10**8, 10**8, n)], pa.decimal128(9, 2)),
+        "dec18": pa.array([None if m else D(int(x)).scaleb(-3) for m, x in zip(mask, rng.integers(-10**17, 10**17, n))],
+                          pa.decimal128(18, 3)),
+        "dec38": pa.array([D(int(x) * 10**15 + 7).scaleb(-4) for x in rng.integers(-10**17, 10**17, n)], pa.decimal128(38, 4)),
+        "dec32": pa.array([D(int(x)).scaleb(-2) for x in rng.integers(-10**8, 10**8, n)], pa.decimal32(9, 2)),
+        "dec64": pa.array([None if m else D(int(x)).scaleb(-2) for m, x in zip(mask, rng.integers(-10**14, 10**14, n))],
+                          pa.decimal64(15, 2)),
+        "list": pa.array([None if i % 7 == 0 else list(range(i % 5)) for i in range(n)], pa.list_(pa.int32())),
+        "large_list": pa.array([None if i % 7 == 0 else [str(j) * j for j in range(i % 4)] for i in range(n)],
+                               pa.large_list(pa.string())),
+        "list_list": pa.array([None if i % 9 == 0 else [None if j == 1 else [j, None] for j in range(i % 4)]
+                               for i in range(n)], pa.list_(pa.list_(pa.int16()))),
+        "struct": pa.array([None if i % 11 == 0 else {"a": i if i % 3 else None, "b": "x" * (i % 20)} for i in range(n)],
+                           pa.struct([("a", pa.int64()), ("b", pa.string())])),
+        "list_struct": pa.array([[{"x": j, "y": None if j % 2 else float(j)} for j in range(i % 3)] for i in range(n)],
+                                pa.list_(pa.struct([("x", pa.int32()), ("y", pa.float64())]))),
+        "map": pa.array([None if i % 10 == 0 else [(f"k{j}", None if j % 3 == 0 else j) for j in range(i % 4)]
+                         for i in range(n)], pa.map_(pa.string(), pa.int64())),
+        "fsl": pa.array([None if i % 6 == 0 else [i, None if i % 5 == 0 else i + 1, i + 2] for i in range(n)],
+                        pa.list_(pa.int32(), 3)),
+        "list_fsl": pa.array([None if i % 8 == 0 else [None if j == 1 else [j, j + 1] for j in range(i % 4)]
+                              for i in range(n)], pa.list_(pa.list_(pa.int16(), 2))),
+        "dict_i8": pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 3, n).astype(np.int8), mask=mask),
+                                                  pa.array(["a", "bb", "a dictionary value longer than twelve"])),
+        "dict_u32_nullvalue": pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 3, n).astype(np.uint32)),
+                                                             pa.array([1.5, None, 3.5])),
+        "null": pa.nulls(n),
+        "ree": pa.RunEndEncodedArray.from_arrays(pa.array(np.arange(1, 501, dtype=np.int32) * 10),
+                                                 pa.array([None if i % 9 == 0 else i for i in range(500)], pa.int64())),
+        "ree_str": pa.RunEndEncodedArray.from_arrays(pa.array(np.arange(1, 301, dtype=np.int16) * 10),
+                                                     pa.array(["run %d of a run-end encoded column" % i for i in range(300)])),
+        "list_view": pa.ListViewArray.from_arrays(pa.array(np.arange(n, dtype=np.int32) * 2),
+                                                  pa.array(np.full(n, 2, np.int32)),
+                                                  pa.array(np.arange(2 * n, dtype=np.int64))),
+        "uuid": pa.ExtensionArray.from_storage(pa.uuid(), pa.array([bytes(rng.integers(0, 256, 16).astype(np.uint8))
+                                                                    for _ in range(n)], pa.binary(16))),
+        "bool8": pa.ExtensionArray.from_storage(pa.bool8(), pa.array(rng.integers(-2, 3, n).astype(np.int8), mask=mask)),
+        "json": pa.ExtensionArray.from_storage(pa.json_(), pa.array(['{"k": %d}' % i for i in range(n)])),
+    }
+    return {k: v for k, v in cases.items() if v is not None}
+
+
+_CASES = None
+
+
+def _cases():
+    global _CASES
+    if _CASES is None:
+        _CASES = _roundtrip_cases()
+    return _CASES
+
+
+@pytest.mark.parametrize("name", ["i64", "i32_nulls", "u16", "f64", "bool", "str", "large_str", "str_view", "bin", "fsb",
+                                  "date32", "date64", "time32s", "time32ms", "time64ns", "ts_s", "ts_ns", "ts_tz_ms",
+                                  "ts_tz_ns", "dur_s", "dur_ns", "iv_m", "iv_mdn", "dec4", "dec9", "dec18", "dec38",
+                                  "dec32", "dec64", "list", "large_list", "list_list", "struct", "list_struct", "map",
+                                  "fsl", "list_fsl", "dict_i8", "dict_u32_nullvalue", "null", "ree", "ree_str",
+                                  "list_view", "uuid", "bool8", "json"])
+def test_oracle_equals_reference_on_roundtrip_cases(name):
+    cases = _cases()
+    if name not in cases:
+        pytest.skip("pyarrow cannot build this type here")
+    assert check(cases[name], name) == "ok"
+
+
+def test_oracle_equals_reference_with_array_offsets():
+    """non-zero ArrowArray.offset (duckdb/tools/pythonpkg/tests/fast/arrow/test_arrow_offsets.py): unaligned validity
+    (ShiftRight), list rebasing, bool unpack at a bit offset"""
+    for name in ("i32_nulls", "bool", "str", "list", "struct", "dec18", "fsl"):
+        arr = _cases()[name]
+        for off in (3, 2049):
+            assert check(arr.slice(off), f"{name}[{off}:]") == "ok"
+
+
+def test_oracle_equals_reference_on_writer_tables():
+    from writer_cases import nested_table, scalar_table
+    for t in (scalar_table(), nested_table()):
+        for name in t.column_names:
+            col = t.column(name).combine_chunks()
+            assert check(col, name) == "ok"
+
+
+def test_q6_known_answers_through_the_reference():
+    """benchmark/lineitem.py:41 on dbgen SF0.01 = test/nodejs/arrow_test.js:424's 1193053.2253, computed (1) on the
+    dbgen table and (2) over arrow_scan of the reference appender's own record batches"""
+    R.query("call dbgen(sf=0.01)")
+    q6 = ("select sum(l_extendedprice * l_discount) from {} where l_shipdate >= date '1994-01-01' and "
+          "l_shipdate < date '1995-01-01' and l_discount between 0.05 and 0.07 and l_quantity < 24")
+    assert R.query(q6.format("lineitem")) == [["1193053.2253"]]
+    batches = list(R.export("select * from lineitem", 20_000))
+    assert sum(b.num_rows for b in batches) == 60175
+    R.register("li_arrow", pa.Table.from_batches(batches))
+    assert R.query(q6.format("li_arrow")) == [["1193053.2253"]]
+    for t in ("lineitem", "orders", "partsupp", "part", "customer", "supplier", "nation", "region"):
+        R.query(f"drop table {t}")

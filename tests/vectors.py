@@ -57,6 +57,20 @@ def make_string_t(start: np.ndarray, length: np.ndarray, heap: np.ndarray, ptr_b
     return rec.reshape(-1)
 
 
+def _and_mask(hv: HostVector, mask: np.ndarray) -> None:
+    """parent NULLs -> child NULLs, down through row-aligned children (STRUCT fields, ARRAY elements)"""
+    if hv.type == "SQLNULL":
+        return
+    hv.validity = mask.copy() if hv.validity is None else (hv.validity & mask)
+    if hv.type in ("VARCHAR", "BLOB", "BIT") and hv.str_len is not None:
+        hv.str_len = np.where(hv.validity, hv.str_len, 0)
+    if hv.type == "STRUCT":
+        for k in hv.children:
+            _and_mask(k, mask)
+    elif hv.type == "ARRAY":
+        _and_mask(hv.children[0], np.repeat(mask, hv.param))
+
+
 def from_arrow(arr: pa.Array, name: str = "") -> HostVector:
     """Arrow array -> the DuckDB vector the reference's scan would produce for it (logical content)."""
     if isinstance(arr, pa.ChunkedArray):
@@ -113,9 +127,15 @@ def from_arrow(arr: pa.Array, name: str = "") -> HostVector:
             return HostVector("MAP", n, ent.view(np.uint8).reshape(-1), valid, [child], name=name)
         return HostVector("LIST", n, ent.view(np.uint8).reshape(-1), valid, [from_arrow(arr.values, "l")], name=name)
     if pa.types.is_fixed_size_list(t):
-        return HostVector("ARRAY", n, None, valid, [from_arrow(arr.values, "")], name=name, param=t.list_size)
+        child = from_arrow(arr.values, "")
+        if valid is not None:  # the scan broadcasts a NULL array row over its k child rows (arrow_conversion.cpp:313-323)
+            _and_mask(child, np.repeat(valid, t.list_size))
+        return HostVector("ARRAY", n, None, valid, [child], name=name, param=t.list_size)
     if pa.types.is_struct(t):
         kids = [from_arrow(arr.field(i), t.field(i).name) for i in range(t.num_fields)]
+        if valid is not None:  # the scan ANDs the struct's NULLs into every child (arrow_conversion.cpp:1143-1151)
+            for k in kids:
+                _and_mask(k, valid)
         return HostVector("STRUCT", n, None, valid, kids, name=name)
     if str(t) == "month_day_nano_interval":
         raw = _values(arr, np.dtype([("m", np.int32), ("d", np.int32), ("ns", np.int64)]))
