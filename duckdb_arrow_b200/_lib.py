@@ -147,6 +147,7 @@ def _load() -> C.CDLL:
         "b2a_scan_filter": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
+        "b2a_read_arrow_device": (i32, [vp, vp, u32, vp]),
         "b2a_multifile_open": (i32, [P(C.c_char_p), u32, P(MultiFileOptions), P(vp)]),
         "b2a_multifile_close": (None, [vp]),
         "b2a_multifile_counts": (i32, [vp, P(u32), P(u32), P(u32)]),

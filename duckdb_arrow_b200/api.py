@@ -272,12 +272,19 @@ class ArrowScan:
         self._h_out = h_out
         return h_out.numpy()
 
+    def read_device(self, d_out=None, n_slices: int = 0):
+        """b2a_read_arrow_device: host image -> pipelined H2D of the projected buffers + decode -> vectors in d_out
+        (device); the current stream is ordered behind the last decode (no host sync, nothing copied back)."""
+        d_out = self.alloc_out() if d_out is None else d_out
+        check(lib.b2a_read_arrow_device(self._h, C.c_void_p(d_out.data_ptr()), n_slices, self._stream_ptr()))
+        return d_out
+
     @property
     def gpu_launches(self) -> int:
         return int(lib.b2a_scan_gpu_launches(self._h))
 
     # -- pushed-down filters and the Q6-style consumer (new behaviour; the reference filters above the scan)
-    def filter(self, predicates, d_out=None):
+    def filter(self, predicates, d_out=None, out=None):
         """predicates: [(column name | projected index, op, int constant)], ANDed.  Returns (sel, count, total):
         torch tensors uint32[n_chunks*2048], uint32[n_chunks], uint64[1] on the device — one selection vector per
         2 048-row DuckDB vector."""
@@ -290,9 +297,12 @@ class ArrowScan:
             arr[i].cmp = _lib.CMP[op]
             arr[i].constant = int(const)
         dev = f"cuda:{self.device}"
-        sel = torch.empty(max(1, self.n_chunks) * VECTOR_SIZE, dtype=torch.int32, device=dev)
-        count = torch.zeros(max(1, self.n_chunks), dtype=torch.int32, device=dev)
-        total = torch.zeros(1, dtype=torch.int64, device=dev)
+        if out is not None:  # (sel, count, total) of an earlier call: no allocation (CUDA-graph capture)
+            sel, count, total = out
+        else:
+            sel = torch.empty(max(1, self.n_chunks) * VECTOR_SIZE, dtype=torch.int32, device=dev)
+            count = torch.zeros(max(1, self.n_chunks), dtype=torch.int32, device=dev)
+            total = torch.zeros(1, dtype=torch.int64, device=dev)
         check(lib.b2a_scan_filter(self._h, C.c_void_p(d_out.data_ptr()), arr, len(predicates),
                                   C.c_void_p(sel.data_ptr()), C.c_void_p(count.data_ptr()),
                                   C.c_void_p(total.data_ptr()), self._stream_ptr()))
@@ -312,6 +322,21 @@ class ArrowScan:
                                        C.c_void_p(res.data_ptr()), self._stream_ptr()))
         lo, hi = [int(x) for x in res.cpu().tolist()]
         return (hi << 64) | (lo & 0xFFFFFFFFFFFFFFFF)
+
+    def sum_product_async(self, col_a, col_b, sel=None, count=None, d_out=None, result=None):
+        """sum_product without the read-back: returns the int64[2] device tensor {lo, hi} of the 128-bit sum, written by
+        work queued on the current stream (graph-capturable once the column table is cached by a first call)."""
+        torch = self._torch()
+        d_out = self.d_out if d_out is None else d_out
+        names = [f.name for f in self.reader.output_columns()]
+        ia = names.index(col_a) if isinstance(col_a, str) else col_a
+        ib = names.index(col_b) if isinstance(col_b, str) else col_b
+        res = torch.zeros(2, dtype=torch.int64, device=f"cuda:{self.device}") if result is None else result
+        check(lib.b2a_scan_sum_product(self._h, C.c_void_p(d_out.data_ptr()), ia, ib,
+                                       C.c_void_p(sel.data_ptr() if sel is not None else 0),
+                                       C.c_void_p(count.data_ptr() if count is not None else 0),
+                                       C.c_void_p(res.data_ptr()), self._stream_ptr()))
+        return res
 
     # -- layout
     def column(self, batch: int, flat: int) -> _lib.ColumnOut:

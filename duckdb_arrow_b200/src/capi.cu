@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <string>
 #include <thread>
@@ -484,6 +485,12 @@ int b2a_scan_finish(b2a_scan *s, void *cuda_stream) {
 			return Fail(B2A_ECONVERSION, "DuckDB does not support Strings over 4GB");
 		case B2A_DEV_INDEX_U32:
 			return Fail(B2A_ECONVERSION, "DuckDB only supports indices that fit on an uint32");
+		case B2A_DEV_DICT_INDEX:
+			return Fail(B2A_EINVAL, "Arrow IPC: dictionary index outside the dictionary");
+		case B2A_DEV_VIEW_RANGE:
+			return Fail(B2A_EINVAL, "Arrow IPC: string view refers to bytes outside its variadic data buffers");
+		case B2A_DEV_LIST_CHILD:
+			return Fail(B2A_EINVAL, "Arrow IPC: list offsets exceed the length of the child array");
 		default:
 			return Fail(B2A_EINTERNAL, "unknown device error code " + std::to_string(err));
 		}
@@ -564,10 +571,13 @@ struct HostPipe {
 	uint8_t *d_stage[kRing] = {nullptr, nullptr, nullptr};
 	uint64_t stage_bytes = 0;
 	cudaEvent_t ev_start = nullptr;
+	cudaEvent_t ev_user = nullptr;
 	uint8_t *d_out = nullptr;
 	uint64_t d_out_bytes = 0;
 };
-static thread_local HostPipe g_pipe;
+// keyed by device: streams, events, staging rings and the arena belong to the device they were created on
+// (a thread may scan on several GPUs one after the other)
+static thread_local std::map<int, HostPipe> g_pipes;
 
 static int UploadRanges(b2a_scan *s, const ScanPlan::RangeList &ranges, cudaStream_t st) {
 	const ScanPlan &p = s->plan;
@@ -581,10 +591,14 @@ static int UploadRanges(b2a_scan *s, const ScanPlan::RangeList &ranges, cudaStre
 	return B2A_OK;
 }
 
-extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices) {
+// h_out_pinned != NULL: vectors come back to the host (b2a_read_arrow_host).  d_out_user != NULL: vectors stay in the
+// caller's device arena for device-side consumers (b2a_read_arrow_device): no D2H, string_t point into the device image,
+// and `user_stream` is made to wait for the last decode instead of the host.
+static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, uint32_t n_slices, void *user_stream) {
 	NEED_DEVICE(s);
 	const ScanPlan &p = s->plan;
-	HostPipe &hp = g_pipe;
+	HostPipe &hp = g_pipes[s->device];
+	const bool to_host = d_out_user == nullptr;
 	if (!hp.in) {
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking));
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.compute, cudaStreamNonBlocking));
@@ -594,7 +608,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		CUDA_OK(cudaMalloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
 	}
 	s->d_image = s->d_image_owned;
-	if (hp.d_out_bytes < p.out_bytes) {
+	if (to_host && hp.d_out_bytes < p.out_bytes) {
 		cudaFree(hp.d_out);
 		hp.d_out = nullptr;
 		hp.d_out_bytes = 0;
@@ -629,19 +643,29 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	}
 	const uint8_t *h_image = s->r->reader.Image();
 	uint8_t *h_out = static_cast<uint8_t *>(h_out_pinned);
-	if (p.stats_bytes) {
-		CUDA_OK(cudaMemsetAsync(hp.d_out + p.stats_base, 0, p.stats_bytes, hp.compute));
-	}
 	DecodeLaunch l;
 	l.d_tasks = s->d_tasks;
 	l.d_tile_task = s->d_tile_task;
 	l.image_origin = s->d_image - p.image_lo;
-	l.out = hp.d_out;
-	l.string_ptr_origin = reinterpret_cast<uint64_t>(h_image);
+	uint8_t *const arena = to_host ? hp.d_out : static_cast<uint8_t *>(d_out_user);
+	l.out = arena;
+	l.string_ptr_origin = to_host ? reinterpret_cast<uint64_t>(h_image)
+	                              : reinterpret_cast<uint64_t>(s->d_image) - p.image_lo;
 	l.d_err = s->d_err;
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
 	l.lean = p.lean;
+	if (!to_host && user_stream) { // the caller's earlier work on the arena (a previous step's consumers) comes first
+		if (!hp.ev_user) {
+			CUDA_OK(cudaEventCreateWithFlags(&hp.ev_user, cudaEventDisableTiming));
+		}
+		CUDA_OK(cudaEventRecord(hp.ev_user, static_cast<cudaStream_t>(user_stream)));
+		CUDA_OK(cudaStreamWaitEvent(hp.compute, hp.ev_user, 0));
+		CUDA_OK(cudaStreamWaitEvent(hp.in, hp.ev_user, 0));
+	}
+	if (p.stats_bytes) {
+		CUDA_OK(cudaMemsetAsync(arena + p.stats_base, 0, p.stats_bytes, hp.compute));
+	}
 
 	// ---- how the bytes get up: a pinned image is read by the copy engine range by range; anything else (an mmap'ed
 	// file, a pageable buffer) is packed into pinned staging buffers by host threads, one large copy per slice
@@ -756,7 +780,7 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		CUDA_OK(cudaEventRecord(hp.ev_c[sl], hp.compute));
 		CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[sl], 0));
 		const uint64_t o0 = p.batch_out0[b0], o1 = p.batch_out0[b1];
-		if (o1 > o0 && !has_phase2) {
+		if (to_host && o1 > o0 && !has_phase2) {
 			CUDA_OK(cudaMemcpyAsync(h_out + o0, hp.d_out + o0, o1 - o0, cudaMemcpyDeviceToHost, hp.out));
 		}
 		if (trace) {
@@ -804,6 +828,18 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 	CUDA_OK(cudaEventRecord(hp.ev_c[n_slices], hp.compute));
 	CUDA_OK(cudaStreamWaitEvent(hp.out, hp.ev_c[n_slices], 0));
 	// REE gathers write into the batches' regions after the per-slice copies would have left: one copy of the whole arena
+	if (!to_host) {
+		// device consumers: order the caller's stream behind the last decode; the host only waits for the staging ring
+		if (user_stream) {
+			CUDA_OK(cudaStreamWaitEvent(static_cast<cudaStream_t>(user_stream), hp.ev_c[n_slices], 0));
+		} else {
+			CUDA_OK(cudaStreamSynchronize(hp.compute));
+		}
+		if (workers) { // the pinned ring is reused by the next call: its last copies must have left the host
+			CUDA_OK(cudaEventSynchronize(hp.ev_in[n_slices]));
+		}
+		return B2A_OK;
+	}
 	const uint64_t d2h_from = has_phase2 ? 0 : tail_out0;
 	if (p.out_bytes > d2h_from) {
 		CUDA_OK(cudaMemcpyAsync(h_out + d2h_from, hp.d_out + d2h_from, p.out_bytes - d2h_from, cudaMemcpyDeviceToHost,
@@ -821,6 +857,29 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		}
 	}
 	return b2a_scan_finish(s, hp.compute);
+}
+
+extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices) {
+	B2A_TRY
+	if (!h_out_pinned) {
+		return Fail(B2A_EINVAL, "b2a_read_arrow_host needs a (pinned) host output arena");
+	}
+	return ReadArrowPipeline(s, h_out_pinned, nullptr, n_slices, nullptr);
+	B2A_CATCH
+}
+
+extern "C" int b2a_read_arrow_device(b2a_scan *s, void *d_out, uint32_t n_slices, void *cuda_stream) {
+	B2A_TRY
+	NEED_DEVICE(s);
+	if (s->plan.alias_direct) {
+		return Fail(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan keeps its direct columns on the host: device consumers need "
+		                        "a scan created without the flag");
+	}
+	if (!d_out || (reinterpret_cast<uintptr_t>(d_out) & 255) != 0) {
+		return Fail(B2A_EINVAL, "output arena must be a 256-byte aligned device pointer");
+	}
+	return ReadArrowPipeline(s, nullptr, d_out, n_slices, cuda_stream);
+	B2A_CATCH
 }
 
 // ------------------------------------------------------------------ filter / aggregate consumers
@@ -846,7 +905,9 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 		}
 		flats.push_back(f.flat_index);
 		if (widths) {
-			widths->push_back(static_cast<uint8_t>(f.out_width));
+			// unsigned 8/16/32-bit values are zero-extended by the filter kernel (0x80 flag); UBIGINT is refused above
+			const bool uns = f.type_id == B2A_T_UTINYINT || f.type_id == B2A_T_USMALLINT || f.type_id == B2A_T_UINTEGER;
+			widths->push_back(static_cast<uint8_t>(f.out_width | (uns ? 0x80 : 0)));
 		}
 	}
 	if (!s->d_chunk_rows) {

@@ -265,7 +265,14 @@ void Reader::ParseRecordBatch(const uint8_t *tbl_buf, size_t tbl_len, size_t tab
 	size_t vdata;
 	uint32_t n_var = rb.vec(4, vdata, 8);
 	for (uint32_t i = 0; i < n_var; i++) {
-		out.variadic_counts.push_back(b.rd<int64_t>(vdata + 8 * size_t(i)));
+		const int64_t c = b.rd<int64_t>(vdata + 8 * size_t(i));
+		// a count is a number of buffers of THIS message: negative or larger than the buffer list is malformed (and
+		// would wrap the sums below / in the planner)
+		if (c < 0 || static_cast<uint64_t>(c) > n_buffers) {
+			throw Error(B2A_EIO, "Arrow IPC: variadicBufferCounts[" + std::to_string(i) + "] = " + std::to_string(c) +
+			                         " is not a valid buffer count");
+		}
+		out.variadic_counts.push_back(c);
 	}
 	if (!is_dictionary) {
 		if (n_nodes != static_cast<uint32_t>(flat_buffer_start.front())) {

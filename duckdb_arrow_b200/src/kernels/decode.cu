@@ -446,10 +446,15 @@ __device__ __forceinline__ void op_string_view(const b2a_task &t, const uint8_t 
 				uint32_t buffer_index = b.x;
 				uint32_t offset = b.y;
 				if (buffer_index >= static_cast<uint32_t>(t.param)) {
-					raise(err, B2A_DEV_BAD_OFFSETS);
+					raise(err, B2A_DEV_VIEW_RANGE);
 				} else {
-					uint64_t data_off = variadic[t.variadic0 + buffer_index] + offset;
-					v = make_string_t(image, data_off, len, ptr_origin + data_off);
+					const uint64_t *vb = variadic + t.variadic0 + 2 * static_cast<uint64_t>(buffer_index);
+					if (static_cast<uint64_t>(offset) + len > vb[1]) { // {image offset, length} of the data buffer
+						raise(err, B2A_DEV_VIEW_RANGE);
+					} else {
+						uint64_t data_off = vb[0] + offset;
+						v = make_string_t(image, data_off, len, ptr_origin + data_off);
+					}
 				}
 			}
 		}
@@ -529,6 +534,9 @@ __device__ __forceinline__ void op_list(const b2a_task &t, const uint8_t *__rest
 		}
 		if (i + 1 == t.rows) {
 			aux[(t.rows + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE] = o1;
+			if (static_cast<uint64_t>(o1) > static_cast<uint64_t>(t.param)) { // offsets are monotone: the last one bounds all
+				raise(err, B2A_DEV_LIST_CHILD);
+			}
 		}
 	}
 }
@@ -620,7 +628,8 @@ __device__ __forceinline__ i128 load_i128(const uint8_t *p, uint64_t i, bool swa
 // SetSelectionVector* fast path (no NULL indices, little-endian, index width 1/2/4): 8 rows per thread per trip —
 // 8-byte loads (IPC buffers are 8-byte aligned and tiles start on a multiple of 2 048 rows), two 16-byte sel_t stores.
 template <int W, bool SIGNED>
-__device__ __forceinline__ void dict_index_widen(const uint2 (&x)[W == 4 ? 4 : (W == 2 ? 2 : 1)], uint4 *d) {
+__device__ __forceinline__ void dict_index_widen(const uint2 (&x)[W == 4 ? 4 : (W == 2 ? 2 : 1)], uint4 *d,
+                                                 uint32_t limit, uint32_t *err) {
 	uint32_t v[8];
 	if (W == 1) {
 #pragma unroll
@@ -644,13 +653,17 @@ __device__ __forceinline__ void dict_index_widen(const uint2 (&x)[W == 4 ? 4 : (
 			v[2 * k + 1] = x[W == 4 ? k : 0].y;
 		}
 	}
+	const uint32_t m = max(max(max(v[0], v[1]), max(v[2], v[3])), max(max(v[4], v[5]), max(v[6], v[7])));
+	if (m >= limit) { // sign-extended negatives are >= limit as well
+		raise(err, B2A_DEV_DICT_INDEX);
+	}
 	stg_stream16(d, make_uint4(v[0], v[1], v[2], v[3]));
 	stg_stream16(d + 1, make_uint4(v[4], v[5], v[6], v[7]));
 }
 
 template <int W, bool SIGNED>
 __device__ __forceinline__ void dict_index_fast(const uint8_t *__restrict__ src, uint8_t *__restrict__ dst, uint64_t row0,
-                                                uint64_t nrows) {
+                                                uint64_t nrows, uint32_t limit, uint32_t *err) {
 	constexpr int L = W == 4 ? 4 : (W == 2 ? 2 : 1); // 8-byte loads per group of 8 rows
 	constexpr int U = W == 4 ? 2 : 4;                // groups in flight per thread
 	const uint64_t groups = nrows >> 3;
@@ -668,7 +681,7 @@ __device__ __forceinline__ void dict_index_fast(const uint8_t *__restrict__ src,
 		}
 #pragma unroll
 		for (int u = 0; u < U; u++) {
-			dict_index_widen<W, SIGNED>(x[u], d + 2 * (g + u * kThreads));
+			dict_index_widen<W, SIGNED>(x[u], d + 2 * (g + u * kThreads), limit, err);
 		}
 	}
 	for (; g < groups; g += kThreads) {
@@ -677,7 +690,7 @@ __device__ __forceinline__ void dict_index_fast(const uint8_t *__restrict__ src,
 		for (int k = 0; k < L; k++) {
 			x[k] = ldg_stream8(s + g * L + k);
 		}
-		dict_index_widen<W, SIGNED>(x, d + 2 * g);
+		dict_index_widen<W, SIGNED>(x, d + 2 * g, limit, err);
 	}
 }
 
@@ -688,15 +701,18 @@ __device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__re
 	const bool swap = t.flags & B2A_TASK_F_BSWAP;
 	if (t.op == B2A_OP_DICT_INDEX && t.n_masks == 0 && !swap && t.src_width <= 4) {
 		const bool sgn = t.flags & B2A_TASK_F_SIGNED;
+		const uint32_t limit = t.param > 0xFFFFFFFFll ? 0xFFFFFFFFu : static_cast<uint32_t>(t.param);
 		switch (t.src_width) {
 		case 1:
-			sgn ? dict_index_fast<1, true>(src, dst, row0, nrows) : dict_index_fast<1, false>(src, dst, row0, nrows);
+			sgn ? dict_index_fast<1, true>(src, dst, row0, nrows, limit, err)
+			    : dict_index_fast<1, false>(src, dst, row0, nrows, limit, err);
 			break;
 		case 2:
-			sgn ? dict_index_fast<2, true>(src, dst, row0, nrows) : dict_index_fast<2, false>(src, dst, row0, nrows);
+			sgn ? dict_index_fast<2, true>(src, dst, row0, nrows, limit, err)
+			    : dict_index_fast<2, false>(src, dst, row0, nrows, limit, err);
 			break;
 		default:
-			dict_index_fast<4, false>(src, dst, row0, nrows);
+			dict_index_fast<4, false>(src, dst, row0, nrows, limit, err);
 			break;
 		}
 		const uint64_t done = nrows & ~7ull; // the last (< 8) rows of the batch take the row-wise path below
@@ -824,6 +840,8 @@ __device__ __forceinline__ void op_scalar(const b2a_task &t, const uint8_t *__re
 				idx = static_cast<uint64_t>(t.param);
 			} else if (t.src_width == 8 && static_cast<uint64_t>(t.param) > 0xFFFFFFFFull && idx > 0xFFFFFFFFull) {
 				raise(err, B2A_DEV_INDEX_U32);
+			} else if (idx >= static_cast<uint64_t>(t.param)) { // negative indices land here too (sign-extended)
+				raise(err, B2A_DEV_DICT_INDEX);
 			}
 			reinterpret_cast<uint32_t *>(dst)[i] = static_cast<uint32_t>(idx);
 			break;

@@ -82,14 +82,19 @@ int LaunchDecompress(const DecompLaunch &l, void *stream) {
 		return 0;
 	}
 	const uint32_t ctas = (l.n_workers + kWarpsPerCta - 1) / kWarpsPerCta;
-	static bool attr_set = false;
-	if (!attr_set) {
+	// the attribute is per device: a process may launch on several GPUs
+	static bool attr_set[64] = {};
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+		dev = 0;
+	}
+	if (!attr_set[dev]) {
 		cudaError_t e = cudaFuncSetAttribute(b2a_decompress_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
 		                                     static_cast<int>(kSmemPerCta));
 		if (e != cudaSuccess) {
 			return static_cast<int>(e);
 		}
-		attr_set = true;
+		attr_set[dev] = true;
 	}
 	b2a_decompress_kernel<<<ctas, kWarpsPerCta * 32, kSmemPerCta, static_cast<cudaStream_t>(stream)>>>(
 	    l, DecompWorkspaceBytes());

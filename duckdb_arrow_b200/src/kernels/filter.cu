@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kFilterThreads)
 		for (uint32_t p = 0; p < fp.n_preds; p++) {
 			const uint64_t doff = __ldg(cc + 2 * p), voff = __ldg(cc + 2 * p + 1);
 			int64_t v[kFilterRowsPerThread];
-			switch (fp.widths[p]) {
+			switch (fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
 			case 1:
 				load_pred_values<int8_t>(out + doff, rows, v);
 				break;
@@ -83,6 +83,15 @@ __global__ void __launch_bounds__(kFilterThreads)
 				break;
 			case 4:
 				load_pred_values<int32_t>(out + doff, rows, v);
+				break;
+			case 0x81:
+				load_pred_values<uint8_t>(out + doff, rows, v);
+				break;
+			case 0x82:
+				load_pred_values<uint16_t>(out + doff, rows, v);
+				break;
+			case 0x84:
+				load_pred_values<uint32_t>(out + doff, rows, v);
 				break;
 			default:
 				load_pred_values<int64_t>(out + doff, rows, v);

@@ -18,6 +18,9 @@
 #define B2A_DEV_STRING_4GB 3u      /* "DuckDB does not support Strings over 4GB" */
 #define B2A_DEV_INDEX_U32 4u       /* "DuckDB only supports indices that fit on an uint32" */
 #define B2A_DEV_UNION_TAG 5u       /* "Arrow union tag out of range: %d" */
+#define B2A_DEV_DICT_INDEX 6u      /* dictionary index outside [0, dictionary length) */
+#define B2A_DEV_VIEW_RANGE 7u      /* string view: buffer index / offset + length outside its variadic data buffer */
+#define B2A_DEV_LIST_CHILD 8u      /* list: last offset beyond the child array */
 
 struct b2a_mask_ref {
 	uint64_t src; /* image offset of an Arrow validity bitmap */

@@ -494,7 +494,8 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		uint64_t data_bytes = 0;
 		for (size_t i = 0; i < n_variadic; i++) {
 			const BufferSlice &vb = rb.buffers[buf_idx + i];
-			variadic.push_back(vb.offset);
+			variadic.push_back(vb.offset); // (offset, length) pairs: the kernel checks offset + len of every long view
+			variadic.push_back(vb.length);
 			Touch(vb.offset, vb.length);
 			data_bytes += vb.length;
 		}
@@ -536,6 +537,8 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		t.dst = slot.data_off = Alloc(L * 16);
 		uint64_t n_chunks_col = (L + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
 		t.aux = slot.aux_off = Alloc((n_chunks_col + 1) * 8);
+		// the child's node follows in pre-order: the last offset must not exceed its length (nanoarrow FULL validation)
+		t.param = node_idx < rb.nodes.size() ? static_cast<int64_t>(rb.nodes[node_idx].length) : 0;
 		if (!chain.levels.empty()) {
 			t.variadic0 = static_cast<uint32_t>(variadic.size());
 			t.src2_len = chain.levels.size();

@@ -255,6 +255,13 @@ int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_
 
 /* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
 int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
+/* Host buffers in, DEVICE vectors out, for consumers that run on the GPU (b2a_scan_filter, b2a_scan_sum_product): only
+ * the buffers of the PROJECTED columns cross PCIe (the reference's projection pushdown, src/scanner/read_arrow.cpp:44-50,
+ * base_stream_reader.cpp:146-212), slice by slice behind the decode launches; nothing is copied back.  Vectors land in
+ * d_out (device, b2a_scan_sizes.out_bytes, 256-byte aligned); string_t point into the device image.  `cuda_stream` first
+ * orders the pipeline behind the caller's earlier work on d_out and is then made to wait for the last decode: work
+ * queued on it afterwards sees every vector.  Not for B2A_SCAN_HOST_ALIAS scans. */
+int b2a_read_arrow_device(b2a_scan *s, void *d_out, uint32_t n_slices, void *cuda_stream);
 
 /* ---------------- src/file_scanner: multi-file read_arrow (lists, globs, union_by_name, filename, hive) ----------------
  * Replaces what the reference gets from DuckDB's MultiFileReader framework through ArrowMultiFileInfo / ArrowFileScan

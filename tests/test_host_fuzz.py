@@ -79,3 +79,41 @@ def test_mutated_streams_of_the_rarer_layouts_never_crash(b2a):
         planned += 1
         assert s.image_lo + s.image_bytes <= len(b) + 16
     assert planned > 0 and rejected > 0
+
+
+def test_negative_variadic_buffer_counts_are_rejected(b2a):
+    """RecordBatch.variadicBufferCounts entries are buffer counts of the message: a negative one (or a pair like {-1, +1}
+    that sums to what the schema needs) must end in B2AError at parse time — it used to wrap the planner's bounds check."""
+    import struct
+
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+    long_ = ["a string view longer than twelve bytes %d" % i for i in range(50)]
+    t = pa.table({"a": pa.array(long_, pa.string_view()), "b": pa.array(long_[::-1], pa.string_view())})
+    sink = pa.BufferOutputStream()
+    with ipc.new_stream(sink, t.schema) as w:
+        w.write_table(t)
+    data = sink.getvalue().to_pybytes()
+    r = b2a.ArrowIPCReader.open_buffers([data])
+    b2a.ArrowScan(r, device=-1)
+    # the vector [1, 1] of int64 counts: u32 length 2, then two int64 ones (8-byte aligned after the length)
+    pos = [i for i in range(0, len(data) - 24, 4) if data[i:i + 4] == struct.pack("<I", 2)
+           and data[i + 4:i + 8] in (b"\0\0\0\0",) and data[i + 8:i + 24] == struct.pack("<qq", 1, 1)]
+    pos += [i for i in range(0, len(data) - 20, 4) if data[i:i + 4] == struct.pack("<I", 2)
+            and data[i + 4:i + 20] == struct.pack("<qq", 1, 1)]
+    assert pos, "variadicBufferCounts vector not found in the RecordBatch message"
+    hit = 0
+    for i in pos:
+        start = i + 8 if data[i + 8:i + 24] == struct.pack("<qq", 1, 1) else i + 4
+        for counts in ((-1, 3), (3, -1), (-1, 1), (1 << 40, 1), (-(1 << 62), 1)):
+            b = bytearray(data)
+            b[start:start + 16] = struct.pack("<qq", *counts)
+            try:
+                rr = b2a.ArrowIPCReader.open_buffers([bytes(b)])
+                b2a.ArrowScan(rr, device=-1)
+            except b2a.B2AError as e:
+                hit += 1
+                assert "variadicBufferCounts" in str(e) or "buffers" in str(e)
+                continue
+            raise AssertionError(f"counts {counts} were accepted")
+    assert hit >= 5
