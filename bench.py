@@ -128,6 +128,28 @@ def stream_path(sf: float):
     return path, "synthetic"
 
 
+def build_stream(rows: int, seed: int, pin: bool, sf: float | None = None):
+    """The lineitem stream as ONE host tensor (tests / tools): the dbgen stream of the scale factor with `rows` rows
+    when oracle/_ref is present, else the numpy-drawn stand-in.  -> (torch uint8 tensor, stream bytes)"""
+    import torch
+    from tools import dbgen_lineitem as D
+    sf_of = {v: k for k, v in D.ROWS.items()}
+    if D.available() and (sf is not None or rows in sf_of):
+        path = D.lineitem_path(sf if sf is not None else sf_of[rows], BATCH_ROWS, log=log)
+        size = os.path.getsize(path)
+        host = torch.empty(size + 64, dtype=torch.uint8, pin_memory=pin)
+        with open(path, "rb") as f:
+            f.readinto(host.numpy()[:size])
+        return host, size
+    import pyarrow as pa
+    from tools import lineitem
+    cap = int(rows * 150) + (1 << 20)
+    host = torch.empty(cap, dtype=torch.uint8, pin_memory=pin)
+    sink = pa.FixedSizeBufferWriter(pa.py_buffer(host.numpy()))
+    lineitem.write_stream(sink, rows, seed=seed, unique=16)
+    return host, sink.tell()
+
+
 def batch_index(path):
     from tools import dbgen_lineitem as D
     return D.message_index(path)
@@ -595,7 +617,7 @@ def leg_multifile(ctx, args, path, steps):
     files_per_gpu, rows_per_file = args.files_per_gpu, int(600_037_902 // 64 * min(1.0, args.sf / 10.0))
     paths = _multifile_inputs(ctx, path, files_per_gpu * ctx.world, rows_per_file)
     mine = ctx.P.file_shard(paths, ctx.rank, ctx.world)
-    mfs = b2a.MultiFileScan(paths, device=ctx.local_rank, union_by_name=True)   # global bind: union over ALL files
+    mfs = b2a.api.MultiFileScan(paths, device=ctx.local_rank, union_by_name=True)   # global bind: union over ALL files
     cur = torch.cuda.current_stream()
     files, alg, my_rows = [], 0, 0
     for p in mine:

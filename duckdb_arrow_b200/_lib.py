@@ -85,6 +85,11 @@ WRITE_LIST_VIEW = 0x2  # B2A_WRITE_LIST_VIEW
 WRITE_STRING_VIEW = 0x4  # B2A_WRITE_STRING_VIEW
 
 
+class HostStream(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("size", C.c_uint64), ("n_batches", C.c_uint64), ("writer", C.c_void_p),
+                ("gpu_launches", C.c_uint64), ("priv", C.c_void_p)]
+
+
 class MultiFileOptions(C.Structure):
     _fields_ = [("union_by_name", C.c_uint32), ("filename", C.c_uint32), ("hive_partitioning", C.c_uint32),
                 ("hive_types_autocast", C.c_uint32), ("filename_column", C.c_char_p)]
@@ -148,6 +153,10 @@ def _load() -> C.CDLL:
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
         "b2a_read_arrow_device": (i32, [vp, vp, u32, vp]),
+        "b2a_write_arrow_host": (i32, [P(Vector), u32, u64, P(WriteOptions), i32, P(HostStream)]),
+        "b2a_host_stream_release": (None, [P(HostStream)]),
+        "b2a_pinned_alloc": (i32, [P(vp), u64]),
+        "b2a_pinned_free": (None, [vp]),
         "b2a_multifile_open": (i32, [P(C.c_char_p), u32, P(MultiFileOptions), P(vp)]),
         "b2a_multifile_close": (None, [vp]),
         "b2a_multifile_counts": (i32, [vp, P(u32), P(u32), P(u32)]),

@@ -27,6 +27,7 @@ SOURCES = [
     "kernels/scatter.cu",
     "capi.cu",
     "capi_writer.cu",
+    "capi_writer_host.cu",
     "capi_multifile.cu",
 ]
 

@@ -574,6 +574,44 @@ struct HostPipe {
 	cudaEvent_t ev_user = nullptr;
 	uint8_t *d_out = nullptr;
 	uint64_t d_out_bytes = 0;
+	int device = -1;
+	HostPipe() = default;
+	HostPipe(const HostPipe &) = delete;
+	HostPipe &operator=(const HostPipe &) = delete;
+	// a DuckDB-side caller runs the pipeline on short-lived worker threads: everything goes back when the thread ends
+	~HostPipe() {
+		if (!in || device < 0 || cudaSetDevice(device) != cudaSuccess) {
+			(void)cudaGetLastError();
+			return;
+		}
+		cudaStreamSynchronize(in);
+		cudaStreamSynchronize(compute);
+		cudaStreamSynchronize(out);
+		for (auto e : ev_in) {
+			cudaEventDestroy(e);
+		}
+		for (auto e : ev_c) {
+			cudaEventDestroy(e);
+		}
+		for (auto e : ev_out) {
+			cudaEventDestroy(e);
+		}
+		if (ev_start) {
+			cudaEventDestroy(ev_start);
+		}
+		if (ev_user) {
+			cudaEventDestroy(ev_user);
+		}
+		for (uint32_t k = 0; k < kRing; k++) {
+			cudaFreeHost(h_stage[k]);
+			cudaFree(d_stage[k]);
+		}
+		cudaFree(d_out);
+		cudaStreamDestroy(in);
+		cudaStreamDestroy(compute);
+		cudaStreamDestroy(out);
+		(void)cudaGetLastError();
+	}
 };
 // keyed by device: streams, events, staging rings and the arena belong to the device they were created on
 // (a thread may scan on several GPUs one after the other)
@@ -598,6 +636,7 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 	NEED_DEVICE(s);
 	const ScanPlan &p = s->plan;
 	HostPipe &hp = g_pipes[s->device];
+	hp.device = s->device;
 	const bool to_host = d_out_user == nullptr;
 	if (!hp.in) {
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking));

@@ -408,6 +408,32 @@ uint64_t b2a_writer_gpu_launches(b2a_writer *w);
  * right after b2a_writer_create, also without a device.  The pointer stays valid until b2a_writer_destroy. */
 int b2a_writer_schema_message(b2a_writer *w, const void **data, uint64_t *size);
 
+/* ---------------- host-facing writer: HOST vectors in, HOST stream bytes out ----------------
+ * What COPY ... (FORMAT ARROWS) and to_arrow_ipc hold is host memory: the flat vectors of one row group
+ * (ColumnDataCollectionSerializer::Serialize(ColumnDataCollection&) concatenates the collection into ONE DataChunk and
+ * runs ArrowConverter::ToArrowArray over it, src/writer/column_data_collection_serializer.cpp:80-115).  `host_columns`
+ * is that chunk as a b2a_vector tree with HOST pointers (data, validity; string_t records may point into DuckDB's
+ * string heaps).  The call uploads the tree, runs the b2a_writer kernels (measure + encode), and returns the complete
+ * stream — Schema message, one RecordBatch message per `row_group_size` rows, end-of-stream marker — in pinned host
+ * memory.  `writer` stays valid until release: b2a_writer_batch(writer, i) gives the byte range of message i, so a
+ * COPY sink writes the schema once and then only the RecordBatch messages of every row group. */
+typedef struct b2a_host_stream {
+	void *data;            /* pinned host memory, `size` bytes: the stream */
+	uint64_t size;
+	uint64_t n_batches;
+	b2a_writer *writer;    /* owned by the stream */
+	uint64_t gpu_launches; /* kernels launched for this stream */
+	void *priv;
+} b2a_host_stream;
+int b2a_write_arrow_host(const b2a_vector *host_columns, uint32_t n_columns, uint64_t rows, const b2a_write_options *opt,
+                         int device, b2a_host_stream *out);
+void b2a_host_stream_release(b2a_host_stream *s);
+
+/* Pinned (page-locked) host memory for the arenas b2a_read_arrow_host fills: a DuckDB-side caller must not link the
+ * CUDA runtime itself. */
+int b2a_pinned_alloc(void **out, uint64_t bytes);
+void b2a_pinned_free(void *p);
+
 #ifdef __cplusplus
 }
 #endif

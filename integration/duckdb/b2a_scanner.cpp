@@ -1,9 +1,8 @@
-#include "b2a_file_scan.hpp"
+// see b2a_scanner.hpp
+#include "b2a_scanner.hpp"
 
 #include "duckdb/common/exception.hpp"
 #include "duckdb/common/exception/conversion_exception.hpp"
-#include "duckdb/common/multi_file/multi_file_reader.hpp"
-#include "duckdb/common/types/vector.hpp"
 #include "duckdb/main/query_result.hpp"
 
 #include <cstdlib>
@@ -11,20 +10,8 @@
 namespace duckdb {
 namespace ext_nanoarrow {
 
-// ---------------------------------------------------------------------------------------------- slab
-B2ASlab::B2ASlab(idx_t bytes) : size(bytes) {
-	// production: cudaHostAlloc (pinned) so that b2a_read_arrow_host moves data at full PCIe rate
-	data = reinterpret_cast<data_ptr_t>(std::aligned_alloc(256, (bytes + 255) & ~idx_t(255)));
-	if (!data) {
-		throw OutOfMemoryException("B2ASlab: cannot allocate %llu bytes", bytes);
-	}
-}
-B2ASlab::~B2ASlab() {
-	std::free(data);
-}
-
-// ---------------------------------------------------------------------------------------------- errors
-void B2AFileScan::Throw(int status) const {
+// ---------------------------------------------------------------------------------------------- errors / device
+void B2AThrow(int status) {
 	const string msg = b2a_last_error();
 	switch (status) { // b2a_status names the DuckDB exception class the reference would have thrown
 	case B2A_EINVAL:
@@ -37,13 +24,77 @@ void B2AFileScan::Throw(int status) const {
 		throw ConversionException(msg);
 	case B2A_EOOM:
 		throw OutOfMemoryException(msg);
+	case B2A_ECUDA: // no device / a CUDA failure: an I/O-class error, not a reason to invalidate the database
+		throw IOException(msg);
 	default:
 		throw InternalException(msg);
 	}
 }
 
+int B2ADevice() {
+	const char *e = std::getenv("B2A_DEVICE");
+	return e ? std::atoi(e) : 0;
+}
+
+// ---------------------------------------------------------------------------------------------- pinned arena pool
+namespace {
+struct SlabPool {
+	std::mutex mu;
+	vector<std::pair<data_ptr_t, idx_t>> free_list;
+	idx_t cached_bytes = 0;
+	static constexpr idx_t kMaxCached = idx_t(4) << 30;
+	~SlabPool() {
+		for (auto &e : free_list) {
+			b2a_pinned_free(e.first);
+		}
+	}
+};
+SlabPool &Pool() {
+	static SlabPool pool;
+	return pool;
+}
+} // namespace
+
+shared_ptr<B2ASlab> B2ASlab::Acquire(idx_t bytes) {
+	bytes = (bytes + 255) & ~idx_t(255);
+	auto &pool = Pool();
+	{
+		std::lock_guard<std::mutex> guard(pool.mu);
+		idx_t best = pool.free_list.size();
+		for (idx_t i = 0; i < pool.free_list.size(); i++) { // smallest arena that fits
+			if (pool.free_list[i].second >= bytes &&
+			    (best == pool.free_list.size() || pool.free_list[i].second < pool.free_list[best].second)) {
+				best = i;
+			}
+		}
+		if (best != pool.free_list.size() && pool.free_list[best].second <= 2 * bytes + (idx_t(1) << 20)) {
+			auto e = pool.free_list[best];
+			pool.free_list.erase(pool.free_list.begin() + NumericCast<int64_t>(best));
+			pool.cached_bytes -= e.second;
+			return make_shared_ptr<B2ASlab>(e.first, e.second);
+		}
+	}
+	void *p = nullptr;
+	int rc = b2a_pinned_alloc(&p, bytes);
+	if (rc) {
+		B2AThrow(rc);
+	}
+	return make_shared_ptr<B2ASlab>(data_ptr_cast(p), bytes);
+}
+
+B2ASlab::~B2ASlab() {
+	auto &pool = Pool();
+	std::lock_guard<std::mutex> guard(pool.mu);
+	if (pool.cached_bytes + capacity <= SlabPool::kMaxCached) {
+		pool.free_list.emplace_back(data, capacity);
+		pool.cached_bytes += capacity;
+	} else {
+		b2a_pinned_free(data);
+	}
+}
+
 // ---------------------------------------------------------------------------------------------- schema
-LogicalType B2AFileScan::TypeOf(uint32_t flat) const {
+LogicalType B2AScanner::TypeOf(uint32_t flat) const {
 	const b2a_field_info &f = fields[flat];
 	switch (f.type_id) {
 	case B2A_T_SQLNULL:
@@ -135,13 +186,10 @@ LogicalType B2AFileScan::TypeOf(uint32_t flat) const {
 	}
 }
 
-B2AFileScan::B2AFileScan(ClientContext &context, const OpenFileInfo &file_p, int device_p)
-    : BaseFileReader(file_p), device(device_p) {
-	// ArrowFileScan::ArrowFileScan (arrow_file_scan.cpp:11-26): open, read the schema, names + types, de-duplicate
-	int rc = b2a_reader_open_file(file.path.c_str(), &reader);
-	if (rc) {
-		Throw(rc);
-	}
+
+B2AScanner::B2AScanner(b2a_reader *reader_p, int device_p) : device(device_p), reader(reader_p) {
+	// ArrowFileScan::ArrowFileScan (arrow_file_scan.cpp:11-26) / ScanArrowIPCBind (scan_arrow_ipc.cpp:20-48): read the
+	// schema, names + types (ArrowTableFunction::PopulateArrowTableType), de-duplicate the names
 	uint32_t n_top = 0, n_flat = 0;
 	b2a_reader_num_fields(reader, &n_top, &n_flat);
 	fields.resize(n_flat);
@@ -151,7 +199,11 @@ B2AFileScan::B2AFileScan(ClientContext &context, const OpenFileInfo &file_p, int
 	for (uint32_t i = 0; i < n_flat; i++) {
 		if (fields[i].parent < 0) {
 			top_level.push_back(i);
-			names.emplace_back(fields[i].name);
+			string name = fields[i].name;
+			if (name.empty()) { // arrow.cpp:31-34
+				name = "v" + std::to_string(names.size());
+			}
+			names.push_back(std::move(name));
 			types.push_back(TypeOf(i));
 		}
 	}
@@ -159,86 +211,163 @@ B2AFileScan::B2AFileScan(ClientContext &context, const OpenFileInfo &file_p, int
 	if (types.empty()) {
 		throw InvalidInputException("Provided table/dataframe must have at least one column");
 	}
-	columns = MultiFileColumnDefinition::ColumnsFromNamesAndTypes(names, types);
 	const void *img = nullptr;
 	uint64_t img_size = 0;
 	b2a_reader_image(reader, &img, &img_size);
 	image = const_data_ptr_cast(img);
 }
 
-B2AFileScan::~B2AFileScan() {
+B2AScanner::Slice::~Slice() {
+	dictionaries.clear();
 	if (scan) {
 		b2a_scan_destroy(scan);
 	}
+}
+
+B2AScanner::~B2AScanner() {
+	if (worker.joinable()) {
+		{
+			std::lock_guard<std::mutex> guard(mu);
+			stop = true;
+		}
+		cv.notify_all();
+		worker.join();
+	}
+	current.reset();
+	result.reset();
 	if (reader) {
 		b2a_reader_close(reader);
 	}
 }
 
-shared_ptr<BaseUnionData> B2AFileScan::GetUnionData(idx_t file_idx) {
-	auto data = make_shared_ptr<BaseUnionData>(file);
-	data->names = names;
-	data->types = types;
-	return data;
+// ---------------------------------------------------------------------------------------------- slices
+unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
+	auto s = make_uniq<Slice>();
+	s->batch_lo = lo;
+	s->batch_hi = hi;
+	// DirectConversion columns alias the stream image (zero copy, as in the reference); everything that needs
+	// conversion goes host -> device -> kernels -> host inside b2a_read_arrow_host
+	int rc = b2a_scan_create_ex(reader, device, lo, hi, B2A_SCAN_HOST_ALIAS, &s->scan);
+	if (rc == B2A_OK) {
+		uint64_t image_lo, image_bytes, out_bytes, algorithmic, n_tasks, n_tiles;
+		b2a_scan_sizes(s->scan, &image_lo, &image_bytes, &out_bytes, &algorithmic, &n_tasks, &n_tiles);
+		try {
+			s->slab = B2ASlab::Acquire(NumericCast<idx_t>(out_bytes));
+			rc = b2a_read_arrow_host(s->scan, s->slab->data, 0);
+		} catch (std::exception &e) {
+			s->status = B2A_EOOM;
+			s->error = e.what();
+			return s;
+		}
+	}
+	if (rc != B2A_OK) {
+		s->status = rc;
+		s->error = b2a_last_error();
+	}
+	return s;
 }
 
-// ---------------------------------------------------------------------------------------------- scan
-bool B2AFileScan::TryInitializeScan(ClientContext &context, GlobalTableFunctionState &gstate,
-                                    LocalTableFunctionState &lstate) {
-	// one scan per file, like the reference (arrow_file_scan.cpp:35-41); a second thread is turned away
-	bool expected = false;
-	if (!claimed.compare_exchange_strong(expected, true)) {
-		return false;
+void B2AScanner::WorkerLoop() {
+	while (true) {
+		uint64_t lo, hi;
+		{
+			std::unique_lock<std::mutex> lock(mu);
+			cv.wait(lock, [&] { return stop || has_request; });
+			if (stop) {
+				return;
+			}
+			lo = req_lo;
+			hi = req_hi;
+			has_request = false;
+		}
+		auto s = Load(lo, hi);
+		{
+			std::lock_guard<std::mutex> guard(mu);
+			result = std::move(s);
+			has_result = true;
+		}
+		cv.notify_all();
 	}
-	// projection pushdown: IPCStreamReader::SetColumnProjection (base_stream_reader.cpp:146-212)
+}
+
+void B2AScanner::Request(uint64_t slice) {
+	std::lock_guard<std::mutex> guard(mu);
+	req_lo = slice_bounds[slice];
+	req_hi = slice_bounds[slice + 1];
+	has_request = true;
+	cv.notify_all();
+}
+
+unique_ptr<B2AScanner::Slice> B2AScanner::Take() {
+	std::unique_lock<std::mutex> lock(mu);
+	cv.wait(lock, [&] { return has_result; });
+	has_result = false;
+	return std::move(result);
+}
+
+void B2AScanner::Begin(const vector<idx_t> &columns) {
 	vector<const char *> proj;
 	projected_flat.clear();
-	for (auto &index : column_indexes) {
-		const auto col = index.GetPrimaryIndex();
+	for (auto col : columns) {
 		if (col >= top_level.size()) {
-			throw InternalException("B2AFileScan: column index %llu out of range", col);
+			throw InternalException("B2AScanner: column index %llu out of range", col);
 		}
 		proj.push_back(names[col].c_str());
 		projected_flat.push_back(top_level[col]);
 	}
-	int rc;
 	if (!proj.empty()) {
-		rc = b2a_reader_set_projection(reader, proj.data(), NumericCast<uint32_t>(proj.size()));
+		int rc = b2a_reader_set_projection(reader, proj.data(), NumericCast<uint32_t>(proj.size()));
 		if (rc) {
-			Throw(rc);
+			B2AThrow(rc);
 		}
 	}
-	uint64_t n_rows = 0;
-	b2a_reader_num_batches(reader, &n_batches, &n_rows);
-	// DirectConversion columns alias the file image (zero copy, as in the reference); everything that needs conversion
-	// goes host -> device -> kernel -> host inside b2a_read_arrow_host
-	rc = b2a_scan_create_ex(reader, device, 0, n_batches, B2A_SCAN_HOST_ALIAS, &scan);
-	if (rc) {
-		Throw(rc);
+	b2a_reader_num_batches(reader, &n_batches, &total_rows);
+	// slices of whole record batches, ~256 MiB of message bodies each
+	static const uint64_t target = [] {
+		const char *e = std::getenv("B2A_SLICE_MB");
+		return (e ? NumericCast<uint64_t>(std::atoll(e)) : 256) << 20;
+	}();
+	slice_bounds.clear();
+	slice_bounds.push_back(0);
+	uint64_t acc = 0;
+	for (uint64_t b = 0; b < n_batches; b++) {
+		b2a_batch_info bi;
+		b2a_reader_batch_info(reader, b, &bi);
+		acc += bi.body_length;
+		if (acc >= target && b + 1 < n_batches) {
+			slice_bounds.push_back(b + 1);
+			acc = 0;
+		}
 	}
-	uint64_t image_lo, image_bytes, out_bytes, algorithmic, n_tasks, n_tiles;
-	b2a_scan_sizes(scan, &image_lo, &image_bytes, &out_bytes, &algorithmic, &n_tasks, &n_tiles);
-	slab = make_shared_ptr<B2ASlab>(NumericCast<idx_t>(out_bytes));
-	rc = b2a_read_arrow_host(scan, slab->data, 0);
-	if (rc) {
-		Throw(rc);
+	if (n_batches > 0) {
+		slice_bounds.push_back(n_batches);
 	}
-	batch = 0;
-	chunk_offset = 0;
-	return true;
+	n_slices = slice_bounds.size() > 1 ? slice_bounds.size() - 1 : 0;
+	requested = taken = 0;
+	current.reset();
+	rows_done = 0;
+	if (n_slices > 0) {
+		worker = std::thread([this] { WorkerLoop(); });
+		Request(0);
+		requested = 1;
+	}
 }
 
-void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t count) {
+// ---------------------------------------------------------------------------------------------- vectors
+void B2AScanner::PointVector(Slice &slice, Vector &vec, uint32_t flat, uint64_t batch, idx_t offset, idx_t count) {
+	b2a_scan *scan = slice.scan;
+	const shared_ptr<B2ASlab> &slab = slice.slab;
+	auto &dictionaries = slice.dictionaries;
 	const b2a_field_info &f = fields[flat];
 	b2a_column_out co;
 	int rc = b2a_scan_column(scan, batch, flat, &co);
 	if (rc) {
-		Throw(rc);
+		B2AThrow(rc);
 	}
 	// validity: an absent mask means the reference would not have touched it either (all valid)
 	if (co.validity_off != B2A_NONE && f.dict_id < 0) {
 		if (offset % 64 != 0) {
-			throw InternalException("B2AFileScan: vectors start on multiples of 64 rows");
+			throw InternalException("B2AScanner: vectors start on multiples of 64 rows");
 		}
 		FlatVector::Validity(vec).Initialize(
 		    reinterpret_cast<validity_t *>(slab->data + co.validity_off) + offset / 64, count);
@@ -252,7 +381,7 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 			uint32_t dict_flat = 0;
 			rc = b2a_scan_dictionary(scan, flat, &dco, &dict_flat);
 			if (rc) {
-				Throw(rc);
+				B2AThrow(rc);
 			}
 			auto base = make_uniq<Vector>(vec.GetType(), NumericCast<idx_t>(dco.rows) + 1);
 			FlatVector::SetData(*base, slab->data + dco.data_off);
@@ -276,7 +405,7 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 		auto &entries = StructVector::GetEntries(vec);
 		idx_t i = 0;
 		for (int32_t c = f.first_child; c >= 0; c = fields[NumericCast<uint32_t>(c)].next_sibling) {
-			PointVector(*entries[i++], NumericCast<uint32_t>(c), offset, count);
+			PointVector(slice, *entries[i++], NumericCast<uint32_t>(c), batch, offset, count);
 		}
 		return;
 	}
@@ -291,7 +420,7 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 		tag.GetBuffer()->SetAuxiliaryData(make_uniq<B2ASlabAuxData>(slab));
 		idx_t i = 1;
 		for (int32_t c = f.first_child; c >= 0; c = fields[NumericCast<uint32_t>(c)].next_sibling) {
-			PointVector(*entries[i++], NumericCast<uint32_t>(c), offset, count);
+			PointVector(slice, *entries[i++], NumericCast<uint32_t>(c), batch, offset, count);
 		}
 		return;
 	}
@@ -311,14 +440,14 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 			child_hi = NumericCast<idx_t>(starts[k + 1]);
 		}
 		auto &child = ListVector::GetEntry(vec);
-		PointVector(child, NumericCast<uint32_t>(f.first_child), child_lo, child_hi - child_lo);
+		PointVector(slice, child, NumericCast<uint32_t>(f.first_child), batch, child_lo, child_hi - child_lo);
 		ListVector::SetListSize(vec, child_hi - child_lo);
 		break;
 	}
 	case B2A_T_ARRAY: {
 		auto &child = ArrayVector::GetEntry(vec);
 		const auto k = NumericCast<idx_t>(f.param);
-		PointVector(child, NumericCast<uint32_t>(f.first_child), offset * k, count * k);
+		PointVector(slice, child, NumericCast<uint32_t>(f.first_child), batch, offset * k, count * k);
 		return;
 	}
 	default: {
@@ -332,26 +461,69 @@ void B2AFileScan::PointVector(Vector &vec, uint32_t flat, idx_t offset, idx_t co
 	vec.GetBuffer()->SetAuxiliaryData(make_uniq<B2ASlabAuxData>(slab));
 }
 
-void B2AFileScan::Scan(ClientContext &context, GlobalTableFunctionState &global_state,
-                       LocalTableFunctionState &local_state, DataChunk &chunk) {
+void B2AScanner::Next(DataChunk &chunk) {
 	// ArrowTableFunction::ArrowScanFunction (duckdb/src/function/table/arrow.cpp:172-201): at most 2 048 rows per call,
 	// next record batch when the current one is exhausted.  No per-chunk conversion is left: vectors are re-pointed.
-	while (batch < n_batches) {
-		b2a_batch_info bi;
-		b2a_reader_batch_info(reader, batch, &bi);
-		if (chunk_offset < bi.rows) {
-			const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, NumericCast<idx_t>(bi.rows) - chunk_offset);
-			for (idx_t c = 0; c < chunk.ColumnCount() && c < projected_flat.size(); c++) {
-				PointVector(chunk.data[c], projected_flat[c], chunk_offset, n);
+	while (true) {
+		if (!current) {
+			if (taken == n_slices) {
+				chunk.SetCardinality(0);
+				return;
 			}
-			chunk.SetCardinality(n);
-			chunk_offset += n;
-			return;
+			current = Take();
+			if (current->status != B2A_OK) {
+				string msg = current->error;
+				int status = current->status;
+				current.reset();
+				// re-raise on the executor's thread with the class the reference would have used
+				switch (status) {
+				case B2A_EINVAL:
+					throw InvalidInputException(msg);
+				case B2A_EIO:
+					throw IOException(msg);
+				case B2A_ENOTIMPL:
+					throw NotImplementedException(msg);
+				case B2A_ECONVERSION:
+					throw ConversionException(msg);
+				case B2A_EOOM:
+					throw OutOfMemoryException(msg);
+				case B2A_ECUDA:
+					throw IOException(msg);
+				default:
+					throw InternalException(msg);
+				}
+			}
+			gpu_launches += b2a_scan_gpu_launches(current->scan);
+			batch = current->batch_lo;
+			chunk_offset = 0;
+			taken++;
+			if (requested < n_slices) { // decode the following slice while this one is consumed
+				Request(requested);
+				requested++;
+			}
 		}
-		batch++;
-		chunk_offset = 0;
+		while (batch < current->batch_hi) {
+			b2a_batch_info bi;
+			b2a_reader_batch_info(reader, batch, &bi);
+			if (chunk_offset < bi.rows) {
+				const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, NumericCast<idx_t>(bi.rows) - chunk_offset);
+				for (idx_t c = 0; c < chunk.ColumnCount() && c < projected_flat.size(); c++) {
+					PointVector(*current, chunk.data[c], projected_flat[c], batch, chunk_offset, n);
+				}
+				chunk.SetCardinality(n);
+				chunk_offset += n;
+				rows_done += n;
+				return;
+			}
+			batch++;
+			chunk_offset = 0;
+		}
+		current.reset(); // the slab lives on for as long as a vector points into it
 	}
-	chunk.SetCardinality(0);
+}
+
+double B2AScanner::Progress() const {
+	return total_rows ? 100.0 * static_cast<double>(rows_done) / static_cast<double>(total_rows) : 100.0;
 }
 
 } // namespace ext_nanoarrow

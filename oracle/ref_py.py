@@ -61,12 +61,14 @@ def lib() -> C.CDLL:
         _lib.ref_file_open.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         _lib.ref_file_read.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_char_p, C.c_int]
         _lib.ref_file_close.argtypes = [C.c_void_p]
+        _lib.ref_load_extension.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
         err = C.create_string_buffer(512)
         if _lib.ref_open(err, 512) != 0:
             raise RefError(4, err.value.decode())
     return _lib
 
 
+_loaded_extensions = set()
 _streams = []  # exported ArrowArrayStream structs referenced by registered views
 
 
@@ -203,3 +205,14 @@ class BufferedFile:
 
     def __del__(self):
         self.close()
+
+
+def load_extension(path: str, name: str = "nanoarrow") -> None:
+    """dlopen + <name>_init(DatabaseInstance&) on the session's database (what LOAD does after its signature check)."""
+    path = os.path.abspath(path)
+    if path in _loaded_extensions:
+        return
+    err = C.create_string_buffer(1024)
+    if lib().ref_load_extension(path.encode(), name.encode(), err, 1024) != 0:
+        raise RefError(4, err.value.decode())
+    _loaded_extensions.add(path)

@@ -27,6 +27,7 @@
 #include "tpch_extension.hpp"
 
 #include <chrono>
+#include <dlfcn.h>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -737,6 +738,30 @@ int ref_export_next(void *handle, uint64_t batch_rows, ArrowArray *out_array, ch
 
 void ref_export_end(void *handle) {
 	delete (Export *)handle;
+}
+
+// Loads a DuckDB extension library into the session's database the way DuckDB's loader does once it has verified the
+// file (duckdb/src/main/extension/extension_load.cpp:529-548): dlopen, dlsym("<name>_init"), call it with the
+// DatabaseInstance.  Used by the tests to run the reference's SQL statements against integration/duckdb's
+// libnanoarrow_b2a.so — the drop-in surface over libb2arrow.so — inside the reference's own DuckDB.
+int ref_load_extension(const char *path, const char *name, char *err, int errlen) {
+	try {
+		auto &s = session();
+		void *h = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+		if (!h) {
+			throw IOException("dlopen(%s): %s", path, dlerror());
+		}
+		std::string sym = std::string(name) + "_init";
+		typedef void (*init_t)(DatabaseInstance &);
+		auto init = (init_t)dlsym(h, sym.c_str());
+		if (!init) {
+			throw IOException("%s has no symbol %s", path, sym);
+		}
+		init(*s.db->instance);
+		return 0;
+	} catch (std::exception &e) {
+		return fail(err, errlen, e);
+	}
 }
 
 const char *ref_source_id() {

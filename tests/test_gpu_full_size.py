@@ -12,7 +12,9 @@ other row is checked on the device, exactly, by statements that do not depend on
   * pushed-down filters + the Q6 aggregate == numpy over pyarrow's decoding of all rows;
   * COPY -> read round trip (test/sql/write_arrow_stream.test:17-25): the vectors written by the encode kernels, read
     back by pyarrow, equal the source batches column by column.
-Source = tools/lineitem (16 distinct batches cycled, like bench.py)."""
+Source = bench.build_stream: the dbgen SF10 stream written through the reference's appender (tools/dbgen_lineitem.py)
+where oracle/_ref is in the tree — then the COPY test also demands that every message BODY the encode kernels write is
+byte-identical to the body the reference's ArrowAppender produced for the same rows — else tools/lineitem."""
 import numpy as np
 import pyarrow as pa
 import pyarrow.ipc as ipc
@@ -175,4 +177,25 @@ def test_sf10_copy_round_trip(b2a, sf10):
             assert a.column(i).equals(b.column(i)), (n, a.schema.names[i])
         n += 1
     assert n == 489
+    # where the source stream was written by the REFERENCE's appender (dbgen data): every record-batch body of the GPU
+    # writer must be byte-identical to the reference's (validity 0xFF fill, values, offsets, characters, 8-byte padding)
+    from tools import dbgen_lineitem as D
+    if D.available():
+        src = sf10["host"].numpy()[: sf10["size"]]
+        pos, k = 0, 0
+        import struct
+        while pos + 8 <= len(src):
+            cont, meta = struct.unpack_from("<Ii", src, pos)
+            if cont != 0xFFFFFFFF or meta == 0:
+                break
+            msg = ipc.read_message(pa.py_buffer(src[pos:]))
+            body = msg.body.size
+            if msg.type == "record batch":
+                bi = w.batch(k)
+                mine = stream[bi.body_offset: bi.body_offset + bi.body_length]
+                ref = src[pos + 8 + meta: pos + 8 + meta + body]
+                assert bi.body_length == body and np.array_equal(mine, ref), f"body of batch {k} differs from the reference's"
+                k += 1
+            pos += 8 + meta + body
+        assert k == 489
     w.close()

@@ -1,10 +1,8 @@
-"""The DuckDB-side binding (integration/duckdb/*.cpp: the B200 variant of the extension's ArrowFileScan) must compile
-against the reference checkout's DuckDB headers.  Syntax check only — DuckDB itself is not built in this repository —
-and only where the reference tree is present (it does not exist on the GPU box)."""
-import glob
+"""The DuckDB-side binding (integration/duckdb/*.cpp) must compile against the reference checkout's DuckDB headers and
+link against the reference's DuckDB (oracle/_ref) — only where the reference tree is present (it does not exist on the
+GPU box, which gets the prebuilt extension with the tree).  tests/test_duckdb_extension.py then loads and runs it."""
 import os
 import shutil
-import subprocess
 
 import pytest
 
@@ -14,10 +12,12 @@ DUCKDB_INCLUDE = "/root/reference/duckdb/src/include"
 
 @pytest.mark.skipif(not os.path.isdir(DUCKDB_INCLUDE) or shutil.which("g++") is None,
                     reason="reference DuckDB headers / g++ not available")
-def test_duckdb_binding_compiles_against_reference_headers():
-    sources = sorted(glob.glob(os.path.join(ROOT, "integration", "duckdb", "*.cpp")))
-    assert sources
-    for src in sources:
-        r = subprocess.run(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-I", os.path.join(ROOT, "include"),
-                            "-I", DUCKDB_INCLUDE, src], capture_output=True, text=True)
-        assert r.returncode == 0, r.stderr[-4000:]
+def test_duckdb_binding_builds_against_the_reference():
+    import sys
+    sys.path.insert(0, ROOT)
+    from integration import build
+    out = build.build(verbose=False)
+    assert out and os.path.exists(out)
+    import subprocess
+    syms = subprocess.run(["nm", "-D", "--defined-only", out], capture_output=True, text=True).stdout
+    assert " nanoarrow_init" in syms and " nanoarrow_version" in syms
