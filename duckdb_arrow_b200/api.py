@@ -117,6 +117,13 @@ class ArrowIPCReader:
         check(lib.b2a_reader_batch_info(self._h, i, C.byref(bi)))
         return bi
 
+    @property
+    def used_footer(self) -> bool:
+        """the message index came from the Arrow file footer rather than from walking the message prefixes"""
+        u = C.c_int32()
+        check(lib.b2a_reader_used_footer(self._h, C.byref(u)))
+        return bool(u.value)
+
     def image(self) -> np.ndarray:
         p, n = C.c_void_p(), C.c_uint64()
         check(lib.b2a_reader_image(self._h, C.byref(p), C.byref(n)))

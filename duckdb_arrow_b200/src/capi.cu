@@ -198,6 +198,14 @@ int b2a_reader_image(b2a_reader *r, const void **data, uint64_t *size) {
 	return B2A_OK;
 }
 
+int b2a_reader_used_footer(b2a_reader *r, int *used) {
+	if (!r || !used) {
+		return Fail(B2A_EINVAL, "null argument");
+	}
+	*used = r->reader.UsedFooter() ? 1 : 0;
+	return B2A_OK;
+}
+
 int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, const char **value, uint32_t *n) {
 	const auto &m = r->reader.BaseSchema().metadata;
 	*n = static_cast<uint32_t>(m.size());
@@ -717,7 +725,23 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		const bool stage = force ? force[0] == '1' : !pinned;
 		s->stage_mode = stage ? 2 : 1;
 		if (stage) {
-			s->stage_plan.Build(p, n_slices);
+			// file-backed images: how the bytes leave the file.  B2A_FILE_IO = mmap | pread | direct (default pread:
+			// one pread per <= 1 MiB piece straight into the pinned ring; "direct" = O_DIRECT where the file system has it)
+			s->stage_io = 0;
+			s->stage_fd = -1;
+			const int fd = s->r->reader.FileDescriptor();
+			if (fd >= 0) {
+				const char *io = getenv("B2A_FILE_IO");
+				const std::string mode = io ? io : "pread";
+				if (mode == "direct" && s->r->reader.DirectFileDescriptor() >= 0) {
+					s->stage_io = 2;
+					s->stage_fd = s->r->reader.DirectFileDescriptor();
+				} else if (mode != "mmap") {
+					s->stage_io = 1;
+					s->stage_fd = fd;
+				}
+			}
+			s->stage_plan.Build(p, n_slices, s->stage_io == 2 ? 4096 : 16);
 			std::vector<ScatterPiece> sp;
 			sp.reserve(s->stage_plan.pieces.size());
 			for (auto &pc : s->stage_plan.pieces) {
@@ -757,7 +781,8 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 			}
 			return static_cast<uint32_t>(n);
 		}();
-		workers.reset(new StageWorkers(s->stage_plan, h_image, hp.h_stage, HostPipe::kRing, n_threads));
+		workers.reset(new StageWorkers(s->stage_plan, h_image, hp.h_stage, HostPipe::kRing, n_threads, s->stage_io,
+		                               s->stage_fd, s->r->reader.ImageSize()));
 		workers->Allow(HostPipe::kRing - 1);
 	}
 	for (uint32_t sl = 0; sl < n_slices; sl++) {
@@ -768,6 +793,9 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		if (staged) {
 			const uint32_t k = sl % HostPipe::kRing;
 			workers->WaitPacked(sl);
+			if (workers->Failed()) {
+				return Fail(B2A_EIO, "Arrow IPC: reading the file into the staging buffers failed");
+			}
 			if (sl >= HostPipe::kRing) { // the device twin is free once slice sl - kRing has been scattered out of it
 				CUDA_OK(cudaStreamWaitEvent(hp.in, hp.ev_c[sl - HostPipe::kRing], 0));
 			}

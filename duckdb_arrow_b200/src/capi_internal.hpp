@@ -39,6 +39,8 @@ struct b2a_scan {
 	uint32_t n_workers = 0;
 	// host path over a pageable image (mmap'ed file): staged uploads, see scanner/host_stage.hpp
 	int stage_mode = 0; // 0 undecided, 1 direct cudaMemcpyAsync per range (pinned image), 2 staged
+	int stage_io = 0;   // staged: 0 memcpy from the image (mmap / caller memory), 1 pread(fd), 2 pread(O_DIRECT fd)
+	int stage_fd = -1;
 	b2a::StagePlan stage_plan;
 	b2a::ScatterPiece *d_stage_pieces = nullptr;
 };

@@ -90,8 +90,21 @@ public:
 		return has_variadic;
 	}
 
+	// the message index came from the Arrow file footer (Block{offset, metaDataLength, bodyLength}) instead of the walk
+	bool UsedFooter() const {
+		return used_footer;
+	}
+	// file descriptor of a file-backed image (-1: caller buffers): staged uploads pread() from it
+	int FileDescriptor() const {
+		return fd;
+	}
+	// the same file opened with O_DIRECT (-1: not a file, or the file system refuses it, e.g. tmpfs); opened on first use
+	int DirectFileDescriptor();
+
 private:
 	void Index();
+	bool IndexFromFooter();
+	bool used_footer = false;
 	bool ReadNextMessage(uint64_t &pos); // false at end of stream
 	void ParseRecordBatch(const uint8_t *tbl_buf, size_t tbl_len, size_t table_pos, uint64_t body_offset,
 	                      uint64_t body_length, RecordBatch &out, bool is_dictionary);
@@ -102,6 +115,8 @@ private:
 	void *mmap_base = nullptr;
 	uint64_t mmap_len = 0;
 	int fd = -1;
+	int fd_direct = -2; // -2: not tried yet
+	std::string path;
 	std::vector<uint8_t> owned;
 
 	Schema schema;

@@ -1,11 +1,14 @@
 #include "scanner/host_stage.hpp"
 
+#include <cerrno>
 #include <cstring>
+#include <unistd.h>
 
 namespace b2a {
 
-void StagePlan::Build(const ScanPlan &plan, uint32_t n_slices_p) {
+void StagePlan::Build(const ScanPlan &plan, uint32_t n_slices_p, uint64_t align_p) {
 	n_slices = n_slices_p;
+	align = align_p;
 	pieces.clear();
 	slice_piece0.assign(1, 0);
 	slice_bytes.clear();
@@ -20,12 +23,16 @@ void StagePlan::Build(const ScanPlan &plan, uint32_t n_slices_p) {
 					continue;
 				}
 				// keep the range's phase inside a 16-byte vector so that the device-side scatter copies aligned vectors
-				const uint64_t dst0 = r.first - plan.image_lo;
-				cursor = ((cursor + 15) & ~uint64_t(15)) + (dst0 & 15);
+				// (image_lo is a multiple of 256, so a staging offset congruent to the FILE offset modulo `align` is also
+				// congruent to the device offset modulo 16)
+				cursor = ((cursor + align - 1) & ~(align - 1)) + (r.first & (align - 1));
 				for (uint64_t o = r.first; o < r.second; o += kPieceBytes) {
 					const uint64_t n = std::min<uint64_t>(kPieceBytes, r.second - o);
 					pieces.push_back(StagePiece {o, cursor, o - plan.image_lo, n});
 					cursor += n;
+				}
+				if (align > 16) { // block reads overshoot the range's end: keep the next range out of that block
+					cursor = (cursor + align - 1) & ~(align - 1);
 				}
 			}
 		}
@@ -36,8 +43,9 @@ void StagePlan::Build(const ScanPlan &plan, uint32_t n_slices_p) {
 }
 
 StageWorkers::StageWorkers(const StagePlan &plan_p, const uint8_t *image_p, uint8_t *const *ring_p, uint32_t ring_size_p,
-                           uint32_t n_threads)
-    : plan(plan_p), image(image_p), ring(ring_p), ring_size(ring_size_p), remaining(plan_p.n_slices) {
+                           uint32_t n_threads, int io_p, int fd_p, uint64_t file_size_p)
+    : plan(plan_p), image(image_p), ring(ring_p), ring_size(ring_size_p), remaining(plan_p.n_slices), io(io_p), fd(fd_p),
+      file_size(file_size_p) {
 	for (uint32_t sl = 0; sl < plan.n_slices; sl++) {
 		remaining[sl].store(plan.slice_piece0[sl + 1] - plan.slice_piece0[sl], std::memory_order_relaxed);
 	}
@@ -81,7 +89,36 @@ void StageWorkers::Run() {
 			std::this_thread::yield();
 		}
 		const StagePiece &pc = plan.pieces[q];
-		std::memcpy(ring[slice % ring_size] + pc.stage, image + pc.src, pc.bytes);
+		uint8_t *dst = ring[slice % ring_size] + pc.stage;
+		if (io == 0 || fd < 0) {
+			std::memcpy(dst, image + pc.src, pc.bytes);
+		} else {
+			// the reference reads through BufferedFileReader, 4 KiB per read() (ipc_file_stream_reader.cpp:80-138); here
+			// every piece (<= 1 MiB) is one pread straight into pinned memory, many in flight
+			uint64_t off = pc.src, left = pc.bytes;
+			if (io == 2) { // O_DIRECT: whole blocks around the piece (the plan keeps dst - (off % 4096) block aligned)
+				const uint64_t a0 = off & ~uint64_t(4095);
+				dst -= off - a0;
+				left = ((pc.src + pc.bytes + 4095) & ~uint64_t(4095)) - a0;
+				off = a0;
+			}
+			while (left > 0) {
+				const ssize_t got = pread(fd, dst, left, static_cast<off_t>(off));
+				if (got < 0 && errno == EINTR) {
+					continue;
+				}
+				if (got <= 0) {
+					if (io == 2 && got == 0 && off >= file_size) {
+						break; // the last block of the file is short
+					}
+					failed.store(true, std::memory_order_release);
+					break;
+				}
+				dst += got;
+				off += static_cast<uint64_t>(got);
+				left -= std::min<uint64_t>(left, static_cast<uint64_t>(got));
+			}
+		}
 		remaining[slice].fetch_sub(1, std::memory_order_release);
 	}
 }

@@ -30,14 +30,24 @@ struct StagePlan {
 	uint64_t max_slice_bytes = 0;
 	uint32_t n_slices = 0;
 
-	void Build(const ScanPlan &plan, uint32_t n_slices);
+	// align = 16: pieces keep their phase inside a 16-byte vector (all the scatter kernel needs).  align = 4096
+	// (O_DIRECT reads): a piece's staging offset is congruent to its FILE offset modulo 4096 and every range is padded
+	// to whole blocks, so that the enclosing aligned block range can be read straight into the pinned buffer.
+	void Build(const ScanPlan &plan, uint32_t n_slices, uint64_t align = 16);
+	uint64_t align = 16;
 };
 
 // Worker threads that pack pieces in order; the caller gates them slice by slice (a staging buffer may be refilled only
 // after its previous content has crossed the bus) and waits for a slice to be complete before sending it.
 class StageWorkers {
 public:
-	StageWorkers(const StagePlan &plan, const uint8_t *image, uint8_t *const *ring, uint32_t ring_size, uint32_t n_threads);
+	// io: 0 = memcpy from the (mmap'ed / caller) image, 1 = pread(fd) into the pinned ring, 2 = pread(fd opened with
+	// O_DIRECT) of the enclosing 4 KiB blocks (plan built with align = 4096)
+	StageWorkers(const StagePlan &plan, const uint8_t *image, uint8_t *const *ring, uint32_t ring_size, uint32_t n_threads,
+	             int io = 0, int fd = -1, uint64_t file_size = 0);
+	bool Failed() const {
+		return failed.load(std::memory_order_acquire);
+	}
 	~StageWorkers();
 	void Allow(uint32_t slice);      // slices <= `slice` may be packed
 	void WaitPacked(uint32_t slice); // blocks until every piece of `slice` is in its staging buffer
@@ -52,6 +62,9 @@ private:
 	std::atomic<int64_t> allowed {-1};
 	std::vector<std::atomic<uint32_t>> remaining;
 	std::vector<std::thread> threads;
+	int io = 0, fd = -1;
+	uint64_t file_size = 0;
+	std::atomic<bool> failed {false};
 };
 
 } // namespace b2a

@@ -203,6 +203,10 @@ int b2a_reader_num_batches(b2a_reader *r, uint64_t *n_batches, uint64_t *n_rows)
 int b2a_reader_batch_info(b2a_reader *r, uint64_t batch, b2a_batch_info *out);
 /* the host bytes of the stream (mmap of the file, or the caller's single buffer) */
 int b2a_reader_image(b2a_reader *r, const void **data, uint64_t *size);
+/* 1 when the message index of an Arrow FILE came from its footer (Block{offset, metaDataLength, bodyLength}) instead of
+ * the sequential walk over the message prefixes the reference does (ipc_file_stream_reader.cpp:96-132); same messages
+ * either way.  B2A_NO_FOOTER=1 in the environment forces the walk. */
+int b2a_reader_used_footer(b2a_reader *r, int *used);
 int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, const char **value, uint32_t *n);
 
 /* ---------------- src/scanner + kernels: record batches -> DuckDB vectors ---------------- */

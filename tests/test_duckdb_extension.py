@@ -199,7 +199,7 @@ def test_multifile_reading_test(db, cuda_device):
 def test_to_arrow_ipc_test(db, cuda_device):
     """test/sql/to_arrow_ipc.test + test/python/test_arrow_ipc_writer.py: the blobs form a stream pyarrow reads"""
     q("SET disabled_optimizers='column_lifetime'")
-    out = rows("SELECT length(ipc), header FROM to_arrow_ipc((SELECT 'Its working!'))")
+    out = rows("SELECT octet_length(ipc), header FROM to_arrow_ipc((SELECT 'Its working!'))")
     assert len(out) == 2 and out[0][1] == "true" and out[1][1] == "false"
     q("create or replace table data as select * from range(0,2000) tbl(col)")
     out = rows("WITH data_union AS (SELECT * FROM data UNION ALL SELECT * FROM data) "

@@ -218,3 +218,37 @@ def test_two_devices_in_one_process(b2a, cuda_device):
     for dev in (0, 1, 0):
         ds = b2a.read_arrow(DBGEN, device=dev)
         compare_scan_with_oracle(ds, batches)
+
+
+@pytest.mark.parametrize("mode", ["mmap", "pread", "direct"])
+def test_file_io_modes_give_the_same_vectors(b2a, cuda_device, mode, tmp_path, monkeypatch):
+    """the staged host path reads a file-backed image by memcpy from the mapping, by pread() into the
+    pinned ring, or by O_DIRECT block reads (falls back to pread where the file system refuses O_DIRECT, e.g. tmpfs)"""
+    import shutil
+    p = str(tmp_path / "li.arrows")  # tmp_path is on a real file system on the box: O_DIRECT gets its chance
+    shutil.copy(DBGEN, p)
+    monkeypatch.setenv("B2A_FILE_IO", mode)
+    batches = list(ipc.open_stream(p))
+    for host_alias in (True, False):
+        ds = b2a.read_arrow(p, host_alias=host_alias)
+        compare_scan_with_oracle(ds, batches)
+
+
+def test_arrow_file_through_the_footer_index(b2a, cuda_device, tmp_path):
+    """.arrow inputs are indexed from the footer (no sequential header walk) and decode to the same vectors"""
+    for rel in ("data/fruit.arrow", "arrow-testing/1.0.0-littleendian/generated_primitive.arrow_file"):
+        path = os.path.join(GOLDEN, rel)
+        ds = b2a.read_arrow(path)
+        assert ds.reader.used_footer
+        f = ipc.open_file(path)
+        compare_scan_with_oracle(ds, [f.get_batch(i) for i in range(f.num_record_batches)])
+    # the reference-written lineitem as a FILE (footer) vs as a stream (walk): identical vectors
+    t = ipc.open_stream(DBGEN).read_all()
+    p = str(tmp_path / "li.arrow")
+    with ipc.new_file(p, t.schema) as w:
+        for b in t.to_batches(max_chunksize=2500):
+            w.write_batch(b)
+    ds = b2a.read_arrow(p)
+    assert ds.reader.used_footer and ds.num_rows == t.num_rows
+    f = ipc.open_file(p)
+    compare_scan_with_oracle(ds, [f.get_batch(i) for i in range(f.num_record_batches)])

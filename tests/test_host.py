@@ -300,3 +300,47 @@ def test_writer_schema_message_string_views(b2a):
     assert sch.field("m").type == pa.map_(pa.string_view(), pa.int64())
     with pytest.raises(B2AError, match="UUID"):
         b2a.ArrowWriter([v("UUID", "id")], 0, device=-1, produce_arrow_string_view=True)
+
+
+def test_arrow_file_footer_index_equals_the_walk(b2a, tmp_path):
+    """an Arrow FILE is indexed from its footer blocks; a stream, or a file whose footer is damaged, by
+    walking the message prefixes like the reference does (ipc_file_stream_reader.cpp:96-132).  Same messages either way."""
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+    for rel in ("data/fruit.arrow", "data/test.arrow", "arrow-testing/1.0.0-littleendian/generated_primitive.arrow_file"):
+        path = os.path.join(GOLDEN, rel)
+        r = b2a.ArrowIPCReader.open_file(path)
+        assert r.used_footer
+        f = ipc.open_file(path)
+        assert r.num_batches == f.num_record_batches
+        assert [r.batch_info(i).rows for i in range(r.num_batches)] == \
+            [f.get_batch(i).num_rows for i in range(f.num_record_batches)]
+        # damage the footer (its length word, then a block offset): the reader falls back to the walk, same index
+        raw = bytearray(open(path, "rb").read())
+        ref = [(r.batch_info(i).meta_offset, r.batch_info(i).body_offset, r.batch_info(i).body_length, r.batch_info(i).rows)
+               for i in range(r.num_batches)]
+        for damage in ("length", "block"):
+            b = bytearray(raw)
+            if damage == "length":
+                b[-10:-6] = (2**31 - 1).to_bytes(4, "little")
+            else:
+                import struct
+                off = struct.pack("<q", ref[0][0])
+                k = bytes(b).rfind(off)  # the first record-batch Block of the footer
+                assert k > ref[-1][1]
+                b[k:k + 8] = struct.pack("<q", ref[0][0] + 8)
+            p = tmp_path / f"damaged_{damage}.arrow"
+            p.write_bytes(bytes(b))
+            r2 = b2a.ArrowIPCReader.open_file(str(p))
+            assert not r2.used_footer
+            got = [(r2.batch_info(i).meta_offset, r2.batch_info(i).body_offset, r2.batch_info(i).body_length,
+                    r2.batch_info(i).rows) for i in range(r2.num_batches)]
+            assert got == ref
+    assert not b2a.ArrowIPCReader.open_file(os.path.join(GOLDEN, "data", "test.arrows")).used_footer
+    # a dictionary-encoded file: the footer's dictionary blocks come first
+    t = pa.table({"d": pa.array(["a", "b", "a", None] * 100).dictionary_encode(), "i": pa.array(range(400))})
+    p = tmp_path / "dict.arrow"
+    with ipc.new_file(str(p), t.schema) as w:
+        w.write_table(t, max_chunksize=150)
+    r = b2a.ArrowIPCReader.open_file(str(p))
+    assert r.used_footer and r.num_rows == 400 and r.num_batches == 3
