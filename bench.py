@@ -541,7 +541,23 @@ def leg_copy(ctx, args, scan, reader, d_out, my_rows, steps):
                         "kernel_ms": enc_ms, "algorithmic_bytes_per_launch": int(alg), "traffic": None},
            "config": {"workload": f"lineitem SF{args.sf:g} COPY TO arrows, row_group_size {BATCH_ROWS}"}}
     w.close()
-    del d_stream, cols
+    del d_stream
+    # the SET produce_arrow_string_view = true variant of the same COPY (ArrowVarcharToStringViewData)
+    try:
+        wv = b2a.ArrowWriter(cols, my_rows, BATCH_ROWS, produce_arrow_string_view=True)
+        wv.measure()
+        d_sv = torch.empty(wv.stream_bytes, dtype=torch.uint8, device=ctx.dev)
+        ms_v, enc_v = _time_steps(ctx, lambda: wv.encode(d_sv), min(steps, 3), 3)
+        wv.finish()
+        out["string_view"] = {"encode_ms": ms_v, "algorithmic_bytes_per_launch": int(wv.algorithmic_bytes),
+                              "achieved_gbs": wv.algorithmic_bytes / (enc_v / 1e3) / 1e9,
+                              "frac": wv.algorithmic_bytes / (enc_v / 1e3) / 1e9 / ctx.peak,
+                              "vs_offsets_writer": ms_v / ms}
+        wv.close()
+        del d_sv
+    except Exception as e:  # noqa: BLE001
+        out["string_view"] = {"error": repr(e)}
+    del cols
     return out
 
 

@@ -154,6 +154,7 @@ def _load() -> C.CDLL:
         "b2a_reader_used_footer": (i32, [vp, P(i32)]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
         "b2a_read_arrow_device": (i32, [vp, vp, u32, vp]),
+        "b2a_read_arrow_host_scratch": (i32, [vp, vp, vp, u32]),
         "b2a_write_arrow_host": (i32, [P(Vector), u32, u64, P(WriteOptions), i32, P(HostStream)]),
         "b2a_host_stream_release": (None, [P(HostStream)]),
         "b2a_pinned_alloc": (i32, [P(vp), u64]),

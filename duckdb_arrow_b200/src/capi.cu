@@ -640,7 +640,8 @@ static int UploadRanges(b2a_scan *s, const ScanPlan::RangeList &ranges, cudaStre
 // h_out_pinned != NULL: vectors come back to the host (b2a_read_arrow_host).  d_out_user != NULL: vectors stay in the
 // caller's device arena for device-side consumers (b2a_read_arrow_device): no D2H, string_t point into the device image,
 // and `user_stream` is made to wait for the last decode instead of the host.
-static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, uint32_t n_slices, void *user_stream) {
+static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, uint32_t n_slices, void *user_stream,
+                             void *h_scratch = nullptr) {
 	NEED_DEVICE(s);
 	const ScanPlan &p = s->plan;
 	HostPipe &hp = g_pipes[s->device];
@@ -696,8 +697,11 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 	l.image_origin = s->d_image - p.image_lo;
 	uint8_t *const arena = to_host ? hp.d_out : static_cast<uint8_t *>(d_out_user);
 	l.out = arena;
-	l.string_ptr_origin = to_host ? reinterpret_cast<uint64_t>(h_image)
-	                              : reinterpret_cast<uint64_t>(s->d_image) - p.image_lo;
+	// string_t pointers: host consumers read the characters where they lie in the HOST image (like the reference's
+	// pointers); bodies that were decompressed exist only in the scratch region, whose host copy is `h_scratch`
+	l.string_ptr_origin = !to_host ? reinterpret_cast<uint64_t>(s->d_image) - p.image_lo
+	                      : (p.compressed && h_scratch) ? reinterpret_cast<uint64_t>(h_scratch) - p.scratch_base
+	                                                    : reinterpret_cast<uint64_t>(h_image);
 	l.d_err = s->d_err;
 	l.d_variadic = s->d_variadic;
 	l.sm_count = s->sm_count;
@@ -725,14 +729,15 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		const bool stage = force ? force[0] == '1' : !pinned;
 		s->stage_mode = stage ? 2 : 1;
 		if (stage) {
-			// file-backed images: how the bytes leave the file.  B2A_FILE_IO = mmap | pread | direct (default pread:
-			// one pread per <= 1 MiB piece straight into the pinned ring; "direct" = O_DIRECT where the file system has it)
+			// file-backed images: how the bytes leave the file.  B2A_FILE_IO = mmap (default: host threads copy out
+			// of the mapping) | pread (one pread per <= 1 MiB piece straight into the pinned ring) | direct (O_DIRECT
+			// block reads where the file system has them — bypasses the page cache, runs at the disk's rate)
 			s->stage_io = 0;
 			s->stage_fd = -1;
 			const int fd = s->r->reader.FileDescriptor();
 			if (fd >= 0) {
 				const char *io = getenv("B2A_FILE_IO");
-				const std::string mode = io ? io : "pread";
+				const std::string mode = io ? io : "mmap"; // measured on the box: profiles/r02_file_io.txt
 				if (mode == "direct" && s->r->reader.DirectFileDescriptor() >= 0) {
 					s->stage_io = 2;
 					s->stage_fd = s->r->reader.DirectFileDescriptor();
@@ -912,6 +917,10 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		CUDA_OK(cudaMemcpyAsync(h_out + d2h_from, hp.d_out + d2h_from, p.out_bytes - d2h_from, cudaMemcpyDeviceToHost,
 		                        hp.out));
 	}
+	if (p.compressed && h_scratch && p.scratch_bytes) {
+		CUDA_OK(cudaMemcpyAsync(h_scratch, s->d_image + (p.scratch_base - p.image_lo), p.scratch_bytes,
+		                        cudaMemcpyDeviceToHost, hp.out));
+	}
 	CUDA_OK(cudaStreamSynchronize(hp.out));
 	if (trace) {
 		CUDA_OK(cudaStreamSynchronize(hp.compute));
@@ -932,6 +941,19 @@ extern "C" int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_s
 		return Fail(B2A_EINVAL, "b2a_read_arrow_host needs a (pinned) host output arena");
 	}
 	return ReadArrowPipeline(s, h_out_pinned, nullptr, n_slices, nullptr);
+	B2A_CATCH
+}
+
+extern "C" int b2a_read_arrow_host_scratch(b2a_scan *s, void *h_out_pinned, void *h_scratch_pinned, uint32_t n_slices) {
+	B2A_TRY
+	if (!h_out_pinned) {
+		return Fail(B2A_EINVAL, "b2a_read_arrow_host_scratch needs a (pinned) host output arena");
+	}
+	if (s->plan.compressed && s->plan.scratch_bytes && !h_scratch_pinned) {
+		return Fail(B2A_EINVAL, "compressed scan: a host buffer of b2a_scan_scratch().scratch_bytes is needed for the "
+		                        "decompressed character buffers");
+	}
+	return ReadArrowPipeline(s, h_out_pinned, nullptr, n_slices, nullptr, h_scratch_pinned);
 	B2A_CATCH
 }
 

@@ -375,7 +375,8 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 	const uint64_t ptr_base = ptr_origin + t.src2;
 	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
 	const uint64_t end = row0 + nrows;
-	for (uint64_t base = row0 + threadIdx.x; base < end; base += kStrUnroll * kThreads) {
+	// (the loop condition is warp-uniform — the first lane's row — because the offsets travel through full-warp shuffles)
+	for (uint64_t base = row0 + threadIdx.x; base - (threadIdx.x & 31) < end; base += kStrUnroll * kThreads) {
 		OFF o0[kStrUnroll], o1[kStrUnroll];
 #pragma unroll
 		for (int u = 0; u < kStrUnroll; u++) {
@@ -383,7 +384,16 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 			o0[u] = o1[u] = 0;
 			if (i < end) {
 				o0[u] = load_off<OFF>(offs, i, swap);
-				o1[u] = load_off<OFF>(offs, i + 1, swap);
+			}
+		}
+		// offsets[i + 1] is the next lane's offsets[i] (rows of a warp are adjacent): one load per row, the end offset
+		// comes through a shuffle; only the warp's last lane and the row before `end` load theirs
+#pragma unroll
+		for (int u = 0; u < kStrUnroll; u++) {
+			const uint64_t i = base + u * kThreads;
+			const OFF up = __shfl_down_sync(0xffffffffu, o0[u], 1);
+			if (i < end) {
+				o1[u] = ((threadIdx.x & 31) == 31 || i + 1 >= end) ? load_off<OFF>(offs, i + 1, swap) : up;
 			}
 		}
 		StrFetch f[kStrUnroll];
@@ -421,91 +431,6 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 				stg_stream16(dst + i, v);
 			}
 		}
-	}
-}
-
-// Short strings (mean length <= 12: flags, codes, modes — planner flag B2A_TASK_F_SHORTSTR).  The row-per-thread loop
-// above spends its time on three dependent small loads per 21..32 bytes of traffic.  Here 1 024 rows at a time: the
-// 1 025 offsets and the rows' character window (contiguous, offsets are monotone) are brought into shared memory with
-// coalesced 8-byte loads (IPC buffers are 8-byte aligned), then every thread builds the string_t of its rows from
-// shared memory and stores them coalesced.  A chunk whose window does not fit (a run of long strings) reads its
-// characters from global memory like op_string.  Same checks, same result bits.
-static constexpr uint32_t kShortRows = 1024;
-static constexpr uint32_t kShortChars = 12 * 1024; // bytes of characters staged per chunk
-struct ShortStrSmem {
-	uint32_t off[kShortRows + 2];
-	uint32_t chr[kShortChars / 4 + 4];
-};
-
-__device__ __forceinline__ void op_string_short(const b2a_task &t, const uint8_t *__restrict__ image,
-                                                uint8_t *__restrict__ out, uint64_t row0, uint64_t nrows,
-                                                uint64_t ptr_origin, uint32_t *err, ShortStrSmem &sm) {
-	const uint8_t *offs = image + t.src;
-	const uint8_t *chars = image + t.src2;
-	const bool masked = t.n_masks != 0;
-	const uint64_t src2_len = t.src2_len;
-	const uint64_t ptr_base = ptr_origin + t.src2;
-	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
-	const uint64_t end = row0 + nrows;
-	for (uint64_t r0 = row0; r0 < end; r0 += kShortRows) {
-		const uint32_t n = static_cast<uint32_t>(end - r0 < kShortRows ? end - r0 : kShortRows);
-		// ---- offsets r0 .. r0 + n (r0 is a multiple of 1 024: the pairs are 8-byte aligned; the pair holding the last
-		// offset may reach into the buffer's zero padding, never past the body)
-		{
-			const uint2 *src = reinterpret_cast<const uint2 *>(offs + r0 * 4);
-			const uint32_t pairs = (n + 2) >> 1;
-			for (uint32_t k = threadIdx.x; k < pairs; k += kThreads) {
-				const uint2 v = ldg_stream8(src + k);
-				sm.off[2 * k] = v.x;
-				sm.off[2 * k + 1] = v.y;
-			}
-		}
-		__syncthreads();
-		const uint32_t w0 = sm.off[0], w1 = sm.off[n];
-		const uint32_t a0 = w0 & ~7u; // window start rounded down to the 8-byte grid of the character buffer
-		const bool window_ok = w1 >= w0 && static_cast<uint64_t>(w1) <= src2_len;
-		const bool staged = window_ok && (w1 - a0) <= kShortChars;
-		if (staged) {
-			const uint2 *src = reinterpret_cast<const uint2 *>(chars + a0);
-			const uint32_t pairs = (w1 - a0 + 7) >> 3;
-			for (uint32_t k = threadIdx.x; k < pairs; k += kThreads) {
-				const uint2 v = ldg_stream8(src + k);
-				sm.chr[2 * k] = v.x;
-				sm.chr[2 * k + 1] = v.y;
-			}
-			// words a thread may touch past the window's last byte (funnel shifts read up to 4 words from an aligned start)
-			if (threadIdx.x < 4) {
-				sm.chr[2 * pairs + threadIdx.x] = 0;
-			}
-			__syncthreads();
-		}
-		for (uint32_t r = threadIdx.x; r < n; r += kThreads) {
-			const uint64_t i = r0 + r;
-			const uint32_t o0 = sm.off[r], o1 = sm.off[r + 1];
-			uint4 v = make_uint4(0, 0, 0, 0);
-			if (o1 < o0 || static_cast<uint64_t>(o1) > src2_len) {
-				raise(err, B2A_DEV_BAD_OFFSETS);
-			} else if (!masked || eff_valid(t, image, i)) {
-				const uint32_t len = o1 - o0;
-				StrFetch f;
-				if (staged && o0 >= w0 && o1 <= w1) {
-					const uint32_t rel = o0 - a0;
-					const uint32_t *wp = sm.chr + (rel >> 2);
-					f.shift = (rel & 3u) * 8u;
-					const uint32_t need = len > 12 ? 4u : len;
-					const uint32_t nwords = (need + (rel & 3u) + 3u) >> 2;
-					f.w0 = nwords > 0 ? wp[0] : 0u;
-					f.w1 = nwords > 1 ? wp[1] : 0u;
-					f.w2 = nwords > 2 ? wp[2] : 0u;
-					f.w3 = nwords > 3 ? wp[3] : 0u;
-				} else {
-					f = fetch_chars(chars + o0, len);
-				}
-				v = assemble_string_t(f, len, ptr_base + o0);
-			}
-			stg_stream16(dst + i, v);
-		}
-		__syncthreads(); // the next chunk overwrites the staging area
 	}
 }
 
@@ -1189,7 +1114,6 @@ __global__ void __launch_bounds__(kThreads)
                       const uint8_t *__restrict__ image, uint8_t *__restrict__ out, uint64_t ptr_origin,
                       uint32_t *err, const uint64_t *__restrict__ variadic) {
 	__shared__ b2a_task s_task[2];
-	__shared__ ShortStrSmem s_short;
 	uint32_t tile = tile_begin + blockIdx.x;
 	if (tile >= tile_end) {
 		return;
@@ -1235,11 +1159,7 @@ __global__ void __launch_bounds__(kThreads)
 			op_bool(t, image, out, row0, nrows);
 			break;
 		case B2A_OP_STRING32:
-			if (t.flags & B2A_TASK_F_SHORTSTR) {
-				op_string_short(t, image, out, row0, nrows, ptr_origin, err, s_short);
-			} else {
-				op_string<uint32_t>(t, image, out, row0, nrows, ptr_origin, err);
-			}
+			op_string<uint32_t>(t, image, out, row0, nrows, ptr_origin, err);
 			break;
 		case B2A_OP_STRING64:
 			op_string<uint64_t>(t, image, out, row0, nrows, ptr_origin, err);

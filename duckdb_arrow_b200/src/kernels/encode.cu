@@ -868,6 +868,348 @@ __device__ __forceinline__ void enc_string(const b2a_enc_task &t, uint8_t *__res
 	}
 }
 
+// ------------------------------------------------------------------------------------------------
+// mbarrier + 1-D bulk async copy (TMA unit, SASS UBLKCP): global -> shared without passing through registers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t enc_smem_u32(const void *p) {
+	return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void enc_mbar_init(uint64_t *bar, uint32_t count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(enc_smem_u32(bar)), "r"(count) : "memory");
+	asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void enc_bulk_load(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+	// earlier generic-proxy accesses of the staging area (the previous tile) are ordered before the async-proxy writes
+	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(enc_smem_u32(bar)), "r"(bytes) : "memory");
+	asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+	                 enc_smem_u32(dst_smem)),
+	             "l"(src_gmem), "r"(bytes), "r"(enc_smem_u32(bar))
+	             : "memory");
+}
+__device__ __forceinline__ void enc_mbar_wait(uint64_t *bar, uint32_t parity) {
+	asm volatile("{\n"
+	             ".reg .pred P1;\n"
+	             "ENC_WAIT:\n"
+	             "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+	             "@P1 bra ENC_DONE;\n"
+	             "bra ENC_WAIT;\n"
+	             "ENC_DONE:\n"
+	             "}" ::"r"(enc_smem_u32(bar)),
+	             "r"(parity)
+	             : "memory");
+}
+
+// 16 bytes starting at byte offset `sb` of the staging area (any alignment): two aligned 16-byte shared loads and a
+// funnel shift; `sb & 15` is the same for every thread of a store loop, so the switch is a uniform branch
+__device__ __forceinline__ uint4 stage_load16(const uint8_t *stage, uint32_t sb) {
+	const uint4 a = *reinterpret_cast<const uint4 *>(stage + (sb & ~15u));
+	if ((sb & 15u) == 0) {
+		return a;
+	}
+	const uint4 b = *reinterpret_cast<const uint4 *>(stage + (sb & ~15u) + 16);
+	const uint32_t r = (sb & 3u) * 8u;
+	switch ((sb & 15u) >> 2) {
+	case 0:
+		return make_uint4(__funnelshift_r(a.x, a.y, r), __funnelshift_r(a.y, a.z, r), __funnelshift_r(a.z, a.w, r),
+		                  __funnelshift_r(a.w, b.x, r));
+	case 1:
+		return make_uint4(__funnelshift_r(a.y, a.z, r), __funnelshift_r(a.z, a.w, r), __funnelshift_r(a.w, b.x, r),
+		                  __funnelshift_r(b.x, b.y, r));
+	case 2:
+		return make_uint4(__funnelshift_r(a.z, a.w, r), __funnelshift_r(a.w, b.x, r), __funnelshift_r(b.x, b.y, r),
+		                  __funnelshift_r(b.y, b.z, r));
+	default:
+		return make_uint4(__funnelshift_r(a.w, b.x, r), __funnelshift_r(b.x, b.y, r), __funnelshift_r(b.y, b.z, r),
+		                  __funnelshift_r(b.z, b.w, r));
+	}
+}
+
+// Exclusive scan of the tile's 1 024 lengths in ROW order for the coalesced row mapping (row = u * 256 + thread): four
+// warp scans, then the 32 warp totals are scanned by every warp for itself — one barrier.
+__device__ __forceinline__ void enc_tile_scan(const uint32_t (&len)[kRowsPerThread], uint64_t (&rel)[kRowsPerThread],
+                                              uint64_t &window, uint64_t *s_wsum) {
+	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		uint64_t inc = len[u];
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+			if (lane >= static_cast<uint32_t>(o)) {
+				inc += n;
+			}
+		}
+		rel[u] = inc - len[u];
+		if (lane == 31) {
+			s_wsum[u * (kThreads / 32) + warp] = inc;
+		}
+	}
+	__syncthreads();
+	uint64_t inc = s_wsum[lane]; // kRowsPerThread * kThreads / 32 == 32 entries
+	const uint64_t own = inc;
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1) {
+		const uint64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+		if (lane >= static_cast<uint32_t>(o)) {
+			inc += n;
+		}
+	}
+	window = __shfl_sync(0xffffffffu, inc, 31);
+	const uint64_t exc = inc - own;
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		rel[u] += __shfl_sync(0xffffffffu, exc, u * (kThreads / 32) + static_cast<int>(warp));
+	}
+}
+
+// Staging area (window byte 0 at byte `ph`) -> stream: head bytes up to the first 16-byte boundary of the DESTINATION,
+// aligned 16-byte vectors (shifted from the staging phase to the destination's), tail bytes
+__device__ __forceinline__ void enc_stage_flush(const uint8_t *stage, uint32_t ph, uint8_t *gdst, uint32_t total) {
+	const uint32_t pd = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(gdst) & 15);
+	uint32_t head = (16u - pd) & 15u;
+	if (head > total) {
+		head = total;
+	}
+	if (threadIdx.x < head) {
+		gdst[threadIdx.x] = stage[ph + threadIdx.x];
+	}
+	const uint32_t nvec = (total - head) >> 4;
+	uint4 *gvec = reinterpret_cast<uint4 *>(gdst + head);
+	const uint32_t sb0 = ph + head;
+	for (uint32_t v = threadIdx.x; v < nvec; v += kThreads) {
+		st16(gvec + v, stage_load16(stage, sb0 + 16u * v));
+	}
+	for (uint32_t b = head + (nvec << 4) + threadIdx.x; b < total; b += kThreads) {
+		gdst[b] = stage[ph + b];
+	}
+}
+
+// K12, second generation (VARCHAR / BLOB with int32 or int64 offsets; UUID keeps enc_string): string_t -> offsets +
+// characters (ArrowVarcharData::AppendTemplated, varchar_data.hpp:53-111).  Tile = 1 024 rows.
+//  * the 16 KiB of string_t are read fully coalesced (row = u * 256 + thread), the tile-wide exclusive scan of the lengths
+//    is four warp scans + one 32-entry scan every warp repeats for itself (ONE barrier), offsets leave as coalesced 4 / 8
+//    byte stores;
+//  * contiguous-heap tiles (vectors that come out of a scan: pointer - window offset is the same address for every
+//    non-inlined string): the span first .. last non-inlined string is ONE bulk async copy (cp.async.bulk -> UBLKCP) of
+//    the enclosing 16-byte blocks into the staging area, issued by one thread, no registers in between; inlined strings
+//    are patched in from the string_t registers afterwards.  The staging area then has the SOURCE's phase inside a
+//    16-byte vector; the store loop shifts to the destination's phase (stage_load16) and writes aligned 16-byte vectors;
+//  * any other tile assembles its characters string by string (put_string_words) at the destination's phase.
+// Page safety of the bulk copy as in enc_string: a tile qualifies only if every group of 128 consecutive rows holds a
+// non-inlined string, so any run of inlined strings inside the span is shorter than 256 x 12 B < 4 KiB.
+template <typename OFF>
+__device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                            uint8_t *stage, uint32_t *err, uint64_t *bar, uint32_t &parity) {
+	__shared__ uint64_t s_wsum[32];
+	__shared__ unsigned long long s_base, s_lo, s_hi;
+	__shared__ uint32_t s_grp[8];
+	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	const uint32_t lane = threadIdx.x & 31;
+	uint4 e[kRowsPerThread];
+	uint32_t len[kRowsPerThread];
+	uint64_t rel[kRowsPerThread];
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+		len[u] = 0;
+		e[u] = make_uint4(0, 0, 0, 0);
+		if (i < t.rows) {
+			bool valid;
+			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid));
+		}
+	}
+	if (threadIdx.x < 8) {
+		s_grp[threadIdx.x] = 0;
+	}
+	if (threadIdx.x == 0) {
+		s_lo = ~0ull;
+		s_hi = 0;
+		s_base = 0;
+	}
+	uint64_t window;
+	enc_tile_scan(len, rel, window, s_wsum);
+	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+	// ---- offsets: out[i] = running sum before row i, out[rows] = total
+	{
+		OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+			if (i < t.rows) {
+				const uint64_t v = tile_base + rel[u];
+				if (sizeof(OFF) == 4 && v + len[u] > 0x7FFFFFFFull) {
+					enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
+				}
+				offs[i] = static_cast<OFF>(v);
+				if (i + 1 == t.rows) {
+					offs[i + 1] = static_cast<OFF>(v + len[u]);
+				}
+			}
+		}
+		if (t.rows == 0 && k == 0 && threadIdx.x == 0) {
+			offs[0] = 0;
+		}
+	}
+	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the character buffer up to 8 bytes
+		const uint64_t total = tile_base + window;
+		zero_range(stream, t.dst2 + total, t.dst2 + align8(total));
+	}
+	if (window == 0) {
+		return;
+	}
+	// ---- characters
+	uint8_t *gdst = stream + t.dst2 + tile_base; // window start in the stream
+	const uint32_t pd = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(gdst) & 15);
+	if (window + 48 > kStageBytes) { // (a tile of very long strings) straight to global memory, string by string
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			put_string(gdst + rel[u], e[u], len[u]);
+		}
+		return;
+	}
+	bool fast = false;
+	if (window >= 8ull * B2A_ENC_STR_TILE) { // (tiles that average under 8 B per row — flags, codes — rarely qualify)
+		unsigned long long my_base = 0, my_lo = ~0ull, my_hi = 0;
+		bool has_long = false, bad = false;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			if (len[u] > 12) {
+				const unsigned long long b = ((static_cast<unsigned long long>(e[u].w) << 32) | e[u].z) - rel[u];
+				bad = bad || (has_long && b != my_base);
+				my_base = b;
+				has_long = true;
+				my_lo = my_lo < rel[u] ? my_lo : rel[u];
+				my_hi = my_hi > rel[u] + len[u] ? my_hi : rel[u] + len[u];
+				s_grp[u * 2 + (threadIdx.x >> 7)] = 1; // (same value from every writer)
+			}
+		}
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) {
+			const unsigned long long l2 = __shfl_xor_sync(0xffffffffu, my_lo, o), h2 = __shfl_xor_sync(0xffffffffu, my_hi, o);
+			my_lo = my_lo < l2 ? my_lo : l2;
+			my_hi = my_hi > h2 ? my_hi : h2;
+		}
+		const uint32_t longs = __ballot_sync(0xffffffffu, has_long);
+		if (longs != 0 && lane == static_cast<uint32_t>(__ffs(longs) - 1)) {
+			atomicMin(&s_lo, my_lo);
+			atomicMax(&s_hi, my_hi);
+			s_base = my_base; // any candidate: every thread checks its own against it below
+		}
+		__syncthreads();
+		bad = bad || (has_long && my_base != s_base);
+		if (threadIdx.x < 8) { // every 128-row group that has rows at all must hold a non-inlined string
+			const uint64_t g0 = row0 + (threadIdx.x >> 1) * static_cast<uint64_t>(kThreads) + (threadIdx.x & 1) * 128u;
+			bad = bad || (g0 < t.rows && s_grp[threadIdx.x] == 0);
+		}
+		fast = !__syncthreads_or(bad);
+	}
+	uint32_t ph; // phase of window byte 0 inside the staging area
+	if (fast) {
+		const unsigned long long S = s_base;
+		const uint64_t lo = s_lo, hi = s_hi;
+		ph = static_cast<uint32_t>(S & 15ull);
+		if (threadIdx.x == 0) {
+			const unsigned long long a0 = (S + lo) & ~15ull, a1 = (S + hi + 15ull) & ~15ull;
+			enc_bulk_load(stage + (a0 - (S & ~15ull)), reinterpret_cast<const void *>(a0), static_cast<uint32_t>(a1 - a0), bar);
+		}
+		enc_mbar_wait(bar, parity);
+		parity ^= 1u;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			if (len[u] <= 12) {
+				put_string_words(stage + ph + rel[u], e[u], len[u]);
+			}
+		}
+	} else {
+		ph = pd;
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			put_string_words(stage + ph + rel[u], e[u], len[u]);
+		}
+	}
+	__syncthreads();
+	enc_stage_flush(stage, ph, gdst, static_cast<uint32_t>(window));
+}
+
+// ArrowVarcharToStringViewData::Append (varchar_data.hpp:136-187), second generation: same tile, coalesced row mapping and
+// scan as enc_string2; the 16-byte views leave as coalesced stores, and the tile's slice of the ONE data buffer (the
+// strings longer than 12 bytes, end to end) is assembled in the staging area at the destination's phase — every thread
+// fetches its own long strings eight words at a time (put_string_words) — and flushed with aligned 16-byte stores.
+__device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                                 uint8_t *stage, uint32_t *err) {
+	__shared__ uint64_t s_wsum[32];
+	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	uint4 e[kRowsPerThread];
+	uint32_t len[kRowsPerThread]; // bytes that go to the data buffer (0 for NULL / inlined rows)
+	bool valid[kRowsPerThread];
+	uint64_t rel[kRowsPerThread];
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+		len[u] = 0;
+		valid[u] = false;
+		e[u] = make_uint4(0, 0, 0, 0);
+		if (i < t.rows) {
+			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid[u]));
+		}
+	}
+	uint64_t window;
+	enc_tile_scan(len, rel, window, s_wsum);
+	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+		if (i >= t.rows) {
+			continue;
+		}
+		uint4 v = make_uint4(0, 0, 0, 0);
+		if (valid[u] && len[u] == 0) { // inlined: string_t and the view share the layout; bytes past the length are zeroed
+			const uint32_t n = e[u].x;
+			auto keep = [n](uint32_t w, uint32_t first) {
+				return n >= first + 4 ? w : n <= first ? 0u : (w & ((1u << (8 * (n - first))) - 1u));
+			};
+			v = make_uint4(n, keep(e[u].y, 0), keep(e[u].z, 4), keep(e[u].w, 8));
+		} else if (valid[u]) {
+			const uint64_t run = tile_base + rel[u];
+			if (run > 0x7FFFFFFFull) { // the view's offset is an int32 (UnsafeNumericCast<int32_t>(append_data.offset))
+				enc_raise(err, B2A_DEV_ENC_OFFSET_I32);
+			}
+			v = make_uint4(e[u].x, e[u].y, 0u, static_cast<uint32_t>(run));
+		}
+		// buffers start on 8-byte boundaries of the stream (not 16): two 8-byte stores
+		uint2 *o = reinterpret_cast<uint2 *>(stream + t.dst) + 2 * i;
+		st8(o, make_uint2(v.x, v.y));
+		st8(o + 1, make_uint2(v.z, v.w));
+	}
+	if (row0 + B2A_ENC_STR_TILE >= t.rows) { // last tile: zero padding of the data buffer up to 8 bytes
+		const uint64_t total = tile_base + window;
+		zero_range(stream, t.dst2 + total, t.dst2 + align8(total));
+	}
+	if (window == 0) {
+		return;
+	}
+	uint8_t *gdst = stream + t.dst2 + tile_base;
+	if (window + 48 > kStageBytes) {
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			if (len[u]) {
+				put_string(gdst + rel[u], e[u], len[u]);
+			}
+		}
+		return;
+	}
+	const uint32_t pd = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(gdst) & 15);
+#pragma unroll
+	for (int u = 0; u < kRowsPerThread; u++) {
+		if (len[u]) {
+			put_string_words(stage + pd + rel[u], e[u], len[u]);
+		}
+	}
+	__syncthreads();
+	enc_stage_flush(stage, pd, gdst, static_cast<uint32_t>(window));
+}
+
 // ArrowListData<BUFTYPE>::AppendOffsets: offsets only (children are appended through the selection built by
 // b2a_enc_expand_kernel)
 // VIEW: ArrowListViewData<BUFTYPE>::AppendListMetadata — offsets[i] = the running offset BEFORE row i, sizes[i] = its
@@ -1051,10 +1393,15 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
     b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
                       uint8_t *__restrict__ stream, uint32_t *err) {
 	__shared__ b2a_enc_task s_task[2];
-	__shared__ __align__(16) uint8_t stage[kStageBytes];
+	__shared__ __align__(128) uint8_t stage[kStageBytes + 64];
+	__shared__ __align__(8) uint64_t s_bar; // completion of the bulk copies of enc_string2
+	uint32_t bulk_parity = 0;
 	uint32_t tile = blockIdx.x;
 	if (tile >= n_tiles) {
 		return;
+	}
+	if (threadIdx.x == 0) {
+		enc_mbar_init(&s_bar, 1);
 	}
 	const uint32_t stride = gridDim.x;
 	const bool loader = threadIdx.x < kEncTaskVecs;
@@ -1100,10 +1447,10 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 			enc_bool(t, stream, row0, nrows);
 			break;
 		case B2A_ENC_STRING32:
-			enc_string<int32_t>(t, stream, k, stage, err);
+			enc_string2<int32_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
 			break;
 		case B2A_ENC_STRING64:
-			enc_string<int64_t>(t, stream, k, stage, err);
+			enc_string2<int64_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
 			break;
 		case B2A_ENC_LIST32:
 			enc_list<int32_t>(t, stream, k, err);
@@ -1126,7 +1473,7 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 				} else if (t.op == B2A_ENC_LISTVIEW64) {
 					enc_list<int64_t, true>(t, stream, k, err);
 				} else if (t.op == B2A_ENC_STRINGVIEW) {
-					enc_string_view(t, stream, k, err);
+					enc_string_view2(t, stream, k, stage, err);
 				}
 			}
 			break;

@@ -9,8 +9,6 @@
 #define B2A_TASK_F_SIGNED 0x2u     /* DICT_INDEX / DECIMAL: source is signed */
 #define B2A_TASK_F_ADD_NULL 0x4u   /* VALIDITY of a dictionary: extra NULL slot at index `rows` */
 #define B2A_TASK_F_BLOB 0x8u
-#define B2A_TASK_F_SHORTSTR 0x20u  /* STRING32, little-endian, mean length <= 12: offsets + the tile's character window
-                                      are staged through shared memory (op_string_short) */
 #define B2A_TASK_F_PHASE2 0x10u    /* reads vectors another task decoded (REE gather, UNION): runs in the second launch */
 
 /* device error codes (atomicMax into the scan's error word) */

@@ -478,14 +478,6 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		t.dst = slot.data_off = Alloc(L * 16);
 		slot.chars_off = bufs[2].offset;
 		slot.chars_len = bufs[2].length;
-		// short strings (flags, codes, modes): three dependent small loads per row are the cost, not the bytes — the
-		// kernel stages offsets and characters of 1 024 rows at a time through shared memory instead
-		if (f.op == B2A_OP_STRING32 && !(t.flags & B2A_TASK_F_BSWAP) && L > 0 && t.src2_len <= 12 * L) {
-			static const bool off = getenv("B2A_NO_SHORTSTR") != nullptr;
-			if (!off) {
-				t.flags |= B2A_TASK_F_SHORTSTR;
-			}
-		}
 		if (L > 0) {
 			Touch(t.src, (L + 1) * ow);
 			Touch(t.src2, t.src2_len);

@@ -259,6 +259,10 @@ int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_
 
 /* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
 int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
+/* The same for streams with compressed bodies (BodyCompression ZSTD / LZ4_FRAME): the decompressed buffers exist only
+ * on the device, so the character buffers string_t point into come back as well — into `h_scratch_pinned`
+ * (b2a_scan_scratch().scratch_bytes) — and the pointers refer to that copy.  Uncompressed scans ignore the argument. */
+int b2a_read_arrow_host_scratch(b2a_scan *s, void *h_out_pinned, void *h_scratch_pinned, uint32_t n_slices);
 /* Host buffers in, DEVICE vectors out, for consumers that run on the GPU (b2a_scan_filter, b2a_scan_sum_product): only
  * the buffers of the PROJECTED columns cross PCIe (the reference's projection pushdown, src/scanner/read_arrow.cpp:44-50,
  * base_stream_reader.cpp:146-212), slice by slice behind the decode launches; nothing is copied back.  Vectors land in

@@ -247,13 +247,20 @@ unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
 	s->batch_hi = hi;
 	// DirectConversion columns alias the stream image (zero copy, as in the reference); everything that needs
 	// conversion goes host -> device -> kernels -> host inside b2a_read_arrow_host
-	int rc = b2a_scan_create_ex(reader, device, lo, hi, B2A_SCAN_HOST_ALIAS, &s->scan);
+	// (compressed bodies have nothing to alias: every buffer is decompressed on the device, base_stream_reader.cpp:11-50)
+	b2a_batch_info first;
+	bool compressed = lo < hi && b2a_reader_batch_info(reader, lo, &first) == B2A_OK && first.compressed != 0;
+	int rc = b2a_scan_create_ex(reader, device, lo, hi, compressed ? 0 : B2A_SCAN_HOST_ALIAS, &s->scan);
 	if (rc == B2A_OK) {
 		uint64_t image_lo, image_bytes, out_bytes, algorithmic, n_tasks, n_tiles;
 		b2a_scan_sizes(s->scan, &image_lo, &image_bytes, &out_bytes, &algorithmic, &n_tasks, &n_tiles);
+		uint64_t scratch_offset = 0, scratch_bytes = 0, n_jobs = 0;
+		b2a_scan_scratch(s->scan, &scratch_offset, &scratch_bytes, &n_jobs);
 		try {
-			s->slab = B2ASlab::Acquire(NumericCast<idx_t>(out_bytes));
-			rc = b2a_read_arrow_host(s->scan, s->slab->data, 0);
+			// vectors first, the host copy of the decompressed character buffers behind them in the same arena
+			const idx_t out_padded = (NumericCast<idx_t>(out_bytes) + 255) & ~idx_t(255);
+			s->slab = B2ASlab::Acquire(out_padded + NumericCast<idx_t>(scratch_bytes));
+			rc = b2a_read_arrow_host_scratch(s->scan, s->slab->data, scratch_bytes ? s->slab->data + out_padded : nullptr, 0);
 		} catch (std::exception &e) {
 			s->status = B2A_EOOM;
 			s->error = e.what();
