@@ -375,8 +375,7 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 	const uint64_t ptr_base = ptr_origin + t.src2;
 	uint4 *dst = reinterpret_cast<uint4 *>(out + t.dst);
 	const uint64_t end = row0 + nrows;
-	// (the loop condition is warp-uniform — the first lane's row — because the offsets travel through full-warp shuffles)
-	for (uint64_t base = row0 + threadIdx.x; base - (threadIdx.x & 31) < end; base += kStrUnroll * kThreads) {
+	for (uint64_t base = row0 + threadIdx.x; base < end; base += kStrUnroll * kThreads) {
 		OFF o0[kStrUnroll], o1[kStrUnroll];
 #pragma unroll
 		for (int u = 0; u < kStrUnroll; u++) {
@@ -384,16 +383,7 @@ __device__ __forceinline__ void op_string(const b2a_task &t, const uint8_t *__re
 			o0[u] = o1[u] = 0;
 			if (i < end) {
 				o0[u] = load_off<OFF>(offs, i, swap);
-			}
-		}
-		// offsets[i + 1] is the next lane's offsets[i] (rows of a warp are adjacent): one load per row, the end offset
-		// comes through a shuffle; only the warp's last lane and the row before `end` load theirs
-#pragma unroll
-		for (int u = 0; u < kStrUnroll; u++) {
-			const uint64_t i = base + u * kThreads;
-			const OFF up = __shfl_down_sync(0xffffffffu, o0[u], 1);
-			if (i < end) {
-				o1[u] = ((threadIdx.x & 31) == 31 || i + 1 >= end) ? load_off<OFF>(offs, i + 1, swap) : up;
+				o1[u] = load_off<OFF>(offs, i + 1, swap);
 			}
 		}
 		StrFetch f[kStrUnroll];

@@ -62,6 +62,8 @@ def lib() -> C.CDLL:
         _lib.ref_file_read.argtypes = [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_char_p, C.c_int]
         _lib.ref_file_close.argtypes = [C.c_void_p]
         _lib.ref_load_extension.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int]
+        _lib.ref_scan_arrow_ipc_view.argtypes = [C.c_char_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.c_uint32,
+                                                 C.c_char_p, C.c_int]
         err = C.create_string_buffer(512)
         if _lib.ref_open(err, 512) != 0:
             raise RefError(4, err.value.decode())
@@ -216,3 +218,14 @@ def load_extension(path: str, name: str = "nanoarrow") -> None:
     if lib().ref_load_extension(path.encode(), name.encode(), err, 1024) != 0:
         raise RefError(4, err.value.decode())
     _loaded_extensions.add(path)
+
+
+def scan_arrow_ipc_view(name: str, buffers: list[tuple[int, int]]) -> None:
+    """CREATE VIEW name AS FROM scan_arrow_ipc([{ptr, size}, ...]) — the POINTER values are built through the API, as
+    DuckDB's clients do."""
+    n = len(buffers)
+    ptrs = (C.c_uint64 * n)(*[b[0] for b in buffers])
+    sizes = (C.c_uint64 * n)(*[b[1] for b in buffers])
+    err = C.create_string_buffer(1024)
+    if lib().ref_scan_arrow_ipc_view(name.encode(), ptrs, sizes, n, err, 1024) != 0:
+        raise RefError(4, err.value.decode())

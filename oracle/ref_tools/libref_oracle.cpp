@@ -764,6 +764,30 @@ int ref_load_extension(const char *path, const char *name, char *err, int errlen
 	}
 }
 
+// scan_arrow_ipc takes LIST(STRUCT(ptr POINTER, size UBIGINT)): POINTER values cannot be written in SQL, clients build
+// them through the API (duckdb/tools/pythonpkg/src/python_replacement_scan.cpp:24-55).  Creates view `name` over
+// scan_arrow_ipc(buffers) on the session's connection.
+int ref_scan_arrow_ipc_view(const char *name, const uint64_t *ptrs, const uint64_t *sizes, uint32_t n, char *err,
+                            int errlen) {
+	try {
+		auto &s = session();
+		vector<Value> entries;
+		for (uint32_t i = 0; i < n; i++) {
+			child_list_t<Value> fields;
+			fields.emplace_back("ptr", Value::POINTER(ptrs[i]));
+			fields.emplace_back("size", Value::UBIGINT(sizes[i]));
+			entries.push_back(Value::STRUCT(std::move(fields)));
+		}
+		child_list_t<LogicalType> st {{"ptr", LogicalType::POINTER}, {"size", LogicalType::UBIGINT}};
+		vector<Value> params;
+		params.push_back(Value::LIST(LogicalType::STRUCT(st), std::move(entries)));
+		s.con->TableFunction("scan_arrow_ipc", params)->CreateView(name, true, true);
+		return 0;
+	} catch (std::exception &e) {
+		return fail(err, errlen, e);
+	}
+}
+
 const char *ref_source_id() {
 	return DuckDB::SourceID();
 }

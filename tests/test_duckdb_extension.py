@@ -263,8 +263,8 @@ def test_scan_arrow_ipc_over_caller_buffers(db, cuda_device):
     raw = open(os.path.join(DATA, "test.arrows"), "rb").read()
     a, b = raw[:40_000 // 8 * 8], raw[40_000 // 8 * 8:]
     ka, kb = ctypes.create_string_buffer(a, len(a)), ctypes.create_string_buffer(b, len(b))
-    arg = (f"[{{'ptr': {ctypes.addressof(ka)}::UBIGINT::POINTER, 'size': {len(a)}::UBIGINT}}, "
-           f"{{'ptr': {ctypes.addressof(kb)}::UBIGINT::POINTER, 'size': {len(b)}::UBIGINT}}]")
-    assert rows(f"SELECT count(*), count(message) FROM scan_arrow_ipc({arg})") == [("15487", "15487")]
-    assert rows(f"SELECT message FROM scan_arrow_ipc({arg}) WHERE \"commit\" = "
-                "'fa5f0299f046c46e1b2f671e5e3b4f1956522711'") == [("ARROW-1: Initial Arrow Code Commit",)]
+    R.scan_arrow_ipc_view("ipc_view", [(ctypes.addressof(ka), len(a)), (ctypes.addressof(kb), len(b))])
+    assert rows("SELECT count(*), count(message) FROM ipc_view") == [("15487", "15487")]
+    assert rows("SELECT message FROM ipc_view WHERE \"commit\" = 'fa5f0299f046c46e1b2f671e5e3b4f1956522711'") == \
+        [("ARROW-1: Initial Arrow Code Commit",)]
+    assert rows("SELECT count(*) FROM ipc_view WHERE dayname(time::TIMESTAMP) = 'Wednesday'") == [("2927",)]
