@@ -926,16 +926,19 @@ __device__ __forceinline__ uint4 stage_load16(const uint8_t *stage, uint32_t sb)
 }
 
 // Exclusive scan of the tile's 1 024 lengths in ROW order for the coalesced row mapping (row = u * 256 + thread): four
-// warp scans, then the 32 warp totals are scanned by every warp for itself — one barrier.
-__device__ __forceinline__ void enc_tile_scan(const uint32_t (&len)[kRowsPerThread], uint64_t (&rel)[kRowsPerThread],
-                                              uint64_t &window, uint64_t *s_wsum) {
+// warp scans, then the 32 warp totals are scanned by every warp for itself — one barrier.  32-bit sums: a tile whose
+// strings could overflow them (one string of 4 MiB or more) reports `big` and is handled by the 64-bit generic path.
+__device__ __forceinline__ void enc_tile_scan(const uint32_t (&len)[kRowsPerThread], uint32_t (&rel)[kRowsPerThread],
+                                              uint32_t &window, bool &big, uint32_t *s_wsum, uint32_t *s_big) {
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	bool mine_big = false;
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
-		uint64_t inc = len[u];
+		mine_big = mine_big || len[u] >= (1u << 22);
+		uint32_t inc = len[u];
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
-			const uint64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+			const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
 			if (lane >= static_cast<uint32_t>(o)) {
 				inc += n;
 			}
@@ -945,21 +948,35 @@ __device__ __forceinline__ void enc_tile_scan(const uint32_t (&len)[kRowsPerThre
 			s_wsum[u * (kThreads / 32) + warp] = inc;
 		}
 	}
+	if (mine_big) {
+		*s_big = 1;
+	}
 	__syncthreads();
-	uint64_t inc = s_wsum[lane]; // kRowsPerThread * kThreads / 32 == 32 entries
-	const uint64_t own = inc;
+	big = *s_big != 0;
+	uint32_t inc = s_wsum[lane]; // kRowsPerThread * kThreads / 32 == 32 entries
+	const uint32_t own = inc;
 #pragma unroll
 	for (int o = 1; o < 32; o <<= 1) {
-		const uint64_t n = __shfl_up_sync(0xffffffffu, inc, o);
+		const uint32_t n = __shfl_up_sync(0xffffffffu, inc, o);
 		if (lane >= static_cast<uint32_t>(o)) {
 			inc += n;
 		}
 	}
 	window = __shfl_sync(0xffffffffu, inc, 31);
-	const uint64_t exc = inc - own;
+	const uint32_t exc = inc - own;
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		rel[u] += __shfl_sync(0xffffffffu, exc, u * (kThreads / 32) + static_cast<int>(warp));
+	}
+}
+
+// an inlined string (<= 12 bytes, in the string_t registers) into the staging area; one-character strings (flags, codes)
+// are a single byte store
+__device__ __forceinline__ void put_inlined(uint8_t *dst, const uint4 &e, uint32_t len) {
+	if (len == 1) {
+		*dst = static_cast<uint8_t>(e.y);
+	} else {
+		put_string_words(dst, e, len);
 	}
 }
 
@@ -1001,14 +1018,16 @@ __device__ __forceinline__ void enc_stage_flush(const uint8_t *stage, uint32_t p
 template <typename OFF>
 __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                             uint8_t *stage, uint32_t *err, uint64_t *bar, uint32_t &parity) {
-	__shared__ uint64_t s_wsum[32];
-	__shared__ unsigned long long s_base, s_lo, s_hi;
+	__shared__ uint32_t s_wsum[32];
+	__shared__ unsigned long long s_base;
+	__shared__ uint32_t s_lo, s_hi, s_big;
 	__shared__ uint32_t s_grp[8];
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
 	const uint32_t lane = threadIdx.x & 31;
+	const uint64_t tile_base = __ldg(reinterpret_cast<const unsigned long long *>(t.scratch) + k); // (needed late: issued early)
 	uint4 e[kRowsPerThread];
 	uint32_t len[kRowsPerThread];
-	uint64_t rel[kRowsPerThread];
+	uint32_t rel[kRowsPerThread];
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
@@ -1023,13 +1042,19 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 		s_grp[threadIdx.x] = 0;
 	}
 	if (threadIdx.x == 0) {
-		s_lo = ~0ull;
+		s_lo = ~0u;
 		s_hi = 0;
 		s_base = 0;
+		s_big = 0;
 	}
-	uint64_t window;
-	enc_tile_scan(len, rel, window, s_wsum);
-	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+	uint32_t window;
+	bool big;
+	enc_tile_scan(len, rel, window, big, s_wsum, &s_big);
+	if (big) { // (a string of 4 MiB or more in this tile) the generic 64-bit path
+		__syncthreads();
+		enc_string<OFF>(t, stream, k, stage, err);
+		return;
+	}
 	// ---- offsets: out[i] = running sum before row i, out[rows] = total
 	{
 		OFF *offs = reinterpret_cast<OFF *>(stream + t.dst);
@@ -1069,8 +1094,9 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 		return;
 	}
 	bool fast = false;
-	if (window >= 8ull * B2A_ENC_STR_TILE) { // (tiles that average under 8 B per row — flags, codes — rarely qualify)
-		unsigned long long my_base = 0, my_lo = ~0ull, my_hi = 0;
+	if (window >= 8u * B2A_ENC_STR_TILE) { // (tiles that average under 8 B per row — flags, codes — rarely qualify)
+		unsigned long long my_base = 0;
+		uint32_t my_lo = ~0u, my_hi = 0;
 		bool has_long = false, bad = false;
 #pragma unroll
 		for (int u = 0; u < kRowsPerThread; u++) {
@@ -1086,7 +1112,7 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 		}
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) {
-			const unsigned long long l2 = __shfl_xor_sync(0xffffffffu, my_lo, o), h2 = __shfl_xor_sync(0xffffffffu, my_hi, o);
+			const uint32_t l2 = __shfl_xor_sync(0xffffffffu, my_lo, o), h2 = __shfl_xor_sync(0xffffffffu, my_hi, o);
 			my_lo = my_lo < l2 ? my_lo : l2;
 			my_hi = my_hi > h2 ? my_hi : h2;
 		}
@@ -1107,7 +1133,7 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 	uint32_t ph; // phase of window byte 0 inside the staging area
 	if (fast) {
 		const unsigned long long S = s_base;
-		const uint64_t lo = s_lo, hi = s_hi;
+		const uint32_t lo = s_lo, hi = s_hi;
 		ph = static_cast<uint32_t>(S & 15ull);
 		if (threadIdx.x == 0) {
 			const unsigned long long a0 = (S + lo) & ~15ull, a1 = (S + hi + 15ull) & ~15ull;
@@ -1118,19 +1144,22 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 #pragma unroll
 		for (int u = 0; u < kRowsPerThread; u++) {
 			if (len[u] <= 12) {
-				put_string_words(stage + ph + rel[u], e[u], len[u]);
+				put_inlined(stage + ph + rel[u], e[u], len[u]);
 			}
 		}
 	} else {
 		ph = pd;
 #pragma unroll
 		for (int u = 0; u < kRowsPerThread; u++) {
-			put_string_words(stage + ph + rel[u], e[u], len[u]);
+			put_inlined(stage + ph + rel[u], e[u], len[u]);
 		}
 	}
 	__syncthreads();
-	enc_stage_flush(stage, ph, gdst, static_cast<uint32_t>(window));
+	enc_stage_flush(stage, ph, gdst, window);
 }
+
+__device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
+                                                uint32_t *err); // generic 64-bit path, below
 
 // ArrowVarcharToStringViewData::Append (varchar_data.hpp:136-187), second generation: same tile, coalesced row mapping and
 // scan as enc_string2; the 16-byte views leave as coalesced stores, and the tile's slice of the ONE data buffer (the
@@ -1138,12 +1167,17 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 // fetches its own long strings eight words at a time (put_string_words) — and flushed with aligned 16-byte stores.
 __device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
                                                  uint8_t *stage, uint32_t *err) {
-	__shared__ uint64_t s_wsum[32];
+	__shared__ uint32_t s_wsum[32];
+	__shared__ uint32_t s_big;
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
+	const uint64_t tile_base = __ldg(reinterpret_cast<const unsigned long long *>(t.scratch) + k);
 	uint4 e[kRowsPerThread];
 	uint32_t len[kRowsPerThread]; // bytes that go to the data buffer (0 for NULL / inlined rows)
 	bool valid[kRowsPerThread];
-	uint64_t rel[kRowsPerThread];
+	uint32_t rel[kRowsPerThread];
+	if (threadIdx.x == 0) {
+		s_big = 0;
+	}
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
@@ -1154,9 +1188,14 @@ __device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t 
 			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid[u]));
 		}
 	}
-	uint64_t window;
-	enc_tile_scan(len, rel, window, s_wsum);
-	const uint64_t tile_base = reinterpret_cast<const uint64_t *>(t.scratch)[k];
+	uint32_t window;
+	bool big;
+	enc_tile_scan(len, rel, window, big, s_wsum, &s_big);
+	if (big) {
+		__syncthreads();
+		enc_string_view(t, stream, k, err);
+		return;
+	}
 #pragma unroll
 	for (int u = 0; u < kRowsPerThread; u++) {
 		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
@@ -1207,7 +1246,7 @@ __device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t 
 		}
 	}
 	__syncthreads();
-	enc_stage_flush(stage, pd, gdst, static_cast<uint32_t>(window));
+	enc_stage_flush(stage, pd, gdst, window);
 }
 
 // ArrowListData<BUFTYPE>::AppendOffsets: offsets only (children are appended through the selection built by
@@ -1446,12 +1485,21 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 		case B2A_ENC_BOOL:
 			enc_bool(t, stream, row0, nrows);
 			break;
+#ifdef B2A_ENC_STRING_V1 // A/B builds only (tools/build_variants.py): the first-generation string path
+		case B2A_ENC_STRING32:
+			enc_string<int32_t>(t, stream, k, stage, err);
+			break;
+		case B2A_ENC_STRING64:
+			enc_string<int64_t>(t, stream, k, stage, err);
+			break;
+#else
 		case B2A_ENC_STRING32:
 			enc_string2<int32_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
 			break;
 		case B2A_ENC_STRING64:
 			enc_string2<int64_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
 			break;
+#endif
 		case B2A_ENC_LIST32:
 			enc_list<int32_t>(t, stream, k, err);
 			break;

@@ -268,3 +268,22 @@ def test_scan_arrow_ipc_over_caller_buffers(db, cuda_device):
     assert rows("SELECT message FROM ipc_view WHERE \"commit\" = 'fa5f0299f046c46e1b2f671e5e3b4f1956522711'") == \
         [("ARROW-1: Initial Arrow Code Commit",)]
     assert rows("SELECT count(*) FROM ipc_view WHERE dayname(time::TIMESTAMP) = 'Wednesday'") == [("2927",)]
+
+
+@pytest.mark.gpu
+def test_multifile_options_of_duckdbs_framework(db, cuda_device):
+    """hive_types / hive_types_autocast / union_by_name casts belong to DuckDB's MultiFileReader
+    (duckdb/src/common/multi_file/multi_file_reader.cpp:137-197): with the extension linked they apply to read_arrow
+    exactly as they do in the reference"""
+    g = "'data/multifile/hive/*/*.arrow'"
+    assert rows(f"SELECT DISTINCT typeof(part) FROM read_arrow({g}, hive_partitioning=true)") == [("VARCHAR",)]
+    assert rows(f"SELECT DISTINCT typeof(part) FROM read_arrow({g}, hive_partitioning=true, "
+                "hive_types={'part': BLOB})") == [("BLOB",)]
+    assert rows(f"SELECT count(*) FROM read_arrow({g}, hive_partitioning=true) WHERE part = 'a'") == [("4",)]
+    with pytest.raises(R.RefError, match="hive_types"):
+        q(f"FROM read_arrow({g}, hive_partitioning=true, hive_types={{'nope': INT}})")
+    # a VARCHAR / DOUBLE / BIGINT weight column across three files, union_by_name: DuckDB's mapper casts per chunk
+    three = ("['data/multifile/different_type_int.arrows','data/multifile/glob/f1.arrow', "
+             "'data/multifile/different_type.arrows']")
+    got = rows(f"SELECT fruit, weight FROM read_arrow({three}, union_by_name=true) ORDER BY ALL")
+    assert len(got) == 6 and all(isinstance(w, str) for _, w in got)
