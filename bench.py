@@ -513,7 +513,7 @@ def leg_copy(ctx, args, scan, reader, d_out, my_rows, steps):
     torch.cuda.synchronize()
 
     def new_writer():
-        return b2a.ArrowWriter(cols, my_rows, BATCH_ROWS)
+        return b2a.ArrowWriter(cols, my_rows, BATCH_ROWS, device=ctx.local_rank)
 
     w = new_writer()
     w.measure()
@@ -544,7 +544,7 @@ def leg_copy(ctx, args, scan, reader, d_out, my_rows, steps):
     del d_stream
     # the SET produce_arrow_string_view = true variant of the same COPY (ArrowVarcharToStringViewData)
     try:
-        wv = b2a.ArrowWriter(cols, my_rows, BATCH_ROWS, produce_arrow_string_view=True)
+        wv = b2a.ArrowWriter(cols, my_rows, BATCH_ROWS, device=ctx.local_rank, produce_arrow_string_view=True)
         wv.measure()
         d_sv = torch.empty(wv.stream_bytes, dtype=torch.uint8, device=ctx.dev)
         ms_v, enc_v = _time_steps(ctx, lambda: wv.encode(d_sv), min(steps, 3), 3)
