@@ -18,7 +18,10 @@ namespace b2a {
 
 static constexpr int kThreads = 256;
 static constexpr int kRowsPerThread = B2A_ENC_STR_TILE / kThreads; // 4
-static constexpr uint32_t kStageBytes = 40 * 1024;                 // shared-memory staging of one tile's characters
+static constexpr uint32_t kStageBytes = 37 * 1024;                 // shared-memory staging of one tile's characters
+static constexpr uint32_t kRecBytes = B2A_ENC_STR_TILE * 16;       // the string_t records of one tile (prefetched)
+static constexpr uint32_t kEncStageArea = (kStageBytes + 64 + 127) & ~127u;
+static constexpr uint32_t kEncDynSmem = kEncStageArea + kRecBytes; // dynamic shared memory of b2a_encode_kernel
 
 __device__ __forceinline__ void enc_raise(uint32_t *err, uint32_t code) {
 	atomicMax(err, code);
@@ -1002,6 +1005,46 @@ __device__ __forceinline__ void enc_stage_flush(const uint8_t *stage, uint32_t p
 	}
 }
 
+// Cross-tile pipeline of the string ops: while a CTA works on tile n, the 16 KiB of string_t records of ITS next tile
+// (n + gridDim.x) arrive in shared memory by one bulk async copy — a tile otherwise starts with every warp waiting for
+// that first load (27 % of the stall samples of the first cut, profiles/r02_encode_kernel_v2_first_cut_details.txt).
+struct EncRecPipe {
+	uint8_t *rec;             // kRecBytes, 128-byte aligned
+	uint64_t *bar;            // completion of the records copy
+	uint32_t parity;          // phase the next wait expects
+	bool ready;               // `rec` receives the CURRENT tile's records
+	bool next_ready;          // ... the next tile's (set while the current tile is processed)
+	const b2a_enc_task *next; // descriptor of the CTA's next tile (resident in shared memory), nullptr if none
+	uint32_t next_tile;
+};
+
+// issues the copy for the next tile if it is a string tile whose rows are adjacent records (no selection vector);
+// every thread evaluates the condition (it is uniform), one thread issues
+__device__ __forceinline__ bool enc_prefetch_records(const EncRecPipe &rp) {
+#ifdef B2A_ENC_STRING_V1
+	return false;
+#else
+	if (!rp.next) {
+		return false;
+	}
+	const b2a_enc_task &tn = *rp.next;
+	if (!(tn.op == B2A_ENC_STRING32 || tn.op == B2A_ENC_STRING64 || tn.op == B2A_ENC_STRINGVIEW) || tn.sel != 0 ||
+	    (tn.src & 15u) != 0) {
+		return false;
+	}
+	const uint64_t r0 = static_cast<uint64_t>(rp.next_tile - tn.tile0) * B2A_ENC_STR_TILE;
+	if (r0 >= tn.rows) {
+		return false;
+	}
+	const uint64_t n = tn.rows - r0 < B2A_ENC_STR_TILE ? tn.rows - r0 : B2A_ENC_STR_TILE;
+	if (threadIdx.x == 0) {
+		enc_bulk_load(rp.rec, reinterpret_cast<const void *>(tn.src + (tn.row0 + r0) * 16), static_cast<uint32_t>(n * 16),
+		              rp.bar);
+	}
+	return true;
+#endif
+}
+
 // K12, second generation (VARCHAR / BLOB with int32 or int64 offsets; UUID keeps enc_string): string_t -> offsets +
 // characters (ArrowVarcharData::AppendTemplated, varchar_data.hpp:53-111).  Tile = 1 024 rows.
 //  * the 16 KiB of string_t are read fully coalesced (row = u * 256 + thread), the tile-wide exclusive scan of the lengths
@@ -1017,7 +1060,8 @@ __device__ __forceinline__ void enc_stage_flush(const uint8_t *stage, uint32_t p
 // non-inlined string, so any run of inlined strings inside the span is shorter than 256 x 12 B < 4 KiB.
 template <typename OFF>
 __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
-                                            uint8_t *stage, uint32_t *err, uint64_t *bar, uint32_t &parity) {
+                                            uint8_t *stage, uint32_t *err, uint64_t *bar, uint32_t &parity,
+                                            EncRecPipe &rp) {
 	__shared__ uint32_t s_wsum[32];
 	__shared__ unsigned long long s_base;
 	__shared__ uint32_t s_lo, s_hi, s_big;
@@ -1028,14 +1072,31 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 	uint4 e[kRowsPerThread];
 	uint32_t len[kRowsPerThread];
 	uint32_t rel[kRowsPerThread];
+	const bool from_pipe = rp.ready;
+	if (from_pipe) { // the records were fetched while the previous tile was processed
+		enc_mbar_wait(rp.bar, rp.parity);
+		rp.parity ^= 1u;
+		const uint4 *rec = reinterpret_cast<const uint4 *>(rp.rec);
 #pragma unroll
-	for (int u = 0; u < kRowsPerThread; u++) {
-		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
-		len[u] = 0;
-		e[u] = make_uint4(0, 0, 0, 0);
-		if (i < t.rows) {
-			bool valid;
-			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid));
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint32_t r = static_cast<uint32_t>(u) * kThreads + threadIdx.x;
+			len[u] = 0;
+			e[u] = make_uint4(0, 0, 0, 0);
+			if (row0 + r < t.rows) {
+				e[u] = rec[r];
+				len[u] = src_valid(t, t.row0 + row0 + r) ? e[u].x : 0u;
+			}
+		}
+	} else {
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+			len[u] = 0;
+			e[u] = make_uint4(0, 0, 0, 0);
+			if (i < t.rows) {
+				bool valid;
+				len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid));
+			}
 		}
 	}
 	if (threadIdx.x < 8) {
@@ -1050,6 +1111,9 @@ __device__ __forceinline__ void enc_string2(const b2a_enc_task &t, uint8_t *__re
 	uint32_t window;
 	bool big;
 	enc_tile_scan(len, rel, window, big, s_wsum, &s_big);
+	if (from_pipe) { // every thread has its records in registers (the scan's barrier): the area takes the next tile's
+		rp.next_ready = enc_prefetch_records(rp);
+	}
 	if (big) { // (a string of 4 MiB or more in this tile) the generic 64-bit path
 		__syncthreads();
 		enc_string<OFF>(t, stream, k, stage, err);
@@ -1166,7 +1230,7 @@ __device__ __forceinline__ void enc_string_view(const b2a_enc_task &t, uint8_t *
 // strings longer than 12 bytes, end to end) is assembled in the staging area at the destination's phase — every thread
 // fetches its own long strings eight words at a time (put_string_words) — and flushed with aligned 16-byte stores.
 __device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint32_t k,
-                                                 uint8_t *stage, uint32_t *err) {
+                                                 uint8_t *stage, uint32_t *err, EncRecPipe &rp) {
 	__shared__ uint32_t s_wsum[32];
 	__shared__ uint32_t s_big;
 	const uint64_t row0 = static_cast<uint64_t>(k) * B2A_ENC_STR_TILE;
@@ -1178,19 +1242,41 @@ __device__ __forceinline__ void enc_string_view2(const b2a_enc_task &t, uint8_t 
 	if (threadIdx.x == 0) {
 		s_big = 0;
 	}
+	const bool from_pipe = rp.ready;
+	if (from_pipe) {
+		enc_mbar_wait(rp.bar, rp.parity);
+		rp.parity ^= 1u;
+		const uint4 *rec = reinterpret_cast<const uint4 *>(rp.rec);
 #pragma unroll
-	for (int u = 0; u < kRowsPerThread; u++) {
-		const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
-		len[u] = 0;
-		valid[u] = false;
-		e[u] = make_uint4(0, 0, 0, 0);
-		if (i < t.rows) {
-			len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid[u]));
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint32_t r = static_cast<uint32_t>(u) * kThreads + threadIdx.x;
+			len[u] = 0;
+			valid[u] = false;
+			e[u] = make_uint4(0, 0, 0, 0);
+			if (row0 + r < t.rows) {
+				e[u] = rec[r];
+				valid[u] = src_valid(t, t.row0 + row0 + r);
+				len[u] = (valid[u] && e[u].x > 12u) ? e[u].x : 0u;
+			}
+		}
+	} else {
+#pragma unroll
+		for (int u = 0; u < kRowsPerThread; u++) {
+			const uint64_t i = row0 + static_cast<uint64_t>(u) * kThreads + threadIdx.x;
+			len[u] = 0;
+			valid[u] = false;
+			e[u] = make_uint4(0, 0, 0, 0);
+			if (i < t.rows) {
+				len[u] = static_cast<uint32_t>(entry_len(t, i, e[u], valid[u]));
+			}
 		}
 	}
 	uint32_t window;
 	bool big;
 	enc_tile_scan(len, rel, window, big, s_wsum, &s_big);
+	if (from_pipe) {
+		rp.next_ready = enc_prefetch_records(rp);
+	}
 	if (big) {
 		__syncthreads();
 		enc_string_view(t, stream, k, err);
@@ -1431,9 +1517,14 @@ template <bool FULL>
 __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
     b2a_encode_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task, uint32_t n_tiles,
                       uint8_t *__restrict__ stream, uint32_t *err) {
-	__shared__ b2a_enc_task s_task[2];
-	__shared__ __align__(128) uint8_t stage[kStageBytes + 64];
-	__shared__ __align__(8) uint64_t s_bar; // completion of the bulk copies of enc_string2
+	// descriptors: a ring of three — the current tile's, the next tile's (resident: the record prefetch reads it) and the
+	// one after that (arriving by cp.async)
+	__shared__ b2a_enc_task s_task[3];
+	extern __shared__ __align__(128) uint8_t enc_dyn_smem[]; // kEncDynSmem bytes: character stage, then the record area
+	uint8_t *const stage = enc_dyn_smem;
+	uint8_t *const s_rec = enc_dyn_smem + kEncStageArea;
+	__shared__ __align__(8) uint64_t s_bar;     // completion of the character bulk copies of enc_string2
+	__shared__ __align__(8) uint64_t s_bar_rec; // completion of the record prefetch
 	uint32_t bulk_parity = 0;
 	uint32_t tile = blockIdx.x;
 	if (tile >= n_tiles) {
@@ -1441,29 +1532,46 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 	}
 	if (threadIdx.x == 0) {
 		enc_mbar_init(&s_bar, 1);
+		enc_mbar_init(&s_bar_rec, 1);
 	}
-	const uint32_t stride = gridDim.x;
+	const uint64_t stride = gridDim.x;
 	const bool loader = threadIdx.x < kEncTaskVecs;
-	uint32_t ti_next = 0;
+	uint32_t ti_next2 = 0; // task of tile + 2 * stride (loader threads)
 	if (loader) {
 		const uint32_t ti = __ldg(tile_task + tile);
 		reinterpret_cast<uint4 *>(&s_task[0])[threadIdx.x] =
 		    __ldg(reinterpret_cast<const uint4 *>(tasks + ti) + threadIdx.x);
 		if (tile + stride < n_tiles) {
-			ti_next = __ldg(tile_task + tile + stride);
+			const uint32_t ti1 = __ldg(tile_task + tile + stride);
+			reinterpret_cast<uint4 *>(&s_task[1])[threadIdx.x] =
+			    __ldg(reinterpret_cast<const uint4 *>(tasks + ti1) + threadIdx.x);
+		}
+		if (tile + 2 * stride < n_tiles) {
+			ti_next2 = __ldg(tile_task + tile + 2 * stride);
 		}
 	}
+	EncRecPipe rp;
+	rp.rec = s_rec;
+	rp.bar = &s_bar_rec;
+	rp.parity = 0;
+	rp.ready = false; // the CTA's first tile loads its records itself
 	__syncthreads();
-	for (uint32_t buf = 0;; buf ^= 1) {
-		const uint32_t next = tile + stride;
-		if (loader && next < n_tiles) {
-			enc_cp_async16(reinterpret_cast<uint4 *>(&s_task[buf ^ 1]) + threadIdx.x,
-			               reinterpret_cast<const uint4 *>(tasks + ti_next) + threadIdx.x);
-			if (next + stride < n_tiles) {
-				ti_next = __ldg(tile_task + next + stride);
+	for (uint32_t slot = 0;; slot = slot == 2 ? 0 : slot + 1) {
+		const uint64_t next = tile + stride, next2 = tile + 2 * stride;
+		if (loader && next2 < n_tiles) {
+			enc_cp_async16(reinterpret_cast<uint4 *>(&s_task[slot == 0 ? 2 : slot - 1]) + threadIdx.x,
+			               reinterpret_cast<const uint4 *>(tasks + ti_next2) + threadIdx.x);
+			if (next2 + stride < n_tiles) {
+				ti_next2 = __ldg(tile_task + next2 + stride);
 			}
 		}
-		const b2a_enc_task &t = s_task[buf];
+		const b2a_enc_task &t = s_task[slot];
+		rp.next = next < n_tiles ? &s_task[slot == 2 ? 0 : slot + 1] : nullptr;
+		rp.next_tile = static_cast<uint32_t>(next);
+		rp.next_ready = false;
+		if (!rp.ready) { // the record area is not in use by this tile: the next tile's records may start right away
+			rp.next_ready = enc_prefetch_records(rp);
+		}
 		const uint32_t k = tile - t.tile0;
 		const uint64_t row0 = static_cast<uint64_t>(k) * t.tile_rows;
 		uint64_t nrows = t.rows > row0 ? t.rows - row0 : 0;
@@ -1494,10 +1602,10 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 			break;
 #else
 		case B2A_ENC_STRING32:
-			enc_string2<int32_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
+			enc_string2<int32_t>(t, stream, k, stage, err, &s_bar, bulk_parity, rp);
 			break;
 		case B2A_ENC_STRING64:
-			enc_string2<int64_t>(t, stream, k, stage, err, &s_bar, bulk_parity);
+			enc_string2<int64_t>(t, stream, k, stage, err, &s_bar, bulk_parity, rp);
 			break;
 #endif
 		case B2A_ENC_LIST32:
@@ -1521,7 +1629,7 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 				} else if (t.op == B2A_ENC_LISTVIEW64) {
 					enc_list<int64_t, true>(t, stream, k, err);
 				} else if (t.op == B2A_ENC_STRINGVIEW) {
-					enc_string_view2(t, stream, k, stage, err);
+					enc_string_view2(t, stream, k, stage, err, rp);
 				}
 			}
 			break;
@@ -1534,20 +1642,44 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 		}
 		enc_cp_async_wait_all();
 		__syncthreads();
-		tile = next;
+		tile = static_cast<uint32_t>(next);
+		rp.ready = rp.next_ready;
 	}
 }
 
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-static uint32_t PersistentGrid(const void *kernel, int sm_count, uint32_t n_tiles) {
+static uint32_t PersistentGrid(const void *kernel, int sm_count, uint32_t n_tiles, size_t dyn_smem = 0) {
 	int per_sm = 0;
-	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, 0) != cudaSuccess || per_sm <= 0) {
+	if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem) != cudaSuccess || per_sm <= 0) {
 		per_sm = 2;
 	}
 	uint32_t grid = static_cast<uint32_t>(sm_count) * static_cast<uint32_t>(per_sm);
 	return grid > n_tiles ? n_tiles : grid;
+}
+
+// more than 48 KiB of shared memory per CTA is an opt-in, per kernel and per device
+static int EncodeSmemOptIn() {
+	static bool done[64][2] = {};
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+		dev = 0;
+	}
+	if (!done[dev][0]) {
+		cudaError_t e = cudaFuncSetAttribute(b2a_encode_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                                     static_cast<int>(kEncDynSmem));
+		if (e != cudaSuccess) {
+			return static_cast<int>(e);
+		}
+		e = cudaFuncSetAttribute(b2a_encode_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                         static_cast<int>(kEncDynSmem));
+		if (e != cudaSuccess) {
+			return static_cast<int>(e);
+		}
+		done[dev][0] = true;
+	}
+	return 0;
 }
 
 int LaunchEncMeasure(const EncodeLaunch &l, void *stream) {
@@ -1579,15 +1711,18 @@ int LaunchEncode(const EncodeLaunch &l, void *stream) {
 	if (l.n_tiles == 0) {
 		return 0;
 	}
+	if (int e = EncodeSmemOptIn()) {
+		return e;
+	}
 	if (l.full) {
 		const uint32_t grid =
-		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<true>), l.sm_count, l.n_tiles);
-		b2a_encode_kernel<true><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<true>), l.sm_count, l.n_tiles, kEncDynSmem);
+		b2a_encode_kernel<true><<<grid, kThreads, kEncDynSmem, static_cast<cudaStream_t>(stream)>>>(
 		    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
 	} else {
 		const uint32_t grid =
-		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<false>), l.sm_count, l.n_tiles);
-		b2a_encode_kernel<false><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+		    PersistentGrid(reinterpret_cast<const void *>(b2a_encode_kernel<false>), l.sm_count, l.n_tiles, kEncDynSmem);
+		b2a_encode_kernel<false><<<grid, kThreads, kEncDynSmem, static_cast<cudaStream_t>(stream)>>>(
 		    l.d_tasks, l.d_tile_task, l.n_tiles, l.stream_out, l.d_err);
 	}
 	return static_cast<int>(cudaGetLastError());
