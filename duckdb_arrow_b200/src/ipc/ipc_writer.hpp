@@ -25,6 +25,7 @@ struct WriteField {
 	bool string_view = false;   // produce_arrow_string_view: "vu"
 	bool list_view = false;     // arrow_output_list_view: "+vl" / "+vL"
 	bool large_offsets = false; // arrow_large_buffer_size: "U" / "Z" / "+L" (set by the write planner)
+	bool lossless = false;      // arrow_lossless_conversion: extension types (set by the write planner)
 	std::vector<WriteField> children;
 	std::string format; // the C-data-interface format string the reference would set (for tests / diagnostics)
 };

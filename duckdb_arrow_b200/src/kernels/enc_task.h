@@ -26,6 +26,8 @@ enum b2a_enc_op {
 	B2A_ENC_LISTVIEW32,   /* ArrowListViewData<int32_t>::AppendListMetadata, list_view_data.hpp:59-103: offsets -> dst,
 	                         sizes -> dst2, `rows` entries each; a NULL row = {running offset, 0} */
 	B2A_ENC_LISTVIEW64,
+	B2A_ENC_UUID_BLOB,    /* ArrowScalarData<hugeint_t, hugeint_t, ArrowUUIDBlobConverter>, scalar_data.hpp:70-87: the UUID's 16
+	                         bytes big-endian (upper ^ sign bit first), NULL rows skipped */
 	B2A_ENC_STRINGVIEW    /* ArrowVarcharToStringViewData::Append, varchar_data.hpp:136-187: arrow_string_view_t[rows] -> dst,
 	                         the characters of the strings longer than 12 bytes -> dst2 (buffer index 0, int32 offset) */
 };

@@ -32,11 +32,16 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.src_width = w.dst_width = width;
 		w.n_buffers = 2;
 	};
+	wf.lossless = lossless;
 	switch (v.type_id) {
 	case B2A_T_SQLNULL:
 		w.n_buffers = 0;
 		break;
 	case B2A_T_BOOLEAN:
+		if (lossless) { // arrow.bool8: ArrowBool8::DuckToArrow copies the byte of every row, then ArrowScalarData<int8_t>
+			fixed(1);
+			break;
+		}
 		w.op = B2A_ENC_BOOL;
 		w.src_width = 1;
 		w.n_buffers = 2;
@@ -67,11 +72,21 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		fixed(8);
 		break;
 	case B2A_T_TIME_TZ: // ArrowScalarData<int64_t, dtime_tz_t, ArrowTimeTzConverter>, arrow_appender.cpp:164-171
+		if (lossless) { // ArrowScalarData<int64_t>: the dtime_tz_t bits as they are (w:8)
+			fixed(8);
+			break;
+		}
 		w.op = B2A_ENC_TIMETZ;
 		w.src_width = w.dst_width = 8;
 		w.n_buffers = 2;
 		break;
 	case B2A_T_UUID: // ArrowVarcharData<hugeint_t, ArrowUUIDConverter, int32_t>, arrow_appender.cpp:180-191
+		if (lossless) { // ArrowScalarData<hugeint_t, hugeint_t, ArrowUUIDBlobConverter>: 16 big-endian bytes, NULLs skipped
+			w.op = B2A_ENC_UUID_BLOB;
+			w.src_width = w.dst_width = 16;
+			w.n_buffers = 2;
+			break;
+		}
 		if (string_view) {
 			// the reference declares "vu" for a UUID column (arrow_converter.cpp:176-177) but appends offsets + characters
 			// (arrow_appender.cpp:180-191): schema and buffers disagree there, nothing to be compatible with
@@ -92,6 +107,12 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 1;
 		break;
 	case B2A_T_HUGEINT:
+		fixed(16);
+		break;
+	case B2A_T_UHUGEINT: // only arrow_lossless_conversion has a format for it (arrow_converter.cpp:161-171)
+		if (!lossless) {
+			throw Error(B2A_ENOTIMPL, "Unsupported Arrow type UHUGEINT");
+		}
 		fixed(16);
 		break;
 	case B2A_T_DECIMAL:
@@ -118,8 +139,13 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 			break;
 		}
 		/* fall through */
+	case B2A_T_JSON: // VARCHAR with the JSON alias: arrow.json under arrow_lossless_conversion, plain utf8 otherwise
 	case B2A_T_BLOB:
+	case B2A_T_VARINT:
 	case B2A_T_BIT: // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
+		if (v.type_id == B2A_T_VARINT && !lossless) {
+			throw Error(B2A_ENOTIMPL, "Unsupported Arrow type VARINT");
+		}
 		w.op = large_offsets ? B2A_ENC_STRING64 : B2A_ENC_STRING32;
 		w.src_width = 16;
 		w.dst_width = large_offsets ? 8 : 4;
@@ -197,6 +223,7 @@ void WritePlan::Build(const b2a_vector *columns, uint32_t n_columns, uint64_t ro
 	large_offsets = opt && (opt->flags & B2A_WRITE_LARGE_OFFSETS);
 	list_view = opt && (opt->flags & B2A_WRITE_LIST_VIEW);
 	string_view = opt && (opt->flags & B2A_WRITE_STRING_VIEW);
+	lossless = opt && (opt->flags & B2A_WRITE_LOSSLESS);
 	if (opt) {
 		for (uint32_t i = 0; i < opt->n_kv_metadata; i++) {
 			kv_metadata.emplace_back(opt->kv_keys[i], opt->kv_values[i]);

@@ -70,6 +70,7 @@ struct WritePlan {
 	bool large_offsets = false; // B2A_WRITE_LARGE_OFFSETS
 	bool list_view = false;     // B2A_WRITE_LIST_VIEW
 	bool string_view = false;   // B2A_WRITE_STRING_VIEW
+	bool lossless = false;      // B2A_WRITE_LOSSLESS
 	size_t n_variadic = 0;      // string-view nodes per batch: RecordBatch.variadicBufferCounts = [1] * n_variadic
 	uint64_t total_rows = 0;
 

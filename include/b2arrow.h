@@ -388,6 +388,12 @@ typedef struct b2a_write_options {
  * arrow_appender.cpp:234-235, arrow_converter.cpp:189-190): 16-byte views + ONE variadic data buffer holding the strings
  * longer than 12 bytes end to end (RecordBatch.variadicBufferCounts = [1] per such field).  BLOB / BIT keep offsets. */
 #define B2A_WRITE_STRING_VIEW 0x4u
+/* SET arrow_lossless_conversion = true (ClientProperties.arrow_lossless_conversion; arrow_converter.cpp:118-128,161-279,
+ * arrow_appender.cpp:161-191, arrow_type_extension.cpp:366-390): types Arrow has no 1:1 type for keep their bits and get
+ * an extension type instead of a lossy stand-in — UUID -> arrow.uuid over w:16 (big-endian bytes), HUGEINT / UHUGEINT ->
+ * arrow.opaque{DuckDB, hugeint | uhugeint} over w:16, TIME_TZ -> arrow.opaque{DuckDB, time_tz} over w:8, BIT / VARINT ->
+ * arrow.opaque{DuckDB, bit | varint} over z / Z, BOOLEAN -> arrow.bool8 over c (one byte per row), JSON -> arrow.json. */
+#define B2A_WRITE_LOSSLESS 0x8u
 
 typedef struct b2a_writer b2a_writer;
 

@@ -280,7 +280,7 @@ def test_multifile_options_of_duckdbs_framework(db, cuda_device):
     assert rows(f"SELECT DISTINCT typeof(part) FROM read_arrow({g}, hive_partitioning=true, "
                 "hive_types={'part': BLOB})") == [("BLOB",)]
     assert rows(f"SELECT count(*) FROM read_arrow({g}, hive_partitioning=true) WHERE part = 'a'") == [("4",)]
-    with pytest.raises(R.RefError, match="hive_types"):
+    with pytest.raises(R.RefError, match="hive_type"):
         q(f"FROM read_arrow({g}, hive_partitioning=true, hive_types={{'nope': INT}})")
     # a VARCHAR / DOUBLE / BIGINT weight column across three files, union_by_name: DuckDB's mapper casts per chunk
     three = ("['data/multifile/different_type_int.arrows','data/multifile/glob/f1.arrow', "
