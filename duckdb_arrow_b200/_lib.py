@@ -83,6 +83,7 @@ class WriteOptions(C.Structure):
 WRITE_LARGE_OFFSETS = 0x1  # B2A_WRITE_LARGE_OFFSETS
 WRITE_LIST_VIEW = 0x2  # B2A_WRITE_LIST_VIEW
 WRITE_STRING_VIEW = 0x4  # B2A_WRITE_STRING_VIEW
+WRITE_LOSSLESS = 0x8  # B2A_WRITE_LOSSLESS
 
 
 class HostStream(C.Structure):

@@ -733,7 +733,8 @@ class ArrowWriter:
 
     def __init__(self, columns: list[DeviceVector], rows: int, row_group_size: int = 122_880,
                  kv_metadata: dict | None = None, device: int = 0, arrow_large_buffer_size: bool = False,
-                 arrow_output_list_view: bool = False, produce_arrow_string_view: bool = False):
+                 arrow_output_list_view: bool = False, produce_arrow_string_view: bool = False,
+                 arrow_lossless_conversion: bool = False):
         self.device, self.columns = device, columns
         self._keep: list = []
         arr = (_lib.Vector * len(columns))()
@@ -743,7 +744,8 @@ class ArrowWriter:
         opt.row_group_size = row_group_size
         opt.flags = ((_lib.WRITE_LARGE_OFFSETS if arrow_large_buffer_size else 0)
                      | (_lib.WRITE_LIST_VIEW if arrow_output_list_view else 0)
-                     | (_lib.WRITE_STRING_VIEW if produce_arrow_string_view else 0))
+                     | (_lib.WRITE_STRING_VIEW if produce_arrow_string_view else 0)
+                     | (_lib.WRITE_LOSSLESS if arrow_lossless_conversion else 0))
         kv = kv_metadata or {}
         if kv:
             ks = (C.c_char_p * len(kv))(*[str(k).encode() for k in kv])
@@ -821,14 +823,16 @@ class ArrowWriter:
 
 def copy_to_arrows(columns: list[DeviceVector], path: str | None = None, row_group_size: int = 122_880,
                    chunk_size: int | None = None, kv_metadata: dict | None = None, device: int = 0,
-                   arrow_large_buffer_size: bool = False, arrow_output_list_view: bool = False, produce_arrow_string_view: bool = False) -> np.ndarray:
+                   arrow_large_buffer_size: bool = False, arrow_output_list_view: bool = False,
+                   produce_arrow_string_view: bool = False, arrow_lossless_conversion: bool = False) -> np.ndarray:
     """`COPY tbl TO 'x.arrows' (FORMAT ARROWS, ROW_GROUP_SIZE n, KV_METADATA {...})`
     (src/writer/write_arrow_stream.cpp:54-125: `chunk_size` is an alias of `row_group_size`).
-    `arrow_large_buffer_size` / `arrow_output_list_view` / `produce_arrow_string_view` are the session settings of those names (`SET ... = true`),
+    `arrow_large_buffer_size` / `arrow_output_list_view` / `produce_arrow_string_view` / `arrow_lossless_conversion` are
+    the session settings of those names (`SET ... = true`),
     which the reference's writer sees through `context.GetClientProperties()` (src/writer/arrow_stream_writer.cpp:11)."""
     rows = columns[0].rows if columns else 0
     w = ArrowWriter(columns, rows, chunk_size or row_group_size, kv_metadata, device, arrow_large_buffer_size,
-                    arrow_output_list_view, produce_arrow_string_view)
+                    arrow_output_list_view, produce_arrow_string_view, arrow_lossless_conversion)
     stream = w.write()
     if path is not None:
         with open(path, "wb") as f:
@@ -839,12 +843,13 @@ def copy_to_arrows(columns: list[DeviceVector], path: str | None = None, row_gro
 
 
 def to_arrow_ipc(columns: list[DeviceVector], device: int = 0,
-                 arrow_large_buffer_size: bool = False, arrow_output_list_view: bool = False, produce_arrow_string_view: bool = False) -> list[tuple[bytes, bool]]:
+                 arrow_large_buffer_size: bool = False, arrow_output_list_view: bool = False,
+                 produce_arrow_string_view: bool = False, arrow_lossless_conversion: bool = False) -> list[tuple[bytes, bool]]:
     """`FROM to_arrow_ipc((FROM t))`: rows of (ipc BLOB, header BOOL) — first the schema message, then one
     record-batch message per 120 x 2 048 rows (src/writer/to_arrow_ipc.cpp:21,116-155, to_arrow_ipc.hpp:28)."""
     rows = columns[0].rows if columns else 0
     w = ArrowWriter(columns, rows, 120 * VECTOR_SIZE, None, device, arrow_large_buffer_size, arrow_output_list_view,
-                    produce_arrow_string_view)
+                    produce_arrow_string_view, arrow_lossless_conversion)
     stream = w.write()
     out = []
     first = w.batch(0).meta_offset if w.n_batches else w.stream_bytes - 8

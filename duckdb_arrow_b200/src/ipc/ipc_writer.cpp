@@ -46,6 +46,28 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		o.tag = ArrowTypeTag::Timestamp;
 		o.table = b.end_table();
 	};
+	auto fixed_binary = [&](int32_t width) {
+		b.start_table();
+		b.add_scalar<int32_t>(0, width, 0);
+		o.tag = ArrowTypeTag::FixedSizeBinary;
+		o.table = b.end_table();
+	};
+	if (f.lossless) { // the storage types of the extension types, arrow_type_extension.cpp:366-379
+		switch (f.type_id) {
+		case B2A_T_BOOLEAN:
+			int_type(8, true);
+			return o;
+		case B2A_T_HUGEINT:
+		case B2A_T_UUID:
+			fixed_binary(16);
+			return o;
+		case B2A_T_TIME_TZ:
+			fixed_binary(8);
+			return o;
+		default:
+			break;
+		}
+	}
 	switch (f.type_id) {
 	case B2A_T_SQLNULL:
 		empty(ArrowTypeTag::Null);
@@ -96,10 +118,15 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 		o.table = b.end_table();
 		break;
 	}
+	case B2A_T_UHUGEINT:
+		fixed_binary(16);
+		break;
 	case B2A_T_VARCHAR:
+	case B2A_T_JSON:
 		empty(f.string_view ? ArrowTypeTag::Utf8View : f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
 		break;
 	case B2A_T_BLOB:
+	case B2A_T_VARINT:
 	case B2A_T_BIT: // arrow_converter.cpp:268-279 without arrow_lossless_conversion: plain binary
 		empty(f.large_offsets ? ArrowTypeTag::LargeBinary : ArrowTypeTag::Binary);
 		break;
@@ -178,6 +205,43 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 	return o;
 }
 
+// The extension a field is written as: {ARROW:extension:name, ARROW:extension:metadata}; empty name = none.
+// arrow_converter.cpp:118-128 (alias types), :130-279 (the arrow_lossless_conversion branches), :387-393 (types
+// without a case of their own); names and metadata of arrow_type_extension.cpp:366-390, schema_metadata.cpp:58-73.
+std::pair<std::string, std::string> ExtensionOf(const WriteField &f) {
+	auto opaque = [](const char *type_name) {
+		return std::make_pair(std::string("arrow.opaque"),
+		                      std::string("{\"type_name\":\"") + type_name + "\",\"vendor_name\":\"DuckDB\"}");
+	};
+	switch (f.type_id) {
+	case B2A_T_UHUGEINT:
+		return opaque("uhugeint");
+	case B2A_T_VARINT:
+		return opaque("varint");
+	default:
+		break;
+	}
+	if (!f.lossless) {
+		return {};
+	}
+	switch (f.type_id) {
+	case B2A_T_BOOLEAN:
+		return {"arrow.bool8", ""};
+	case B2A_T_UUID:
+		return {"arrow.uuid", ""};
+	case B2A_T_JSON:
+		return {"arrow.json", ""};
+	case B2A_T_HUGEINT:
+		return opaque("hugeint");
+	case B2A_T_TIME_TZ:
+		return opaque("time_tz");
+	case B2A_T_BIT:
+		return opaque("bit");
+	default:
+		return {};
+	}
+}
+
 uint32_t BuildField(fb::Builder &b, const WriteField &f) {
 	std::vector<uint32_t> kids;
 	for (auto &c : f.children) {
@@ -189,6 +253,22 @@ uint32_t BuildField(fb::Builder &b, const WriteField &f) {
 		tz = b.create_string(f.timezone.empty() ? std::string("UTC") : f.timezone);
 	}
 	TypeOut ty = BuildType(b, f, tz);
+	uint32_t custom = 0;
+	const auto ext = ExtensionOf(f);
+	if (!ext.first.empty()) { // Field.custom_metadata, in the order ArrowSchemaMetadata::SerializeMetadata emits
+		std::vector<uint32_t> kvs;
+		const std::pair<const char *, const std::string *> entries[2] = {{"ARROW:extension:metadata", &ext.second},
+		                                                                {"ARROW:extension:name", &ext.first}};
+		for (auto &e : entries) {
+			uint32_t k = b.create_string(e.first);
+			uint32_t v = b.create_string(*e.second);
+			b.start_table();
+			b.add_offset(0, k);
+			b.add_offset(1, v);
+			kvs.push_back(b.end_table());
+		}
+		custom = b.create_offset_vector(kvs);
+	}
 	uint32_t name = b.create_string(f.name);
 	b.start_table();
 	b.add_offset(0, name);
@@ -196,6 +276,9 @@ uint32_t BuildField(fb::Builder &b, const WriteField &f) {
 	b.add_scalar<uint8_t>(2, static_cast<uint8_t>(ty.tag), 0);
 	b.add_offset(3, ty.table);
 	b.add_offset(5, kids_vec);
+	if (custom) {
+		b.add_offset(6, custom);
+	}
 	return b.end_table();
 }
 
@@ -230,6 +313,22 @@ void ResolveArrowFormat(WriteField &f) {
 			                            " children, expected " + std::to_string(n));
 		}
 	};
+	if (f.lossless) {
+		switch (f.type_id) {
+		case B2A_T_BOOLEAN:
+			f.format = "c";
+			return;
+		case B2A_T_HUGEINT:
+		case B2A_T_UUID:
+			f.format = "w:16";
+			return;
+		case B2A_T_TIME_TZ:
+			f.format = "w:8";
+			return;
+		default:
+			break;
+		}
+	}
 	switch (f.type_id) {
 	case B2A_T_SQLNULL:
 		f.format = "n";
@@ -277,11 +376,16 @@ void ResolveArrowFormat(WriteField &f) {
 		f.format = "d:" + std::to_string(f.decimal_width) + "," + std::to_string(f.decimal_scale) + "," +
 		           std::to_string(DecimalBitWidth(f.decimal_width));
 		break;
+	case B2A_T_UHUGEINT:
+		f.format = "w:16";
+		break;
 	case B2A_T_VARCHAR:
+	case B2A_T_JSON:
 	case B2A_T_UUID:
 		f.format = f.string_view ? "vu" : f.large_offsets ? "U" : "u";
 		break;
 	case B2A_T_BLOB:
+	case B2A_T_VARINT:
 	case B2A_T_BIT:
 		f.format = f.large_offsets ? "Z" : "z";
 		break;

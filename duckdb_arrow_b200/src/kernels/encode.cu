@@ -406,6 +406,24 @@ __device__ __forceinline__ void enc_timetz(const b2a_enc_task &t, uint8_t *__res
 	}
 }
 
+// ArrowUUIDBlobConverter (scalar_data.hpp:70-87), arrow_lossless_conversion: hugeint_t{u64 lower; i64 upper} -> the 16
+// bytes of the UUID, most significant first (the stored sign bit of `upper` flipped back); SkipNulls: 0 here
+__device__ __forceinline__ void enc_uuid_blob(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
+                                              uint64_t nrows) {
+	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
+		const uint64_t sr = map_row(t, i);
+		uint4 o = make_uint4(0, 0, 0, 0);
+		if (src_valid(t, sr)) {
+			const uint4 e = __ldg(reinterpret_cast<const uint4 *>(t.src) + sr);
+			o.x = __byte_perm(e.w ^ 0x80000000u, 0, 0x0123);
+			o.y = __byte_perm(e.z, 0, 0x0123);
+			o.z = __byte_perm(e.y, 0, 0x0123);
+			o.w = __byte_perm(e.x, 0, 0x0123);
+		}
+		reinterpret_cast<uint4 *>(stream + t.dst)[i] = o;
+	}
+}
+
 // ArrowUnionData::Append (union_data.cpp:34-47): type id = tag of a valid union row, 0 for a NULL one
 __device__ __forceinline__ void enc_union_tag(const b2a_enc_task &t, uint8_t *__restrict__ stream, uint64_t row0,
                                               uint64_t nrows) {
@@ -1620,6 +1638,8 @@ __global__ void __launch_bounds__(kThreads, B2A_ENC_MIN_BLOCKS)
 					enc_timetz(t, stream, row0, nrows);
 				} else if (t.op == B2A_ENC_UNION_TAG) {
 					enc_union_tag(t, stream, row0, nrows);
+				} else if (t.op == B2A_ENC_UUID_BLOB) {
+					enc_uuid_blob(t, stream, row0, nrows);
 				} else if (t.op == B2A_ENC_UUID32) {
 					enc_string<int32_t, true>(t, stream, k, stage, err);
 				} else if (t.op == B2A_ENC_UUID64) {

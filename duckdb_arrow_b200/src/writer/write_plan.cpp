@@ -38,10 +38,15 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 0;
 		break;
 	case B2A_T_BOOLEAN:
-		if (lossless) { // arrow.bool8: ArrowBool8::DuckToArrow copies the byte of every row, then ArrowScalarData<int8_t>
+		if (lossless && depth == 0) {
+			// arrow.bool8: ArrowBool8::DuckToArrow copies the byte of every row, then ArrowScalarData<int8_t>.  ROOT columns
+			// only — ArrowAppender::Append runs duckdb_to_arrow on root_data[i] (arrow_appender.cpp:40-48) while a nested
+			// BOOLEAN keeps ArrowBoolData (:147-149).  The reference still labels the nested field arrow.bool8 / "c" over
+			// those bit-packed bytes; here the buffers are the same and the nested field says what they are: "b".
 			fixed(1);
 			break;
 		}
+		wf.lossless = false;
 		w.op = B2A_ENC_BOOL;
 		w.src_width = 1;
 		w.n_buffers = 2;
@@ -109,10 +114,7 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	case B2A_T_HUGEINT:
 		fixed(16);
 		break;
-	case B2A_T_UHUGEINT: // only arrow_lossless_conversion has a format for it (arrow_converter.cpp:161-171)
-		if (!lossless) {
-			throw Error(B2A_ENOTIMPL, "Unsupported Arrow type UHUGEINT");
-		}
+	case B2A_T_UHUGEINT: // no switch case in SetArrowFormat: always the registered extension (arrow_converter.cpp:387-393)
 		fixed(16);
 		break;
 	case B2A_T_DECIMAL:
@@ -131,6 +133,7 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 		w.n_buffers = 2;
 		break;
 	case B2A_T_VARCHAR:
+	case B2A_T_JSON: // VARCHAR with the JSON alias: same appender; arrow.json in the schema under arrow_lossless_conversion
 		if (string_view) { // ArrowVarcharToStringViewData, arrow_appender.cpp:234-235: validity, views, one data buffer
 			w.op = B2A_ENC_STRINGVIEW;
 			w.src_width = w.dst_width = 16;
@@ -139,13 +142,9 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 			break;
 		}
 		/* fall through */
-	case B2A_T_JSON: // VARCHAR with the JSON alias: arrow.json under arrow_lossless_conversion, plain utf8 otherwise
 	case B2A_T_BLOB:
-	case B2A_T_VARINT:
-	case B2A_T_BIT: // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
-		if (v.type_id == B2A_T_VARINT && !lossless) {
-			throw Error(B2A_ENOTIMPL, "Unsupported Arrow type VARINT");
-		}
+	case B2A_T_VARINT: // always arrow.opaque{DuckDB, varint} (arrow_converter.cpp:387-393), appended like a BLOB
+	case B2A_T_BIT:    // arrow_appender.cpp:239-247: the internal bit string is appended like a BLOB
 		w.op = large_offsets ? B2A_ENC_STRING64 : B2A_ENC_STRING32;
 		w.src_width = 16;
 		w.dst_width = large_offsets ? 8 : 4;

@@ -269,6 +269,9 @@ struct VectorTree {
 };
 
 static int32_t B2ATypeId(const LogicalType &t) {
+	if (t.IsJSONType()) { // VARCHAR with the JSON alias: arrow.json under arrow_lossless_conversion (arrow_converter.cpp:118-128)
+		return B2A_T_JSON;
+	}
 	switch (t.id()) {
 	case LogicalTypeId::SQLNULL: return B2A_T_SQLNULL;
 	case LogicalTypeId::BOOLEAN: return B2A_T_BOOLEAN;
@@ -302,8 +305,10 @@ static int32_t B2ATypeId(const LogicalType &t) {
 	case LogicalTypeId::UNION: return B2A_T_UNION;
 	case LogicalTypeId::TIME_TZ: return B2A_T_TIME_TZ;
 	case LogicalTypeId::BIT: return B2A_T_BIT;
+	case LogicalTypeId::UHUGEINT: return B2A_T_UHUGEINT;
+	case LogicalTypeId::VARINT: return B2A_T_VARINT;
 	default:
-		// ENUM (dictionary output), UHUGEINT / VARINT (no Arrow format without arrow_lossless_conversion): DESIGN.md §9
+		// ENUM (dictionary output): DESIGN.md §9
 		throw NotImplementedException("Unsupported Arrow type %s", t.ToString());
 	}
 }
@@ -392,7 +397,7 @@ static WriteSettings SettingsOf(ClientContext &context) {
 		s.flags |= B2A_WRITE_STRING_VIEW;
 	}
 	if (props.arrow_lossless_conversion) {
-		throw NotImplementedException("arrow_lossless_conversion is not supported by the B200 Arrow writer");
+		s.flags |= B2A_WRITE_LOSSLESS;
 	}
 	return s;
 }

@@ -12,6 +12,9 @@ Restates DuckDB's ArrowAppender, one function per appender, over host vectors (t
   ArrowTimeTzConverter      .../appender/scalar_data.hpp:54-68 (TIME_TZ -> time64[us], the offset is dropped)
   ArrowUUIDConverter        .../appender/varchar_data.hpp:33-43 + UUID::ToString duckdb/src/common/types/uuid.cpp:70-101
   ArrowUnionData            duckdb/src/common/arrow/appender/union_data.cpp:24-52 (flat members)
+  arrow_lossless_conversion arrow_appender.cpp:144-191 + arrow_type_extension.cpp:345-390: BOOLEAN as one byte per row
+                            (ArrowBool8::DuckToArrow), UUID through ArrowUUIDBlobConverter (scalar_data.hpp:70-87),
+                            TIME_TZ / HUGEINT / UHUGEINT bits as they are, BIT / VARINT like BLOB, JSON like VARCHAR
 and the body packing of the nanoarrow encoder the reference calls (ArrowIpcEncoderEncodeSimpleRecordBatch,
 src/writer/column_data_collection_serializer.cpp:86-92): buffers in pre-order, each padded with zeros to 8 bytes.
 nanoarrow is not in the reference tree (CMakeLists.txt:7-13), so the exact FILE bytes of the reference writer are
@@ -44,7 +47,7 @@ def _validity_buffer(valid: np.ndarray) -> tuple[bytes, int]:
 
 
 def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False, view: bool = False,
-           sview: bool = False):
+           sview: bool = False, lossless: bool = False):
     """Append rows `idx` (input row indices: the UnifiedVectorFormat selection) of vector hv; pre-order output.
     nodes: [(length, null_count)], buffers: [bytes] (unpadded).
     large: ClientProperties.arrow_offset_size == LARGE (SET arrow_large_buffer_size): int64 offsets for VARCHAR / BLOB /
@@ -54,7 +57,11 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
     sview: ClientProperties.produce_arrow_string_view: VARCHAR -> ArrowVarcharToStringViewData (varchar_data.hpp:129-202):
     16-byte views {length, 12 bytes zero padded} / {length, first 4 bytes, buffer index 0, int32 offset} (NULL: zeros) and
     one data buffer with the strings longer than 12 bytes; the fourth C-data buffer (data-buffer sizes) is not part of the
-    IPC body (it becomes RecordBatch.variadicBufferCounts)."""
+    IPC body (it becomes RecordBatch.variadicBufferCounts).
+    lossless: ClientProperties.arrow_lossless_conversion (see the module header); True for a top-level column, "nested"
+    below one: the bool8 route exists for ROOT columns only (ArrowAppender::Append converts root_data[i] through
+    duckdb_to_arrow, arrow_appender.cpp:40-48; a nested BOOLEAN keeps ArrowBoolData, :147-149)."""
+    below = "nested" if lossless else False
     off_t = np.int64 if large else np.int32
     n = len(idx)
     t = hv.type
@@ -74,7 +81,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
             import copy
             member = copy.copy(c)
             member.validity = valid_full & (tags_full == m) & own
-            append(member, idx, nodes, buffers, large, view, sview)
+            append(member, idx, nodes, buffers, large, view, sview, below)
         return
     valid = _valid(hv, idx)
     vbuf, nulls = _validity_buffer(valid)
@@ -82,7 +89,18 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
         vbuf, nulls = b"", 0
     nodes.append((n, nulls))
     buffers.append(vbuf)
-    if t == "BOOLEAN":
+    if t == "BOOLEAN" and lossless is True:  # arrow.bool8: the byte of every row, NULL slots included
+        buffers.append(hv.data[idx].astype(np.uint8).tobytes())
+    elif t == "UUID" and lossless:  # most significant byte first, the stored sign bit flipped back; NULLs skipped (0)
+        raw = hv.data.view(np.uint64).reshape(-1, 2)[idx]
+        out = np.zeros((n, 2), ">u8")
+        out[:, 0] = raw[:, 1] ^ np.uint64(1 << 63)
+        out[:, 1] = raw[:, 0]
+        out[~valid] = 0
+        buffers.append(out.tobytes())
+    elif t == "TIME_TZ" and lossless:
+        buffers.append(hv.data.reshape(-1, 8)[idx].tobytes() if n else b"")
+    elif t == "BOOLEAN":
         data = hv.data[idx] != 0
         bits = np.ones(((n + 7) // 8) * 8, bool)
         bits[:n] = ~valid | data  # only a VALID false clears the bit
@@ -101,7 +119,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
     elif t == "TIME_TZ":  # dtime_tz_t: micros in the upper 40 bits (OFFSET_BITS = 24); NULL slots unwritten (0 here)
         bits = hv.data.view(np.uint64)[idx]
         buffers.append(np.where(valid, bits >> np.uint64(24), 0).astype(np.int64).tobytes())
-    elif t == "VARCHAR" and sview:
+    elif t in ("VARCHAR", "JSON") and sview:
         slen = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
         is_long = slen > 12
         long_len = np.where(is_long, slen, 0)
@@ -121,7 +139,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
                + np.repeat(hv.str_start[idx], long_len))
         buffers.append(views.tobytes())
         buffers.append(hv.heap[pos].tobytes() if total else b"")
-    elif t in ("VARCHAR", "BLOB", "BIT"):
+    elif t in ("VARCHAR", "BLOB", "BIT", "VARINT", "JSON"):
         length = np.where(valid, hv.str_len[idx], 0).astype(np.int64)
         offs = np.zeros(n + 1, np.int64)
         np.cumsum(length, out=offs[1:])
@@ -151,14 +169,14 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
         child = hv.children[0]
         if t == "MAP":
             child._no_validity_buffer = True  # the entries struct's validity buffer is never resized (map_data.hpp)
-        append(child, child_sel, nodes, buffers, large, view, sview)
+        append(child, child_sel, nodes, buffers, large, view, sview, below)
     elif t == "STRUCT":
         for c in hv.children:
-            append(c, idx, nodes, buffers, large, view, sview)
+            append(c, idx, nodes, buffers, large, view, sview, below)
     elif t == "ARRAY":
         k = hv.param
         child_idx = (idx[:, None] * k + np.arange(k)[None, :]).reshape(-1)
-        append(hv.children[0], child_idx, nodes, buffers, large, view, sview)
+        append(hv.children[0], child_idx, nodes, buffers, large, view, sview, below)
     elif t == "DECIMAL" and hv.decimal[0] <= 4:
         buffers.append(hv.data.view(np.int16)[idx].astype(np.int32).tobytes())
     elif t == "INTERVAL":
@@ -173,7 +191,7 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
 
 
 def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, large: bool = False,
-                      view: bool = False, sview: bool = False):
+                      view: bool = False, sview: bool = False, lossless: bool = False):
     """-> [(rows, nodes, buffers[(offset, length)], body bytes)] per record batch"""
     out = []
     for r0 in range(0, rows, row_group_size):
@@ -181,7 +199,7 @@ def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, l
         idx = np.arange(r0, r0 + n, dtype=np.int64)
         nodes, bufs = [], []
         for c in columns:
-            append(c, idx, nodes, bufs, large, view, sview)
+            append(c, idx, nodes, bufs, large, view, sview, lossless)
         body, slices = b"", []
         for b in bufs:
             slices.append((len(body), len(b)))

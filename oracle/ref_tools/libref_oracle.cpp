@@ -559,11 +559,25 @@ void ref_file_close(void *handle) {
 // ColumnDataCollectionSerializer::Serialize(ColumnDataCollection&) builds, column_data_collection_serializer.cpp:97-115)
 // and hands it to ArrowConverter::ToArrowArray / ToArrowSchema under the given ClientProperties.
 //   flags: 1 arrow_large_buffer_size, 2 arrow_output_list_view, 4 produce_arrow_string_view, 8 arrow_lossless_conversion
+// The extension types' PopulateSchema callbacks read the settings from the context, not from the ClientProperties
+// handed to ToArrowSchema (arrow_type_extension.cpp:306-316): keep the two in step.
+static void ApplyFlags(Connection &con, uint32_t flags) {
+	const char *names[4] = {"arrow_large_buffer_size", "arrow_output_list_view", "produce_arrow_string_view",
+	                        "arrow_lossless_conversion"};
+	for (int i = 0; i < 4; i++) {
+		auto r = con.Query(string("SET ") + names[i] + " = " + ((flags >> i) & 1 ? "true" : "false"));
+		if (r->HasError()) {
+			r->GetErrorObject().Throw();
+		}
+	}
+}
+
 int ref_append(ArrowArrayStream *stream, uint32_t flags, ArrowArray *out_array, ArrowSchema *out_schema, char *err,
                int errlen) {
 	try {
 		auto &s = session();
 		auto &context = *s.con->context;
+		ApplyFlags(*s.con, flags);
 		s.con->BeginTransaction();
 		try {
 			RefScan scan(context, stream);
@@ -674,6 +688,7 @@ void *ref_export_begin(const char *sql, uint32_t flags, ArrowSchema *out_schema,
 	try {
 		auto &s = session();
 		auto e = new Export();
+		ApplyFlags(*s.meta, flags);
 		e->options = s.meta->context->GetClientProperties();
 		e->result = s.con->SendQuery(sql);
 		if (e->result->HasError()) {

@@ -287,3 +287,47 @@ def test_multifile_options_of_duckdbs_framework(db, cuda_device):
              "'data/multifile/different_type.arrows']")
     got = rows(f"SELECT fruit, weight FROM read_arrow({three}, union_by_name=true) ORDER BY ALL")
     assert len(got) == 6 and all(isinstance(w, str) for _, w in got)
+
+
+@pytest.mark.gpu
+def test_arrow_lossless_conversion_through_copy(db, cuda_device):
+    """SET arrow_lossless_conversion (ClientProperties -> B2A_WRITE_LOSSLESS): COPY writes the extension types of
+    duckdb/src/common/arrow/arrow_type_extension.cpp:366-390 and read_arrow brings the DuckDB types back; without the
+    setting UUID / HUGEINT / TIME_TZ / BIT come back as the lossy stand-ins, UHUGEINT / VARINT survive either way."""
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+    q("CREATE OR REPLACE TABLE ll AS SELECT "
+      "CASE WHEN i % 7 = 0 THEN NULL ELSE (i * 1000003)::HUGEINT * 18446744073709551629 END AS h, "
+      "(i::UHUGEINT * 18446744073709551557) AS uh, "
+      "CASE WHEN i % 5 = 0 THEN NULL ELSE i % 3 = 0 END AS b, "
+      "CASE WHEN i % 11 = 0 THEN NULL ELSE uuid() END AS u, "
+      "CASE WHEN i % 13 = 0 THEN NULL ELSE ('12:34:56+02'::TIMETZ + to_seconds(i)) END AS tz, "
+      "CASE WHEN i % 9 = 0 THEN NULL ELSE i::INTEGER::BIT END AS bt, "
+      "(i::VARCHAR || '340282366920938463463374607431768211507')::VARINT AS vi, "
+      "{'u': uuid(), 'b': i % 2 = 0} AS st "
+      "FROM range(5000) t(i)")
+    p = f"{db}/lossless.arrows"
+    q("SET arrow_lossless_conversion = true")
+    try:
+        q(f"COPY ll TO '{p}' (FORMAT ARROWS, ROW_GROUP_SIZE 2048)")
+    finally:
+        q("SET arrow_lossless_conversion = false")
+    t = ipc.open_stream(p).read_all()
+    ty = {f.name: f.type for f in t.schema}
+    assert ty["h"] == pa.opaque(pa.binary(16), "hugeint", "DuckDB") and ty["u"] == pa.uuid() and ty["b"] == pa.bool8()
+    assert ty["tz"] == pa.opaque(pa.binary(8), "time_tz", "DuckDB") and ty["bt"] == pa.opaque(pa.binary(), "bit", "DuckDB")
+    assert ty["st"].field("u").type == pa.uuid() and ty["st"].field("b").type == pa.bool_()
+    d = rows(f"DESCRIBE SELECT * FROM read_arrow('{p}')")
+    assert [r[1] for r in d] == ["HUGEINT", "UHUGEINT", "BOOLEAN", "UUID", "TIME WITH TIME ZONE", "BIT", "VARINT",
+                                 "STRUCT(u UUID, b BOOLEAN)"]
+    assert rows(f"SELECT count(*) FROM (SELECT * FROM ll EXCEPT ALL SELECT * FROM read_arrow('{p}'))") == [("0",)]
+    assert rows(f"SELECT count(*) FROM (SELECT * FROM read_arrow('{p}') EXCEPT ALL SELECT * FROM ll)") == [("0",)]
+    # the lossy routes of the same table
+    p2 = f"{db}/lossy.arrows"
+    q(f"COPY ll TO '{p2}' (FORMAT ARROWS)")
+    d = rows(f"DESCRIBE SELECT * FROM read_arrow('{p2}')")
+    assert [r[1] for r in d] == ["DECIMAL(38,0)", "UHUGEINT", "BOOLEAN", "VARCHAR", "TIME", "BLOB", "VARINT",
+                                 "STRUCT(u VARCHAR, b BOOLEAN)"]
+    assert rows(f"SELECT count(*) FROM ll JOIN read_arrow('{p2}') r ON ll.u::VARCHAR = r.u") == \
+        rows("SELECT count(u) FROM ll")
+    q("DROP TABLE ll")

@@ -139,11 +139,68 @@ def test_null_map_keys_are_rejected(b2a, cuda_device):
 
 
 def test_unsupported_type_is_not_implemented(b2a):
-    """UHUGEINT / VARINT have no case in SetArrowFormat without arrow_lossless_conversion (arrow_converter.cpp:115-395)"""
+    """a type id the appender has no routine for (arrow_appender.cpp:300-302)"""
     from duckdb_arrow_b200 import DeviceVector
-    for t in ("UHUGEINT", "VARINT"):
-        with pytest.raises(b2a.B2AError, match="Unsupported type"):
-            b2a.ArrowWriter([DeviceVector(t, 0, None, None, name="u")], 0, device=-1)
+    with pytest.raises(b2a.B2AError, match="Unsupported type"):
+        b2a.ArrowWriter([DeviceVector("INVALID", 0, None, None, name="u")], 0, device=-1)
+
+
+@pytest.mark.parametrize("settings", [dict(arrow_lossless_conversion=True),
+                                      dict(arrow_lossless_conversion=True, arrow_large_buffer_size=True),
+                                      dict(arrow_lossless_conversion=True, produce_arrow_string_view=True),
+                                      dict()])
+@pytest.mark.parametrize("rgs", [2048, 1000])
+def test_lossless_conversion_bit_exact_vs_oracle(b2a, cuda_device, rgs, settings):
+    """SET arrow_lossless_conversion = true (arrow_converter.cpp:130-279, arrow_appender.cpp:144-191): BOOLEAN -> arrow.bool8
+    bytes (root columns), UUID -> arrow.uuid big-endian w:16 (B2A_ENC_UUID_BLOB), HUGEINT / UHUGEINT / TIME_TZ ->
+    arrow.opaque w:16 / w:8, BIT / VARINT -> arrow.opaque binary; bodies bit-exact vs the restatement that
+    tests/test_ref_append.py pins to the reference appender, and pyarrow reads the extension types back.  Without the
+    setting the same vectors take the lossy routes and UHUGEINT / VARINT stay extension types."""
+    from writer_cases import lossless_table
+    n = 4000
+    table = lossless_table(n)
+    host = table_vectors(table)
+    lossless = settings.get("arrow_lossless_conversion", False)
+    w = b2a.ArrowWriter([to_device(h) for h in host], n, rgs, **settings)
+    stream = w.write()
+    exp = OW.serialize_batches(host, n, rgs, large=settings.get("arrow_large_buffer_size", False),
+                               sview=settings.get("produce_arrow_string_view", False), lossless=lossless)
+    assert w.n_batches == len(exp)
+    for i, (rows, nodes, slices, body) in enumerate(exp):
+        bi = w.batch(i)
+        assert bi.rows == rows and bi.body_length == len(body)
+        got = bytes(stream[bi.body_offset: bi.body_offset + bi.body_length])
+        if got != body:
+            bad = next(k for k in range(len(body)) if got[k] != body[k])
+            which = max(j for j, (o, l) in enumerate(slices) if o <= bad)
+            raise AssertionError(f"batch {i}: body differs at byte {bad} (buffer #{which} {slices[which]})")
+    got = ipc.open_stream(pa.py_buffer(stream)).read_all()
+    types = {f.name: f.type for f in got.schema}
+    binary = pa.large_binary() if settings.get("arrow_large_buffer_size") else pa.binary()
+    assert types["uhuge"] == pa.opaque(pa.binary(16), "uhugeint", "DuckDB")
+    assert types["vint"] == pa.opaque(binary, "varint", "DuckDB")
+    if lossless:
+        assert types["huge"] == pa.opaque(pa.binary(16), "hugeint", "DuckDB")
+        assert types["id"] == pa.uuid() and types["flag"] == pa.bool8()
+        assert types["ttz"] == pa.opaque(pa.binary(8), "time_tz", "DuckDB")
+        assert types["bits"] == pa.opaque(binary, "bit", "DuckDB")
+        assert types["st"].field("id").type == pa.uuid()
+        assert types["st"].field("flag").type == pa.bool_()  # nested: ArrowBoolData's bits, labelled as what they are
+        assert types["l_id"].value_type == pa.uuid()
+        for name in ("huge", "uhuge", "id", "id_nn", "ttz", "bits", "vint"):
+            assert got.column(name).combine_chunks().storage.to_pylist() == \
+                table.column(name).combine_chunks().storage.to_pylist(), name
+        want = [None if v is None else int(v != 0) for v in table.column("flag").combine_chunks().storage.to_pylist()]
+        assert got.column("flag").combine_chunks().storage.to_pylist() == want
+        assert got.column("l_id").to_pylist() == table.column("l_id").to_pylist()
+    else:
+        assert types["huge"] == pa.decimal128(38, 0) and types["id"] == pa.string() and types["flag"] == pa.bool_()
+        assert types["ttz"] == pa.time64("us") and types["bits"] == binary
+        ids = table.column("id").to_pylist()
+        assert got.column("id").to_pylist() == [None if v is None else str(v) for v in ids]
+    # this repo's reader takes the stream back to the same vectors
+    r = b2a.ArrowIPCReader.open_buffers([stream])
+    assert r.num_rows == n
 
 
 @pytest.mark.parametrize("rgs", [122_880, 2048, 1000])

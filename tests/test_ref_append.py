@@ -26,9 +26,15 @@ def _bytes(buf, size):
     return ctypes.string_at(buf.address, size)
 
 
-def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path="") -> None:
+def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path="", depth=0) -> None:
     """Pre-order (length, null_count) + buffers of what the reference appender produced; `notes[i]` says which kind of
     buffer bufs[i] is and the validity of its rows (for the buffers whose NULL slots the appender leaves unwritten)."""
+    packed_bool8 = False
+    if isinstance(arr.type, pa.BaseExtensionType):  # the buffers are those of the storage array
+        # a NESTED arrow.bool8 of the reference carries ArrowBoolData's bit-packed buffer under its int8 label
+        # (arrow_appender.cpp:40-48 converts root columns only): read it as the bits it holds
+        packed_bool8 = arr.type.extension_name == "arrow.bool8" and depth > 0
+        arr = arr.storage
     t, n = arr.type, len(arr)
     assert arr.offset == 0
     b = arr.buffers()
@@ -40,7 +46,7 @@ def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path=
         bufs.append(_bytes(b[1], n))
         notes.append((path, "type_ids", None, 1))
         for i in range(t.num_fields):
-            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}")
+            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}", depth + 1)
         return
     nodes.append((n, arr.null_count))
     valid = np.asarray(arr.is_valid().to_numpy(zero_copy_only=False), bool) if n else np.zeros(0, bool)
@@ -48,21 +54,21 @@ def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path=
     notes.append((path, "validity", None, 0))
     if pa.types.is_struct(t):
         for i in range(t.num_fields):
-            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}")
+            ref_nodes_buffers(arr.field(i), nodes, bufs, notes, f"{path}.{t.field(i).name}", depth + 1)
     elif pa.types.is_list(t) or pa.types.is_large_list(t) or pa.types.is_map(t):
         w = 8 if pa.types.is_large_list(t) else 4
         bufs.append(_bytes(b[1], (n + 1) * w))
         notes.append((path, "offsets", None, w))
-        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]", depth + 1)
     elif pa.types.is_list_view(t) or pa.types.is_large_list_view(t):
         w = 8 if pa.types.is_large_list_view(t) else 4
         bufs.append(_bytes(b[1], n * w))
         notes.append((path, "view_offsets", None, w))
         bufs.append(_bytes(b[2], n * w))
         notes.append((path, "view_sizes", None, w))
-        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]", depth + 1)
     elif pa.types.is_fixed_size_list(t):
-        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]")
+        ref_nodes_buffers(arr.values, nodes, bufs, notes, path + "[]", depth + 1)
     elif pa.types.is_string_view(t):
         bufs.append(_bytes(b[1], n * 16))
         notes.append((path, "views", valid, 16))
@@ -78,7 +84,7 @@ def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path=
         last = int(np.frombuffer(bufs[-1], np.int64 if w == 8 else np.int32)[-1]) if n else 0
         bufs.append(_bytes(b[2], last))
         notes.append((path, "chars", None, 1))
-    elif pa.types.is_boolean(t):
+    elif pa.types.is_boolean(t) or packed_bool8:
         bufs.append(_bytes(b[1], (n + 7) // 8))
         notes.append((path, "bool", None, 0))
     else:
@@ -88,6 +94,9 @@ def ref_nodes_buffers(arr: pa.Array, nodes: list, bufs: list, notes: list, path=
 
 
 def _table(case):
+    if case == "lossless":
+        from writer_cases import lossless_table
+        return lossless_table(3000)
     if case == "scalar":
         return scalar_table(5000)
     if case == "nested":
@@ -117,9 +126,24 @@ def _same_buffer(rb: bytes, ob: bytes, note) -> tuple[bool, str]:
 @pytest.mark.parametrize("case,rgs", [("scalar", 2048), ("scalar", 5000), ("nested", 1000), ("nested", 3000),
                                       ("lineitem", 5000)])
 def test_appender_restatement_equals_reference(case, rgs, flags):
+    _check_against_reference(case, rgs, flags)
+
+
+@pytest.mark.parametrize("flags", [R.FLAG_LOSSLESS, R.FLAG_LOSSLESS | R.FLAG_LARGE, R.FLAG_LOSSLESS | R.FLAG_STRING_VIEW,
+                                   0])
+@pytest.mark.parametrize("rgs", [1000, 2048])  # ArrowBool8::DuckToArrow fills a 2 048-row Vector: one chunk at most
+def test_lossless_conversion_equals_reference(rgs, flags):
+    """SET arrow_lossless_conversion: arrow.bool8 / arrow.uuid / arrow.opaque{DuckDB, ...} storage buffers exactly as the
+    reference appender lays them out; with flags = 0 the same vectors take the lossy routes (36-character UUIDs,
+    time64[us], bit-packed booleans) and UHUGEINT / VARINT stay extension types."""
+    _check_against_reference("lossless", rgs, flags)
+
+
+def _check_against_reference(case, rgs, flags):
     table = _table(case)
     cols = table_vectors(table)
-    kw = dict(large=bool(flags & R.FLAG_LARGE), view=bool(flags & R.FLAG_LIST_VIEW), sview=bool(flags & R.FLAG_STRING_VIEW))
+    kw = dict(large=bool(flags & R.FLAG_LARGE), view=bool(flags & R.FLAG_LIST_VIEW), sview=bool(flags & R.FLAG_STRING_VIEW),
+              lossless=bool(flags & R.FLAG_LOSSLESS))
     row = 0
     loose = set()
     for n, nodes, slices, body in OW.serialize_batches(cols, table.num_rows, rgs, **kw):
@@ -142,6 +166,10 @@ def test_appender_restatement_equals_reference(case, rgs, flags):
     assert row == table.num_rows
     # only the columns whose NULL slots the reference leaves unwritten may fall back to the valid-row comparison
     allowed = {"dec4", "iv"}
+    if case == "lossless" and flags & R.FLAG_LOSSLESS:  # ArrowUUIDBlobConverter::SkipNulls (scalar_data.hpp:80-82)
+        allowed |= {"id", "st.id", "l_id[]"}
+    elif case == "lossless":  # ArrowTimeTzConverter::SkipNulls (:60-62)
+        allowed |= {"ttz"}
     assert loose <= allowed, f"NULL slots differ in {sorted(loose - allowed)}"
 
 

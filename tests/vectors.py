@@ -11,6 +11,7 @@ import numpy as np
 import pyarrow as pa
 
 VS = 2048
+STRING_TYPES = ("VARCHAR", "BLOB", "BIT", "VARINT", "JSON")  # string_t vectors
 
 
 class HostVector:
@@ -62,7 +63,7 @@ def _and_mask(hv: HostVector, mask: np.ndarray) -> None:
     if hv.type == "SQLNULL":
         return
     hv.validity = mask.copy() if hv.validity is None else (hv.validity & mask)
-    if hv.type in ("VARCHAR", "BLOB", "BIT") and hv.str_len is not None:
+    if hv.type in STRING_TYPES and hv.str_len is not None:
         hv.str_len = np.where(hv.validity, hv.str_len, 0)
     if hv.type == "STRUCT":
         for k in hv.children:
@@ -137,6 +138,34 @@ def from_arrow(arr: pa.Array, name: str = "") -> HostVector:
             for k in kids:
                 _and_mask(k, valid)
         return HostVector("STRUCT", n, None, valid, kids, name=name)
+    if isinstance(t, pa.BaseExtensionType):  # the extension types of arrow_type_extension.cpp:366-390
+        st = arr.storage
+        ext = t.extension_name
+        if ext == "arrow.bool8":  # ArrowBool8::ArrowToDuck: every row, NULL slots included
+            return HostVector("BOOLEAN", n, (_values(st, np.int8) != 0).astype(np.uint8), valid, name=name)
+        if ext == "arrow.uuid":  # big-endian bytes -> hugeint_t{lower, upper ^ sign}; NULL slots are not converted
+            raw = _values(st, np.dtype((np.void, 16))).view(np.uint8).reshape(n, 16)
+            be = raw.view(">u8").reshape(n, 2)
+            out = np.zeros((n, 2), np.uint64)
+            out[:, 0] = be[:, 1]
+            out[:, 1] = be[:, 0] ^ np.uint64(1 << 63)
+            if valid is not None:
+                out[~valid] = 0
+            return HostVector("UUID", n, out.view(np.uint8).reshape(-1), valid, name=name)
+        if ext == "arrow.json":
+            hv = from_arrow(st, name)
+            hv.type = "JSON"
+            return hv
+        if ext == "arrow.opaque" and t.vendor_name == "DuckDB":
+            kind = {"hugeint": "HUGEINT", "uhugeint": "UHUGEINT", "time_tz": "TIME_TZ", "bit": "BIT",
+                    "varint": "VARINT"}[t.type_name]
+            if kind in ("BIT", "VARINT"):
+                hv = from_arrow(st, name)
+                hv.type = kind
+                return hv
+            w = st.type.byte_width
+            return HostVector(kind, n, _values(st, np.dtype((np.void, w))).view(np.uint8).reshape(-1), valid, name=name)
+        raise NotImplementedError(str(t))
     if str(t) == "month_day_nano_interval":
         raw = _values(arr, np.dtype([("m", np.int32), ("d", np.int32), ("ns", np.int64)]))
         out = np.zeros(n, np.dtype([("m", np.int32), ("d", np.int32), ("us", np.int64)]))
@@ -189,7 +218,7 @@ def to_device(hv: HostVector, device: int = 0):
     dev = f"cuda:{device}"
     keep = []
     data = None
-    if hv.type in ("VARCHAR", "BLOB", "BIT"):
+    if hv.type in STRING_TYPES:
         heap = torch.from_numpy(np.concatenate([hv.heap, np.zeros(16, np.uint8)])).to(dev)
         keep.append(heap)
         rec = make_string_t(hv.str_start, hv.str_len, hv.heap, heap.data_ptr())

@@ -91,6 +91,75 @@ def nested_table(n=3000, seed=2) -> pa.Table:
     return pa.table(cols)
 
 
+def lossless_table(n=4000, seed=12):
+    """One column of every type arrow_lossless_conversion changes (arrow_converter.cpp:130-279) plus the two that are
+    extension types whatever the setting (UHUGEINT, VARINT; :387-393), as the Arrow extension arrays the reference scans
+    into BOOLEAN / UUID / HUGEINT / UHUGEINT / TIME_TZ / BIT / VARINT vectors; a struct and a list carry them nested."""
+    rng = np.random.default_rng(seed)
+
+    def fixed(width, null_p=0.2):
+        raw = rng.integers(0, 256, (n, width)).astype(np.uint8)
+        raw[0], raw[1 % n] = 0, 255
+        mask = rng.random(n) < null_p
+        st = pa.Array.from_buffers(pa.binary(width), n, [None, pa.py_buffer(raw.tobytes())])
+        return st, mask
+
+    def with_nulls(st, mask):
+        valid = np.packbits(~mask, bitorder="little").tobytes()
+        bufs = st.buffers()
+        return pa.Array.from_buffers(st.type, len(st), [pa.py_buffer(valid)] + bufs[1:], int(mask.sum()))
+
+    def opaque(st, type_name):
+        return pa.ExtensionArray.from_storage(pa.opaque(st.type, type_name, "DuckDB"), st)
+
+    cols = {}
+    st, m = fixed(16)
+    cols["huge"] = opaque(with_nulls(st, m), "hugeint")
+    st, m = fixed(16)
+    cols["uhuge"] = opaque(with_nulls(st, m), "uhugeint")
+    st, m = fixed(16)
+    cols["id"] = pa.ExtensionArray.from_storage(pa.uuid(), with_nulls(st, m))
+    st, _ = fixed(16)
+    cols["id_nn"] = pa.ExtensionArray.from_storage(pa.uuid(), st)
+    micros = rng.integers(0, 86_400_000_000, n).astype(np.uint64)
+    offs = rng.integers(0, 2 * 57599, n).astype(np.uint64)  # dtime_tz_t: micros << 24 | (MAX_OFFSET - offset)
+    bits = ((micros << np.uint64(24)) | offs).astype("<u8")
+    st = pa.Array.from_buffers(pa.binary(8), n, [None, pa.py_buffer(bits.tobytes())])
+    cols["ttz"] = opaque(with_nulls(st, rng.random(n) < 0.2), "time_tz")
+    flags = rng.integers(0, 3, n).astype(np.int8)  # bool8: any non-zero byte is true
+    cols["flag"] = pa.ExtensionArray.from_storage(pa.bool8(), with_nulls(pa.array(flags, pa.int8()), rng.random(n) < 0.2))
+    # BIT: first byte = number of padding bits (0..7), padding bits set; VARINT: 3-byte header + magnitude
+    bit_vals = []
+    for _ in range(n):
+        nb = int(rng.integers(1, 20))
+        pad = int(rng.integers(0, 8))
+        body = bytearray(rng.integers(0, 256, nb).astype(np.uint8).tobytes())
+        body[0] |= (0xFF << (8 - pad)) & 0xFF if pad else 0
+        bit_vals.append(bytes([pad]) + bytes(body))
+    cols["bits"] = opaque(pa.array(_nullify(rng, bit_vals), pa.binary()), "bit")
+    var_vals = []
+    for _ in range(n):
+        nb = int(rng.integers(1, 24))
+        mag = bytearray(rng.integers(0, 256, nb).astype(np.uint8).tobytes())
+        if nb > 1 and mag[0] == 0:
+            mag[0] = 1
+        head = (0x800000 | nb).to_bytes(3, "big")  # positive: header = byte count with the top bit set
+        var_vals.append(head + bytes(mag))
+    cols["vint"] = opaque(pa.array(_nullify(rng, var_vals), pa.binary()), "varint")
+    cols["plain"] = pa.array(_nullify(rng, rng.integers(-1000, 1000, n).tolist()), pa.int32())
+    cols["s"] = pa.array(_nullify(rng, ["v%d" % i if i % 3 else "a string well past twelve bytes %d" % i
+                                         for i in range(n)]), pa.string())
+    nested = pa.StructArray.from_arrays([cols["id"], cols["flag"], cols["bits"]], names=["id", "flag", "bits"])
+    cols["st"] = nested
+    lens = rng.integers(0, 4, n)
+    lo = np.zeros(n + 1, np.int32)
+    np.cumsum(lens, out=lo[1:])
+    take = pa.array(rng.integers(0, n, int(lo[-1])), pa.int64())
+    cols["l_id"] = pa.ListArray.from_arrays(pa.array(lo, pa.int32()), cols["id"].take(take))
+    cols["l_flag"] = pa.ListArray.from_arrays(pa.array(lo, pa.int32()), cols["flag"].take(take))
+    return pa.table(cols)
+
+
 def rare_columns(n=5000, seed=4):
     """The writable types Arrow has no 1:1 array for (so they cannot come from vectors.from_arrow): UUID (written as its
     36-character string), TIME_TZ (time64[us], offset dropped), BIT (the internal bytes as binary) and sparse UNIONs
