@@ -19,7 +19,7 @@ STATUS = {0: "OK", 1: "InvalidInputException", 2: "IOException", 3: "NotImplemen
 TYPE_NAMES = ["INVALID", "SQLNULL", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT",
               "UINTEGER", "UBIGINT", "HUGEINT", "UHUGEINT", "FLOAT", "DOUBLE", "DECIMAL", "VARCHAR", "BLOB", "DATE",
               "TIME", "TIMESTAMP", "TIMESTAMP_S", "TIMESTAMP_MS", "TIMESTAMP_NS", "TIMESTAMP WITH TIME ZONE",
-              "INTERVAL", "UUID", "LIST", "STRUCT", "MAP", "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON"]
+              "INTERVAL", "UUID", "LIST", "STRUCT", "MAP", "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON", "ENUM"]
 T = {n: i for i, n in enumerate(TYPE_NAMES)}
 
 OP_NAMES = ["NONE", "COPY", "BOOL", "STRING32", "STRING64", "STRING_VIEW", "BLOB_FIXED", "LIST32", "LIST64",
@@ -185,6 +185,7 @@ def _load() -> C.CDLL:
         "b2a_writer_batch": (i32, [vp, u64, P(BatchInfo)]),
         "b2a_writer_gpu_launches": (u64, [vp]),
         "b2a_writer_schema_message": (i32, [vp, P(vp), P(u64)]),
+        "b2a_writer_preamble": (i32, [vp, P(u64)]),
     }
     for name, (res, args) in sig.items():
         if not hasattr(lib, name):

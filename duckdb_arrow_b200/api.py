@@ -795,6 +795,13 @@ class ArrowWriter:
         check(lib.b2a_writer_schema_message(self._h, C.byref(ptr), C.byref(size)))
         return C.string_at(ptr, size.value)
 
+    @property
+    def preamble_bytes(self) -> int:
+        """schema message + DictionaryBatch messages (one per ENUM field): the stream before its first record batch"""
+        n = C.c_uint64()
+        check(lib.b2a_writer_preamble(self._h, C.byref(n)))
+        return int(n.value)
+
     def batch(self, i: int) -> _lib.BatchInfo:
         bi = _lib.BatchInfo()
         check(lib.b2a_writer_batch(self._h, i, C.byref(bi)))
@@ -852,8 +859,7 @@ def to_arrow_ipc(columns: list[DeviceVector], device: int = 0,
                     produce_arrow_string_view, arrow_lossless_conversion)
     stream = w.write()
     out = []
-    first = w.batch(0).meta_offset if w.n_batches else w.stream_bytes - 8
-    out.append((bytes(stream[:first]), True))
+    out.append((bytes(stream[:w.preamble_bytes]), True))  # schema (+ the dictionaries of ENUM columns)
     for i in range(w.n_batches):
         bi = w.batch(i)
         out.append((bytes(stream[bi.meta_offset: bi.body_offset + bi.body_length]), False))

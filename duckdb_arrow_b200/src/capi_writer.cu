@@ -296,11 +296,13 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 			n_tiles_total += WritePlan::ScanTiles(p.nodes[static_cast<size_t>(ni)].rows);
 		}
 		void *chunk = nullptr;
-		int rc = DeviceAlloc(w, (n_tiles_total + pending.size()) * 8, &chunk, st);
+		int rc = DeviceAlloc(w, (n_tiles_total + pending.size() + 1) * 8, &chunk, st);
 		if (rc != B2A_OK) {
 			return rc;
 		}
 		uint64_t *base = static_cast<uint64_t *>(chunk);
+		uint64_t *d_heap_bytes = base + n_tiles_total + pending.size();
+		W_CUDA(cudaMemsetAsync(d_heap_bytes, 0, 8, st));
 		uint64_t cursor = 0;
 		for (size_t j = 0; j < pending.size(); j++) {
 			WNode &n = p.nodes[static_cast<size_t>(pending[j])];
@@ -322,14 +324,16 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		l.d_tile_task = w->d_tile_task;
 		l.n_tasks = static_cast<uint32_t>(tasks.size());
 		l.n_tiles = static_cast<uint32_t>(tiles.size());
+		l.d_heap_bytes = d_heap_bytes;
 		int e = LaunchEncMeasure(l, st);
 		if (e != 0) {
 			return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
 		}
 		w->launches += 2;
-		std::vector<uint64_t> totals(pending.size());
-		W_CUDA(cudaMemcpyAsync(totals.data(), base + n_tiles_total, pending.size() * 8, cudaMemcpyDeviceToHost, st));
+		std::vector<uint64_t> totals(pending.size() + 1);
+		W_CUDA(cudaMemcpyAsync(totals.data(), base + n_tiles_total, (pending.size() + 1) * 8, cudaMemcpyDeviceToHost, st));
 		W_CUDA(cudaStreamSynchronize(st));
+		p.heap_bytes += totals[pending.size()];
 		trace.Mark("measure kernels + totals");
 		// ---- lists: child selection vectors (ArrowListData::AppendOffsets child_sel), children become new nodes
 		std::vector<b2a_enc_task> xtasks;
@@ -507,7 +511,9 @@ int b2a_writer_headers(b2a_writer *w, void *h_stream) {
 	const WritePlan &p = w->plan;
 	uint8_t *h = static_cast<uint8_t *>(h_stream);
 	std::memcpy(h, p.schema_message.data(), p.schema_message.size());
-	for (auto &b : p.batches) {
+	for (size_t bi = 0; bi < p.dict_batches.size() + p.batches.size(); bi++) {
+		const bool is_dict = bi < p.dict_batches.size();
+		const WBatch &b = is_dict ? p.dict_batches[bi] : p.batches[bi - p.dict_batches.size()];
 		std::vector<NodeSlice> nodes;
 		std::vector<BufferSlice> buffers;
 		for (int ni : b.preorder) {
@@ -518,8 +524,10 @@ int b2a_writer_headers(b2a_writer *w, void *h_stream) {
 				buffers.push_back(n.buf[k]);
 			}
 		}
-		std::vector<uint8_t> msg = EncodeRecordBatchMessage(b.rows, nodes, buffers, b.body_length, p.n_variadic);
-		if (msg.size() != p.batch_header_bytes) {
+		std::vector<uint8_t> msg = is_dict
+		                               ? EncodeDictionaryBatchMessage(b.dictionary_id, b.rows, nodes, buffers, b.body_length)
+		                               : EncodeRecordBatchMessage(b.rows, nodes, buffers, b.body_length, p.n_variadic);
+		if (msg.size() != (is_dict ? p.dict_header_bytes : p.batch_header_bytes)) {
 			return SetLastError(B2A_EINTERNAL, "writer: record batch header size changed after layout");
 		}
 		std::memcpy(h + b.meta_offset, msg.data(), msg.size());
@@ -541,6 +549,17 @@ int b2a_writer_batch(b2a_writer *w, uint64_t i, b2a_batch_info *out) {
 	out->body_offset = p.batches[i].body_offset;
 	out->body_length = p.batches[i].body_length;
 	out->buffer_bytes = p.batches[i].body_length;
+	return B2A_OK;
+}
+
+int b2a_writer_preamble(b2a_writer *w, uint64_t *bytes) {
+	if (!w || !bytes) {
+		return SetLastError(B2A_EINVAL, "writer: null argument");
+	}
+	if (!w->plan.laid_out) {
+		return SetLastError(B2A_EINVAL, "writer: call b2a_writer_measure first");
+	}
+	*bytes = w->plan.preamble_bytes;
 	return B2A_OK;
 }
 

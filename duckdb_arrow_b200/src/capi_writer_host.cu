@@ -112,6 +112,10 @@ int FixedWidth(const b2a_vector &v) {
 		return 16;
 	case B2A_T_DECIMAL:
 		return v.decimal_width <= 4 ? 2 : v.decimal_width <= 9 ? 4 : v.decimal_width <= 18 ? 8 : 16;
+	case B2A_T_ENUM: { // codes sized by the dictionary (EnumTypeInfo::DictType)
+		const uint64_t n = v.n_children == 1 && v.children ? v.children[0].rows : 0;
+		return n <= 0xFF ? 1 : n <= 0xFFFF ? 2 : 4;
+	}
 	default:
 		return 0; // STRUCT / ARRAY / SQLNULL: no data of their own
 	}

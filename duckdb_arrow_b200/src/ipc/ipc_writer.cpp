@@ -121,6 +121,9 @@ TypeOut BuildType(fb::Builder &b, const WriteField &f, uint32_t tz_string) {
 	case B2A_T_UHUGEINT:
 		fixed_binary(16);
 		break;
+	case B2A_T_ENUM: // a dictionary-encoded field carries the VALUE type; the index type sits in Field.dictionary
+		empty(ArrowTypeTag::Utf8);
+		break;
 	case B2A_T_VARCHAR:
 	case B2A_T_JSON:
 		empty(f.string_view ? ArrowTypeTag::Utf8View : f.large_offsets ? ArrowTypeTag::LargeUtf8 : ArrowTypeTag::Utf8);
@@ -269,12 +272,26 @@ uint32_t BuildField(fb::Builder &b, const WriteField &f) {
 		}
 		custom = b.create_offset_vector(kvs);
 	}
+	uint32_t dict = 0;
+	if (f.dictionary_id >= 0) { // DictionaryEncoding{id, indexType: Int, isOrdered = false}
+		b.start_table();
+		b.add_scalar<int32_t>(0, f.index_bits, 0);
+		b.add_scalar<uint8_t>(1, 0, 0); // unsigned: "C" / "S" / "I" (arrow_converter.cpp:364-376)
+		uint32_t index_type = b.end_table();
+		b.start_table();
+		b.add_scalar_force<int64_t>(0, f.dictionary_id);
+		b.add_offset(1, index_type);
+		dict = b.end_table();
+	}
 	uint32_t name = b.create_string(f.name);
 	b.start_table();
 	b.add_offset(0, name);
 	b.add_scalar<uint8_t>(1, f.nullable ? 1 : 0, 0);
 	b.add_scalar<uint8_t>(2, static_cast<uint8_t>(ty.tag), 0);
 	b.add_offset(3, ty.table);
+	if (dict) {
+		b.add_offset(4, dict);
+	}
 	b.add_offset(5, kids_vec);
 	if (custom) {
 		b.add_offset(6, custom);
@@ -378,6 +395,12 @@ void ResolveArrowFormat(WriteField &f) {
 		break;
 	case B2A_T_UHUGEINT:
 		f.format = "w:16";
+		break;
+	case B2A_T_ENUM:
+		if (f.dictionary_id < 0 || (f.index_bits != 8 && f.index_bits != 16 && f.index_bits != 32)) {
+			throw Error(B2A_EINVAL, "writer: ENUM field '" + f.name + "' without a dictionary");
+		}
+		f.format = f.index_bits == 8 ? "C" : f.index_bits == 16 ? "S" : "I";
 		break;
 	case B2A_T_VARCHAR:
 	case B2A_T_JSON:
@@ -509,6 +532,29 @@ std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<N
 	}
 	uint32_t rb = b.end_table();
 	return FinishMessage(b, 3 /* MessageHeader::RecordBatch */, rb, static_cast<int64_t>(body_length));
+}
+
+std::vector<uint8_t> EncodeDictionaryBatchMessage(int64_t id, uint64_t rows, const std::vector<NodeSlice> &nodes,
+                                                  const std::vector<BufferSlice> &buffers, uint64_t body_length) {
+	fb::Builder b;
+	uint32_t buf_vec = b.create_struct_vector(buffers.data(), buffers.size(), 16, 8);
+	uint32_t node_vec = b.create_struct_vector(nodes.data(), nodes.size(), 16, 8);
+	b.start_table();
+	b.add_scalar_force<int64_t>(0, static_cast<int64_t>(rows));
+	b.add_offset(1, node_vec);
+	b.add_offset(2, buf_vec);
+	uint32_t rb = b.end_table();
+	b.start_table();
+	b.add_scalar_force<int64_t>(0, id);
+	b.add_offset(1, rb);
+	uint32_t db = b.end_table();
+	return FinishMessage(b, 2 /* MessageHeader::DictionaryBatch */, db, static_cast<int64_t>(body_length));
+}
+
+size_t DictionaryBatchMessageSize(size_t n_nodes, size_t n_buffers) {
+	std::vector<NodeSlice> nodes(n_nodes, NodeSlice {1, 1});
+	std::vector<BufferSlice> buffers(n_buffers, BufferSlice {8, 8});
+	return EncodeDictionaryBatchMessage(1, 1, nodes, buffers, 8).size();
 }
 
 size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers, size_t n_variadic) {

@@ -26,6 +26,8 @@ struct WriteField {
 	bool list_view = false;     // arrow_output_list_view: "+vl" / "+vL"
 	bool large_offsets = false; // arrow_large_buffer_size: "U" / "Z" / "+L" (set by the write planner)
 	bool lossless = false;      // arrow_lossless_conversion: extension types (set by the write planner)
+	int64_t dictionary_id = -1; // ENUM: id of its DictionaryBatch (set by the write planner)
+	int index_bits = 0;         // ENUM: 8 / 16 / 32, unsigned ("C" / "S" / "I")
 	std::vector<WriteField> children;
 	std::string format; // the C-data-interface format string the reference would set (for tests / diagnostics)
 };
@@ -41,6 +43,12 @@ std::vector<uint8_t> EncodeRecordBatchMessage(uint64_t rows, const std::vector<N
                                               size_t n_variadic = 0);
 // size of a RecordBatch message header with the given node / buffer counts (independent of the values)
 size_t RecordBatchMessageSize(size_t n_nodes, size_t n_buffers, size_t n_variadic = 0);
+// DictionaryBatch{id, data: RecordBatch, isDelta = false}: the values of one dictionary (here always one utf8 column:
+// validity, int32 offsets, characters); the reference's appender builds it in ArrowEnumData::Initialize
+// (appender/enum_data.hpp:67-75), the message form is Arrow's (Message.header_type = DictionaryBatch)
+std::vector<uint8_t> EncodeDictionaryBatchMessage(int64_t id, uint64_t rows, const std::vector<NodeSlice> &nodes,
+                                                  const std::vector<BufferSlice> &buffers, uint64_t body_length);
+size_t DictionaryBatchMessageSize(size_t n_nodes, size_t n_buffers);
 // ArrowStreamWriter::Finalize: FFFFFFFF 00000000
 std::vector<uint8_t> EncodeEndOfStream();
 

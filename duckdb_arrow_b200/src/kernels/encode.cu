@@ -124,8 +124,11 @@ __device__ __forceinline__ uint64_t entry_len(const b2a_enc_task &t, uint64_t i,
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads)
     b2a_enc_measure_kernel(const b2a_enc_task *__restrict__ tasks, const uint32_t *__restrict__ tile_task,
-                           uint32_t n_tiles) {
+                           uint32_t n_tiles, unsigned long long *__restrict__ heap_bytes) {
 	__shared__ uint64_t warp_sums[kThreads / 32];
+	// bytes pass 2 will have to fetch from the string heap (strings longer than the 12 inlined bytes): part of the
+	// algorithmic traffic of the encode launch; one atomic per CTA
+	uint64_t heap_acc = 0;
 	for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
 		const b2a_enc_task &t = tasks[__ldg(tile_task + tile)];
 		const uint32_t k = tile - t.tile0;
@@ -137,7 +140,11 @@ __global__ void __launch_bounds__(kThreads)
 			if (i < t.rows) {
 				uint4 e;
 				bool valid;
-				sum += entry_len(t, i, e, valid);
+				const uint64_t len = entry_len(t, i, e, valid);
+				sum += len;
+				if (len > 12 && (t.op == B2A_ENC_STRING32 || t.op == B2A_ENC_STRING64 || t.op == B2A_ENC_STRINGVIEW)) {
+					heap_acc += len;
+				}
 			}
 		}
 		for (int o = 16; o > 0; o >>= 1) {
@@ -155,6 +162,14 @@ __global__ void __launch_bounds__(kThreads)
 			reinterpret_cast<uint64_t *>(t.scratch)[k] = s;
 		}
 		__syncthreads();
+	}
+	if (heap_bytes) {
+		for (int o = 16; o > 0; o >>= 1) {
+			heap_acc += __shfl_xor_sync(0xffffffffu, heap_acc, o);
+		}
+		if ((threadIdx.x & 31) == 0 && heap_acc) {
+			atomicAdd(heap_bytes, static_cast<unsigned long long>(heap_acc));
+		}
 	}
 }
 
@@ -412,15 +427,17 @@ __device__ __forceinline__ void enc_uuid_blob(const b2a_enc_task &t, uint8_t *__
                                               uint64_t nrows) {
 	for (uint64_t i = row0 + threadIdx.x; i < row0 + nrows; i += kThreads) {
 		const uint64_t sr = map_row(t, i);
-		uint4 o = make_uint4(0, 0, 0, 0);
+		uint2 hi = make_uint2(0, 0), lo = make_uint2(0, 0);
 		if (src_valid(t, sr)) {
 			const uint4 e = __ldg(reinterpret_cast<const uint4 *>(t.src) + sr);
-			o.x = __byte_perm(e.w ^ 0x80000000u, 0, 0x0123);
-			o.y = __byte_perm(e.z, 0, 0x0123);
-			o.z = __byte_perm(e.y, 0, 0x0123);
-			o.w = __byte_perm(e.x, 0, 0x0123);
+			hi.x = __byte_perm(e.w ^ 0x80000000u, 0, 0x0123);
+			hi.y = __byte_perm(e.z, 0, 0x0123);
+			lo.x = __byte_perm(e.y, 0, 0x0123);
+			lo.y = __byte_perm(e.x, 0, 0x0123);
 		}
-		reinterpret_cast<uint4 *>(stream + t.dst)[i] = o;
+		uint2 *out = reinterpret_cast<uint2 *>(stream + t.dst) + 2 * i; // body buffers are 8-byte aligned, not 16
+		out[0] = hi;
+		out[1] = lo;
 	}
 }
 
@@ -1707,7 +1724,8 @@ int LaunchEncMeasure(const EncodeLaunch &l, void *stream) {
 	if (l.n_tiles) {
 		uint32_t grid = static_cast<uint32_t>(l.sm_count) * 8;
 		grid = grid > l.n_tiles ? l.n_tiles : grid;
-		b2a_enc_measure_kernel<<<grid, kThreads, 0, st>>>(l.d_tasks, l.d_tile_task, l.n_tiles);
+		b2a_enc_measure_kernel<<<grid, kThreads, 0, st>>>(l.d_tasks, l.d_tile_task, l.n_tiles,
+		                                                  reinterpret_cast<unsigned long long *>(l.d_heap_bytes));
 	}
 	if (l.n_tasks) {
 		uint32_t grid = l.n_tasks < 65535u ? l.n_tasks : 65535u;

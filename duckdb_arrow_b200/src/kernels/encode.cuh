@@ -14,6 +14,7 @@ struct EncodeLaunch {
 	uint32_t n_tiles = 0;
 	uint8_t *stream_out = nullptr;  // device image of the IPC stream being produced
 	uint32_t *d_err = nullptr;
+	uint64_t *d_heap_bytes = nullptr; // measure: += bytes of the strings longer than 12 (what pass 2 reads from the heap)
 	int sm_count = 148;
 	bool full = false; // some task needs an op of the full instantiation (B2A_ENC_OP_IS_RARE)
 };

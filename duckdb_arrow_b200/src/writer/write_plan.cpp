@@ -114,6 +114,21 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	case B2A_T_HUGEINT:
 		fixed(16);
 		break;
+	case B2A_T_ENUM: { // ArrowEnumData<int8_t / int16_t / int32_t>, arrow_appender.cpp:253-268: the codes are copied as they are
+		if (v.n_children != 1 || !v.children || v.children[0].type_id != B2A_T_VARCHAR) {
+			throw Error(B2A_EINVAL, "writer: ENUM '" + wf.name + "' needs one VARCHAR child (its dictionary values)");
+		}
+		const uint64_t n_values = v.children[0].rows;
+		if (n_values > 0xFFFFFFFFull) {
+			throw Error(B2A_EINVAL, "writer: ENUM dictionary too large");
+		}
+		const int width = n_values <= 0xFF ? 1 : n_values <= 0xFFFF ? 2 : 4; // EnumTypeInfo::DictType
+		fixed(width);
+		wf.index_bits = width * 8;
+		wf.dictionary_id = static_cast<int64_t>(dict_vecs.size());
+		dict_vecs.push_back(-1); // the id is taken in field pre-order, before any ENUM nested deeper could take it
+		break;
+	}
 	case B2A_T_UHUGEINT: // no switch case in SetArrowFormat: always the registered extension (arrow_converter.cpp:387-393)
 		fixed(16);
 		break;
@@ -179,6 +194,19 @@ int WritePlan::AddVec(const b2a_vector &v, WriteField &wf, int depth) {
 	if (v.n_children < 0 || (v.n_children > 0 && !v.children)) {
 		throw Error(B2A_EINVAL, "writer: bad children of '" + wf.name + "'");
 	}
+	if (v.type_id == B2A_T_ENUM) {
+		// the dictionary: a utf8 array with int32 offsets whatever the settings (EnumAppendVector, enum_data.hpp:34-65,
+		// child format "u", arrow_converter.cpp:384); not a child of the field
+		const bool sv = string_view, lo = large_offsets, ll = lossless;
+		string_view = large_offsets = lossless = false;
+		WriteField values;
+		const int dv = AddVec(v.children[0], values, depth + 1);
+		string_view = sv;
+		large_offsets = lo;
+		lossless = ll;
+		dict_vecs[static_cast<size_t>(wf.dictionary_id)] = dv;
+		return idx;
+	}
 	wf.children.resize(static_cast<size_t>(v.n_children));
 	for (int c = 0; c < v.n_children; c++) {
 		if (v.type_id == B2A_T_UNION) {
@@ -239,6 +267,13 @@ void WritePlan::Build(const b2a_vector *columns, uint32_t n_columns, uint64_t ro
 		ResolveArrowFormat(fields[c]);
 	}
 	schema_message = EncodeSchemaMessage(fields, kv_metadata);
+	for (size_t d = 0; d < dict_vecs.size(); d++) {
+		WBatch b;
+		b.dictionary_id = static_cast<int64_t>(d);
+		b.rows = vecs[static_cast<size_t>(dict_vecs[d])].rows;
+		b.top.push_back(AddNode(dict_vecs[d], b.rows, 0, 0));
+		dict_batches.push_back(b);
+	}
 	for (uint64_t r0 = 0; r0 < rows; r0 += row_group_size) {
 		WBatch b;
 		b.row0 = r0;
@@ -305,8 +340,15 @@ void WritePlan::Layout() {
 	uint64_t cursor = schema_message.size();
 	body_bytes = 0;
 	algorithmic_in = algorithmic_out = 0;
-	for (size_t bi = 0; bi < batches.size(); bi++) {
-		WBatch &b = batches[bi];
+	dict_header_bytes = dict_batches.empty() ? 0 : DictionaryBatchMessageSize(1, 3);
+	const size_t n_dicts = dict_batches.size();
+	for (size_t bi_all = 0; bi_all < n_dicts + batches.size(); bi_all++) {
+		const bool is_dict = bi_all < n_dicts;
+		const size_t bi = is_dict ? bi_all : bi_all - n_dicts;
+		WBatch &b = is_dict ? dict_batches[bi] : batches[bi];
+		if (!is_dict && bi == 0) {
+			preamble_bytes = cursor;
+		}
 		b.preorder.clear();
 		for (int t : b.top) {
 			Preorder(t, b.preorder);
@@ -362,7 +404,7 @@ void WritePlan::Layout() {
 				off += Align8(len);
 			}
 		}
-		if (bi == 0) {
+		if (!is_dict && bi == 0) {
 			n_nodes = b.preorder.size();
 			n_buffers = nb;
 			n_variadic = 0;
@@ -372,11 +414,16 @@ void WritePlan::Layout() {
 			batch_header_bytes = RecordBatchMessageSize(n_nodes, n_buffers, n_variadic);
 		}
 		b.meta_offset = cursor;
-		b.body_offset = cursor + batch_header_bytes;
+		b.body_offset = cursor + (is_dict ? dict_header_bytes : batch_header_bytes);
 		b.body_length = off;
 		cursor = b.body_offset + off;
 		body_bytes += off;
 	}
+	if (batches.empty()) {
+		preamble_bytes = cursor;
+	}
+	// the vectors' own bytes + what the string appenders fetch from the heap (a non-inlined string_t holds a pointer)
+	algorithmic_in += heap_bytes;
 	algorithmic_out = body_bytes;
 	stream_bytes = cursor + 8; // end-of-stream marker
 	laid_out = true;
@@ -420,7 +467,8 @@ void WritePlan::ScanTasks(const std::vector<int> &node_ids, std::vector<b2a_enc_
 }
 
 void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const {
-	for (auto &b : batches) {
+	for (size_t bi = 0; bi < dict_batches.size() + batches.size(); bi++) {
+		const WBatch &b = bi < dict_batches.size() ? dict_batches[bi] : batches[bi - dict_batches.size()];
 		for (int ni : b.preorder) {
 			const WNode &n = nodes[static_cast<size_t>(ni)];
 			const WVec &v = vecs[static_cast<size_t>(n.vec)];

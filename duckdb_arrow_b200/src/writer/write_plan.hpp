@@ -54,6 +54,7 @@ struct WNode {
 struct WBatch {
 	uint64_t rows = 0;
 	uint64_t row0 = 0;
+	int64_t dictionary_id = -1; // >= 0: a DictionaryBatch (one utf8 column: the values of that ENUM dictionary)
 	std::vector<int> top; // node index per column
 	uint64_t meta_offset = 0, body_offset = 0, body_length = 0;
 	std::vector<int> preorder; // nodes in RecordBatch.nodes order
@@ -66,6 +67,12 @@ struct WritePlan {
 	std::vector<int> top_vecs;
 	std::vector<WNode> nodes;
 	std::vector<WBatch> batches;
+	// one per ENUM field, in field pre-order = dictionary id order; laid out between the schema message and the first
+	// record batch (a dictionary must precede the first batch that refers to it)
+	std::vector<WBatch> dict_batches;
+	std::vector<int> dict_vecs; // dictionary id -> index of its VARCHAR vector in `vecs`
+	size_t dict_header_bytes = 0;
+	uint64_t preamble_bytes = 0; // schema message + dictionary batches
 	uint64_t row_group_size = 122880;
 	bool large_offsets = false; // B2A_WRITE_LARGE_OFFSETS
 	bool list_view = false;     // B2A_WRITE_LIST_VIEW
@@ -78,6 +85,7 @@ struct WritePlan {
 	size_t batch_header_bytes = 0;
 	uint64_t stream_bytes = 0, body_bytes = 0;
 	uint64_t algorithmic_in = 0, algorithmic_out = 0;
+	uint64_t heap_bytes = 0; // characters of the strings longer than 12 bytes (summed by the measure kernel)
 	bool laid_out = false;
 
 	// builds vecs / fields from the C-ABI description and creates the nodes that need no device-side measurement

@@ -86,7 +86,12 @@ typedef enum b2a_type_id {
 	B2A_T_TIME_TZ, /* arrow.opaque {DuckDB, time_tz} over w:8: dtime_tz_t bits, copied */
 	B2A_T_BIT,     /* arrow.opaque {DuckDB, bit} over z / Z: string_t like BLOB */
 	B2A_T_VARINT,  /* arrow.opaque {DuckDB, varint} over z / Z */
-	B2A_T_JSON     /* arrow.json over u / U / vu: VARCHAR with the JSON alias */
+	B2A_T_JSON,    /* arrow.json over u / U / vu: VARCHAR with the JSON alias */
+	B2A_T_ENUM     /* writer only (the scan returns dictionary-encoded columns as VARCHAR, like the reference): data = the
+	                  codes, uint8 / uint16 / uint32 by dictionary size (EnumTypeInfo::DictType: <= 255, <= 65 535, else);
+	                  children[0] = the VARCHAR vector of the dictionary values in insert order (EnumType::GetValuesInsertOrder).
+	                  Written as a dictionary-encoded utf8 field "C" / "S" / "I" + one DictionaryBatch per stream
+	                  (arrow_converter.cpp:362-386, appender/enum_data.hpp:24-87) */
 } b2a_type_id;
 
 /* Conversion op of one field = which kernel body runs for its value buffer(s). */
@@ -403,6 +408,9 @@ void b2a_writer_destroy(b2a_writer *w);
 /* Pass 1: data-dependent sizes (string bytes, list child counts) are reduced on the device, read back, and the
  * stream is laid out (message offsets, per-buffer body offsets).  Synchronises `cuda_stream`. */
 int b2a_writer_measure(b2a_writer *w, void *cuda_stream);
+/* algorithmic_bytes = what the encode launch must read and write: the bytes of the input vectors (validity words, values,
+ * string_t / list_entry_t records), the characters of the strings longer than 12 bytes (a non-inlined string_t holds a
+ * pointer into the heap; summed by pass 1) and every byte of the produced bodies. */
 int b2a_writer_sizes(b2a_writer *w, uint64_t *stream_bytes, uint64_t *n_batches, uint64_t *body_bytes,
                      uint64_t *algorithmic_bytes);
 /* Pass 2: every buffer of every record batch is written at its final stream offset inside d_stream
@@ -421,6 +429,11 @@ uint64_t b2a_writer_gpu_launches(b2a_writer *w);
  * types = ArrowConverter::ToArrowSchema, duckdb/src/common/arrow/arrow_converter.cpp:115-432).  Host only: available
  * right after b2a_writer_create, also without a device.  The pointer stays valid until b2a_writer_destroy. */
 int b2a_writer_schema_message(b2a_writer *w, const void **data, uint64_t *size);
+/* Bytes of the stream before its first record batch message: the Schema message followed by one DictionaryBatch message
+ * (header + body) per ENUM field, in dictionary-id order.  A caller that cuts record-batch messages out of several
+ * streams (COPY writes one row group per call, to_arrow_ipc one blob per message) sends [0, preamble) of the first
+ * stream once.  Valid after b2a_writer_measure; the dictionary bodies are there after b2a_writer_encode + the D2H copy. */
+int b2a_writer_preamble(b2a_writer *w, uint64_t *bytes);
 
 /* ---------------- host-facing writer: HOST vectors in, HOST stream bytes out ----------------
  * What COPY ... (FORMAT ARROWS) and to_arrow_ipc hold is host memory: the flat vectors of one row group

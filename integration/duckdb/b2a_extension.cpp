@@ -307,8 +307,8 @@ static int32_t B2ATypeId(const LogicalType &t) {
 	case LogicalTypeId::BIT: return B2A_T_BIT;
 	case LogicalTypeId::UHUGEINT: return B2A_T_UHUGEINT;
 	case LogicalTypeId::VARINT: return B2A_T_VARINT;
+	case LogicalTypeId::ENUM: return B2A_T_ENUM;
 	default:
-		// ENUM (dictionary output): DESIGN.md §9
 		throw NotImplementedException("Unsupported Arrow type %s", t.ToString());
 	}
 }
@@ -366,6 +366,15 @@ static void FillVector(VectorTree &tree, Vector &vec, idx_t count, const string 
 		           type.id() == LogicalTypeId::MAP ? "entries" : "l", kids[0]);
 		break;
 	}
+	case LogicalTypeId::ENUM: {
+		// the codes + the dictionary values in insert order (ArrowEnumData::Initialize, appender/enum_data.hpp:67-75)
+		out.data = FlatVector::GetData(vec);
+		const idx_t n_values = EnumType::GetSize(type);
+		tree.keep.push_back(make_uniq<Vector>(EnumType::GetValuesInsertOrder(type), idx_t(0), n_values));
+		auto kids = children(1);
+		FillVector(tree, *tree.keep.back(), n_values, "dictionary", kids[0]);
+		break;
+	}
 	case LogicalTypeId::ARRAY: {
 		const auto k = ArrayType::GetSize(type);
 		out.param = NumericCast<int64_t>(k);
@@ -421,15 +430,14 @@ struct HostStream {
 		return {const_data_ptr_cast(s.data) + bi.meta_offset,
 		        NumericCast<idx_t>(bi.body_offset + bi.body_length - bi.meta_offset)};
 	}
-	//! the Schema message
+	//! what precedes the first record batch: the Schema message + the DictionaryBatch messages of ENUM columns
 	std::pair<const_data_ptr_t, idx_t> Schema() const {
-		const void *p = nullptr;
 		uint64_t n = 0;
-		int rc = b2a_writer_schema_message(s.writer, &p, &n);
+		int rc = b2a_writer_preamble(s.writer, &n);
 		if (rc) {
 			B2AThrow(rc);
 		}
-		return {const_data_ptr_cast(p), NumericCast<idx_t>(n)};
+		return {const_data_ptr_cast(s.data), NumericCast<idx_t>(n)};
 	}
 };
 

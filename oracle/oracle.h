@@ -31,7 +31,8 @@ enum {
 	O_INVALID = 0, O_SQLNULL, O_BOOLEAN, O_TINYINT, O_SMALLINT, O_INTEGER, O_BIGINT, O_UTINYINT, O_USMALLINT,
 	O_UINTEGER, O_UBIGINT, O_HUGEINT, O_UHUGEINT, O_FLOAT, O_DOUBLE, O_DECIMAL, O_VARCHAR, O_BLOB, O_DATE, O_TIME,
 	O_TIMESTAMP, O_TIMESTAMP_SEC, O_TIMESTAMP_MS, O_TIMESTAMP_NS, O_TIMESTAMP_TZ, O_INTERVAL, O_UUID, O_LIST,
-	O_STRUCT, O_MAP, O_ARRAY, O_UNION, O_TIME_TZ, O_BIT, O_VARINT, O_JSON
+	O_STRUCT, O_MAP, O_ARRAY, O_UNION, O_TIME_TZ, O_BIT, O_VARINT, O_JSON,
+	O_ENUM /* writer side only (oracle_write.py): the scan never produces it */
 };
 
 /* ArrowVariableSizeType (duckdb/src/include/duckdb/function/table/arrow/enum/arrow_variable_size_type.hpp) */

@@ -19,7 +19,7 @@ T = {n: i for i, n in enumerate(
     ["INVALID", "SQLNULL", "BOOLEAN", "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT", "UINTEGER",
      "UBIGINT", "HUGEINT", "UHUGEINT", "FLOAT", "DOUBLE", "DECIMAL", "VARCHAR", "BLOB", "DATE", "TIME", "TIMESTAMP",
      "TIMESTAMP_SEC", "TIMESTAMP_MS", "TIMESTAMP_NS", "TIMESTAMP_TZ", "INTERVAL", "UUID", "LIST", "STRUCT", "MAP",
-     "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON"])}
+     "ARRAY", "UNION", "TIME_TZ", "BIT", "VARINT", "JSON", "ENUM"])}
 WIDTH = {"BOOLEAN": 1, "TINYINT": 1, "UTINYINT": 1, "SMALLINT": 2, "USMALLINT": 2, "INTEGER": 4, "UINTEGER": 4,
          "FLOAT": 4, "DATE": 4, "BIGINT": 8, "UBIGINT": 8, "DOUBLE": 8, "TIME": 8, "TIMESTAMP": 8, "TIMESTAMP_SEC": 8,
          "TIMESTAMP_MS": 8, "TIMESTAMP_NS": 8, "TIMESTAMP_TZ": 8, "HUGEINT": 16, "UHUGEINT": 16, "UUID": 16,

@@ -12,6 +12,8 @@ Restates DuckDB's ArrowAppender, one function per appender, over host vectors (t
   ArrowTimeTzConverter      .../appender/scalar_data.hpp:54-68 (TIME_TZ -> time64[us], the offset is dropped)
   ArrowUUIDConverter        .../appender/varchar_data.hpp:33-43 + UUID::ToString duckdb/src/common/types/uuid.cpp:70-101
   ArrowUnionData            duckdb/src/common/arrow/appender/union_data.cpp:24-52 (flat members)
+  ArrowEnumData             .../appender/enum_data.hpp:24-87: the codes copied as they are (NULL slots included); the
+                            dictionary = serialize_dictionaries below
   arrow_lossless_conversion arrow_appender.cpp:144-191 + arrow_type_extension.cpp:345-390: BOOLEAN as one byte per row
                             (ArrowBool8::DuckToArrow), UUID through ArrowUUIDBlobConverter (scalar_data.hpp:70-87),
                             TIME_TZ / HUGEINT / UHUGEINT bits as they are, BIT / VARINT like BLOB, JSON like VARCHAR
@@ -188,6 +190,32 @@ def append(hv, idx: np.ndarray, nodes: list, buffers: list, large: bool = False,
     else:
         w = hv.data.size // hv.rows if hv.rows else 1
         buffers.append(hv.data.reshape(-1, w)[idx].tobytes() if n else b"")
+
+
+def serialize_dictionaries(columns: list):
+    """The DictionaryBatch bodies of a stream: one per ENUM field in field pre-order (= dictionary id order), each the
+    utf8 array ArrowEnumData::Initialize builds from EnumType::GetValuesInsertOrder (appender/enum_data.hpp:34-75): 0xFF
+    validity, int32 offsets whatever arrow_large_buffer_size says, the characters.
+    -> [(rows, nodes, buffers[(offset, length)], body bytes)]"""
+    out = []
+
+    def walk(hv):
+        if hv.type == "ENUM":
+            d = hv.children[0]
+            nodes, bufs = [], []
+            append(d, np.arange(d.rows, dtype=np.int64), nodes, bufs)
+            body, slices = b"", []
+            for b in bufs:
+                slices.append((len(body), len(b)))
+                body += _pad8(b)
+            out.append((d.rows, nodes, slices, body))
+            return
+        for c in hv.children:
+            walk(c)
+
+    for c in columns:
+        walk(c)
+    return out
 
 
 def serialize_batches(columns: list, rows: int, row_group_size: int = 122_880, large: bool = False,

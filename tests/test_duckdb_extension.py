@@ -331,3 +331,44 @@ def test_arrow_lossless_conversion_through_copy(db, cuda_device):
     assert rows(f"SELECT count(*) FROM ll JOIN read_arrow('{p2}') r ON ll.u::VARCHAR = r.u") == \
         rows("SELECT count(u) FROM ll")
     q("DROP TABLE ll")
+
+
+@pytest.mark.gpu
+def test_enum_columns_through_copy_and_to_arrow_ipc(db, cuda_device):
+    """ENUM columns leave as dictionary-encoded fields with their DictionaryBatch behind the schema message
+    (arrow_converter.cpp:362-386, appender/enum_data.hpp:24-87) and come back as VARCHAR, which is what the reference's scan
+    makes of a dictionary-encoded column (arrow_conversion.cpp:960-1010)."""
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+    big = ", ".join(f"'value number {i:03d}'" for i in range(300))
+    q("CREATE TYPE mood_x AS ENUM ('sad', 'ok', 'happy', 'a mood well past twelve bytes')")
+    q(f"CREATE TYPE big_x AS ENUM ({big})")
+    try:
+        q("CREATE OR REPLACE TABLE en AS SELECT i, CASE WHEN i % 7 = 0 THEN NULL ELSE "
+          "(['sad','ok','happy','a mood well past twelve bytes'])[1 + i % 4]::mood_x END AS m, "
+          "('value number ' || lpad((i * 7 % 300)::VARCHAR, 3, '0'))::big_x AS b, "
+          "{'m': (['sad','ok'])[1 + i % 2]::mood_x, 'k': i} AS st FROM range(5000) t(i)")
+        p = f"{db}/enum.arrows"
+        q(f"COPY en TO '{p}' (FORMAT ARROWS, ROW_GROUP_SIZE 2048)")
+        t = ipc.open_stream(p).read_all()
+        t.validate(full=True)
+        assert t.schema.field("m").type == pa.dictionary(pa.uint8(), pa.string())
+        assert t.schema.field("b").type == pa.dictionary(pa.uint16(), pa.string())
+        assert t.schema.field("st").type.field("m").type == pa.dictionary(pa.uint8(), pa.string())
+        assert t.num_rows == 5000 and t.column("m").null_count == 715
+        d = rows(f"DESCRIBE SELECT * FROM read_arrow('{p}')")
+        assert [r[1] for r in d] == ["BIGINT", "VARCHAR", "VARCHAR", "STRUCT(m VARCHAR, k BIGINT)"]
+        same = ("SELECT i, m::VARCHAR, b::VARCHAR, {'m': st.m::VARCHAR, 'k': st.k} FROM en")
+        assert rows(f"SELECT count(*) FROM ({same} EXCEPT ALL SELECT * FROM read_arrow('{p}'))") == [("0",)]
+        assert rows(f"SELECT count(*) FROM (SELECT * FROM read_arrow('{p}') EXCEPT ALL {same})") == [("0",)]
+        # to_arrow_ipc: the header blob carries schema + dictionaries, so the concatenation is a readable stream
+        blobs = q("SELECT hex(ipc), header FROM to_arrow_ipc((SELECT m, b FROM en))")
+        assert [r[1] for r in blobs][:2] == ["true", "false"]
+        stream = b"".join(bytes.fromhex(r[0]) for r in blobs) + b"\xff\xff\xff\xff\x00\x00\x00\x00"
+        t2 = ipc.open_stream(pa.py_buffer(stream)).read_all()
+        assert t2.column("m").to_pylist() == t.column("m").to_pylist()
+        assert t2.column("b").to_pylist() == t.column("b").to_pylist()
+    finally:
+        q("DROP TABLE IF EXISTS en")
+        q("DROP TYPE mood_x")
+        q("DROP TYPE big_x")

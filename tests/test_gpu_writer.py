@@ -235,6 +235,64 @@ def test_uuid_time_tz_bit_union_bit_exact_vs_oracle(b2a, cuda_device, rgs):
     assert {f.name: f.format for f in r.columns}["u"].startswith("+us:") and r.num_rows == n
 
 
+@pytest.mark.parametrize("settings", [dict(), dict(arrow_large_buffer_size=True), dict(produce_arrow_string_view=True)])
+@pytest.mark.parametrize("rgs", [2048, 1000])
+def test_enum_columns_dictionary_batches(b2a, cuda_device, rgs, settings):
+    """ENUM -> dictionary-encoded field + one DictionaryBatch per ENUM field between the schema and the first record batch
+    (arrow_converter.cpp:362-386, appender/enum_data.hpp:24-87): uint8 codes for a 4-value ENUM, uint16 for a 300-value
+    one, also inside a struct and below a list; record-batch bodies and dictionary bodies bit-exact vs the restatement
+    pinned in tests/test_ref_append.py::test_enum_columns_equal_reference; pyarrow and this repo's reader read it back."""
+    rng = np.random.default_rng(21)
+    n = 5000
+    moods = ["sad", "ok", "happy", "a mood well past twelve bytes"]
+    big = [f"value number {i:03d}" for i in range(300)]
+    m = pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 4, n), pa.uint8(), mask=rng.random(n) < 0.15), pa.array(moods))
+    b = pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 300, n), pa.uint16()), pa.array(big))
+    k = pa.array(range(n), pa.int64())
+    st = pa.StructArray.from_arrays([m, k], names=["m", "k"])
+    lens = rng.integers(0, 4, n)
+    lo = np.zeros(n + 1, np.int32)
+    np.cumsum(lens, out=lo[1:])
+    lb = pa.ListArray.from_arrays(pa.array(lo, pa.int32()), b.take(pa.array(rng.integers(0, n, int(lo[-1])))))
+    s = pa.array(["s%d" % i if i % 3 else "a string well past twelve bytes %d" % i for i in range(n)])
+    table = pa.table({"m": m, "b": b, "st": st, "lb": lb, "s": s})
+    host = table_vectors(table)
+    w = b2a.ArrowWriter([to_device(h) for h in host], n, rgs, **settings)
+    stream = w.write()
+    kw = dict(large=settings.get("arrow_large_buffer_size", False), sview=settings.get("produce_arrow_string_view", False))
+    exp = OW.serialize_batches(host, n, rgs, **kw)
+    assert w.n_batches == len(exp)
+    for i, (rows, nodes, slices, body) in enumerate(exp):
+        bi = w.batch(i)
+        assert bi.rows == rows and bi.body_length == len(body)
+        assert bytes(stream[bi.body_offset: bi.body_offset + bi.body_length]) == body, f"batch {i}"
+    # the dictionary region: [schema, 4 x (DictionaryBatch header + body)) — every body is at the end of its message
+    dicts = OW.serialize_dictionaries(host)
+    assert len(dicts) == 4
+    region = bytes(stream[len(w.schema_message()): w.preamble_bytes])
+    pos = 0
+    for d, (rows, nodes, slices, body) in enumerate(dicts):
+        assert region[pos: pos + 4] == b"\xff\xff\xff\xff"
+        meta = int.from_bytes(region[pos + 4: pos + 8], "little")
+        assert region[pos + 8 + meta: pos + 8 + meta + len(body)] == body, f"dictionary {d}"
+        pos += 8 + meta + len(body)
+    assert pos == len(region)
+    got = ipc.open_stream(pa.py_buffer(stream)).read_all()
+    assert got.schema.field("m").type == pa.dictionary(pa.uint8(), pa.string())
+    assert got.schema.field("b").type == pa.dictionary(pa.uint16(), pa.string())
+    for name in table.column_names:
+        assert got.column(name).to_pylist() == table.column(name).to_pylist(), name
+    # this repo's reader: dictionary-encoded columns come back as VARCHAR, like the reference's scan
+    r = b2a.ArrowIPCReader.open_buffers([stream])
+    assert r.num_rows == n
+
+
+def test_enum_needs_its_dictionary(b2a):
+    from duckdb_arrow_b200 import DeviceVector
+    with pytest.raises(b2a.B2AError, match="needs one VARCHAR child"):
+        b2a.ArrowWriter([DeviceVector("ENUM", 0, None, None, name="e")], 0, device=-1)
+
+
 def test_union_with_nested_member_is_rejected(b2a):
     from duckdb_arrow_b200 import DeviceVector
     m = DeviceVector("LIST", 0, None, None, [DeviceVector("INTEGER", 0, None, None, name="l")], name="m")

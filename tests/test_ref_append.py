@@ -204,3 +204,64 @@ def test_dbgen_export_has_a_bitmap_per_column():
         assert col.null_count == 0
         v = col.buffers()[0]
         assert v is not None and ctypes.string_at(v.address, 2500) == b"\xff" * 2500
+
+
+@pytest.mark.parametrize("flags", [0, R.FLAG_LARGE])  # under produce_arrow_string_view the reference finalises the
+# dictionary as a 4-buffer view array over int32 offsets + format "u" (FinalizeChild(VARCHAR)): not importable
+def test_enum_columns_equal_reference(flags):
+    """ENUM -> dictionary-encoded column (arrow_converter.cpp:362-386, appender/enum_data.hpp:24-87): code width by
+    dictionary size, codes copied as they are, the dictionary a utf8 array with int32 offsets and a 0xFF validity buffer
+    whatever the settings say — against what the reference appender exports for a small (uint8) and a 300-value (uint16)
+    ENUM, top level and inside a struct."""
+    big = ", ".join(f"'value number {i:03d}'" for i in range(300))
+    R.query("CREATE TYPE mood_t AS ENUM ('sad', 'ok', 'happy', 'a mood well past twelve bytes')")
+    R.query(f"CREATE TYPE big_t AS ENUM ({big})")
+    try:
+        sql = ("SELECT CASE WHEN i % 7 = 0 THEN NULL ELSE (['sad','ok','happy','a mood well past twelve bytes'])[1 + i % 4]::mood_t "
+               "END AS m, ('value number ' || lpad((i * 7 % 300)::VARCHAR, 3, '0'))::big_t AS b, "
+               "{'m': (['sad','ok'])[1 + i % 2]::mood_t, 'k': i} AS st FROM range(5000) t(i)")
+        batches = list(R.export(sql, 2048, flags))
+    finally:
+        R.query("DROP TYPE mood_t")
+        R.query("DROP TYPE big_t")
+    assert [b.num_rows for b in batches] == [2048, 2048, 904]
+    assert str(batches[0].schema.field("m").type) == "dictionary<values=string, indices=uint8, ordered=0>"
+    assert str(batches[0].schema.field("b").type) == "dictionary<values=string, indices=uint16, ordered=0>"
+    for b in batches:
+        cols = table_vectors(pa.Table.from_batches([b]))
+        (n, nodes, slices, body), = OW.serialize_batches(cols, b.num_rows, 1 << 20, large=bool(flags & R.FLAG_LARGE),
+                                                         sview=bool(flags & R.FLAG_STRING_VIEW))
+        rnodes, rbufs = [], []
+
+        def walk(arr):
+            bufs = arr.buffers()
+            if pa.types.is_struct(arr.type):
+                rnodes.append((len(arr), arr.null_count))
+                rbufs.append(_bytes(bufs[0], (len(arr) + 7) // 8))
+                for i in range(arr.type.num_fields):
+                    walk(arr.field(i))
+                return
+            if pa.types.is_dictionary(arr.type):
+                idx = arr.indices
+                rnodes.append((len(arr), arr.null_count))
+                rbufs.append(_bytes(idx.buffers()[0], (len(arr) + 7) // 8))
+                rbufs.append(_bytes(idx.buffers()[1], len(arr) * idx.type.bit_width // 8))
+                return
+            rnodes.append((len(arr), arr.null_count))
+            rbufs.append(_bytes(bufs[0], (len(arr) + 7) // 8))
+            rbufs.append(_bytes(bufs[1], len(arr) * arr.type.bit_width // 8))
+
+        for c in b.columns:
+            walk(c)
+        assert rnodes == nodes
+        assert [body[o:o + l] for o, l in slices] == rbufs
+        # the dictionaries, in field pre-order
+        dicts = OW.serialize_dictionaries(cols)
+        ref_dicts = [b.column("m").dictionary, b.column("b").dictionary, b.column("st").field(0).dictionary]
+        assert len(dicts) == 3
+        for (rows, dnodes, dslices, dbody), rd in zip(dicts, ref_dicts):
+            assert rd.type == pa.string() and rows == len(rd) and dnodes == [(len(rd), 0)]
+            rb = rd.buffers()
+            last = int(np.frombuffer(_bytes(rb[1], (rows + 1) * 4), np.int32)[-1])
+            want = [_bytes(rb[0], (rows + 7) // 8), _bytes(rb[1], (rows + 1) * 4), _bytes(rb[2], last)]
+            assert [dbody[o:o + l] for o, l in dslices] == want

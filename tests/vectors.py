@@ -138,6 +138,13 @@ def from_arrow(arr: pa.Array, name: str = "") -> HostVector:
             for k in kids:
                 _and_mask(k, valid)
         return HostVector("STRUCT", n, None, valid, kids, name=name)
+    if pa.types.is_dictionary(t):  # a DuckDB ENUM: codes sized by the dictionary (EnumTypeInfo::DictType) + its values
+        nvals = len(arr.dictionary)
+        dt = np.uint8 if nvals <= 0xFF else np.uint16 if nvals <= 0xFFFF else np.uint32
+        idx = arr.indices
+        codes = _values(idx, np.dtype(idx.type.to_pandas_dtype())).astype(dt)
+        return HostVector("ENUM", n, codes.view(np.uint8), valid, [from_arrow(arr.dictionary.cast(pa.string()), "dictionary")],
+                          name=name)
     if isinstance(t, pa.BaseExtensionType):  # the extension types of arrow_type_extension.cpp:366-390
         st = arr.storage
         ext = t.extension_name
