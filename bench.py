@@ -532,13 +532,24 @@ def leg_copy(ctx, args, scan, reader, d_out, my_rows, steps):
     measure_ms = _max_over_ranks(ctx, float(np.median(m)))
     rows = int(_sum_over_ranks(ctx, my_rows))
     alg = w.algorithmic_bytes
+    traffic, traffic_source = None, None
+    try:
+        te = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["b2a_encode_kernel"]
+        traffic = int((te["dram_bytes_read"] + te["dram_bytes_write"]) / 59986052 * my_rows)
+        traffic_source = ("profiles/traffic.json: dram__bytes_read+write of b2a_encode_kernel from the builder's ncu --set "
+                          "full capture on SF10, per row, x the rows of this launch (not measured in this run)")
+    except Exception:  # noqa: BLE001
+        pass
     out = {"metric": "COPY lineitem TO (FORMAT ARROWS) rows/s (device-resident vectors -> IPC stream in HBM)",
            "value": rows / ((ms + measure_ms) / 1e3), "unit": "rows/s", "encode_only_value": rows / (ms / 1e3),
            "encode_ms": ms, "measure_ms": measure_ms, "rows": rows, "n_batches_rank0": int(w.n_batches),
            "stream_bytes_rank0": int(w.stream_bytes), "scaling": "strong",
            "roofline": {"bound": "hbm", "kernel": "b2a_encode_kernel", "achieved": alg / (enc_ms / 1e3) / 1e9,
                         "peak": ctx.peak, "unit": "GB/s", "frac": alg / (enc_ms / 1e3) / 1e9 / ctx.peak,
-                        "kernel_ms": enc_ms, "algorithmic_bytes_per_launch": int(alg), "traffic": None},
+                        "kernel_ms": enc_ms, "algorithmic_bytes_per_launch": int(alg), "traffic": traffic,
+                        "traffic_source": traffic_source,
+                        "algorithmic_bytes_note": "input vectors (156 B/row) + characters of the strings longer than 12 "
+                                                  "bytes fetched from the string heap + every byte of the produced bodies"},
            "config": {"workload": f"lineitem SF{args.sf:g} COPY TO arrows, row_group_size {BATCH_ROWS}"}}
     w.close()
     del d_stream

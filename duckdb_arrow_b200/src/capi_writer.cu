@@ -235,6 +235,9 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 		p.vecs[i].validity = reinterpret_cast<uint64_t>(mask);
 		p.vecs[i].union_mask_ready = true;
 	}
+	std::vector<b2a_enc_task> enc_tasks;
+	std::vector<uint32_t> enc_tiles;
+	bool skeleton_ready = false;
 	for (;;) {
 		// ---- fixed-size lists under a selection: child selection = sel[i / k] * k + i % k
 		for (;;) {
@@ -330,6 +333,21 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 			return SetLastError(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
 		}
 		w->launches += 2;
+		// While the measure kernels read the string_t records: if no list is pending the node set is final, and
+		// everything about the encode tasks except their stream offsets can be built now (the D2H copy of the totals
+		// below returns when the kernels are done).
+		if (!skeleton_ready) {
+			bool final_nodes = true;
+			for (int ni : pending) {
+				final_nodes = final_nodes && !WritePlan::IsListOp(p.vecs[static_cast<size_t>(p.nodes[static_cast<size_t>(ni)].vec)].op);
+			}
+			if (final_nodes) {
+				p.BuildPreorders();
+				p.EncodeTaskSkeleton(enc_tasks, enc_tiles);
+				skeleton_ready = true;
+				trace.Mark("encode task skeleton (host, overlapped)");
+			}
+		}
 		std::vector<uint64_t> totals(pending.size() + 1);
 		W_CUDA(cudaMemcpyAsync(totals.data(), base + n_tiles_total, (pending.size() + 1) * 8, cudaMemcpyDeviceToHost, st));
 		W_CUDA(cudaStreamSynchronize(st));
@@ -392,10 +410,14 @@ int b2a_writer_measure(b2a_writer *w, void *cuda_stream) {
 	for (size_t i = 0; i < p.nodes.size(); i++) {
 		p.nodes[i].null_counter = reinterpret_cast<uint64_t>(w->d_null_counts + i);
 	}
-	std::vector<b2a_enc_task> tasks;
-	std::vector<uint32_t> tiles;
+	std::vector<b2a_enc_task> &tasks = enc_tasks;
+	std::vector<uint32_t> &tiles = enc_tiles;
 	trace.Mark("null count alloc");
-	p.EncodeTasks(tasks, tiles);
+	if (skeleton_ready) {
+		p.PatchEncodeTasks(tasks);
+	} else {
+		p.EncodeTasks(tasks, tiles);
+	}
 	trace.Mark("encode tasks (host)");
 	int rc = UploadTasks(w, tasks, tiles, st);
 	if (rc != B2A_OK) {

@@ -458,6 +458,12 @@ static void PushTask(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &ti
 
 void WritePlan::ScanTasks(const std::vector<int> &node_ids, std::vector<b2a_enc_task> &tasks,
                           std::vector<uint32_t> &tile_task) const {
+	uint64_t n_tiles = 0;
+	for (int ni : node_ids) {
+		n_tiles += ScanTiles(nodes[static_cast<size_t>(ni)].rows);
+	}
+	tasks.reserve(tasks.size() + node_ids.size());
+	tile_task.reserve(tile_task.size() + n_tiles);
 	for (int ni : node_ids) {
 		const WNode &n = nodes[static_cast<size_t>(ni)];
 		b2a_enc_task t = BaseTask(n, vecs[static_cast<size_t>(n.vec)]);
@@ -466,7 +472,9 @@ void WritePlan::ScanTasks(const std::vector<int> &node_ids, std::vector<b2a_enc_
 	}
 }
 
-void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const {
+// One walk for the three users below: emit(task, n_tiles) is called once per encode task, in launch order.
+template <class EMIT>
+void WritePlan::WalkEncodeTasks(EMIT &&emit) const {
 	for (size_t bi = 0; bi < dict_batches.size() + batches.size(); bi++) {
 		const WBatch &b = bi < dict_batches.size() ? dict_batches[bi] : batches[bi - dict_batches.size()];
 		for (int ni : b.preorder) {
@@ -479,7 +487,7 @@ void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32
 					t.dst = b.body_offset + n.buf[0].offset;
 					t.dst_len = n.buf[0].length;
 					t.tile_rows = 1u << 16;
-					PushTask(tasks, tile_task, t, (n.rows + t.tile_rows - 1) / t.tile_rows);
+					emit(t, (n.rows + t.tile_rows - 1) / t.tile_rows);
 				}
 				continue;
 			}
@@ -490,7 +498,7 @@ void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32
 				t.dst_len = n.buf[0].length;
 				t.counter = n.null_counter;
 				t.tile_rows = 1u << 20;
-				PushTask(tasks, tile_task, t, (n.rows + t.tile_rows - 1) / t.tile_rows);
+				emit(t, (n.rows + t.tile_rows - 1) / t.tile_rows);
 			}
 			if (v.n_buffers < 2) {
 				continue;
@@ -503,7 +511,7 @@ void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32
 				if (v.n_buffers >= 3) {
 					t.dst2 = b.body_offset + n.buf[2].offset;
 				}
-				PushTask(tasks, tile_task, t, ScanTiles(n.rows));
+				emit(t, ScanTiles(n.rows));
 				continue;
 			}
 			if (n.rows == 0) {
@@ -517,8 +525,51 @@ void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32
 				tile_rows = std::max<uint64_t>(2048, tile_rows / 2048 * 2048);
 			}
 			t.tile_rows = static_cast<uint32_t>(tile_rows);
-			PushTask(tasks, tile_task, t, (n.rows + tile_rows - 1) / tile_rows);
+			emit(t, (n.rows + tile_rows - 1) / tile_rows);
 		}
+	}
+}
+
+void WritePlan::EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const {
+	WalkEncodeTasks([&](const b2a_enc_task &t, uint64_t n_tiles) { PushTask(tasks, tile_task, t, n_tiles); });
+}
+
+void WritePlan::BuildPreorders() {
+	for (auto *set : {&dict_batches, &batches}) {
+		for (auto &b : *set) {
+			b.preorder.clear();
+			for (int t : b.top) {
+				Preorder(t, b.preorder);
+			}
+		}
+	}
+}
+
+void WritePlan::EncodeTaskSkeleton(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const {
+	uint64_t n_tasks = 0, n_tiles = 0;
+	WalkEncodeTasks([&](const b2a_enc_task &, uint64_t k) {
+		n_tasks++;
+		n_tiles += k;
+	});
+	tasks.reserve(n_tasks);
+	tile_task.reserve(n_tiles);
+	EncodeTasks(tasks, tile_task);
+}
+
+void WritePlan::PatchEncodeTasks(std::vector<b2a_enc_task> &tasks) const {
+	size_t k = 0;
+	WalkEncodeTasks([&](const b2a_enc_task &t, uint64_t) {
+		if (k >= tasks.size() || tasks[k].op != t.op || tasks[k].rows != t.rows) {
+			throw Error(B2A_EINTERNAL, "writer: encode task skeleton does not match the laid-out plan");
+		}
+		tasks[k].dst = t.dst;
+		tasks[k].dst2 = t.dst2;
+		tasks[k].dst_len = t.dst_len;
+		tasks[k].counter = t.counter;
+		k++;
+	});
+	if (k != tasks.size()) {
+		throw Error(B2A_EINTERNAL, "writer: encode task skeleton does not match the laid-out plan");
 	}
 }
 

@@ -98,6 +98,12 @@ struct WritePlan {
 	void Layout();
 	// encode tasks for all nodes (dst = absolute stream offsets); needs Layout()
 	void EncodeTasks(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const;
+	// The same walk split in two, so that the host builds the 10^4 tasks / 10^6 tile entries of a large table WHILE the
+	// measure kernels run: the skeleton (everything but the stream offsets; needs the final node set and
+	// BuildPreorders()) before the totals are known, the offsets (dst / dst2 / dst_len) after Layout().
+	void BuildPreorders();
+	void EncodeTaskSkeleton(std::vector<b2a_enc_task> &tasks, std::vector<uint32_t> &tile_task) const;
+	void PatchEncodeTasks(std::vector<b2a_enc_task> &tasks) const;
 	// measure-phase tasks for the given scan nodes
 	void ScanTasks(const std::vector<int> &node_ids, std::vector<b2a_enc_task> &tasks,
 	               std::vector<uint32_t> &tile_task) const;
@@ -122,6 +128,8 @@ private:
 	int AddVec(const b2a_vector &v, WriteField &wf, int depth);
 	void Preorder(int node, std::vector<int> &out) const;
 	b2a_enc_task BaseTask(const WNode &n, const WVec &v) const;
+	template <class EMIT>
+	void WalkEncodeTasks(EMIT &&emit) const;
 };
 
 } // namespace b2a
