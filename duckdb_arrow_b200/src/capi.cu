@@ -1082,6 +1082,97 @@ extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predica
 	B2A_CATCH
 }
 
+// b2a_scan_filter for callers that may not allocate device memory (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc): the per-chunk tables are built on the host on every call and copied into the fixed __device__
+// array of kernels/filter.cu — no cudaMalloc, cudaFree or allocating library call on this path, nothing cached in the
+// scan.  Same validation, same kernel, same results as b2a_scan_filter.
+extern "C" int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds,
+                                        void *d_sel, void *d_count, void *d_total, void *cuda_stream) {
+	B2A_TRY
+	NEED_DEVICE(s);
+	if (n_preds == 0 || n_preds > 8) {
+		return Fail(B2A_EINVAL, "between 1 and 8 predicates are supported");
+	}
+	if (!preds || !d_out || !d_sel || !d_count || !d_total) {
+		return Fail(B2A_EINVAL, "b2a_scan_filter_no_alloc: null argument");
+	}
+	const ScanPlan &p = s->plan;
+	if (p.alias_direct) {
+		return Fail(B2A_EINVAL, "filters / aggregates need device-resident vectors: create the scan without "
+		                        "B2A_SCAN_HOST_ALIAS");
+	}
+	const uint64_t need = FilterNoAllocBytesNeeded(p.n_chunks, n_preds);
+	if (need > FilterNoAllocScratchBytes()) {
+		return Fail(B2A_EINVAL, "b2a_scan_filter_no_alloc: " + std::to_string(p.n_chunks) + " vectors x " +
+		                            std::to_string(n_preds) + " predicates need " + std::to_string(need) +
+		                            " bytes of table, the fixed device scratch holds " +
+		                            std::to_string(FilterNoAllocScratchBytes()) +
+		                            " (use b2a_scan_filter, or scan a narrower batch range)");
+	}
+	const Schema &schema = s->r->reader.BaseSchema();
+	FilterLaunch l;
+	std::vector<int> flats;
+	for (uint32_t i = 0; i < n_preds; i++) {
+		if (preds[i].cmp > B2A_CMP_GE) {
+			return Fail(B2A_EINVAL, "unknown comparison");
+		}
+		if (preds[i].column >= p.top_columns.size()) {
+			return Fail(B2A_EINVAL, "predicate column index out of range");
+		}
+		const Field &f = *schema.fields[static_cast<size_t>(p.top_columns[preds[i].column])];
+		if (f.dict_id >= 0 || f.out_width > 8 || f.out_width == 0 || f.type_id == B2A_T_FLOAT ||
+		    f.type_id == B2A_T_DOUBLE || f.type_id == B2A_T_UBIGINT) {
+			return Fail(B2A_ENOTIMPL, "filter pushdown supports signed integer-like columns (integers, dates, "
+			                          "timestamps, DECIMAL up to 18 digits) only: column '" + f.name + "'");
+		}
+		flats.push_back(f.flat_index);
+		const bool uns = f.type_id == B2A_T_UTINYINT || f.type_id == B2A_T_USMALLINT || f.type_id == B2A_T_UINTEGER;
+		l.preds[i] = preds[i];
+		l.widths[i] = static_cast<uint8_t>(f.out_width | (uns ? 0x80 : 0));
+	}
+	std::vector<uint32_t> rows;
+	std::vector<uint64_t> table;
+	rows.reserve(p.n_chunks);
+	table.reserve(p.n_chunks * 2 * n_preds);
+	for (uint64_t b = 0; b < p.batch_rows.size(); b++) {
+		const uint64_t nchunks = (p.batch_rows[b] + B2A_VECTOR_SIZE - 1) / B2A_VECTOR_SIZE;
+		for (uint64_t k = 0; k < nchunks; k++) {
+			const uint64_t left = p.batch_rows[b] - k * B2A_VECTOR_SIZE;
+			rows.push_back(left > B2A_VECTOR_SIZE ? B2A_VECTOR_SIZE : static_cast<uint32_t>(left));
+			for (size_t c = 0; c < flats.size(); c++) {
+				const b2a_column_out &co = p.Column(p.batch_lo + b, static_cast<uint32_t>(flats[c]));
+				const Field &f = *schema.flat[static_cast<size_t>(flats[c])];
+				table.push_back(co.data_off + k * B2A_VECTOR_SIZE * static_cast<uint64_t>(f.out_width));
+				table.push_back(co.validity_off == B2A_NONE ? B2A_NONE : co.validity_off + k * (B2A_VECTOR_SIZE / 8));
+			}
+		}
+	}
+	if (rows.size() != p.n_chunks) {
+		return Fail(B2A_EINTERNAL, "b2a_scan_filter_no_alloc: chunk count mismatch");
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	CUDA_OK(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), st));
+	l.out = static_cast<const uint8_t *>(d_out);
+	l.n_chunks = p.n_chunks;
+	l.n_preds = n_preds;
+	l.d_sel = static_cast<uint32_t *>(d_sel);
+	l.d_count = static_cast<uint32_t *>(d_count);
+	l.d_total = static_cast<unsigned long long *>(d_total);
+	l.sm_count = s->sm_count;
+	int e = LaunchFilterNoAlloc(l, table.data(), rows.data(), cuda_stream);
+	if (e == -1) {
+		return Fail(B2A_EINVAL, "b2a_scan_filter_no_alloc: tables exceed the fixed device scratch");
+	}
+	if (e != 0) {
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+	}
+	if (l.n_chunks) {
+		s->launches++;
+	}
+	return B2A_OK;
+	B2A_CATCH
+}
+
 extern "C" int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_t col_b, const void *d_sel,
                                     const void *d_count, void *d_result_i128, void *cuda_stream) {
 	B2A_TRY

@@ -43,6 +43,14 @@ struct FilterLaunch {
 };
 int LaunchFilter(const FilterLaunch &l, void *stream);
 
+// The no-allocation variant (b2a_scan_filter_no_alloc): the per-chunk tables live in a file-scope __device__ array of
+// filter.cu instead of cudaMalloc'ed memory.  l.d_chunk_col / l.d_chunk_rows are ignored; the HOST tables are copied into
+// the array on `stream` (h_chunk_col: 2 * n_preds uint64 per chunk, h_chunk_rows: one uint32 per chunk) before the launch.
+// Returns 0, a cudaError_t, or -1 when the tables do not fit FilterNoAllocScratchBytes().
+uint64_t FilterNoAllocScratchBytes();
+uint64_t FilterNoAllocBytesNeeded(uint64_t n_chunks, uint32_t n_preds);
+int LaunchFilterNoAlloc(const FilterLaunch &l, const uint64_t *h_chunk_col, const uint32_t *h_chunk_rows, void *stream);
+
 struct SumProductLaunch {
 	const uint8_t *out = nullptr;
 	const uint64_t *d_chunk_col = nullptr; // per chunk: {a data, a validity, b data, b validity} arena offsets

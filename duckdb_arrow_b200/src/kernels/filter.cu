@@ -183,6 +183,83 @@ int LaunchFilter(const FilterLaunch &l, void *stream) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// No-allocation variant of the filter launch.  The kernel's per-chunk tables (where every 2 048-row vector of every
+// predicate column starts in the arena, and how many rows it holds) are scratch the ordinary path keeps in cudaMalloc'ed
+// memory; here they live in ONE file-scope device array of a fixed size that every GPU loading the library holds until
+// the process exits.  In host code `g_filter_scratch` is only a stand-in for the symbol: its device address comes from
+// cudaGetSymbolAddress, once per device, with that device current.  Every call shares the array and overwrites the part
+// it needs (nothing in it has to start at zero: both tables are written in full before the kernel reads them, on the
+// same stream); two calls that overlap on the GPU — different streams, different scans, different host threads — race.
+// ------------------------------------------------------------------------------------------------
+static constexpr uint64_t kFilterScratchBytes = 4ull << 20; // 4 MiB: 49 932 vectors (102 M rows) under 5 predicates
+static __device__ __align__(256) unsigned char g_filter_scratch[kFilterScratchBytes];
+
+uint64_t FilterNoAllocScratchBytes() {
+	return kFilterScratchBytes;
+}
+
+// the column table first (8-byte entries), the row counts behind it on a 256-byte boundary
+static uint64_t FilterRowsOffset(uint64_t n_chunks, uint32_t n_preds) {
+	return (n_chunks * 2 * n_preds * sizeof(uint64_t) + 255) & ~uint64_t(255);
+}
+
+uint64_t FilterNoAllocBytesNeeded(uint64_t n_chunks, uint32_t n_preds) {
+	return FilterRowsOffset(n_chunks, n_preds) + n_chunks * sizeof(uint32_t);
+}
+
+static int FilterScratchAddress(unsigned char **out) {
+	static unsigned char *addr[64] = {};
+	int dev = 0;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) {
+		return static_cast<int>(e);
+	}
+	if (dev < 0 || dev >= 64) {
+		return static_cast<int>(cudaErrorInvalidDevice);
+	}
+	if (!addr[dev]) { // (a race between two host threads stores the same value twice)
+		void *p = nullptr;
+		e = cudaGetSymbolAddress(&p, g_filter_scratch);
+		if (e != cudaSuccess) {
+			return static_cast<int>(e);
+		}
+		addr[dev] = static_cast<unsigned char *>(p);
+	}
+	*out = addr[dev];
+	return 0;
+}
+
+int LaunchFilterNoAlloc(const FilterLaunch &l, const uint64_t *h_chunk_col, const uint32_t *h_chunk_rows, void *stream) {
+	if (l.n_chunks == 0) {
+		return 0;
+	}
+	if (FilterNoAllocBytesNeeded(l.n_chunks, l.n_preds) > kFilterScratchBytes) {
+		return -1;
+	}
+	unsigned char *scratch = nullptr;
+	int rc = FilterScratchAddress(&scratch);
+	if (rc != 0) {
+		return rc;
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(stream);
+	const uint64_t col_bytes = l.n_chunks * 2 * l.n_preds * sizeof(uint64_t);
+	const uint64_t rows_off = FilterRowsOffset(l.n_chunks, l.n_preds);
+	// pageable host memory: the copies are staged before the calls return, so the caller's tables may go away
+	cudaError_t e = cudaMemcpyAsync(scratch, h_chunk_col, col_bytes, cudaMemcpyHostToDevice, st);
+	if (e != cudaSuccess) {
+		return static_cast<int>(e);
+	}
+	e = cudaMemcpyAsync(scratch + rows_off, h_chunk_rows, l.n_chunks * sizeof(uint32_t), cudaMemcpyHostToDevice, st);
+	if (e != cudaSuccess) {
+		return static_cast<int>(e);
+	}
+	FilterLaunch k = l;
+	k.d_chunk_col = reinterpret_cast<const uint64_t *>(scratch);
+	k.d_chunk_rows = reinterpret_cast<const uint32_t *>(scratch + rows_off);
+	return LaunchFilter(k, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
 // sum(a*b) over selected rows, int64 x int64 -> int128 (DuckDB: DECIMAL(15,2)*DECIMAL(15,2) summed as HUGEINT)
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kFilterThreads)

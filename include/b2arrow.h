@@ -258,6 +258,17 @@ int b2a_scan_download_scratch(b2a_scan *s, void *h_scratch, void *cuda_stream);
 int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds, void *d_sel,
                     void *d_count, void *d_total, void *cuda_stream);
 int b2a_scan_num_chunks(b2a_scan *s, uint64_t *n_chunks);
+/* b2a_scan_filter without any device allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same kernel, same results; the kernel's per-vector tables (16 bytes per vector and
+ * predicate + 4 bytes per vector), which b2a_scan_filter keeps in cudaMalloc'ed memory cached in the scan, go into a
+ * fixed 4 MiB `static __device__` array that every GPU loading the library holds until exit.  Limit: a scan whose
+ * tables exceed 4 MiB (more than 49 932 vectors = 102 M rows under 5 predicates, 31 775 under 8) fails with
+ * B2A_EINVAL and a message that says so.  The call issues no cudaMalloc / cudaFree / allocating library routine.  All
+ * calls on a device share the array and each overwrites the part it needs (nothing has to start at zero): calls that
+ * overlap on the GPU — other streams, other scans, other host threads — race; serialise them on one stream. */
+int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds, void *d_sel,
+                             void *d_count, void *d_total, void *cuda_stream);
 /* Q6-style consumer: sum(a*b) over selected rows of two int64 DECIMAL columns (HUGEINT accumulator, lo/hi). */
 int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_t col_b, const void *d_sel,
                          const void *d_count, void *d_result_i128, void *cuda_stream);
