@@ -12,6 +12,8 @@ DUCKDB_INCLUDE = "/root/reference/duckdb/src/include"
 
 @pytest.mark.skipif(not os.path.isdir(DUCKDB_INCLUDE) or shutil.which("g++") is None,
                     reason="reference DuckDB headers / g++ not available")
+@pytest.mark.skipif(not os.path.exists(os.path.join(ROOT, "oracle", "_ref", "libduckdb_ref.so")),
+                    reason="oracle/_ref/libduckdb_ref.so not built yet (__graft_entry__.build() / python oracle/build_ref.py)")
 def test_duckdb_binding_builds_against_the_reference():
     import sys
     sys.path.insert(0, ROOT)
