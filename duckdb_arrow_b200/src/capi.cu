@@ -7,6 +7,8 @@
 
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -217,22 +219,105 @@ int b2a_reader_schema_metadata(b2a_reader *r, uint32_t i, const char **key, cons
 }
 
 // ------------------------------------------------------------------ scan
+// Device memory owned by a scan comes from the device's stream-ordered pool (release threshold raised once per device) on
+// a private stream that is synchronised right after the allocation, so the memory is usable from any stream when the
+// helper returns.  A read_arrow over a file is many scans (the DuckDB extension decodes slice by slice): cudaMalloc /
+// cudaFree per table cost more than a slice's PCIe time (6 ms of 12 per 256 MiB slice, B2A_SCANNER_TRACE), and every
+// cudaFree waited for the device.  cudaGetDeviceProperties, 1-2 ms per call, went the same way (SmCount).
+static std::mutex g_dev_mu;
+static cudaStream_t g_alloc_stream[64] = {};
+static int g_sm_count[64] = {};
+
+static cudaError_t AllocStream(cudaStream_t *out) {
+	int dev = 0;
+	cudaError_t e = cudaGetDevice(&dev);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	if (dev < 0 || dev >= 64) {
+		return cudaErrorInvalidDevice;
+	}
+	std::lock_guard<std::mutex> lock(g_dev_mu);
+	if (!g_alloc_stream[dev]) {
+		cudaMemPool_t pool;
+		if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+			uint64_t threshold = UINT64_MAX;
+			cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &threshold);
+		}
+		e = cudaStreamCreateWithFlags(&g_alloc_stream[dev], cudaStreamNonBlocking);
+		if (e != cudaSuccess) {
+			g_alloc_stream[dev] = nullptr;
+			return e;
+		}
+	}
+	*out = g_alloc_stream[dev];
+	return cudaSuccess;
+}
+
+#define ScanAlloc(pp, bytes) ScanAllocRaw(reinterpret_cast<void **>(pp), bytes)
+static cudaError_t ScanAllocRaw(void **p, size_t bytes) {
+	cudaStream_t st;
+	cudaError_t e = AllocStream(&st);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	void *q = nullptr;
+	e = cudaMallocAsync(&q, bytes ? bytes : 16, st);
+	if (e != cudaSuccess) {
+		return e;
+	}
+	*p = q;
+	return cudaStreamSynchronize(st);
+}
+
+static void ScanFree(void *p) {
+	cudaStream_t st;
+	if (p && AllocStream(&st) == cudaSuccess) {
+		cudaFreeAsync(p, st);
+	}
+}
+
+static cudaError_t SmCount(int device, int *out) {
+	if (device < 0 || device >= 64) {
+		return cudaErrorInvalidDevice;
+	}
+	{
+		std::lock_guard<std::mutex> lock(g_dev_mu);
+		if (g_sm_count[device]) {
+			*out = g_sm_count[device];
+			return cudaSuccess;
+		}
+	}
+	int n = 0;
+	cudaError_t e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+	if (e == cudaSuccess) {
+		std::lock_guard<std::mutex> lock(g_dev_mu);
+		g_sm_count[device] = n;
+		*out = n;
+	}
+	return e;
+}
+
 static void FreeScanDevice(b2a_scan *s) {
 	if (s->device >= 0) {
 		cudaSetDevice(s->device);
-		cudaFree(s->d_tasks);
-		cudaFree(s->d_tile_task);
-		cudaFree(s->d_variadic);
-		cudaFree(s->d_err);
-		cudaFree(s->d_image_owned);
-		cudaFree(s->d_chunk_col);
-		cudaFree(s->d_chunk_col2);
-		cudaFree(s->d_chunk_rows);
-		cudaFree(s->d_jobs);
-		cudaFree(s->d_job_order);
-		cudaFree(s->d_stage_pieces);
-		cudaFree(s->d_workspaces);
-		cudaFree(s->d_decomp_state);
+		if (s->launches || s->d_image_owned) {
+			cudaDeviceSynchronize(); // what the cudaFree of each buffer used to imply: nothing of this scan is in flight
+		}
+		ScanFree(s->d_tasks);
+		ScanFree(s->d_tile_task);
+		ScanFree(s->d_variadic);
+		ScanFree(s->d_err);
+		ScanFree(s->d_image_owned);
+		ScanFree(s->d_chunk_col);
+		ScanFree(s->d_chunk_col2);
+		ScanFree(s->d_chunk_rows);
+		ScanFree(s->d_jobs);
+		ScanFree(s->d_job_order);
+		ScanFree(s->d_stage_pieces);
+		ScanFree(s->d_workspaces);
+		ScanFree(s->d_decomp_state);
+		(void)cudaGetLastError();
 	}
 }
 
@@ -290,16 +375,14 @@ int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t ba
 	s->plan.Build(r->reader, batch_lo, batch_hi);
 	if (device >= 0) {
 		CUDA_OK(cudaSetDevice(device));
-		cudaDeviceProp prop;
-		CUDA_OK(cudaGetDeviceProperties(&prop, device));
-		s->sm_count = prop.multiProcessorCount;
+		CUDA_OK(SmCount(device, &s->sm_count));
 		const ScanPlan &p = s->plan;
 		size_t nt = p.tasks.size() ? p.tasks.size() : 1, nl = p.tile_task.size() ? p.tile_task.size() : 1,
 		       nv = p.variadic.size() ? p.variadic.size() : 1;
-		CUDA_OK(cudaMalloc(&s->d_tasks, nt * sizeof(b2a_task)));
-		CUDA_OK(cudaMalloc(&s->d_tile_task, nl * sizeof(uint32_t)));
-		CUDA_OK(cudaMalloc(&s->d_variadic, nv * sizeof(uint64_t)));
-		CUDA_OK(cudaMalloc(&s->d_err, sizeof(uint32_t)));
+		CUDA_OK(ScanAlloc(&s->d_tasks, nt * sizeof(b2a_task)));
+		CUDA_OK(ScanAlloc(&s->d_tile_task, nl * sizeof(uint32_t)));
+		CUDA_OK(ScanAlloc(&s->d_variadic, nv * sizeof(uint64_t)));
+		CUDA_OK(ScanAlloc(&s->d_err, sizeof(uint32_t)));
 		CUDA_OK(cudaMemcpy(s->d_tasks, p.tasks.data(), p.tasks.size() * sizeof(b2a_task), cudaMemcpyHostToDevice));
 		CUDA_OK(cudaMemcpy(s->d_tile_task, p.tile_task.data(), p.tile_task.size() * sizeof(uint32_t),
 		                   cudaMemcpyHostToDevice));
@@ -311,7 +394,7 @@ int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t ba
 			if (s->n_workers > p.jobs.size()) {
 				s->n_workers = static_cast<uint32_t>(p.jobs.size());
 			}
-			CUDA_OK(cudaMalloc(&s->d_jobs, p.jobs.size() * sizeof(b2a_decomp_job)));
+			CUDA_OK(ScanAlloc(&s->d_jobs, p.jobs.size() * sizeof(b2a_decomp_job)));
 			CUDA_OK(cudaMemcpy(s->d_jobs, p.jobs.data(), p.jobs.size() * sizeof(b2a_decomp_job), cudaMemcpyHostToDevice));
 			std::vector<uint32_t> order(p.jobs.size());
 			for (size_t i = 0; i < order.size(); i++) {
@@ -320,10 +403,10 @@ int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t ba
 			std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
 				return p.jobs[a].dst_len > p.jobs[b].dst_len;
 			});
-			CUDA_OK(cudaMalloc(&s->d_job_order, order.size() * sizeof(uint32_t)));
+			CUDA_OK(ScanAlloc(&s->d_job_order, order.size() * sizeof(uint32_t)));
 			CUDA_OK(cudaMemcpy(s->d_job_order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-			CUDA_OK(cudaMalloc(&s->d_workspaces, static_cast<size_t>(s->n_workers) * DecompWorkspaceBytes()));
-			CUDA_OK(cudaMalloc(&s->d_decomp_state, 2 * sizeof(uint32_t)));
+			CUDA_OK(ScanAlloc(&s->d_workspaces, static_cast<size_t>(s->n_workers) * DecompWorkspaceBytes()));
+			CUDA_OK(ScanAlloc(&s->d_decomp_state, 2 * sizeof(uint32_t)));
 			CUDA_OK(cudaMemset(s->d_decomp_state, 0, 2 * sizeof(uint32_t)));
 		}
 	}
@@ -371,7 +454,7 @@ int b2a_scan_upload(b2a_scan *s, void *cuda_stream) {
 	uint64_t bytes = p.image_hi - p.image_lo;
 	if (!s->d_image_owned) {
 		// +64: the string kernel fetches whole aligned words around the last characters
-		CUDA_OK(cudaMalloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
+		CUDA_OK(ScanAlloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
 	}
 	if (bytes) {
 		CUDA_OK(cudaMemcpyAsync(s->d_image_owned, s->r->reader.Image() + p.image_lo, bytes, cudaMemcpyHostToDevice,
@@ -653,7 +736,7 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.out, cudaStreamNonBlocking));
 	}
 	if (!s->d_image_owned) {
-		CUDA_OK(cudaMalloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
+		CUDA_OK(ScanAlloc(&s->d_image_owned, DeviceImageBytes(p) + 64));
 	}
 	s->d_image = s->d_image_owned;
 	if (to_host && hp.d_out_bytes < p.out_bytes) {
@@ -752,10 +835,13 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 			for (auto &pc : s->stage_plan.pieces) {
 				sp.push_back(ScatterPiece {pc.stage, pc.dst, pc.bytes});
 			}
-			cudaFree(s->d_stage_pieces);
+			if (s->d_stage_pieces) {
+				cudaDeviceSynchronize(); // (an earlier b2a_read_arrow_device of this scan may still be scattering)
+				ScanFree(s->d_stage_pieces);
+			}
 			s->d_stage_pieces = nullptr;
 			if (!sp.empty()) {
-				CUDA_OK(cudaMalloc(&s->d_stage_pieces, sp.size() * sizeof(ScatterPiece)));
+				CUDA_OK(ScanAlloc(&s->d_stage_pieces, sp.size() * sizeof(ScatterPiece)));
 				CUDA_OK(cudaMemcpy(s->d_stage_pieces, sp.data(), sp.size() * sizeof(ScatterPiece), cudaMemcpyHostToDevice));
 			}
 		}
@@ -1009,7 +1095,7 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 				left -= n;
 			}
 		}
-		CUDA_OK(cudaMalloc(&s->d_chunk_rows, (rows.size() ? rows.size() : 1) * sizeof(uint32_t)));
+		CUDA_OK(ScanAlloc(&s->d_chunk_rows, (rows.size() ? rows.size() : 1) * sizeof(uint32_t)));
 		CUDA_OK(cudaMemcpy(s->d_chunk_rows, rows.data(), rows.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
 	}
 	if (key == cols && *d_table) {
@@ -1028,9 +1114,12 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 			}
 		}
 	}
-	cudaFree(*d_table);
+	if (*d_table) {
+		cudaDeviceSynchronize(); // (a launch that reads the old table may be in flight; cudaFree used to wait for it)
+		ScanFree(*d_table);
+	}
 	*d_table = nullptr;
-	CUDA_OK(cudaMalloc(d_table, (table.size() ? table.size() : 1) * sizeof(uint64_t)));
+	CUDA_OK(ScanAlloc(d_table, (table.size() ? table.size() : 1) * sizeof(uint64_t)));
 	CUDA_OK(cudaMemcpy(*d_table, table.data(), table.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
 	key = cols;
 	return B2A_OK;

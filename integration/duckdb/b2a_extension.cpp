@@ -54,24 +54,10 @@ public:
 	}
 
 	bool TryInitializeScan(ClientContext &context, GlobalTableFunctionState &gstate,
-	                       LocalTableFunctionState &lstate) override {
-		// one scan thread per file, like the reference (arrow_file_scan.cpp:35-41); a second thread is turned away
-		bool expected = false;
-		if (!claimed.compare_exchange_strong(expected, true)) {
-			return false;
-		}
-		vector<idx_t> cols;
-		for (auto &index : column_indexes) {
-			cols.push_back(index.GetPrimaryIndex());
-		}
-		scanner->Begin(cols);
-		return true;
-	}
+	                       LocalTableFunctionState &lstate) override;
 
 	void Scan(ClientContext &context, GlobalTableFunctionState &global_state, LocalTableFunctionState &local_state,
-	          DataChunk &chunk) override {
-		scanner->Next(chunk);
-	}
+	          DataChunk &chunk) override;
 
 	shared_ptr<BaseUnionData> GetUnionData(idx_t file_idx) override {
 		auto data = make_shared_ptr<BaseUnionData>(file);
@@ -87,13 +73,35 @@ public:
 	unique_ptr<B2AScanner> scanner;
 
 private:
-	atomic<bool> claimed {false};
 };
 
 class B2AFileReaderOptions : public BaseFileReaderOptions {};
 
 struct B2AFileGlobalState : public GlobalTableFunctionState {};
-struct B2AFileLocalState : public LocalTableFunctionState {};
+//! one scan thread of the pipeline: the decoded slice it is walking
+struct B2AFileLocalState : public LocalTableFunctionState {
+	B2AScanner::Cursor cursor;
+};
+
+// The reference gives ONE file one scan thread (arrow_file_scan.cpp:35-41: a second thread is turned away).  Here the
+// unit is a decoded slice of the file (~256 MiB of record batches): every thread that asks (MultiFileFunction calls this
+// under its global lock, in batch_index order) gets the next one, so the operators above the scan run on all threads.
+bool B2AFileScan::TryInitializeScan(ClientContext &context, GlobalTableFunctionState &gstate,
+                                    LocalTableFunctionState &lstate) {
+	if (!scanner->Begun()) {
+		vector<idx_t> cols;
+		for (auto &index : column_indexes) {
+			cols.push_back(index.GetPrimaryIndex());
+		}
+		scanner->Begin(cols);
+	}
+	return scanner->TakeSlice(lstate.Cast<B2AFileLocalState>().cursor);
+}
+
+void B2AFileScan::Scan(ClientContext &context, GlobalTableFunctionState &global_state,
+                       LocalTableFunctionState &local_state, DataChunk &chunk) {
+	scanner->NextFrom(local_state.Cast<B2AFileLocalState>().cursor, chunk);
+}
 struct B2AMultiFileData final : public TableFunctionData {};
 
 //! reference: ArrowMultiFileInfo (src/file_scanner/arrow_multi_file_info.cpp) — no options of its own, the first file
@@ -133,10 +141,7 @@ struct B2AMultiFileInfo : MultiFileReaderInterface {
 	}
 	optional_idx MaxThreads(const MultiFileBindData &bind_data_p, const MultiFileGlobalState &global_state,
 	                        FileExpandResult expand_result) override {
-		if (expand_result == FileExpandResult::MULTIPLE_FILES) {
-			return optional_idx();
-		}
-		return 1;
+		return optional_idx(); // a single file is scanned by every thread too (slice by slice)
 	}
 	unique_ptr<GlobalTableFunctionState> InitializeGlobalState(ClientContext &context, MultiFileBindData &bind_data,
 	                                                           MultiFileGlobalState &global_state) override {

@@ -1,6 +1,9 @@
 // see b2a_scanner.hpp
 #include "b2a_scanner.hpp"
 
+#include <chrono>
+#include <cstdio>
+
 #include "duckdb/common/exception.hpp"
 #include "duckdb/common/exception/conversion_exception.hpp"
 #include "duckdb/main/query_result.hpp"
@@ -187,7 +190,8 @@ LogicalType B2AScanner::TypeOf(uint32_t flat) const {
 }
 
 
-B2AScanner::B2AScanner(b2a_reader *reader_p, int device_p) : device(device_p), reader(reader_p) {
+B2AScanner::B2AScanner(b2a_reader *reader_p, int device_p)
+    : device(device_p), reader(reader_p), bin(make_shared_ptr<B2AScanBin>()) {
 	// ArrowFileScan::ArrowFileScan (arrow_file_scan.cpp:11-26) / ScanArrowIPCBind (scan_arrow_ipc.cpp:20-48): read the
 	// schema, names + types (ArrowTableFunction::PopulateArrowTableType), de-duplicate the names
 	uint32_t n_top = 0, n_flat = 0;
@@ -217,10 +221,25 @@ B2AScanner::B2AScanner(b2a_reader *reader_p, int device_p) : device(device_p), r
 	image = const_data_ptr_cast(img);
 }
 
+B2AScanBin::~B2AScanBin() {
+	for (auto scan : scans) {
+		b2a_scan_destroy(scan);
+	}
+}
+
+void B2AScanBin::Add(b2a_scan *scan) {
+	std::lock_guard<std::mutex> guard(mu);
+	scans.push_back(scan);
+}
+
 B2AScanner::Slice::~Slice() {
 	dictionaries.clear();
 	if (scan) {
-		b2a_scan_destroy(scan);
+		if (bin) {
+			bin->Add(scan);
+		} else {
+			b2a_scan_destroy(scan);
+		}
 	}
 }
 
@@ -233,16 +252,29 @@ B2AScanner::~B2AScanner() {
 		cv.notify_all();
 		worker.join();
 	}
-	current.reset();
-	result.reset();
+	own.slice.reset();
+	ready.clear();
+	bin.reset(); // (the scans go now unless a cursor of another thread still holds a slice)
 	if (reader) {
 		b2a_reader_close(reader);
 	}
 }
 
 // ---------------------------------------------------------------------------------------------- slices
+// B2A_SCANNER_TRACE=1: wall clock of the producer's steps per slice, on stderr
+static bool ScannerTrace() {
+	static const bool on = std::getenv("B2A_SCANNER_TRACE") != nullptr;
+	return on;
+}
+static double NowMs() {
+	return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
+	const double t0 = NowMs();
+	double t1 = t0, t2 = t0;
 	auto s = make_uniq<Slice>();
+	s->bin = bin;
 	s->batch_lo = lo;
 	s->batch_hi = hi;
 	// DirectConversion columns alias the stream image (zero copy, as in the reference); everything that needs
@@ -251,6 +283,7 @@ unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
 	b2a_batch_info first;
 	bool compressed = lo < hi && b2a_reader_batch_info(reader, lo, &first) == B2A_OK && first.compressed != 0;
 	int rc = b2a_scan_create_ex(reader, device, lo, hi, compressed ? 0 : B2A_SCAN_HOST_ALIAS, &s->scan);
+	t1 = NowMs();
 	if (rc == B2A_OK) {
 		uint64_t image_lo, image_bytes, out_bytes, algorithmic, n_tasks, n_tiles;
 		b2a_scan_sizes(s->scan, &image_lo, &image_bytes, &out_bytes, &algorithmic, &n_tasks, &n_tiles);
@@ -260,6 +293,7 @@ unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
 			// vectors first, the host copy of the decompressed character buffers behind them in the same arena
 			const idx_t out_padded = (NumericCast<idx_t>(out_bytes) + 255) & ~idx_t(255);
 			s->slab = B2ASlab::Acquire(out_padded + NumericCast<idx_t>(scratch_bytes));
+			t2 = NowMs();
 			rc = b2a_read_arrow_host_scratch(s->scan, s->slab->data, scratch_bytes ? s->slab->data + out_padded : nullptr, 0);
 		} catch (std::exception &e) {
 			s->status = B2A_EOOM;
@@ -271,48 +305,101 @@ unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
 		s->status = rc;
 		s->error = b2a_last_error();
 	}
+	if (ScannerTrace()) {
+		std::fprintf(stderr, "[b2a scanner] batches %llu-%llu: scan_create %.2f ms, slab %.2f ms, read_arrow_host %.2f ms\n",
+		             static_cast<unsigned long long>(lo), static_cast<unsigned long long>(hi), t1 - t0, t2 - t1,
+		             NowMs() - t2);
+	}
 	return s;
 }
 
+B2AScanner::Cursor::Cursor() = default;
+B2AScanner::Cursor::~Cursor() = default;
+B2AScanner::Cursor::Cursor(Cursor &&) noexcept = default;
+B2AScanner::Cursor &B2AScanner::Cursor::operator=(Cursor &&) noexcept = default;
+
 void B2AScanner::WorkerLoop() {
-	while (true) {
-		uint64_t lo, hi;
+	for (idx_t k = 0; k < n_slices; k++) {
 		{
 			std::unique_lock<std::mutex> lock(mu);
-			cv.wait(lock, [&] { return stop || has_request; });
+			cv.wait(lock, [&] { return stop || ready.size() < depth; });
 			if (stop) {
 				return;
 			}
-			lo = req_lo;
-			hi = req_hi;
-			has_request = false;
 		}
-		auto s = Load(lo, hi);
+		shared_ptr<Slice> s = Load(slice_bounds[k], slice_bounds[k + 1]);
+		s->next_batch = s->batch_lo;
+		const bool failed = s->status != B2A_OK;
 		{
 			std::lock_guard<std::mutex> guard(mu);
-			result = std::move(s);
-			has_result = true;
+			ready.push_back(std::move(s));
+			produced = failed ? n_slices : k + 1; // nothing is decoded behind a failed slice
 		}
 		cv.notify_all();
+		if (failed) {
+			return;
+		}
 	}
 }
 
-void B2AScanner::Request(uint64_t slice) {
-	std::lock_guard<std::mutex> guard(mu);
-	req_lo = slice_bounds[slice];
-	req_hi = slice_bounds[slice + 1];
-	has_request = true;
-	cv.notify_all();
-}
-
-unique_ptr<B2AScanner::Slice> B2AScanner::Take() {
-	std::unique_lock<std::mutex> lock(mu);
-	cv.wait(lock, [&] { return has_result; });
-	has_result = false;
-	return std::move(result);
+bool B2AScanner::TakeSlice(Cursor &cursor) {
+	cursor.slice.reset();
+	shared_ptr<Slice> s;
+	uint64_t lo = 0, hi = 0;
+	bool first = false, drained = false;
+	{
+		std::unique_lock<std::mutex> lock(mu);
+		cv.wait(lock, [&] { return !ready.empty() || produced == n_slices; });
+		if (ready.empty()) {
+			return false;
+		}
+		s = ready.front();
+		first = s->next_batch == s->batch_lo;
+		lo = s->next_batch;
+		hi = s->status != B2A_OK ? s->batch_hi : MinValue<uint64_t>(lo + 1, s->batch_hi);
+		s->next_batch = hi;
+		if (hi >= s->batch_hi) {
+			ready.pop_front();
+			drained = true;
+		}
+	}
+	if (drained) {
+		cv.notify_all(); // room for the producer
+	}
+	if (s->status != B2A_OK) {
+		// re-raise on the executor's thread with the class the reference would have used
+		const string msg = s->error;
+		switch (s->status) {
+		case B2A_EINVAL:
+			throw InvalidInputException(msg);
+		case B2A_EIO:
+			throw IOException(msg);
+		case B2A_ENOTIMPL:
+			throw NotImplementedException(msg);
+		case B2A_ECONVERSION:
+			throw ConversionException(msg);
+		case B2A_EOOM:
+			throw OutOfMemoryException(msg);
+		case B2A_ECUDA:
+			throw IOException(msg);
+		default:
+			throw InternalException(msg);
+		}
+	}
+	if (first) {
+		gpu_launches += b2a_scan_gpu_launches(s->scan);
+	}
+	cursor.batch = lo;
+	cursor.batch_end = hi;
+	cursor.chunk_offset = 0;
+	cursor.slice = std::move(s);
+	return true;
 }
 
 void B2AScanner::Begin(const vector<idx_t> &columns) {
+	if (begun) {
+		throw InternalException("B2AScanner::Begin called twice");
+	}
 	vector<const char *> proj;
 	projected_flat.clear();
 	for (auto col : columns) {
@@ -329,10 +416,11 @@ void B2AScanner::Begin(const vector<idx_t> &columns) {
 		}
 	}
 	b2a_reader_num_batches(reader, &n_batches, &total_rows);
-	// slices of whole record batches, ~256 MiB of message bodies each
+	// slices of whole record batches, ~512 MiB of message bodies each (measured on the box, tools/bench_sql.py: 128 MiB ...
+	// 1 GiB within 15 % of each other once a scan costs 0.1 ms to create; smaller slices start the consumers earlier)
 	static const uint64_t target = [] {
 		const char *e = std::getenv("B2A_SLICE_MB");
-		return (e ? NumericCast<uint64_t>(std::atoll(e)) : 256) << 20;
+		return (e ? NumericCast<uint64_t>(std::atoll(e)) : 512) << 20;
 	}();
 	slice_bounds.clear();
 	slice_bounds.push_back(0);
@@ -350,13 +438,13 @@ void B2AScanner::Begin(const vector<idx_t> &columns) {
 		slice_bounds.push_back(n_batches);
 	}
 	n_slices = slice_bounds.size() > 1 ? slice_bounds.size() - 1 : 0;
-	requested = taken = 0;
-	current.reset();
 	rows_done = 0;
+	begun = true;
+	if (const char *e = std::getenv("B2A_SLICES_AHEAD")) {
+		depth = MaxValue<idx_t>(1, NumericCast<idx_t>(std::atoll(e)));
+	}
 	if (n_slices > 0) {
 		worker = std::thread([this] { WorkerLoop(); });
-		Request(0);
-		requested = 1;
 	}
 }
 
@@ -382,6 +470,7 @@ void B2AScanner::PointVector(Slice &slice, Vector &vec, uint32_t flat, uint64_t 
 	if (f.dict_id >= 0) {
 		// ColumnArrowToDuckDBDictionary (arrow_conversion.cpp:1360-1419): the dictionary values were decoded once per scan
 		// (+1 NULL slot at index dict_rows), the kernel already widened the indices to sel_t with NULL -> dict_rows
+		std::lock_guard<std::mutex> dict_guard(slice.dict_mu);
 		auto entry = dictionaries.find(flat);
 		if (entry == dictionaries.end()) {
 			b2a_column_out dco;
@@ -468,69 +557,46 @@ void B2AScanner::PointVector(Slice &slice, Vector &vec, uint32_t flat, uint64_t 
 	vec.GetBuffer()->SetAuxiliaryData(make_uniq<B2ASlabAuxData>(slab));
 }
 
-void B2AScanner::Next(DataChunk &chunk) {
+void B2AScanner::NextFrom(Cursor &cur, DataChunk &chunk) {
 	// ArrowTableFunction::ArrowScanFunction (duckdb/src/function/table/arrow.cpp:172-201): at most 2 048 rows per call,
 	// next record batch when the current one is exhausted.  No per-chunk conversion is left: vectors are re-pointed.
-	while (true) {
-		if (!current) {
-			if (taken == n_slices) {
-				chunk.SetCardinality(0);
-				return;
-			}
-			current = Take();
-			if (current->status != B2A_OK) {
-				string msg = current->error;
-				int status = current->status;
-				current.reset();
-				// re-raise on the executor's thread with the class the reference would have used
-				switch (status) {
-				case B2A_EINVAL:
-					throw InvalidInputException(msg);
-				case B2A_EIO:
-					throw IOException(msg);
-				case B2A_ENOTIMPL:
-					throw NotImplementedException(msg);
-				case B2A_ECONVERSION:
-					throw ConversionException(msg);
-				case B2A_EOOM:
-					throw OutOfMemoryException(msg);
-				case B2A_ECUDA:
-					throw IOException(msg);
-				default:
-					throw InternalException(msg);
-				}
-			}
-			gpu_launches += b2a_scan_gpu_launches(current->scan);
-			batch = current->batch_lo;
-			chunk_offset = 0;
-			taken++;
-			if (requested < n_slices) { // decode the following slice while this one is consumed
-				Request(requested);
-				requested++;
-			}
-		}
-		while (batch < current->batch_hi) {
+	if (cur.slice) {
+		while (cur.batch < cur.batch_end) {
 			b2a_batch_info bi;
-			b2a_reader_batch_info(reader, batch, &bi);
-			if (chunk_offset < bi.rows) {
-				const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, NumericCast<idx_t>(bi.rows) - chunk_offset);
+			b2a_reader_batch_info(reader, cur.batch, &bi);
+			if (cur.chunk_offset < bi.rows) {
+				const idx_t n = MinValue<idx_t>(STANDARD_VECTOR_SIZE, NumericCast<idx_t>(bi.rows) - cur.chunk_offset);
 				for (idx_t c = 0; c < chunk.ColumnCount() && c < projected_flat.size(); c++) {
-					PointVector(*current, chunk.data[c], projected_flat[c], batch, chunk_offset, n);
+					PointVector(*cur.slice, chunk.data[c], projected_flat[c], cur.batch, cur.chunk_offset, n);
 				}
 				chunk.SetCardinality(n);
-				chunk_offset += n;
+				cur.chunk_offset += n;
 				rows_done += n;
 				return;
 			}
-			batch++;
-			chunk_offset = 0;
+			cur.batch++;
+			cur.chunk_offset = 0;
 		}
-		current.reset(); // the slab lives on for as long as a vector points into it
+		cur.slice.reset(); // the slab lives on for as long as a vector points into it
+	}
+	chunk.SetCardinality(0);
+}
+
+void B2AScanner::Next(DataChunk &chunk) {
+	while (true) {
+		if (!own.slice && (n_slices == 0 || !TakeSlice(own))) {
+			chunk.SetCardinality(0);
+			return;
+		}
+		NextFrom(own, chunk);
+		if (chunk.size() > 0) {
+			return;
+		}
 	}
 }
 
 double B2AScanner::Progress() const {
-	return total_rows ? 100.0 * static_cast<double>(rows_done) / static_cast<double>(total_rows) : 100.0;
+	return total_rows ? 100.0 * static_cast<double>(rows_done.load()) / static_cast<double>(total_rows) : 100.0;
 }
 
 } // namespace ext_nanoarrow

@@ -8,8 +8,11 @@
 // (include/b2arrow.h); what is left here is pointing DuckDB vectors at the decoded slabs, 2 048 rows at a time —
 // the zero-copy idiom of the reference's DirectConversion (arrow_conversion.cpp:454-461), applied to every type.
 //
-// The stream is decoded in slices of whole record batches; while DuckDB consumes slice i a worker thread runs
-// b2a_read_arrow_host for slice i + 1 (PCIe both ways + kernels overlap the executor).
+// The stream is decoded in slices of whole record batches by one producer thread (b2a_read_arrow_host per slice: PCIe both
+// ways + kernels overlap the executor), a few slices ahead of the consumers.  A consumer is a Cursor: one DuckDB scan thread
+// holding one record batch of a decoded slice and walking its 2 048-row vectors — the reference gives ONE file one scan
+// thread (arrow_file_scan.cpp:35-41); here every thread of the pipeline takes the next record batch of the same file, in
+// order (slices are large so that PCIe runs at its rate, the unit handed to a thread is small so that the last one is).
 //===----------------------------------------------------------------------===//
 #pragma once
 
@@ -19,7 +22,9 @@
 #include "duckdb/common/types/vector.hpp"
 #include "duckdb/common/unordered_map.hpp"
 
+#include <atomic>
 #include <condition_variable>
+#include <deque>
 #include <mutex>
 #include <thread>
 
@@ -50,8 +55,31 @@ struct B2ASlabAuxData : public VectorAuxiliaryData {
 	shared_ptr<B2ASlab> slab;
 };
 
+//! Finished b2a_scan handles of one scanner, destroyed together when the last slice and the scanner are gone:
+//! b2a_scan_destroy frees device memory, cudaFree waits for the device — in the middle of a scan that would stall the
+//! producer's pipeline once per slice
+struct B2AScanBin {
+	~B2AScanBin();
+	void Add(b2a_scan *scan);
+	std::mutex mu;
+	vector<b2a_scan *> scans;
+};
+
 class B2AScanner {
+	struct Slice;
+
 public:
+	//! One consumer's position: the slice it holds and where in it the next vector starts
+	struct Cursor {
+		Cursor();
+		~Cursor();
+		Cursor(Cursor &&) noexcept;
+		Cursor &operator=(Cursor &&) noexcept;
+		shared_ptr<Slice> slice;
+		uint64_t batch = 0, batch_end = 0; // record batches [batch, batch_end) of the slice are this cursor's
+		idx_t chunk_offset = 0;
+	};
+
 	//! takes ownership of `reader` (b2a_reader_open_file / b2a_reader_open_buffers)
 	B2AScanner(b2a_reader *reader, int device);
 	~B2AScanner();
@@ -63,10 +91,17 @@ public:
 		return types;
 	}
 	//! projection pushdown (IPCStreamReader::SetColumnProjection, base_stream_reader.cpp:146-212): `columns` = top-level
-	//! column index behind every column of the chunks Next() will fill; starts decoding the first slice
+	//! column index behind every column of the chunks that will be filled; starts the producer.  Once per scanner.
 	void Begin(const vector<idx_t> &columns);
-	//! ArrowScanFunction: at most STANDARD_VECTOR_SIZE rows per call, 0 rows = end of stream
+	bool Begun() const {
+		return begun;
+	}
+	//! ArrowScanFunction for a single consumer: at most STANDARD_VECTOR_SIZE rows per call, 0 rows = end of stream
 	void Next(DataChunk &chunk);
+	//! Several consumers: TakeSlice gives `cursor` the next record batch of the stream (false: none left; blocks while the
+	//! producer is still decoding its slice; thread-safe), NextFrom fills `chunk` from the cursor's rows (0 rows: exhausted)
+	bool TakeSlice(Cursor &cursor);
+	void NextFrom(Cursor &cursor, DataChunk &chunk);
 	//! 0..100
 	double Progress() const;
 	uint64_t GpuLaunches() const {
@@ -76,9 +111,12 @@ public:
 private:
 	struct Slice {
 		b2a_scan *scan = nullptr;
+		shared_ptr<B2AScanBin> bin;
 		shared_ptr<B2ASlab> slab;
 		uint64_t batch_lo = 0, batch_hi = 0;
+		std::mutex dict_mu; // a slice is shared by the cursors that walk its record batches
 		unordered_map<uint32_t, unique_ptr<Vector>> dictionaries; // flat field -> decoded dictionary values
+		uint64_t next_batch = 0; // first record batch not yet handed to a cursor (under B2AScanner::mu)
 		int status = 0;
 		string error;
 		~Slice();
@@ -87,8 +125,6 @@ private:
 	LogicalType TypeOf(uint32_t flat) const;
 	void PointVector(Slice &slice, Vector &vec, uint32_t flat, uint64_t batch, idx_t offset, idx_t count);
 	unique_ptr<Slice> Load(uint64_t lo, uint64_t hi);
-	void Request(uint64_t slice);
-	unique_ptr<Slice> Take();
 	void WorkerLoop();
 
 	int device;
@@ -100,20 +136,22 @@ private:
 	vector<uint32_t> projected_flat;
 	const_data_ptr_t image = nullptr;
 	vector<uint64_t> slice_bounds; // batch index where slice k starts (+ end)
-	uint64_t n_batches = 0, total_rows = 0, rows_done = 0;
-	idx_t n_slices = 0, requested = 0, taken = 0;
-	unique_ptr<Slice> current;
-	uint64_t batch = 0;
-	idx_t chunk_offset = 0;
-	uint64_t gpu_launches = 0;
+	uint64_t n_batches = 0, total_rows = 0;
+	idx_t n_slices = 0;
+	bool begun = false;
+	std::atomic<uint64_t> rows_done {0};
+	std::atomic<uint64_t> gpu_launches {0};
+	Cursor own; // the single consumer of Next()
+	shared_ptr<B2AScanBin> bin;
 
-	// prefetch worker (one thread per scanner: the C ABI keeps its streams / staging per thread and device)
+	// producer (one thread per scanner: the C ABI keeps its streams / staging per thread and device): decodes the slices
+	// in order, at most `depth` finished ones waiting
 	std::thread worker;
 	std::mutex mu;
 	std::condition_variable cv;
-	bool stop = false, has_request = false, has_result = false;
-	uint64_t req_lo = 0, req_hi = 0;
-	unique_ptr<Slice> result;
+	bool stop = false;
+	idx_t produced = 0, handed_out = 0, depth = 2;
+	std::deque<shared_ptr<Slice>> ready;
 };
 
 } // namespace ext_nanoarrow
