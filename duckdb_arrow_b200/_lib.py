@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("B2A_LIB") or os.path.join(HERE, "libb2arrow.so")
 B2A_NONE = 0xFFFFFFFFFFFFFFFF
 VECTOR_SIZE = 2048
 SCAN_HOST_ALIAS = 0x1
+SCAN_DEVICE_ALIAS = 0x2
 
 STATUS = {0: "OK", 1: "InvalidInputException", 2: "IOException", 3: "NotImplementedException",
           4: "ConversionException", 5: "CudaError", 6: "InternalException", 7: "OutOfMemoryException"}

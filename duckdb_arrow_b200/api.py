@@ -169,8 +169,10 @@ class ArrowScan:
     """One scan of a batch range of a reader on one GPU (b2a_scan)."""
 
     def __init__(self, reader: ArrowIPCReader, device: int = 0, batch_lo: int = 0, batch_hi: int | None = None,
-                 host_alias: bool = False):
-        """host_alias: B2A_SCAN_HOST_ALIAS — DirectConversion columns stay in the host image (zero copy, like the
+                 host_alias: bool = False, device_alias: bool = False):
+        """device_alias: B2A_SCAN_DEVICE_ALIAS — DirectConversion columns stay in the DEVICE image for device consumers
+        (filter / sum_product): no copy into the arena.
+        host_alias: B2A_SCAN_HOST_ALIAS — DirectConversion columns stay in the host image (zero copy, like the
         reference); such a scan is consumed through read_host() only."""
         self.reader = reader
         self.device = device
@@ -178,7 +180,9 @@ class ArrowScan:
         hi = reader.num_batches if batch_hi is None else batch_hi
         self.batch_lo, self.batch_hi = batch_lo, hi
         h = C.c_void_p()
-        check(lib.b2a_scan_create_ex(reader._h, device, batch_lo, hi, _lib.SCAN_HOST_ALIAS if host_alias else 0,
+        self.device_alias = device_alias
+        flags = (_lib.SCAN_HOST_ALIAS if host_alias else 0) | (_lib.SCAN_DEVICE_ALIAS if device_alias else 0)
+        check(lib.b2a_scan_create_ex(reader._h, device, batch_lo, hi, flags,
                                      C.byref(h)))
         self._h = h
         ub = C.c_uint64()
@@ -249,7 +253,7 @@ class ArrowScan:
     def alloc_out(self):
         torch = self._torch()
         if self.d_out is None:
-            self.d_out = torch.empty(self.out_bytes, dtype=torch.uint8, device=f"cuda:{self.device}")
+            self.d_out = torch.empty(max(self.out_bytes, 256), dtype=torch.uint8, device=f"cuda:{self.device}")
         return self.d_out
 
     def decode(self, d_out=None, string_ptr_base: int = 0):
@@ -274,7 +278,7 @@ class ArrowScan:
         """b2a_read_arrow_host: host image -> (pipelined H2D, decode, D2H) -> host vectors in pinned memory."""
         torch = self._torch()
         if h_out is None:
-            h_out = torch.empty(self.out_bytes, dtype=torch.uint8, pin_memory=True)
+            h_out = torch.empty(max(self.out_bytes, 256), dtype=torch.uint8, pin_memory=True)
         check(lib.b2a_read_arrow_host(self._h, C.c_void_p(h_out.data_ptr()), n_slices))
         self._h_out = h_out
         return h_out.numpy()

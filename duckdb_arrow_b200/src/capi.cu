@@ -365,13 +365,17 @@ int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch
 int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, uint32_t flags,
                        b2a_scan **out) {
 	B2A_TRY
-	if (flags & ~B2A_SCAN_HOST_ALIAS) {
+	if (flags & ~(B2A_SCAN_HOST_ALIAS | B2A_SCAN_DEVICE_ALIAS)) {
 		return Fail(B2A_EINVAL, "unknown scan flags");
+	}
+	if ((flags & B2A_SCAN_HOST_ALIAS) && (flags & B2A_SCAN_DEVICE_ALIAS)) {
+		return Fail(B2A_EINVAL, "B2A_SCAN_HOST_ALIAS and B2A_SCAN_DEVICE_ALIAS exclude each other");
 	}
 	std::unique_ptr<b2a_scan> s(new b2a_scan());
 	s->r = r;
 	s->device = device;
-	s->plan.alias_direct = (flags & B2A_SCAN_HOST_ALIAS) != 0;
+	s->plan.alias_direct = (flags & (B2A_SCAN_HOST_ALIAS | B2A_SCAN_DEVICE_ALIAS)) != 0;
+	s->plan.alias_on_device = (flags & B2A_SCAN_DEVICE_ALIAS) != 0;
 	s->plan.Build(r->reader, batch_lo, batch_hi);
 	if (device >= 0) {
 		CUDA_OK(cudaSetDevice(device));
@@ -474,7 +478,7 @@ int b2a_scan_set_device_image(b2a_scan *s, const void *d_image) {
 
 int b2a_scan_decode(b2a_scan *s, void *d_out, uint64_t string_ptr_base, void *cuda_stream) {
 	NEED_DEVICE(s);
-	if (s->plan.alias_direct) {
+	if (s->plan.alias_direct && !s->plan.alias_on_device) {
 		return Fail(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan has host-resident direct columns: use b2a_read_arrow_host");
 	}
 	if (!s->d_image) {
@@ -727,6 +731,10 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
                              void *h_scratch = nullptr) {
 	NEED_DEVICE(s);
 	const ScanPlan &p = s->plan;
+	if (p.alias_on_device && d_out_user == nullptr) {
+		return Fail(B2A_EINVAL, "a B2A_SCAN_DEVICE_ALIAS scan leaves its direct columns in the device image: use "
+		                        "b2a_read_arrow_device / b2a_scan_decode");
+	}
 	HostPipe &hp = g_pipes[s->device];
 	hp.device = s->device;
 	const bool to_host = d_out_user == nullptr;
@@ -1046,7 +1054,7 @@ extern "C" int b2a_read_arrow_host_scratch(b2a_scan *s, void *h_out_pinned, void
 extern "C" int b2a_read_arrow_device(b2a_scan *s, void *d_out, uint32_t n_slices, void *cuda_stream) {
 	B2A_TRY
 	NEED_DEVICE(s);
-	if (s->plan.alias_direct) {
+	if (s->plan.alias_direct && !s->plan.alias_on_device) {
 		return Fail(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan keeps its direct columns on the host: device consumers need "
 		                        "a scan created without the flag");
 	}
@@ -1059,10 +1067,13 @@ extern "C" int b2a_read_arrow_device(b2a_scan *s, void *d_out, uint32_t n_slices
 
 // ------------------------------------------------------------------ filter / aggregate consumers
 // Builds (and caches) the per-chunk column table for the given projected top-level columns.
-static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vector<uint32_t> &key, uint64_t **d_table,
-                      std::vector<uint8_t> *widths) {
+// A column a B2A_SCAN_DEVICE_ALIAS scan left in the device image is addressed through the same `arena + offset` form the
+// kernels use: offset = (address in the image) - (arena address), modulo 2^64.
+static int ChunkTable(b2a_scan *s, const void *d_out, const std::vector<uint32_t> &cols_in, std::vector<uint32_t> &key,
+                      uint64_t **d_table, std::vector<uint8_t> *widths) {
 	const ScanPlan &p = s->plan;
-	if (p.alias_direct) {
+	std::vector<uint32_t> cols = cols_in;
+	if (p.alias_direct && !p.alias_on_device) {
 		return Fail(B2A_EINVAL, "filters / aggregates need device-resident vectors: create the scan without "
 		                        "B2A_SCAN_HOST_ALIAS");
 	}
@@ -1098,9 +1109,23 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 		CUDA_OK(ScanAlloc(&s->d_chunk_rows, (rows.size() ? rows.size() : 1) * sizeof(uint32_t)));
 		CUDA_OK(cudaMemcpy(s->d_chunk_rows, rows.data(), rows.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
 	}
-	if (key == cols && *d_table) {
+	std::vector<uint32_t> want = cols;
+	if (p.alias_on_device) { // the table holds addresses relative to THIS arena and THIS image
+		if (!s->d_image) {
+			return Fail(B2A_EINVAL, "no device image: call b2a_scan_upload, b2a_scan_set_device_image or "
+			                        "b2a_read_arrow_device first");
+		}
+		const uint64_t a = reinterpret_cast<uint64_t>(d_out), b = reinterpret_cast<uint64_t>(s->d_image);
+		for (uint64_t v : {a, b}) {
+			want.push_back(static_cast<uint32_t>(v));
+			want.push_back(static_cast<uint32_t>(v >> 32));
+		}
+	}
+	if (key == want && *d_table) {
 		return B2A_OK;
 	}
+	const uint64_t image_delta =
+	    reinterpret_cast<uint64_t>(s->d_image) - p.image_lo - reinterpret_cast<uint64_t>(d_out); // (alias columns only)
 	std::vector<uint64_t> table;
 	table.reserve(p.n_chunks * 2 * cols.size());
 	for (uint64_t b = 0; b < p.batch_rows.size(); b++) {
@@ -1109,7 +1134,8 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 			for (size_t c = 0; c < flats.size(); c++) {
 				const b2a_column_out &co = p.Column(p.batch_lo + b, static_cast<uint32_t>(flats[c]));
 				const Field &f = *schema.flat[static_cast<size_t>(flats[c])];
-				table.push_back(co.data_off + k * B2A_VECTOR_SIZE * static_cast<uint64_t>(f.out_width));
+				const uint64_t base = co.data_off != B2A_NONE ? co.data_off : image_delta + co.image_off;
+				table.push_back(base + k * B2A_VECTOR_SIZE * static_cast<uint64_t>(f.out_width));
 				table.push_back(co.validity_off == B2A_NONE ? B2A_NONE : co.validity_off + k * (B2A_VECTOR_SIZE / 8));
 			}
 		}
@@ -1121,17 +1147,22 @@ static int ChunkTable(b2a_scan *s, const std::vector<uint32_t> &cols, std::vecto
 	*d_table = nullptr;
 	CUDA_OK(ScanAlloc(d_table, (table.size() ? table.size() : 1) * sizeof(uint64_t)));
 	CUDA_OK(cudaMemcpy(*d_table, table.data(), table.size() * sizeof(uint64_t), cudaMemcpyHostToDevice));
-	key = cols;
+	key = want;
 	return B2A_OK;
 }
 
-extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds,
+extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predicate *preds_in, uint32_t n_preds,
                                void *d_sel, void *d_count, void *d_total, void *cuda_stream) {
 	B2A_TRY
 	NEED_DEVICE(s);
-	if (n_preds == 0 || n_preds > 8) {
+	if (n_preds == 0 || n_preds > 8 || !preds_in) {
 		return Fail(B2A_EINVAL, "between 1 and 8 predicates are supported");
 	}
+	// predicates on the same column next to each other (the kernel then loads the column once); AND does not care
+	std::vector<b2a_predicate> sorted(preds_in, preds_in + n_preds);
+	std::stable_sort(sorted.begin(), sorted.end(),
+	                 [](const b2a_predicate &a, const b2a_predicate &b) { return a.column < b.column; });
+	const b2a_predicate *preds = sorted.data();
 	std::vector<uint32_t> cols;
 	for (uint32_t i = 0; i < n_preds; i++) {
 		cols.push_back(preds[i].column);
@@ -1140,7 +1171,7 @@ extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predica
 		}
 	}
 	std::vector<uint8_t> widths;
-	int rc = ChunkTable(s, cols, s->chunk_col_key, &s->d_chunk_col, &widths);
+	int rc = ChunkTable(s, d_out, cols, s->chunk_col_key, &s->d_chunk_col, &widths);
 	if (rc != B2A_OK) {
 		return rc;
 	}
@@ -1175,16 +1206,20 @@ extern "C" int b2a_scan_filter(b2a_scan *s, const void *d_out, const b2a_predica
 // forbid cudaMalloc): the per-chunk tables are built on the host on every call and copied into the fixed __device__
 // array of kernels/filter.cu — no cudaMalloc, cudaFree or allocating library call on this path, nothing cached in the
 // scan.  Same validation, same kernel, same results as b2a_scan_filter.
-extern "C" int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds,
+extern "C" int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2a_predicate *preds_in, uint32_t n_preds,
                                         void *d_sel, void *d_count, void *d_total, void *cuda_stream) {
 	B2A_TRY
 	NEED_DEVICE(s);
 	if (n_preds == 0 || n_preds > 8) {
 		return Fail(B2A_EINVAL, "between 1 and 8 predicates are supported");
 	}
-	if (!preds || !d_out || !d_sel || !d_count || !d_total) {
+	if (!preds_in || !d_out || !d_sel || !d_count || !d_total) {
 		return Fail(B2A_EINVAL, "b2a_scan_filter_no_alloc: null argument");
 	}
+	std::vector<b2a_predicate> sorted(preds_in, preds_in + n_preds); // same order as b2a_scan_filter: columns together
+	std::stable_sort(sorted.begin(), sorted.end(),
+	                 [](const b2a_predicate &a, const b2a_predicate &b) { return a.column < b.column; });
+	const b2a_predicate *preds = sorted.data();
 	const ScanPlan &p = s->plan;
 	if (p.alias_direct) {
 		return Fail(B2A_EINVAL, "filters / aggregates need device-resident vectors: create the scan without "
@@ -1268,7 +1303,7 @@ extern "C" int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col
 	NEED_DEVICE(s);
 	std::vector<uint32_t> cols = {col_a, col_b};
 	std::vector<uint8_t> widths;
-	int rc = ChunkTable(s, cols, s->chunk_col2_key, &s->d_chunk_col2, &widths);
+	int rc = ChunkTable(s, d_out, cols, s->chunk_col2_key, &s->d_chunk_col2, &widths);
 	if (rc != B2A_OK) {
 		return rc;
 	}

@@ -15,25 +15,9 @@ static constexpr int kFilterThreads = 256;
 struct FilterParams {
 	b2a_predicate preds[8];
 	uint8_t widths[8];
+	uint8_t same_column[8]; // predicate p reads the column of predicate p - 1: its values are in registers already
 	uint32_t n_preds;
 };
-
-__device__ __forceinline__ bool cmp_i64(int64_t v, uint32_t cmp, int64_t c) {
-	switch (cmp) {
-	case B2A_CMP_EQ:
-		return v == c;
-	case B2A_CMP_NE:
-		return v != c;
-	case B2A_CMP_LT:
-		return v < c;
-	case B2A_CMP_LE:
-		return v <= c;
-	case B2A_CMP_GT:
-		return v > c;
-	default:
-		return v >= c;
-	}
-}
 
 // chunk_col: per chunk, per predicate: {arena offset of the chunk's first value, arena offset of the chunk's first
 // validity word or B2A_NONE_OFF}
@@ -54,27 +38,52 @@ __device__ __forceinline__ void load_pred_values(const uint8_t *__restrict__ p, 
 	}
 }
 
-__global__ void __launch_bounds__(kFilterThreads)
+__global__ void __launch_bounds__(kFilterThreads, 8)
     b2a_filter_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
                       const uint32_t *__restrict__ chunk_rows, uint64_t n_chunks, FilterParams fp,
                       uint32_t *__restrict__ sel, uint32_t *__restrict__ count, unsigned long long *total) {
 	constexpr int kWarps = kFilterThreads / 32;
 	__shared__ uint32_t counts[kFilterRowsPerThread * kWarps]; // (k, warp) -> passing rows, then exclusive prefix
 	__shared__ uint32_t chunk_total;
+	// the vector's table entries ({data, validity} offset per predicate + its row count), fetched one vector ahead by the
+	// first threads of the CTA: no vector starts with an exposed table -> data dependent-load pair
+	__shared__ uint64_t s_tbl[2][16];
+	__shared__ uint32_t s_rows[2];
 	const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-	for (uint64_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-		const uint32_t rows = __ldg(chunk_rows + chunk);
-		const uint64_t *cc = chunk_col + chunk * 2 * fp.n_preds;
+	const uint32_t n_entries = 2 * fp.n_preds;
+	if (blockIdx.x < n_chunks) {
+		if (threadIdx.x < n_entries) {
+			s_tbl[0][threadIdx.x] = __ldg(chunk_col + static_cast<uint64_t>(blockIdx.x) * n_entries + threadIdx.x);
+		}
+		if (threadIdx.x == 32) {
+			s_rows[0] = __ldg(chunk_rows + blockIdx.x);
+		}
+	}
+	__syncthreads();
+	uint32_t cur = 0;
+	for (uint64_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, cur ^= 1u) {
+		const uint64_t next = chunk + gridDim.x;
+		if (next < n_chunks) { // (visible after this iteration's barriers; the buffer was last read two vectors ago)
+			if (threadIdx.x < n_entries) {
+				s_tbl[cur ^ 1u][threadIdx.x] = __ldg(chunk_col + next * n_entries + threadIdx.x);
+			}
+			if (threadIdx.x == 32) {
+				s_rows[cur ^ 1u] = __ldg(chunk_rows + next);
+			}
+		}
+		const uint32_t rows = s_rows[cur];
+		const uint64_t *cc = s_tbl[cur];
 		uint32_t *csel = sel + chunk * B2A_VECTOR_SIZE;
 		uint32_t pass = 0; // bit k: row k * 256 + thread passes
 #pragma unroll
 		for (int k = 0; k < kFilterRowsPerThread; k++) {
 			pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
 		}
+		int64_t v[kFilterRowsPerThread];
 		for (uint32_t p = 0; p < fp.n_preds; p++) {
-			const uint64_t doff = __ldg(cc + 2 * p), voff = __ldg(cc + 2 * p + 1);
-			int64_t v[kFilterRowsPerThread];
-			switch (fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
+			const bool reuse = fp.same_column[p] != 0; // (values loaded and masked by NULLs under the previous predicate)
+			const uint64_t doff = cc[2 * p], voff = reuse ? B2A_NONE_OFF : cc[2 * p + 1];
+			switch (reuse ? 0xFFu : fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
 			case 1:
 				load_pred_values<int8_t>(out + doff, rows, v);
 				break;
@@ -93,6 +102,8 @@ __global__ void __launch_bounds__(kFilterThreads)
 			case 0x84:
 				load_pred_values<uint32_t>(out + doff, rows, v);
 				break;
+			case 0xFF:
+				break;
 			default:
 				load_pred_values<int64_t>(out + doff, rows, v);
 				break;
@@ -109,13 +120,19 @@ __global__ void __launch_bounds__(kFilterThreads)
 					}
 				}
 			}
+			// the comparison as a truth table over {v < c, v == c, v > c} (bits 0, 1, 2): no branch on the operator per value
 			const uint32_t cmp = fp.preds[p].cmp;
+			const uint32_t accept = cmp == B2A_CMP_EQ   ? 2u
+			                        : cmp == B2A_CMP_NE ? 5u
+			                        : cmp == B2A_CMP_LT ? 1u
+			                        : cmp == B2A_CMP_LE ? 3u
+			                        : cmp == B2A_CMP_GT ? 4u
+			                                            : 6u;
 			const int64_t c = fp.preds[p].constant;
 #pragma unroll
 			for (int k = 0; k < kFilterRowsPerThread; k++) {
-				if (!cmp_i64(v[k], cmp, c)) {
-					pass &= ~(1u << k);
-				}
+				const uint32_t which = v[k] < c ? 0u : (v[k] == c ? 1u : 2u);
+				pass &= ~((((accept >> which) & 1u) ^ 1u) << k);
 			}
 		}
 		// ---- compaction: ascending row order = k-major, then warp, then lane
@@ -172,8 +189,23 @@ int LaunchFilter(const FilterLaunch &l, void *stream) {
 	for (uint32_t i = 0; i < l.n_preds; i++) {
 		fp.preds[i] = l.preds[i];
 		fp.widths[i] = l.widths[i];
+		fp.same_column[i] = i > 0 && l.preds[i].column == l.preds[i - 1].column;
 	}
-	uint64_t grid = static_cast<uint64_t>(l.sm_count) * 8;
+	// one wave of resident CTAs striding over the vectors (a grid of 8 per SM at 6 resident left a third wave-tail)
+	static int per_sm_cached[64] = {};
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+		dev = 0;
+	}
+	if (per_sm_cached[dev] == 0) {
+		int per_sm = 0;
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2a_filter_kernel, kFilterThreads, 0) != cudaSuccess ||
+		    per_sm <= 0) {
+			per_sm = 4;
+		}
+		per_sm_cached[dev] = per_sm;
+	}
+	uint64_t grid = static_cast<uint64_t>(l.sm_count) * static_cast<uint64_t>(per_sm_cached[dev]);
 	if (grid > l.n_chunks) {
 		grid = l.n_chunks;
 	}

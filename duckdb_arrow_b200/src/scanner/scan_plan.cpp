@@ -40,7 +40,8 @@ RecordBatch ScanPlan::VirtualBatch(const Reader &reader, const RecordBatch &rb) 
 	// reference fails on it for want of a decompressor; here it is decoded by kernels/lz4_decode.cuh)
 	const uint32_t frame_codec = rb.compression == 1 ? B2A_CODEC_ZSTD : B2A_CODEC_LZ4;
 	if (alias_direct) {
-		throw Error(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS scan cannot alias compressed bodies: create the scan without it");
+		throw Error(B2A_EINVAL, "a B2A_SCAN_HOST_ALIAS / B2A_SCAN_DEVICE_ALIAS scan cannot alias compressed bodies: create "
+		                        "the scan without it");
 	}
 	RecordBatch v = rb;
 	const uint8_t *image = reader.Image();
@@ -589,7 +590,10 @@ void ScanPlan::EmitField(const Reader &reader, const Field &f, const RecordBatch
 		const uint64_t sw = static_cast<uint64_t>(f.src_width), dw = static_cast<uint64_t>(f.out_width);
 		NeedBytes(bufs[1], L * sw, f, "data");
 		if (alias_direct && f.op == B2A_OP_COPY && (!big_endian || sw == 1)) {
-			slot.image_off = bufs[1].offset; // DirectConversion: the host vector points at the Arrow buffer itself
+			slot.image_off = bufs[1].offset; // DirectConversion: the vector points at the Arrow buffer itself
+			if (alias_on_device) {
+				Touch(bufs[1].offset, L * sw); // (read in place by device consumers: part of the upload)
+			}
 			break;
 		}
 		t.src = bufs[1].offset;

@@ -38,6 +38,7 @@ struct ScanPlan {
 
 	// host-alias mode (B2A_SCAN_HOST_ALIAS): DirectConversion columns alias the host image, no task is emitted
 	bool alias_direct = false;
+	bool alias_on_device = false; // B2A_SCAN_DEVICE_ALIAS: the aliased buffers are read on the device, so they are uploaded
 	// image ranges the tasks of each batch read (merged when close), + the ranges of the dictionary batches;
 	// the host path uploads exactly these
 	typedef std::vector<std::pair<uint64_t, uint64_t>> RangeList;

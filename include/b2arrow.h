@@ -222,6 +222,14 @@ int b2a_scan_create(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch
  * need real conversion work (strings, bools, validity, lists, scalar transforms, swapped endianness) are uploaded,
  * converted and downloaded.  Such a scan can be used with b2a_read_arrow_host only. */
 #define B2A_SCAN_HOST_ALIAS 0x1u
+/* B2A_SCAN_DEVICE_ALIAS = the same zero-copy rule for consumers that live on the DEVICE (b2a_scan_filter,
+ * b2a_scan_sum_product, a caller's own kernels): DirectConversion columns are uploaded with the image but not copied into
+ * the arena — b2a_column_out.image_off says where in the DEVICE image (d_image + image_off - image_lo) the vector is,
+ * data_off is B2A_NONE; validity masks and every column that needs conversion are decoded into the arena as usual.
+ * A Q6-shaped scan (four fixed-width columns) then runs no decode launch at all.  For b2a_scan_decode /
+ * b2a_read_arrow_device; not for b2a_read_arrow_host (a host consumer cannot follow a device address), not with
+ * B2A_SCAN_HOST_ALIAS, not for compressed bodies. */
+#define B2A_SCAN_DEVICE_ALIAS 0x2u
 int b2a_scan_create_ex(b2a_reader *r, int device, uint64_t batch_lo, uint64_t batch_hi, uint32_t flags, b2a_scan **out);
 void b2a_scan_destroy(b2a_scan *s);
 int b2a_scan_sizes(b2a_scan *s, uint64_t *image_lo, uint64_t *image_bytes, uint64_t *out_bytes,

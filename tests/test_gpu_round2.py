@@ -253,3 +253,80 @@ def test_arrow_file_through_the_footer_index(b2a, cuda_device, tmp_path):
     assert ds.reader.used_footer and ds.num_rows == t.num_rows
     f = ipc.open_file(p)
     compare_scan_with_oracle(ds, [f.get_batch(i) for i in range(f.num_record_batches)])
+
+
+def test_device_alias_scan_feeds_the_consumers_from_the_image(b2a, cuda_device):
+    """B2A_SCAN_DEVICE_ALIAS: DirectConversion columns stay in the device image (the reference's zero-copy rule,
+    arrow_conversion.cpp:454-461, for consumers that live on the device) — no decode work for a Q6-shaped projection, the
+    filter and the aggregate read the Arrow buffers in place and give the same selection vectors and the reference's answer"""
+    import torch
+    cols = ["l_quantity", "l_extendedprice", "l_discount", "l_shipdate"]
+    r = b2a.ArrowIPCReader.open_file(DBGEN)
+    r.set_projection(cols)
+    alias = b2a.ArrowScan(r, device=0, device_alias=True)
+    r2 = b2a.ArrowIPCReader.open_file(DBGEN)
+    r2.set_projection(cols)
+    plain = b2a.ArrowScan(r2, device=0)
+    assert alias.n_tiles == 0 and plain.n_tiles > 0, "nothing to convert: no decode launch"
+    assert alias.upload_bytes == plain.upload_bytes, "the aliased buffers still cross PCIe"
+    f = next(x for x in r.output_columns() if x.name == "l_quantity")
+    co, cp = alias.column(0, f.index), plain.column(0, f.index)
+    none = (1 << 64) - 1
+    assert co.data_off == none and co.image_off != none and cp.data_off != none and cp.image_off == none
+    for s in (alias, plain):
+        s.upload()
+        s.decode()
+        s.finish()
+    assert alias.gpu_launches == 0
+    n, total_s = ANSWERS["q6_count_sum"]
+    sel_a, cnt_a, tot_a = alias.filter(Q6_PREDS)
+    sel_p, cnt_p, tot_p = plain.filter(Q6_PREDS)
+    assert int(tot_a.item()) == int(tot_p.item()) == int(n)
+    assert torch.equal(cnt_a, cnt_p)
+    keep = torch.arange(2048, device="cuda:0")[None, :] < cnt_a[:, None]
+    assert torch.equal(sel_a.view(-1, 2048)[keep], sel_p.view(-1, 2048)[keep])
+    revenue = alias.sum_product("l_extendedprice", "l_discount", sel_a, cnt_a)
+    assert f"{revenue // 10000}.{revenue % 10000:04d}" == total_s
+    assert alias.sum_product("l_extendedprice", "l_discount") == plain.sum_product("l_extendedprice", "l_discount")
+    # the same through the pipelined upload (read_device), on a fresh scan
+    r3 = b2a.ArrowIPCReader.open_file(DBGEN)
+    r3.set_projection(cols)
+    piped = b2a.ArrowScan(r3, device=0, device_alias=True)
+    piped.d_out = piped.read_device(n_slices=2)
+    _, _, tot = piped.filter(Q6_PREDS)
+    assert int(tot.item()) == int(n)
+
+
+def test_device_alias_with_nulls_strings_and_host_consumers(b2a, cuda_device):
+    """columns with NULLs keep their masks in the arena, strings are decoded as usual, only the fixed-width data is
+    aliased; a host consumer (read_host) is refused, and so is the combination with the host alias"""
+    import torch
+    rng = np.random.default_rng(3)
+    n = 10_000
+    k = pa.array(rng.integers(-1000, 1000, n), pa.int64(), mask=rng.random(n) < 0.2)
+    d = pa.array(rng.integers(0, 20000, n).astype(np.int32), pa.date32())
+    s = pa.array([None if i % 9 == 0 else "s%d" % i for i in range(n)], pa.string())
+    buf = _stream(pa.table({"k": k, "d": d, "s": s}), chunk=3000)
+    preds = [("k", ">=", 0), ("d", "<", 15000)]
+    res = []
+    for device_alias in (True, False):
+        r = b2a.ArrowIPCReader.open_buffers([buf])
+        scan = b2a.ArrowScan(r, device=0, device_alias=device_alias)
+        scan.upload()
+        scan.decode()
+        scan.finish()
+        sel, cnt, tot = scan.filter(preds)
+        res.append((sel.view(-1, 2048).cpu(), cnt.cpu(), int(tot.item())))
+        if device_alias:
+            assert scan.gpu_launches >= 1  # the strings and the masks were decoded
+            with pytest.raises(b2a.B2AError, match="DEVICE_ALIAS"):
+                scan.read_host()
+    (sa, ca, ta), (sp, cp, tp) = res
+    kk = np.asarray(k.fill_null(-1).to_numpy(zero_copy_only=False))
+    want = int(((kk >= 0) & np.asarray(k.is_valid()) & (np.asarray(d.cast(pa.int32())) < 15000)).sum())
+    assert ta == tp == want
+    assert torch.equal(ca, cp)
+    keep = torch.arange(2048)[None, :] < ca[:, None]
+    assert torch.equal(sa[keep], sp[keep])
+    with pytest.raises(b2a.B2AError, match="exclude each other"):
+        b2a.ArrowScan(b2a.ArrowIPCReader.open_buffers([buf]), device=0, device_alias=True, host_alias=True)
