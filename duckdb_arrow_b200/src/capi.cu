@@ -673,7 +673,7 @@ struct HostPipe {
 	HostPipe() = default;
 	HostPipe(const HostPipe &) = delete;
 	HostPipe &operator=(const HostPipe &) = delete;
-	// a DuckDB-side caller runs the pipeline on short-lived worker threads: everything goes back when the thread ends
+	// (pipes live in the process-wide free list below: this runs at process exit)
 	~HostPipe() {
 		if (!in || device < 0 || cudaSetDevice(device) != cudaSuccess) {
 			(void)cudaGetLastError();
@@ -708,9 +708,42 @@ struct HostPipe {
 		(void)cudaGetLastError();
 	}
 };
-// keyed by device: streams, events, staging rings and the arena belong to the device they were created on
-// (a thread may scan on several GPUs one after the other)
-static thread_local std::map<int, HostPipe> g_pipes;
+// Streams, events, staging rings and the arena belong to the device they were created on.  A pipe is leased for the
+// duration of one call and goes back to a process-wide free list: a DuckDB-side caller runs every query's pipeline on a new
+// worker thread, and a pipe per THREAD meant new streams, a new 96 MiB pinned ring and a new device arena per query.
+static std::mutex g_pipe_mu;
+static std::vector<std::unique_ptr<HostPipe>> g_free_pipes;
+
+struct PipeLease {
+	std::unique_ptr<HostPipe> pipe;
+	explicit PipeLease(int device) {
+		{
+			std::lock_guard<std::mutex> lock(g_pipe_mu);
+			for (size_t i = 0; i < g_free_pipes.size(); i++) {
+				if (g_free_pipes[i]->device == device) {
+					pipe = std::move(g_free_pipes[i]);
+					g_free_pipes.erase(g_free_pipes.begin() + static_cast<std::ptrdiff_t>(i));
+					break;
+				}
+			}
+		}
+		if (!pipe) {
+			pipe.reset(new HostPipe());
+			pipe->device = device;
+		}
+	}
+	~PipeLease() {
+		// (a call that failed half way leaves work queued on the pipe's streams: drain it before the next user)
+		if (pipe->in && cudaSetDevice(pipe->device) == cudaSuccess) {
+			cudaStreamSynchronize(pipe->in);
+			cudaStreamSynchronize(pipe->compute);
+			cudaStreamSynchronize(pipe->out);
+		}
+		(void)cudaGetLastError();
+		std::lock_guard<std::mutex> lock(g_pipe_mu);
+		g_free_pipes.push_back(std::move(pipe));
+	}
+};
 
 static int UploadRanges(b2a_scan *s, const ScanPlan::RangeList &ranges, cudaStream_t st) {
 	const ScanPlan &p = s->plan;
@@ -735,8 +768,8 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 		return Fail(B2A_EINVAL, "a B2A_SCAN_DEVICE_ALIAS scan leaves its direct columns in the device image: use "
 		                        "b2a_read_arrow_device / b2a_scan_decode");
 	}
-	HostPipe &hp = g_pipes[s->device];
-	hp.device = s->device;
+	PipeLease lease(s->device);
+	HostPipe &hp = *lease.pipe;
 	const bool to_host = d_out_user == nullptr;
 	if (!hp.in) {
 		CUDA_OK(cudaStreamCreateWithFlags(&hp.in, cudaStreamNonBlocking));

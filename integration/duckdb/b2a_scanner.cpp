@@ -294,7 +294,13 @@ unique_ptr<B2AScanner::Slice> B2AScanner::Load(uint64_t lo, uint64_t hi) {
 			const idx_t out_padded = (NumericCast<idx_t>(out_bytes) + 255) & ~idx_t(255);
 			s->slab = B2ASlab::Acquire(out_padded + NumericCast<idx_t>(scratch_bytes));
 			t2 = NowMs();
-			rc = b2a_read_arrow_host_scratch(s->scan, s->slab->data, scratch_bytes ? s->slab->data + out_padded : nullptr, 0);
+			// sub-slices of the H2D / decode / D2H pipeline inside this slice (0 = the library's default)
+			static const uint32_t pipe_slices = [] {
+				const char *e = std::getenv("B2A_PIPE_SLICES");
+				return e ? NumericCast<uint32_t>(std::atoll(e)) : 0u;
+			}();
+			rc = b2a_read_arrow_host_scratch(s->scan, s->slab->data, scratch_bytes ? s->slab->data + out_padded : nullptr,
+			                                 pipe_slices);
 		} catch (std::exception &e) {
 			s->status = B2A_EOOM;
 			s->error = e.what();
