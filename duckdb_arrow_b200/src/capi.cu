@@ -908,8 +908,12 @@ static int ReadArrowPipeline(b2a_scan *s, void *h_out_pinned, void *d_out_user, 
 			const char *e = getenv("B2A_STAGE_THREADS");
 			int n = e ? atoi(e) : 0;
 			if (n <= 0) {
+				// measured on the 16-core box, one process (tools/gpu_r2_s.sh): 8 threads 137 ms, 12 threads 122 ms (= the
+				// time from a pinned image), 16 threads 131 ms per SF10 file; several ranks on one node share the cores
 				const unsigned hw = std::thread::hardware_concurrency();
-				n = hw >= 16 ? 8 : (hw >= 4 ? static_cast<int>(hw / 2) : 1);
+				const char *lws = getenv("LOCAL_WORLD_SIZE");
+				const bool alone = !lws || atoi(lws) <= 1;
+				n = hw >= 16 ? (alone ? 12 : 8) : (hw >= 4 ? static_cast<int>(hw / 2) : 1);
 			}
 			return static_cast<uint32_t>(n);
 		}();
