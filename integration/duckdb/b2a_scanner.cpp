@@ -244,14 +244,17 @@ B2AScanner::Slice::~Slice() {
 }
 
 B2AScanner::~B2AScanner() {
-	if (worker.joinable()) {
+	if (!workers.empty()) {
 		{
 			std::lock_guard<std::mutex> guard(mu);
 			stop = true;
 		}
 		cv.notify_all();
-		worker.join();
+		for (auto &w : workers) {
+			w.join();
+		}
 	}
+	out_of_order.clear();
 	own.slice.reset();
 	ready.clear();
 	bin.reset(); // (the scans go now unless a cursor of another thread still holds a slice)
@@ -325,26 +328,36 @@ B2AScanner::Cursor::Cursor(Cursor &&) noexcept = default;
 B2AScanner::Cursor &B2AScanner::Cursor::operator=(Cursor &&) noexcept = default;
 
 void B2AScanner::WorkerLoop() {
-	for (idx_t k = 0; k < n_slices; k++) {
+	while (true) {
+		idx_t k;
 		{
 			std::unique_lock<std::mutex> lock(mu);
-			cv.wait(lock, [&] { return stop || ready.size() < depth; });
-			if (stop) {
+			// a slice is started while fewer than `depth` are started-but-not-drained (drained = popped from `ready`)
+			cv.wait(lock, [&] {
+				return stop || produced == n_slices || claimed == n_slices || claimed < handed_out + depth;
+			});
+			if (stop || produced == n_slices || claimed == n_slices) {
 				return;
 			}
+			k = claimed++;
 		}
 		shared_ptr<Slice> s = Load(slice_bounds[k], slice_bounds[k + 1]);
 		s->next_batch = s->batch_lo;
-		const bool failed = s->status != B2A_OK;
 		{
 			std::lock_guard<std::mutex> guard(mu);
-			ready.push_back(std::move(s));
-			produced = failed ? n_slices : k + 1; // nothing is decoded behind a failed slice
+			out_of_order[k] = std::move(s);
+			while (produced < n_slices) { // move what is now in order
+				auto it = out_of_order.find(produced);
+				if (it == out_of_order.end()) {
+					break;
+				}
+				const bool failed = it->second->status != B2A_OK;
+				ready.push_back(std::move(it->second));
+				out_of_order.erase(it);
+				produced = failed ? n_slices : produced + 1; // nothing is handed out behind a failed slice
+			}
 		}
 		cv.notify_all();
-		if (failed) {
-			return;
-		}
 	}
 }
 
@@ -366,6 +379,7 @@ bool B2AScanner::TakeSlice(Cursor &cursor) {
 		s->next_batch = hi;
 		if (hi >= s->batch_hi) {
 			ready.pop_front();
+			handed_out++;
 			drained = true;
 		}
 	}
@@ -449,8 +463,12 @@ void B2AScanner::Begin(const vector<idx_t> &columns) {
 	if (const char *e = std::getenv("B2A_SLICES_AHEAD")) {
 		depth = MaxValue<idx_t>(1, NumericCast<idx_t>(std::atoll(e)));
 	}
-	if (n_slices > 0) {
-		worker = std::thread([this] { WorkerLoop(); });
+	idx_t producers = 2;
+	if (const char *e = std::getenv("B2A_PRODUCERS")) {
+		producers = MaxValue<idx_t>(1, NumericCast<idx_t>(std::atoll(e)));
+	}
+	for (idx_t i = 0; i < MinValue<idx_t>(producers, n_slices); i++) {
+		workers.emplace_back([this] { WorkerLoop(); });
 	}
 }
 

@@ -144,14 +144,18 @@ private:
 	Cursor own; // the single consumer of Next()
 	shared_ptr<B2AScanBin> bin;
 
-	// producer (one thread per scanner: the C ABI keeps its streams / staging per thread and device): decodes the slices
-	// in order, at most `depth` finished ones waiting
-	std::thread worker;
+	// producers: two threads take turns at the slices (each call of b2a_read_arrow_host leases its own streams / staging
+	// ring / arena), so that the pipeline of slice k + 1 fills while the one of slice k drains; slices are handed out in
+	// order, at most `depth` started ones ahead of the consumers
+	vector<std::thread> workers;
 	std::mutex mu;
 	std::condition_variable cv;
 	bool stop = false;
-	idx_t produced = 0, handed_out = 0, depth = 2;
-	std::deque<shared_ptr<Slice>> ready;
+	idx_t claimed = 0;  // next slice a producer takes
+	idx_t produced = 0; // slices [0, produced) are in `ready` or already handed out (n_slices after a failure)
+	idx_t handed_out = 0, depth = 3;
+	std::deque<shared_ptr<Slice>> ready;                 // finished, in order
+	unordered_map<idx_t, shared_ptr<Slice>> out_of_order; // finished before their predecessor
 };
 
 } // namespace ext_nanoarrow
