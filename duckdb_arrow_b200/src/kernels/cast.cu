@@ -17,6 +17,7 @@
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
 #include "cast.cuh"
+#include "cast_parse.cuh"
 
 #include "b2arrow.h"
 
@@ -568,60 +569,12 @@ __device__ __noinline__ uint32_t parse_double(const char *s, uint32_t n, double 
 	return 0;
 }
 
-// IntegerCastLoop<.., ALLOW_EXPONENT=false, decimal separator '.'>: sign, digits, optional fraction -> rounded
+// VARCHAR -> BIGINT: DuckDB's TrySimpleIntegerCast<int64_t>, restated in cast_parse.cuh (pinned on the CPU against the compiled
+// reference: tests/test_cast_parse.py).  Result codes are B2A_CAST_DEV_RANGE / B2A_CAST_DEV_PARSE.
 __device__ __noinline__ uint32_t parse_int64(const char *s, uint32_t n, int64_t *out) {
-	uint32_t i = 0;
-	while (i < n && is_space(s[i])) {
-		i++;
-	}
-	while (n > i && is_space(s[n - 1])) {
-		n--;
-	}
-	if (i >= n) {
-		return B2A_CAST_DEV_PARSE;
-	}
-	bool neg = false;
-	if (s[i] == '-') {
-		neg = true;
-		i++;
-	} else if (s[i] == '+') {
-		i++;
-	}
-	uint64_t v = 0;
-	bool any = false;
-	const uint64_t limit = neg ? (1ull << 63) : (1ull << 63) - 1;
-	for (; i < n && s[i] >= '0' && s[i] <= '9'; i++) {
-		any = true;
-		const uint64_t d = static_cast<uint64_t>(s[i] - '0');
-		if (v > (limit - d) / 10) {
-			return B2A_CAST_DEV_RANGE;
-		}
-		v = v * 10 + d;
-	}
-	if (i < n && s[i] == '.') {
-		i++;
-		bool first = true, frac_any = false;
-		for (; i < n && s[i] >= '0' && s[i] <= '9'; i++) {
-			frac_any = true;
-			if (first && s[i] >= '5') {
-				if (v >= limit) {
-					return B2A_CAST_DEV_RANGE;
-				}
-				v++;
-			}
-			first = false;
-		}
-		if (!any && !frac_any) {
-			return B2A_CAST_DEV_PARSE;
-		}
-		any = true;
-	}
-	if (!any || i != n) {
-		return B2A_CAST_DEV_PARSE;
-	}
-	*out = neg ? static_cast<int64_t>(0 - v) : static_cast<int64_t>(v);
-	return 0;
+	return castp::varchar_to_bigint(s, n, out);
 }
+static_assert(castp::OUT_OF_RANGE == B2A_CAST_DEV_RANGE && castp::NOT_A_NUMBER == B2A_CAST_DEV_PARSE, "cast error codes");
 
 // casts that cannot fail and do not need the validity mask (a NULL row's data slot is unspecified in DuckDB):
 // integer widening, integer -> FLOAT/DOUBLE, FLOAT -> DOUBLE.  8 rows in flight per thread.

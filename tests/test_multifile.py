@@ -282,6 +282,26 @@ def test_double_to_varchar_shortest_roundtrip(b2a, cuda_device, tmp_path):
 
 
 @pytest.mark.gpu
+def test_varchar_to_bigint_like_duckdb(b2a, cuda_device, tmp_path):
+    """the device cast behind a BIGINT global column fed by a VARCHAR file = DuckDB's TrySimpleIntegerCast (the restatement
+    in kernels/cast_parse.cuh is pinned against the compiled reference in tests/test_cast_parse.py; here: the kernel runs it)
+    — exponents, '_' separators, hex / binary literals, fractions, the int64 limits; errors stay errors"""
+    good = {"42": 42, " -7 ": -7, "1e3": 1000, "1.5e1": 15, "25e-1": 3, "-25e-1": -3, "1_000": 1000, "0x1F": 31,
+            "0b101": 5, "2.5": 3, "-2.5": -3, "1.": 1, ".5": 1, "9223372036854775807": 2**63 - 1,
+            "-9223372036854775808": -2**63, "12345e-2": 123, "+8": 8}
+    _write(str(tmp_path / "a.arrows"), pa.table({"v": pa.array([1], pa.int64())}))
+    _write(str(tmp_path / "b.arrows"), pa.table({"v": pa.array(list(good) + [None])}))
+    got = [r[0] for r in rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "b.arrows")]))[1:]]
+    assert got == list(good.values()) + [None]
+    for k, (text, what) in enumerate([("abc", "could not convert a string"), ("1e", "could not convert a string"),
+                                      ("9223372036854775808", "out of range"), ("1e19", "out of range"),
+                                      ("1__0", "could not convert a string")]):
+        _write(str(tmp_path / f"bad{k}.arrows"), pa.table({"v": pa.array([text])}))
+        with pytest.raises(b2a.B2AError, match=what):
+            rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / f"bad{k}.arrows")]))
+
+
+@pytest.mark.gpu
 def test_varchar_to_double_exact_or_loud(b2a, cuda_device, tmp_path):
     texts = ["2.2", "134.2", "-0.5", "1e3", "  7.25 ", "+3", "1234567890123456", "1E-5", "nan", "inf", "-Infinity", "0",
              "-0.0", ".5", "5."]
