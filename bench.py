@@ -385,10 +385,11 @@ def _decimal_str(v: int, scale: int) -> str:
     return f"{sign}{v // 10 ** scale}.{v % 10 ** scale:0{scale}d}"
 
 
-def _q6_device_variant(ctx, path, steps, device_alias):
+def _q6_device_variant(ctx, path, steps, device_alias, fused=False):
     """decode -> filter -> sum(a*b) over this rank's shard as one CUDA graph.  device_alias: B2A_SCAN_DEVICE_ALIAS — the
     four fixed-width columns are read in place in the device image (the reference's zero-copy DirectConversion for device
-    consumers): nothing to decode, the graph holds the filter and the aggregate only."""
+    consumers): nothing to decode, the graph holds the filter and the aggregate only.  fused: b2a_scan_filter_sum_product —
+    count and sum in ONE kernel, no selection vectors in between."""
     torch, b2a = ctx.torch, ctx.b2a
     reader = b2a.ArrowIPCReader.open_file(path)
     reader.set_projection(Q6_COLUMNS)
@@ -402,16 +403,23 @@ def _q6_device_variant(ctx, path, steps, device_alias):
     d_out = torch.empty(max(scan.out_bytes, 256), dtype=torch.uint8, device=ctx.dev)
     res = torch.zeros(2, dtype=torch.int64, device=ctx.dev)
     scan.decode(d_out)
-    fout = scan.filter(Q6_PREDS, d_out)               # first call builds + caches the per-chunk column tables
-    scan.sum_product_async("l_extendedprice", "l_discount", fout[0], fout[1], d_out, res)
+    if fused:                                         # first call builds + caches the per-chunk column tables
+        total_t, res = scan.filter_sum_product(Q6_PREDS, "l_extendedprice", "l_discount", d_out)
+        fout = (None, None, total_t)
+    else:
+        fout = scan.filter(Q6_PREDS, d_out)
+        scan.sum_product_async("l_extendedprice", "l_discount", fout[0], fout[1], d_out, res)
     scan.finish()
     decodes = scan.n_tiles > 0
 
     def body():
         if decodes:
             scan.decode(d_out)
-        scan.filter(Q6_PREDS, d_out, out=fout)
-        scan.sum_product_async("l_extendedprice", "l_discount", fout[0], fout[1], d_out, res)
+        if fused:
+            scan.filter_sum_product(Q6_PREDS, "l_extendedprice", "l_discount", d_out, out=(fout[2], res))
+        else:
+            scan.filter(Q6_PREDS, d_out, out=fout)
+            scan.sum_product_async("l_extendedprice", "l_discount", fout[0], fout[1], d_out, res)
 
     graph = None
     side = torch.cuda.Stream()
@@ -434,8 +442,9 @@ def _q6_device_variant(ctx, path, steps, device_alias):
     rows, selected, total = _combine_q6(ctx, fout[2], res, my_rows)
     scan.finish()
     # decode (if any) + the predicate columns (4 + 8 + 8 B/row) + selection entries and the two factors of the selected rows
-    alg = (scan.algorithmic_bytes if decodes else 0) + my_rows * 20 + int(fout[2].item()) * (4 + 16)
-    kernels = (["b2a_decode_kernel"] if decodes else []) + ["b2a_filter_kernel", "b2a_sum_product_kernel"]
+    alg = (scan.algorithmic_bytes if decodes else 0) + my_rows * 20 + int(fout[2].item()) * ((0 if fused else 4) + 16)
+    kernels = (["b2a_decode_kernel"] if decodes else []) + \
+        (["b2a_filter_sum_kernel"] if fused else ["b2a_filter_kernel", "b2a_sum_product_kernel"])
     r = {"ms_per_step": ms, "value": rows / (ms / 1e3), "rows": rows, "selected": selected, "sum": _decimal_str(total, 4),
          "cuda_graph": graph is not None, "kernels_per_step": len(kernels),
          "roofline": {"bound": "hbm", "kernels": kernels, "achieved": alg / (ms / 1e3) / 1e9, "peak": ctx.peak,
@@ -453,17 +462,26 @@ def leg_filter_q6(ctx, args, path, steps):
     columns read in place in the device image (B2A_SCAN_DEVICE_ALIAS — they are DirectConversion columns, which the
     reference does not copy either); `materialised`: the same with the vectors copied into the arena first (what rounds
     1 and 2 reported before the flag existed)."""
-    zero = _q6_device_variant(ctx, path, steps, device_alias=True)
+    fused = _q6_device_variant(ctx, path, steps, device_alias=True, fused=True)
+    two = _q6_device_variant(ctx, path, steps, device_alias=True)
     mat = _q6_device_variant(ctx, path, steps, device_alias=False)
+    # `value` = the faster of the two zero-copy forms (one fused kernel wins where the step is launch-bound, i.e. on a small
+    # shard; filter + aggregate as two kernels at full occupancy wins on a whole SF10), both reported
+    zero, variant = (fused, "fused") if fused["ms_per_step"] <= two["ms_per_step"] else (two, "two_kernels")
+    keys = ("value", "ms_per_step", "kernels_per_step", "cuda_graph", "roofline")
     out = {"metric": "read_arrow + pushed-down Q6 filters + sum(l_extendedprice*l_discount), rows/s (device-resident)",
            "value": zero["value"], "unit": "rows/s", "ms_per_step": zero["ms_per_step"], "rows": zero["rows"],
            "selected": zero["selected"], "selectivity": zero["selected"] / max(1, zero["rows"]), "sum": zero["sum"],
            "scaling": "strong", "cuda_graph": zero["cuda_graph"], "kernels_per_step": zero["kernels_per_step"],
+           "variant": variant,
            "zero_copy": "B2A_SCAN_DEVICE_ALIAS: fixed-width columns are consumed in place in the device image",
            "collective": "one all_reduce(SUM) of 6 int64 lanes after the timed loop (rows, selected, 128-bit sum limbs)",
            "roofline": zero["roofline"],
-           "materialised": {k: mat[k] for k in ("value", "ms_per_step", "kernels_per_step", "cuda_graph", "roofline")},
-           "same_answer_both_ways": bool(zero["sum"] == mat["sum"] and zero["selected"] == mat["selected"]),
+           "zero_copy_fused": {k: fused[k] for k in keys},
+           "zero_copy_two_kernels": {k: two[k] for k in keys},
+           "materialised": {k: mat[k] for k in keys},
+           "same_answer_every_way": bool(fused["sum"] == mat["sum"] == two["sum"]
+                                         and fused["selected"] == mat["selected"] == two["selected"]),
            "config": {"workload": f"lineitem SF{args.sf:g}, columns {Q6_COLUMNS}, predicates {Q6_PREDS}"}}
     known = Q6_KNOWN.get(float(args.sf))
     if known is not None and ctx.data_kind == "dbgen":

@@ -154,6 +154,7 @@ def _load() -> C.CDLL:
         "b2a_scan_filter": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_filter_no_alloc": (i32, [vp, vp, P(Predicate), u32, vp, vp, vp, vp]),
         "b2a_scan_sum_product": (i32, [vp, vp, u32, u32, vp, vp, vp, vp]),
+        "b2a_scan_filter_sum_product": (i32, [vp, vp, P(Predicate), u32, u32, u32, vp, vp, vp]),
         "b2a_reader_used_footer": (i32, [vp, P(i32)]),
         "b2a_read_arrow_host": (i32, [vp, vp, u32]),
         "b2a_read_arrow_device": (i32, [vp, vp, u32, vp]),

@@ -319,6 +319,31 @@ class ArrowScan:
                                   C.c_void_p(total.data_ptr()), self._stream_ptr()))
         return sel, count, total
 
+    def filter_sum_product(self, predicates, col_a, col_b, d_out=None, out=None):
+        """b2a_scan_filter_sum_product: count and sum(a*b) over the rows passing the ANDed predicates in ONE launch (no
+        selection vectors).  Returns (total int64[1], sum int64[2] = {lo, hi}) device tensors, written by work queued on the
+        current stream; `out` = the pair of an earlier call (no allocation: CUDA-graph capture)."""
+        torch = self._torch()
+        d_out = self.d_out if d_out is None else d_out
+        names = [f.name for f in self.reader.output_columns()]
+        arr = (_lib.Predicate * len(predicates))()
+        for i, (col, op, const) in enumerate(predicates):
+            arr[i].column = names.index(col) if isinstance(col, str) else col
+            arr[i].cmp = _lib.CMP[op]
+            arr[i].constant = int(const)
+        ia = names.index(col_a) if isinstance(col_a, str) else col_a
+        ib = names.index(col_b) if isinstance(col_b, str) else col_b
+        dev = f"cuda:{self.device}"
+        if out is not None:
+            total, res = out
+        else:
+            total = torch.zeros(1, dtype=torch.int64, device=dev)
+            res = torch.zeros(2, dtype=torch.int64, device=dev)
+        check(lib.b2a_scan_filter_sum_product(self._h, C.c_void_p(d_out.data_ptr()), arr, len(predicates), ia, ib,
+                                              C.c_void_p(total.data_ptr()), C.c_void_p(res.data_ptr()),
+                                              self._stream_ptr()))
+        return total, res
+
     def sum_product(self, col_a, col_b, sel=None, count=None, d_out=None) -> int:
         """sum(a*b) over the selected rows (all rows when sel is None) as an exact Python int (HUGEINT)."""
         torch = self._torch()

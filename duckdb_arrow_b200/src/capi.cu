@@ -311,6 +311,7 @@ static void FreeScanDevice(b2a_scan *s) {
 		ScanFree(s->d_image_owned);
 		ScanFree(s->d_chunk_col);
 		ScanFree(s->d_chunk_col2);
+		ScanFree(s->d_chunk_col3);
 		ScanFree(s->d_chunk_rows);
 		ScanFree(s->d_jobs);
 		ScanFree(s->d_job_order);
@@ -1324,6 +1325,64 @@ extern "C" int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2
 	if (e == -1) {
 		return Fail(B2A_EINVAL, "b2a_scan_filter_no_alloc: tables exceed the fixed device scratch");
 	}
+	if (e != 0) {
+		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+	}
+	if (l.n_chunks) {
+		s->launches++;
+	}
+	return B2A_OK;
+	B2A_CATCH
+}
+
+// The Q6 shape in one launch: count and sum(a * b) over the rows that pass the predicates, no selection vectors in between.
+extern "C" int b2a_scan_filter_sum_product(b2a_scan *s, const void *d_out, const b2a_predicate *preds_in, uint32_t n_preds,
+                                           uint32_t col_a, uint32_t col_b, void *d_total, void *d_result_i128,
+                                           void *cuda_stream) {
+	B2A_TRY
+	NEED_DEVICE(s);
+	if (n_preds == 0 || n_preds > 8 || !preds_in) {
+		return Fail(B2A_EINVAL, "between 1 and 8 predicates are supported");
+	}
+	if (!d_total || !d_result_i128) {
+		return Fail(B2A_EINVAL, "b2a_scan_filter_sum_product: null output");
+	}
+	std::vector<b2a_predicate> sorted(preds_in, preds_in + n_preds);
+	std::stable_sort(sorted.begin(), sorted.end(),
+	                 [](const b2a_predicate &a, const b2a_predicate &b) { return a.column < b.column; });
+	std::vector<uint32_t> cols;
+	for (auto &pr : sorted) {
+		cols.push_back(pr.column);
+		if (pr.cmp > B2A_CMP_GE) {
+			return Fail(B2A_EINVAL, "unknown comparison");
+		}
+	}
+	cols.push_back(col_a);
+	cols.push_back(col_b);
+	std::vector<uint8_t> widths;
+	int rc = ChunkTable(s, d_out, cols, s->chunk_col3_key, &s->d_chunk_col3, &widths);
+	if (rc != B2A_OK) {
+		return rc;
+	}
+	if (widths[n_preds] != 8 || widths[n_preds + 1] != 8) {
+		return Fail(B2A_ENOTIMPL, "sum_product needs two 8-byte integer columns (BIGINT / DECIMAL(<=18))");
+	}
+	cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+	CUDA_OK(cudaMemsetAsync(d_total, 0, sizeof(unsigned long long), st));
+	CUDA_OK(cudaMemsetAsync(d_result_i128, 0, 16, st));
+	FilterLaunch l;
+	l.out = static_cast<const uint8_t *>(d_out);
+	l.d_chunk_col = s->d_chunk_col3;
+	l.d_chunk_rows = s->d_chunk_rows;
+	l.n_chunks = s->plan.n_chunks;
+	l.n_preds = n_preds;
+	for (uint32_t i = 0; i < n_preds; i++) {
+		l.preds[i] = sorted[i];
+		l.widths[i] = widths[i];
+	}
+	l.d_total = static_cast<unsigned long long *>(d_total);
+	l.sm_count = s->sm_count;
+	int e = LaunchFilterSum(l, static_cast<unsigned long long *>(d_result_i128), cuda_stream);
 	if (e != 0) {
 		return Fail(B2A_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
 	}

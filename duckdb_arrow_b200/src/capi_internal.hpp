@@ -29,8 +29,9 @@ struct b2a_scan {
 	// filter support
 	uint64_t *d_chunk_col = nullptr;   // filter: per chunk, per predicate {data, validity}
 	uint64_t *d_chunk_col2 = nullptr;  // sum_product: per chunk {a, va, b, vb}
+	uint64_t *d_chunk_col3 = nullptr;  // filter_sum_product: per chunk, per predicate {data, validity}, then {a, va, b, vb}
 	uint32_t *d_chunk_rows = nullptr;
-	std::vector<uint32_t> chunk_col_key, chunk_col2_key;
+	std::vector<uint32_t> chunk_col_key, chunk_col2_key, chunk_col3_key;
 	// compressed bodies: decompress jobs, per-warp decoder workspaces, job counter + error word
 	b2a_decomp_job *d_jobs = nullptr;
 	uint32_t *d_job_order = nullptr; // all jobs, largest output first (whole-scan launches: shortens the tail)

@@ -42,6 +42,9 @@ struct FilterLaunch {
 	int sm_count = 148;
 };
 int LaunchFilter(const FilterLaunch &l, void *stream);
+// filter + sum(a * b) in one kernel: l.d_chunk_col holds n_preds + 2 {data, validity} pairs per chunk (the predicates',
+// then a's and b's); l.d_sel / l.d_count are not used; l.d_total += passing rows, d_result (lo, hi) += the 128-bit sum
+int LaunchFilterSum(const FilterLaunch &l, unsigned long long *d_result, void *stream);
 
 // The no-allocation variant (b2a_scan_filter_no_alloc): the per-chunk tables live in a file-scope __device__ array of
 // filter.cu instead of cudaMalloc'ed memory.  l.d_chunk_col / l.d_chunk_rows are ignored; the HOST tables are copied into

@@ -38,6 +38,74 @@ __device__ __forceinline__ void load_pred_values(const uint8_t *__restrict__ p, 
 	}
 }
 
+// bit k of the result: row k * 256 + thread of the vector is valid and passes every predicate.  cc = the vector's table
+// entries {data offset, validity offset} per predicate (shared memory).
+__device__ __forceinline__ uint32_t filter_pass_bits(const uint8_t *__restrict__ out, const uint64_t *cc, uint32_t rows,
+                                                     const FilterParams &fp) {
+	uint32_t pass = 0; // bit k: row k * 256 + thread passes
+#pragma unroll
+	for (int k = 0; k < kFilterRowsPerThread; k++) {
+		pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
+	}
+	int64_t v[kFilterRowsPerThread];
+	for (uint32_t p = 0; p < fp.n_preds; p++) {
+		const bool reuse = fp.same_column[p] != 0; // (values loaded and masked by NULLs under the previous predicate)
+		const uint64_t doff = cc[2 * p], voff = reuse ? B2A_NONE_OFF : cc[2 * p + 1];
+		switch (reuse ? 0xFFu : fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
+		case 1:
+			load_pred_values<int8_t>(out + doff, rows, v);
+			break;
+		case 2:
+			load_pred_values<int16_t>(out + doff, rows, v);
+			break;
+		case 4:
+			load_pred_values<int32_t>(out + doff, rows, v);
+			break;
+		case 0x81:
+			load_pred_values<uint8_t>(out + doff, rows, v);
+			break;
+		case 0x82:
+			load_pred_values<uint16_t>(out + doff, rows, v);
+			break;
+		case 0x84:
+			load_pred_values<uint32_t>(out + doff, rows, v);
+			break;
+		case 0xFF:
+			break;
+		default:
+			load_pred_values<int64_t>(out + doff, rows, v);
+			break;
+		}
+		if (voff != B2A_NONE_OFF) {
+#pragma unroll
+			for (int k = 0; k < kFilterRowsPerThread; k++) {
+				const uint32_t r = k * kFilterThreads + threadIdx.x;
+				if (r < rows) {
+					const uint64_t w = __ldg(reinterpret_cast<const unsigned long long *>(out + voff) + (r >> 6));
+					if (!((w >> (r & 63)) & 1)) {
+						pass &= ~(1u << k);
+					}
+				}
+			}
+		}
+		// the comparison as a truth table over {v < c, v == c, v > c} (bits 0, 1, 2): no branch on the operator per value
+		const uint32_t cmp = fp.preds[p].cmp;
+		const uint32_t accept = cmp == B2A_CMP_EQ   ? 2u
+		                        : cmp == B2A_CMP_NE ? 5u
+		                        : cmp == B2A_CMP_LT ? 1u
+		                        : cmp == B2A_CMP_LE ? 3u
+		                        : cmp == B2A_CMP_GT ? 4u
+		                                            : 6u;
+		const int64_t c = fp.preds[p].constant;
+#pragma unroll
+		for (int k = 0; k < kFilterRowsPerThread; k++) {
+			const uint32_t which = v[k] < c ? 0u : (v[k] == c ? 1u : 2u);
+			pass &= ~((((accept >> which) & 1u) ^ 1u) << k);
+		}
+	}
+	return pass;
+}
+
 __global__ void __launch_bounds__(kFilterThreads, 8)
     b2a_filter_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
                       const uint32_t *__restrict__ chunk_rows, uint64_t n_chunks, FilterParams fp,
@@ -74,67 +142,7 @@ __global__ void __launch_bounds__(kFilterThreads, 8)
 		const uint32_t rows = s_rows[cur];
 		const uint64_t *cc = s_tbl[cur];
 		uint32_t *csel = sel + chunk * B2A_VECTOR_SIZE;
-		uint32_t pass = 0; // bit k: row k * 256 + thread passes
-#pragma unroll
-		for (int k = 0; k < kFilterRowsPerThread; k++) {
-			pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
-		}
-		int64_t v[kFilterRowsPerThread];
-		for (uint32_t p = 0; p < fp.n_preds; p++) {
-			const bool reuse = fp.same_column[p] != 0; // (values loaded and masked by NULLs under the previous predicate)
-			const uint64_t doff = cc[2 * p], voff = reuse ? B2A_NONE_OFF : cc[2 * p + 1];
-			switch (reuse ? 0xFFu : fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
-			case 1:
-				load_pred_values<int8_t>(out + doff, rows, v);
-				break;
-			case 2:
-				load_pred_values<int16_t>(out + doff, rows, v);
-				break;
-			case 4:
-				load_pred_values<int32_t>(out + doff, rows, v);
-				break;
-			case 0x81:
-				load_pred_values<uint8_t>(out + doff, rows, v);
-				break;
-			case 0x82:
-				load_pred_values<uint16_t>(out + doff, rows, v);
-				break;
-			case 0x84:
-				load_pred_values<uint32_t>(out + doff, rows, v);
-				break;
-			case 0xFF:
-				break;
-			default:
-				load_pred_values<int64_t>(out + doff, rows, v);
-				break;
-			}
-			if (voff != B2A_NONE_OFF) {
-#pragma unroll
-				for (int k = 0; k < kFilterRowsPerThread; k++) {
-					const uint32_t r = k * kFilterThreads + threadIdx.x;
-					if (r < rows) {
-						const uint64_t w = __ldg(reinterpret_cast<const unsigned long long *>(out + voff) + (r >> 6));
-						if (!((w >> (r & 63)) & 1)) {
-							pass &= ~(1u << k);
-						}
-					}
-				}
-			}
-			// the comparison as a truth table over {v < c, v == c, v > c} (bits 0, 1, 2): no branch on the operator per value
-			const uint32_t cmp = fp.preds[p].cmp;
-			const uint32_t accept = cmp == B2A_CMP_EQ   ? 2u
-			                        : cmp == B2A_CMP_NE ? 5u
-			                        : cmp == B2A_CMP_LT ? 1u
-			                        : cmp == B2A_CMP_LE ? 3u
-			                        : cmp == B2A_CMP_GT ? 4u
-			                                            : 6u;
-			const int64_t c = fp.preds[p].constant;
-#pragma unroll
-			for (int k = 0; k < kFilterRowsPerThread; k++) {
-				const uint32_t which = v[k] < c ? 0u : (v[k] == c ? 1u : 2u);
-				pass &= ~((((accept >> which) & 1u) ^ 1u) << k);
-			}
-		}
+		const uint32_t pass = filter_pass_bits(out, cc, rows, fp); // bit k: row k * 256 + thread passes
 		// ---- compaction: ascending row order = k-major, then warp, then lane
 		uint32_t before[kFilterRowsPerThread];
 #pragma unroll
@@ -211,6 +219,121 @@ int LaunchFilter(const FilterLaunch &l, void *stream) {
 	}
 	b2a_filter_kernel<<<static_cast<uint32_t>(grid), kFilterThreads, 0, static_cast<cudaStream_t>(stream)>>>(
 	    l.out, l.d_chunk_col, l.d_chunk_rows, l.n_chunks, fp, l.d_sel, l.d_count, l.d_total);
+	return static_cast<int>(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------------------------------------
+// Filter + aggregate in one kernel (the Q6 shape): count and sum(a * b) over the rows that pass, with no selection vector in
+// between — b2a_filter_kernel writes sel_t / counts that b2a_sum_product_kernel reads back, and the pair is two launches.
+// Per vector: the predicate bits, then the two factors of the passing rows (NULL factors are skipped, as DuckDB's sum
+// skips a NULL product); per CTA: one warp reduction and one pair of atomics at the very end.  Table per vector =
+// n_preds {data, validity} pairs followed by the pairs of a and b.  One barrier per vector (the table prefetch).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kFilterThreads, 5)
+    b2a_filter_sum_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
+                          const uint32_t *__restrict__ chunk_rows, uint64_t n_chunks, FilterParams fp,
+                          unsigned long long *total, unsigned long long *result) {
+	__shared__ uint64_t s_tbl[2][20];
+	__shared__ uint32_t s_rows[2];
+	const uint32_t n_entries = 2 * (fp.n_preds + 2);
+	if (blockIdx.x < n_chunks) {
+		if (threadIdx.x < n_entries) {
+			s_tbl[0][threadIdx.x] = __ldg(chunk_col + static_cast<uint64_t>(blockIdx.x) * n_entries + threadIdx.x);
+		}
+		if (threadIdx.x == 32) {
+			s_rows[0] = __ldg(chunk_rows + blockIdx.x);
+		}
+	}
+	__syncthreads();
+	__int128 acc = 0;
+	uint32_t n_pass = 0;
+	uint32_t cur = 0;
+	for (uint64_t chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x, cur ^= 1u) {
+		const uint64_t next = chunk + gridDim.x;
+		if (next < n_chunks) {
+			if (threadIdx.x < n_entries) {
+				s_tbl[cur ^ 1u][threadIdx.x] = __ldg(chunk_col + next * n_entries + threadIdx.x);
+			}
+			if (threadIdx.x == 32) {
+				s_rows[cur ^ 1u] = __ldg(chunk_rows + next);
+			}
+		}
+		const uint32_t rows = s_rows[cur];
+		const uint64_t *cc = s_tbl[cur];
+		uint32_t pass = filter_pass_bits(out, cc, rows, fp);
+		if (pass) {
+			const uint64_t *ab = cc + 2 * fp.n_preds;
+			const int64_t *a = reinterpret_cast<const int64_t *>(out + ab[0]);
+			const int64_t *b = reinterpret_cast<const int64_t *>(out + ab[2]);
+			const unsigned long long *va =
+			    ab[1] != B2A_NONE_OFF ? reinterpret_cast<const unsigned long long *>(out + ab[1]) : nullptr;
+			const unsigned long long *vb =
+			    ab[3] != B2A_NONE_OFF ? reinterpret_cast<const unsigned long long *>(out + ab[3]) : nullptr;
+#pragma unroll
+			for (int k = 0; k < kFilterRowsPerThread; k++) {
+				if ((pass >> k) & 1u) {
+					const uint32_t r = k * kFilterThreads + threadIdx.x;
+					const bool ok = (!va || ((__ldg(va + (r >> 6)) >> (r & 63)) & 1)) &&
+					                (!vb || ((__ldg(vb + (r >> 6)) >> (r & 63)) & 1));
+					if (ok) {
+						acc += static_cast<__int128>(__ldg(a + r)) * static_cast<__int128>(__ldg(b + r));
+					}
+				}
+			}
+			n_pass += __popc(pass);
+		}
+		__syncthreads(); // the next vector's table entries are in place; this vector's are free to be overwritten
+	}
+	uint64_t lo = static_cast<uint64_t>(acc), hi = static_cast<uint64_t>(acc >> 64);
+	for (int o = 16; o > 0; o >>= 1) {
+		const uint64_t olo = __shfl_xor_sync(0xffffffffu, lo, o), ohi = __shfl_xor_sync(0xffffffffu, hi, o);
+		const uint64_t nlo = lo + olo;
+		hi = hi + ohi + (nlo < lo ? 1 : 0);
+		lo = nlo;
+		n_pass += __shfl_xor_sync(0xffffffffu, n_pass, o);
+	}
+	if ((threadIdx.x & 31) == 0) {
+		if (n_pass) {
+			atomicAdd(total, static_cast<unsigned long long>(n_pass));
+		}
+		if (lo | hi) {
+			const unsigned long long old = atomicAdd(result, static_cast<unsigned long long>(lo));
+			const unsigned long long carry = (old + lo) < old ? 1ull : 0ull;
+			atomicAdd(result + 1, static_cast<unsigned long long>(hi) + carry);
+		}
+	}
+}
+
+int LaunchFilterSum(const FilterLaunch &l, unsigned long long *d_result, void *stream) {
+	if (l.n_chunks == 0) {
+		return 0;
+	}
+	FilterParams fp;
+	fp.n_preds = l.n_preds;
+	for (uint32_t i = 0; i < l.n_preds; i++) {
+		fp.preds[i] = l.preds[i];
+		fp.widths[i] = l.widths[i];
+		fp.same_column[i] = i > 0 && l.preds[i].column == l.preds[i - 1].column;
+	}
+	static int per_sm_cached[64] = {};
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+		dev = 0;
+	}
+	if (per_sm_cached[dev] == 0) {
+		int per_sm = 0;
+		if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2a_filter_sum_kernel, kFilterThreads, 0) != cudaSuccess ||
+		    per_sm <= 0) {
+			per_sm = 4;
+		}
+		per_sm_cached[dev] = per_sm;
+	}
+	uint64_t grid = static_cast<uint64_t>(l.sm_count) * static_cast<uint64_t>(per_sm_cached[dev]);
+	if (grid > l.n_chunks) {
+		grid = l.n_chunks;
+	}
+	b2a_filter_sum_kernel<<<static_cast<uint32_t>(grid), kFilterThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+	    l.out, l.d_chunk_col, l.d_chunk_rows, l.n_chunks, fp, l.d_total, d_result);
 	return static_cast<int>(cudaGetLastError());
 }
 

@@ -281,6 +281,12 @@ int b2a_scan_filter_no_alloc(b2a_scan *s, const void *d_out, const b2a_predicate
 int b2a_scan_sum_product(b2a_scan *s, const void *d_out, uint32_t col_a, uint32_t col_b, const void *d_sel,
                          const void *d_count, void *d_result_i128, void *cuda_stream);
 
+/* The two above fused for a consumer that needs no selection vectors (the Q6 shape, benchmark/lineitem.py:41): *d_total =
+ * rows that pass the predicates (uint64), d_result_i128 = sum(a*b) over them (rows where a or b is NULL add nothing, like
+ * DuckDB's sum).  One launch; nothing the reference has (it filters and aggregates above the scan). */
+int b2a_scan_filter_sum_product(b2a_scan *s, const void *d_out, const b2a_predicate *preds, uint32_t n_preds,
+                                uint32_t col_a, uint32_t col_b, void *d_total, void *d_result_i128, void *cuda_stream);
+
 /* One call, host buffers in, host vectors out (upload, decode, download pipelined over `n_slices`). */
 int b2a_read_arrow_host(b2a_scan *s, void *h_out_pinned, uint32_t n_slices);
 /* The same for streams with compressed bodies (BodyCompression ZSTD / LZ4_FRAME): the decompressed buffers exist only

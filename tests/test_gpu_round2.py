@@ -330,3 +330,52 @@ def test_device_alias_with_nulls_strings_and_host_consumers(b2a, cuda_device):
     assert torch.equal(sa[keep], sp[keep])
     with pytest.raises(b2a.B2AError, match="exclude each other"):
         b2a.ArrowScan(b2a.ArrowIPCReader.open_buffers([buf]), device=0, device_alias=True, host_alias=True)
+
+
+def test_filter_sum_product_fused_equals_the_two_kernels(b2a, cuda_device):
+    """b2a_scan_filter_sum_product: count + sum(a*b) over the passing rows in ONE launch — the same numbers as
+    b2a_scan_filter followed by b2a_scan_sum_product, the reference's Q6 answer on the dbgen fixture (plain and
+    device-alias scans), and NULL factors / NULL predicate values skipped like DuckDB's sum and filter skip them"""
+    import torch
+    n, total_s = ANSWERS["q6_count_sum"]
+    for device_alias in (False, True):
+        r = b2a.ArrowIPCReader.open_file(DBGEN)
+        r.set_projection(["l_quantity", "l_extendedprice", "l_discount", "l_shipdate"])
+        scan = b2a.ArrowScan(r, device=0, device_alias=device_alias)
+        scan.upload()
+        scan.decode()
+        scan.finish()
+        launches = scan.gpu_launches
+        total, res = scan.filter_sum_product(Q6_PREDS, "l_extendedprice", "l_discount")
+        torch.cuda.synchronize()
+        assert scan.gpu_launches == launches + 1
+        lo, hi = [int(x) for x in res.cpu().tolist()]
+        revenue = (hi << 64) | (lo & 0xFFFFFFFFFFFFFFFF)
+        assert int(total.item()) == int(n) and f"{revenue // 10000}.{revenue % 10000:04d}" == total_s
+        # a second call into the same outputs (what a captured graph replays)
+        scan.filter_sum_product(Q6_PREDS, "l_extendedprice", "l_discount", out=(total, res))
+        torch.cuda.synchronize()
+        assert int(total.item()) == int(n) and [int(x) for x in res.cpu().tolist()] == [lo, hi]
+    # NULLs in a predicate column and in both factors, negative products, several batches
+    rng = np.random.default_rng(11)
+    rows = 50_000
+    k = pa.array(rng.integers(-100, 100, rows), pa.int64(), mask=rng.random(rows) < 0.1)
+    a = pa.array(rng.integers(-10**12, 10**12, rows), pa.int64(), mask=rng.random(rows) < 0.2)
+    b = pa.array(rng.integers(-10**6, 10**6, rows), pa.int64(), mask=rng.random(rows) < 0.2)
+    buf = _stream(pa.table({"k": k, "a": a, "b": b}), chunk=7000)
+    r = b2a.ArrowIPCReader.open_buffers([buf])
+    scan = b2a.ArrowScan(r, device=0)
+    scan.upload()
+    scan.decode()
+    scan.finish()
+    preds = [("k", ">=", -20), ("k", "<", 35)]
+    total, res = scan.filter_sum_product(preds, "a", "b")
+    torch.cuda.synchronize()
+    kk, aa, bb = (np.asarray(x.fill_null(0).to_numpy(zero_copy_only=False), dtype=object) for x in (k, a, b))
+    passing = np.asarray(k.is_valid()) & (kk >= -20) & (kk < 35)
+    both = passing & np.asarray(a.is_valid()) & np.asarray(b.is_valid())
+    want = int(sum(int(x) * int(y) for x, y in zip(aa[both], bb[both])))
+    lo, hi = [int(x) for x in res.cpu().tolist()]
+    got = ((hi << 64) | (lo & 0xFFFFFFFFFFFFFFFF))
+    got = got - (1 << 128) if got >= 1 << 127 else got
+    assert int(total.item()) == int(passing.sum()) and got == want

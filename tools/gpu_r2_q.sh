@@ -7,5 +7,6 @@ import json
 d=json.loads(open('gpurun_out/bench_q.json').read().strip().splitlines()[-1])
 f=d['legs']['filter_q6']
 print('zero-copy ms', f['ms_per_step'], 'G rows/s', f['value']/1e9, 'frac', f['roofline']['frac'], 'kernels', f['kernels_per_step'], 'graph', f['cuda_graph'])
-print('materialised ms', f['materialised']['ms_per_step'], 'frac', f['materialised']['roofline']['frac'], 'same', f['same_answer_both_ways'], f.get('sum'), f.get('known_answer_ok'))
+print('two kernels ms', f['zero_copy_two_kernels']['ms_per_step'], 'fused', f['zero_copy_fused']['ms_per_step'], f['variant'])
+print('materialised ms', f['materialised']['ms_per_step'], 'frac', f['materialised']['roofline']['frac'], 'same', f['same_answer_every_way'], f.get('sum'), f.get('known_answer_ok'))
 PY
