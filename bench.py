@@ -445,11 +445,21 @@ def _q6_device_variant(ctx, path, steps, device_alias, fused=False):
     alg = (scan.algorithmic_bytes if decodes else 0) + my_rows * 20 + int(fout[2].item()) * ((0 if fused else 4) + 16)
     kernels = (["b2a_decode_kernel"] if decodes else []) + \
         (["b2a_filter_sum_kernel"] if fused else ["b2a_filter_kernel", "b2a_sum_product_kernel"])
+    traffic, traffic_source = None, None
+    if not decodes:  # the filter kernel is (nearly) the whole step: its DRAM bytes from the builder's ncu capture
+        try:
+            tf = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["b2a_filter_kernel"]
+            traffic = int((tf["dram_bytes_read"] + tf["dram_bytes_write"]) / tf["rows_per_launch"] * my_rows)
+            traffic_source = ("profiles/traffic.json: dram__bytes_read+write of b2a_filter_kernel (ncu --set full, SF10), per "
+                              "row, x the rows of this launch (not measured in this run)")
+        except Exception:  # noqa: BLE001
+            pass
     r = {"ms_per_step": ms, "value": rows / (ms / 1e3), "rows": rows, "selected": selected, "sum": _decimal_str(total, 4),
          "cuda_graph": graph is not None, "kernels_per_step": len(kernels),
          "roofline": {"bound": "hbm", "kernels": kernels, "achieved": alg / (ms / 1e3) / 1e9, "peak": ctx.peak,
                       "unit": "GB/s", "frac": alg / (ms / 1e3) / 1e9 / ctx.peak,
-                      "algorithmic_bytes_per_step_rank0": int(alg), "traffic": None}}
+                      "algorithmic_bytes_per_step_rank0": int(alg), "traffic": traffic,
+                      "traffic_source": traffic_source}}
     del d_image, d_out
     scan.close()
     reader.close()
