@@ -29,66 +29,41 @@ struct FilterParams {
 // order: three barriers per vector.
 static constexpr int kFilterRowsPerThread = B2A_VECTOR_SIZE / kFilterThreads; // 8
 
-template <typename T>
-__device__ __forceinline__ void load_pred_values(const uint8_t *__restrict__ p, uint32_t rows, int64_t (&v)[kFilterRowsPerThread]) {
+// One run of predicates on ONE column (the host sorts the predicates by column): the vector's values are loaded once, in the
+// column's own type — a 4-byte date is compared as 4 bytes, not widened to 64 bits first —, masked by the column's NULLs,
+// and every predicate of the run is a 3-bit truth table over {v < c, v == c, v > c} (bits 0, 1, 2) looked up per value: no
+// branch on the operator.  A constant outside the type's range decides the predicate for the whole vector.
+// Returns the index of the first predicate behind the run.  FULL: the vector holds all 2 048 rows (no bounds checks).
+template <typename T, bool FULL>
+__device__ __forceinline__ uint32_t filter_run(const uint8_t *__restrict__ out, const uint64_t *cc, uint32_t rows,
+                                               const FilterParams &fp, uint32_t p, uint32_t &pass) {
+	const T *col = reinterpret_cast<const T *>(out + cc[2 * p]);
+	const uint64_t voff = cc[2 * p + 1];
+	T v[kFilterRowsPerThread];
 #pragma unroll
 	for (int k = 0; k < kFilterRowsPerThread; k++) {
 		const uint32_t r = k * kFilterThreads + threadIdx.x;
-		v[k] = r < rows ? static_cast<int64_t>(__ldg(reinterpret_cast<const T *>(p) + r)) : 0;
+		v[k] = (FULL || r < rows) ? __ldg(col + r) : T(0);
 	}
-}
-
-// bit k of the result: row k * 256 + thread of the vector is valid and passes every predicate.  cc = the vector's table
-// entries {data offset, validity offset} per predicate (shared memory).
-__device__ __forceinline__ uint32_t filter_pass_bits(const uint8_t *__restrict__ out, const uint64_t *cc, uint32_t rows,
-                                                     const FilterParams &fp) {
-	uint32_t pass = 0; // bit k: row k * 256 + thread passes
+	if (voff != B2A_NONE_OFF) {
+		const unsigned long long *mask = reinterpret_cast<const unsigned long long *>(out + voff);
 #pragma unroll
-	for (int k = 0; k < kFilterRowsPerThread; k++) {
-		pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
-	}
-	int64_t v[kFilterRowsPerThread];
-	for (uint32_t p = 0; p < fp.n_preds; p++) {
-		const bool reuse = fp.same_column[p] != 0; // (values loaded and masked by NULLs under the previous predicate)
-		const uint64_t doff = cc[2 * p], voff = reuse ? B2A_NONE_OFF : cc[2 * p + 1];
-		switch (reuse ? 0xFFu : fp.widths[p]) { // 0x80 | width: unsigned column, zero-extended (UTINYINT / USMALLINT / UINTEGER)
-		case 1:
-			load_pred_values<int8_t>(out + doff, rows, v);
-			break;
-		case 2:
-			load_pred_values<int16_t>(out + doff, rows, v);
-			break;
-		case 4:
-			load_pred_values<int32_t>(out + doff, rows, v);
-			break;
-		case 0x81:
-			load_pred_values<uint8_t>(out + doff, rows, v);
-			break;
-		case 0x82:
-			load_pred_values<uint16_t>(out + doff, rows, v);
-			break;
-		case 0x84:
-			load_pred_values<uint32_t>(out + doff, rows, v);
-			break;
-		case 0xFF:
-			break;
-		default:
-			load_pred_values<int64_t>(out + doff, rows, v);
-			break;
-		}
-		if (voff != B2A_NONE_OFF) {
-#pragma unroll
-			for (int k = 0; k < kFilterRowsPerThread; k++) {
-				const uint32_t r = k * kFilterThreads + threadIdx.x;
-				if (r < rows) {
-					const uint64_t w = __ldg(reinterpret_cast<const unsigned long long *>(out + voff) + (r >> 6));
-					if (!((w >> (r & 63)) & 1)) {
-						pass &= ~(1u << k);
-					}
+		for (int k = 0; k < kFilterRowsPerThread; k++) {
+			const uint32_t r = k * kFilterThreads + threadIdx.x;
+			if (FULL || r < rows) {
+				const uint64_t w = __ldg(mask + (r >> 6));
+				if (!((w >> (r & 63)) & 1)) {
+					pass &= ~(1u << k);
 				}
 			}
 		}
-		// the comparison as a truth table over {v < c, v == c, v > c} (bits 0, 1, 2): no branch on the operator per value
+	}
+	constexpr bool kSigned = T(-1) < T(0);
+	constexpr int64_t kLo = !kSigned ? 0 : sizeof(T) == 8 ? INT64_MIN : -(int64_t(1) << (8 * (sizeof(T) & 7) - 1));
+	constexpr int64_t kHi = sizeof(T) == 8 ? INT64_MAX
+	                        : kSigned      ? (int64_t(1) << (8 * (sizeof(T) & 7) - 1)) - 1
+	                                       : (int64_t(1) << (8 * (sizeof(T) & 7))) - 1;
+	do {
 		const uint32_t cmp = fp.preds[p].cmp;
 		const uint32_t accept = cmp == B2A_CMP_EQ   ? 2u
 		                        : cmp == B2A_CMP_NE ? 5u
@@ -97,13 +72,68 @@ __device__ __forceinline__ uint32_t filter_pass_bits(const uint8_t *__restrict__
 		                        : cmp == B2A_CMP_GT ? 4u
 		                                            : 6u;
 		const int64_t c = fp.preds[p].constant;
+		if (sizeof(T) < 8 && c > kHi) { // every value is below the constant
+			pass = (accept & 1u) ? pass : 0u;
+		} else if (sizeof(T) < 8 && c < kLo) { // every value is above it
+			pass = (accept & 4u) ? pass : 0u;
+		} else {
+			const T ct = static_cast<T>(c);
+#pragma unroll
+			for (int k = 0; k < kFilterRowsPerThread; k++) {
+				const uint32_t which = v[k] < ct ? 0u : (v[k] == ct ? 1u : 2u);
+				pass &= ~((((accept >> which) & 1u) ^ 1u) << k);
+			}
+		}
+		p++;
+	} while (p < fp.n_preds && fp.same_column[p]);
+	return p;
+}
+
+// bit k of the result: row k * 256 + thread of the vector is valid and passes every predicate.  cc = the vector's table
+// entries {data offset, validity offset} per predicate (shared memory).
+template <bool FULL>
+__device__ __forceinline__ uint32_t filter_pass_bits_t(const uint8_t *__restrict__ out, const uint64_t *cc, uint32_t rows,
+                                                       const FilterParams &fp) {
+	uint32_t pass = 0xFFu; // bit k: row k * 256 + thread passes
+	if (!FULL) {
+		pass = 0;
 #pragma unroll
 		for (int k = 0; k < kFilterRowsPerThread; k++) {
-			const uint32_t which = v[k] < c ? 0u : (v[k] == c ? 1u : 2u);
-			pass &= ~((((accept >> which) & 1u) ^ 1u) << k);
+			pass |= (k * kFilterThreads + threadIdx.x < rows ? 1u : 0u) << k;
+		}
+	}
+	uint32_t p = 0;
+	while (p < fp.n_preds) {
+		switch (fp.widths[p]) { // 0x80 | width: unsigned column (UTINYINT / USMALLINT / UINTEGER)
+		case 1:
+			p = filter_run<int8_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		case 2:
+			p = filter_run<int16_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		case 4:
+			p = filter_run<int32_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		case 0x81:
+			p = filter_run<uint8_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		case 0x82:
+			p = filter_run<uint16_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		case 0x84:
+			p = filter_run<uint32_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
+		default:
+			p = filter_run<int64_t, FULL>(out, cc, rows, fp, p, pass);
+			break;
 		}
 	}
 	return pass;
+}
+
+__device__ __forceinline__ uint32_t filter_pass_bits(const uint8_t *__restrict__ out, const uint64_t *cc, uint32_t rows,
+                                                     const FilterParams &fp) {
+	return rows == B2A_VECTOR_SIZE ? filter_pass_bits_t<true>(out, cc, rows, fp) : filter_pass_bits_t<false>(out, cc, rows, fp);
 }
 
 __global__ void __launch_bounds__(kFilterThreads, 8)
@@ -229,7 +259,7 @@ int LaunchFilter(const FilterLaunch &l, void *stream) {
 // skips a NULL product); per CTA: one warp reduction and one pair of atomics at the very end.  Table per vector =
 // n_preds {data, validity} pairs followed by the pairs of a and b.  One barrier per vector (the table prefetch).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kFilterThreads, 5)
+__global__ void __launch_bounds__(kFilterThreads, 6)
     b2a_filter_sum_kernel(const uint8_t *__restrict__ out, const uint64_t *__restrict__ chunk_col,
                           const uint32_t *__restrict__ chunk_rows, uint64_t n_chunks, FilterParams fp,
                           unsigned long long *total, unsigned long long *result) {
