@@ -379,3 +379,49 @@ def test_filter_sum_product_fused_equals_the_two_kernels(b2a, cuda_device):
     got = ((hi << 64) | (lo & 0xFFFFFFFFFFFFFFFF))
     got = got - (1 << 128) if got >= 1 << 127 else got
     assert int(total.item()) == int(passing.sum()) and got == want
+
+
+def test_filter_every_width_and_constants_outside_the_type(b2a, cuda_device):
+    """predicate columns of every width the filter takes (1 / 2 / 4 / 8 bytes, signed and unsigned, date32, timestamp) are
+    compared in their own type: constants at, just inside and far outside the type's range, all six operators, NULLs, a
+    ragged last vector — per-vector selection vectors against numpy; the fused filter + aggregate sees the same rows"""
+    import torch
+    from test_gpu_parity import _check_filter, _device_scan
+    rng = np.random.default_rng(17)
+    n = 2048 * 3 + 777
+    def col(lo, hi, dt, ty, null_p=0.1):
+        return pa.array(rng.integers(lo, hi, n).astype(dt), ty, mask=rng.random(n) < null_p)
+    t = pa.table({
+        "i8": col(-128, 128, np.int8, pa.int8()), "i16": col(-2**15, 2**15, np.int16, pa.int16()),
+        "i32": col(-2**31, 2**31, np.int32, pa.int32()), "i64": col(-2**62, 2**62, np.int64, pa.int64(), 0.0),
+        "u8": col(0, 256, np.uint8, pa.uint8()), "u16": col(0, 2**16, np.uint16, pa.uint16(), 0.0),
+        "u32": col(0, 2**32, np.uint32, pa.uint32()),
+        "d": pa.array(rng.integers(-30000, 30000, n).astype(np.int32), pa.date32()),
+        "w": pa.array(rng.integers(1, 1000, n), pa.int64()),
+    })
+    r, scan = _device_scan(b2a, _stream(t, chunk=2048 * 2 + 500))
+    brows = [r.batch_info(i).rows for i in range(r.num_batches)]
+    edges = {"i8": (-128, 127), "i16": (-2**15, 2**15 - 1), "i32": (-2**31, 2**31 - 1), "u8": (0, 255),
+             "u16": (0, 2**16 - 1), "u32": (0, 2**32 - 1), "d": (-2**31, 2**31 - 1), "i64": (-2**63, 2**63 - 1)}
+    checked = 0
+    for name, (lo, hi) in edges.items():
+        consts = {lo, hi, lo + 1, hi - 1, 0, (lo + hi) // 3}
+        if name != "i64":
+            consts |= {lo - 1, hi + 1, lo - 10**9, hi + 10**12, -2**62, 2**62}
+        for c in sorted(consts):
+            for op in ("=", "!=", "<", "<=", ">", ">="):
+                preds = [(name, op, c)]
+                sel, count, total = scan.filter(preds)
+                mask = _check_filter(scan, t, preds, sel, count, total, brows)
+                tot2, res = scan.filter_sum_product(preds, "w", "w")
+                torch.cuda.synchronize()
+                ww = np.asarray(t.column("w").to_numpy(), dtype=object)
+                assert int(tot2.item()) == int(mask.sum())
+                lo64, hi64 = [int(x) for x in res.cpu().tolist()]
+                assert ((hi64 << 64) | (lo64 & 0xFFFFFFFFFFFFFFFF)) == int(sum(int(x) * int(x) for x in ww[mask]))
+                checked += 1
+    # runs: several predicates on one column next to predicates on another, given out of order
+    preds = [("i32", ">=", -2**30), ("u8", "<", 200), ("i32", "<", 2**30), ("d", ">=", -20000), ("u8", ">", 3), ("d", "!=", 0)]
+    sel, count, total = scan.filter(preds)
+    _check_filter(scan, t, preds, sel, count, total, brows)
+    assert checked > 400
