@@ -1,10 +1,51 @@
 #include "scanner/host_stage.hpp"
 
 #include <cerrno>
+#include <cstdlib>
 #include <cstring>
 #include <unistd.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 namespace b2a {
+
+// Copy into the pinned ring with non-temporal stores: the bytes are read next by the copy engine, not by a core, and a
+// plain store to a line that is not in the cache first READS it (memcpy of pieces <= 1 MiB stays below glibc's own
+// non-temporal threshold): a third of the staging threads' memory traffic.  Source and destination of a piece share their
+// phase inside a 16-byte vector (StagePlan), so both become aligned together.
+static void StreamCopy(uint8_t *dst, const uint8_t *src, uint64_t n) {
+#if defined(__SSE2__)
+	static const bool plain = std::getenv("B2A_STAGE_PLAIN_MEMCPY") != nullptr;
+	if (!plain && n >= 256 && ((reinterpret_cast<uintptr_t>(dst) ^ reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+		const uint64_t head = (16 - (reinterpret_cast<uintptr_t>(dst) & 15)) & 15;
+		std::memcpy(dst, src, head);
+		dst += head;
+		src += head;
+		n -= head;
+		const uint64_t nv = n >> 4;
+		const __m128i *s = reinterpret_cast<const __m128i *>(src);
+		__m128i *d = reinterpret_cast<__m128i *>(dst);
+		uint64_t i = 0;
+		for (; i + 4 <= nv; i += 4) {
+			const __m128i a = _mm_load_si128(s + i), b = _mm_load_si128(s + i + 1), c = _mm_load_si128(s + i + 2),
+			              e = _mm_load_si128(s + i + 3);
+			_mm_stream_si128(d + i, a);
+			_mm_stream_si128(d + i + 1, b);
+			_mm_stream_si128(d + i + 2, c);
+			_mm_stream_si128(d + i + 3, e);
+		}
+		for (; i < nv; i++) {
+			_mm_stream_si128(d + i, _mm_load_si128(s + i));
+		}
+		_mm_sfence();
+		std::memcpy(dst + (nv << 4), src + (nv << 4), n & 15);
+		return;
+	}
+#endif
+	std::memcpy(dst, src, n);
+}
+
 
 void StagePlan::Build(const ScanPlan &plan, uint32_t n_slices_p, uint64_t align_p) {
 	n_slices = n_slices_p;
@@ -91,7 +132,7 @@ void StageWorkers::Run() {
 		const StagePiece &pc = plan.pieces[q];
 		uint8_t *dst = ring[slice % ring_size] + pc.stage;
 		if (io == 0 || fd < 0) {
-			std::memcpy(dst, image + pc.src, pc.bytes);
+			StreamCopy(dst, image + pc.src, pc.bytes);
 		} else {
 			// the reference reads through BufferedFileReader, 4 KiB per read() (ipc_file_stream_reader.cpp:80-138); here
 			// every piece (<= 1 MiB) is one pread straight into pinned memory, many in flight
