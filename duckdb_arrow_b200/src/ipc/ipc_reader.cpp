@@ -17,13 +17,93 @@
 #include <unistd.h>
 #include <unordered_set>
 
+#include <mutex>
+#include <thread>
+#include <vector>
+
 namespace b2a {
 
 static const uint32_t kContinuationToken = 0xFFFFFFFFu;
 
+// ---- mappings of large files are kept for the next open of the same (unchanged) file: unmapping an 8.5 GB mapping whose
+// pages were touched and faulting a fresh one in again cost ~ 30 ms per read_arrow call (tools/time_call_parts.py), and the
+// address-space lock held by munmap stalls whoever maps next.  A mapping is identified by {device, inode, size, mtime ns}
+// and handed to ONE reader at a time; at most two idle mappings are kept, an evicted one is unmapped by a detached thread,
+// 128 MiB at a time.
+namespace {
+struct IdleMapping {
+	dev_t dev;
+	ino_t ino;
+	off_t size;
+	int64_t mtime_ns;
+	void *base;
+};
+std::mutex g_map_mu;
+std::vector<IdleMapping> g_idle_maps; // oldest first
+constexpr size_t kCachedMappingMin = size_t(64) << 20;
+constexpr size_t kIdleMappings = 2;
+
+int64_t MtimeNs(const struct stat &st) {
+	return static_cast<int64_t>(st.st_mtim.tv_sec) * 1000000000ll + st.st_mtim.tv_nsec;
+}
+
+void UnmapInBackground(void *base_p, size_t len) {
+	uint8_t *base = static_cast<uint8_t *>(base_p);
+	try {
+		std::thread([base, len] {
+			const size_t step = size_t(128) << 20;
+			for (size_t off = 0; off < len; off += step) {
+				munmap(base + off, len - off < step ? len - off : step);
+			}
+		}).detach();
+	} catch (...) {
+		munmap(base, len);
+	}
+}
+
+void *TakeIdleMapping(const struct stat &st) {
+	std::lock_guard<std::mutex> lock(g_map_mu);
+	for (size_t i = 0; i < g_idle_maps.size(); i++) {
+		const IdleMapping &m = g_idle_maps[i];
+		if (m.dev == st.st_dev && m.ino == st.st_ino && m.size == st.st_size && m.mtime_ns == MtimeNs(st)) {
+			void *base = m.base;
+			g_idle_maps.erase(g_idle_maps.begin() + static_cast<std::ptrdiff_t>(i));
+			return base;
+		}
+	}
+	return nullptr;
+}
+
+void ReleaseMapping(int fd, void *base, size_t len) {
+	struct stat st;
+	if (len < kCachedMappingMin || fd < 0 || fstat(fd, &st) != 0 || static_cast<size_t>(st.st_size) != len) {
+		if (len >= kCachedMappingMin) {
+			UnmapInBackground(base, len);
+		} else {
+			munmap(base, len);
+		}
+		return;
+	}
+	IdleMapping evicted {};
+	bool evict = false;
+	{
+		std::lock_guard<std::mutex> lock(g_map_mu);
+		g_idle_maps.push_back(IdleMapping {st.st_dev, st.st_ino, st.st_size, MtimeNs(st), base});
+		if (g_idle_maps.size() > kIdleMappings) {
+			evicted = g_idle_maps.front();
+			g_idle_maps.erase(g_idle_maps.begin());
+			evict = true;
+		}
+	}
+	if (evict) {
+		UnmapInBackground(evicted.base, static_cast<size_t>(evicted.size));
+	}
+}
+} // namespace
+
 Reader::~Reader() {
 	if (mmap_base) {
-		munmap(mmap_base, mmap_len);
+		ReleaseMapping(fd, mmap_base, mmap_len); // (before the descriptor goes: the mapping is filed under the file's identity)
 	}
 	if (fd >= 0) {
 		close(fd);
@@ -52,7 +132,10 @@ void Reader::OpenFile(const std::string &path_p) {
 	}
 	image_size = static_cast<uint64_t>(st.st_size);
 	if (image_size > 0) {
-		mmap_base = mmap(nullptr, image_size, PROT_READ, MAP_PRIVATE, fd, 0);
+		mmap_base = image_size >= kCachedMappingMin ? TakeIdleMapping(st) : nullptr;
+		if (!mmap_base) {
+			mmap_base = mmap(nullptr, image_size, PROT_READ, MAP_PRIVATE, fd, 0);
+		}
 		if (mmap_base == MAP_FAILED) {
 			mmap_base = nullptr;
 			throw Error(B2A_EIO, "Cannot mmap file \"" + path + "\"");

@@ -344,3 +344,51 @@ def test_arrow_file_footer_index_equals_the_walk(b2a, tmp_path):
         w.write_table(t, max_chunksize=150)
     r = b2a.ArrowIPCReader.open_file(str(p))
     assert r.used_footer and r.num_rows == 400 and r.num_batches == 3
+
+
+def test_large_file_mappings_are_reused_and_never_stale(b2a, tmp_path):
+    """a file of >= 64 MiB keeps its mapping for the next open (ipc_reader.cpp: idle mappings, keyed by device / inode / size
+    / mtime); the same bytes come back through a reused mapping, two readers open at once get a mapping each, and a file
+    rewritten under the same name (other inode or mtime) is read fresh"""
+    import pyarrow as pa
+    import pyarrow.ipc as ipc
+
+    def write(path, seed):
+        rng = np.random.default_rng(seed)
+        t = pa.table({"v": pa.array(rng.integers(0, 2**62, 9_000_000), pa.int64())})
+        with ipc.new_stream(path, t.schema) as w:
+            w.write_table(t, max_chunksize=1_000_000)
+        return t
+
+    def first_values(r):
+        img = r.image()
+        bi = r.batch_info(0)
+        return bytes(img[bi.body_offset: bi.body_offset + 64])
+
+    p = str(tmp_path / "big.arrows")
+    t1 = write(p, 1)
+    assert os.path.getsize(p) >= 64 << 20
+    want1 = t1.column("v").chunk(0).buffers()[1].to_pybytes()[:64]
+    r = b2a.ArrowIPCReader.open_file(p)
+    assert r.num_batches == 9 and first_values(r) == want1
+    r.close()
+    ra, rb = b2a.ArrowIPCReader.open_file(p), b2a.ArrowIPCReader.open_file(p)  # one reuses the idle mapping, one maps anew
+    assert first_values(ra) == want1 and first_values(rb) == want1
+    ra.close()
+    rb.close()
+    os.remove(p)
+    t2 = write(p, 2)  # same name, same size, other content
+    want2 = t2.column("v").chunk(0).buffers()[1].to_pybytes()[:64]
+    assert want2 != want1
+    r = b2a.ArrowIPCReader.open_file(p)
+    assert first_values(r) == want2
+    r.close()
+    # modified IN PLACE (same inode and size; the mtime moves): no stale mapping either
+    with open(p, "r+b") as f:
+        bi_off = b2a.ArrowIPCReader.open_file(p).batch_info(0).body_offset
+        f.seek(bi_off)
+        f.write(b"\xAB" * 64)
+    os.utime(p, ns=(1, 1))
+    r = b2a.ArrowIPCReader.open_file(p)
+    assert first_values(r) == b"\xAB" * 64
+    r.close()
