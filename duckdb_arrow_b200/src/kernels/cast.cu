@@ -10,14 +10,15 @@
 //   integer -> VARCHAR      NumericHelper::FormatSigned                 (decimal digits, '-' sign)
 //   FLOAT/DOUBLE -> VARCHAR StringCast::Operation<double> = fmt "{}"    (shortest round-trip digits; fixed notation for
 //                           -4 <= exp10 < 16 with a trailing ".0" for integers, else d.ddde[+-]XX; nan / inf / -inf)
-//   VARCHAR -> DOUBLE       TryCast::Operation<string_t,double> (fast_float): restricted to inputs the Clinger fast
-//                           path converts exactly (<= 19 significant digits giving a mantissa < 2^53, |exp10| <= 22);
-//                           anything else raises B2A_CAST_DEV_PRECISION instead of returning an approximation
+//   VARCHAR -> DOUBLE       TryCast::Operation<string_t,double> = TryDoubleCast over fast_float, restated in
+//                           cast_parse_double.cuh (grammar, Clinger, Eisel-Lemire, inf / nan); only the big-decimal
+//                           fallback (> 19 digits beside a rounding boundary) raises B2A_CAST_DEV_PRECISION
 //   VARCHAR -> BIGINT       TryCast::Operation<string_t,int64_t>: optional sign, digits, optional fraction that rounds
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
 #include "cast.cuh"
 #include "cast_parse.cuh"
+#include "cast_parse_double.cuh"
 
 #include "b2arrow.h"
 
@@ -456,118 +457,15 @@ __device__ __forceinline__ const char *string_chars(const uint8_t *rec, int64_t 
 	return reinterpret_cast<const char *>(static_cast<uintptr_t>(static_cast<int64_t>(p) + ptr_delta));
 }
 
-__device__ __forceinline__ bool is_space(char c) {
-	return c == ' ' || (c >= '\t' && c <= '\r');
-}
-
-__constant__ double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
-                                  1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
-
-// 0 ok, else device error code
+// VARCHAR -> DOUBLE: DuckDB's TryDoubleCast over its vendored fast_float (grammar with '_' separators, Clinger's fast path,
+// Eisel-Lemire, inf / nan), restated in cast_parse_double.cuh and pinned on the CPU against the compiled reference
+// (tests/test_cast_parse.py).  The reference's big-decimal fallback (more than 19 digits next to a rounding boundary,
+// ~0.05 % of random long inputs) is not restated: B2A_CAST_DEV_PRECISION, never an approximation.
 __device__ __noinline__ uint32_t parse_double(const char *s, uint32_t n, double *out) {
-	uint32_t i = 0;
-	while (i < n && is_space(s[i])) {
-		i++;
-	}
-	while (n > i && is_space(s[n - 1])) {
-		n--;
-	}
-	if (i >= n) {
-		return B2A_CAST_DEV_PARSE;
-	}
-	bool neg = false;
-	if (s[i] == '-') {
-		neg = true;
-		i++;
-	} else if (s[i] == '+') {
-		i++;
-		if (i < n && s[i] == '-') {
-			return B2A_CAST_DEV_PARSE;
-		}
-	}
-	// nan / inf / infinity (case-insensitive)
-	{
-		const uint32_t r = n - i;
-		auto lc = [&](uint32_t j) { return static_cast<char>(s[i + j] | 0x20); };
-		if (r == 3 && lc(0) == 'n' && lc(1) == 'a' && lc(2) == 'n') {
-			*out = neg ? -nan("") : nan("");
-			return 0;
-		}
-		if ((r == 3 && lc(0) == 'i' && lc(1) == 'n' && lc(2) == 'f') ||
-		    (r == 8 && lc(0) == 'i' && lc(1) == 'n' && lc(2) == 'f' && lc(3) == 'i' && lc(4) == 'n' && lc(5) == 'i' &&
-		     lc(6) == 't' && lc(7) == 'y')) {
-			*out = neg ? -INFINITY : INFINITY;
-			return 0;
-		}
-	}
-	uint64_t mant = 0;
-	int digits = 0, sig = 0, exp10 = 0;
-	bool any = false, dropped_nonzero = false;
-	for (; i < n && s[i] >= '0' && s[i] <= '9'; i++) {
-		any = true;
-		if (sig < 19) {
-			mant = mant * 10 + static_cast<uint64_t>(s[i] - '0');
-			if (mant) {
-				sig++;
-			}
-		} else {
-			exp10++;
-			dropped_nonzero |= s[i] != '0';
-		}
-		digits++;
-	}
-	if (i < n && s[i] == '.') {
-		i++;
-		for (; i < n && s[i] >= '0' && s[i] <= '9'; i++) {
-			any = true;
-			if (sig < 19) {
-				mant = mant * 10 + static_cast<uint64_t>(s[i] - '0');
-				if (mant) {
-					sig++;
-				}
-				exp10--;
-			} else {
-				dropped_nonzero |= s[i] != '0';
-			}
-		}
-	}
-	if (!any) {
-		return B2A_CAST_DEV_PARSE;
-	}
-	if (i < n && (s[i] == 'e' || s[i] == 'E')) {
-		i++;
-		bool eneg = false;
-		if (i < n && (s[i] == '-' || s[i] == '+')) {
-			eneg = s[i] == '-';
-			i++;
-		}
-		if (i >= n) {
-			return B2A_CAST_DEV_PARSE;
-		}
-		int e = 0;
-		for (; i < n && s[i] >= '0' && s[i] <= '9'; i++) {
-			if (e < 100000) {
-				e = e * 10 + (s[i] - '0');
-			}
-		}
-		exp10 += eneg ? -e : e;
-	}
-	if (i != n) {
-		return B2A_CAST_DEV_PARSE;
-	}
-	if (mant == 0) {
-		*out = neg ? -0.0 : 0.0;
-		return 0;
-	}
-	// Clinger fast path: exact when mantissa < 2^53 and |exp10| <= 22 (one correctly rounded IEEE operation)
-	if (dropped_nonzero || mant > (1ull << 53) || exp10 < -22 || exp10 > 22) {
-		return B2A_CAST_DEV_PRECISION;
-	}
-	double d = static_cast<double>(mant);
-	d = exp10 < 0 ? d / kPow10[-exp10] : d * kPow10[exp10];
-	*out = neg ? -d : d;
-	return 0;
+	return castd::varchar_to_double(s, n, out);
 }
+static_assert(castd::NOT_A_NUMBER == B2A_CAST_DEV_PARSE && castd::NEEDS_MORE_PRECISION == B2A_CAST_DEV_PRECISION,
+              "cast error codes");
 
 // VARCHAR -> BIGINT: DuckDB's TrySimpleIntegerCast<int64_t>, restated in cast_parse.cuh (pinned on the CPU against the compiled
 // reference: tests/test_cast_parse.py).  Result codes are B2A_CAST_DEV_RANGE / B2A_CAST_DEV_PARSE.
