@@ -310,8 +310,9 @@ int b2a_multifile_finalize_finish(b2a_mf_finalize *fin, void *cuda_stream) {
 			return SetLastError(B2A_ECONVERSION, "file \"" + path + "\": could not convert a string to the "
 			                                                        "destination type of its column cast");
 		default:
-			return SetLastError(B2A_ENOTIMPL, "file \"" + path + "\": VARCHAR -> DOUBLE cast of a value that needs "
-			                                                     "extended precision is not implemented on the device");
+			return SetLastError(B2A_ENOTIMPL, "file \"" + path + "\": VARCHAR -> DOUBLE cast of a string on which the "
+			                                                     "reference cast reads past the end of its input ('_' "
+			                                                     "separators in a long integer) is not implemented on the device");
 		}
 	}
 	return B2A_OK;

@@ -7,7 +7,7 @@
 #define B2A_CAST_DEV_OK 0u
 #define B2A_CAST_DEV_RANGE 1u      /* ConversionException: value out of range for the destination type */
 #define B2A_CAST_DEV_PARSE 2u      /* ConversionException: could not convert string to the destination type */
-#define B2A_CAST_DEV_PRECISION 3u  /* NotImplemented: VARCHAR -> DOUBLE of a value that needs extended precision */
+#define B2A_CAST_DEV_PRECISION 3u  /* NotImplemented: VARCHAR -> DOUBLE where the reference reads past the end of the string */
 
 struct __attribute__((aligned(16))) b2a_cast_task {
 	uint64_t src;      /* scan arena offset: source vector data */
