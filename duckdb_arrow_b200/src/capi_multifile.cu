@@ -189,7 +189,14 @@ int b2a_multifile_finalize_create(b2a_multifile *m, uint32_t file, b2a_scan *sca
 			continue;
 		}
 		const MfType &to = m->mf.columns[static_cast<size_t>(c)].type;
-		const int sw = TypeWidth(mp.from.type_id), dw = TypeWidth(to.type_id);
+		const bool from_decimal = mp.from.type_id == B2A_T_DECIMAL;
+		const int sw = from_decimal ? DecimalPhysicalWidth(mp.from.decimal_width) : TypeWidth(mp.from.type_id);
+		const int dw = TypeWidth(to.type_id);
+		// VARCHAR results: a fixed slot per row, sized for the longest text of the source type (kernels/cast.cuh)
+		const uint64_t stride = (mp.from.type_id == B2A_T_TIMESTAMP || mp.from.type_id == B2A_T_HUGEINT ||
+		                         (from_decimal && mp.from.decimal_width > 18))
+		                            ? B2A_CAST_HEAP_STRIDE_WIDE
+		                            : B2A_CAST_HEAP_STRIDE;
 		for (uint64_t b = 0; b < nb; b++) {
 			const b2a_column_out &src = p.Column(p.batch_lo + b, static_cast<uint32_t>(mp.local_flat));
 			b2a_column_out &dst = fin->cols[b * ncol + static_cast<size_t>(c)];
@@ -206,9 +213,14 @@ int b2a_multifile_finalize_create(b2a_multifile *m, uint32_t file, b2a_scan *sca
 			t.dst = dst.data_off;
 			t.heap = B2A_NONE;
 			if (to.type_id == B2A_T_VARCHAR) {
-				dst.chars_off = alloc(src.rows * B2A_CAST_HEAP_STRIDE);
-				dst.chars_len = src.rows * B2A_CAST_HEAP_STRIDE;
+				dst.chars_off = alloc(src.rows * stride);
+				dst.chars_len = src.rows * stride;
 				t.heap = dst.chars_off;
+				t.heap_stride = static_cast<uint8_t>(stride);
+			}
+			if (from_decimal) {
+				t.decimal_width = static_cast<uint8_t>(mp.from.decimal_width);
+				t.decimal_scale = static_cast<uint8_t>(mp.from.decimal_scale);
 			}
 			t.rows = src.rows;
 			t.tile0 = tile;

@@ -296,6 +296,10 @@ bool CastSupported(const MfType &from, const MfType &to) {
 	if (a == B2A_T_DATE && b == B2A_T_TIMESTAMP) {
 		return true;
 	}
+	if (b == B2A_T_VARCHAR && (a == B2A_T_BOOLEAN || a == B2A_T_DATE || a == B2A_T_TIME || a == B2A_T_TIMESTAMP ||
+	                           a == B2A_T_DECIMAL || a == B2A_T_HUGEINT)) {
+		return true; // kernels/cast_format.cuh
+	}
 	return false;
 }
 

@@ -74,7 +74,7 @@ static std::string MetaValue(const Field &f, const char *key) {
 
 // physical decimal type: width<=4 int16, <=9 int32, <=18 int64, <=38 hugeint
 // (duckdb/src/common/types.cpp DecimalType / arrow_converter.cpp:234-256)
-static int DecimalPhysicalWidth(int width) {
+int DecimalPhysicalWidth(int width) {
 	if (width <= 4) {
 		return 2;
 	}

@@ -110,5 +110,6 @@ struct SchemaParser {
 void MapFieldToDuckDB(Field &f);
 
 int TypeWidth(int type_id);
+int DecimalPhysicalWidth(int decimal_width); // bytes of DuckDB's physical type for DECIMAL(width, .)
 
 } // namespace b2a

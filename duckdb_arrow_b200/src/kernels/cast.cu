@@ -15,9 +15,11 @@
 //   VARCHAR -> BIGINT       TryCast::Operation<string_t,int64_t>: optional sign, digits, optional fraction that rounds
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
+//   BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR   StringCast::Operation, restated in cast_format.cuh
 #include "cast.cuh"
 #include "cast_parse.cuh"
 #include "cast_parse_double.cuh"
+#include "cast_format.cuh"
 
 #include "b2arrow.h"
 
@@ -573,7 +575,7 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 					const uint32_t k = s_sint ? format_u64(sv < 0 ? 0 - static_cast<uint64_t>(sv) : static_cast<uint64_t>(sv),
 					                                       sv < 0, buf)
 					                          : format_u64(uv, false, buf);
-					const uint64_t h = t.heap + row * B2A_CAST_HEAP_STRIDE;
+					const uint64_t h = t.heap + row * t.heap_stride;
 					store_string(dst, l.final_arena + h, l.dst_ptr_origin + h, buf, k);
 				}
 			} else if (from == B2A_T_FLOAT || from == B2A_T_DOUBLE) {
@@ -591,7 +593,7 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 				} else if (to == B2A_T_VARCHAR) {
 					char buf[32];
 					const uint32_t k = format_double(v, from == B2A_T_FLOAT, buf);
-					const uint64_t h = t.heap + row * B2A_CAST_HEAP_STRIDE;
+					const uint64_t h = t.heap + row * t.heap_stride;
 					store_string(dst, l.final_arena + h, l.dst_ptr_origin + h, buf, k);
 				} else {
 					// TryCastWithOverflowCheckFloat: finite, lo <= v < hi, nearbyint (round half to even)
@@ -634,6 +636,34 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 					}
 					*reinterpret_cast<int64_t *>(dst) = v;
 				}
+			} else if (to == B2A_T_VARCHAR) { // BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT (cast_format.cuh)
+				char buf[castf::kMaxChars];
+				uint32_t k = 0;
+				if (from == B2A_T_BOOLEAN) {
+					k = castf::format_bool(*src != 0, buf);
+				} else if (from == B2A_T_DATE) {
+					k = castf::format_date(*reinterpret_cast<const int32_t *>(src), buf);
+				} else if (from == B2A_T_TIME) {
+					k = castf::format_time(*reinterpret_cast<const int64_t *>(src), buf);
+				} else if (from == B2A_T_TIMESTAMP) {
+					k = castf::format_timestamp(*reinterpret_cast<const int64_t *>(src), buf);
+					if (k == 0) {
+						raise(l.d_err, B2A_CAST_DEV_RANGE);
+						continue;
+					}
+				} else { // DECIMAL in its physical width, HUGEINT
+					__int128 v;
+					if (sw == 16) {
+						const uint64_t lo = *reinterpret_cast<const uint64_t *>(src);
+						const int64_t hi = *reinterpret_cast<const int64_t *>(src + 8);
+						v = (static_cast<__int128>(hi) << 64) | static_cast<__int128>(lo);
+					} else {
+						v = load_signed(src, sw);
+					}
+					k = castf::format_decimal(v, t.decimal_width, t.decimal_scale, buf);
+				}
+				const uint64_t h = t.heap + row * t.heap_stride;
+				store_string(dst, l.final_arena + h, l.dst_ptr_origin + h, buf, k);
 			} else if (from == B2A_T_DATE && to == B2A_T_TIMESTAMP) {
 				const int32_t d = *reinterpret_cast<const int32_t *>(src);
 				int64_t us;

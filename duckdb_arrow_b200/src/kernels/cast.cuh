@@ -13,15 +13,18 @@ struct __attribute__((aligned(16))) b2a_cast_task {
 	uint64_t src;      /* scan arena offset: source vector data */
 	uint64_t validity; /* scan arena offset: ValidityMask words, UINT64_MAX = all valid */
 	uint64_t dst;      /* final arena offset: destination vector data */
-	uint64_t heap;     /* final arena offset: string heap of this task (B2A_CAST_HEAP_STRIDE bytes per row) */
+	uint64_t heap;     /* final arena offset: string heap of this task (heap_stride bytes per row) */
 	uint64_t rows;
 	uint32_t tile0;    /* first global tile (2 048 rows each) */
 	uint16_t from, to; /* b2a_type_id */
 	uint8_t src_width, dst_width;
-	uint8_t pad[6];
+	uint8_t heap_stride;                  /* VARCHAR results: B2A_CAST_HEAP_STRIDE or _WIDE */
+	uint8_t decimal_width, decimal_scale; /* DECIMAL sources */
+	uint8_t pad[3];
 };
 
-#define B2A_CAST_HEAP_STRIDE 32u
+#define B2A_CAST_HEAP_STRIDE 32u      /* integers (<= 20 chars), FLOAT / DOUBLE (<= 24), DATE (<= 18), TIME (<= 15) */
+#define B2A_CAST_HEAP_STRIDE_WIDE 48u /* TIMESTAMP (<= 33), HUGEINT / DECIMAL of more than 18 digits (<= 40) */
 
 namespace b2a {
 

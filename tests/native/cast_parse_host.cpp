@@ -3,6 +3,7 @@
 // DOUBLE)) without a GPU.  Test infrastructure only.
 #include "kernels/cast_parse.cuh"
 #include "kernels/cast_parse_double.cuh"
+#include "kernels/cast_format.cuh"
 
 extern "C" unsigned b2a_test_varchar_to_bigint(const char *s, size_t n, long long *out) {
 	int64_t v = 0;
@@ -19,4 +20,21 @@ extern "C" unsigned b2a_test_varchar_to_double(const char *s, size_t n, unsigned
 	memcpy(&b, &v, sizeof(b));
 	*bits = b;
 	return rc;
+}
+
+// kind: 0 BOOLEAN, 1 DATE, 2 TIME, 3 TIMESTAMP, 4 DECIMAL / HUGEINT (value = low / high 64 bits, width, scale); -> length
+extern "C" unsigned b2a_test_format(int kind, unsigned long long low, long long high, unsigned width, unsigned scale, char *out) {
+	using namespace b2a::castf;
+	switch (kind) {
+	case 0:
+		return format_bool(low != 0, out);
+	case 1:
+		return format_date(static_cast<int32_t>(static_cast<int64_t>(low)), out);
+	case 2:
+		return format_time(static_cast<int64_t>(low), out);
+	case 3:
+		return format_timestamp(static_cast<int64_t>(low), out);
+	default:
+		return format_decimal((static_cast<__int128>(high) << 64) | static_cast<__int128>(low), width, scale, out);
+	}
 }

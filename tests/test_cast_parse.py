@@ -227,3 +227,131 @@ def test_varchar_to_double_golden_fixture(parse_double):
     for s, _ in doc["undefined_in_reference"]:
         assert parse_double(s)[0] == 3, s
     assert max(len(s) for s, _ in doc["values"]) > 768  # the big-decimal fallback with truncated digits is in there
+
+
+# ---- BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR (src/kernels/cast_format.cuh) ---------------------------
+
+@pytest.fixture(scope="module")
+def fmt(parse_double):  # (parse_double builds the shared library)
+    lib = ctypes.CDLL(os.path.join(ROOT, "tests", "native", "libcast_parse_host.so"))
+    lib.b2a_test_format.argtypes = [ctypes.c_int, ctypes.c_ulonglong, ctypes.c_longlong, ctypes.c_uint, ctypes.c_uint,
+                                    ctypes.c_char_p]
+    lib.b2a_test_format.restype = ctypes.c_uint
+
+    def f(kind: int, value: int, width: int = 0, scale: int = 0) -> str:
+        buf = ctypes.create_string_buffer(64)
+        v = value & ((1 << 128) - 1)
+        low, high = v & ((1 << 64) - 1), v >> 64
+        if high >= 1 << 63:
+            high -= 1 << 64
+        n = lib.b2a_test_format(kind, low, high, width, scale, buf)
+        assert n <= 48
+        return buf.raw[:n].decode()
+    return f
+
+
+def arrow_array_of(type_name: str, raw: list):
+    """raw integers (days, microseconds, unscaled decimal values, 0 / 1) -> a pyarrow array of the Arrow type DuckDB maps to
+    `type_name`"""
+    import decimal
+    import pyarrow as pa
+    if type_name == "DATE":
+        return pa.array(raw, pa.int32()).cast(pa.date32())
+    if type_name == "TIME":
+        return pa.array(raw, pa.int64()).cast(pa.time64("us"))
+    if type_name == "TIMESTAMP":
+        return pa.array(raw, pa.int64()).cast(pa.timestamp("us"))
+    if type_name == "BOOLEAN":
+        return pa.array([bool(v) for v in raw])
+    width, scale = (int(x) for x in type_name[8:-1].split(","))
+    with decimal.localcontext() as ctx:
+        ctx.prec = 60
+        return pa.array([decimal.Decimal(v).scaleb(-scale) for v in raw], pa.decimal128(width, scale))
+
+
+def cast_to_varchar_cases(seed=3, n=3000):
+    """-> {type name: (pyarrow array, [raw integer per row])}: edge values and random ones over each type's whole range"""
+    rng = np.random.default_rng(seed)
+    out = {}
+    d = [0, 1, -1, 365, -365, 11016, -719528, -719529, -719162, -719163, 2932896, 2932897, 2 ** 31 - 1, -(2 ** 31 - 1),
+         2 ** 31 - 2, -(2 ** 31 - 2), 59, 60, 789, 790, -141427, 2 ** 31 - 400, 146097, -146097, 146096, -146098]
+    d += [int(x) for x in rng.integers(-(2 ** 31 - 1), 2 ** 31 - 1, n)] + [int(x) for x in rng.integers(-800000, 3000000, n)]
+    out["DATE"] = (arrow_array_of("DATE", d), d)
+    t = [0, 1, 10, 100, 999999, 1000000, 59999999, 60000000, 3599999999, 3600000000, 86399999999, 86400000000, 123000, 120000,
+         45296789000, 45296000000, 45296700000]
+    t += [int(x) for x in rng.integers(0, 86400000000, n)] + [int(x) * 1000 for x in rng.integers(0, 86400000, n // 3)]
+    out["TIME"] = (arrow_array_of("TIME", t), t)
+    ts = [0, 1, -1, 999999, -999999, 1000000, -1000000, 86400000000, -86400000000, 86399999999, -86399999999, -86400000001,
+          2 ** 63 - 1, -(2 ** 63 - 1), 2 ** 63 - 2, -(2 ** 63 - 2), 1700000000123456, -62135596800000000, -62135596800000001,
+          -62167219200000000, -62167219200000001, 253402300799999999, 253402300800000000]
+    ts += [int(x) for x in rng.integers(-(2 ** 63 - 1), 2 ** 63 - 1, n)]
+    ts += [int(x) for x in rng.integers(-70000000000000000, 260000000000000000, n)]
+    out["TIMESTAMP"] = (arrow_array_of("TIMESTAMP", ts), ts)
+    out["BOOLEAN"] = (arrow_array_of("BOOLEAN", [1, 0, 1]), [1, 0, 1])
+    for width, scale in [(3, 0), (3, 3), (4, 2), (4, 4), (9, 0), (9, 4), (9, 9), (15, 2), (18, 0), (18, 18), (18, 17), (19, 0),
+                         (20, 5), (38, 0), (38, 10), (38, 37), (38, 38), (30, 30), (25, 24)]:
+        top = 10 ** width - 1
+        vals = [0, 1, -1, 5, -5, 10 ** scale, -(10 ** scale), 10 ** scale - 1, -(10 ** scale - 1), top, -top, top // 10, 10 ** (width - 1)]
+        vals += [int(rng.integers(-9, 10)) * 10 ** int(rng.integers(0, width)) for _ in range(60)]
+        for _ in range(max(20, n // 12)):
+            nd = int(rng.integers(1, width + 1))
+            v = int("".join(str(x) for x in rng.integers(0, 10, nd)))
+            vals.append(-v if rng.random() < 0.5 else v)
+        vals = [v for v in vals if abs(v) <= top]
+        out[f"DECIMAL({width},{scale})"] = (arrow_array_of(f"DECIMAL({width},{scale})", vals), vals)
+    return out
+
+
+KIND = {"BOOLEAN": 0, "DATE": 1, "TIME": 2, "TIMESTAMP": 3}
+
+
+def _format_with(fmt, type_name, raw):
+    if type_name.startswith("DECIMAL"):
+        width, scale = (int(x) for x in type_name[8:-1].split(","))
+        return fmt(4, raw, width, scale)
+    if type_name == "HUGEINT":
+        return fmt(4, raw, 0, 0)
+    return fmt(KIND[type_name], raw)
+
+
+@needs_ref
+def test_to_varchar_equals_the_reference_cast(fmt):
+    import pyarrow as pa
+    n = 0
+    for k, (type_name, (arr, raw)) in enumerate(cast_to_varchar_cases().items()):
+        if type_name == "TIMESTAMP":
+            # the first (partial) day of the int64 range: the reference throws "Date out of range in timestamp conversion"
+            low = [i for i, v in enumerate(raw) if -(2 ** 63 - 1) < v < -9223372022400000000]
+            assert low and all(_format_with(fmt, type_name, raw[i]) == "" for i in low)
+            R.register("t_fmt_low", pa.table({"c": arr.take(pa.array(low[:1]))}))
+            with pytest.raises(R.RefError, match="Date out of range"):
+                R.query("SELECT CAST(c AS VARCHAR) FROM t_fmt_low")
+            keep = [i for i in range(len(raw)) if i not in set(low)]
+            arr, raw = arr.take(pa.array(keep)), [raw[i] for i in keep]
+        R.register(f"t_fmt_{k}", pa.table({"i": pa.array(range(len(raw)), pa.int64()), "c": arr}))
+        rows = R.query(f"SELECT i, typeof(c), CAST(c AS VARCHAR) FROM t_fmt_{k} ORDER BY i")
+        assert len(rows) == len(raw) and rows[0][1] == type_name, (type_name, rows[0])
+        bad = [(v, r[2], _format_with(fmt, type_name, v)) for v, r in zip(raw, rows) if r[2] != _format_with(fmt, type_name, v)]
+        assert not bad, f"{type_name}: {len(bad)} of {len(raw)} differ, first {bad[:8]}"
+        n += len(raw)
+        if type_name == "DECIMAL(38,0)":
+            R.register("t_fmt_huge", pa.table({"i": pa.array(range(len(raw)), pa.int64()), "c": arr}))  # (a view reads once)
+            rows = R.query("SELECT i, typeof(CAST(c AS HUGEINT)), CAST(CAST(c AS HUGEINT) AS VARCHAR) FROM t_fmt_huge ORDER BY i")
+            assert rows[0][1] == "HUGEINT"
+            bad = [(v, r[2]) for v, r in zip(raw, rows) if r[2] != _format_with(fmt, "HUGEINT", v)]
+            assert not bad, bad[:8]
+    assert n > 20000
+
+
+def test_to_varchar_golden_fixture(fmt):
+    """tests/golden/cast_to_varchar.json (the reference's text, tools/gen_cast_varchar_golden.py) against the CPU build of the
+    device header: runs where oracle/_ref is absent, and is what the GPU test of the kernel compares with"""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "cast_to_varchar.json")) as f:
+        doc = json.load(f)
+    assert len(doc["types"]) >= 23
+    for type_name, case in doc["types"].items():
+        for raw, text in zip(case["raw"], case["text"]):
+            assert _format_with(fmt, type_name, int(raw)) == text, (type_name, raw)
+    for raw in doc["timestamp_out_of_range"]:
+        assert _format_with(fmt, "TIMESTAMP", int(raw)) == ""

@@ -346,6 +346,35 @@ def test_varchar_to_double_equals_the_reference_or_loud(b2a, cuda_device, tmp_pa
 
 
 @pytest.mark.gpu
+def test_temporal_decimal_boolean_to_varchar_equal_the_reference(b2a, cuda_device, tmp_path):
+    """a VARCHAR column in the first file, BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL(w,s) in the next: the device cast
+    (kernels/cast_format.cuh) against the text of the REFERENCE's CAST(c AS VARCHAR) (tests/golden/cast_to_varchar.json,
+    tools/gen_cast_varchar_golden.py) — every physical decimal width, " (BC)" years, +-infinity, 24:00:00"""
+    import json
+    from test_cast_parse import arrow_array_of
+    with open(os.path.join(os.path.dirname(__file__), "golden", "cast_to_varchar.json")) as fh:
+        doc = json.load(fh)
+    _write(str(tmp_path / "a.arrows"), pa.table({"v": pa.array(["first"])}))
+    for k, (type_name, case) in enumerate(doc["types"].items()):
+        raw = [int(x) for x in case["raw"]]
+        arr = arrow_array_of(type_name, raw)
+        arr = pa.concat_arrays([arr, pa.nulls(1, arr.type)])
+        _write(str(tmp_path / f"t{k}.arrows"), pa.table({"v": arr}), batch=200)
+        mfs = b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / f"t{k}.arrows")])
+        assert mfs.types == ["VARCHAR"]
+        got = [r[0] for r in rows_of(mfs)]
+        assert got[0] == "first" and got[-1] is None, type_name
+        bad = [(v, w, g) for v, w, g in zip(raw, case["text"], got[1:-1]) if w != g]
+        assert not bad and len(got) == len(raw) + 2, f"{type_name}: {len(bad)} differ, first {bad[:6]}"
+    # the first partial day of the int64 range: the reference throws "Date out of range in timestamp conversion"
+    low = [int(x) for x in doc["timestamp_out_of_range"]][:1]
+    assert low
+    _write(str(tmp_path / "low.arrows"), pa.table({"v": arrow_array_of("TIMESTAMP", [0] + low)}))
+    with pytest.raises(b2a.B2AError, match="out of range"):
+        rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "low.arrows")]))
+
+
+@pytest.mark.gpu
 def test_lineitem_glob_dictionary_union_by_name(b2a, cuda_device, tmp_path):
     """BASELINE config 4 in small: glob of lineitem files, dictionary-encoded strings, two schema variants under
     union_by_name (column order + INTEGER l_linenumber cast to BIGINT on the device); rows equal pyarrow's reading."""
