@@ -645,8 +645,11 @@ class MultiFileFile:
         co = _lib.ColumnOut()
         check(lib.b2a_multifile_finalize_column(self._fin, batch, column, C.byref(co)))
         src = self.reader.fields[mi.local_flat]
-        width = {"VARCHAR": 16, "DOUBLE": 8, "FLOAT": 4, "BIGINT": 8, "UBIGINT": 8, "INTEGER": 4, "UINTEGER": 4,
-                 "SMALLINT": 2, "USMALLINT": 2, "TINYINT": 1, "UTINYINT": 1, "TIMESTAMP": 8}[gc.type_id]
+        if gc.type_id == "DECIMAL":  # DuckDB's physical type for the width
+            width = 2 if gc.decimal[0] <= 4 else 4 if gc.decimal[0] <= 9 else 8 if gc.decimal[0] <= 18 else 16
+        else:
+            width = {"VARCHAR": 16, "DOUBLE": 8, "FLOAT": 4, "BIGINT": 8, "UBIGINT": 8, "INTEGER": 4, "UINTEGER": 4,
+                     "SMALLINT": 2, "USMALLINT": 2, "TINYINT": 1, "UTINYINT": 1, "TIMESTAMP": 8, "HUGEINT": 16}[gc.type_id]
         f = Field(src.index, gc.name, "", gc.type_id, "CAST", width, src.out_width, [], -1, True, 0, 0, 0, -1, "INVALID")
         return CastColumnView(self.ds, co, f, batch, self.final, self._h_final.data_ptr())
 

@@ -191,7 +191,8 @@ int b2a_multifile_finalize_create(b2a_multifile *m, uint32_t file, b2a_scan *sca
 		const MfType &to = m->mf.columns[static_cast<size_t>(c)].type;
 		const bool from_decimal = mp.from.type_id == B2A_T_DECIMAL;
 		const int sw = from_decimal ? DecimalPhysicalWidth(mp.from.decimal_width) : TypeWidth(mp.from.type_id);
-		const int dw = TypeWidth(to.type_id);
+		const bool to_decimal = to.type_id == B2A_T_DECIMAL;
+		const int dw = to_decimal ? DecimalPhysicalWidth(to.decimal_width) : TypeWidth(to.type_id);
 		// VARCHAR results: a fixed slot per row, sized for the longest text of the source type (kernels/cast.cuh)
 		const uint64_t stride = (mp.from.type_id == B2A_T_TIMESTAMP || mp.from.type_id == B2A_T_HUGEINT ||
 		                         (from_decimal && mp.from.decimal_width > 18))
@@ -221,6 +222,10 @@ int b2a_multifile_finalize_create(b2a_multifile *m, uint32_t file, b2a_scan *sca
 			if (from_decimal) {
 				t.decimal_width = static_cast<uint8_t>(mp.from.decimal_width);
 				t.decimal_scale = static_cast<uint8_t>(mp.from.decimal_scale);
+			}
+			if (to_decimal) {
+				t.dst_decimal_width = static_cast<uint8_t>(to.decimal_width);
+				t.dst_decimal_scale = static_cast<uint8_t>(to.decimal_scale);
 			}
 			t.rows = src.rows;
 			t.tile0 = tile;

@@ -91,6 +91,15 @@ static MfType Scalar(int type_id) {
 	return t;
 }
 
+static MfType Decimal(int width, int scale) {
+	MfType t;
+	t.type_id = B2A_T_DECIMAL;
+	t.decimal_width = width;
+	t.decimal_scale = scale;
+	t.name = "DECIMAL(" + std::to_string(width) + "," + std::to_string(scale) + ")";
+	return t;
+}
+
 // KeywordHelper::WriteOptionallyQuoted, reduced: quote anything that is not a plain lower-case identifier
 static std::string FieldName(const std::string &n) {
 	bool plain = !n.empty() && !std::isdigit(static_cast<unsigned char>(n[0]));
@@ -268,6 +277,55 @@ MfType ForceMaxType(const MfType &l, const MfType &r) {
 	if ((a == B2A_T_DATE && b == B2A_T_TIMESTAMP) || (a == B2A_T_TIMESTAMP && b == B2A_T_DATE)) {
 		return Scalar(B2A_T_TIMESTAMP);
 	}
+	if (a == B2A_T_DECIMAL && b == B2A_T_DECIMAL) {
+		// CombineEqualTypes (types.cpp): the digits in front of the point and behind it both have to fit; past 38 digits
+		// the scale gives way
+		const int extra = std::max(l.decimal_width - l.decimal_scale, r.decimal_width - r.decimal_scale);
+		int scale = std::max(l.decimal_scale, r.decimal_scale);
+		int width = extra + scale;
+		if (width > 38) {
+			width = 38;
+			scale = width - extra;
+		}
+		return Decimal(width, scale);
+	}
+	if (a == B2A_T_DECIMAL || b == B2A_T_DECIMAL) {
+		const MfType &d = a == B2A_T_DECIMAL ? l : r;
+		const int o = a == B2A_T_DECIMAL ? b : a;
+		if (o == B2A_T_FLOAT || o == B2A_T_DOUBLE) {
+			return Scalar(o); // DECIMAL casts implicitly to FLOAT / DOUBLE, not the other way (CastRules::ImplicitCast)
+		}
+		if (IsInt(o) || o == B2A_T_HUGEINT) {
+			// DecimalSizeCheck (types.cpp:859-887) over LogicalType::GetDecimalProperties of the integer type
+			int other_width = 38;
+			switch (o) {
+			case B2A_T_TINYINT:
+			case B2A_T_UTINYINT:
+				other_width = 3;
+				break;
+			case B2A_T_SMALLINT:
+			case B2A_T_USMALLINT:
+				other_width = 5;
+				break;
+			case B2A_T_INTEGER:
+			case B2A_T_UINTEGER:
+				other_width = 10;
+				break;
+			case B2A_T_BIGINT:
+				other_width = 19;
+				break;
+			case B2A_T_UBIGINT:
+				other_width = 20;
+				break;
+			default:
+				break;
+			}
+			if (other_width > d.decimal_width - d.decimal_scale) {
+				return Decimal(std::min(other_width + d.decimal_scale, 38), d.decimal_scale);
+			}
+			return d;
+		}
+	}
 	if (a == B2A_T_DECIMAL || b == B2A_T_DECIMAL || TypeScore(a) >= 100 || TypeScore(b) >= 100) {
 		throw Error(B2A_ENOTIMPL, "union_by_name: combining the column types " + l.name + " and " + r.name +
 		                              " is not implemented");
@@ -294,6 +352,12 @@ bool CastSupported(const MfType &from, const MfType &to) {
 		return true;
 	}
 	if (a == B2A_T_DATE && b == B2A_T_TIMESTAMP) {
+		return true;
+	}
+	if (IsInt(a) && (b == B2A_T_DECIMAL || b == B2A_T_HUGEINT)) {
+		return true; // kernels/cast_decimal.cuh; widening to 128 bits
+	}
+	if (a == B2A_T_DECIMAL && (b == B2A_T_DECIMAL || b == B2A_T_DOUBLE || b == B2A_T_FLOAT)) {
 		return true;
 	}
 	if (b == B2A_T_VARCHAR && (a == B2A_T_BOOLEAN || a == B2A_T_DATE || a == B2A_T_TIME || a == B2A_T_TIMESTAMP ||

@@ -16,10 +16,12 @@
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
 //   BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR   StringCast::Operation, restated in cast_format.cuh
+//   integer -> DECIMAL / HUGEINT, DECIMAL -> DECIMAL / DOUBLE / FLOAT   restated in cast_decimal.cuh
 #include "cast.cuh"
 #include "cast_parse.cuh"
 #include "cast_parse_double.cuh"
 #include "cast_format.cuh"
+#include "cast_decimal.cuh"
 
 #include "b2arrow.h"
 
@@ -95,6 +97,23 @@ __device__ __forceinline__ bool int_fits(bool src_signed, int64_t sv, uint64_t u
 		return sv >= 0 && static_cast<uint64_t>(sv) <= hi;
 	}
 	return uv <= hi;
+}
+
+__device__ __forceinline__ __int128 load_i128(const uint8_t *p, int w) { // a signed integer of 2 / 4 / 8 / 16 bytes
+	if (w == 16) {
+		const uint64_t lo = *reinterpret_cast<const uint64_t *>(p);
+		const int64_t hi = *reinterpret_cast<const int64_t *>(p + 8);
+		return (static_cast<__int128>(hi) << 64) | static_cast<__int128>(lo);
+	}
+	return load_signed(p, w);
+}
+__device__ __forceinline__ void store_i128(uint8_t *p, int w, __int128 v) {
+	if (w == 16) {
+		*reinterpret_cast<uint64_t *>(p) = static_cast<uint64_t>(v);
+		*reinterpret_cast<int64_t *>(p + 8) = static_cast<int64_t>(v >> 64);
+	} else {
+		store_int(p, w, static_cast<uint64_t>(v));
+	}
 }
 
 // ---- VARCHAR results: DuckDB string_t (len, 12 inlined bytes | 4 prefix bytes + pointer)
@@ -566,6 +585,16 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 						continue;
 					}
 					store_int(dst, dw, s_sint ? static_cast<uint64_t>(sv) : uv);
+				} else if (to == B2A_T_HUGEINT) {
+					store_i128(dst, 16, s_sint ? static_cast<__int128>(sv) : static_cast<__int128>(uv));
+				} else if (to == B2A_T_DECIMAL) {
+					__int128 r;
+					if (!castx::int_to_decimal(s_sint ? static_cast<__int128>(sv) : static_cast<__int128>(uv),
+					                           t.dst_decimal_width, t.dst_decimal_scale, &r)) {
+						raise(l.d_err, B2A_CAST_DEV_RANGE);
+						continue;
+					}
+					store_i128(dst, dw, r);
 				} else if (to == B2A_T_DOUBLE) {
 					*reinterpret_cast<double *>(dst) = s_sint ? static_cast<double>(sv) : static_cast<double>(uv);
 				} else if (to == B2A_T_FLOAT) {
@@ -636,6 +665,21 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 					}
 					*reinterpret_cast<int64_t *>(dst) = v;
 				}
+			} else if (from == B2A_T_DECIMAL && to != B2A_T_VARCHAR) { // cast_decimal.cuh
+				const __int128 v = load_i128(src, sw);
+				if (to == B2A_T_DOUBLE) {
+					*reinterpret_cast<double *>(dst) = castx::decimal_to_double(v, sw, t.decimal_scale);
+				} else if (to == B2A_T_FLOAT) {
+					*reinterpret_cast<float *>(dst) = castx::decimal_to_float(v, sw, t.decimal_scale);
+				} else {
+					__int128 r;
+					if (!castx::decimal_to_decimal(v, t.decimal_width, t.decimal_scale, t.dst_decimal_width,
+					                               t.dst_decimal_scale, &r)) {
+						raise(l.d_err, B2A_CAST_DEV_RANGE);
+						continue;
+					}
+					store_i128(dst, dw, r);
+				}
 			} else if (to == B2A_T_VARCHAR) { // BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT (cast_format.cuh)
 				char buf[castf::kMaxChars];
 				uint32_t k = 0;
@@ -652,15 +696,7 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 						continue;
 					}
 				} else { // DECIMAL in its physical width, HUGEINT
-					__int128 v;
-					if (sw == 16) {
-						const uint64_t lo = *reinterpret_cast<const uint64_t *>(src);
-						const int64_t hi = *reinterpret_cast<const int64_t *>(src + 8);
-						v = (static_cast<__int128>(hi) << 64) | static_cast<__int128>(lo);
-					} else {
-						v = load_signed(src, sw);
-					}
-					k = castf::format_decimal(v, t.decimal_width, t.decimal_scale, buf);
+					k = castf::format_decimal(load_i128(src, sw), t.decimal_width, t.decimal_scale, buf);
 				}
 				const uint64_t h = t.heap + row * t.heap_stride;
 				store_string(dst, l.final_arena + h, l.dst_ptr_origin + h, buf, k);

@@ -20,7 +20,8 @@ struct __attribute__((aligned(16))) b2a_cast_task {
 	uint8_t src_width, dst_width;
 	uint8_t heap_stride;                  /* VARCHAR results: B2A_CAST_HEAP_STRIDE or _WIDE */
 	uint8_t decimal_width, decimal_scale; /* DECIMAL sources */
-	uint8_t pad[3];
+	uint8_t dst_decimal_width, dst_decimal_scale; /* DECIMAL results */
+	uint8_t pad[1];
 };
 
 #define B2A_CAST_HEAP_STRIDE 32u      /* integers (<= 20 chars), FLOAT / DOUBLE (<= 24), DATE (<= 18), TIME (<= 15) */

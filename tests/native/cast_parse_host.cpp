@@ -4,6 +4,7 @@
 #include "kernels/cast_parse.cuh"
 #include "kernels/cast_parse_double.cuh"
 #include "kernels/cast_format.cuh"
+#include "kernels/cast_decimal.cuh"
 
 extern "C" unsigned b2a_test_varchar_to_bigint(const char *s, size_t n, long long *out) {
 	int64_t v = 0;
@@ -37,4 +38,32 @@ extern "C" unsigned b2a_test_format(int kind, unsigned long long low, long long 
 	default:
 		return format_decimal((static_cast<__int128>(high) << 64) | static_cast<__int128>(low), width, scale, out);
 	}
+}
+
+static __int128 wide(unsigned long long low, long long high) {
+	return (static_cast<__int128>(high) << 64) | static_cast<__int128>(low);
+}
+// op 0: integer -> DECIMAL(dw,ds); 1: DECIMAL(sw,ss) -> DECIMAL(dw,ds).  Returns 1 when the cast succeeds.
+extern "C" int b2a_test_to_decimal(int op, unsigned long long low, long long high, unsigned sw, unsigned ss, unsigned dw,
+                                   unsigned ds, unsigned long long *out_low, long long *out_high) {
+	__int128 r = 0;
+	const bool ok = op == 0 ? b2a::castx::int_to_decimal(wide(low, high), dw, ds, &r)
+	                        : b2a::castx::decimal_to_decimal(wide(low, high), sw, ss, dw, ds, &r);
+	*out_low = static_cast<unsigned long long>(r);
+	*out_high = static_cast<long long>(r >> 64);
+	return ok ? 1 : 0;
+}
+// DECIMAL of `src_bytes` physical bytes -> the bits of the DOUBLE (as_float = 0) or FLOAT (1)
+extern "C" unsigned long long b2a_test_decimal_to_real(unsigned long long low, long long high, int src_bytes, unsigned scale,
+                                                       int as_float) {
+	if (as_float) {
+		const float f = b2a::castx::decimal_to_float(wide(low, high), src_bytes, scale);
+		uint32_t b;
+		memcpy(&b, &f, sizeof(b));
+		return b;
+	}
+	const double d = b2a::castx::decimal_to_double(wide(low, high), src_bytes, scale);
+	uint64_t b;
+	memcpy(&b, &d, sizeof(b));
+	return b;
 }

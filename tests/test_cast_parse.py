@@ -355,3 +355,164 @@ def test_to_varchar_golden_fixture(fmt):
             assert _format_with(fmt, type_name, int(raw)) == text, (type_name, raw)
     for raw in doc["timestamp_out_of_range"]:
         assert _format_with(fmt, "TIMESTAMP", int(raw)) == ""
+
+
+# ---- into and out of DECIMAL (src/kernels/cast_decimal.cuh) -------------------------------------------------------------------
+
+@pytest.fixture(scope="module")
+def dec(parse_double):
+    lib = ctypes.CDLL(os.path.join(ROOT, "tests", "native", "libcast_parse_host.so"))
+    lib.b2a_test_to_decimal.argtypes = [ctypes.c_int, ctypes.c_ulonglong, ctypes.c_longlong] + [ctypes.c_uint] * 4 + [
+        ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_longlong)]
+    lib.b2a_test_to_decimal.restype = ctypes.c_int
+    lib.b2a_test_decimal_to_real.argtypes = [ctypes.c_ulonglong, ctypes.c_longlong, ctypes.c_int, ctypes.c_uint, ctypes.c_int]
+    lib.b2a_test_decimal_to_real.restype = ctypes.c_ulonglong
+
+    def split(value):
+        v = value & ((1 << 128) - 1)
+        low, high = v & ((1 << 64) - 1), v >> 64
+        return low, high - (1 << 64) if high >= 1 << 63 else high
+
+    class D:
+        @staticmethod
+        def to_decimal(op, value, sw, ss, dw, ds):
+            """-> the unscaled result, None when the reference's cast fails"""
+            lo, hi = ctypes.c_ulonglong(0), ctypes.c_longlong(0)
+            low, high = split(value)
+            ok = lib.b2a_test_to_decimal(op, low, high, sw, ss, dw, ds, ctypes.byref(lo), ctypes.byref(hi))
+            return (hi.value << 64 | lo.value) if ok else None
+
+        @staticmethod
+        def to_real(value, src_bytes, scale, as_float):
+            low, high = split(value)
+            return int(lib.b2a_test_decimal_to_real(low, high, src_bytes, scale, 1 if as_float else 0))
+    return D
+
+
+def physical_bytes(width):
+    return 2 if width <= 4 else 4 if width <= 9 else 8 if width <= 18 else 16
+
+
+def decimal_values(rng, width, scale, n):
+    top = 10 ** width - 1
+    vals = [0, 1, -1, 5, -5, top, -top, top // 10, 10 ** scale, -(10 ** scale), 10 ** scale // 2, -(10 ** scale // 2),
+            10 ** scale // 2 - 1, 10 ** scale * 3 // 2, -(10 ** scale * 3 // 2), 10 ** (width - 1), 2 ** 53, 2 ** 53 + 1, -(2 ** 53) - 1,
+            2 ** 24, 2 ** 24 + 1, 2 ** 64 - 1, 2 ** 64, -(2 ** 64), -(2 ** 64) + 1, -1 - 2 ** 63, 2 ** 63]
+    for _ in range(n):
+        nd = int(rng.integers(1, width + 1))
+        v = int("".join(str(x) for x in rng.integers(0, 10, nd)))
+        vals.append(-v if rng.random() < 0.5 else v)
+    for _ in range(n // 4):  # ...5 and ...49999 / ...50000 tails: the rounding of a scale-down
+        head = int(rng.integers(0, 10 ** max(1, min(width - scale, 9))))
+        tail = ("5" + "0" * (scale - 1)) if scale else ""
+        v = int(str(head) + tail) if tail else head
+        vals += [v, -v, v - 1, -(v - 1), v + 1]
+    return [v for v in vals if abs(v) <= top]
+
+
+def _unscaled(col):
+    import decimal
+    scale = col.type.scale
+    with decimal.localcontext() as ctx:
+        ctx.prec = 80
+        return [None if x is None else int(x.scaleb(scale)) for x in col.to_pylist()]
+
+
+def _export_column(sql):
+    import pyarrow as pa
+    batches = list(R.export(sql))
+    t = pa.Table.from_batches(batches).sort_by("i")
+    return t.column("r").combine_chunks()
+
+
+@needs_ref
+def test_casts_to_decimal_equal_the_reference(dec):
+    import pyarrow as pa
+    rng = np.random.default_rng(21)
+    n = 0
+    ints = {"TINYINT": pa.int8(), "SMALLINT": pa.int16(), "INTEGER": pa.int32(), "BIGINT": pa.int64(), "UTINYINT": pa.uint8(),
+            "USMALLINT": pa.uint16(), "UINTEGER": pa.uint32(), "UBIGINT": pa.uint64()}
+    targets = [(3, 0), (4, 1), (5, 0), (9, 2), (10, 0), (12, 2), (18, 0), (18, 3), (19, 0), (20, 0), (22, 2), (38, 0), (38, 19), (38, 30)]
+    k = 0
+    for name, t in ints.items():
+        info = np.iinfo(t.to_pandas_dtype())
+        vals = [int(info.min), int(info.max), 0, 1, 99, 100, 999, 1000, 9999, 10000, 99999, 100000] + \
+               [int(x) for x in rng.integers(info.min, info.max, 300, dtype=t.to_pandas_dtype(), endpoint=True)] + \
+               [int(x) for x in rng.integers(max(info.min, -100000), min(info.max, 100000), 200, endpoint=True)]
+        vals = [v for v in vals if info.min <= v <= info.max]
+        if info.min < 0:
+            vals += [-v for v in vals if info.min <= -v <= info.max]
+        for dw, ds in targets:
+            k += 1
+            R.register(f"t_i2d_{k}", pa.table({"i": pa.array(range(len(vals)), pa.int64()), "c": pa.array(vals, t)}))
+            got = _unscaled(_export_column(f"SELECT i, TRY_CAST(c AS DECIMAL({dw},{ds})) AS r FROM t_i2d_{k}"))
+            want = [dec.to_decimal(0, v, 0, 0, dw, ds) for v in vals]
+            bad = [(v, g, w) for v, g, w in zip(vals, got, want) if (None if w is None else _signed128(w)) != g]
+            assert not bad, f"{name} -> DECIMAL({dw},{ds}): {bad[:6]}"
+            n += len(vals)
+    pairs = [((4, 2), (9, 4)), ((4, 2), (4, 3)), ((4, 2), (3, 2)), ((4, 2), (4, 0)), ((4, 2), (2, 0)), ((9, 4), (18, 6)),
+             ((9, 4), (9, 6)), ((9, 4), (5, 1)), ((9, 9), (4, 2)), ((15, 2), (18, 4)), ((15, 2), (38, 10)), ((15, 2), (15, 0)),
+             ((15, 2), (12, 1)), ((18, 6), (18, 9)), ((18, 6), (9, 2)), ((18, 18), (18, 2)), ((18, 0), (38, 20)), ((18, 0), (38, 21)),
+             ((38, 10), (38, 0)), ((38, 10), (38, 12)), ((38, 10), (18, 2)), ((38, 10), (30, 10)), ((38, 0), (38, 5)), ((25, 5), (38, 18)),
+             ((25, 5), (20, 0)), ((38, 37), (38, 1)), ((20, 10), (4, 1)), ((38, 38), (38, 0)), ((38, 19), (9, 0))]
+    for (sw, ss), (dw, ds) in pairs:
+        k += 1
+        vals = decimal_values(rng, sw, ss, 250)
+        arr = arrow_array_of(f"DECIMAL({sw},{ss})", vals)
+        R.register(f"t_d2d_{k}", pa.table({"i": pa.array(range(len(vals)), pa.int64()), "c": arr}))
+        got = _unscaled(_export_column(f"SELECT i, TRY_CAST(c AS DECIMAL({dw},{ds})) AS r FROM t_d2d_{k}"))
+        want = [dec.to_decimal(1, v, sw, ss, dw, ds) for v in vals]
+        bad = [(v, g, w) for v, g, w in zip(vals, got, want) if (None if w is None else _signed128(w)) != g]
+        assert not bad, f"DECIMAL({sw},{ss}) -> DECIMAL({dw},{ds}): {len(bad)} differ, first {bad[:6]}"
+        n += len(vals)
+    assert n > 30000
+
+
+def _signed128(v):
+    v &= (1 << 128) - 1
+    return v - (1 << 128) if v >= 1 << 127 else v
+
+
+@needs_ref
+def test_decimal_to_double_and_float_equal_the_reference(dec):
+    import pyarrow as pa
+    rng = np.random.default_rng(22)
+    n = 0
+    for k, (w, s) in enumerate([(4, 0), (4, 2), (4, 4), (9, 0), (9, 3), (9, 9), (15, 2), (18, 0), (18, 4), (18, 18), (19, 0), (20, 5),
+                                (30, 10), (38, 0), (38, 10), (38, 20), (38, 38)]):
+        vals = decimal_values(rng, w, s, 400)
+        for as_float, sql_type, view in ((False, "DOUBLE", np.uint64), (True, "FLOAT", np.uint32)):
+            R.register(f"t_d2r_{k}_{int(as_float)}", pa.table({"i": pa.array(range(len(vals)), pa.int64()),
+                                                              "c": arrow_array_of(f"DECIMAL({w},{s})", vals)}))
+            col = _export_column(f"SELECT i, CAST(c AS {sql_type}) AS r FROM t_d2r_{k}_{int(as_float)}")
+            got = col.to_numpy(zero_copy_only=False).view(view)
+            want = [dec.to_real(v, physical_bytes(w), s, as_float) for v in vals]
+            bad = [(v, hex(int(g)), hex(x)) for v, g, x in zip(vals, got, want) if int(g) != x]
+            assert not bad, f"DECIMAL({w},{s}) -> {sql_type}: {len(bad)} of {len(vals)} differ, first {bad[:6]}"
+            n += len(vals)
+    assert n > 10000
+
+
+INT_ARROW = {"TINYINT": "int8", "SMALLINT": "int16", "INTEGER": "int32", "BIGINT": "int64", "UTINYINT": "uint8",
+             "USMALLINT": "uint16", "UINTEGER": "uint32", "UBIGINT": "uint64"}
+
+
+def test_decimal_cast_golden_fixture(dec):
+    """tests/golden/cast_decimal.json (the reference's results, tools/gen_cast_decimal_golden.py) against the CPU build of the
+    device header: runs where oracle/_ref is absent, and is what the GPU test of the kernel compares with"""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "cast_decimal.json")) as f:
+        doc = json.load(f)
+    assert len(doc["cases"]) >= 70
+    for case in doc["cases"]:
+        src, dst = case["from"], case["to"]
+        sw, ss = (int(x) for x in src[8:-1].split(",")) if src.startswith("DECIMAL") else (0, 0)
+        for raw, want in zip(case["raw"], case["result"]):
+            v = int(raw)
+            if dst in ("DOUBLE", "FLOAT"):
+                got = dec.to_real(v, physical_bytes(sw), ss, dst == "FLOAT")
+                assert got == int(want), (src, dst, raw)
+            else:
+                dw, ds = (int(x) for x in dst[8:-1].split(","))
+                got = dec.to_decimal(1 if src.startswith("DECIMAL") else 0, v, sw, ss, dw, ds)
+                assert (None if got is None else _signed128(got)) == (None if want is None else int(want)), (src, dst, raw)

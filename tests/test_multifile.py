@@ -374,6 +374,106 @@ def test_temporal_decimal_boolean_to_varchar_equal_the_reference(b2a, cuda_devic
         rows_of(b2a.read_arrow([str(tmp_path / "a.arrows"), str(tmp_path / "low.arrows")]))
 
 
+def test_union_by_name_numeric_and_decimal_types_match_the_reference(b2a, tmp_path):
+    """LogicalType::ForceMaxLogicalType for the DECIMAL pairs (types.cpp: CombineEqualTypes, DecimalSizeCheck), bind only:
+    the global type of a two-file union_by_name scan against typeof() of a UNION ALL of the same two types in the compiled
+    reference (both go through MaxLogicalType's numeric rules)"""
+    from oracle import ref_py as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built (needs /root/reference)")
+    from test_cast_parse import INT_ARROW, arrow_array_of
+    types = ["DECIMAL(15,2)", "DECIMAL(18,4)", "DECIMAL(4,0)", "DECIMAL(38,10)", "DECIMAL(38,0)", "DECIMAL(30,25)", "DECIMAL(9,9)",
+             "TINYINT", "SMALLINT", "INTEGER", "BIGINT", "UTINYINT", "USMALLINT", "UINTEGER", "UBIGINT", "DOUBLE", "FLOAT"]
+
+    def array_of(t):
+        if t in INT_ARROW:
+            return pa.array([1], getattr(pa, INT_ARROW[t])())
+        if t in ("DOUBLE", "FLOAT"):
+            return pa.array([1.0], pa.float64() if t == "DOUBLE" else pa.float32())
+        return arrow_array_of(t, [1])
+
+    for k, t in enumerate(types):
+        _write(str(tmp_path / f"t{k}.arrows"), pa.table({"v": array_of(t)}))
+    n = 0
+    for i, a in enumerate(types):
+        for j, b in enumerate(types):
+            if i == j or not (a.startswith("DECIMAL") or b.startswith("DECIMAL")):
+                continue
+            want = R.query(f"SELECT typeof(x) FROM (SELECT CAST(NULL AS {a}) x UNION ALL SELECT CAST(NULL AS {b})) LIMIT 1")[0][0]
+            try:
+                got = b2a.read_arrow([str(tmp_path / f"t{i}.arrows"), str(tmp_path / f"t{j}.arrows")], union_by_name=True).types[0]
+            except b2a.B2AError as e:  # the type is decided before the cast is looked up: the message names it
+                assert "not implemented on the device" in str(e) and f"to {want} " in str(e), (a, b, want, str(e))
+                continue
+            assert got == want, (a, b, got, want)
+            n += 1
+    assert n > 100
+
+
+@pytest.mark.gpu
+def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp_path):
+    """the first file fixes the column's type, the second holds another one: integer -> DECIMAL, DECIMAL -> DECIMAL (scale up /
+    down with rounding), DECIMAL -> DOUBLE / FLOAT on the device (kernels/cast_decimal.cuh) against the REFERENCE's results
+    (tests/golden/cast_decimal.json, tools/gen_cast_decimal_golden.py): unscaled integers and floating-point bits, exact; a
+    value the reference refuses to cast fails the scan with a conversion error"""
+    import json
+    from test_cast_parse import INT_ARROW, arrow_array_of
+    with open(os.path.join(os.path.dirname(__file__), "golden", "cast_decimal.json")) as fh:
+        doc = json.load(fh)
+
+    def array_of(type_name, raw):
+        if type_name in INT_ARROW:
+            return pa.array(raw, getattr(pa, INT_ARROW[type_name])())
+        if type_name == "DOUBLE":
+            return pa.array([float(v) for v in raw], pa.float64())
+        if type_name == "FLOAT":
+            return pa.array([float(v) for v in raw], pa.float32())
+        return arrow_array_of(type_name, raw)
+
+    def result_of(mfs, dst):
+        out = []
+        for f in mfs.files:
+            f.scan()
+            for b in range(f.reader.num_batches):
+                v = f.column(b, 0)
+                d = np.ascontiguousarray(v.data)
+                if dst == "DOUBLE":
+                    vals = d.view(np.uint64).ravel().tolist()
+                elif dst == "FLOAT":
+                    vals = d.view(np.uint32).ravel().tolist()
+                elif d.shape[1] == 16:
+                    w = d.view(np.uint64).reshape(-1, 2)
+                    vals = [(int(hi) << 64 | int(lo)) - ((1 << 128) if int(hi) >> 63 else 0) for lo, hi in w]
+                else:
+                    vals = d.view({2: np.int16, 4: np.int32, 8: np.int64}[d.shape[1]]).ravel().tolist()
+                out += [int(x) if ok else None for x, ok in zip(vals, v.valid)]
+        return out
+
+    n = 0
+    for k, case in enumerate(doc["cases"]):
+        src, dst = case["from"], case["to"]
+        first = str(tmp_path / f"first_{dst}.arrows")
+        if not os.path.exists(first):
+            _write(first, pa.table({"v": array_of(dst, [1])}))
+        good = [(int(r), int(w)) for r, w in zip(case["raw"], case["result"]) if w is not None]
+        bad = [int(r) for r, w in zip(case["raw"], case["result"]) if w is None]
+        arr = array_of(src, [r for r, _ in good])
+        _write(str(tmp_path / f"c{k}.arrows"), pa.table({"v": pa.concat_arrays([arr, pa.nulls(1, arr.type)])}), batch=100)
+        mfs = b2a.read_arrow([first, str(tmp_path / f"c{k}.arrows")])
+        assert mfs.types == [dst]
+        got = result_of(mfs, dst)[1:]
+        assert got[-1] is None and len(got) == len(good) + 1, (src, dst)
+        wrong = [(r, w, g) for (r, w), g in zip(good, got) if w != g]
+        assert not wrong, f"{src} -> {dst}: {len(wrong)} of {len(good)} differ, first {wrong[:6]}"
+        n += len(good)
+        if bad:
+            _write(str(tmp_path / f"b{k}.arrows"), pa.table({"v": array_of(src, [good[0][0] if good else 0, bad[0]])}))
+            with pytest.raises(b2a.B2AError, match="out of range"):
+                rows = result_of(b2a.read_arrow([first, str(tmp_path / f"b{k}.arrows")]), dst)
+                raise AssertionError(f"{src} -> {dst}: {bad[0]} was cast to {rows[-1]}")
+    assert n > 7000
+
+
 @pytest.mark.gpu
 def test_lineitem_glob_dictionary_union_by_name(b2a, cuda_device, tmp_path):
     """BASELINE config 4 in small: glob of lineitem files, dictionary-encoded strings, two schema variants under
