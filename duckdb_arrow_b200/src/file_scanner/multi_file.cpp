@@ -357,7 +357,10 @@ bool CastSupported(const MfType &from, const MfType &to) {
 	if (IsInt(a) && (b == B2A_T_DECIMAL || b == B2A_T_HUGEINT)) {
 		return true; // kernels/cast_decimal.cuh; widening to 128 bits
 	}
-	if (a == B2A_T_DECIMAL && (b == B2A_T_DECIMAL || b == B2A_T_DOUBLE || b == B2A_T_FLOAT)) {
+	if (a == B2A_T_DECIMAL && (b == B2A_T_DECIMAL || b == B2A_T_DOUBLE || b == B2A_T_FLOAT || IsInt(b))) {
+		return true;
+	}
+	if (fa && b == B2A_T_DECIMAL) {
 		return true;
 	}
 	if (b == B2A_T_VARCHAR && (a == B2A_T_BOOLEAN || a == B2A_T_DATE || a == B2A_T_TIME || a == B2A_T_TIMESTAMP ||

@@ -16,7 +16,7 @@
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
 //   BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR   StringCast::Operation, restated in cast_format.cuh
-//   integer -> DECIMAL / HUGEINT, DECIMAL -> DECIMAL / DOUBLE / FLOAT   restated in cast_decimal.cuh
+//   integer / FLOAT / DOUBLE -> DECIMAL, integer -> HUGEINT, DECIMAL -> DECIMAL / integer / DOUBLE / FLOAT   cast_decimal.cuh
 #include "cast.cuh"
 #include "cast_parse.cuh"
 #include "cast_parse_double.cuh"
@@ -619,6 +619,13 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 						continue;
 					}
 					*reinterpret_cast<float *>(dst) = f;
+				} else if (to == B2A_T_DECIMAL) {
+					__int128 r;
+					if (!castx::real_to_decimal(v, from == B2A_T_FLOAT, t.dst_decimal_width, t.dst_decimal_scale, &r)) {
+						raise(l.d_err, B2A_CAST_DEV_RANGE);
+						continue;
+					}
+					store_i128(dst, dw, r);
 				} else if (to == B2A_T_VARCHAR) {
 					char buf[32];
 					const uint32_t k = format_double(v, from == B2A_T_FLOAT, buf);
@@ -671,6 +678,16 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 					*reinterpret_cast<double *>(dst) = castx::decimal_to_double(v, sw, t.decimal_scale);
 				} else if (to == B2A_T_FLOAT) {
 					*reinterpret_cast<float *>(dst) = castx::decimal_to_float(v, sw, t.decimal_scale);
+				} else if (is_signed_int(to) || is_unsigned_int(to)) {
+					const __int128 one = 1;
+					const bool sg = is_signed_int(to);
+					__int128 r;
+					if (!castx::decimal_to_int(v, t.decimal_scale, sg ? -(one << (8 * dw - 1)) : 0,
+					                           sg ? (one << (8 * dw - 1)) - 1 : (one << (8 * dw)) - 1, &r)) {
+						raise(l.d_err, B2A_CAST_DEV_RANGE);
+						continue;
+					}
+					store_int(dst, dw, static_cast<uint64_t>(r));
 				} else {
 					__int128 r;
 					if (!castx::decimal_to_decimal(v, t.decimal_width, t.decimal_scale, t.dst_decimal_width,

@@ -6,6 +6,11 @@
 //                                  up = x 10^d with a limit check only when the source may not fit; down = round half away
 //                                  from zero as (v / (10^d / 2) +- 1) / 2, with the reference's range test (whose rounding
 //                                  looks at the WHOLE fraction — 10^source_scale — not at the digits dropped)
+//   DECIMAL -> integer             TryCastDecimalToNumeric / TryCastHugeDecimalToNumeric (cast_operators.cpp:2399-2427): round
+//                                  half away from zero, then the integer range check
+//   FLOAT / DOUBLE -> DECIMAL      DoubleToDecimalCast (cast_operators.cpp:2333-2346): round(v x 10^s) in double, |.| < 10^w,
+//                                  then back through the SOURCE type — a FLOAT's product is rounded to float again before
+//                                  it becomes an integer, so DECIMAL(9,.) can receive 1000000000 — restated as it is
 //   DECIMAL -> DOUBLE / FLOAT      TryCastDecimalToFloatingPoint (cast_operators.cpp:2672-2755): one division when the
 //                                  integer is exact in the target (or scale 0), else integer part + fraction / 10^s;
 //                                  128-bit integers become floating point as low + high x 2^64 (hugeint.cpp:649-661), not
@@ -13,6 +18,7 @@
 // `__host__ __device__`: pinned on the CPU against the compiled reference (tests/test_cast_parse.py).
 #pragma once
 #include <stdint.h>
+#include <string.h>
 
 #if defined(__CUDACC__)
 #define CASTX_HD __host__ __device__
@@ -131,6 +137,68 @@ CASTX_HD inline float decimal_to_float(i128 input, int src_bytes, uint32_t scale
 	}
 	const i128 p = pow10(scale);
 	return to_float(input / p, src_bytes) + to_float(input % p, src_bytes) / static_cast<float>(pow10_double(scale));
+}
+
+// false = "Failed to cast decimal value ... to type ..."; lo / hi = the range of the destination integer type
+CASTX_HD inline bool decimal_to_int(i128 input, uint32_t scale, i128 lo, i128 hi, i128 *out) {
+	const i128 power = pow10(scale);
+	const i128 rounding = (input < 0 ? -power : power) / 2;
+	const i128 scaled = (input + rounding) / power;
+	if (scaled < lo || scaled > hi) {
+		return false;
+	}
+	*out = scaled;
+	return true;
+}
+
+// an integer-valued finite double, |v| < 2^127, as a 128-bit integer (what ConvertFloatingToBigint's fmod / division by 2^64
+// and a static_cast to int64 both give)
+CASTX_HD inline i128 integral_double_to_i128(double v) {
+	uint64_t bits;
+	memcpy(&bits, &v, sizeof(bits));
+	const int exponent = static_cast<int>((bits >> 52) & 0x7FF);
+	if (exponent < 1023) {
+		return 0; // |v| < 1
+	}
+	const i128 mantissa = static_cast<i128>((bits & ((uint64_t(1) << 52) - 1)) | (uint64_t(1) << 52));
+	const int shift = exponent - 1075;
+	const i128 magnitude = shift >= 0 ? mantissa << shift : mantissa >> -shift;
+	return (bits >> 63) ? -magnitude : magnitude;
+}
+
+CASTX_HD inline bool finite(double v) {
+	uint64_t bits;
+	memcpy(&bits, &v, sizeof(bits));
+	return ((bits >> 52) & 0x7FF) != 0x7FF;
+}
+
+// round half away from zero of a double (std::round), without <cmath> differences between host and device
+CASTX_HD inline double round_half_away(double v) {
+#if defined(__CUDA_ARCH__)
+	return ::round(v);
+#else
+	return __builtin_round(v);
+#endif
+}
+CASTX_HD inline double nearby_even(double v) {
+#if defined(__CUDA_ARCH__)
+	return ::rint(v);
+#else
+	return __builtin_rint(v);
+#endif
+}
+
+// false = "Could not cast value ... to DECIMAL(w,s)".  `from_float`: the source is a FLOAT (passed widened to double)
+CASTX_HD inline bool real_to_decimal(double input, bool from_float, uint32_t width, uint32_t scale, i128 *out) {
+	const double value = input * pow10_double(scale);
+	const double rounded = round_half_away(value);
+	if (rounded <= -pow10_double(width) || rounded >= pow10_double(width) || !finite(rounded)) {
+		return false;
+	}
+	// Cast::Operation<SRC, DST>(static_cast<SRC>(rounded)): nearbyint of the value in the SOURCE type
+	const double back = from_float ? static_cast<double>(static_cast<float>(rounded)) : rounded;
+	*out = integral_double_to_i128(nearby_even(back));
+	return true;
 }
 
 } // namespace castx

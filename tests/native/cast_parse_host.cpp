@@ -43,12 +43,33 @@ extern "C" unsigned b2a_test_format(int kind, unsigned long long low, long long 
 static __int128 wide(unsigned long long low, long long high) {
 	return (static_cast<__int128>(high) << 64) | static_cast<__int128>(low);
 }
-// op 0: integer -> DECIMAL(dw,ds); 1: DECIMAL(sw,ss) -> DECIMAL(dw,ds).  Returns 1 when the cast succeeds.
+// op 0: integer -> DECIMAL(dw,ds); 1: DECIMAL(sw,ss) -> DECIMAL(dw,ds); 2: DECIMAL -> integer; 3 / 4: DOUBLE / FLOAT ->
+// DECIMAL.  Returns 1 when the cast succeeds.
 extern "C" int b2a_test_to_decimal(int op, unsigned long long low, long long high, unsigned sw, unsigned ss, unsigned dw,
                                    unsigned ds, unsigned long long *out_low, long long *out_high) {
 	__int128 r = 0;
-	const bool ok = op == 0 ? b2a::castx::int_to_decimal(wide(low, high), dw, ds, &r)
-	                        : b2a::castx::decimal_to_decimal(wide(low, high), sw, ss, dw, ds, &r);
+	bool ok;
+	if (op == 0) {
+		ok = b2a::castx::int_to_decimal(wide(low, high), dw, ds, &r);
+	} else if (op == 1) {
+		ok = b2a::castx::decimal_to_decimal(wide(low, high), sw, ss, dw, ds, &r);
+	} else if (op == 2) { // DECIMAL(., ss) -> a signed (ds = 1) or unsigned (ds = 0) integer of dw bytes
+		const __int128 one = 1;
+		const __int128 lo = ds ? -(one << (8 * dw - 1)) : 0;
+		const __int128 hi = ds ? (one << (8 * dw - 1)) - 1 : (dw == 16 ? ~static_cast<__int128>(0) : (one << (8 * dw)) - 1);
+		ok = b2a::castx::decimal_to_int(wide(low, high), ss, lo, hi, &r);
+	} else { // op 3 / 4: the bits of a DOUBLE / FLOAT (in `low`) -> DECIMAL(dw,ds)
+		double v;
+		if (op == 3) {
+			memcpy(&v, &low, sizeof(v));
+		} else {
+			float f;
+			const uint32_t b = static_cast<uint32_t>(low);
+			memcpy(&f, &b, sizeof(f));
+			v = f;
+		}
+		ok = b2a::castx::real_to_decimal(v, op == 4, dw, ds, &r);
+	}
 	*out_low = static_cast<unsigned long long>(r);
 	*out_high = static_cast<long long>(r >> 64);
 	return ok ? 1 : 0;

@@ -503,7 +503,7 @@ def test_decimal_cast_golden_fixture(dec):
     import json
     with open(os.path.join(ROOT, "tests", "golden", "cast_decimal.json")) as f:
         doc = json.load(f)
-    assert len(doc["cases"]) >= 70
+    assert len(doc["cases"]) >= 130
     for case in doc["cases"]:
         src, dst = case["from"], case["to"]
         sw, ss = (int(x) for x in src[8:-1].split(",")) if src.startswith("DECIMAL") else (0, 0)
@@ -512,7 +512,65 @@ def test_decimal_cast_golden_fixture(dec):
             if dst in ("DOUBLE", "FLOAT"):
                 got = dec.to_real(v, physical_bytes(sw), ss, dst == "FLOAT")
                 assert got == int(want), (src, dst, raw)
+            elif dst in INT_RANGE:
+                nbytes, signed = INT_RANGE[dst]
+                got = dec.to_decimal(2, v, 0, ss, nbytes, 1 if signed else 0)
+                assert (None if got is None else _signed128(got)) == (None if want is None else int(want)), (src, dst, raw)
+            elif src in ("DOUBLE", "FLOAT"):  # raw = the bits of the source value
+                dw, ds = (int(x) for x in dst[8:-1].split(","))
+                got = dec.to_decimal(4 if src == "FLOAT" else 3, v, 0, 0, dw, ds)
+                assert (None if got is None else _signed128(got)) == (None if want is None else int(want)), (src, dst, raw)
             else:
                 dw, ds = (int(x) for x in dst[8:-1].split(","))
                 got = dec.to_decimal(1 if src.startswith("DECIMAL") else 0, v, sw, ss, dw, ds)
                 assert (None if got is None else _signed128(got)) == (None if want is None else int(want)), (src, dst, raw)
+
+
+INT_RANGE = {"TINYINT": (1, True), "SMALLINT": (2, True), "INTEGER": (4, True), "BIGINT": (8, True), "UTINYINT": (1, False),
+             "USMALLINT": (2, False), "UINTEGER": (4, False), "UBIGINT": (8, False)}
+
+
+def real_values(rng, width, scale, n, as_float):
+    """doubles (or floats) around everything DoubleToDecimalCast decides: ties of the rounding, the 10^width limit, the
+    precision of the source type"""
+    lim = 10.0 ** (width - scale)
+    vals = [0.0, -0.0, 0.5, -0.5, 1.5, 2.5, -2.5, 0.05, 0.15, 0.25, 0.35, 1e-10, lim, -lim, lim - 1, lim - 0.5, lim - 0.4, lim * 0.999999,
+            np.nextafter(lim, 0), -np.nextafter(lim, 0), lim / 10, 123456789.123456789, 999999999.0, 999999936.0, 99999999999999999.0,
+            float("inf"), float("-inf"), float("nan"), 1e300, -1e300, 1e38, 9.9e37]
+    vals += [float(x) for x in rng.uniform(-lim * 1.05, lim * 1.05, n)]
+    vals += [float(x) for x in rng.uniform(-1000, 1000, n)]
+    vals += [float(int(x)) / 10 ** scale + 0.5 / 10 ** scale for x in rng.integers(-10 ** min(width, 15), 10 ** min(width, 15), n)]
+    vals += [float(int(x)) for x in rng.integers(-10 ** min(width - scale, 18), 10 ** min(width - scale, 18), n)]
+    with np.errstate(over="ignore"):
+        return np.array(vals, dtype=np.float32 if as_float else np.float64)
+
+
+@needs_ref
+def test_decimal_to_integer_and_real_to_decimal_equal_the_reference(dec):
+    import pyarrow as pa
+    rng = np.random.default_rng(23)
+    n, k = 0, 0
+    for (w, s) in [(4, 0), (4, 2), (9, 0), (9, 3), (9, 9), (15, 2), (18, 0), (18, 4), (18, 18), (20, 5), (38, 0), (38, 10), (38, 30)]:
+        vals = decimal_values(rng, w, s, 200)
+        for name, (nbytes, signed) in INT_RANGE.items():
+            k += 1
+            R.register(f"t_d2i_{k}", pa.table({"i": pa.array(range(len(vals)), pa.int64()), "c": arrow_array_of(f"DECIMAL({w},{s})", vals)}))
+            got = _export_column(f"SELECT i, TRY_CAST(c AS {name}) AS r FROM t_d2i_{k}").to_pylist()
+            want = [dec.to_decimal(2, v, 0, s, nbytes, 1 if signed else 0) for v in vals]
+            want = [None if x is None else _signed128(x) for x in want]
+            bad = [(v, g, x) for v, g, x in zip(vals, got, want) if g != x]
+            assert not bad, f"DECIMAL({w},{s}) -> {name}: {len(bad)} differ, first {bad[:6]}"
+            n += len(vals)
+    for (w, s) in [(4, 0), (4, 2), (4, 4), (9, 0), (9, 2), (9, 9), (15, 2), (18, 0), (18, 6), (18, 18), (19, 0), (25, 5), (38, 0), (38, 10), (38, 37)]:
+        for as_float in (False, True):
+            k += 1
+            arr = real_values(rng, w, s, 150, as_float)
+            R.register(f"t_r2d_{k}", pa.table({"i": pa.array(range(len(arr)), pa.int64()), "c": pa.array(arr)}))
+            got = _unscaled(_export_column(f"SELECT i, TRY_CAST(c AS DECIMAL({w},{s})) AS r FROM t_r2d_{k}"))
+            bits = arr.view(np.uint32 if as_float else np.uint64)
+            want = [dec.to_decimal(4 if as_float else 3, int(b), 0, 0, w, s) for b in bits]
+            want = [None if x is None else _signed128(x) for x in want]
+            bad = [(float(v), g, x) for v, g, x in zip(arr, got, want) if g != x]
+            assert not bad, f"{'FLOAT' if as_float else 'DOUBLE'} -> DECIMAL({w},{s}): {len(bad)} of {len(arr)} differ, first {bad[:6]}"
+            n += len(arr)
+    assert n > 30000

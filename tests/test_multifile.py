@@ -412,8 +412,8 @@ def test_union_by_name_numeric_and_decimal_types_match_the_reference(b2a, tmp_pa
 
 @pytest.mark.gpu
 def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp_path):
-    """the first file fixes the column's type, the second holds another one: integer -> DECIMAL, DECIMAL -> DECIMAL (scale up /
-    down with rounding), DECIMAL -> DOUBLE / FLOAT on the device (kernels/cast_decimal.cuh) against the REFERENCE's results
+    """the first file fixes the column's type, the second holds another one: integer / FLOAT / DOUBLE -> DECIMAL, DECIMAL ->
+    DECIMAL (scale up / down with rounding), DECIMAL -> integer / DOUBLE / FLOAT on the device (kernels/cast_decimal.cuh) against the REFERENCE's results
     (tests/golden/cast_decimal.json, tools/gen_cast_decimal_golden.py): unscaled integers and floating-point bits, exact; a
     value the reference refuses to cast fails the scan with a conversion error"""
     import json
@@ -421,13 +421,14 @@ def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp
     with open(os.path.join(os.path.dirname(__file__), "golden", "cast_decimal.json")) as fh:
         doc = json.load(fh)
 
-    def array_of(type_name, raw):
+    def array_of(type_name, raw, bits=False):
         if type_name in INT_ARROW:
             return pa.array(raw, getattr(pa, INT_ARROW[type_name])())
-        if type_name == "DOUBLE":
-            return pa.array([float(v) for v in raw], pa.float64())
-        if type_name == "FLOAT":
-            return pa.array([float(v) for v in raw], pa.float32())
+        if type_name in ("DOUBLE", "FLOAT"):
+            wide = type_name == "DOUBLE"
+            if bits:  # the fixture holds the bit patterns of floating-point SOURCE values
+                return pa.array(np.array(raw, dtype=np.uint64 if wide else np.uint32).view(np.float64 if wide else np.float32))
+            return pa.array([float(v) for v in raw], pa.float64() if wide else pa.float32())
         return arrow_array_of(type_name, raw)
 
     def result_of(mfs, dst):
@@ -441,6 +442,8 @@ def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp
                     vals = d.view(np.uint64).ravel().tolist()
                 elif dst == "FLOAT":
                     vals = d.view(np.uint32).ravel().tolist()
+                elif dst in INT_ARROW:
+                    vals = d.view(getattr(np, INT_ARROW[dst])).ravel().tolist()
                 elif d.shape[1] == 16:
                     w = d.view(np.uint64).reshape(-1, 2)
                     vals = [(int(hi) << 64 | int(lo)) - ((1 << 128) if int(hi) >> 63 else 0) for lo, hi in w]
@@ -457,7 +460,7 @@ def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp
             _write(first, pa.table({"v": array_of(dst, [1])}))
         good = [(int(r), int(w)) for r, w in zip(case["raw"], case["result"]) if w is not None]
         bad = [int(r) for r, w in zip(case["raw"], case["result"]) if w is None]
-        arr = array_of(src, [r for r, _ in good])
+        arr = array_of(src, [r for r, _ in good], bits=True)
         _write(str(tmp_path / f"c{k}.arrows"), pa.table({"v": pa.concat_arrays([arr, pa.nulls(1, arr.type)])}), batch=100)
         mfs = b2a.read_arrow([first, str(tmp_path / f"c{k}.arrows")])
         assert mfs.types == [dst]
@@ -467,11 +470,11 @@ def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp
         assert not wrong, f"{src} -> {dst}: {len(wrong)} of {len(good)} differ, first {wrong[:6]}"
         n += len(good)
         if bad:
-            _write(str(tmp_path / f"b{k}.arrows"), pa.table({"v": array_of(src, [good[0][0] if good else 0, bad[0]])}))
+            _write(str(tmp_path / f"b{k}.arrows"), pa.table({"v": array_of(src, [good[0][0] if good else 0, bad[0]], bits=True)}))
             with pytest.raises(b2a.B2AError, match="out of range"):
                 rows = result_of(b2a.read_arrow([first, str(tmp_path / f"b{k}.arrows")]), dst)
                 raise AssertionError(f"{src} -> {dst}: {bad[0]} was cast to {rows[-1]}")
-    assert n > 7000
+    assert n > 13000
 
 
 @pytest.mark.gpu

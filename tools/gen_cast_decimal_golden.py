@@ -1,6 +1,7 @@
 """tests/golden/cast_decimal.json: the REFERENCE'S results (the DuckDB compiled from /root/reference/duckdb into oracle/_ref) for
 the casts into and out of DECIMAL that the multi-file mapper runs on the device — integer -> DECIMAL / HUGEINT, DECIMAL ->
-DECIMAL (scale up, scale down with rounding, both with their range checks), DECIMAL -> DOUBLE / FLOAT (bit patterns) — for the
+DECIMAL (scale up, scale down with rounding, both with their range checks), DECIMAL -> integer, FLOAT / DOUBLE -> DECIMAL
+(raw = the bit patterns of the source values), DECIMAL -> DOUBLE / FLOAT (results = bit patterns) — for the
 GPU test in tests/test_multifile.py; /root/reference does not exist on the GPU box, the fixture travels.  Rows on which the
 reference's cast fails carry null.   Run in the build container:  python tools/gen_cast_decimal_golden.py"""
 import json
@@ -15,7 +16,7 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from oracle import ref_py as R  # noqa: E402
-from test_cast_parse import _export_column, _unscaled, arrow_array_of, decimal_values  # noqa: E402
+from test_cast_parse import INT_RANGE, _export_column, _unscaled, arrow_array_of, decimal_values, real_values  # noqa: E402
 
 INTS = {"TINYINT": pa.int8(), "SMALLINT": pa.int16(), "INTEGER": pa.int32(), "BIGINT": pa.int64(), "UTINYINT": pa.uint8(),
         "USMALLINT": pa.uint16(), "UINTEGER": pa.uint32(), "UBIGINT": pa.uint64()}
@@ -34,8 +35,8 @@ def main():
         if dst in ("DOUBLE", "FLOAT"):
             bits = col.to_numpy(zero_copy_only=False).view(np.uint64 if dst == "DOUBLE" else np.uint32)
             result = [str(int(b)) for b in bits]
-        elif dst == "HUGEINT":
-            raise AssertionError("HUGEINT has no Arrow type: cast to DECIMAL(38,0) in SQL instead")
+        elif dst in INT_RANGE:
+            result = [None if v is None else str(v) for v in col.to_pylist()]
         else:
             result = [None if v is None else str(v) for v in _unscaled(col)]
         cases.append({"from": src, "to": dst, "raw": [str(v) for v in raw], "result": result})
@@ -58,6 +59,16 @@ def main():
         vals = decimal_values(rng, w, s, 80)
         for dst in ("DOUBLE", "FLOAT"):
             run(f"DECIMAL({w},{s})", dst, vals, arrow_array_of(f"DECIMAL({w},{s})", vals))
+    for w, s in [(4, 2), (9, 0), (15, 2), (18, 4), (20, 5), (38, 10)]:
+        vals = decimal_values(rng, w, s, 50)
+        for dst in INT_RANGE:
+            run(f"DECIMAL({w},{s})", dst, vals, arrow_array_of(f"DECIMAL({w},{s})", vals))
+    for w, s in [(4, 2), (9, 2), (9, 9), (15, 2), (18, 6), (25, 5), (38, 10)]:
+        for as_float in (False, True):
+            arr = real_values(rng, w, s, 40, as_float)
+            bits = arr.view(np.uint32 if as_float else np.uint64)
+            # (the raw column holds the BIT PATTERNS of the source values)
+            run("FLOAT" if as_float else "DOUBLE", f"DECIMAL({w},{s})", [int(b) for b in bits], pa.array(arr))
     doc = {"source": "TRY_CAST(c AS <to>) of oracle/_ref (reference DuckDB), tools/gen_cast_decimal_golden.py", "cases": cases}
     path = os.path.join(ROOT, "tests", "golden", "cast_decimal.json")
     with open(path, "w") as f:
