@@ -263,3 +263,21 @@ def test_q6_known_answers_through_the_reference():
     assert R.query(q6.format("li_arrow")) == [["1193053.2253"]]
     for t in ("lineitem", "orders", "partsupp", "part", "customer", "supplier", "nation", "region"):
         R.query(f"drop table {t}")
+
+
+@pytest.mark.parametrize("n", [1, 64, 1500, 2048, 2049, 5000, 9000])
+def test_oracle_equals_reference_on_sparse_unions(n):
+    """the reference's tests hold no union fixture that passes, the compiled reference itself does the job —
+    arrow_conversion.cpp:1173-1221 incl. its type_ids[row] read without the chunk offset (rows past 2 048 of a batch take the
+    batch's first tags), which the restatement reproduces and the GPU path is compared with (tests/test_union.py)"""
+    from test_union import _table, _union_array
+    assert check(_union_array(n, seed=n), f"union[{n}]") == "ok"
+    t = _table(n, seed=n + 1)
+    assert check(t.column("st").combine_chunks(), f"struct<union>[{n}]") == "ok"
+
+
+def test_reference_rejects_a_union_tag_out_of_range_like_the_oracle():
+    a = pa.array([1, 2, 3], pa.int64())
+    u = pa.UnionArray.from_sparse(pa.array([0, 1, 0], pa.int8()), [a, a], ["a", "b"])
+    bad = pa.UnionArray.from_buffers(u.type, 3, [None, pa.py_buffer(np.array([0, 5, 0], np.int8))], children=[a, a])
+    assert check(bad, "bad tag") == "error"

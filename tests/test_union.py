@@ -1,9 +1,11 @@
 """Sparse unions (second half: arrow_conversion.cpp:1173-1221; type mapping arrow_duck_schema.cpp:235-259).
 The reference's tests hold no union fixture that passes (test/sql/arrow_testing.test:72-74 skips generated_union because of
-its dense column), so the oracle's restatement is pinned against pyarrow's own reading of the same arrays for batches of at
-most 2 048 rows, where the reference's chunk-offset quirk (type_ids indexed without the chunk offset, :1209) cannot show;
-the quirk itself is pinned by construction in test_oracle_union_reads_type_ids_without_chunk_offset.  The GPU path is then
-compared with the oracle bit for bit, quirk included."""
+its dense column).  The oracle's restatement is pinned twice: against the COMPILED REFERENCE's arrow scan over the same arrays,
+chunk-offset quirk included (tests/test_ref_scan.py::test_oracle_equals_reference_on_sparse_unions — type_ids indexed without
+the chunk offset, :1209), and here against pyarrow's own reading for batches of at most 2 048 rows, where the quirk cannot show
+(this file also runs where oracle/_ref is absent); the quirk is pinned by construction in
+test_oracle_union_reads_type_ids_without_chunk_offset.  The GPU path is then compared with the oracle bit for bit, quirk
+included."""
 import numpy as np
 import pyarrow as pa
 import pyarrow.ipc as ipc
