@@ -649,7 +649,7 @@ class MultiFileFile:
             width = 2 if gc.decimal[0] <= 4 else 4 if gc.decimal[0] <= 9 else 8 if gc.decimal[0] <= 18 else 16
         else:
             width = {"VARCHAR": 16, "DOUBLE": 8, "FLOAT": 4, "BIGINT": 8, "UBIGINT": 8, "INTEGER": 4, "UINTEGER": 4,
-                     "SMALLINT": 2, "USMALLINT": 2, "TINYINT": 1, "UTINYINT": 1, "TIMESTAMP": 8, "HUGEINT": 16}[gc.type_id]
+                     "SMALLINT": 2, "USMALLINT": 2, "TINYINT": 1, "UTINYINT": 1, "TIMESTAMP": 8, "HUGEINT": 16, "DATE": 4}[gc.type_id]
         f = Field(src.index, gc.name, "", gc.type_id, "CAST", width, src.out_width, [], -1, True, 0, 0, 0, -1, "INVALID")
         return CastColumnView(self.ds, co, f, batch, self.final, self._h_final.data_ptr())
 

@@ -15,6 +15,7 @@
 //   VARCHAR -> BIGINT       TryCast::Operation<string_t,int64_t>: optional sign, digits, optional fraction that rounds
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
+//   VARCHAR -> DATE / TIMESTAMP   Date::TryConvertDate / Timestamp::TryConvertTimestamp, restated in cast_parse_temporal.cuh
 //   BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR   StringCast::Operation, restated in cast_format.cuh
 //   integer / FLOAT / DOUBLE -> DECIMAL, integer -> HUGEINT, DECIMAL -> DECIMAL / integer / DOUBLE / FLOAT   cast_decimal.cuh
 #include "cast.cuh"
@@ -22,6 +23,7 @@
 #include "cast_parse_double.cuh"
 #include "cast_format.cuh"
 #include "cast_decimal.cuh"
+#include "cast_parse_temporal.cuh"
 
 #include "b2arrow.h"
 
@@ -493,6 +495,7 @@ __device__ __noinline__ uint32_t parse_int64(const char *s, uint32_t n, int64_t 
 	return castp::varchar_to_bigint(s, n, out);
 }
 static_assert(castp::OUT_OF_RANGE == B2A_CAST_DEV_RANGE && castp::NOT_A_NUMBER == B2A_CAST_DEV_PARSE, "cast error codes");
+static_assert(castt::OUT_OF_RANGE == B2A_CAST_DEV_RANGE && castt::BAD_FORMAT == B2A_CAST_DEV_PARSE, "cast error codes");
 
 // casts that cannot fail and do not need the validity mask (a NULL row's data slot is unspecified in DuckDB):
 // integer widening, integer -> FLOAT/DOUBLE, FLOAT -> DOUBLE.  8 rows in flight per thread.
@@ -663,6 +666,22 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 						continue;
 					}
 					*reinterpret_cast<double *>(dst) = d;
+				} else if (to == B2A_T_DATE) {
+					int32_t d = 0;
+					const uint32_t e = castt::varchar_to_date(s, len, &d);
+					if (e) {
+						raise(l.d_err, e);
+						continue;
+					}
+					*reinterpret_cast<int32_t *>(dst) = d;
+				} else if (to == B2A_T_TIMESTAMP) {
+					int64_t v = 0;
+					const uint32_t e = castt::varchar_to_timestamp(s, len, &v);
+					if (e) {
+						raise(l.d_err, e);
+						continue;
+					}
+					*reinterpret_cast<int64_t *>(dst) = v;
 				} else {
 					int64_t v = 0;
 					const uint32_t e = parse_int64(s, len, &v);

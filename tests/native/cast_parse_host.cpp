@@ -5,6 +5,7 @@
 #include "kernels/cast_parse_double.cuh"
 #include "kernels/cast_format.cuh"
 #include "kernels/cast_decimal.cuh"
+#include "kernels/cast_parse_temporal.cuh"
 
 extern "C" unsigned b2a_test_varchar_to_bigint(const char *s, size_t n, long long *out) {
 	int64_t v = 0;
@@ -87,4 +88,18 @@ extern "C" unsigned long long b2a_test_decimal_to_real(unsigned long long low, l
 	uint64_t b;
 	memcpy(&b, &d, sizeof(b));
 	return b;
+}
+
+// kind 0: VARCHAR -> DATE (days), 1: VARCHAR -> TIMESTAMP (microseconds); rc as castt::Result
+extern "C" unsigned b2a_test_parse_temporal(int kind, const char *s, size_t n, long long *out) {
+	if (kind == 0) {
+		int32_t d = 0;
+		const uint32_t rc = b2a::castt::varchar_to_date(s, n, &d);
+		*out = d;
+		return rc;
+	}
+	int64_t t = 0;
+	const uint32_t rc = b2a::castt::varchar_to_timestamp(s, n, &t);
+	*out = t;
+	return rc;
 }

@@ -574,3 +574,126 @@ def test_decimal_to_integer_and_real_to_decimal_equal_the_reference(dec):
             assert not bad, f"{'FLOAT' if as_float else 'DOUBLE'} -> DECIMAL({w},{s}): {len(bad)} of {len(arr)} differ, first {bad[:6]}"
             n += len(arr)
     assert n > 30000
+
+
+# ---- VARCHAR -> DATE / TIMESTAMP (src/kernels/cast_parse_temporal.cuh) ---------------------------------------------------------
+
+@pytest.fixture(scope="module")
+def temporal(parse_double):
+    lib = ctypes.CDLL(os.path.join(ROOT, "tests", "native", "libcast_parse_host.so"))
+    lib.b2a_test_parse_temporal.argtypes = [ctypes.c_int, ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(ctypes.c_longlong)]
+    lib.b2a_test_parse_temporal.restype = ctypes.c_uint
+
+    def f(kind: int, s: str):
+        b = s.encode()
+        out = ctypes.c_longlong(0)
+        rc = lib.b2a_test_parse_temporal(kind, b, len(b), ctypes.byref(out))
+        return None if rc else int(out.value)
+    return f
+
+
+HAND_DATE = """2020-01-01|2020-1-1|2020/01/01|2020\\01\\01|2020 01 01|2020-01/01|2020-02-29|2021-02-29|2000-02-29|1900-02-29|2020-13-01
+2020-00-10|2020-01-00|2020-01-32|2020-04-31|0001-01-01|0000-01-01|-0001-01-01|0001-01-01 (BC)|0000-01-01 (BC)|-0001-01-01 (BC)
+0044-03-15 (bc)|0044-03-15 (Bc)|0044-03-15(BC)|0044-03-15  (BC)|1-1-1|12-1-1|99999-12-31|5881580-07-10|5881580-07-11|5881581-01-01
+-5877641-06-25|-5877641-06-24|5877642-06-25 (BC)|5877642-06-24 (BC)|100000000-01-01|1000000000-01-01|99999999-01-01
+infinity|-infinity|Infinity|INFINITY|epoch|-epoch|EPOCH|infinit|infinityx|infinity |  infinity  |epoch x|+infinity
+ 2020-01-01|2020-01-01 |2020-01-01abc|2020-01-011|2020-01-01 12:00:00|2020-01-01T12|2020-01-1x|2020-01|2020|2020-|2020-01-|-|
+20200101|2020-0101|2020.01.01|2020-01-01 (BC) x|2020-01-01 (BC)1|abc|12:00:00|+2020-01-01|--2020-01-01|2020--01-01|1970-01-01
+1969-12-31|2038-01-19|9999-12-31|1582-10-10|0100-03-01|0400-02-29|0300-02-29|-0400-02-29|-0399-02-29|\t2020-01-01\t""".replace("\n", "|").split("|")
+
+HAND_TS = """2020-01-01 12:34:56|2020-01-01T12:34:56|2020-01-01 12:34:56.789|2020-01-01 12:34:56.123456|2020-01-01 12:34:56.1234567
+2020-01-01 12:34:56.|2020-01-01 12:34|2020-01-01 12:|2020-01-01 12|2020-01-01 1:2:3|2020-01-01 12:3|2020-01-01 12:34:5|2020-01-01 12:60:00
+2020-01-01 12:00:60|2020-01-01 24:00:00|2020-01-01 24:00:00.000001|2020-01-01 25:00:00|2020-01-01 23:59:59.999999|2020-01-01
+2020-01-01 |2020-01-01T|2020-01-01  12:00:00|2020-01-01 12:00:00 |2020-01-01 12:00:00  |2020-01-01 12:00:00Z|2020-01-01 12:00:00z
+2020-01-01 12:00:00 Z|2020-01-01 12:00:00Z |2020-01-01 12:00:00+01|2020-01-01 12:00:00-01|2020-01-01 12:00:00+01:30|2020-01-01 12:00:00+0130
+2020-01-01 12:00:00+01:30:15|2020-01-01 12:00:00+013015|2020-01-01 12:00:00+1|2020-01-01 12:00:00+01:|2020-01-01 12:00:00+01:3
+2020-01-01 12:00:00+01:30:|2020-01-01 12:00:00+01:30:1|2020-01-01 12:00:00+99:59:59|2020-01-01 12:00:00-99:59:59|2020-01-01 12:00:00 +01
+2020-01-01 12:00:00 UTC|2020-01-01 12:00:00 utc|2020-01-01 12:00:00 Utc |2020-01-01 12:00:00UTC|2020-01-01 12:00:00 UTC x
+2020-01-01 12:00:00 Europe/Amsterdam|2020-01-01 12:00:00 GMT|2020-01-01 12:00:00 UT|2020-01-01 12:00:00 UTC+1|2020-01-01 12:00:00 x y
+2020-01-01 12:00:00+01 UTC|2020-01-01 12:00:00Z UTC|2020-01-01 12:00:00abc|2020-01-01abc|2020-01-01 abc|2020-01-01 (BC) 12:00:00
+0044-03-15 (BC) 12:00:00|infinity|-infinity|epoch|infinity 12:00:00|epoch 12:00:00|294247-01-10 04:00:54.775806|294247-01-10 04:00:54.775807
+294247-01-10 04:00:54.775808|294247-01-11 00:00:00|290309-12-22 (BC) 00:00:00|290309-12-21 (BC) 23:59:59|290309-12-22 (BC) 00:00:00+01
+294247-01-10 04:00:54.775806-00:00:01|1970-01-01 00:00:00|1969-12-31 23:59:59.999999|1970-01-01 00:00:00.000001|2020-01-01 000000012:00:00
+2020-01-01 0000000012:00:00|2020-01-01 999999999:00:00|2020-01-01 12.5|2020-01-01 12:00:00.5Z|2020-01-01 12:00:00.5+02|12:00:00|
+2020/01/01 12:00:00|2020 01 01 12:00:00| 2020-01-01 12:00:00|2020-01-01\t12:00:00|2020-01-01 12:00:00\t|5881580-07-10 00:00:00""".replace("\n", "|").split("|")
+
+
+def _reference_temporal(strings, sql_type, tag):
+    import pyarrow as pa
+    out = []
+    for i in range(0, len(strings), 2000):
+        part = strings[i:i + 2000]
+        R.register(f"t_tmp_{tag}_{i}", pa.table({"i": pa.array(range(len(part)), pa.int64()), "s": pa.array(part, pa.string())}))
+        col = _export_column(f"SELECT i, TRY_CAST(s AS {sql_type}) AS r FROM t_tmp_{tag}_{i}")
+        ints = col.cast(pa.int32() if sql_type == "DATE" else pa.int64())
+        out += ints.to_pylist()
+    return out
+
+
+def temporal_strings(rng, n):
+    """(date strings, timestamp strings): the hand-written edge cases, well-formed random values over the whole range, and
+    random mutations of well-formed ones"""
+    dates = list(HAND_DATE)
+    for _ in range(n):
+        y = int(rng.integers(-5877700, 5881700)) if rng.random() < 0.3 else int(rng.integers(-100, 3000))
+        m, d = int(rng.integers(0, 14)), int(rng.integers(0, 33))
+        sep = "-/ \\"[int(rng.integers(0, 4))] if rng.random() < 0.3 else "-"
+        sep = "\\" if sep == "\\" else sep
+        text = (("%04d" % y) if rng.random() < 0.8 else str(y)) + sep + (("%02d" % m) if rng.random() < 0.8 else str(m)) + sep + \
+               (("%02d" % d) if rng.random() < 0.8 else str(d))
+        if rng.random() < 0.1:
+            text += " (BC)"
+        dates.append(text)
+    stamps = list(HAND_TS)
+    for _ in range(n):
+        base = dates[int(rng.integers(len(HAND_DATE), len(dates)))] if rng.random() < 0.3 else "%04d-%02d-%02d" % (
+            int(rng.integers(1, 9999)), int(rng.integers(1, 13)), int(rng.integers(1, 29)))
+        h, mi, s = int(rng.integers(0, 26)), int(rng.integers(0, 62)), int(rng.integers(0, 62))
+        t = "%02d:%02d:%02d" % (h, mi, s)
+        if rng.random() < 0.5:
+            t += "." + "".join(str(x) for x in rng.integers(0, 10, int(rng.integers(0, 9))))
+        r = rng.random()
+        suffix = "" if r < 0.5 else "Z" if r < 0.6 else "%+03d" % int(rng.integers(-15, 16)) if r < 0.75 else \
+            "%+03d:%02d" % (int(rng.integers(-15, 16)), int(rng.integers(0, 60))) if r < 0.85 else " UTC" if r < 0.92 else " PST"
+        stamps.append(base + (" " if rng.random() < 0.8 else "T") + t + suffix)
+    alphabet = "0123456789-:/ .TZ+()BCbcutUe"
+    for pool in (dates, stamps):
+        for _ in range(n // 2):
+            s = list(pool[int(rng.integers(0, len(pool)))])
+            for _ in range(int(rng.integers(1, 3))):
+                k = int(rng.integers(0, len(s) + 1))
+                op = rng.random()
+                c = alphabet[int(rng.integers(0, len(alphabet)))]
+                if op < 0.4 and s:
+                    s[min(k, len(s) - 1)] = c
+                elif op < 0.7:
+                    s.insert(k, c)
+                elif s:
+                    del s[min(k, len(s) - 1)]
+            pool.append("".join(s))
+    return dates, stamps
+
+
+@needs_ref
+def test_varchar_to_date_and_timestamp_equal_the_reference(temporal):
+    rng = np.random.default_rng(31)
+    dates, stamps = temporal_strings(rng, 4000)
+    for kind, sql_type, strings in ((0, "DATE", dates + stamps[:3000]), (1, "TIMESTAMP", stamps + dates[:3000])):
+        want = _reference_temporal(strings, sql_type, sql_type.lower())
+        got = [temporal(kind, s) for s in strings]
+        bad = [(s, w, g) for s, w, g in zip(strings, want, got) if w != g]
+        assert not bad, f"{sql_type}: {len(bad)} of {len(strings)} differ, first {bad[:10]}"
+        assert sum(w is not None for w in want) > 2000 and sum(w is None for w in want) > 1000, sql_type
+
+
+def test_temporal_parse_golden_fixture(temporal):
+    """tests/golden/cast_temporal.json (the reference's results, tools/gen_cast_temporal_golden.py) against the CPU build of the
+    device header: runs where oracle/_ref is absent, and is what the GPU test of the kernel compares with"""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "cast_temporal.json")) as f:
+        doc = json.load(f)
+    for kind, sql_type in ((0, "DATE"), (1, "TIMESTAMP")):
+        case = doc[sql_type]
+        assert len(case["strings"]) > 1000
+        for s, want in zip(case["strings"], case["result"]):
+            assert temporal(kind, s) == want, (sql_type, s)

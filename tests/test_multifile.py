@@ -478,6 +478,43 @@ def test_casts_into_and_out_of_decimal_equal_the_reference(b2a, cuda_device, tmp
 
 
 @pytest.mark.gpu
+def test_varchar_to_date_and_timestamp_equal_the_reference(b2a, cuda_device, tmp_path):
+    """a DATE / TIMESTAMP column in the first file, text in the second: the device parsers (kernels/cast_parse_temporal.cuh)
+    against the REFERENCE's TRY_CAST (tests/golden/cast_temporal.json, tools/gen_cast_temporal_golden.py): BC years, the
+    separators, infinity / epoch, UTC offsets, the limits of both ranges; a string the reference refuses fails the scan"""
+    import json
+    with open(os.path.join(os.path.dirname(__file__), "golden", "cast_temporal.json")) as fh:
+        doc = json.load(fh)
+    for sql_type, pa_type, np_type in (("DATE", pa.date32(), np.int32), ("TIMESTAMP", pa.timestamp("us"), np.int64)):
+        case = doc[sql_type]
+        first = str(tmp_path / f"first_{sql_type}.arrows")
+        _write(first, pa.table({"v": pa.array([0], pa.int32() if sql_type == "DATE" else pa.int64()).cast(pa_type)}))
+        good = [(s, w) for s, w in zip(case["strings"], case["result"]) if w is not None]
+        bad = [s for s, w in zip(case["strings"], case["result"]) if w is None]
+        assert len(good) > 400 and len(bad) > 300
+        _write(str(tmp_path / f"good_{sql_type}.arrows"), pa.table({"v": pa.array([s for s, _ in good] + [None], pa.string())}), batch=300)
+        mfs = b2a.read_arrow([first, str(tmp_path / f"good_{sql_type}.arrows")])
+        assert mfs.types == [sql_type]
+        got = []
+        for f in mfs.files:
+            f.scan()
+            for b in range(f.reader.num_batches):
+                v = f.column(b, 0)
+                vals = np.ascontiguousarray(v.data).view(np_type).ravel().tolist()
+                got += [int(x) if ok else None for x, ok in zip(vals, v.valid)]
+        assert got[0] == 0 and got[-1] is None and len(got) == len(good) + 2
+        wrong = [(s, w, g) for (s, w), g in zip(good, got[1:-1]) if w != g]
+        assert not wrong, f"{sql_type}: {len(wrong)} of {len(good)} differ, first {wrong[:6]}"
+        for k, s in enumerate(bad[:: max(1, len(bad) // 6)][:6]):
+            _write(str(tmp_path / f"bad_{sql_type}_{k}.arrows"), pa.table({"v": pa.array([good[0][0], s], pa.string())}))
+            with pytest.raises(b2a.B2AError, match="could not convert a string|out of range"):
+                for f in b2a.read_arrow([first, str(tmp_path / f"bad_{sql_type}_{k}.arrows")]).files:
+                    f.scan()
+                    [f.column(b, 0) for b in range(f.reader.num_batches)]
+                raise AssertionError(f"{sql_type}: {s!r} was accepted")
+
+
+@pytest.mark.gpu
 def test_lineitem_glob_dictionary_union_by_name(b2a, cuda_device, tmp_path):
     """BASELINE config 4 in small: glob of lineitem files, dictionary-encoded strings, two schema variants under
     union_by_name (column order + INTEGER l_linenumber cast to BIGINT on the device); rows equal pyarrow's reading."""
