@@ -348,7 +348,8 @@ bool CastSupported(const MfType &from, const MfType &to) {
 	if (fa && (b == B2A_T_DOUBLE || b == B2A_T_FLOAT || IsInt(b) || b == B2A_T_VARCHAR)) {
 		return true;
 	}
-	if (a == B2A_T_VARCHAR && (b == B2A_T_DOUBLE || b == B2A_T_BIGINT || b == B2A_T_DATE || b == B2A_T_TIMESTAMP)) {
+	if (a == B2A_T_VARCHAR && (b == B2A_T_DOUBLE || b == B2A_T_BIGINT || b == B2A_T_DATE || b == B2A_T_TIMESTAMP ||
+	                           b == B2A_T_DECIMAL)) {
 		return true;
 	}
 	if (a == B2A_T_DATE && b == B2A_T_TIMESTAMP) {

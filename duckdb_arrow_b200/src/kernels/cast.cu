@@ -16,6 +16,7 @@
 //                           half away from zero (IntegerCastLoop: decimals are rounded)
 //   DATE -> TIMESTAMP       days * 86 400 000 000 us, +-infinity preserved
 //   VARCHAR -> DATE / TIMESTAMP   Date::TryConvertDate / Timestamp::TryConvertTimestamp, restated in cast_parse_temporal.cuh
+//   VARCHAR -> DECIMAL      TryDecimalStringCast, restated in cast_parse_decimal.cuh
 //   BOOLEAN / DATE / TIME / TIMESTAMP / DECIMAL / HUGEINT -> VARCHAR   StringCast::Operation, restated in cast_format.cuh
 //   integer / FLOAT / DOUBLE -> DECIMAL, integer -> HUGEINT, DECIMAL -> DECIMAL / integer / DOUBLE / FLOAT   cast_decimal.cuh
 #include "cast.cuh"
@@ -24,6 +25,7 @@
 #include "cast_format.cuh"
 #include "cast_decimal.cuh"
 #include "cast_parse_temporal.cuh"
+#include "cast_parse_decimal.cuh"
 
 #include "b2arrow.h"
 
@@ -666,6 +668,13 @@ __global__ void __launch_bounds__(256, 4) b2a_cast_kernel(CastLaunch l) {
 						continue;
 					}
 					*reinterpret_cast<double *>(dst) = d;
+				} else if (to == B2A_T_DECIMAL) {
+					__int128 r;
+					if (!castq::varchar_to_decimal(s, len, t.dst_decimal_width, t.dst_decimal_scale, &r)) {
+						raise(l.d_err, B2A_CAST_DEV_PARSE);
+						continue;
+					}
+					store_i128(dst, dw, r);
 				} else if (to == B2A_T_DATE) {
 					int32_t d = 0;
 					const uint32_t e = castt::varchar_to_date(s, len, &d);

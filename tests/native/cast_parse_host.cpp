@@ -6,6 +6,7 @@
 #include "kernels/cast_format.cuh"
 #include "kernels/cast_decimal.cuh"
 #include "kernels/cast_parse_temporal.cuh"
+#include "kernels/cast_parse_decimal.cuh"
 
 extern "C" unsigned b2a_test_varchar_to_bigint(const char *s, size_t n, long long *out) {
 	int64_t v = 0;
@@ -102,4 +103,14 @@ extern "C" unsigned b2a_test_parse_temporal(int kind, const char *s, size_t n, l
 	const uint32_t rc = b2a::castt::varchar_to_timestamp(s, n, &t);
 	*out = t;
 	return rc;
+}
+
+// VARCHAR -> DECIMAL(width, scale): 1 when the cast succeeds
+extern "C" int b2a_test_parse_decimal(const char *s, size_t n, unsigned width, unsigned scale, unsigned long long *out_low,
+                                      long long *out_high) {
+	__int128 r = 0;
+	const bool ok = b2a::castq::varchar_to_decimal(s, n, width, scale, &r);
+	*out_low = static_cast<unsigned long long>(r);
+	*out_high = static_cast<long long>(r >> 64);
+	return ok ? 1 : 0;
 }

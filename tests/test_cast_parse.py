@@ -697,3 +697,77 @@ def test_temporal_parse_golden_fixture(temporal):
         assert len(case["strings"]) > 1000
         for s, want in zip(case["strings"], case["result"]):
             assert temporal(kind, s) == want, (sql_type, s)
+
+
+# ---- VARCHAR -> DECIMAL (src/kernels/cast_parse_decimal.cuh) --------------------------------------------------------------------
+
+@pytest.fixture(scope="module")
+def parse_decimal(parse_double):
+    lib = ctypes.CDLL(os.path.join(ROOT, "tests", "native", "libcast_parse_host.so"))
+    lib.b2a_test_parse_decimal.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_uint, ctypes.c_uint,
+                                           ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_longlong)]
+    lib.b2a_test_parse_decimal.restype = ctypes.c_int
+
+    def f(s: str, width: int, scale: int):
+        b = s.encode()
+        lo, hi = ctypes.c_ulonglong(0), ctypes.c_longlong(0)
+        ok = lib.b2a_test_parse_decimal(b, len(b), width, scale, ctypes.byref(lo), ctypes.byref(hi))
+        return _signed128(hi.value << 64 | lo.value) if ok else None
+    return f
+
+
+DECIMAL_TARGETS = [(4, 0), (4, 2), (4, 4), (9, 0), (9, 3), (9, 9), (15, 2), (18, 0), (18, 6), (18, 18), (19, 0), (22, 4), (38, 0),
+                   (38, 10), (38, 38)]
+
+
+def decimal_strings(rng, n):
+    strings = [s for s in HAND + HAND_DOUBLE if "\\" not in s]
+    strings += [" " + s for s in HAND[:30]] + [s + " " for s in HAND[:30]]
+    strings += ["9.995", "9.994", "-9.995", "99.99", "99.995", "0.005", "0.0049", "-0.005", ".5", "5.", "-.5", "0.5e1", "5e-1", "55e-1",
+                "45e-1", "-45e-1", "1.5e0", "12345e-3", "12355e-3", "1e2", "1.25e1", "1.255e2", "1.2345678901234567890123456789e5",
+                "0.00000000000000000000000000000000000001", "99999999999999999999999999999999999999", "1e37", "1e38", "1e-38", "1e-39",
+                "0.0e100", "0e100", "00000000000000000000000000000000000000000001", "0000.0001", "1_000.5", "1_0e1", "1e1_0", "1.0_5",
+                "123456789012345678.5", "0.1234567890123456789", "9999.5", "9999.4", "999.95", "99.9999999999", "1.00000000000000000000001",
+                "+1.5", "+.5", "+-1", "1e+2", "1E2", "1e", "1e-", "e1", ".e1", "1.e1", "12e-1", "15e-1", "25e-1", "1.5e-1", "0.15e1"]
+    for _ in range(n):
+        nd = int(rng.integers(1, 40)) if rng.random() < 0.2 else int(rng.integers(1, 12))
+        digits = "".join(str(d) for d in rng.integers(0, 10, nd))
+        cut = int(rng.integers(0, nd + 1))
+        body = digits[:cut] + ("." + digits[cut:] if cut < nd or rng.random() < 0.1 else "")
+        r = rng.random()
+        exp = "" if r < 0.6 else "e" + str(int(rng.integers(-8, 9))) if r < 0.95 else "e" + str(int(rng.integers(-45, 45)))
+        strings.append(("-" if rng.random() < 0.3 else "") + body + exp)
+    return list(dict.fromkeys(strings))
+
+
+def _reference_decimal(strings, width, scale, tag):
+    import pyarrow as pa
+    R.register(f"t_pd_{tag}", pa.table({"i": pa.array(range(len(strings)), pa.int64()), "s": pa.array(strings, pa.string())}))
+    return _unscaled(_export_column(f"SELECT i, TRY_CAST(s AS DECIMAL({width},{scale})) AS r FROM t_pd_{tag}"))
+
+
+@needs_ref
+def test_varchar_to_decimal_equals_the_reference(parse_decimal):
+    rng = np.random.default_rng(41)
+    strings = decimal_strings(rng, 2500)
+    n_ok = 0
+    for k, (w, s) in enumerate(DECIMAL_TARGETS):
+        want = _reference_decimal(strings, w, s, f"pin{k}")
+        got = [parse_decimal(t, w, s) for t in strings]
+        bad = [(t, x, g) for t, x, g in zip(strings, want, got) if x != g]
+        assert not bad, f"DECIMAL({w},{s}): {len(bad)} of {len(strings)} differ, first {bad[:8]}"
+        n_ok += sum(x is not None for x in want)
+    assert n_ok > 15000
+
+
+def test_varchar_to_decimal_golden_fixture(parse_decimal):
+    """tests/golden/cast_varchar_decimal.json (the reference's results, tools/gen_cast_varchar_decimal_golden.py) against the CPU
+    build of the device header: runs where oracle/_ref is absent, and is what the GPU test of the kernel compares with"""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "cast_varchar_decimal.json")) as f:
+        doc = json.load(f)
+    assert len(doc["strings"]) > 800 and len(doc["targets"]) == 7
+    for target, results in doc["targets"].items():
+        w, s = (int(x) for x in target[8:-1].split(","))
+        for text, want in zip(doc["strings"], results):
+            assert parse_decimal(text, w, s) == (None if want is None else int(want)), (target, text)

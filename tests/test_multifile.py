@@ -515,6 +515,47 @@ def test_varchar_to_date_and_timestamp_equal_the_reference(b2a, cuda_device, tmp
 
 
 @pytest.mark.gpu
+def test_varchar_to_decimal_equals_the_reference(b2a, cuda_device, tmp_path):
+    """a DECIMAL(w,s) column in the first file, text in the second: the device parser (kernels/cast_parse_decimal.cuh) against
+    the REFERENCE's TRY_CAST (tests/golden/cast_varchar_decimal.json): every physical width, rounding on the first digit past
+    the scale, exponents, the width limit; a string the reference refuses fails the scan"""
+    import json
+    from test_cast_parse import arrow_array_of
+    with open(os.path.join(os.path.dirname(__file__), "golden", "cast_varchar_decimal.json")) as fh:
+        doc = json.load(fh)
+    for k, (target, results) in enumerate(doc["targets"].items()):
+        first = str(tmp_path / f"first{k}.arrows")
+        _write(first, pa.table({"v": arrow_array_of(target, [1])}))
+        good = [(s, int(w)) for s, w in zip(doc["strings"], results) if w is not None]
+        bad = [s for s, w in zip(doc["strings"], results) if w is None]
+        _write(str(tmp_path / f"good{k}.arrows"), pa.table({"v": pa.array([s for s, _ in good] + [None], pa.string())}), batch=250)
+        mfs = b2a.read_arrow([first, str(tmp_path / f"good{k}.arrows")])
+        assert mfs.types == [target]
+        got = []
+        for f in mfs.files:
+            f.scan()
+            for b in range(f.reader.num_batches):
+                v = f.column(b, 0)
+                d = np.ascontiguousarray(v.data)
+                if d.shape[1] == 16:
+                    w2 = d.view(np.uint64).reshape(-1, 2)
+                    vals = [(int(hi) << 64 | int(lo)) - ((1 << 128) if int(hi) >> 63 else 0) for lo, hi in w2]
+                else:
+                    vals = d.view({2: np.int16, 4: np.int32, 8: np.int64}[d.shape[1]]).ravel().tolist()
+                got += [int(x) if ok else None for x, ok in zip(vals, v.valid)]
+        assert got[-1] is None and len(got) == len(good) + 2
+        wrong = [(s, w, g) for (s, w), g in zip(good, got[1:-1]) if w != g]
+        assert not wrong, f"{target}: {len(wrong)} of {len(good)} differ, first {wrong[:6]}"
+        for j, s in enumerate(bad[:: max(1, len(bad) // 3)][:3]):
+            _write(str(tmp_path / f"bad{k}_{j}.arrows"), pa.table({"v": pa.array([good[0][0], s], pa.string())}))
+            with pytest.raises(b2a.B2AError, match="could not convert a string"):
+                for f in b2a.read_arrow([first, str(tmp_path / f"bad{k}_{j}.arrows")]).files:
+                    f.scan()
+                    [f.column(b, 0) for b in range(f.reader.num_batches)]
+                raise AssertionError(f"{target}: {s!r} was accepted")
+
+
+@pytest.mark.gpu
 def test_lineitem_glob_dictionary_union_by_name(b2a, cuda_device, tmp_path):
     """BASELINE config 4 in small: glob of lineitem files, dictionary-encoded strings, two schema variants under
     union_by_name (column order + INTEGER l_linenumber cast to BIGINT on the device); rows equal pyarrow's reading."""
