@@ -281,3 +281,17 @@ def test_reference_rejects_a_union_tag_out_of_range_like_the_oracle():
     u = pa.UnionArray.from_sparse(pa.array([0, 1, 0], pa.int8()), [a, a], ["a", "b"])
     bad = pa.UnionArray.from_buffers(u.type, 3, [None, pa.py_buffer(np.array([0, 5, 0], np.int8))], children=[a, a])
     assert check(bad, "bad tag") == "error"
+
+
+def test_oracle_equals_reference_on_unions_and_list_views_below_a_list():
+    """Shapes the product refuses at bind time (a union or a list view below a list) — the restatement takes
+    them and agrees with the compiled reference, so the refusal is a limit of the device planner, not of the checker."""
+    rng = np.random.default_rng(5)
+    m = 900
+    u = pa.UnionArray.from_sparse(pa.array(rng.integers(0, 2, m * 3).astype(np.int8)),
+                                  [pa.array(range(m * 3), pa.int64()), pa.array([str(i) for i in range(m * 3)])], ["i", "s"])
+    offsets = pa.array(np.arange(0, m * 3 + 1, 3, dtype=np.int32))
+    assert check(pa.ListArray.from_arrays(offsets, u), "list<union>") == "ok"
+    lv = pa.ListViewArray.from_arrays(pa.array(np.arange(m * 3, dtype=np.int32)), pa.array(np.full(m * 3, 1, np.int32)),
+                                      pa.array(np.arange(m * 3 + 5, dtype=np.int64)))
+    assert check(pa.ListArray.from_arrays(offsets, lv), "list<list_view>") == "ok"
