@@ -325,6 +325,12 @@ void slab_append(RSlab *s, Vector &v, idx_t count, idx_t dict_len_hint) {
 			s->dict = slab_new(t);
 			// dictionary values + the NULL slot SetSelectionVector points NULL indices at (arrow_conversion.cpp:1227-1348)
 			idx_t n = dict_len_hint;
+			if (n == 0) {
+				// a dictionary below a list / struct: DuckDB's dictionary Vector carries no length, take what sel can reach
+				for (idx_t i = 0; i < count; i++) {
+					n = MaxValue<idx_t>(n, sel.get_index(i) + 1);
+				}
+			}
 			auto &mask = FlatVector::Validity(child);
 			bool null_slot = mask.GetData() != nullptr && mask.Capacity() > dict_len_hint;
 			slab_append(s->dict, child, n, 0);

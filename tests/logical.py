@@ -61,6 +61,8 @@ def slab_to_py(slab, t: pa.DataType) -> list:
     t = _storage_type(t)
     n = slab.rows
     if pa.types.is_dictionary(t):
+        if slab.dict is None:  # a dictionary column that arrived flattened (the reference does that to MAP values)
+            return slab_to_py(slab, t.value_type)
         vals = slab_to_py(slab.dict, t.value_type)
         return [vals[int(slab.sel[i])] if int(slab.sel[i]) < len(vals) else None for i in range(n)]
     if pa.types.is_null(t):

@@ -295,3 +295,47 @@ def test_oracle_equals_reference_on_unions_and_list_views_below_a_list():
     lv = pa.ListViewArray.from_arrays(pa.array(np.arange(m * 3, dtype=np.int32)), pa.array(np.full(m * 3, 1, np.int32)),
                                       pa.array(np.arange(m * 3 + 5, dtype=np.int64)))
     assert check(pa.ListArray.from_arrays(offsets, lv), "list<list_view>") == "ok"
+
+
+def _dictionary_of(k, rng):
+    return pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 2, k).astype(np.int16), mask=rng.random(k) < 0.3),
+                                          pa.array([10, 20], pa.int64()))
+
+
+def test_oracle_equals_reference_on_dictionaries_below_struct_and_list():
+    """dictionary-encoded children of STRUCT / LIST / LIST<STRUCT>: same selection vectors, same dictionary (+ NULL slot)"""
+    rng = np.random.default_rng(0)
+    n = 3000
+    offs = np.concatenate([[0], np.cumsum(rng.integers(0, 3, n))]).astype(np.int32)
+    m = int(offs[-1])
+    assert check(pa.StructArray.from_arrays([_dictionary_of(n, rng), pa.array(range(n))], ["d", "i"]), "struct<dict>") == "ok"
+    assert check(pa.ListArray.from_arrays(pa.array(offs[:1001]), _dictionary_of(int(offs[1000]), rng)), "list<dict>") == "ok"
+    inner = pa.StructArray.from_arrays([_dictionary_of(m, rng), pa.array(range(m))], ["d", "i"])
+    assert check(pa.ListArray.from_arrays(pa.array(offs[:1001]), inner.slice(0, int(offs[1000]))), "list<struct<dict>>") == "ok"
+
+
+def test_reference_flattens_dictionary_values_of_a_map():
+    """MAP<VARCHAR, dictionary>: the reference hands back a FLAT value vector, the restatement (and the device path) a
+    dictionary vector over the decoded dictionary — same values row by row, a representation difference only"""
+    from logical import slab_to_py
+    rng = np.random.default_rng(1)
+    n = 500
+    offs = np.concatenate([[0], np.cumsum(rng.integers(0, 3, n))]).astype(np.int32)
+    m = int(offs[-1])
+    arr = pa.MapArray.from_arrays(pa.array(offs), pa.array([f"k{i}" for i in range(m)]), _dictionary_of(m, rng))
+    ref, ora = R.scan_column(arr), O.scan_column(arr)
+    assert ref.children[0].children[1].sel is None and ora.children[0].children[1].sel is not None
+    assert slab_to_py(ref, arr.type) == slab_to_py(ora, arr.type)
+
+
+def test_reference_types_a_dictionary_below_a_fixed_size_list_by_its_indices():
+    """fixed_size_list<dictionary<int16, string>>[3]: ArrowType::GetDuckType(use_dictionary = true) rebuilds STRUCT / LIST /
+    MAP / UNION around their dictionary children but has no ARRAY case (arrow_duck_schema.cpp:313-365), so the reference
+    declares SMALLINT[3] — the index type — and reads the dictionary's strings as 16-bit integers.  The restatement and the
+    product give VARCHAR[3] with the decoded dictionary; pinned here so that the difference is a known one."""
+    rng = np.random.default_rng(2)
+    d = pa.DictionaryArray.from_arrays(pa.array(rng.integers(0, 2, 6).astype(np.int16)), pa.array(["a", "b"]))
+    arr = pa.FixedSizeListArray.from_arrays(d, 3)
+    ref, ora = R.scan_column(arr), O.scan_column(arr)
+    assert ref.children[0].type_id == O.T["SMALLINT"] and ref.children[0].dict.width == 2
+    assert ora.children[0].type_id == O.T["VARCHAR"] and ora.children[0].dict.width == 16
