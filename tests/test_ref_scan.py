@@ -339,3 +339,20 @@ def test_reference_types_a_dictionary_below_a_fixed_size_list_by_its_indices():
     ref, ora = R.scan_column(arr), O.scan_column(arr)
     assert ref.children[0].type_id == O.T["SMALLINT"] and ref.children[0].dict.width == 2
     assert ora.children[0].type_id == O.T["VARCHAR"] and ora.children[0].dict.width == 16
+
+
+@pytest.mark.parametrize("seed0", [7000, 7040, 7080])
+def test_oracle_equals_reference_on_random_nested_arrays(seed0):
+    """a slice of the differential fuzz behind DESIGN section 7 (tests/fuzz_arrays.py; ~2 500 arrays were run by hand): random
+    nested types, NULL rates, lengths around the 2 048-row chunk and ArrowArray.offset — identical vectors, or the same error"""
+    import fuzz_arrays
+    n_ok = 0
+    for seed in range(seed0, seed0 + 40):
+        rng = np.random.default_rng(seed)
+        n = int(rng.choice([1, 63, 64, 65, 100, 2047, 2048, 2049, 3000, 5000]))
+        arr = fuzz_arrays.gen(rng, n)
+        off = int(rng.choice([0, 0, 1, 7, 64, 2048])) if n > 2100 else int(rng.choice([0, 0, 1]))
+        if off and off < len(arr):
+            arr = arr.slice(off)
+        n_ok += check(arr, f"seed {seed}: {arr.type}") == "ok"
+    assert n_ok >= 38
