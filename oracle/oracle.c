@@ -1128,8 +1128,8 @@ static int ColumnArrowToDuckDBRunEndEncoded(OState *st, OVector *vector, const O
 	default:
 		return fail(st, O_ENOTIMPL, "RunEndEncoded value type not supported yet");
 	}
-	if (values_type->id == O_LIST || values_type->id == O_MAP || values_type->id == O_BLOB ||
-	    values_type->id == O_UHUGEINT || values_type->id == O_UUID) {
+	if (values_type->id == O_LIST || values_type->id == O_MAP || values_type->id == O_UHUGEINT ||
+	    values_type->id == O_UUID) { /* (BLOB is physical VARCHAR: FlattenRunEnds<.., string_t>, :706-711) */
 		return fail(st, O_ENOTIMPL, "RunEndEncoded value type not supported yet");
 	}
 	FlattenRunEnds(vector, st->ree_runs[slot], st->ree_values[slot], run_width, compressed_size, scan_offset, size);

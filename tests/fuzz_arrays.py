@@ -74,3 +74,32 @@ def gen(rng, n, depth=0, allow_null=True):
         return pa.DictionaryArray.from_arrays(idx, dv)
     raise AssertionError(kind)
 
+
+
+# ---- random Arrow TYPES over the whole zoo the type mapping knows (and a few it must refuse), for the schema-level comparison
+LEAVES=[pa.int8(),pa.int16(),pa.int32(),pa.int64(),pa.uint8(),pa.uint16(),pa.uint32(),pa.uint64(),pa.float16(),pa.float32(),pa.float64(),
+ pa.bool_(),pa.string(),pa.large_string(),pa.string_view(),pa.binary(),pa.large_binary(),pa.binary_view(),pa.binary(7),pa.date32(),pa.date64(),
+ pa.time32("s"),pa.time32("ms"),pa.time64("us"),pa.time64("ns"),pa.timestamp("s"),pa.timestamp("ms"),pa.timestamp("us"),pa.timestamp("ns"),
+ pa.timestamp("us",tz="UTC"),pa.timestamp("ns",tz="Europe/Amsterdam"),pa.duration("s"),pa.duration("ms"),pa.duration("us"),pa.duration("ns"),
+ pa.month_day_nano_interval(),pa.decimal128(4,1),pa.decimal128(9,2),pa.decimal128(18,3),pa.decimal128(38,10),pa.decimal256(40,3),
+ pa.decimal32(7,2),pa.decimal64(15,2),pa.null(),pa.uuid(),pa.bool8(),pa.json_(),pa.opaque(pa.binary(16),"hugeint","DuckDB"),
+ pa.opaque(pa.binary(16),"uhugeint","DuckDB"),pa.opaque(pa.binary(8),"time_tz","DuckDB"),pa.opaque(pa.binary(),"bit","DuckDB"),
+ pa.opaque(pa.binary(),"varint","DuckDB"),pa.opaque(pa.int32(),"other","Vendor")]
+def random_type(rng, depth=0):
+    if depth<3 and rng.random()<0.45:
+        k=int(rng.integers(0,10))
+        if k==0: return pa.list_(random_type(rng, depth + 1))
+        if k==1: return pa.large_list(random_type(rng, depth + 1))
+        if k==2: return pa.struct([pa.field(nm, random_type(rng, depth + 1)) for nm in ["a","B b","c"][:int(rng.integers(1,4))]])
+        if k==3: return pa.map_(pa.string() if rng.random()<0.7 else pa.int32(), random_type(rng, depth + 1))
+        if k==4: return pa.list_(random_type(rng, depth + 1), int(rng.integers(1,4)))
+        if k==5: return pa.dictionary(pa.int8() if rng.random()<0.5 else pa.uint32(), LEAVES[int(rng.integers(0,30))])
+        if k==6: return pa.list_view(random_type(rng, depth + 1))
+        if k==7: return pa.large_list_view(random_type(rng, depth + 1))
+        if k==8: return pa.run_end_encoded(pa.int32(), LEAVES[int(rng.integers(0,30))])
+        if k==9: return pa.union([pa.field("x", random_type(rng, depth + 1)), pa.field("y", LEAVES[int(rng.integers(0,30))])], mode="sparse")
+    return LEAVES[int(rng.integers(0,len(LEAVES)))]
+def empty_array(t):
+    if isinstance(t, pa.BaseExtensionType):
+        return pa.ExtensionArray.from_storage(t, empty_array(t.storage_type))
+    return pa.array([], t)
